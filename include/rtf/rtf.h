@@ -1,0 +1,297 @@
+/*
+ * rtf.h — C ABI of librtf_b200.so, the B200-native ray-tracing core that sits behind
+ * RayTracerFacility's module façade (layer L3 in SURVEY.md §1).
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the
+ * reference checkout):
+ *   RT.hpp   = include/RayTracerFacility/RayTracer/RayTracer.hpp
+ *   CM.hpp   = include/RayTracerFacility/RayTracer/CUDAModule.hpp
+ *   CM.cpp   = src/RayTracerFacility/CUDAModule.cpp
+ *   RT.cu    = src/RayTracerFacility/RayTracer.cu
+ *   PCS.cpp  = src/RayTracerFacility/PointCloudScanner.cpp
+ *
+ * Conventions: plain pointers and sizes only; every function returns an int status
+ * (RTF_OK == 0, negative on error) and never throws or exits (the reference throws on CUDA
+ * errors and exit(2)s on OptiX errors, Optix7.hpp:10-56); rtf_last_error() returns a
+ * thread-local message.  One host thread drives one context.  All host pointers are plain
+ * (pageable or pinned) memory; `_device` variants take device pointers of the context's GPU.
+ */
+#ifndef RTF_RTF_H
+#define RTF_RTF_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define RTF_API __declspec(dllexport)
+#else
+#define RTF_API __attribute__((visibility("default")))
+#endif
+
+/* ---- status codes -------------------------------------------------------------------- */
+#define RTF_OK 0
+#define RTF_ERR_INVALID (-1)   /* bad argument                                              */
+#define RTF_ERR_CUDA (-2)      /* CUDA runtime error (reference: throw, Optix7.hpp:10-22)   */
+#define RTF_ERR_NOT_READY (-3) /* no acceleration structure yet (reference: RT.cu:248,610,760) */
+#define RTF_ERR_NOT_FOUND (-4) /* unknown handle                                            */
+#define RTF_ERR_LIMIT (-5)     /* internal capacity exceeded (e.g. BVH deeper than the stack) */
+
+/* ---- reference-layout POD records ---------------------------------------------------- */
+
+/* UniEngine::Vertex, 80 B.  Layout inferred from its uses at RT.cu:1163-1173, RDD.hpp:132-161. */
+typedef struct rtf_vertex {
+  float position[3];
+  float position_padding;
+  float normal[3];
+  float normal_padding;
+  float tangent[3];
+  float tangent_padding;
+  float color[4];
+  float tex_coord[2];
+  float tex_coord_padding[2];
+} rtf_vertex;
+
+/* IlluminationSampler<glm::vec3>, RT.hpp:187-211, 268 B, in-out. */
+typedef struct rtf_illum_sampler {
+  rtf_vertex a, b, c;
+  float direction[3]; /* out */
+  float energy[3];    /* out */
+  uint8_t front_face;
+  uint8_t back_face;
+  uint8_t pad_[2];
+} rtf_illum_sampler;
+
+/* HitInfo, HitInfo.hpp:4-11, 76 B. */
+typedef struct rtf_hit_info {
+  float position[3];
+  float normal[3];
+  float tangent[3];
+  float color[4];
+  float tex_coord[2];
+  float data[4];
+} rtf_hit_info;
+
+/* PointCloudSample, RT.hpp:222-232, 112 B, in-out. */
+typedef struct rtf_pc_sample {
+  float direction[3]; /* in  */
+  float start[3];     /* in  */
+  uint64_t handle;    /* out: instance's private-component handle (RT.cu:1859) */
+  uint8_t hit;        /* out */
+  uint8_t pad_[3];
+  rtf_hit_info hit_info; /* out */
+} rtf_pc_sample;
+
+/* EnvironmentalLightingType, RT.hpp:99-101 */
+enum { RTF_ENV_SCENE = 0, RTF_ENV_SKYDOME = 1, RTF_ENV_SINGLE_LIGHT_SOURCE = 2 };
+
+/* EnvironmentProperties, RT.hpp:103-151.  Numeric fields keep the reference order; the
+ * GL cube-map id + cudaTextureObject_t[6] become six optional device pointers to
+ * float4 face images (cube map without GL: SURVEY §8 N2, not wired in this round). */
+typedef struct rtf_env {
+  int32_t lighting_type;
+  float skylight_intensity;
+  float ambient_light_intensity;
+  float light_size;
+  float gamma;
+  float sun_direction[3];
+  float color[3];
+  uint32_t environmental_map_id; /* must be 0 in this round */
+  uint64_t environmental_maps[6];
+  struct {
+    float earth_radius;
+    float atmosphere_radius;
+    float hr;
+    float hm;
+    float g;
+    int32_t num_samples;
+    int32_t num_samples_light;
+  } atmosphere;
+  uint32_t pad_;
+} rtf_env;
+
+/* RayProperties, RT.hpp:153-163 */
+typedef struct rtf_ray_props {
+  int32_t bounces;
+  int32_t samples;
+} rtf_ray_props;
+
+/* MaterialType, Enums.hpp:4-8 */
+enum { RTF_MAT_DEFAULT = 0, RTF_MAT_VERTEX_COLOR = 1, RTF_MAT_COMPRESSED_BTF = 2 };
+
+/* The MaterialProperties fields the path reads (RF.cuh:97-98,122-123,152,170; RDD.hpp:250-264)
+ * + RayTracedMaterial::m_materialType (RT.hpp:248). */
+typedef struct rtf_material {
+  int32_t material_type;
+  float albedo_color[3];
+  float subsurface_color[3];
+  float subsurface_factor;
+  float subsurface_radius[3];
+  float metallic;
+  float roughness;
+  float emission;
+  float transmission;
+  float pad_;
+} rtf_material;
+
+/* OutputType, RT.hpp:26-28 */
+enum { RTF_OUT_COLOR = 0, RTF_OUT_NORMAL = 1, RTF_OUT_ALBEDO = 2, RTF_OUT_DEPTH = 3 };
+
+/* The numeric part of CameraProperties (RT.hpp:30-96).  Frame buffers live in headless
+ * device float4 arrays owned by the camera object (GL texture target: unavailable). */
+typedef struct rtf_camera_props {
+  int32_t accumulate; /* m_accumulate */
+  float fov;          /* m_fov, degrees; halved by Set() like RT.cu:32 */
+  float from[3];
+  float horizontal[3];
+  float vertical[3];
+  float inverse_projection_view[16]; /* column-major glm::mat4 */
+  float max_distance;
+  int32_t output_type;
+  float gamma;
+  int32_t width, height;
+  uint64_t frame_id;
+  int32_t modified;
+  float aperture;
+  float focal_length;
+} rtf_camera_props;
+
+/* Parameters of PointCloudScanner::Scan (PCS.cpp:70-92) so that 10^8-ray scans never
+ * materialise 112 B/ray on the host. */
+typedef struct rtf_scan_grid {
+  float center[3];
+  float left[3];
+  float up[3];
+  float direction[3]; /* normalised scan direction (actualVector) */
+  float size[2];      /* m_size */
+  float distance[2];  /* m_distance */
+} rtf_scan_grid;
+
+/* BRDF model.  RTF_BRDF_REFERENCE = mirror-lobe of BSDF.cuh:6-13 + RF.cuh:152-161. */
+enum { RTF_BRDF_REFERENCE = 0 };
+
+typedef struct rtf_ctx rtf_ctx;
+typedef struct rtf_camera rtf_camera;
+
+/* ---- lifecycle: CudaModule::Init / Terminate (CM.hpp:30-36, CM.cpp:23-36) -------------- */
+RTF_API int rtf_create(int device, rtf_ctx** out);
+RTF_API int rtf_destroy(rtf_ctx* ctx);
+RTF_API const char* rtf_last_error(void);
+RTF_API const char* rtf_version(void);
+/* Use an externally owned CUDA stream (e.g. torch's current stream) for all work. NULL = own stream. */
+RTF_API int rtf_set_stream(rtf_ctx* ctx, void* cuda_stream);
+/* Number of kernel launches issued by the context so far (bench.py's gpu_launches claim). */
+RTF_API uint64_t rtf_launch_count(rtf_ctx* ctx);
+
+/* ---- scene sync: RayTracer::m_geometries / m_materials / m_instances (RT.hpp:361-363),
+ *      filled by RayTracerLayer::UpdateMeshesStorage (RayTracerLayer.cpp:18-346) ----------- */
+/* Copies immediately (the reference borrows host vectors until BuildGAS, RT.hpp:280-292). */
+RTF_API int rtf_set_geometry(rtf_ctx* ctx, uint64_t handle, const void* vertices, size_t n_vertices,
+                             size_t vertex_stride_bytes, const uint32_t* triangles, size_t n_triangles,
+                             uint64_t version);
+RTF_API int rtf_set_material(rtf_ctx* ctx, uint64_t handle, const rtf_material* material);
+RTF_API int rtf_set_instance(rtf_ctx* ctx, uint64_t handle, uint64_t geometry_handle, uint64_t material_handle,
+                             const float transform[16] /* column-major glm::mat4 m_globalTransform */,
+                             uint64_t private_component_handle);
+RTF_API int rtf_remove_geometry(rtf_ctx* ctx, uint64_t handle);
+RTF_API int rtf_remove_material(rtf_ctx* ctx, uint64_t handle);
+RTF_API int rtf_remove_instance(rtf_ctx* ctx, uint64_t handle);
+/* RayTracer::BuildIAS (RT.hpp:386, RT.cu:1618-1715) + BuildGAS (RT.cu:1251-1598):
+ * flatten instances (ascending instance handle) to a world-space triangle soup and build the
+ * LBVH -> 8-wide compressed BVH on the device.  morton_bits: 30 or 63 (0 = 63). */
+RTF_API int rtf_commit(rtf_ctx* ctx, int morton_bits);
+RTF_API int rtf_triangle_count(rtf_ctx* ctx, uint64_t* n_triangles);
+
+/* ---- illumination: CudaModule::EstimateIlluminationRayTracing (CM.hpp:38-41, CM.cpp:39-50)
+ *      -> RayTracer::EstimateIllumination (RT.cu:605-756) -> __raygen__IE (IE.cu:30-129) ---- */
+RTF_API int rtf_estimate_illumination(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* ray_props,
+                                      rtf_illum_sampler* probes /* host, in-out */, size_t n, uint32_t seed,
+                                      float push_normal_distance);
+/* Scale variant: the probes are the committed world-space triangles themselves
+ * (TriangleIlluminationEstimator::PrepareLightProbeGroup, TriangleIlluminationEstimator.cpp:94-139),
+ * global triangle order = ascending instance handle, then mesh triangle order.
+ * Traces samples [sample_begin, sample_end) of ray_props->samples for triangles [tri_begin, tri_end).
+ * out6: host, 6 floats per triangle in the range {E.x,E.y,E.z,D.x,D.y,D.z}.
+ * normalise != 0: energy = sum/(faces*samples), direction = normalize(D) (IE.cu:125-128);
+ * normalise == 0: raw partial sums (for cross-GPU sample sharding, summed then finalised). */
+RTF_API int rtf_estimate_illumination_mesh(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* ray_props,
+                                           uint32_t seed, float push_normal_distance, int front_face, int back_face,
+                                           uint64_t tri_begin, uint64_t tri_end, int sample_begin, int sample_end,
+                                           int normalise, float* out6);
+/* Same, result accumulated (+=) into a device array of 6 floats per committed triangle (all triangles). */
+RTF_API int rtf_estimate_illumination_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* ray_props,
+                                                  uint32_t seed, float push_normal_distance, int front_face,
+                                                  int back_face, uint64_t tri_begin, uint64_t tri_end,
+                                                  int sample_begin, int sample_end, float* dev_accum6);
+/* energy = sum/(faces*samples); direction = normalize(D) over a device accumulator (IE.cu:125-128). */
+RTF_API int rtf_illumination_finalize_device(rtf_ctx* ctx, float* dev_accum6, uint64_t n_triangles, int faces,
+                                             int samples);
+/* Statistics of the last illumination / render call: rays traced, paths started. */
+RTF_API int rtf_last_job_stats(rtf_ctx* ctx, uint64_t* rays_traced, uint64_t* paths);
+
+/* ---- LiDAR: CudaModule::SamplePointCloud (CM.hpp:43-45, CM.cpp:52-64)
+ *      -> RayTracer::ScanPointCloud (RT.cu:758-795) -> __raygen__PCS (PCS.cu:44-75) --------- */
+RTF_API int rtf_scan_point_cloud(rtf_ctx* ctx, const rtf_env* env, rtf_pc_sample* samples /* host, in-out */,
+                                 size_t n, uint32_t* prim_ids_out /* host, nullable */);
+/* PointCloudScanner::Scan's ray grid (PCS.cpp:70-92) generated on the device; rays
+ * [ray_begin, ray_end) of the column*row grid; SoA outputs (host, each nullable):
+ * t (float, <0 = miss... see hit), prim_id (0xFFFFFFFF = miss), inst_id. */
+RTF_API int rtf_scan_grid_ray_count(const rtf_scan_grid* grid, uint64_t* n_rays);
+RTF_API int rtf_scan_grid_trace(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin, uint64_t ray_end,
+                          float* t_out, uint32_t* prim_id_out, uint32_t* inst_id_out);
+RTF_API int rtf_scan_grid_trace_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin, uint64_t ray_end,
+                                 float* dev_t_out, uint32_t* dev_prim_id_out);
+
+/* ---- raw closest-hit (the M1 metric; K8 optixTrace) ------------------------ */
+/* rays: n x 8 floats {o.xyz, tmin, d.xyz, tmax}; hits: n x 4 x 32-bit {t, u, v, prim_id(u32)};
+ * prim_id 0xFFFFFFFF = miss.  u,v are OptiX-style barycentrics (weights of vertex 1 and 2). */
+RTF_API int rtf_trace_closest(rtf_ctx* ctx, const float* rays, size_t n, void* hits);
+RTF_API int rtf_trace_closest_device(rtf_ctx* ctx, const float* dev_rays, size_t n, void* dev_hits);
+/* Instrumented variant: also returns per-ray node / triangle visit counts (u32 each, device or NULL). */
+RTF_API int rtf_trace_closest_counts(rtf_ctx* ctx, const float* rays, size_t n, void* hits, uint32_t* node_visits,
+                                     uint32_t* tri_visits);
+
+/* ---- camera: CameraProperties (RT.hpp:30-96, RT.cu:28-92), RayTracer::RenderToCamera
+ *      (RT.hpp:368-371, RT.cu:244-603) -> __raygen__CR (CR.cu:32-147) ---------------------- */
+RTF_API int rtf_camera_create(rtf_ctx* ctx, rtf_camera** out);
+RTF_API int rtf_camera_destroy(rtf_camera* cam);
+RTF_API int rtf_camera_get_props(rtf_camera* cam, rtf_camera_props** props); /* borrowed, mutable */
+RTF_API int rtf_camera_resize(rtf_camera* cam, int width, int height);   /* CameraProperties::Resize */
+/* CameraProperties::Set(position, rotation quaternion {w,x,y,z}) RT.cu:28-46 */
+RTF_API int rtf_camera_set(rtf_camera* cam, const float position[3], const float rotation_wxyz[4]);
+/* returns 1 rendered / 0 no acceleration structure (bool of the reference) or <0 error */
+RTF_API int rtf_render_camera(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* ray_props);
+/* which: RTF_OUT_COLOR / NORMAL / ALBEDO(also depth when output_type == DEPTH); host float4 per pixel */
+RTF_API int rtf_camera_download(rtf_camera* cam, int which, float* host_rgba);
+RTF_API int rtf_camera_device_buffer(rtf_camera* cam, int which, float** dev_rgba);
+
+/* ---- build-stage readback for parity tests (tests/ compares each with the oracle) --------- */
+enum {
+  RTF_DBG_MORTON = 0,       /* u64 per triangle (unsorted order)                 */
+  RTF_DBG_SORTED_IDS = 1,   /* u32 per triangle                                  */
+  RTF_DBG_BIN_CHILDREN = 2, /* 2 x i32 per internal binary node (>=0 internal, <0 = ~leaf) */
+  RTF_DBG_BIN_PARENT = 3,   /* i32 per binary node: internals [0,n-1) then leaves [n-1, 2n-1) */
+  RTF_DBG_BIN_BOXES = 4,    /* 6 floats per binary node, same numbering            */
+  RTF_DBG_WIDE_NODES = 5,   /* 80 B per wide node                                */
+  RTF_DBG_WIDE_TRIS = 6,    /* 48 B per triangle, BVH order                      */
+  RTF_DBG_FLAT_POS = 7,     /* 9 floats per triangle, commit order               */
+  RTF_DBG_FLAT_NRM = 8,     /* 9 floats per triangle, commit order               */
+  RTF_DBG_FLAT_INST = 9,    /* u32 per triangle                                  */
+  RTF_DBG_SCENE_BOUNDS = 10 /* 6 floats                                          */
+};
+RTF_API int rtf_debug_size(rtf_ctx* ctx, int what, uint64_t* bytes);
+RTF_API int rtf_debug_read(rtf_ctx* ctx, int what, void* host_out, uint64_t bytes);
+/* Upload a BVH built elsewhere (the oracle, in tests) so traversal can be checked in isolation. */
+RTF_API int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* wide_nodes, uint64_t n_nodes, const void* wide_tris,
+                                 uint64_t n_tris, int depth);
+/* microbenchmarks for the roofline denominators BASELINE.md asks the builder to measure */
+RTF_API int rtf_microbench_fp32(rtf_ctx* ctx, double* tflops);
+RTF_API int rtf_microbench_l2(rtf_ctx* ctx, double bytes_footprint, double* gbs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTF_RTF_H */

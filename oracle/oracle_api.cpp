@@ -1,0 +1,323 @@
+// oracle_api.cpp — TEST INFRASTRUCTURE ONLY (see oracle/README.md).
+// extern "C" surface of the CPU oracle, loaded with ctypes by tests/, __graft_entry__.smoke() and
+// bench.py's cpu_baseline / --impl reference legs.  The product (raytracerfacility_b200/) never links it.
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "oracle_shade.h"
+
+using namespace orc;
+
+#define ORC_API extern "C" __attribute__((visibility("default")))
+
+template <class F>
+static void parallel_for(uint64_t n, int nthreads, F fn) {
+  if (nthreads <= 0) nthreads = (int)std::thread::hardware_concurrency();
+  if (nthreads < 1) nthreads = 1;
+  if ((uint64_t)nthreads > n) nthreads = n ? (int)n : 1;
+  if (nthreads == 1) {
+    fn(0, 0, n);
+    return;
+  }
+  std::vector<std::thread> th;
+  for (int t = 0; t < nthreads; t++) {
+    uint64_t b = n * (uint64_t)t / (uint64_t)nthreads, e = n * (uint64_t)(t + 1) / (uint64_t)nthreads;
+    th.emplace_back([=] { fn(t, b, e); });
+  }
+  for (auto& x : th) x.join();
+}
+
+ORC_API const char* orc_version() { return "rtf-oracle 0.1 (parity unpinned by the reference: it has no tests; pinned by brute force + closed forms)"; }
+ORC_API int orc_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
+
+// ---- primitives -----------------------------------------------------------------------------
+ORC_API void orc_philox(const uint32_t* ctr, const uint32_t* key, uint32_t* out) { philox4x32_10(ctr, key, out); }
+ORC_API void orc_lcg(uint32_t v0, uint32_t v1, int n, float* out, uint32_t* state_after_init) {
+  LCG g;
+  g.init(v0, v1);
+  if (state_after_init) *state_after_init = g.state;
+  for (int i = 0; i < n; i++) out[i] = g.next();
+}
+ORC_API void orc_sincos2pi(int n, const float* u, float* s, float* c) {
+  for (int i = 0; i < n; i++) sincos2pi(u[i], &s[i], &c[i]);
+}
+ORC_API void orc_path_rng(uint32_t seed, uint32_t stream, uint64_t unit, uint32_t bounce, uint32_t extra, float* r4) {
+  path_rng(seed, stream, unit, bounce, extra, r4);
+}
+ORC_API void orc_sample_hemisphere(float r0, float r1, const float* n, float* out) {
+  V3 d = sample_hemisphere(r0, r1, v3(n[0], n[1], n[2]));
+  out[0] = d.x, out[1] = d.y, out[2] = d.z;
+}
+ORC_API void orc_sample_lobe(float r0, float r1, const float* n, float alpha, float* out) {
+  V3 d = sample_lobe(r0, r1, v3(n[0], n[1], n[2]), alpha);
+  out[0] = d.x, out[1] = d.y, out[2] = d.z;
+}
+ORC_API void orc_env_light(const rtf_env* env, const float* pos, const float* dir, float* out) {
+  V3 c = env_light(v3(pos[0], pos[1], pos[2]), v3(dir[0], dir[1], dir[2]), *env);
+  out[0] = c.x, out[1] = c.y, out[2] = c.z;
+}
+
+// ---- scene ----------------------------------------------------------------------------------
+ORC_API Scene* orc_scene_create() { return new Scene(); }
+ORC_API void orc_scene_destroy(Scene* s) { delete s; }
+ORC_API int orc_scene_add_geometry(Scene* s, const void* verts, uint64_t nv, uint64_t stride, const uint32_t* tris,
+                                   uint64_t nt) {
+  Geometry g;
+  g.verts.resize(nv);
+  for (uint64_t i = 0; i < nv; i++) memcpy(&g.verts[i], (const char*)verts + i * stride, sizeof(rtf_vertex));
+  g.tris.assign(tris, tris + 3 * nt);
+  s->geoms.push_back(std::move(g));
+  return (int)s->geoms.size() - 1;
+}
+ORC_API int orc_scene_add_material(Scene* s, const rtf_material* m) {
+  s->mats.push_back(*m);
+  return (int)s->mats.size() - 1;
+}
+// Instances must be added in ascending handle order (the global primitive numbering).
+ORC_API int orc_scene_add_instance(Scene* s, int geom, int mat, const float* xform16, uint64_t handle) {
+  Instance in;
+  in.geom = (uint32_t)geom, in.mat = (uint32_t)mat, in.handle = handle, in.first_prim = 0;
+  memcpy(in.xform, xform16, 64);
+  s->insts.push_back(in);
+  return (int)s->insts.size() - 1;
+}
+ORC_API void orc_scene_commit(Scene* s, int bits) { commit(*s, bits == 30 ? 30 : 63); }
+ORC_API uint64_t orc_scene_ntris(Scene* s) { return s->tri_inst.size(); }
+ORC_API uint64_t orc_scene_nnodes(Scene* s) { return s->bvh.nodes.size(); }
+ORC_API int orc_scene_depth(Scene* s) { return s->bvh.depth; }
+
+static const void* dbg_ptr(Scene* s, int what, uint64_t* bytes) {
+  BVH& b = s->bvh;
+  switch (what) {
+    case RTF_DBG_MORTON: *bytes = b.morton.size() * 8; return b.morton.data();
+    case RTF_DBG_SORTED_IDS: *bytes = b.order.size() * 4; return b.order.data();
+    case RTF_DBG_BIN_CHILDREN: *bytes = b.children.size() * 4; return b.children.data();
+    case RTF_DBG_BIN_PARENT: *bytes = b.parent.size() * 4; return b.parent.data();
+    case RTF_DBG_BIN_BOXES: *bytes = b.boxes.size() * 24; return b.boxes.data();
+    case RTF_DBG_WIDE_NODES: *bytes = b.nodes.size() * 80; return b.nodes.data();
+    case RTF_DBG_WIDE_TRIS: *bytes = b.tris.size() * 48; return b.tris.data();
+    case RTF_DBG_FLAT_POS: *bytes = s->pos9.size() * 4; return s->pos9.data();
+    case RTF_DBG_FLAT_NRM: *bytes = s->nrm9.size() * 4; return s->nrm9.data();
+    case RTF_DBG_FLAT_INST: *bytes = s->tri_inst.size() * 4; return s->tri_inst.data();
+    case RTF_DBG_SCENE_BOUNDS: *bytes = 24; return &b.scene;
+  }
+  *bytes = 0;
+  return nullptr;
+}
+ORC_API uint64_t orc_debug_size(Scene* s, int what) {
+  uint64_t b = 0;
+  dbg_ptr(s, what, &b);
+  return b;
+}
+ORC_API int orc_debug_read(Scene* s, int what, void* out, uint64_t bytes) {
+  uint64_t b = 0;
+  const void* p = dbg_ptr(s, what, &b);
+  if (!p && b) return -1;
+  if (bytes < b) return -1;
+  if (b) memcpy(out, p, b);
+  return 0;
+}
+
+// ---- closest hit ----------------------------------------------------------------------------
+// rays: n x {o.xyz, tmin, d.xyz, tmax}; hits: n x {t,u,v,prim}
+ORC_API void orc_trace(Scene* s, const float* rays, uint64_t n, void* hits, uint32_t* node_visits, uint32_t* tri_visits,
+                       int nthreads) {
+  Hit* H = (Hit*)hits;
+  parallel_for(n, nthreads, [=](int, uint64_t b, uint64_t e) {
+    for (uint64_t i = b; i < e; i++) {
+      const float* r = rays + 8 * i;
+      Ray ray{v3(r[0], r[1], r[2]), r[3], v3(r[4], r[5], r[6]), r[7]};
+      TraceStats st;
+      H[i] = trace(s->bvh, ray, &st);
+      if (node_visits) node_visits[i] = st.nodes;
+      if (tri_visits) tri_visits[i] = st.tris;
+    }
+  });
+}
+ORC_API void orc_trace_brute(Scene* s, const float* rays, uint64_t n, void* hits, int nthreads) {
+  Hit* H = (Hit*)hits;
+  parallel_for(n, nthreads, [=](int, uint64_t b, uint64_t e) {
+    for (uint64_t i = b; i < e; i++) {
+      const float* r = rays + 8 * i;
+      Ray ray{v3(r[0], r[1], r[2]), r[3], v3(r[4], r[5], r[6]), r[7]};
+      H[i] = trace_brute(s->bvh, ray);
+    }
+  });
+}
+
+// ---- illumination ---------------------------------------------------------------------------
+struct JobStats {
+  uint64_t rays, nodes, tris, paths;
+};
+// Committed triangles [tri_begin, tri_end) with step tri_stride are the probes; out6 holds one
+// record per visited triangle (dense, in visiting order).
+ORC_API void orc_illum_mesh(Scene* s, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push, int front,
+                            int back, uint64_t tri_begin, uint64_t tri_end, uint64_t tri_stride, int s0, int s1,
+                            int normalise, float* out6, JobStats* stats, int nthreads) {
+  if (tri_stride < 1) tri_stride = 1;
+  uint64_t cnt = tri_end > tri_begin ? (tri_end - tri_begin + tri_stride - 1) / tri_stride : 0;
+  int nt = nthreads <= 0 ? (int)std::thread::hardware_concurrency() : nthreads;
+  std::vector<JobStats> per(nt > 0 ? nt : 1, JobStats{0, 0, 0, 0});
+  JobStats* perp = per.data();
+  parallel_for(cnt, nt, [=](int tid, uint64_t b, uint64_t e) {
+    for (uint64_t k = b; k < e; k++) {
+      uint64_t t = tri_begin + k * tri_stride;
+      const float* p = &s->pos9[9 * t];
+      const float* n = &s->nrm9[9 * t];
+      V3 P[3] = {v3(p[0], p[1], p[2]), v3(p[3], p[4], p[5]), v3(p[6], p[7], p[8])};
+      V3 N[3] = {v3(n[0], n[1], n[2]), v3(n[3], n[4], n[5]), v3(n[6], n[7], n[8])};
+      TraceStats st;
+      uint64_t rays = 0;
+      illum_probe(*s, *env, *rp, seed, push, t, P, N, front != 0, back != 0, s0, s1, out6 + 6 * k, &rays, &st);
+      if (normalise) illum_finalize(out6 + 6 * k, (front ? 1 : 0) + (back ? 1 : 0), s1 - s0);
+      perp[tid].rays += rays, perp[tid].nodes += st.nodes, perp[tid].tris += st.tris;
+      perp[tid].paths += (uint64_t)((front ? 1 : 0) + (back ? 1 : 0)) * (uint64_t)(s1 - s0);
+    }
+  });
+  if (stats) {
+    *stats = JobStats{0, 0, 0, 0};
+    for (auto& x : per) stats->rays += x.rays, stats->nodes += x.nodes, stats->tris += x.tris, stats->paths += x.paths;
+  }
+}
+// CudaModule::EstimateIlluminationRayTracing semantics over the 268 B AoS (CUDAModule.cpp:39-50).
+ORC_API void orc_illum_probes(Scene* s, const rtf_env* env, const rtf_ray_props* rp, rtf_illum_sampler* probes, uint64_t n,
+                              uint32_t seed, float push, JobStats* stats, int nthreads) {
+  int nt = nthreads <= 0 ? (int)std::thread::hardware_concurrency() : nthreads;
+  std::vector<JobStats> per(nt > 0 ? nt : 1, JobStats{0, 0, 0, 0});
+  JobStats* perp = per.data();
+  parallel_for(n, nt, [=](int tid, uint64_t b, uint64_t e) {
+    for (uint64_t i = b; i < e; i++) {
+      rtf_illum_sampler& pr = probes[i];
+      V3 P[3] = {v3(pr.a.position[0], pr.a.position[1], pr.a.position[2]),
+                 v3(pr.b.position[0], pr.b.position[1], pr.b.position[2]),
+                 v3(pr.c.position[0], pr.c.position[1], pr.c.position[2])};
+      V3 N[3] = {v3(pr.a.normal[0], pr.a.normal[1], pr.a.normal[2]), v3(pr.b.normal[0], pr.b.normal[1], pr.b.normal[2]),
+                 v3(pr.c.normal[0], pr.c.normal[1], pr.c.normal[2])};
+      float o6[6];
+      TraceStats st;
+      uint64_t rays = 0;
+      bool f = pr.front_face != 0, bk = pr.back_face != 0;
+      illum_probe(*s, *env, *rp, seed, push, i, P, N, f, bk, 0, rp->samples, o6, &rays, &st);
+      int faces = (f ? 1 : 0) + (bk ? 1 : 0);
+      if (faces * rp->samples != 0) {  // IE.cu:125: outputs untouched when sampleSize == 0
+        illum_finalize(o6, faces, rp->samples);
+        for (int k = 0; k < 3; k++) pr.energy[k] = o6[k], pr.direction[k] = o6[3 + k];
+      }
+      perp[tid].rays += rays, perp[tid].nodes += st.nodes, perp[tid].tris += st.tris;
+      perp[tid].paths += (uint64_t)faces * (uint64_t)rp->samples;
+    }
+  });
+  if (stats) {
+    *stats = JobStats{0, 0, 0, 0};
+    for (auto& x : per) stats->rays += x.rays, stats->nodes += x.nodes, stats->tris += x.tris, stats->paths += x.paths;
+  }
+}
+
+// ---- LiDAR ----------------------------------------------------------------------------------
+ORC_API void orc_scan_point_cloud(Scene* s, rtf_pc_sample* samples, uint64_t n, uint32_t* prim_out, int nthreads) {
+  parallel_for(n, nthreads, [=](int, uint64_t b, uint64_t e) {
+    for (uint64_t i = b; i < e; i++) {
+      rtf_pc_sample& sm = samples[i];
+      V3 d = v3(sm.direction[0], sm.direction[1], sm.direction[2]);
+      Ray ray{v3(sm.start[0], sm.start[1], sm.start[2]), 1e-3f, d, 1e20f};  // PCS.cu:58-62
+      Hit h = trace(s->bvh, ray);
+      if (prim_out) prim_out[i] = h.prim;
+      if (h.prim == 0xFFFFFFFFu) {  // __miss__PCS_R, PCS.cu:36-40 (+ HitInfo() defaults, PCS.cu:55)
+        sm.hit = 0, sm.handle = 0;
+        memset(&sm.hit_info, 0, sizeof(sm.hit_info));
+        for (int k = 0; k < 4; k++) sm.hit_info.color[k] = 1.0f;
+      } else {
+        sm.hit = 1;
+        sm.handle = s->insts[s->tri_inst[h.prim]].handle;
+        full_hit_info(*s, h, d, sm.hit_info);
+      }
+    }
+  });
+}
+// PointCloudScanner::Scan ray grid, PointCloudScanner.cpp:70-92.
+static inline void grid_dims(const rtf_scan_grid& g, uint32_t& column, uint32_t& row) {
+  column = (uint32_t)(g.size[0] / g.distance[0]);
+  row = (uint32_t)(g.size[1] / g.distance[1]);
+}
+static inline Ray grid_ray(const rtf_scan_grid& g, uint32_t column, uint32_t row, uint64_t i) {
+  const int column_start = -(int)(column / 2);
+  const int row_start = -(int)(row / 2);
+  const int ci = (int)(i / row), ri = (int)(i % row);
+  V3 center = v3(g.center[0], g.center[1], g.center[2]);
+  V3 left = v3(g.left[0], g.left[1], g.left[2]), up = v3(g.up[0], g.up[1], g.up[2]);
+  V3 pos = (center + (left * (float)(column_start + ci)) * g.distance[0]) + (up * (float)(row_start + ri)) * g.distance[1];
+  V3 dir = normalize(v3(g.direction[0], g.direction[1], g.direction[2]));
+  return Ray{pos, 1e-3f, dir, 1e20f};
+}
+ORC_API uint64_t orc_scan_grid_count(const rtf_scan_grid* g) {
+  uint32_t c, r;
+  grid_dims(*g, c, r);
+  return (uint64_t)c * (uint64_t)r;
+}
+ORC_API void orc_scan_grid(Scene* s, const rtf_scan_grid* g, uint64_t ray_begin, uint64_t ray_end, uint64_t stride,
+                           float* t_out, uint32_t* prim_out, uint32_t* inst_out, JobStats* stats, int nthreads) {
+  uint32_t column, row;
+  grid_dims(*g, column, row);
+  if (stride < 1) stride = 1;
+  uint64_t cnt = ray_end > ray_begin ? (ray_end - ray_begin + stride - 1) / stride : 0;
+  int nt = nthreads <= 0 ? (int)std::thread::hardware_concurrency() : nthreads;
+  std::vector<JobStats> per(nt > 0 ? nt : 1, JobStats{0, 0, 0, 0});
+  JobStats* perp = per.data();
+  parallel_for(cnt, nt, [=](int tid, uint64_t b, uint64_t e) {
+    for (uint64_t k = b; k < e; k++) {
+      Ray ray = grid_ray(*g, column, row, ray_begin + k * stride);
+      TraceStats st;
+      Hit h = trace(s->bvh, ray, &st);
+      if (t_out) t_out[k] = h.t;
+      if (prim_out) prim_out[k] = h.prim;
+      if (inst_out) inst_out[k] = h.prim == 0xFFFFFFFFu ? 0xFFFFFFFFu : s->tri_inst[h.prim];
+      perp[tid].rays++, perp[tid].nodes += st.nodes, perp[tid].tris += st.tris;
+    }
+  });
+  if (stats) {
+    *stats = JobStats{0, 0, 0, 0};
+    for (auto& x : per) stats->rays += x.rays, stats->nodes += x.nodes, stats->tris += x.tris;
+  }
+}
+ORC_API void orc_scan_grid_rays(const rtf_scan_grid* g, uint64_t ray_begin, uint64_t ray_end, float* rays8) {
+  uint32_t column, row;
+  grid_dims(*g, column, row);
+  for (uint64_t i = ray_begin; i < ray_end; i++) {
+    Ray r = grid_ray(*g, column, row, i);
+    float* o = rays8 + 8 * (i - ray_begin);
+    o[0] = r.o.x, o[1] = r.o.y, o[2] = r.o.z, o[3] = r.tmin, o[4] = r.d.x, o[5] = r.d.y, o[6] = r.d.z, o[7] = r.tmax;
+  }
+}
+
+// ---- camera ---------------------------------------------------------------------------------
+// Pixels pixel_begin + k*stride (k = 0..) of the W*H raster (index = x + W*y).  prev_color: the
+// colour buffer before this frame (float4 per visited pixel, may be NULL).  Outputs float4 per visited pixel.
+ORC_API void orc_camera(Scene* s, const rtf_env* env, const rtf_ray_props* rp, const rtf_camera_props* cam,
+                        uint64_t pixel_begin, uint64_t pixel_end, uint64_t stride, const float* prev_color, float* color,
+                        float* normal, float* albedo, JobStats* stats, int nthreads) {
+  if (stride < 1) stride = 1;
+  uint64_t cnt = pixel_end > pixel_begin ? (pixel_end - pixel_begin + stride - 1) / stride : 0;
+  int nt = nthreads <= 0 ? (int)std::thread::hardware_concurrency() : nthreads;
+  std::vector<JobStats> per(nt > 0 ? nt : 1, JobStats{0, 0, 0, 0});
+  JobStats* perp = per.data();
+  parallel_for(cnt, nt, [=](int tid, uint64_t b, uint64_t e) {
+    for (uint64_t k = b; k < e; k++) {
+      uint64_t px = pixel_begin + k * stride;
+      int ix = (int)(px % (uint64_t)cam->width), iy = (int)(px / (uint64_t)cam->width);
+      TraceStats st;
+      uint64_t rays = 0;
+      PixelOut po = camera_pixel(*s, *env, *rp, *cam, ix, iy, &rays, &st);
+      const float zero[4] = {0, 0, 0, 0};
+      camera_resolve(*cam, po, prev_color ? prev_color + 4 * k : zero, color + 4 * k, normal + 4 * k, albedo + 4 * k);
+      perp[tid].rays += rays, perp[tid].nodes += st.nodes, perp[tid].tris += st.tris, perp[tid].paths += rp->samples;
+    }
+  });
+  if (stats) {
+    *stats = JobStats{0, 0, 0, 0};
+    for (auto& x : per) stats->rays += x.rays, stats->nodes += x.nodes, stats->tris += x.tris, stats->paths += x.paths;
+  }
+}

@@ -1,0 +1,451 @@
+// oracle_shade.h — TEST INFRASTRUCTURE ONLY (see oracle/README.md).
+// Scalar CPU restatement of the reference's device programs for the hot path.  Paths are relative
+// to /root/reference; RTU.cuh/RF.cuh/Env.cuh/BSDF.cuh/RDD.hpp live in
+// include/RayTracerFacility/RayTracer/, IE.cu/PCS.cu/CR.cu in src/RayTracerFacility/ptx/.
+//
+// Deliberate, documented departures (SURVEY §7 "Hard parts", §8 "Quirks"):
+//  * RNG: the per-thread LCG stream (LCG.hpp) is replaced by Philox keyed (seed, unit, bounce), so a
+//    path's draws do not depend on other paths or on traversal order (the reference's own sequence is
+//    not reproducible: AnyHitFunc draws per candidate hit in OptiX traversal order, RF.cuh:19).
+//  * Recursion (RF.cuh:136-161 calls optixTrace inside closest-hit) is unrolled into the equivalent
+//    throughput/accumulator loop; products are associated outside-in instead of inside-out.
+//  * sin/cos(2*pi*u) use the portable polynomial in oracle_math.h.
+//  * pow(c, 1/gamma) is skipped when gamma == 1 (identity).
+// Everything else — barycentric sample not folded (IE.cu:56-59), un-normalised probe normal
+// (IE.cu:60-62,81), lobe around the mirror direction (BSDF.cuh:6-13), bounce origin not offset
+// (RF.cuh:138), normal transformed by M and flipped against the ray (RDD.hpp:375-378), dominant-vertex
+// colour pick (RDD.hpp:150-160) — follows the reference.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+#include "../include/rtf/rtf.h"
+#include "oracle_bvh.h"
+
+namespace orc {
+
+struct Geometry {
+  std::vector<rtf_vertex> verts;
+  std::vector<uint32_t> tris;  // 3 per triangle
+};
+struct Instance {
+  uint32_t geom, mat;
+  float xform[16];
+  uint64_t handle;
+  uint32_t first_prim;
+};
+
+struct Scene {
+  std::vector<Geometry> geoms;
+  std::vector<rtf_material> mats;
+  std::vector<Instance> insts;
+  // flattened, commit order (global primitive id)
+  std::vector<float> pos9, nrm9;
+  std::vector<uint32_t> tri_inst;
+  BVH bvh;
+  bool committed = false;
+};
+
+// TriangleIlluminationEstimator.cpp:110-118: position = M*(p,1), normal = M*(n,0), NOT renormalised.
+static inline void flatten(Scene& sc) {
+  sc.pos9.clear(), sc.nrm9.clear(), sc.tri_inst.clear();
+  for (size_t ii = 0; ii < sc.insts.size(); ii++) {
+    Instance& in = sc.insts[ii];
+    const Geometry& g = sc.geoms[in.geom];
+    in.first_prim = (uint32_t)sc.tri_inst.size();
+    for (size_t t = 0; t < g.tris.size() / 3; t++) {
+      for (int k = 0; k < 3; k++) {
+        const rtf_vertex& v = g.verts[g.tris[3 * t + k]];
+        V3 p = mat4_mul_point(in.xform, v3(v.position[0], v.position[1], v.position[2]), 1.0f);
+        V3 n = mat4_mul_point(in.xform, v3(v.normal[0], v.normal[1], v.normal[2]), 0.0f);
+        sc.pos9.push_back(p.x), sc.pos9.push_back(p.y), sc.pos9.push_back(p.z);
+        sc.nrm9.push_back(n.x), sc.nrm9.push_back(n.y), sc.nrm9.push_back(n.z);
+      }
+      sc.tri_inst.push_back((uint32_t)ii);
+    }
+  }
+}
+static inline void commit(Scene& sc, int bits) {
+  flatten(sc);
+  build(sc.bvh, (uint32_t)sc.tri_inst.size(), sc.pos9.data(), sc.tri_inst.data(), bits);
+  sc.committed = true;
+}
+
+// ---- RTU.cuh:89-145 ------------------------------------------------------------------------------
+static inline V3 reflect(V3 i, V3 n) { return i - (2.0f * dot(i, n)) * n; }
+static inline void tangent_space(V3 n, V3& t, V3& b) {  // RTU.cuh:110-120
+  V3 helper = v3(1, 0, 0);
+  if (fabsf(n.x) > 0.99f) helper = v3(0, 0, 1);
+  t = normalize(cross(n, helper));
+  b = normalize(cross(n, t));
+}
+static inline V3 to_world(V3 n, float cos_theta, float r_phi) {
+  float sin_theta = sqrtf(fmaxf(0.0f, 1.0f - cos_theta * cos_theta));
+  float s, c;
+  sincos2pi(r_phi, &s, &c);
+  V3 l = v3(c * sin_theta, s * sin_theta, cos_theta);
+  V3 t, b;
+  tangent_space(n, t, b);
+  return (t * l.x + b * l.y) + n * l.z;
+}
+// RandomSampleHemisphere(rng, n): cosTheta = rnd, phi = 2*pi*rnd (RTU.cuh:135-145)
+static inline V3 sample_hemisphere(float r0, float r1, V3 n) { return to_world(n, r0, r1); }
+// RandomSampleHemisphere(rng, n, alpha): cosTheta = 1 - rnd*(1-alpha)^2 (RTU.cuh:122-133)
+static inline V3 sample_lobe(float r0, float r1, V3 n, float alpha) {
+  float cos_theta = 1.0f - (r0 * (1.0f - alpha)) * (1.0f - alpha);
+  return to_world(n, cos_theta, r1);
+}
+
+// ---- Env.cuh:28-175 ------------------------------------------------------------------------------
+static inline bool solve_quadratic(float a, float b, float c, float& x1, float& x2) {
+  if (b == 0) {
+    if (a == 0) return false;
+    x1 = 0;
+    x2 = sqrtf(-c / a);
+    return true;
+  }
+  float discr = b * b - 4 * a * c;
+  if (discr < 0) return false;
+  float q = (b < 0.f) ? -0.5f * (b - sqrtf(discr)) : -0.5f * (b + sqrtf(discr));
+  x1 = q / a;
+  x2 = c / q;
+  return true;
+}
+static inline bool ray_sphere(V3 o, V3 d, float radius, float& t0, float& t1) {
+  float A = (d.x * d.x + d.y * d.y) + d.z * d.z;
+  float B = 2.0f * ((d.x * o.x + d.y * o.y) + d.z * o.z);
+  float C = ((o.x * o.x + o.y * o.y) + o.z * o.z) - radius * radius;
+  if (!solve_quadratic(A, B, C, t0, t1)) return false;
+  if (t0 > t1) std::swap(t0, t1);
+  return true;
+}
+static inline V3 nishita_sky(V3 position, V3 dir, const rtf_env& env) {  // Env.cuh:75-145
+  float earth = env.atmosphere.earth_radius * 1000.0f;
+  float atmos = env.atmosphere.atmosphere_radius * 1000.0f;
+  float Hr = env.atmosphere.hr, Hm = env.atmosphere.hm;
+  V3 betaR = v3(3.8e-6f, 13.5e-6f, 33.1e-6f);
+  V3 betaM = v3(21e-6f, 21e-6f, 21e-6f);
+  V3 sun = v3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
+  float tmin = 0, tmax = 999999999999.0f;
+  V3 orig = position + v3(0.0f, earth, 0.0f);
+  float t0, t1;
+  if (!ray_sphere(orig, dir, atmos, t0, t1) || t1 < 0.0f) return v3(0, 0, 0);
+  if (t0 > tmin && t0 > 0.0f) tmin = t0;
+  if (t1 < tmax) tmax = t1;
+  unsigned ns = (unsigned)env.atmosphere.num_samples, nl = (unsigned)env.atmosphere.num_samples_light;
+  float seg = (tmax - tmin) / ns;
+  float tcur = tmin;
+  V3 sumR = v3(0, 0, 0), sumM = v3(0, 0, 0);
+  float odR = 0, odM = 0;
+  float mu = dot(dir, sun);
+  float phaseR = 3.f / (16.f * 3.1415926f) * (1.0f + mu * mu);
+  float g = env.atmosphere.g;
+  float phaseM = 3.f / (8.f * 3.1415926f) * ((1.f - g * g) * (1.f + mu * mu)) /
+                 ((2.f + g * g) * powf(1.f + g * g - 2.f * g * mu, 1.5f));
+  for (unsigned i = 0; i < ns; ++i) {
+    V3 sp = orig + (tcur + seg * 0.5f) * dir;
+    float height = length(sp) - earth;
+    float hr = expf(-height / Hr) * seg;
+    float hm = expf(-height / Hm) * seg;
+    odR += hr;
+    odM += hm;
+    float t0l = 0, t1l = 0;
+    ray_sphere(sp, sun, atmos, t0l, t1l);
+    float segl = t1l / nl, tcl = 0;
+    float olR = 0, olM = 0;
+    unsigned j;
+    for (j = 0; j < nl; ++j) {
+      V3 spl = sp + (tcl + segl * 0.5f) * sun;
+      float hl = length(spl) - earth;
+      if (hl < 0) break;
+      olR += expf(-hl / Hr) * segl;
+      olM += expf(-hl / Hm) * segl;
+      tcl += segl;
+    }
+    if (j == nl) {
+      V3 tau = betaR * (odR + olR) + (betaM * 1.1f) * (odM + olM);
+      V3 att = v3(expf(-tau.x), expf(-tau.y), expf(-tau.z));
+      sumR = sumR + att * hr;
+      sumM = sumM + att * hm;
+    }
+    tcur += seg;
+  }
+  return ((sumR * betaR) * phaseR + (sumM * betaM) * phaseM) * 20.0f;
+}
+static inline V3 env_light(V3 position, V3 dir, const rtf_env& env) {  // Env.cuh:147-175
+  V3 c = v3(1, 1, 1);
+  V3 col = v3(env.color[0], env.color[1], env.color[2]);
+  switch (env.lighting_type) {
+    case RTF_ENV_SCENE: c = col * env.skylight_intensity; break;  // cube map: not wired (N2)
+    case RTF_ENV_SKYDOME: c = nishita_sky(position, dir, env) * env.skylight_intensity; break;
+    case RTF_ENV_SINGLE_LIGHT_SOURCE: c = col * env.skylight_intensity; break;
+  }
+  if (env.gamma != 1.0f) {
+    float ig = 1.0f / env.gamma;
+    c = v3(powf(c.x, ig), powf(c.y, ig), powf(c.z, ig));
+  }
+  return vmax(v3(0, 0, 0), c);
+}
+
+// ---- hit reconstruction: RDD.hpp:127-164 (TriangularMesh::GetHitInfo) + :364-382 (SBT::GetHitInfo) ----
+struct SurfaceHit {
+  V3 position, normal;
+  uint32_t inst;
+};
+static inline SurfaceHit surface_hit(const Scene& sc, const Hit& h, V3 ray_dir) {
+  SurfaceHit s;
+  const float* p = &sc.pos9[9 * (size_t)h.prim];
+  const float* n = &sc.nrm9[9 * (size_t)h.prim];
+  float w0 = (1.0f - h.u) - h.v;
+  V3 p0 = v3(p[0], p[1], p[2]), p1 = v3(p[3], p[4], p[5]), p2 = v3(p[6], p[7], p[8]);
+  V3 n0 = v3(n[0], n[1], n[2]), n1 = v3(n[3], n[4], n[5]), n2 = v3(n[6], n[7], n[8]);
+  s.position = (w0 * p0 + h.u * p1) + h.v * p2;
+  V3 nn = normalize((w0 * n0 + h.u * n1) + h.v * n2);
+  if (dot(ray_dir, nn) > 0.0f) nn = neg(nn);
+  s.normal = nn;
+  s.inst = sc.tri_inst[h.prim];
+  return s;
+}
+// Full HitInfo as written by __closesthit__PCS_R (PCS.cu:15-28).
+static inline void full_hit_info(const Scene& sc, const Hit& h, V3 ray_dir, rtf_hit_info& out) {
+  SurfaceHit s = surface_hit(sc, h, ray_dir);
+  const Instance& in = sc.insts[s.inst];
+  const Geometry& g = sc.geoms[in.geom];
+  uint32_t lt = h.prim - in.first_prim;
+  const rtf_vertex& vx = g.verts[g.tris[3 * lt]];
+  const rtf_vertex& vy = g.verts[g.tris[3 * lt + 1]];
+  const rtf_vertex& vz = g.verts[g.tris[3 * lt + 2]];
+  float z = (1.0f - h.u) - h.v;
+  V3 tg = (z * v3(vx.tangent[0], vx.tangent[1], vx.tangent[2]) + h.u * v3(vy.tangent[0], vy.tangent[1], vy.tangent[2])) +
+          h.v * v3(vz.tangent[0], vz.tangent[1], vz.tangent[2]);
+  tg = normalize(mat4_mul_point(in.xform, tg, 0.0f));
+  out.position[0] = s.position.x, out.position[1] = s.position.y, out.position[2] = s.position.z;
+  out.normal[0] = s.normal.x, out.normal[1] = s.normal.y, out.normal[2] = s.normal.z;
+  out.tangent[0] = tg.x, out.tangent[1] = tg.y, out.tangent[2] = tg.z;
+  out.tex_coord[0] = (z * vx.tex_coord[0] + h.u * vy.tex_coord[0]) + h.v * vz.tex_coord[0];
+  out.tex_coord[1] = (z * vx.tex_coord[1] + h.u * vy.tex_coord[1]) + h.v * vz.tex_coord[1];
+  const rtf_vertex* pick = (h.u > z && h.u > h.v) ? &vx : (h.v > z ? &vy : &vz);  // RDD.hpp:150-160 (as written)
+  for (int k = 0; k < 4; k++) out.color[k] = pick->color[k];
+  out.data[0] = pick->position_padding, out.data[1] = pick->normal_padding;
+  out.data[2] = pick->tangent_padding, out.data[3] = pick->tex_coord_padding[0];
+}
+
+// any-hit alpha test (RF.cuh:5-23): Default material only, alpha = 1 - transmission (RDD.hpp:250).
+struct AlphaFilter {
+  const Scene* sc;
+  uint32_t seed;
+  uint64_t unit;
+  uint32_t bounce;
+  bool operator()(const Tri48& tri) const {
+    const rtf_material& m = sc->mats[sc->insts[tri.inst].mat];
+    if (m.material_type != RTF_MAT_DEFAULT) return true;
+    float alpha = 1.0f - m.transmission;
+    if (alpha >= 1.0f) return true;
+    float r[4];
+    path_rng(seed, STREAM_ALPHA, unit, bounce, tri.prim, r);
+    return !(alpha <= r[0]);
+  }
+};
+
+struct PathResult {
+  V3 energy, normal, albedo, position;  // PerRayData, RTU.cuh:26-34
+  bool first_hit;
+  uint32_t rays;
+};
+
+// __closesthit__*_R -> ClosestHitFunc (RF.cuh:25-172, non-BTF branch), __miss__*_R -> MissFunc
+// (RF.cuh:260-272), unrolled.  `o,d,tmin` is the primary ray; returns radiance + first-hit records.
+static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bounces, uint32_t seed, uint64_t unit,
+                                    V3 o, V3 d, float tmin, TraceStats* stats) {
+  PathResult pr;
+  pr.energy = v3(0, 0, 0), pr.normal = v3(0, 0, 0), pr.albedo = v3(0, 0, 0), pr.position = v3(0, 0, 0);
+  pr.first_hit = false;
+  pr.rays = 0;
+  V3 T = v3(1, 1, 1), acc = v3(0, 0, 0);
+  uint32_t hit_count = 0;
+  for (;;) {
+    Ray ray{o, tmin, d, 1e20f};
+    AlphaFilter flt{&sc, seed, unit, hit_count};
+    Hit h = trace(sc.bvh, ray, stats, false, flt);
+    pr.rays++;
+    if (h.prim == 0xFFFFFFFFu) {
+      V3 L = env_light(o, d, env);
+      acc = acc + T * L;
+      if (hit_count == 0) pr.albedo = L;  // MissFunc: m_albedo = m_energy = env colour
+      break;
+    }
+    hit_count++;
+    SurfaceHit sh = surface_hit(sc, h, d);
+    const rtf_material& m = sc.mats[sc.insts[sh.inst].mat];
+    float metallic = m.metallic, roughness = m.roughness;
+    V3 albedo = v3(m.albedo_color[0], m.albedo_color[1], m.albedo_color[2]);
+    if (hit_count == 1) pr.normal = sh.normal, pr.albedo = albedo, pr.position = sh.position, pr.first_hit = true;
+    float f = 1.0f;
+    if (metallic >= 0.0f) f = (metallic + 2) / (metallic + 1);
+    V3 emis = m.emission * albedo;
+    float r[4];
+    if (env.lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE) {  // RF.cuh:61-92
+      path_rng(seed, STREAM_PATH, unit, hit_count, 0, r);
+      V3 sun = v3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
+      V3 nd = sample_lobe(r[0], r[1], sun, 1.0f - env.light_size);
+      V3 col = v3(env.color[0], env.color[1], env.color[2]);
+      acc = acc + T * ((col * env.ambient_light_intensity) * albedo);
+      float ndl = dot(sh.normal, nd);
+      if (ndl > 0.0f) {
+        Ray sr{sh.position, 1e-3f, nd, 1e20f};
+        Hit sh2 = trace(sc.bvh, sr, stats, true);
+        pr.rays++;
+        if (sh2.prim == 0xFFFFFFFFu) {
+          V3 L = env_light(sh.position, nd, env);
+          acc = acc + T * ((L * ndl) * albedo);
+        }
+      }
+      acc = acc + T * emis;
+      break;
+    } else if ((int)hit_count <= bounces) {  // RF.cuh:93-161 (BSSRDF branch off: subsurfaceFactor == 0 only)
+      path_rng(seed, STREAM_PATH, unit, hit_count, 0, r);
+      V3 refl = reflect(d, sh.normal);
+      V3 nd = sample_lobe(r[0], r[1], refl, metallic);
+      float k = clampf(fabsf(dot(sh.normal, nd)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
+      V3 wgt = ((1.0f - m.subsurface_factor) * albedo) * k;
+      acc = acc + T * emis;
+      T = T * wgt;
+      o = sh.position, d = nd, tmin = 1e-3f;
+      continue;
+    } else {
+      acc = acc + T * emis;
+      break;
+    }
+  }
+  pr.energy = acc;
+  return pr;
+}
+
+// 32-lane strided accumulation + xor butterfly: the fixed reduction tree shared with the GPU.
+struct Lanes6 {
+  float v[32][6];
+  Lanes6() { memset(v, 0, sizeof(v)); }
+  void add(int idx, const float x[6]) {
+    for (int k = 0; k < 6; k++) v[idx & 31][k] = v[idx & 31][k] + x[k];
+  }
+  void reduce(float out[6]) {
+    for (int off = 16; off >= 1; off >>= 1) {
+      float nv[32][6];
+      for (int l = 0; l < 32; l++)
+        for (int k = 0; k < 6; k++) nv[l][k] = v[l][k] + v[l ^ off][k];
+      memcpy(v, nv, sizeof(v));
+    }
+    for (int k = 0; k < 6; k++) out[k] = v[0][k];
+  }
+};
+
+// __raygen__IE (IE.cu:30-129) for one probe.  Returns raw sums {E.xyz, D.xyz} over the enabled faces
+// and samples [s0,s1) of S_total.
+static inline void illum_probe(const Scene& sc, const rtf_env& env, const rtf_ray_props& rp, uint32_t seed, float push,
+                               uint64_t probe_id, const V3 P[3], const V3 N[3], bool front, bool back, int s0, int s1,
+                               float out6[6], uint64_t* rays, TraceStats* stats) {
+  for (int k = 0; k < 6; k++) out6[k] = 0.0f;
+  for (int face = 0; face < 2; face++) {
+    if (face == 0 ? !front : !back) continue;
+    Lanes6 lanes;
+    for (int s = s0; s < s1; s++) {
+      uint64_t unit = (probe_id * 2 + (uint64_t)face) * (uint64_t)rp.samples + (uint64_t)s;
+      float r[4];
+      path_rng(seed, STREAM_PATH, unit, 0, 0, r);
+      float a = r[0], b = r[1];
+      float w = (1.0f - a) - b;
+      V3 position = (w * P[0] + a * P[1]) + b * P[2];
+      V3 normal = (w * N[0] + a * N[1]) + b * N[2];
+      if (face == 1) normal = neg(normal);
+      V3 dir = sample_hemisphere(r[2], r[3], normal);
+      V3 origin = position + normal * push;
+      PathResult pr = trace_path(sc, env, rp.bounces, seed, unit, origin, dir, 1e-3f, stats);
+      if (rays) *rays += pr.rays;
+      V3 e = pr.energy * fabsf(dot(normal, dir));
+      V3 dd = dir * length(e);
+      float x[6] = {e.x, e.y, e.z, dd.x, dd.y, dd.z};
+      lanes.add(s - s0, x);
+    }
+    float red[6];
+    lanes.reduce(red);
+    for (int k = 0; k < 6; k++) out6[k] = out6[k] + red[k];
+  }
+}
+static inline void illum_finalize(float v[6], int faces, int samples) {  // IE.cu:125-128
+  int n = faces * samples;
+  if (n == 0) return;
+  float fn = (float)n;
+  v[0] = v[0] / fn, v[1] = v[1] / fn, v[2] = v[2] / fn;
+  V3 d = normalize(v3(v[3], v[4], v[5]));
+  v[3] = d.x, v[4] = d.y, v[5] = d.z;
+}
+
+// __raygen__CR (CR.cu:32-147) for one pixel: per-sample path results summed in sample order.
+struct PixelOut {
+  V3 color, normal, albedo, position;
+};
+static inline PixelOut camera_pixel(const Scene& sc, const rtf_env& env, const rtf_ray_props& rp,
+                                    const rtf_camera_props& cam, int ix, int iy, uint64_t* rays, TraceStats* stats) {
+  PixelOut po{v3(0, 0, 0), v3(0, 0, 0), v3(0, 0, 0), v3(0, 0, 0)};
+  const int W = cam.width, H = cam.height;
+  const uint64_t pixel = (uint64_t)ix + (uint64_t)W * (uint64_t)iy;
+  const float halfX = W / 2.0f, halfY = H / 2.0f;
+  const float* m = cam.inverse_projection_view;
+  const uint32_t seed = (uint32_t)cam.frame_id;
+  const float nsf = (float)rp.samples;
+  V3 hor = v3(cam.horizontal[0], cam.horizontal[1], cam.horizontal[2]);
+  V3 ver = v3(cam.vertical[0], cam.vertical[1], cam.vertical[2]);
+  for (int s = 0; s < rp.samples; s++) {
+    uint64_t unit = pixel * (uint64_t)rp.samples + (uint64_t)s;
+    float r[4];
+    path_rng(seed, STREAM_CAMERA, unit, 0, 0, r);
+    float sx = (((float)ix + r[0]) - halfX) / halfX;
+    float sy = (((float)iy + r[1]) - halfY) / halfY;
+    float st[4], en[4];
+    for (int k = 0; k < 4; k++) {
+      st[k] = (m[k] * sx + m[4 + k] * sy) + (m[8 + k] * -1.0f + m[12 + k] * 1.0f);
+      en[k] = (m[k] * sx + m[4 + k] * sy) + (m[8 + k] * 1.0f + m[12 + k] * 1.0f);
+    }
+    V3 start = v3(st[0] / st[3], st[1] / st[3], st[2] / st[3]);
+    V3 end = v3(en[0] / en[3], en[1] / en[3], en[2] / en[3]);
+    V3 pdir = normalize(end - start);
+    V3 conv = start + pdir * cam.focal_length;
+    float sn, cs;
+    sincos2pi(r[2], &sn, &cs);
+    V3 ap = start + cam.aperture * (hor * sn + ver * cs);
+    V3 dir = normalize(conv - ap);
+    PathResult pr = trace_path(sc, env, rp.bounces, seed, unit, ap, dir, 0.0f, stats);
+    if (rays) *rays += pr.rays;
+    V3 pos = pr.first_hit ? pr.position : (s == 0 ? v3(999999.0f, 999999.0f, 999999.0f) : v3(0, 0, 0));  // CR.cu:48,108
+    po.color = po.color + v3(pr.energy.x / nsf, pr.energy.y / nsf, pr.energy.z / nsf);
+    po.normal = po.normal + v3(pr.normal.x / nsf, pr.normal.y / nsf, pr.normal.z / nsf);
+    po.albedo = po.albedo + v3(pr.albedo.x / nsf, pr.albedo.y / nsf, pr.albedo.z / nsf);
+    po.position = po.position + v3(pos.x / nsf, pos.y / nsf, pos.z / nsf);
+  }
+  return po;
+}
+// CR.cu:112-146: progressive accumulation in gamma space and output writes.  prev = current colour buffer texel.
+static inline void camera_resolve(const rtf_camera_props& cam, const PixelOut& po, const float prev[4], float color[4],
+                                  float normal[4], float albedo[4]) {
+  V3 pc = po.color;
+  if (cam.accumulate && cam.frame_id > 1) {
+    V3 acc = v3(powf(prev[0], cam.gamma), powf(prev[1], cam.gamma), powf(prev[2], cam.gamma));
+    float fid = (float)cam.frame_id;
+    pc = pc + fid * acc;
+    float den = (float)(cam.frame_id + 1);
+    pc = v3(pc.x / den, pc.y / den, pc.z / den);
+  }
+  float ig = (float)(1.0 / (double)cam.gamma);
+  color[0] = powf(pc.x, ig), color[1] = powf(pc.y, ig), color[2] = powf(pc.z, ig), color[3] = 1.0f;
+  if (cam.output_type == RTF_OUT_DEPTH) {
+    V3 from = v3(cam.from[0], cam.from[1], cam.from[2]);
+    float dist = length(from - po.position);
+    float dd = clampf(dist / cam.max_distance, 0.0f, 1.0f);
+    albedo[0] = albedo[1] = albedo[2] = dd, albedo[3] = 1.0f;
+  } else {
+    albedo[0] = po.albedo.x, albedo[1] = po.albedo.y, albedo[2] = po.albedo.z, albedo[3] = 1.0f;
+  }
+  normal[0] = po.normal.x, normal[1] = po.normal.y, normal[2] = po.normal.z, normal[3] = 1.0f;
+}
+
+}  // namespace orc

@@ -1,0 +1,204 @@
+"""ctypes binding of the CPU oracle (oracle/liboracle.so).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs.  Nothing under raytracerfacility_b200/ imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(_HERE))
+from raytracerfacility_b200 import structs as S  # noqa: E402  (POD layouts only)
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "liboracle.so")
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_api.cpp", "oracle_shade.h", "oracle_bvh.h", "oracle_math.h")]
+    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return so
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(build())
+        L = _lib
+        L.orc_version.restype = C.c_char_p
+        L.orc_scene_create.restype = C.c_void_p
+        L.orc_scene_ntris.restype = C.c_uint64
+        L.orc_scene_nnodes.restype = C.c_uint64
+        L.orc_debug_size.restype = C.c_uint64
+        L.orc_scan_grid_count.restype = C.c_uint64
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def philox(ctr, key):
+    out = (C.c_uint32 * 4)()
+    lib().orc_philox((C.c_uint32 * 4)(*ctr), (C.c_uint32 * 2)(*key), out)
+    return list(out)
+
+
+def lcg(v0, v1, n):
+    out = np.zeros(n, dtype=np.float32)
+    st = C.c_uint32()
+    lib().orc_lcg(C.c_uint32(v0), C.c_uint32(v1), n, _p(out), C.byref(st))
+    return out, st.value
+
+
+def sincos2pi(u):
+    u = np.ascontiguousarray(u, dtype=np.float32)
+    s, c = np.empty_like(u), np.empty_like(u)
+    lib().orc_sincos2pi(len(u), _p(u), _p(s), _p(c))
+    return s, c
+
+
+def path_rng(seed, stream, unit, bounce, extra=0):
+    r = (C.c_float * 4)()
+    lib().orc_path_rng(C.c_uint32(seed), C.c_uint32(stream), C.c_uint64(unit), C.c_uint32(bounce), C.c_uint32(extra), r)
+    return list(r)
+
+
+def sample_hemisphere(r0, r1, n):
+    out = (C.c_float * 3)()
+    lib().orc_sample_hemisphere(C.c_float(r0), C.c_float(r1), (C.c_float * 3)(*n), out)
+    return np.array(out[:], dtype=np.float32)
+
+
+def sample_lobe(r0, r1, n, alpha):
+    out = (C.c_float * 3)()
+    lib().orc_sample_lobe(C.c_float(r0), C.c_float(r1), (C.c_float * 3)(*n), C.c_float(alpha), out)
+    return np.array(out[:], dtype=np.float32)
+
+
+def env_light(env, pos, d):
+    out = (C.c_float * 3)()
+    lib().orc_env_light(C.byref(env), (C.c_float * 3)(*pos), (C.c_float * 3)(*d), out)
+    return np.array(out[:], dtype=np.float32)
+
+
+class OracleScene:
+    """CPU oracle scene built from a scenes.SceneDesc (instances in ascending handle order)."""
+
+    def __init__(self, desc, morton_bits=63):
+        L = lib()
+        self.h = C.c_void_p(L.orc_scene_create())
+        gmap, mmap = {}, {}
+        for gh in sorted(desc.geometries):
+            v, t = desc.geometries[gh]
+            v = np.ascontiguousarray(v)
+            t = np.ascontiguousarray(t, dtype=np.uint32)
+            gmap[gh] = L.orc_scene_add_geometry(self.h, _p(v), C.c_uint64(len(v)), C.c_uint64(80), _p(t),
+                                                C.c_uint64(len(t)))
+        for mh in sorted(desc.materials):
+            mmap[mh] = L.orc_scene_add_material(self.h, C.byref(desc.materials[mh]))
+        for ih in sorted(desc.instances):
+            g, m, x, comp = desc.instances[ih]
+            x = np.ascontiguousarray(x, dtype=np.float32)
+            L.orc_scene_add_instance(self.h, gmap[g], mmap[m], _p(x), C.c_uint64(comp))
+        L.orc_scene_commit(self.h, morton_bits)
+        self.n_tris = int(L.orc_scene_ntris(self.h))
+        self.n_nodes = int(L.orc_scene_nnodes(self.h))
+        self.depth = int(L.orc_scene_depth(self.h))
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib().orc_scene_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def debug(self, what):
+        L = lib()
+        nbytes = int(L.orc_debug_size(self.h, what))
+        dt = S.DBG_DTYPES[what]
+        out = np.empty(nbytes // dt.itemsize, dtype=dt)
+        rc = L.orc_debug_read(self.h, what, _p(out), C.c_uint64(nbytes))
+        assert rc == 0
+        return out
+
+    def trace(self, rays, counts=False, nthreads=0):
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        n = len(rays)
+        hits = np.empty(n, dtype=S.HIT_DTYPE)
+        nv = np.empty(n, dtype=np.uint32) if counts else None
+        tv = np.empty(n, dtype=np.uint32) if counts else None
+        lib().orc_trace(self.h, _p(rays), C.c_uint64(n), _p(hits), _p(nv), _p(tv), nthreads)
+        return (hits, nv, tv) if counts else hits
+
+    def trace_brute(self, rays, nthreads=0):
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        hits = np.empty(len(rays), dtype=S.HIT_DTYPE)
+        lib().orc_trace_brute(self.h, _p(rays), C.c_uint64(len(rays)), _p(hits), nthreads)
+        return hits
+
+    def illum_mesh(self, env, rp, seed, push, front=True, back=True, tri_begin=0, tri_end=None, tri_stride=1,
+                   s0=0, s1=None, normalise=True, nthreads=0):
+        tri_end = self.n_tris if tri_end is None else tri_end
+        s1 = rp.samples if s1 is None else s1
+        cnt = max(0, (tri_end - tri_begin + tri_stride - 1) // tri_stride)
+        out = np.zeros((cnt, 6), dtype=np.float32)
+        st = S.JobStats()
+        lib().orc_illum_mesh(self.h, C.byref(env), C.byref(rp), C.c_uint32(seed), C.c_float(push), int(front),
+                             int(back), C.c_uint64(tri_begin), C.c_uint64(tri_end), C.c_uint64(tri_stride), s0, s1,
+                             int(normalise), _p(out), C.byref(st), nthreads)
+        return out, st
+
+    def illum_probes(self, env, rp, probes, seed, push, nthreads=0):
+        assert probes.dtype == S.ILLUM_SAMPLER_DTYPE and probes.flags.c_contiguous
+        st = S.JobStats()
+        lib().orc_illum_probes(self.h, C.byref(env), C.byref(rp), _p(probes), C.c_uint64(len(probes)),
+                               C.c_uint32(seed), C.c_float(push), C.byref(st), nthreads)
+        return st
+
+    def scan_point_cloud(self, samples, nthreads=0):
+        assert samples.dtype == S.PC_SAMPLE_DTYPE and samples.flags.c_contiguous
+        prim = np.empty(len(samples), dtype=np.uint32)
+        lib().orc_scan_point_cloud(self.h, _p(samples), C.c_uint64(len(samples)), _p(prim), nthreads)
+        return prim
+
+    def scan_grid(self, grid, ray_begin=0, ray_end=None, stride=1, nthreads=0):
+        total = int(lib().orc_scan_grid_count(C.byref(grid)))
+        ray_end = total if ray_end is None else ray_end
+        cnt = max(0, (ray_end - ray_begin + stride - 1) // stride)
+        t = np.empty(cnt, dtype=np.float32)
+        prim = np.empty(cnt, dtype=np.uint32)
+        inst = np.empty(cnt, dtype=np.uint32)
+        st = S.JobStats()
+        lib().orc_scan_grid(self.h, C.byref(grid), C.c_uint64(ray_begin), C.c_uint64(ray_end), C.c_uint64(stride),
+                            _p(t), _p(prim), _p(inst), C.byref(st), nthreads)
+        return t, prim, inst, st
+
+    def camera(self, env, rp, cam, pixel_begin=0, pixel_end=None, stride=1, prev_color=None, nthreads=0):
+        pixel_end = cam.width * cam.height if pixel_end is None else pixel_end
+        cnt = max(0, (pixel_end - pixel_begin + stride - 1) // stride)
+        color = np.empty((cnt, 4), dtype=np.float32)
+        normal = np.empty((cnt, 4), dtype=np.float32)
+        albedo = np.empty((cnt, 4), dtype=np.float32)
+        st = S.JobStats()
+        lib().orc_camera(self.h, C.byref(env), C.byref(rp), C.byref(cam), C.c_uint64(pixel_begin),
+                         C.c_uint64(pixel_end), C.c_uint64(stride), _p(prev_color), _p(color), _p(normal), _p(albedo),
+                         C.byref(st), nthreads)
+        return color, normal, albedo, st
+
+
+def scan_grid_count(grid):
+    return int(lib().orc_scan_grid_count(C.byref(grid)))
+
+
+def scan_grid_rays(grid, ray_begin, ray_end):
+    rays = np.empty((ray_end - ray_begin, 8), dtype=np.float32)
+    lib().orc_scan_grid_rays(C.byref(grid), C.c_uint64(ray_begin), C.c_uint64(ray_end), _p(rays))
+    return rays
