@@ -342,32 +342,34 @@ struct Hit {
   float t, u, v;
   uint32_t prim;  // 0xFFFFFFFF = miss
 };
-struct RayPrep {  // per-ray constants of the watertight test
-  int kx, ky, kz;
-  float Sx, Sy, Sz;
+struct RayPrep {  // per-ray shear matrix of the watertight test (axis permutation folded in)
+  float mx[3], my[3], mz[3];
 };
 static inline RayPrep prep_ray(V3 d) {
   float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
   int kz = (ax >= ay && ax >= az) ? 0 : (ay >= az ? 1 : 2);
-  int kx = (kz + 1) % 3, ky = (kx + 1) % 3;
+  int kx = (kz + 1) % 3, ky = (kz + 2) % 3;  // no winding swap: nothing is culled, the sign test is symmetric
   const float dd[3] = {d.x, d.y, d.z};
-  if (dd[kz] < 0.0f) std::swap(kx, ky);
   RayPrep r;
-  r.kx = kx, r.ky = ky, r.kz = kz;
-  r.Sz = 1.0f / dd[kz];
-  r.Sx = dd[kx] * r.Sz;
-  r.Sy = dd[ky] * r.Sz;
+  float Sz = 1.0f / dd[kz];
+  float Sx = dd[kx] * Sz;
+  float Sy = dd[ky] * Sz;
+  for (int a = 0; a < 3; a++) r.mx[a] = r.my[a] = r.mz[a] = 0.0f;
+  r.mx[kx] = 1.0f, r.mx[kz] = -Sx;
+  r.my[ky] = 1.0f, r.my[kz] = -Sy;
+  r.mz[kz] = Sz;
   return r;
 }
+static inline float shear_row(const float m[3], const float a[3]) { return fmaf(m[2], a[2], fmaf(m[1], a[1], m[0] * a[0])); }
 // Woop/Benthin/Wald 2013, no back-face culling.  Updates `best` if this triangle is the new
 // closest hit; equal t resolves to the lower primitive id.
 static inline bool intersect_tri(const Ray& ray, const RayPrep& rp, const Tri48& tri, Hit& best) {
   const float o[3] = {ray.o.x, ray.o.y, ray.o.z};
   float A[3], B[3], C[3];
   for (int a = 0; a < 3; a++) A[a] = tri.v0[a] - o[a], B[a] = tri.v1[a] - o[a], C[a] = tri.v2[a] - o[a];
-  const float Ax = fmaf(-rp.Sx, A[rp.kz], A[rp.kx]), Ay = fmaf(-rp.Sy, A[rp.kz], A[rp.ky]);
-  const float Bx = fmaf(-rp.Sx, B[rp.kz], B[rp.kx]), By = fmaf(-rp.Sy, B[rp.kz], B[rp.ky]);
-  const float Cx = fmaf(-rp.Sx, C[rp.kz], C[rp.kx]), Cy = fmaf(-rp.Sy, C[rp.kz], C[rp.ky]);
+  const float Ax = shear_row(rp.mx, A), Ay = shear_row(rp.my, A);
+  const float Bx = shear_row(rp.mx, B), By = shear_row(rp.my, B);
+  const float Cx = shear_row(rp.mx, C), Cy = shear_row(rp.my, C);
   float U = Cx * By - Cy * Bx;
   float V = Ax * Cy - Ay * Cx;
   float W = Bx * Ay - By * Ax;
@@ -379,7 +381,7 @@ static inline bool intersect_tri(const Ray& ray, const RayPrep& rp, const Tri48&
   if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
   const float det = (U + V) + W;
   if (det == 0.0f) return false;
-  const float Az = rp.Sz * A[rp.kz], Bz = rp.Sz * B[rp.kz], Cz = rp.Sz * C[rp.kz];
+  const float Az = shear_row(rp.mz, A), Bz = shear_row(rp.mz, B), Cz = shear_row(rp.mz, C);
   const float T = fmaf(U, Az, fmaf(V, Bz, W * Cz));
   const float rcp = 1.0f / det;
   const float t = T * rcp;

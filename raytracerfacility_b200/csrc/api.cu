@@ -1,0 +1,656 @@
+// api.cu — extern "C" boundary of librtf_b200.so (declared in include/rtf/rtf.h).
+//
+// Mirrors the module façade of the reference (layer L3): CudaModule::{Init, Terminate,
+// EstimateIlluminationRayTracing, SamplePointCloud} (/root/reference/src/RayTracerFacility/CUDAModule.cpp:23-64),
+// RayTracer::{RenderToCamera, BuildIAS} and the scene maps (RayTracer.hpp:358-394), CameraProperties::{Set, Resize}
+// (RayTracer.cu:28-92).  Status codes instead of exceptions / exit(2) (Optix7.hpp:10-56).
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+#include "rtf_internal.h"
+
+namespace rtf {
+
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  char buf[512];
+  snprintf(buf, sizeof(buf), "CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+  g_error = buf;
+  return RTF_ERR_CUDA;
+}
+int flatten_scene(rtf_ctx* ctx);  // build.cu
+
+}  // namespace rtf
+
+using namespace rtf;
+
+#define CHECK_CTX(ctx)                 \
+  if (!(ctx)) {                        \
+    set_error("null context");         \
+    return RTF_ERR_INVALID;            \
+  }                                    \
+  RTF_CUDA(cudaSetDevice((ctx)->device))
+
+extern "C" {
+
+const char* rtf_last_error(void) { return g_error.c_str(); }
+const char* rtf_version(void) { return "rtf-b200 0.1 (sm_100a)"; }
+
+int rtf_create(int device, rtf_ctx** out) {
+  if (!out) return RTF_ERR_INVALID;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    set_error("no CUDA device: librtf_b200 has no CPU fallback");
+    return RTF_ERR_CUDA;
+  }
+  if (device < 0 || device >= count) {
+    set_error("bad device index");
+    return RTF_ERR_INVALID;
+  }
+  RTF_CUDA(cudaSetDevice(device));
+  rtf_ctx* c = new rtf_ctx();
+  c->device = device;
+  RTF_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  c->own_stream = true;
+  cudaDeviceProp prop;
+  RTF_CUDA(cudaGetDeviceProperties(&prop, device));
+  c->sm_count = prop.multiProcessorCount;
+  *out = c;
+  return RTF_OK;
+}
+
+int rtf_destroy(rtf_ctx* ctx) {
+  if (!ctx) return RTF_OK;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  for (auto& g : ctx->geoms) g.second.d_verts.release(), g.second.d_tris.release();
+  DevBuf* bufs[] = {&ctx->d_pos9, &ctx->d_nrm9, &ctx->d_tri_inst, &ctx->d_nodes, &ctx->d_tris48, &ctx->d_insts, &ctx->d_mats,
+                    &ctx->d_inst_alpha, &ctx->d_stats, &ctx->ba.morton, &ctx->ba.sorted_keys, &ctx->ba.sorted_ids,
+                    &ctx->ba.children, &ctx->ba.parent, &ctx->ba.range, &ctx->ba.boxes, &ctx->ba.flags,
+                    &ctx->ba.scene_bounds, &ctx->ba.keys_alt, &ctx->ba.ids_alt, &ctx->ba.cub_tmp, &ctx->ba.level_a,
+                    &ctx->ba.level_b, &ctx->ba.cnt_int, &ctx->ba.cnt_tri, &ctx->ba.scan_int, &ctx->ba.scan_tri,
+                    &ctx->ba.stash, &ctx->ws.ray_a[0], &ctx->ws.ray_a[1], &ctx->ws.ray_b[0], &ctx->ws.ray_b[1],
+                    &ctx->ws.path_idx[0], &ctx->ws.path_idx[1], &ctx->ws.hits, &ctx->ws.counters, &ctx->ws.thr,
+                    &ctx->ws.acc, &ctx->ws.dir0w, &ctx->ws.first_n, &ctx->ws.first_a, &ctx->ws.first_p,
+                    &ctx->ws.sort_keys, &ctx->ws.sort_keys_alt, &ctx->ws.sort_vals, &ctx->ws.sort_vals_alt,
+                    &ctx->ws.sort_tmp, &ctx->ws.io};
+  for (DevBuf* b : bufs) b->release();
+  if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return RTF_OK;
+}
+
+int rtf_set_stream(rtf_ctx* ctx, void* cuda_stream) {
+  CHECK_CTX(ctx);
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+  if (cuda_stream) {
+    ctx->stream = (cudaStream_t)cuda_stream;
+    ctx->own_stream = false;
+  } else {
+    RTF_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    ctx->own_stream = true;
+  }
+  return RTF_OK;
+}
+uint64_t rtf_launch_count(rtf_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+// ---- scene sync --------------------------------------------------------------------------------------
+int rtf_set_geometry(rtf_ctx* ctx, uint64_t handle, const void* vertices, size_t n_vertices, size_t stride,
+                     const uint32_t* triangles, size_t n_triangles, uint64_t version) {
+  CHECK_CTX(ctx);
+  if ((!vertices && n_vertices) || (!triangles && n_triangles) || stride < sizeof(rtf_vertex)) {
+    set_error("rtf_set_geometry: bad arguments (vertex stride must be >= 80)");
+    return RTF_ERR_INVALID;
+  }
+  for (size_t i = 0; i < 3 * n_triangles; i++)
+    if (triangles[i] >= n_vertices) {
+      set_error("rtf_set_geometry: triangle index out of range");
+      return RTF_ERR_INVALID;
+    }
+  Geometry& g = ctx->geoms[handle];
+  g.verts.resize(n_vertices);
+  for (size_t i = 0; i < n_vertices; i++) memcpy(&g.verts[i], (const char*)vertices + i * stride, sizeof(rtf_vertex));
+  g.tris.assign(triangles, triangles + 3 * n_triangles);
+  g.version = version;
+  g.uploaded = false;
+  return RTF_OK;
+}
+int rtf_set_material(rtf_ctx* ctx, uint64_t handle, const rtf_material* material) {
+  CHECK_CTX(ctx);
+  if (!material) return RTF_ERR_INVALID;
+  if (material->material_type == RTF_MAT_COMPRESSED_BTF) {
+    set_error("CompressedBTF materials are a 'next' row (SURVEY N1), not built in this round");
+    return RTF_ERR_INVALID;
+  }
+  ctx->mats[handle] = *material;
+  return RTF_OK;
+}
+int rtf_set_instance(rtf_ctx* ctx, uint64_t handle, uint64_t geom, uint64_t mat, const float xform[16], uint64_t comp) {
+  CHECK_CTX(ctx);
+  if (!xform) return RTF_ERR_INVALID;
+  Instance& in = ctx->insts[handle];
+  in.geom = geom, in.mat = mat, in.component = comp;
+  memcpy(in.xform, xform, 64);
+  return RTF_OK;
+}
+int rtf_remove_geometry(rtf_ctx* ctx, uint64_t handle) {
+  CHECK_CTX(ctx);
+  auto it = ctx->geoms.find(handle);
+  if (it == ctx->geoms.end()) return RTF_ERR_NOT_FOUND;
+  cudaStreamSynchronize(ctx->stream);
+  it->second.d_verts.release(), it->second.d_tris.release();
+  ctx->geoms.erase(it);
+  return RTF_OK;
+}
+int rtf_remove_material(rtf_ctx* ctx, uint64_t handle) {
+  CHECK_CTX(ctx);
+  return ctx->mats.erase(handle) ? RTF_OK : RTF_ERR_NOT_FOUND;
+}
+int rtf_remove_instance(rtf_ctx* ctx, uint64_t handle) {
+  CHECK_CTX(ctx);
+  return ctx->insts.erase(handle) ? RTF_OK : RTF_ERR_NOT_FOUND;
+}
+
+int rtf_commit(rtf_ctx* ctx, int morton_bits) {
+  CHECK_CTX(ctx);
+  ctx->ready = false;
+  if (morton_bits == 0) morton_bits = 63;
+  if (morton_bits != 30 && morton_bits != 63) {
+    set_error("morton_bits must be 30 or 63");
+    return RTF_ERR_INVALID;
+  }
+  int rc;
+  cudaStream_t st = ctx->stream;
+  // materials -> dense table
+  std::map<uint64_t, uint32_t> mat_index;
+  std::vector<rtf_material> mats;
+  for (auto& m : ctx->mats) mat_index[m.first] = (uint32_t)mats.size(), mats.push_back(m.second);
+  // instances in ascending handle order = global primitive numbering
+  std::vector<InstDev> insts;
+  std::vector<float> alpha;
+  uint64_t first = 0;
+  for (auto& kv : ctx->insts) {
+    const Instance& in = kv.second;
+    auto g = ctx->geoms.find(in.geom);
+    auto m = mat_index.find(in.mat);
+    if (g == ctx->geoms.end() || m == mat_index.end()) {
+      set_error("instance references an unknown geometry or material");
+      return RTF_ERR_NOT_FOUND;
+    }
+    Geometry& geo = g->second;
+    if (!geo.uploaded) {
+      if ((rc = geo.d_verts.reserve(geo.verts.size() * sizeof(rtf_vertex)))) return rc;
+      if ((rc = geo.d_tris.reserve(geo.tris.size() * 4))) return rc;
+      RTF_CUDA(cudaMemcpyAsync(geo.d_verts.p, geo.verts.data(), geo.verts.size() * sizeof(rtf_vertex), cudaMemcpyHostToDevice, st));
+      RTF_CUDA(cudaMemcpyAsync(geo.d_tris.p, geo.tris.data(), geo.tris.size() * 4, cudaMemcpyHostToDevice, st));
+      geo.uploaded = true;
+    }
+    InstDev d;
+    memcpy(d.xform, in.xform, 64);
+    d.handle = in.component;
+    d.mat = m->second;
+    d.first_prim = (uint32_t)first;
+    d.n_prims = (uint32_t)(geo.tris.size() / 3);
+    d.pad_ = 0;
+    d.verts = geo.d_verts.as<rtf_vertex>();
+    d.tris = geo.d_tris.as<uint32_t>();
+    if (d.n_prims == 0) continue;  // nothing to trace; keeps first_prim strictly increasing
+    first += d.n_prims;
+    insts.push_back(d);
+    const rtf_material& mm = mats[d.mat];
+    alpha.push_back(mm.material_type == RTF_MAT_DEFAULT ? 1.0f - mm.transmission : 1.0f);  // RayDataDefinations.hpp:250
+  }
+  if (first >= 0xFFFFFFF0ull) {
+    set_error("more than 2^32 triangles");
+    return RTF_ERR_LIMIT;
+  }
+  ctx->n_tris = (uint32_t)first;
+  ctx->scene = DevScene();
+  if (first == 0) {  // reference: no acceleration structure -> entry points report "not ready"
+    return RTF_OK;
+  }
+  if ((rc = ctx->d_insts.reserve(insts.size() * sizeof(InstDev)))) return rc;
+  if ((rc = ctx->d_mats.reserve(mats.size() * sizeof(rtf_material)))) return rc;
+  if ((rc = ctx->d_inst_alpha.reserve(alpha.size() * 4))) return rc;
+  RTF_CUDA(cudaMemcpyAsync(ctx->d_insts.p, insts.data(), insts.size() * sizeof(InstDev), cudaMemcpyHostToDevice, st));
+  RTF_CUDA(cudaMemcpyAsync(ctx->d_mats.p, mats.data(), mats.size() * sizeof(rtf_material), cudaMemcpyHostToDevice, st));
+  RTF_CUDA(cudaMemcpyAsync(ctx->d_inst_alpha.p, alpha.data(), alpha.size() * 4, cudaMemcpyHostToDevice, st));
+  if ((rc = ctx->d_pos9.reserve(36 * (size_t)first))) return rc;
+  if ((rc = ctx->d_nrm9.reserve(36 * (size_t)first))) return rc;
+  if ((rc = ctx->d_tri_inst.reserve(4 * (size_t)first))) return rc;
+  ctx->scene.n_insts = (uint32_t)insts.size();
+  ctx->scene.insts = ctx->d_insts.as<InstDev>();
+  if ((rc = flatten_scene(ctx))) return rc;
+  RTF_CUDA(cudaStreamSynchronize(st));  // host vectors above die at return
+  if ((rc = build_bvh(ctx, morton_bits))) return rc;
+  {  // shrink the node array to its final size (collapse allocated the n/2 worst case)
+    DevBuf exact;
+    if ((rc = exact.reserve(80 * (size_t)ctx->n_nodes))) return rc;
+    RTF_CUDA(cudaMemcpyAsync(exact.p, ctx->d_nodes.p, 80 * (size_t)ctx->n_nodes, cudaMemcpyDeviceToDevice, st));
+    RTF_CUDA(cudaStreamSynchronize(st));
+    ctx->d_nodes.release();
+    ctx->d_nodes = exact;
+  }
+  ctx->morton_bits = morton_bits;
+  DevScene& s = ctx->scene;
+  s.nodes = ctx->d_nodes.as<uint4>(), s.tris = ctx->d_tris48.as<float4>();
+  s.pos9 = ctx->d_pos9.as<float>(), s.nrm9 = ctx->d_nrm9.as<float>(), s.tri_inst = ctx->d_tri_inst.as<uint32_t>();
+  s.mats = ctx->d_mats.as<rtf_material>(), s.inst_alpha = ctx->d_inst_alpha.as<float>();
+  s.n_tris = ctx->n_tris, s.n_nodes = ctx->n_nodes;
+  s.has_alpha = 0;
+  for (float a : alpha)
+    if (a < 1.0f) s.has_alpha = 1;
+  ctx->ready = true;
+  return RTF_OK;
+}
+int rtf_triangle_count(rtf_ctx* ctx, uint64_t* n) {
+  if (!ctx || !n) return RTF_ERR_INVALID;
+  *n = ctx->n_tris;
+  return RTF_OK;
+}
+
+static int fetch_stats(rtf_ctx* ctx) {
+  unsigned long long s[2] = {0, 0};
+  if (ctx->d_stats.p) RTF_CUDA(cudaMemcpy(s, ctx->d_stats.p, 16, cudaMemcpyDeviceToHost));
+  ctx->last_rays = s[0];
+  return RTF_OK;
+}
+static int not_ready() {
+  set_error("no acceleration structure (call rtf_commit)");
+  return RTF_ERR_NOT_READY;
+}
+
+// ---- illumination ----------------------------------------------------------------------------------------
+int rtf_estimate_illumination(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, rtf_illum_sampler* probes, size_t n,
+                              uint32_t seed, float push) {
+  CHECK_CTX(ctx);
+  if (!env || !rp || (!probes && n)) return RTF_ERR_INVALID;
+  if (!ctx->ready) return not_ready();  // reference: silent return (RayTracer.cu:610-611)
+  if (n == 0) return RTF_OK;            // reference: message + return (RayTracer.cu:612-615)
+  int rc;
+  cudaStream_t st = ctx->stream;
+  const size_t aos = n * sizeof(rtf_illum_sampler), acc = n * 24;
+  if ((rc = ctx->ws.io.reserve(aos + acc + 256))) return rc;
+  rtf_illum_sampler* d_probes = ctx->ws.io.as<rtf_illum_sampler>();
+  float* d_acc = (float*)((char*)ctx->ws.io.p + ((aos + 255) & ~(size_t)255));
+  RTF_CUDA(cudaMemcpyAsync(d_probes, probes, aos, cudaMemcpyHostToDevice, st));
+  RTF_CUDA(cudaMemsetAsync(d_acc, 0, acc, st));
+  if ((rc = illum_mesh_device(ctx, env, rp, seed, push, 1, 1, 0, n, 0, rp->samples, d_acc, d_probes, 0))) return rc;
+  if ((rc = illum_finalize_device(ctx, d_acc, n, 2, rp->samples, d_probes))) return rc;
+  RTF_CUDA(cudaMemcpyAsync(probes, d_probes, aos, cudaMemcpyDeviceToHost, st));
+  RTF_CUDA(cudaStreamSynchronize(st));
+  return fetch_stats(ctx);
+}
+
+int rtf_estimate_illumination_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push,
+                                          int front, int back, uint64_t tri_begin, uint64_t tri_end, int s0, int s1,
+                                          float* dev_accum6) {
+  CHECK_CTX(ctx);
+  if (!env || !rp || !dev_accum6) return RTF_ERR_INVALID;
+  if (!ctx->ready) return not_ready();
+  if (tri_end > ctx->n_tris || tri_begin > tri_end || s0 < 0 || s1 > rp->samples || s0 > s1) {
+    set_error("triangle or sample range out of bounds");
+    return RTF_ERR_INVALID;
+  }
+  return illum_mesh_device(ctx, env, rp, seed, push, front, back, tri_begin, tri_end, s0, s1, dev_accum6 + 6 * tri_begin,
+                           nullptr, 0);
+}
+int rtf_illumination_finalize_device(rtf_ctx* ctx, float* dev_accum6, uint64_t n, int faces, int samples) {
+  CHECK_CTX(ctx);
+  return illum_finalize_device(ctx, dev_accum6, n, faces, samples, nullptr);
+}
+int rtf_estimate_illumination_mesh(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push,
+                                   int front, int back, uint64_t tri_begin, uint64_t tri_end, int s0, int s1, int normalise,
+                                   float* out6) {
+  CHECK_CTX(ctx);
+  if (!env || !rp || !out6) return RTF_ERR_INVALID;
+  if (!ctx->ready) return not_ready();
+  if (tri_end > ctx->n_tris || tri_begin > tri_end || s0 < 0 || s1 > rp->samples || s0 > s1) {
+    set_error("triangle or sample range out of bounds");
+    return RTF_ERR_INVALID;
+  }
+  const uint64_t n = tri_end - tri_begin;
+  if (n == 0) return RTF_OK;
+  int rc;
+  if ((rc = ctx->ws.io.reserve(n * 24))) return rc;
+  float* d_acc = ctx->ws.io.as<float>();
+  RTF_CUDA(cudaMemsetAsync(d_acc, 0, n * 24, ctx->stream));
+  if ((rc = illum_mesh_device(ctx, env, rp, seed, push, front, back, tri_begin, tri_end, s0, s1, d_acc, nullptr, 0))) return rc;
+  if (normalise)
+    if ((rc = illum_finalize_device(ctx, d_acc, n, (front ? 1 : 0) + (back ? 1 : 0), s1 - s0, nullptr))) return rc;
+  RTF_CUDA(cudaMemcpyAsync(out6, d_acc, n * 24, cudaMemcpyDeviceToHost, ctx->stream));
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+  return fetch_stats(ctx);
+}
+int rtf_last_job_stats(rtf_ctx* ctx, uint64_t* rays, uint64_t* paths) {
+  CHECK_CTX(ctx);
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+  int rc = fetch_stats(ctx);
+  if (rc) return rc;
+  if (rays) *rays = ctx->last_rays;
+  if (paths) *paths = ctx->last_paths;
+  return RTF_OK;
+}
+
+// ---- LiDAR --------------------------------------------------------------------------------------------------
+int rtf_scan_point_cloud(rtf_ctx* ctx, const rtf_env* env, rtf_pc_sample* samples, size_t n, uint32_t* prim_ids_out) {
+  CHECK_CTX(ctx);
+  (void)env;  // the reference passes it but PCS never reads it (RayTracer.cu:758-795)
+  if (!samples && n) return RTF_ERR_INVALID;
+  if (!ctx->ready) return not_ready();
+  if (n == 0) return RTF_OK;
+  if (n >= 0xFFFFFFFFull) {
+    set_error("use rtf_scan_grid_trace for > 2^32 rays");
+    return RTF_ERR_LIMIT;
+  }
+  int rc;
+  const size_t aos = n * sizeof(rtf_pc_sample);
+  if ((rc = ctx->ws.io.reserve(aos + 256 + n * 4))) return rc;
+  rtf_pc_sample* d = ctx->ws.io.as<rtf_pc_sample>();
+  uint32_t* d_prim = (uint32_t*)((char*)ctx->ws.io.p + ((aos + 255) & ~(size_t)255));
+  RTF_CUDA(cudaMemcpyAsync(d, samples, aos, cudaMemcpyHostToDevice, ctx->stream));
+  if ((rc = scan_samples_device(ctx, d, n, d_prim))) return rc;
+  RTF_CUDA(cudaMemcpyAsync(samples, d, aos, cudaMemcpyDeviceToHost, ctx->stream));
+  if (prim_ids_out) RTF_CUDA(cudaMemcpyAsync(prim_ids_out, d_prim, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+  return RTF_OK;
+}
+int rtf_scan_grid_ray_count(const rtf_scan_grid* g, uint64_t* n) {
+  if (!g || !n) return RTF_ERR_INVALID;
+  *n = (uint64_t)(uint32_t)(g->size[0] / g->distance[0]) * (uint64_t)(uint32_t)(g->size[1] / g->distance[1]);
+  return RTF_OK;
+}
+int rtf_scan_grid_trace_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t b, uint64_t e, float* dev_t, uint32_t* dev_prim) {
+  CHECK_CTX(ctx);
+  if (!grid) return RTF_ERR_INVALID;
+  return scan_grid_device(ctx, grid, b, e, dev_t, dev_prim, nullptr);
+}
+int rtf_scan_grid_trace(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t b, uint64_t e, float* t_out, uint32_t* prim_out,
+                        uint32_t* inst_out) {
+  CHECK_CTX(ctx);
+  if (!grid) return RTF_ERR_INVALID;
+  if (!ctx->ready) return not_ready();
+  if (e <= b) return RTF_OK;
+  const uint64_t n = e - b;
+  int rc;
+  if ((rc = ctx->ws.io.reserve(n * 12))) return rc;
+  float* dt = ctx->ws.io.as<float>();
+  uint32_t* dp = (uint32_t*)(dt + n);
+  uint32_t* di = dp + n;
+  if ((rc = scan_grid_device(ctx, grid, b, e, dt, dp, di))) return rc;
+  if (t_out) RTF_CUDA(cudaMemcpyAsync(t_out, dt, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (prim_out) RTF_CUDA(cudaMemcpyAsync(prim_out, dp, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (inst_out) RTF_CUDA(cudaMemcpyAsync(inst_out, di, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+  return RTF_OK;
+}
+
+// ---- raw closest hit ------------------------------------------------------------------------------------------
+int rtf_trace_closest_device(rtf_ctx* ctx, const float* dev_rays, size_t n, void* dev_hits) {
+  CHECK_CTX(ctx);
+  if ((!dev_rays || !dev_hits) && n) return RTF_ERR_INVALID;
+  return trace_rays_device(ctx, (const float4*)dev_rays, (const float4*)dev_rays + 1, 2, n, (float4*)dev_hits, nullptr, nullptr);
+}
+int rtf_trace_closest_counts(rtf_ctx* ctx, const float* rays, size_t n, void* hits, uint32_t* node_visits, uint32_t* tri_visits) {
+  CHECK_CTX(ctx);
+  if ((!rays || !hits) && n) return RTF_ERR_INVALID;
+  if (!ctx->ready) return not_ready();
+  if (n == 0) return RTF_OK;
+  int rc;
+  const size_t rb = n * 32, hb = n * 16, cb = n * 4;
+  if ((rc = ctx->ws.io.reserve(rb + hb + 2 * cb))) return rc;
+  float4* dr = ctx->ws.io.as<float4>();
+  float4* dh = (float4*)((char*)ctx->ws.io.p + rb);
+  uint32_t* dn = (uint32_t*)((char*)ctx->ws.io.p + rb + hb);
+  uint32_t* dtv = dn + n;
+  const bool counts = node_visits || tri_visits;
+  RTF_CUDA(cudaMemcpyAsync(dr, rays, rb, cudaMemcpyHostToDevice, ctx->stream));
+  if ((rc = trace_rays_device(ctx, dr, dr + 1, 2, n, dh, counts ? dn : nullptr, counts ? dtv : nullptr))) return rc;
+  RTF_CUDA(cudaMemcpyAsync(hits, dh, hb, cudaMemcpyDeviceToHost, ctx->stream));
+  if (node_visits) RTF_CUDA(cudaMemcpyAsync(node_visits, dn, cb, cudaMemcpyDeviceToHost, ctx->stream));
+  if (tri_visits) RTF_CUDA(cudaMemcpyAsync(tri_visits, dtv, cb, cudaMemcpyDeviceToHost, ctx->stream));
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+  return RTF_OK;
+}
+int rtf_trace_closest(rtf_ctx* ctx, const float* rays, size_t n, void* hits) {
+  return rtf_trace_closest_counts(ctx, rays, n, hits, nullptr, nullptr);
+}
+
+// ---- camera -------------------------------------------------------------------------------------------------------
+int rtf_camera_create(rtf_ctx* ctx, rtf_camera** out) {
+  CHECK_CTX(ctx);
+  if (!out) return RTF_ERR_INVALID;
+  rtf_camera* c = new rtf_camera();
+  c->ctx = ctx;
+  memset(&c->props, 0, sizeof(c->props));
+  c->props.accumulate = 1, c->props.fov = 120.0f, c->props.max_distance = 50.0f, c->props.gamma = 2.2f;  // RayTracer.hpp:48-61
+  c->props.focal_length = 1.0f;
+  *out = c;
+  return RTF_OK;
+}
+int rtf_camera_destroy(rtf_camera* cam) {
+  if (!cam) return RTF_OK;
+  cudaSetDevice(cam->ctx->device);
+  cudaStreamSynchronize(cam->ctx->stream);
+  cam->color.release(), cam->normal.release(), cam->albedo.release();
+  delete cam;
+  return RTF_OK;
+}
+int rtf_camera_get_props(rtf_camera* cam, rtf_camera_props** props) {
+  if (!cam || !props) return RTF_ERR_INVALID;
+  *props = &cam->props;
+  return RTF_OK;
+}
+int rtf_camera_resize(rtf_camera* cam, int width, int height) {  // CameraProperties::Resize, RayTracer.cu:48-92
+  if (!cam || width < 0 || height < 0) return RTF_ERR_INVALID;
+  if (cam->props.width == width && cam->props.height == height) return RTF_OK;
+  RTF_CUDA(cudaSetDevice(cam->ctx->device));
+  RTF_CUDA(cudaStreamSynchronize(cam->ctx->stream));
+  cam->props.width = width, cam->props.height = height, cam->props.modified = 1;
+  const size_t bytes = (size_t)width * height * 16;
+  int rc;
+  if ((rc = cam->color.reserve(bytes)) || (rc = cam->normal.reserve(bytes)) || (rc = cam->albedo.reserve(bytes))) return rc;
+  return RTF_OK;
+}
+
+static void mat4_mul_d(const double* a, const double* b, double* c) {  // column-major c = a*b
+  for (int col = 0; col < 4; col++)
+    for (int row = 0; row < 4; row++) {
+      double s = 0;
+      for (int k = 0; k < 4; k++) s += a[k * 4 + row] * b[col * 4 + k];
+      c[col * 4 + row] = s;
+    }
+}
+static bool mat4_inverse_d(const double* m, double* inv) {
+  double a[4][8];
+  for (int r = 0; r < 4; r++)
+    for (int c = 0; c < 4; c++) a[r][c] = m[c * 4 + r], a[r][4 + c] = r == c ? 1.0 : 0.0;
+  for (int i = 0; i < 4; i++) {
+    int piv = i;
+    for (int r = i + 1; r < 4; r++)
+      if (fabs(a[r][i]) > fabs(a[piv][i])) piv = r;
+    if (a[piv][i] == 0.0) return false;
+    if (piv != i)
+      for (int c = 0; c < 8; c++) std::swap(a[i][c], a[piv][c]);
+    const double d = a[i][i];
+    for (int c = 0; c < 8; c++) a[i][c] /= d;
+    for (int r = 0; r < 4; r++)
+      if (r != i) {
+        const double f = a[r][i];
+        for (int c = 0; c < 8; c++) a[r][c] -= f * a[i][c];
+      }
+  }
+  for (int r = 0; r < 4; r++)
+    for (int c = 0; c < 4; c++) inv[c * 4 + r] = a[r][4 + c];
+  return true;
+}
+// CameraProperties::Set, RayTracer.cu:28-46.  Host-side setup math is done in double and rounded once.
+int rtf_camera_set(rtf_camera* cam, const float position[3], const float q[4]) {
+  if (!cam || !position || !q) return RTF_ERR_INVALID;
+  rtf_camera_props& p = cam->props;
+  if (p.width <= 0 || p.height <= 0) {
+    set_error("resize the camera before Set");
+    return RTF_ERR_INVALID;
+  }
+  const double w = q[0], x = q[1], y = q[2], z = q[3];
+  auto rot = [&](const double v[3], double o[3]) {  // glm quat * vec3
+    const double uv[3] = {y * v[2] - z * v[1], z * v[0] - x * v[2], x * v[1] - y * v[0]};
+    const double uuv[3] = {y * uv[2] - z * uv[1], z * uv[0] - x * uv[2], x * uv[1] - y * uv[0]};
+    for (int k = 0; k < 3; k++) o[k] = v[k] + (uv[k] * w + uuv[k]) * 2.0;
+  };
+  auto norm = [](double v[3]) {
+    const double l = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    v[0] /= l, v[1] /= l, v[2] /= l;
+  };
+  const double f0[3] = {0, 0, -1}, u0[3] = {0, 1, 0};
+  double front[3], up[3];
+  rot(f0, front), rot(u0, up);
+  norm(front), norm(up);
+  const double aspect = (double)p.width / (double)p.height;
+  const double half_fov = (double)(p.fov * 0.5f) * (M_PI / 180.0);  // radians(m_fov * 0.5f): the halved fov quirk
+  const double th = tan(half_fov / 2.0), zn = 0.1, zf = 100.0;
+  double proj[16] = {0};
+  proj[0] = 1.0 / (aspect * th), proj[5] = 1.0 / th, proj[10] = -(zf + zn) / (zf - zn), proj[11] = -1.0;
+  proj[14] = -(2.0 * zf * zn) / (zf - zn);
+  const double eye[3] = {position[0], position[1], position[2]};
+  double s[3] = {front[1] * up[2] - front[2] * up[1], front[2] * up[0] - front[0] * up[2], front[0] * up[1] - front[1] * up[0]};
+  norm(s);
+  const double u[3] = {s[1] * front[2] - s[2] * front[1], s[2] * front[0] - s[0] * front[2], s[0] * front[1] - s[1] * front[0]};
+  double view[16] = {0};
+  view[0] = s[0], view[4] = s[1], view[8] = s[2];
+  view[1] = u[0], view[5] = u[1], view[9] = u[2];
+  view[2] = -front[0], view[6] = -front[1], view[10] = -front[2];
+  view[12] = -(s[0] * eye[0] + s[1] * eye[1] + s[2] * eye[2]);
+  view[13] = -(u[0] * eye[0] + u[1] * eye[1] + u[2] * eye[2]);
+  view[14] = front[0] * eye[0] + front[1] * eye[1] + front[2] * eye[2];
+  view[15] = 1.0;
+  double pv[16], inv[16];
+  mat4_mul_d(proj, view, pv);
+  if (!mat4_inverse_d(pv, inv)) {
+    set_error("singular projection*view");
+    return RTF_ERR_INVALID;
+  }
+  bool changed = false;
+  for (int k = 0; k < 16; k++) {
+    const float v = (float)inv[k];
+    if (v != p.inverse_projection_view[k]) changed = true;
+    p.inverse_projection_view[k] = v;
+  }
+  if (changed) p.modified = 1;
+  for (int k = 0; k < 3; k++) p.from[k] = position[k];
+  double hv[3] = {front[1] * up[2] - front[2] * up[1], front[2] * up[0] - front[0] * up[2], front[0] * up[1] - front[1] * up[0]};
+  norm(hv);
+  for (int k = 0; k < 3; k++) {
+    p.horizontal[k] = (float)(half_fov * aspect * hv[k]);  // "cosFovY" is the angle in radians, RayTracer.cu:40-45
+    p.vertical[k] = (float)(half_fov * up[k]);
+  }
+  return RTF_OK;
+}
+
+struct CamLast {
+  rtf_env env;
+  rtf_ray_props rp;
+  bool valid = false;
+};
+static std::map<rtf_ctx*, CamLast> g_cam_last;  // m_cameraRenderingLaunchParams.m_rayTracerProperties, RayTracer.cu:259-266
+
+int rtf_render_camera(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp) {
+  CHECK_CTX(ctx);
+  if (!env || !cam || !rp) return RTF_ERR_INVALID;
+  rtf_camera_props& p = cam->props;
+  if (p.width == 0 || p.height == 0) return 1;  // RayTracer.cu:246-247
+  if (!ctx->ready) return 0;                    // RayTracer.cu:248-249
+  CamLast& last = g_cam_last[ctx];
+  bool changed = p.modified != 0;
+  p.modified = 0;
+  if (!last.valid || memcmp(&last.env, env, sizeof(rtf_env)) != 0) last.env = *env, changed = true;
+  if (!last.valid || last.rp.bounces != rp->bounces || last.rp.samples != rp->samples) last.rp = *rp, changed = true;
+  last.valid = true;
+  if (!p.accumulate || changed) p.frame_id = 0;  // RayTracer.cu:266-269
+  int rc = render_camera_device(ctx, env, cam, rp);  // launch sees the frame id before the increment (RayTracer.cu:349-352)
+  if (rc) return rc;
+  p.frame_id++;
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+  if ((rc = fetch_stats(ctx))) return rc;
+  return 1;
+}
+int rtf_camera_device_buffer(rtf_camera* cam, int which, float** dev) {
+  if (!cam || !dev) return RTF_ERR_INVALID;
+  *dev = which == RTF_OUT_COLOR ? cam->color.as<float>() : (which == RTF_OUT_NORMAL ? cam->normal.as<float>() : cam->albedo.as<float>());
+  return RTF_OK;
+}
+int rtf_camera_download(rtf_camera* cam, int which, float* host) {
+  if (!cam || !host) return RTF_ERR_INVALID;
+  RTF_CUDA(cudaSetDevice(cam->ctx->device));
+  float* d = nullptr;
+  rtf_camera_device_buffer(cam, which, &d);
+  const size_t bytes = (size_t)cam->props.width * cam->props.height * 16;
+  RTF_CUDA(cudaMemcpyAsync(host, d, bytes, cudaMemcpyDeviceToHost, cam->ctx->stream));
+  RTF_CUDA(cudaStreamSynchronize(cam->ctx->stream));
+  return RTF_OK;
+}
+
+// ---- parity read-back ----------------------------------------------------------------------------------------------
+static const void* dbg_ptr(rtf_ctx* c, int what, uint64_t* bytes) {
+  const uint64_t n = c->n_tris, ni = n ? n - 1 : 0;
+  switch (what) {
+    case RTF_DBG_MORTON: *bytes = n * 8; return c->ba.morton.p;
+    case RTF_DBG_SORTED_IDS: *bytes = n * 4; return c->ba.sorted_ids.p;
+    case RTF_DBG_BIN_CHILDREN: *bytes = ni * 8; return c->ba.children.p;
+    case RTF_DBG_BIN_PARENT: *bytes = (n ? 2 * n - 1 : 0) * 4; return c->ba.parent.p;
+    case RTF_DBG_BIN_BOXES: *bytes = (n ? 2 * n - 1 : 0) * 24; return c->ba.boxes.p;
+    case RTF_DBG_WIDE_NODES: *bytes = (uint64_t)c->n_nodes * 80; return c->d_nodes.p;
+    case RTF_DBG_WIDE_TRIS: *bytes = n * 48; return c->d_tris48.p;
+    case RTF_DBG_FLAT_POS: *bytes = n * 36; return c->d_pos9.p;
+    case RTF_DBG_FLAT_NRM: *bytes = n * 36; return c->d_nrm9.p;
+    case RTF_DBG_FLAT_INST: *bytes = n * 4; return c->d_tri_inst.p;
+    case RTF_DBG_SCENE_BOUNDS: *bytes = 24; return c->ba.scene_bounds.p ? (char*)c->ba.scene_bounds.p + 32 : nullptr;
+  }
+  *bytes = 0;
+  return nullptr;
+}
+int rtf_debug_size(rtf_ctx* ctx, int what, uint64_t* bytes) {
+  if (!ctx || !bytes) return RTF_ERR_INVALID;
+  dbg_ptr(ctx, what, bytes);
+  return RTF_OK;
+}
+int rtf_debug_read(rtf_ctx* ctx, int what, void* out, uint64_t bytes) {
+  CHECK_CTX(ctx);
+  uint64_t b = 0;
+  const void* p = dbg_ptr(ctx, what, &b);
+  if (bytes < b || (b && !p)) return RTF_ERR_INVALID;
+  if (b) {
+    RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+    RTF_CUDA(cudaMemcpy(out, p, b, cudaMemcpyDeviceToHost));
+  }
+  return RTF_OK;
+}
+int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* nodes, uint64_t n_nodes, const void* tris, uint64_t n_tris, int depth) {
+  CHECK_CTX(ctx);
+  if (!nodes || !tris || depth > kMaxStackDepth) return RTF_ERR_INVALID;
+  int rc;
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+  if ((rc = ctx->d_nodes.reserve(n_nodes * 80)) || (rc = ctx->d_tris48.reserve(n_tris * 48))) return rc;
+  RTF_CUDA(cudaMemcpy(ctx->d_nodes.p, nodes, n_nodes * 80, cudaMemcpyHostToDevice));
+  RTF_CUDA(cudaMemcpy(ctx->d_tris48.p, tris, n_tris * 48, cudaMemcpyHostToDevice));
+  ctx->scene.nodes = ctx->d_nodes.as<uint4>(), ctx->scene.tris = ctx->d_tris48.as<float4>();
+  ctx->n_nodes = (uint32_t)n_nodes, ctx->depth = depth;
+  ctx->scene.n_nodes = (uint32_t)n_nodes;
+  if (!ctx->ready) ctx->n_tris = (uint32_t)n_tris, ctx->scene.n_tris = (uint32_t)n_tris;
+  ctx->ready = true;
+  return RTF_OK;
+}
+int rtf_microbench_fp32(rtf_ctx* ctx, double* tflops) {
+  CHECK_CTX(ctx);
+  return microbench_fp32(ctx, tflops);
+}
+int rtf_microbench_l2(rtf_ctx* ctx, double bytes, double* gbs) {
+  CHECK_CTX(ctx);
+  return microbench_l2(ctx, bytes, gbs);
+}
+
+}  // extern "C"

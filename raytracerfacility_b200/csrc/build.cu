@@ -1,0 +1,449 @@
+// build.cu — device LBVH builder: flatten -> bounds -> Morton 30/63 -> radix sort -> Karras radix tree ->
+// refit -> breadth-first greedy surface-area collapse to 8-wide -> quantised 80 B node encode.
+//
+// Replaces RayTracedGeometry::BuildGAS + RayTracer::BuildIAS of the reference
+// (/root/reference/src/RayTracerFacility/RayTracer.cu:1251-1598, :1618-1715: optixAccelBuild +
+// optixAccelCompact, three device syncs and one D2H per geometry) and the instanced pre-bake kernel
+// CopyVerticesInstancedKernel (RayTracer.cu:1148-1175) with a single world-space triangle soup.
+//
+// Every stage is an integer or exactly-rounded float computation, so tests compare each array bit for
+// bit with the CPU oracle (Morton codes, sorted order, radix-tree links, boxes, wide nodes, triangles).
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+#include "rtf_internal.h"
+
+namespace rtf {
+
+#define LAUNCH(ctx, kernel, grid, block, smem, ...)                      \
+  do {                                                                   \
+    kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);     \
+    (ctx)->launches++;                                                   \
+  } while (0)
+
+static inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
+
+// ---- 1. flatten instances to world space (TriangleIlluminationEstimator.cpp:110-118 semantics:
+//         position = M*(p,1), normal = M*(n,0) NOT renormalised) ---------------------------------
+__global__ void k_flatten(const InstDev* __restrict__ insts, uint32_t n_insts, uint32_t n_tris, float* __restrict__ pos9,
+                          float* __restrict__ nrm9, uint32_t* __restrict__ tri_inst) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_tris) return;
+  uint32_t lo = 0, hi = n_insts;  // last instance with first_prim <= t
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (insts[mid].first_prim <= t)
+      lo = mid;
+    else
+      hi = mid;
+  }
+  const InstDev& in = insts[lo];
+  const uint32_t lt = t - in.first_prim;
+  float m[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) m[k] = in.xform[k];
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    const rtf_vertex& v = in.verts[in.tris[3 * lt + k]];
+    const float3 p = mat4_mul(m, f3(v.position[0], v.position[1], v.position[2]), 1.0f);
+    const float3 n = mat4_mul(m, f3(v.normal[0], v.normal[1], v.normal[2]), 0.0f);
+    float* po = pos9 + 9 * (size_t)t + 3 * k;
+    float* no = nrm9 + 9 * (size_t)t + 3 * k;
+    po[0] = p.x, po[1] = p.y, po[2] = p.z;
+    no[0] = n.x, no[1] = n.y, no[2] = n.z;
+  }
+  tri_inst[t] = lo;
+}
+
+// ---- 2. scene bounds: ordered-int atomics (min/max are exact, any order gives the same bits) ------
+__device__ __forceinline__ int float_to_ordered(float f) {
+  int i = __float_as_int(f);
+  return i >= 0 ? i : i ^ 0x7fffffff;
+}
+__device__ __forceinline__ float ordered_to_float(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
+__device__ __forceinline__ Box3 tri_box(const float* __restrict__ pos9, uint32_t t) {
+  const float* p = pos9 + 9 * (size_t)t;
+  const float3 a = f3(p[0], p[1], p[2]), b = f3(p[3], p[4], p[5]), c = f3(p[6], p[7], p[8]);
+  Box3 bx;
+  bx.lo = min3(min3(a, b), c);
+  bx.hi = max3(max3(a, b), c);
+  return bx;
+}
+
+__global__ void k_bounds_init(int* ob) {
+  if (threadIdx.x < 3) ob[threadIdx.x] = float_to_ordered(INFINITY);
+  else if (threadIdx.x < 6) ob[threadIdx.x] = float_to_ordered(-INFINITY);
+}
+__global__ void k_bounds(const float* __restrict__ pos9, uint32_t n, int* __restrict__ ob) {
+  float3 lo = f3(INFINITY, INFINITY, INFINITY), hi = f3(-INFINITY, -INFINITY, -INFINITY);
+  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const Box3 b = tri_box(pos9, t);
+    lo = min3(lo, b.lo), hi = max3(hi, b.hi);
+  }
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    lo.x = fminf(lo.x, __shfl_xor_sync(0xffffffffu, lo.x, off));
+    lo.y = fminf(lo.y, __shfl_xor_sync(0xffffffffu, lo.y, off));
+    lo.z = fminf(lo.z, __shfl_xor_sync(0xffffffffu, lo.z, off));
+    hi.x = fmaxf(hi.x, __shfl_xor_sync(0xffffffffu, hi.x, off));
+    hi.y = fmaxf(hi.y, __shfl_xor_sync(0xffffffffu, hi.y, off));
+    hi.z = fmaxf(hi.z, __shfl_xor_sync(0xffffffffu, hi.z, off));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMin(ob + 0, float_to_ordered(lo.x)), atomicMin(ob + 1, float_to_ordered(lo.y));
+    atomicMin(ob + 2, float_to_ordered(lo.z)), atomicMax(ob + 3, float_to_ordered(hi.x));
+    atomicMax(ob + 4, float_to_ordered(hi.y)), atomicMax(ob + 5, float_to_ordered(hi.z));
+  }
+}
+__global__ void k_bounds_finish(const int* ob, float* fb) {
+  if (threadIdx.x < 6) fb[threadIdx.x] = ordered_to_float(ob[threadIdx.x]);
+}
+
+// ---- 3. Morton codes ---------------------------------------------------------------------------
+__global__ void k_morton(const float* __restrict__ pos9, uint32_t n, const float* __restrict__ fb, int bits,
+                         uint64_t* __restrict__ keys, uint32_t* __restrict__ ids) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const float3 lo = f3(fb[0], fb[1], fb[2]), hi = f3(fb[3], fb[4], fb[5]);
+  const float3 ext = hi - lo;
+  const float3 inv = f3(ext.x > 0 ? 1.0f / ext.x : 0.0f, ext.y > 0 ? 1.0f / ext.y : 0.0f, ext.z > 0 ? 1.0f / ext.z : 0.0f);
+  const Box3 b = tri_box(pos9, t);
+  const float3 c = (b.lo + b.hi) * 0.5f;
+  keys[t] = morton_code(c, lo, inv, bits);
+  ids[t] = t;
+}
+
+// ---- 5. Karras 2012 radix tree -------------------------------------------------------------------
+__device__ __forceinline__ int karras_delta(const uint64_t* __restrict__ keys, int n, int i, int j) {
+  if (j < 0 || j >= n) return -1;
+  const uint64_t a = keys[i], b = keys[j];
+  if (a == b) return 64 + __clz((int)((uint32_t)i ^ (uint32_t)j));
+  return __clzll((long long)(a ^ b));
+}
+__global__ void k_karras(const uint64_t* __restrict__ keys, int n, int2* __restrict__ children, int* __restrict__ parent,
+                         uint2* __restrict__ range) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int ni = n - 1;
+  if (i >= ni) return;
+  const int d = (karras_delta(keys, n, i, i + 1) - karras_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+  const int dmin = karras_delta(keys, n, i, i - d);
+  int lmax = 2;
+  while (karras_delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+  int l = 0;
+  for (int t = lmax / 2; t >= 1; t /= 2)
+    if (karras_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+  const int j = i + l * d;
+  const int dnode = karras_delta(keys, n, i, j);
+  int s = 0, t = l;
+  do {
+    t = (t + 1) >> 1;
+    if (karras_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+  } while (t > 1);
+  const int gamma = i + s * d + min(d, 0);
+  const int lo = min(i, j), hi = max(i, j);
+  const int left = (lo == gamma) ? ~gamma : gamma;
+  const int right = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+  children[i] = make_int2(left, right);
+  range[i] = make_uint2((uint32_t)lo, (uint32_t)hi);
+  parent[left >= 0 ? left : (ni + ~left)] = i;
+  parent[right >= 0 ? right : (ni + ~right)] = i;
+  if (i == 0) parent[0] = -1;
+}
+
+// ---- 6. bottom-up refit: second arriver at a node merges its children (boxes: 6 floats per node,
+//         internals [0,n-1), leaves [n-1,2n-1)) -----------------------------------------------------
+__global__ void k_refit(const float* __restrict__ pos9, const uint32_t* __restrict__ sorted_ids, int n,
+                        const int2* __restrict__ children, const int* __restrict__ parent, float* boxes,
+                        uint32_t* __restrict__ flags) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int ni = n - 1;
+  const Box3 b = tri_box(pos9, sorted_ids[k]);
+  float* bo = boxes + 6 * (size_t)(ni + k);
+  bo[0] = b.lo.x, bo[1] = b.lo.y, bo[2] = b.lo.z, bo[3] = b.hi.x, bo[4] = b.hi.y, bo[5] = b.hi.z;
+  int node = parent[ni + k];
+  while (node >= 0) {
+    __threadfence();
+    if (atomicAdd(flags + node, 1u) == 0u) return;  // first arriver leaves
+    const int2 ch = children[node];
+    const volatile float* bl = boxes + 6 * (size_t)(ch.x >= 0 ? ch.x : ni + ~ch.x);
+    const volatile float* br = boxes + 6 * (size_t)(ch.y >= 0 ? ch.y : ni + ~ch.y);
+    volatile float* bn = boxes + 6 * (size_t)node;
+    bn[0] = fminf(bl[0], br[0]), bn[1] = fminf(bl[1], br[1]), bn[2] = fminf(bl[2], br[2]);
+    bn[3] = fmaxf(bl[3], br[3]), bn[4] = fmaxf(bl[4], br[4]), bn[5] = fmaxf(bl[5], br[5]);
+    node = parent[node];
+  }
+}
+
+// ---- 7. collapse to 8-wide, one breadth-first level per launch pair ---------------------------------
+struct CollapseArgs {
+  const int2* children;
+  const uint2* range;
+  const float* boxes;
+  int n;
+};
+__device__ __forceinline__ Box3 load_box(const float* __restrict__ boxes, int ni, int c) {
+  const float* b = boxes + 6 * (size_t)(c >= 0 ? c : ni + ~c);
+  Box3 r;
+  r.lo = f3(b[0], b[1], b[2]), r.hi = f3(b[3], b[4], b[5]);
+  return r;
+}
+constexpr int kEmptySlot = 0x7fffffff;
+
+// Pass A: greedy expansion by largest half-area + greedy octant slot assignment; stash the binary child
+// of every slot and count internal children / leaf triangles.
+__global__ void k_collapse_plan(CollapseArgs a, const int* __restrict__ level, uint32_t level_n, int* __restrict__ stash,
+                                uint32_t* __restrict__ cnt_int, uint32_t* __restrict__ cnt_tri) {
+  const uint32_t li = blockIdx.x * blockDim.x + threadIdx.x;
+  if (li >= level_n) return;
+  const int ni = a.n - 1;
+  const int R = level[li];
+  int ch[8];
+  int nc;
+  if (R < 0) {
+    ch[0] = R, nc = 1;
+  } else {
+    const int2 c2 = a.children[R];
+    ch[0] = c2.x, ch[1] = c2.y, nc = 2;
+  }
+  while (nc < 8) {
+    int best = -1;
+    float best_area = -INFINITY;
+    for (int i = 0; i < nc; i++) {
+      if (ch[i] < 0) continue;
+      const float ar = half_area(load_box(a.boxes, ni, ch[i]));
+      if (ar > best_area) best_area = ar, best = i;
+    }
+    if (best < 0) break;
+    const int2 c2 = a.children[ch[best]];
+    ch[best] = c2.x;
+    ch[nc++] = c2.y;
+  }
+  const Box3 nb = load_box(a.boxes, ni, R);
+  const float3 center = (nb.lo + nb.hi) * 0.5f;
+  float3 dv[8];
+  for (int i = 0; i < nc; i++) {
+    const Box3 cb = load_box(a.boxes, ni, ch[i]);
+    dv[i] = (cb.lo + cb.hi) * 0.5f - center;
+  }
+  int slot_of[8], child_in_slot[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) slot_of[i] = -1, child_in_slot[i] = -1;
+  for (int it = 0; it < nc; it++) {
+    float best = -INFINITY;
+    int bi = -1, bs = -1;
+    for (int i = 0; i < nc; i++) {
+      if (slot_of[i] >= 0) continue;
+      for (int s = 0; s < 8; s++) {
+        if (child_in_slot[s] >= 0) continue;
+        const float cost = (((s & 4) ? dv[i].x : -dv[i].x) + ((s & 2) ? dv[i].y : -dv[i].y)) + ((s & 1) ? dv[i].z : -dv[i].z);
+        if (bi < 0 || cost > best) best = cost, bi = i, bs = s;
+      }
+    }
+    slot_of[bi] = bs;
+    child_in_slot[bs] = bi;
+  }
+  uint32_t ci = 0, ct = 0;
+  for (int s = 0; s < 8; s++) {
+    const int i = child_in_slot[s];
+    int c = kEmptySlot;
+    if (i >= 0) {
+      c = ch[i];
+      const uint32_t cnt = c >= 0 ? (a.range[c].y - a.range[c].x + 1u) : 1u;
+      if (c >= 0 && cnt > 3u)
+        ci++;
+      else
+        ct += cnt;
+    }
+    stash[8 * (size_t)li + s] = c;
+  }
+  cnt_int[li] = ci;
+  cnt_tri[li] = ct;
+}
+
+// Pass B: encode the node, emit its triangles and the next level's roots.
+__global__ void k_collapse_emit(CollapseArgs a, const int* __restrict__ level, uint32_t level_n, const int* __restrict__ stash,
+                                const uint32_t* __restrict__ scan_int, const uint32_t* __restrict__ scan_tri,
+                                uint32_t level_start, uint32_t next_start, uint32_t tri_cursor, int* __restrict__ next_level,
+                                Node80* __restrict__ nodes, Tri48* __restrict__ tris, const float* __restrict__ pos9,
+                                const uint32_t* __restrict__ tri_inst, const uint32_t* __restrict__ sorted_ids,
+                                const float* __restrict__ inst_alpha) {
+  const uint32_t li = blockIdx.x * blockDim.x + threadIdx.x;
+  if (li >= level_n) return;
+  const int ni = a.n - 1;
+  const int R = level[li];
+  const Box3 nb = load_box(a.boxes, ni, R);
+  Node80 node;
+  node.p[0] = nb.lo.x, node.p[1] = nb.lo.y, node.p[2] = nb.lo.z;
+  const float3 ext = nb.hi - nb.lo;
+  const uint32_t e[3] = {quant_exponent(ext.x), quant_exponent(ext.y), quant_exponent(ext.z)};
+  node.e[0] = (uint8_t)e[0], node.e[1] = (uint8_t)e[1], node.e[2] = (uint8_t)e[2];
+  node.imask = 0;
+  const uint32_t child_off = scan_int[li];
+  node.child_base = next_start + child_off;
+  node.tri_base = tri_cursor + scan_tri[li];
+  uint32_t tri_off = 0, int_off = 0;
+  for (int s = 0; s < 8; s++) {
+    const int c = stash[8 * (size_t)li + s];
+    node.meta[s] = 0;
+    node.qlo[0][s] = node.qlo[1][s] = node.qlo[2][s] = 0;
+    node.qhi[0][s] = node.qhi[1][s] = node.qhi[2][s] = 0;
+    if (c == kEmptySlot) continue;
+    const Box3 cb = load_box(a.boxes, ni, c);
+    quantize_interval(cb.lo.x, cb.hi.x, node.p[0], e[0], node.qlo[0][s], node.qhi[0][s]);
+    quantize_interval(cb.lo.y, cb.hi.y, node.p[1], e[1], node.qlo[1][s], node.qhi[1][s]);
+    quantize_interval(cb.lo.z, cb.hi.z, node.p[2], e[2], node.qlo[2][s], node.qhi[2][s]);
+    const uint32_t cnt = c >= 0 ? (a.range[c].y - a.range[c].x + 1u) : 1u;
+    if (c >= 0 && cnt > 3u) {
+      node.imask |= (uint8_t)(1u << s);
+      node.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
+      next_level[child_off + int_off] = c;
+      int_off++;
+    } else {
+      const uint32_t unary = cnt == 1u ? 1u : (cnt == 2u ? 3u : 7u);
+      node.meta[s] = (uint8_t)((unary << 5) | tri_off);
+      const uint32_t first = c >= 0 ? a.range[c].x : (uint32_t)~c;
+      for (uint32_t j = 0; j < cnt; j++) {
+        const uint32_t prim = sorted_ids[first + j];
+        const float* p = pos9 + 9 * (size_t)prim;
+        Tri48 T;
+        T.v0[0] = p[0], T.v0[1] = p[1], T.v0[2] = p[2];
+        T.v1[0] = p[3], T.v1[1] = p[4], T.v1[2] = p[5];
+        T.v2[0] = p[6], T.v2[1] = p[7], T.v2[2] = p[8];
+        T.prim = prim;
+        T.inst = tri_inst[prim];
+        T.flags = (inst_alpha && inst_alpha[T.inst] < 1.0f) ? (uint32_t)TRI_FLAG_ALPHA : 0u;
+        tris[node.tri_base + tri_off + j] = T;
+      }
+      tri_off += cnt;
+    }
+  }
+  nodes[level_start + li] = node;
+}
+
+int flatten_scene(rtf_ctx* ctx) {
+  const uint32_t n = ctx->n_tris;
+  if (n == 0) return RTF_OK;
+  LAUNCH(ctx, k_flatten, div_up(n, 256), 256, 0, ctx->scene.insts, ctx->scene.n_insts, n, ctx->d_pos9.as<float>(),
+         ctx->d_nrm9.as<float>(), ctx->d_tri_inst.as<uint32_t>());
+  RTF_CUDA(cudaGetLastError());
+  return RTF_OK;
+}
+
+int build_bvh(rtf_ctx* ctx, int bits) {
+  const uint32_t n = ctx->n_tris;
+  BuildArrays& ba = ctx->ba;
+  cudaStream_t st = ctx->stream;
+  ctx->n_nodes = 0, ctx->depth = 0;
+  if (n == 0) return RTF_OK;
+  const int ni = (int)n - 1;
+  int rc;
+  if ((rc = ba.scene_bounds.reserve(64))) return rc;
+  if ((rc = ba.morton.reserve(8 * (size_t)n))) return rc;
+  if ((rc = ba.sorted_keys.reserve(8 * (size_t)n))) return rc;
+  if ((rc = ba.sorted_ids.reserve(4 * (size_t)n))) return rc;
+  if ((rc = ba.ids_alt.reserve(4 * (size_t)n))) return rc;
+  if ((rc = ba.children.reserve(8 * (size_t)n))) return rc;
+  if ((rc = ba.parent.reserve(4 * (size_t)(2 * n)))) return rc;
+  if ((rc = ba.range.reserve(8 * (size_t)n))) return rc;
+  if ((rc = ba.boxes.reserve(24 * (size_t)(2 * n)))) return rc;
+  if ((rc = ba.flags.reserve(4 * (size_t)n))) return rc;
+
+  int* ob = ba.scene_bounds.as<int>();
+  float* fb = ba.scene_bounds.as<float>() + 8;
+  LAUNCH(ctx, k_bounds_init, 1, 32, 0, ob);
+  LAUNCH(ctx, k_bounds, min(div_up(n, 256), 148u * 8u), 256, 0, ctx->d_pos9.as<float>(), n, ob);
+  LAUNCH(ctx, k_bounds_finish, 1, 32, 0, ob, fb);
+  LAUNCH(ctx, k_morton, div_up(n, 256), 256, 0, ctx->d_pos9.as<float>(), n, fb, bits, ba.morton.as<uint64_t>(),
+         ba.ids_alt.as<uint32_t>());
+  {  // 4. stable LSD radix sort of (Morton, id) pairs.  cub::DeviceRadixSort for bring-up (library code; a
+     //    hand-written onesweep sort is the planned replacement).
+    size_t tmp = 0;
+    const int end_bit = bits == 30 ? 30 : 63;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp, ba.morton.as<uint64_t>(), ba.sorted_keys.as<uint64_t>(),
+                                    ba.ids_alt.as<uint32_t>(), ba.sorted_ids.as<uint32_t>(), (int)n, 0, end_bit, st);
+    if ((rc = ba.cub_tmp.reserve(tmp))) return rc;
+    RTF_CUDA(cub::DeviceRadixSort::SortPairs(ba.cub_tmp.p, tmp, ba.morton.as<uint64_t>(), ba.sorted_keys.as<uint64_t>(),
+                                             ba.ids_alt.as<uint32_t>(), ba.sorted_ids.as<uint32_t>(), (int)n, 0, end_bit, st));
+    ctx->launches += 8;
+  }
+  RTF_CUDA(cudaMemsetAsync(ba.parent.p, 0xff, 4 * (size_t)(2 * n), st));
+  if (ni > 0) {
+    LAUNCH(ctx, k_karras, div_up(ni, 256), 256, 0, ba.sorted_keys.as<uint64_t>(), (int)n, ba.children.as<int2>(),
+           ba.parent.as<int>(), ba.range.as<uint2>());
+    RTF_CUDA(cudaMemsetAsync(ba.flags.p, 0, 4 * (size_t)n, st));
+  }
+  LAUNCH(ctx, k_refit, div_up(n, 256), 256, 0, ctx->d_pos9.as<float>(), ba.sorted_ids.as<uint32_t>(), (int)n,
+         ba.children.as<int2>(), ba.parent.as<int>(), ba.boxes.as<float>(), ba.flags.as<uint32_t>());
+
+  // ---- collapse ----
+  const size_t max_nodes = (size_t)n / 2 + 64;
+  const size_t max_level = (size_t)n / 4 + 64;
+  if ((rc = ctx->d_nodes.reserve(80 * max_nodes))) return rc;
+  if ((rc = ctx->d_tris48.reserve(48 * (size_t)n))) return rc;
+  if ((rc = ba.level_a.reserve(4 * max_level))) return rc;
+  if ((rc = ba.level_b.reserve(4 * max_level))) return rc;
+  if ((rc = ba.cnt_int.reserve(4 * (max_level + 1)))) return rc;
+  if ((rc = ba.cnt_tri.reserve(4 * (max_level + 1)))) return rc;
+  if ((rc = ba.scan_int.reserve(4 * (max_level + 1)))) return rc;
+  if ((rc = ba.scan_tri.reserve(4 * (max_level + 1)))) return rc;
+  if ((rc = ba.stash.reserve(32 * max_level))) return rc;
+  size_t scan_tmp = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, scan_tmp, ba.cnt_int.as<uint32_t>(), ba.scan_int.as<uint32_t>(), (int)max_level + 1, st);
+  if ((rc = ba.keys_alt.reserve(scan_tmp))) return rc;
+
+  CollapseArgs ca{ba.children.as<int2>(), ba.range.as<uint2>(), ba.boxes.as<float>(), (int)n};
+  int root = n == 1 ? ~0 : 0;
+  RTF_CUDA(cudaMemcpyAsync(ba.level_a.p, &root, 4, cudaMemcpyHostToDevice, st));
+  int* lv_cur = ba.level_a.as<int>();
+  int* lv_next = ba.level_b.as<int>();
+  uint32_t level_n = 1, level_start = 0, tri_cursor = 0;
+  int depth = 0;
+  while (level_n > 0) {
+    depth++;
+    if ((size_t)level_start + level_n > max_nodes || level_n > max_level) {
+      set_error("BVH collapse exceeded its node budget");
+      return RTF_ERR_LIMIT;
+    }
+    LAUNCH(ctx, k_collapse_plan, div_up(level_n, 128), 128, 0, ca, lv_cur, level_n, ba.stash.as<int>(),
+           ba.cnt_int.as<uint32_t>(), ba.cnt_tri.as<uint32_t>());
+    // one extra element so the exclusive scan also yields the level totals
+    RTF_CUDA(cudaMemsetAsync(ba.cnt_int.as<uint32_t>() + level_n, 0, 4, st));
+    RTF_CUDA(cudaMemsetAsync(ba.cnt_tri.as<uint32_t>() + level_n, 0, 4, st));
+    size_t tmp = scan_tmp;
+    RTF_CUDA(cub::DeviceScan::ExclusiveSum(ba.keys_alt.p, tmp, ba.cnt_int.as<uint32_t>(), ba.scan_int.as<uint32_t>(),
+                                           (int)level_n + 1, st));
+    tmp = scan_tmp;
+    RTF_CUDA(cub::DeviceScan::ExclusiveSum(ba.keys_alt.p, tmp, ba.cnt_tri.as<uint32_t>(), ba.scan_tri.as<uint32_t>(),
+                                           (int)level_n + 1, st));
+    ctx->launches += 2;
+    const uint32_t next_start = level_start + level_n;
+    LAUNCH(ctx, k_collapse_emit, div_up(level_n, 128), 128, 0, ca, lv_cur, level_n, ba.stash.as<int>(),
+           ba.scan_int.as<uint32_t>(), ba.scan_tri.as<uint32_t>(), level_start, next_start, tri_cursor, lv_next,
+           ctx->d_nodes.as<Node80>(), ctx->d_tris48.as<Tri48>(), ctx->d_pos9.as<float>(), ctx->d_tri_inst.as<uint32_t>(),
+           ba.sorted_ids.as<uint32_t>(), ctx->d_inst_alpha.as<float>());
+    uint32_t totals[2];
+    RTF_CUDA(cudaMemcpyAsync(&totals[0], ba.scan_int.as<uint32_t>() + level_n, 4, cudaMemcpyDeviceToHost, st));
+    RTF_CUDA(cudaMemcpyAsync(&totals[1], ba.scan_tri.as<uint32_t>() + level_n, 4, cudaMemcpyDeviceToHost, st));
+    RTF_CUDA(cudaStreamSynchronize(st));
+    level_start = next_start;
+    tri_cursor += totals[1];
+    level_n = totals[0];
+    int* t = lv_cur;
+    lv_cur = lv_next, lv_next = t;
+  }
+  if (tri_cursor != n) {
+    set_error("BVH collapse lost triangles");
+    return RTF_ERR_LIMIT;
+  }
+  ctx->n_nodes = level_start;
+  ctx->depth = depth;
+  if (depth > kMaxStackDepth) {
+    set_error("BVH deeper than the traversal stack");
+    return RTF_ERR_LIMIT;
+  }
+  return RTF_OK;
+}
+
+}  // namespace rtf

@@ -1,0 +1,804 @@
+// render.cu — trace kernels and the wavefront path tracer behind the three entry points.
+//
+// Reference programs re-expressed as wavefront kernels (paths relative to /root/reference/src/RayTracerFacility/ptx/
+// and /root/reference/include/RayTracerFacility/RayTracer/):
+//   __raygen__IE   IlluminationEstimation.cu:30-129  -> k_gen_illum + k_trace_queue/k_shade loop + k_reduce_illum
+//   __raygen__CR   CameraRendering.cu:32-147         -> k_gen_camera + loop + k_resolve_camera
+//   __raygen__PCS  PointCloudScanning.cu:44-75       -> k_scan_grid / k_scan_samples (generate + trace + write)
+//   ClosestHitFunc RayFunctions.cuh:25-172 (non-BTF), MissFunc :260-272, AnyHitFunc :5-23 -> k_shade / traverse()
+// The reference runs one thread per triangle/pixel with a serial loop over samples and recursive
+// optixTrace; here one lane owns one path, rays live in SoA float4 queues that are compacted with
+// warp ballots between bounces, and per-triangle sums use a fixed reduction tree (no float atomics).
+#include <cstdlib>
+
+#include "rtf_internal.h"
+#include "rtf_shade.cuh"
+#include "rtf_trace.cuh"
+
+namespace rtf {
+
+static_assert(kSmemStack + kLocalStack == kMaxStackDepth, "stack split must cover kMaxStackDepth");
+
+#define LAUNCH(ctx, kernel, grid, block, smem, ...)                  \
+  do {                                                               \
+    kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__); \
+    (ctx)->launches++;                                               \
+  } while (0)
+
+static inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
+
+constexpr int kTraceBlock = 128;
+constexpr uint32_t kShadowBit = 0x80000000u;
+
+// ============================ raw closest-hit (M1 metric) =========================================
+// Persistent warps pull 32-ray chunks from a global counter; rays are two float4 streams
+// (origin|tmin, direction|tmax) with a stride so the interleaved n x 8 host layout can be used as is.
+template <bool STATS>
+__global__ void __launch_bounds__(kTraceBlock)
+    k_trace_rays(DevScene sc, const float4* __restrict__ ra, const float4* __restrict__ rb, int stride, uint32_t n,
+                 float4* __restrict__ hits, uint32_t* __restrict__ nv, uint32_t* __restrict__ tv, uint32_t* work) {
+  __shared__ uint2 sstack[kSmemStack * kTraceBlock];
+  const int lane = threadIdx.x & 31;
+  AlphaCtx actx{nullptr, 0u, 0ull, 0u};
+  for (;;) {
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(work, 32u);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= n) break;
+    const uint32_t i = base + lane;
+    if (i < n) {
+      const float4 a = __ldg(ra + (size_t)i * stride), b = __ldg(rb + (size_t)i * stride);
+      uint32_t nvis = 0, tvis = 0;
+      const HitRec h = traverse<kSmemStack, STATS>(sc.nodes, sc.tris, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), a.w, b.w,
+                                                   sstack + threadIdx.x, kTraceBlock, 0u, actx, nvis, tvis);
+      hits[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
+      if (STATS) {
+        if (nv) nv[i] = nvis;
+        if (tv) tv[i] = tvis;
+      }
+    }
+  }
+}
+
+int trace_rays_device(rtf_ctx* ctx, const float4* ra, const float4* rb, int stride, size_t n, float4* hits,
+                      uint32_t* nv, uint32_t* tv) {
+  if (!ctx->ready) {
+    set_error("no acceleration structure (call rtf_commit)");
+    return RTF_ERR_NOT_READY;
+  }
+  if (n == 0) return RTF_OK;
+  int rc;
+  if ((rc = ctx->ws.counters.reserve(4096))) return rc;
+  uint32_t* work = ctx->ws.counters.as<uint32_t>();
+  const size_t chunk = 1u << 30;
+  for (size_t off = 0; off < n; off += chunk) {
+    const uint32_t m = (uint32_t)((n - off) < chunk ? (n - off) : chunk);
+    RTF_CUDA(cudaMemsetAsync(work, 0, 4, ctx->stream));
+    const unsigned grid = min(div_up(m, kTraceBlock), (unsigned)ctx->sm_count * 8u);
+    if (nv || tv)
+      LAUNCH(ctx, k_trace_rays<true>, grid, kTraceBlock, 0, ctx->scene, ra + off * stride, rb + off * stride, stride, m,
+             hits + off, nv ? nv + off : nullptr, tv ? tv + off : nullptr, work);
+    else
+      LAUNCH(ctx, k_trace_rays<false>, grid, kTraceBlock, 0, ctx->scene, ra + off * stride, rb + off * stride, stride, m,
+             hits + off, nullptr, nullptr, work);
+  }
+  RTF_CUDA(cudaGetLastError());
+  return RTF_OK;
+}
+
+// ============================ wavefront machinery ==================================================
+// How a path index of the current batch maps to its RNG unit (and probe / pixel).
+struct PathMap {
+  int mode;            // 0 = illumination, 1 = camera
+  uint64_t unit_base;  // camera: first pixel * spp
+  uint64_t tri_begin;  // illumination: first probe of the batch
+  uint32_t per_probe;  // 2 * sc
+  uint32_t sc;         // samples in this call
+  uint32_t s0;         // first sample
+  uint32_t s_total;    // RayProperties::m_samples
+};
+__device__ __forceinline__ uint64_t unit_of(const PathMap& pm, uint32_t p) {
+  if (pm.mode == 1) return pm.unit_base + p;
+  const uint32_t tl = p / pm.per_probe, rem = p - tl * pm.per_probe;
+  const uint32_t face = rem / pm.sc, s = pm.s0 + (rem - face * pm.sc);
+  return ((pm.tri_begin + tl) * 2ull + face) * (uint64_t)pm.s_total + s;
+}
+
+struct Queues {
+  float4* ray_a[2];
+  float4* ray_b[2];
+  uint32_t* path_idx[2];
+  float4* hits;
+  uint32_t* count;  // count[k] = rays in wavefront k
+  uint32_t* work;   // work[k]  = dynamic-fetch cursor of wavefront k
+};
+struct PathState {
+  float4* thr;    // throughput.xyz, w = hit count (bits) | emission (shadow pending)
+  float4* acc;    // accumulated radiance.xyz
+  float4* dir0w;  // illumination: first direction.xyz, w = |N.dir|
+  float4* aux;    // shadow pending: albedo.xyz, w = N.L
+  float4* first_n;  // camera: first-hit normal
+  float4* first_a;  // camera: first-hit albedo (or miss colour)
+  float4* first_p;  // camera: first-hit position, w = 1 if there was a first hit
+};
+
+// warp-aggregated append: one atomicAdd per warp (ballot + popc), slots keep lane order.
+__device__ __forceinline__ uint32_t warp_append(bool emit, uint32_t* counter) {
+  const unsigned m = __ballot_sync(0xffffffffu, emit);
+  if (m == 0) return 0;
+  const int lane = threadIdx.x & 31;
+  const int leader = __ffs(m) - 1;
+  uint32_t base = 0;
+  if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  return base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+}
+
+// ---- trace one wavefront -----------------------------------------------------------------------------
+__global__ void __launch_bounds__(kTraceBlock)
+    k_trace_queue(DevScene sc, Queues q, int qi, int wave, PathMap pm, uint32_t seed, unsigned long long* stats) {
+  __shared__ uint2 sstack[kSmemStack * kTraceBlock];
+  const int lane = threadIdx.x & 31;
+  const uint32_t n = q.count[wave];
+  if (blockIdx.x == 0 && threadIdx.x == 0 && stats) atomicAdd(stats, (unsigned long long)n);
+  const float4* __restrict__ ra = q.ray_a[qi];
+  const float4* __restrict__ rb = q.ray_b[qi];
+  const uint32_t* __restrict__ pidx = q.path_idx[qi];
+  for (;;) {
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(q.work + wave, 32u);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= n) break;
+    const uint32_t i = base + lane;
+    if (i < n) {
+      const float4 a = __ldg(ra + i), b = __ldg(rb + i);
+      const uint32_t pi = __ldg(pidx + i);
+      uint32_t flags = 0;
+      AlphaCtx actx{sc.inst_alpha, seed, 0ull, (uint32_t)wave};
+      if (pi & kShadowBit) {
+        flags = TRACE_ANY_HIT;  // DISABLE_ANYHIT | TERMINATE_ON_FIRST_HIT, RayFunctions.cuh:81-83
+      } else if (sc.has_alpha) {
+        flags = TRACE_ALPHA;
+        actx.unit = unit_of(pm, pi);
+      }
+      uint32_t nvis = 0, tvis = 0;
+      const HitRec h = traverse<kSmemStack, false>(sc.nodes, sc.tris, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), a.w, b.w,
+                                                   sstack + threadIdx.x, kTraceBlock, flags, actx, nvis, tvis);
+      q.hits[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
+    }
+  }
+}
+
+// ---- shade one wavefront: ClosestHitFunc (RayFunctions.cuh:25-172) / MissFunc (:260-272), unrolled ------
+struct ShadeParams {
+  int bounces;
+  uint32_t seed;
+  int camera;
+};
+__global__ void __launch_bounds__(256)
+    k_shade(DevScene sc, rtf_env env, ShadeParams sp, PathMap pm, Queues q, int qi, int wave, PathState ps) {
+  const uint32_t n = q.count[wave];
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (blockIdx.x * blockDim.x >= n) return;  // whole block idle (uniform exit keeps warp_append safe)
+  bool emit = false;
+  float4 na = make_float4(0, 0, 0, 0), nb = make_float4(0, 0, 0, 0);
+  uint32_t npi = 0;
+  if (i < n) {
+    const float4 a = q.ray_a[qi][i], b = q.ray_b[qi][i];
+    const uint32_t pi = q.path_idx[qi][i];
+    const uint32_t p = pi & ~kShadowBit;
+    const float4 h = q.hits[i];
+    const uint32_t prim = __float_as_uint(h.w);
+    const float3 o = f3(a.x, a.y, a.z), d = f3(b.x, b.y, b.z);
+    const float4 thr4 = ps.thr[p];
+    float3 T = f3(thr4.x, thr4.y, thr4.z);
+    const float4 acc4 = ps.acc[p];
+    float3 acc = f3(acc4.x, acc4.y, acc4.z);
+    if (pi & kShadowBit) {  // shadow ray result, RayFunctions.cuh:70-92
+      const float4 ax = ps.aux[p];
+      const float3 albedo = f3(ax.x, ax.y, ax.z);
+      if (prim == 0xFFFFFFFFu) {
+        const float3 L = env_light(o, d, env);
+        acc = acc + T * ((L * ax.w) * albedo);
+      }
+      acc = acc + T * (thr4.w * albedo);
+      ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
+    } else if (prim == 0xFFFFFFFFu) {  // MissFunc
+      const float3 L = env_light(o, d, env);
+      acc = acc + T * L;
+      ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
+      if (sp.camera && __float_as_uint(thr4.w) == 0u) ps.first_a[p] = make_float4(L.x, L.y, L.z, 0.0f);
+    } else {
+      const uint32_t hit_count = __float_as_uint(thr4.w) + 1u;
+      const SurfaceHit sh = surface_hit(sc, prim, h.y, h.z, d);
+      const rtf_material& m = sc.mats[sc.insts[sh.inst].mat];
+      const float metallic = m.metallic, roughness = m.roughness;
+      const float3 albedo = f3(m.albedo_color[0], m.albedo_color[1], m.albedo_color[2]);
+      if (sp.camera && hit_count == 1u) {
+        ps.first_n[p] = make_float4(sh.normal.x, sh.normal.y, sh.normal.z, 0.0f);
+        ps.first_a[p] = make_float4(albedo.x, albedo.y, albedo.z, 0.0f);
+        ps.first_p[p] = make_float4(sh.position.x, sh.position.y, sh.position.z, 1.0f);
+      }
+      float f = 1.0f;
+      if (metallic >= 0.0f) f = (metallic + 2) / (metallic + 1);
+      const float3 emis = m.emission * albedo;
+      const uint64_t unit = unit_of(pm, p);
+      if (env.lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE) {  // RayFunctions.cuh:61-92
+        const float4 r = path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
+        const float3 sun = f3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
+        const float3 nd = sample_lobe(r.x, r.y, sun, 1.0f - env.light_size);
+        const float3 col = f3(env.color[0], env.color[1], env.color[2]);
+        acc = acc + T * ((col * env.ambient_light_intensity) * albedo);
+        const float ndl = dot3(sh.normal, nd);
+        if (ndl > 0.0f) {
+          emit = true;
+          na = make_float4(sh.position.x, sh.position.y, sh.position.z, 1e-3f);
+          nb = make_float4(nd.x, nd.y, nd.z, 1e20f);
+          npi = p | kShadowBit;
+          ps.thr[p] = make_float4(T.x, T.y, T.z, m.emission);
+          ps.aux[p] = make_float4(albedo.x, albedo.y, albedo.z, ndl);
+        } else {
+          acc = acc + T * emis;
+        }
+        ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
+      } else if ((int)hit_count <= sp.bounces) {  // RayFunctions.cuh:93-161, BSSRDF branch off (factor 0)
+        const float4 r = path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
+        const float3 refl = reflect3(d, sh.normal);
+        const float3 nd = sample_lobe(r.x, r.y, refl, metallic);  // BRDF(), BSDF.cuh:6-13
+        const float k = clampf(fabsf(dot3(sh.normal, nd)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
+        const float3 wgt = ((1.0f - m.subsurface_factor) * albedo) * k;
+        acc = acc + T * emis;
+        T = T * wgt;
+        ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
+        ps.thr[p] = make_float4(T.x, T.y, T.z, __uint_as_float(hit_count));
+        emit = true;
+        na = make_float4(sh.position.x, sh.position.y, sh.position.z, 1e-3f);  // origin not offset, RayFunctions.cuh:138
+        nb = make_float4(nd.x, nd.y, nd.z, 1e20f);
+        npi = p;
+      } else {
+        acc = acc + T * emis;
+        ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
+      }
+    }
+  }
+  const uint32_t slot = warp_append(emit, q.count + wave + 1);
+  if (emit) {
+    q.ray_a[qi ^ 1][slot] = na;
+    q.ray_b[qi ^ 1][slot] = nb;
+    q.path_idx[qi ^ 1][slot] = npi;
+  }
+}
+
+// ---- __raygen__IE path start (IlluminationEstimation.cu:47-80) --------------------------------------------
+struct IllumGen {
+  uint64_t tri_begin;
+  uint32_t n_tris;  // probes in this batch
+  uint32_t sc, s0, s_total;
+  uint32_t seed;
+  float push;
+  int front, back;                   // mesh mode
+  const rtf_illum_sampler* probes;   // probe mode (AoS, device) or nullptr
+  uint64_t probe_base;               // index of probes[0] in the caller's array (= RNG probe id)
+};
+__global__ void __launch_bounds__(256) k_gen_illum(DevScene sc, IllumGen g, Queues q, PathState ps) {
+  const uint32_t per_probe = 2u * g.sc;
+  const uint64_t total = (uint64_t)g.n_tris * per_probe;
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  bool emit = false;
+  float4 na = make_float4(0, 0, 0, 0), nb = make_float4(0, 0, 0, 0);
+  if (p < total) {
+    const uint32_t tl = p / per_probe, rem = p - tl * per_probe;
+    const uint32_t face = rem / g.sc, s = g.s0 + (rem - face * g.sc);
+    const uint64_t probe = g.tri_begin + tl;
+    float3 P0, P1, P2, N0, N1, N2;
+    bool enabled;
+    if (g.probes) {
+      const rtf_illum_sampler& pr = g.probes[probe - g.probe_base];
+      P0 = f3(pr.a.position[0], pr.a.position[1], pr.a.position[2]);
+      P1 = f3(pr.b.position[0], pr.b.position[1], pr.b.position[2]);
+      P2 = f3(pr.c.position[0], pr.c.position[1], pr.c.position[2]);
+      N0 = f3(pr.a.normal[0], pr.a.normal[1], pr.a.normal[2]);
+      N1 = f3(pr.b.normal[0], pr.b.normal[1], pr.b.normal[2]);
+      N2 = f3(pr.c.normal[0], pr.c.normal[1], pr.c.normal[2]);
+      enabled = face == 0 ? pr.front_face != 0 : pr.back_face != 0;
+    } else {
+      const float* pp = sc.pos9 + 9 * probe;
+      const float* nn = sc.nrm9 + 9 * probe;
+      P0 = f3(pp[0], pp[1], pp[2]), P1 = f3(pp[3], pp[4], pp[5]), P2 = f3(pp[6], pp[7], pp[8]);
+      N0 = f3(nn[0], nn[1], nn[2]), N1 = f3(nn[3], nn[4], nn[5]), N2 = f3(nn[6], nn[7], nn[8]);
+      enabled = face == 0 ? g.front != 0 : g.back != 0;
+    }
+    float4 d0w = make_float4(0, 0, 0, 0);
+    if (enabled) {
+      const uint64_t unit = (probe * 2ull + face) * (uint64_t)g.s_total + s;
+      const float4 r = path_rng(g.seed, STREAM_PATH, unit, 0u, 0u);
+      const float a = r.x, b = r.y;
+      const float w = (1.0f - a) - b;  // not folded back when a+b > 1 (IlluminationEstimation.cu:56-59)
+      const float3 position = (w * P0 + a * P1) + b * P2;
+      float3 normal = (w * N0 + a * N1) + b * N2;  // un-normalised
+      if (face == 1) normal = neg3(normal);
+      const float3 dir = sample_hemisphere(r.z, r.w, normal);
+      const float3 origin = position + normal * g.push;
+      emit = true;
+      na = make_float4(origin.x, origin.y, origin.z, 1e-3f);
+      nb = make_float4(dir.x, dir.y, dir.z, 1e20f);
+      d0w = make_float4(dir.x, dir.y, dir.z, fabsf(dot3(normal, dir)));
+    }
+    ps.thr[p] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(0u));
+    ps.acc[p] = make_float4(0, 0, 0, 0);
+    ps.dir0w[p] = d0w;
+  }
+  const uint32_t slot = warp_append(emit, q.count + 0);
+  if (emit) {
+    q.ray_a[0][slot] = na;
+    q.ray_b[0][slot] = nb;
+    q.path_idx[0][slot] = p;
+  }
+}
+
+// ---- per-probe reduction: 32-lane strided partial sums + xor butterfly (fixed tree, no atomics) ----------
+// IlluminationEstimation.cu:81-84: energy = L*|N.dir|; pointEnergy += energy; pointDirection += dir*|energy|.
+__global__ void __launch_bounds__(256)
+    k_reduce_illum(uint32_t n_tris, uint32_t sc_, PathState ps, float* __restrict__ accum6 /* 6 per probe of batch */) {
+  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= n_tris) return;
+  float tot[6] = {0, 0, 0, 0, 0, 0};
+  for (uint32_t face = 0; face < 2; face++) {
+    float v[6] = {0, 0, 0, 0, 0, 0};
+    const uint32_t base = warp * 2u * sc_ + face * sc_;
+    for (uint32_t s = lane; s < sc_; s += 32) {
+      const float4 a = ps.acc[base + s], dw = ps.dir0w[base + s];
+      const float3 e = f3(a.x, a.y, a.z) * dw.w;
+      const float le = length3(e);
+      v[0] = v[0] + e.x, v[1] = v[1] + e.y, v[2] = v[2] + e.z;
+      v[3] = v[3] + dw.x * le, v[4] = v[4] + dw.y * le, v[5] = v[5] + dw.z * le;
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1)
+#pragma unroll
+      for (int k = 0; k < 6; k++) v[k] = v[k] + __shfl_xor_sync(0xffffffffu, v[k], off);
+#pragma unroll
+    for (int k = 0; k < 6; k++) tot[k] = tot[k] + v[k];
+  }
+  if (lane < 6) {
+    float x = tot[0];
+#pragma unroll
+    for (int k = 1; k < 6; k++)
+      if (lane == k) x = tot[k];
+    float* o = accum6 + 6 * (size_t)warp + lane;
+    *o = *o + x;
+  }
+}
+
+// IlluminationEstimation.cu:125-128
+__global__ void k_finalize_illum(float* accum6, uint64_t n, int faces, int samples, rtf_illum_sampler* probes) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  int nf = faces;
+  if (probes) nf = (probes[t].front_face ? 1 : 0) + (probes[t].back_face ? 1 : 0);
+  const int cnt = nf * samples;
+  if (cnt == 0) return;
+  float* v = accum6 + 6 * t;
+  const float fn = (float)cnt;
+  const float3 e = f3(v[0] / fn, v[1] / fn, v[2] / fn);
+  const float3 d = normalize3(f3(v[3], v[4], v[5]));
+  v[0] = e.x, v[1] = e.y, v[2] = e.z, v[3] = d.x, v[4] = d.y, v[5] = d.z;
+  if (probes) {
+    probes[t].energy[0] = e.x, probes[t].energy[1] = e.y, probes[t].energy[2] = e.z;
+    probes[t].direction[0] = d.x, probes[t].direction[1] = d.y, probes[t].direction[2] = d.z;
+  }
+}
+
+static size_t batch_capacity() {
+  static size_t cap = 0;
+  if (!cap) {
+    const char* e = getenv("RTF_BATCH_PATHS");
+    cap = e ? (size_t)atoll(e) : ((size_t)1 << 22);
+    if (cap < 1024) cap = 1024;
+  }
+  return cap;
+}
+
+static int ensure_workspace(rtf_ctx* ctx, size_t cap, bool camera) {
+  Workspace& w = ctx->ws;
+  int rc;
+  for (int k = 0; k < 2; k++) {
+    if ((rc = w.ray_a[k].reserve(16 * cap))) return rc;
+    if ((rc = w.ray_b[k].reserve(16 * cap))) return rc;
+    if ((rc = w.path_idx[k].reserve(4 * cap))) return rc;
+  }
+  if ((rc = w.hits.reserve(16 * cap))) return rc;
+  if ((rc = w.counters.reserve(4096))) return rc;
+  if ((rc = w.thr.reserve(16 * cap))) return rc;
+  if ((rc = w.acc.reserve(16 * cap))) return rc;
+  if ((rc = w.dir0w.reserve(16 * cap))) return rc;
+  if ((rc = w.first_n.reserve(16 * cap))) return rc;  // doubles as `aux` outside camera mode
+  if (camera) {
+    if ((rc = w.first_a.reserve(16 * cap))) return rc;
+    if ((rc = w.first_p.reserve(16 * cap))) return rc;
+    if ((rc = w.sort_keys.reserve(16 * cap))) return rc;  // aux for camera + single light
+  }
+  if ((rc = ctx->d_stats.reserve(64))) return rc;
+  w.capacity = cap;
+  return RTF_OK;
+}
+
+static void bind(rtf_ctx* ctx, Queues& q, PathState& ps, bool camera) {
+  Workspace& w = ctx->ws;
+  for (int k = 0; k < 2; k++) {
+    q.ray_a[k] = w.ray_a[k].as<float4>(), q.ray_b[k] = w.ray_b[k].as<float4>();
+    q.path_idx[k] = w.path_idx[k].as<uint32_t>();
+  }
+  q.hits = w.hits.as<float4>();
+  q.count = w.counters.as<uint32_t>() + 16;
+  q.work = w.counters.as<uint32_t>() + 16 + 64;
+  ps.thr = w.thr.as<float4>(), ps.acc = w.acc.as<float4>(), ps.dir0w = w.dir0w.as<float4>();
+  ps.first_n = w.first_n.as<float4>(), ps.first_a = w.first_a.as<float4>(), ps.first_p = w.first_p.as<float4>();
+  ps.aux = camera ? w.sort_keys.as<float4>() : w.first_n.as<float4>();
+}
+
+// Runs the trace/shade loop for the wavefronts of one batch (no host synchronisation inside).
+static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_t seed, const PathMap& pm, size_t paths,
+                          Queues& q, PathState& ps, bool camera) {
+  const int waves = env->lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE ? 2 : bounces + 1;
+  if (waves + 1 > 60) {
+    set_error("too many bounces");
+    return RTF_ERR_INVALID;
+  }
+  ShadeParams sp{bounces, seed, camera ? 1 : 0};
+  unsigned long long* stats = ctx->d_stats.as<unsigned long long>();
+  const unsigned tgrid = min(div_up(paths, kTraceBlock), (unsigned)ctx->sm_count * 8u);
+  int qi = 0;
+  for (int w = 0; w < waves; w++) {
+    LAUNCH(ctx, k_trace_queue, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, pm, seed, stats);
+    LAUNCH(ctx, k_shade, div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
+    qi ^= 1;
+  }
+  return RTF_OK;
+}
+
+int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push, int front,
+                      int back, uint64_t tri_begin, uint64_t tri_end, int s0, int s1, float* d_accum6,
+                      const rtf_illum_sampler* d_probes, uint64_t probe_base) {
+  if (!ctx->ready) {
+    set_error("no acceleration structure (call rtf_commit)");
+    return RTF_ERR_NOT_READY;
+  }
+  if (env->environmental_map_id != 0) {
+    set_error("cube-map environment is not wired in this round (SURVEY N2)");
+    return RTF_ERR_INVALID;
+  }
+  if (tri_end <= tri_begin || s1 <= s0) return RTF_OK;
+  const uint32_t sc_ = (uint32_t)(s1 - s0);
+  const size_t per_probe = 2 * (size_t)sc_;
+  size_t cap = batch_capacity();
+  if (cap < per_probe) cap = per_probe;
+  int rc;
+  if ((rc = ensure_workspace(ctx, cap, false))) return rc;
+  Queues q;
+  PathState ps;
+  bind(ctx, q, ps, false);
+  const uint64_t tris_per_batch = cap / per_probe;
+  RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, ctx->stream));
+  uint64_t paths_total = 0;
+  for (uint64_t t0 = tri_begin; t0 < tri_end; t0 += tris_per_batch) {
+    const uint32_t nt = (uint32_t)((tri_end - t0) < tris_per_batch ? (tri_end - t0) : tris_per_batch);
+    const size_t paths = (size_t)nt * per_probe;
+    RTF_CUDA(cudaMemsetAsync(ctx->ws.counters.p, 0, 4096, ctx->stream));
+    IllumGen g{t0, nt, sc_, (uint32_t)s0, (uint32_t)rp->samples, seed, push, front, back, d_probes, probe_base};
+    LAUNCH(ctx, k_gen_illum, div_up(paths, 256), 256, 0, ctx->scene, g, q, ps);
+    PathMap pm{0, 0ull, t0, (uint32_t)per_probe, sc_, (uint32_t)s0, (uint32_t)rp->samples};
+    if ((rc = run_wavefronts(ctx, env, rp->bounces, seed, pm, paths, q, ps, false))) return rc;
+    LAUNCH(ctx, k_reduce_illum, div_up((size_t)nt * 32, 256), 256, 0, nt, sc_, ps, d_accum6 + 6 * (t0 - tri_begin));
+    paths_total += paths;
+  }
+  RTF_CUDA(cudaGetLastError());
+  ctx->last_paths = paths_total;
+  return RTF_OK;
+}
+
+int illum_finalize_device(rtf_ctx* ctx, float* d_accum6, uint64_t n, int faces, int samples, rtf_illum_sampler* d_probes) {
+  if (n == 0) return RTF_OK;
+  LAUNCH(ctx, k_finalize_illum, div_up(n, 256), 256, 0, d_accum6, n, faces, samples, d_probes);
+  RTF_CUDA(cudaGetLastError());
+  return RTF_OK;
+}
+
+// ============================ LiDAR =================================================================
+// PointCloudScanner::Scan ray grid (PointCloudScanner.cpp:70-92) generated in the kernel, traced
+// (tmin 1e-3, tmax 1e20, any-hit disabled: PointCloudScanning.cu:58-64) and written as SoA.
+__global__ void __launch_bounds__(kTraceBlock)
+    k_scan_grid(DevScene sc, rtf_scan_grid g, uint32_t column, uint32_t row, uint64_t ray_begin, uint32_t n,
+                float* __restrict__ t_out, uint32_t* __restrict__ prim_out, uint32_t* __restrict__ inst_out, uint32_t* work) {
+  __shared__ uint2 sstack[kSmemStack * kTraceBlock];
+  const int lane = threadIdx.x & 31;
+  const int column_start = -(int)(column / 2), row_start = -(int)(row / 2);
+  const float3 center = f3(g.center[0], g.center[1], g.center[2]);
+  const float3 left = f3(g.left[0], g.left[1], g.left[2]), up = f3(g.up[0], g.up[1], g.up[2]);
+  const float3 dir = normalize3(f3(g.direction[0], g.direction[1], g.direction[2]));
+  AlphaCtx actx{nullptr, 0u, 0ull, 0u};
+  for (;;) {
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(work, 32u);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= n) break;
+    const uint32_t k = base + lane;
+    if (k < n) {
+      const uint64_t i = ray_begin + k;
+      const int ci = (int)(i / row), ri = (int)(i % row);
+      const float3 pos = (center + (left * (float)(column_start + ci)) * g.distance[0]) + (up * (float)(row_start + ri)) * g.distance[1];
+      uint32_t nvis = 0, tvis = 0;
+      const HitRec h = traverse<kSmemStack, false>(sc.nodes, sc.tris, pos, dir, 1e-3f, 1e20f, sstack + threadIdx.x,
+                                                   kTraceBlock, 0u, actx, nvis, tvis);
+      if (t_out) t_out[k] = h.t;
+      if (prim_out) prim_out[k] = h.prim;
+      if (inst_out) inst_out[k] = h.prim == 0xFFFFFFFFu ? 0xFFFFFFFFu : __ldg(sc.tri_inst + h.prim);
+    }
+  }
+}
+__global__ void __launch_bounds__(kTraceBlock)
+    k_scan_samples(DevScene sc, rtf_pc_sample* samples, uint32_t n, uint32_t* __restrict__ prim_out, uint32_t* work) {
+  __shared__ uint2 sstack[kSmemStack * kTraceBlock];
+  const int lane = threadIdx.x & 31;
+  AlphaCtx actx{nullptr, 0u, 0ull, 0u};
+  for (;;) {
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(work, 32u);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= n) break;
+    const uint32_t k = base + lane;
+    if (k < n) {
+      rtf_pc_sample& sm = samples[k];
+      const float3 d = f3(sm.direction[0], sm.direction[1], sm.direction[2]);
+      const float3 o = f3(sm.start[0], sm.start[1], sm.start[2]);
+      uint32_t nvis = 0, tvis = 0;
+      const HitRec h = traverse<kSmemStack, false>(sc.nodes, sc.tris, o, d, 1e-3f, 1e20f, sstack + threadIdx.x, kTraceBlock,
+                                                   0u, actx, nvis, tvis);
+      if (prim_out) prim_out[k] = h.prim;
+      rtf_hit_info hi;
+      if (h.prim == 0xFFFFFFFFu) {  // __miss__PCS_R (PointCloudScanning.cu:36-40) + HitInfo() defaults
+        sm.hit = 0, sm.handle = 0;
+        for (int c = 0; c < 3; c++) hi.position[c] = hi.normal[c] = hi.tangent[c] = 0.0f;
+        for (int c = 0; c < 4; c++) hi.color[c] = 1.0f, hi.data[c] = 0.0f;
+        hi.tex_coord[0] = hi.tex_coord[1] = 0.0f;
+      } else {
+        uint64_t handle;
+        full_hit_info(sc, h.prim, h.u, h.v, d, hi, handle);
+        sm.hit = 1, sm.handle = handle;
+      }
+      sm.hit_info = hi;
+    }
+  }
+}
+
+int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin, uint64_t ray_end, float* d_t,
+                     uint32_t* d_prim, uint32_t* d_inst) {
+  if (!ctx->ready) {
+    set_error("no acceleration structure (call rtf_commit)");
+    return RTF_ERR_NOT_READY;
+  }
+  const uint32_t column = (uint32_t)(grid->size[0] / grid->distance[0]);
+  const uint32_t row = (uint32_t)(grid->size[1] / grid->distance[1]);
+  if (ray_end > (uint64_t)column * row || ray_end < ray_begin) {
+    set_error("ray range outside the scan grid");
+    return RTF_ERR_INVALID;
+  }
+  int rc;
+  if ((rc = ctx->ws.counters.reserve(4096))) return rc;
+  uint32_t* work = ctx->ws.counters.as<uint32_t>();
+  const uint64_t chunk = 1ull << 30;
+  for (uint64_t off = ray_begin; off < ray_end; off += chunk) {
+    const uint32_t m = (uint32_t)((ray_end - off) < chunk ? (ray_end - off) : chunk);
+    RTF_CUDA(cudaMemsetAsync(work, 0, 4, ctx->stream));
+    const unsigned g = min(div_up(m, kTraceBlock), (unsigned)ctx->sm_count * 8u);
+    const uint64_t o = off - ray_begin;
+    LAUNCH(ctx, k_scan_grid, g, kTraceBlock, 0, ctx->scene, *grid, column, row, off, m, d_t ? d_t + o : nullptr,
+           d_prim ? d_prim + o : nullptr, d_inst ? d_inst + o : nullptr, work);
+  }
+  RTF_CUDA(cudaGetLastError());
+  return RTF_OK;
+}
+int scan_samples_device(rtf_ctx* ctx, rtf_pc_sample* d_samples, size_t n, uint32_t* d_prim) {
+  if (!ctx->ready) {
+    set_error("no acceleration structure (call rtf_commit)");
+    return RTF_ERR_NOT_READY;
+  }
+  if (n == 0) return RTF_OK;
+  int rc;
+  if ((rc = ctx->ws.counters.reserve(4096))) return rc;
+  uint32_t* work = ctx->ws.counters.as<uint32_t>();
+  RTF_CUDA(cudaMemsetAsync(work, 0, 4, ctx->stream));
+  const unsigned g = min(div_up(n, kTraceBlock), (unsigned)ctx->sm_count * 8u);
+  LAUNCH(ctx, k_scan_samples, g, kTraceBlock, 0, ctx->scene, d_samples, (uint32_t)n, d_prim, work);
+  RTF_CUDA(cudaGetLastError());
+  return RTF_OK;
+}
+
+// ============================ camera ================================================================
+// __raygen__CR path start, CameraRendering.cu:63-85.
+__global__ void __launch_bounds__(256)
+    k_gen_camera(rtf_camera_props cam, uint64_t pixel_begin, uint32_t n_pixels, uint32_t spp, Queues q, PathState ps) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t total = (uint64_t)n_pixels * spp;
+  bool emit = false;
+  float4 na = make_float4(0, 0, 0, 0), nb = make_float4(0, 0, 0, 0);
+  if (p < total) {
+    const uint64_t pixel = pixel_begin + p / spp;
+    const uint32_t ix = (uint32_t)(pixel % (uint64_t)cam.width), iy = (uint32_t)(pixel / (uint64_t)cam.width);
+    const uint64_t unit = pixel_begin * spp + p;
+    const float4 r = path_rng((uint32_t)cam.frame_id, STREAM_CAMERA, unit, 0u, 0u);
+    const float halfX = cam.width / 2.0f, halfY = cam.height / 2.0f;
+    const float sx = (((float)ix + r.x) - halfX) / halfX;
+    const float sy = (((float)iy + r.y) - halfY) / halfY;
+    const float* m = cam.inverse_projection_view;
+    float st[4], en[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      st[k] = (m[k] * sx + m[4 + k] * sy) + (m[8 + k] * -1.0f + m[12 + k] * 1.0f);
+      en[k] = (m[k] * sx + m[4 + k] * sy) + (m[8 + k] * 1.0f + m[12 + k] * 1.0f);
+    }
+    const float3 start = f3(st[0] / st[3], st[1] / st[3], st[2] / st[3]);
+    const float3 end = f3(en[0] / en[3], en[1] / en[3], en[2] / en[3]);
+    const float3 pdir = normalize3(end - start);
+    const float3 conv = start + pdir * cam.focal_length;
+    float sn, cs;
+    sincos2pi(r.z, sn, cs);
+    const float3 hor = f3(cam.horizontal[0], cam.horizontal[1], cam.horizontal[2]);
+    const float3 ver = f3(cam.vertical[0], cam.vertical[1], cam.vertical[2]);
+    const float3 ap = start + cam.aperture * (hor * sn + ver * cs);
+    const float3 dir = normalize3(conv - ap);
+    emit = true;
+    na = make_float4(ap.x, ap.y, ap.z, 0.0f);  // tmin 0, CameraRendering.cu:89
+    nb = make_float4(dir.x, dir.y, dir.z, 1e20f);
+    ps.thr[p] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(0u));
+    ps.acc[p] = make_float4(0, 0, 0, 0);
+    ps.first_n[p] = make_float4(0, 0, 0, 0);
+    ps.first_a[p] = make_float4(0, 0, 0, 0);
+    ps.first_p[p] = make_float4(0, 0, 0, 0);
+  }
+  const uint32_t slot = warp_append(emit, q.count + 0);
+  if (emit) {
+    q.ray_a[0][slot] = na;
+    q.ray_b[0][slot] = nb;
+    q.path_idx[0][slot] = p;
+  }
+}
+// CameraRendering.cu:101-146: per-pixel sums in sample order, progressive accumulation in gamma space.
+__global__ void __launch_bounds__(256)
+    k_resolve_camera(rtf_camera_props cam, uint64_t pixel_begin, uint32_t n_pixels, uint32_t spp, PathState ps,
+                     float4* __restrict__ color, float4* __restrict__ normal, float4* __restrict__ albedo) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_pixels) return;
+  const uint64_t pixel = pixel_begin + k;
+  const float nsf = (float)spp;
+  float3 pc = f3(0, 0, 0), pn = f3(0, 0, 0), pa = f3(0, 0, 0), pp = f3(0, 0, 0);
+  for (uint32_t s = 0; s < spp; s++) {
+    const size_t p = (size_t)k * spp + s;
+    const float4 e = ps.acc[p], n4 = ps.first_n[p], a4 = ps.first_a[p], p4 = ps.first_p[p];
+    float3 pos = f3(p4.x, p4.y, p4.z);
+    if (p4.w == 0.0f) pos = s == 0 ? f3(999999.0f, 999999.0f, 999999.0f) : f3(0, 0, 0);  // CameraRendering.cu:48,108
+    pc = pc + f3(e.x / nsf, e.y / nsf, e.z / nsf);
+    pn = pn + f3(n4.x / nsf, n4.y / nsf, n4.z / nsf);
+    pa = pa + f3(a4.x / nsf, a4.y / nsf, a4.z / nsf);
+    pp = pp + f3(pos.x / nsf, pos.y / nsf, pos.z / nsf);
+  }
+  if (cam.accumulate && cam.frame_id > 1) {
+    const float4 prev = color[pixel];
+    const float3 accd = f3(powf(prev.x, cam.gamma), powf(prev.y, cam.gamma), powf(prev.z, cam.gamma));
+    const float fid = (float)cam.frame_id;
+    pc = pc + fid * accd;
+    const float den = (float)(cam.frame_id + 1);
+    pc = f3(pc.x / den, pc.y / den, pc.z / den);
+  }
+  const float ig = (float)(1.0 / (double)cam.gamma);
+  color[pixel] = make_float4(powf(pc.x, ig), powf(pc.y, ig), powf(pc.z, ig), 1.0f);
+  if (cam.output_type == RTF_OUT_DEPTH) {
+    const float3 from = f3(cam.from[0], cam.from[1], cam.from[2]);
+    const float dd = clampf(length3(from - pp) / cam.max_distance, 0.0f, 1.0f);
+    albedo[pixel] = make_float4(dd, dd, dd, 1.0f);
+  } else {
+    albedo[pixel] = make_float4(pa.x, pa.y, pa.z, 1.0f);
+  }
+  normal[pixel] = make_float4(pn.x, pn.y, pn.z, 1.0f);
+}
+
+int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp) {
+  const rtf_camera_props& cp = cam->props;
+  const uint64_t n_pixels = (uint64_t)cp.width * (uint64_t)cp.height;
+  if (n_pixels == 0 || rp->samples <= 0) return RTF_OK;
+  if (env->environmental_map_id != 0) {
+    set_error("cube-map environment is not wired in this round (SURVEY N2)");
+    return RTF_ERR_INVALID;
+  }
+  const uint32_t spp = (uint32_t)rp->samples;
+  size_t cap = batch_capacity();
+  if (cap < spp) cap = spp;
+  int rc;
+  if ((rc = ensure_workspace(ctx, cap, true))) return rc;
+  Queues q;
+  PathState ps;
+  bind(ctx, q, ps, true);
+  const uint64_t px_per_batch = cap / spp;
+  RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, ctx->stream));
+  for (uint64_t p0 = 0; p0 < n_pixels; p0 += px_per_batch) {
+    const uint32_t np = (uint32_t)((n_pixels - p0) < px_per_batch ? (n_pixels - p0) : px_per_batch);
+    const size_t paths = (size_t)np * spp;
+    RTF_CUDA(cudaMemsetAsync(ctx->ws.counters.p, 0, 4096, ctx->stream));
+    LAUNCH(ctx, k_gen_camera, div_up(paths, 256), 256, 0, cp, p0, np, spp, q, ps);
+    PathMap pm{1, p0 * spp, 0ull, 0u, 0u, 0u, 0u};
+    if ((rc = run_wavefronts(ctx, env, rp->bounces, (uint32_t)cp.frame_id, pm, paths, q, ps, true))) return rc;
+    LAUNCH(ctx, k_resolve_camera, div_up(np, 256), 256, 0, cp, p0, np, spp, ps, cam->color.as<float4>(),
+           cam->normal.as<float4>(), cam->albedo.as<float4>());
+  }
+  RTF_CUDA(cudaGetLastError());
+  ctx->last_paths = n_pixels * spp;
+  return RTF_OK;
+}
+
+// ============================ roofline denominators ===================================================
+__global__ void k_fp32_peak(float* out, int iters) {
+  float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.0f, a2 = a0 + 2.0f, a3 = a0 + 3.0f;
+  float a4 = a0 + 4.0f, a5 = a0 + 5.0f, a6 = a0 + 6.0f, a7 = a0 + 7.0f;
+  const float b = 1.000001f, c = 1e-7f;
+  for (int i = 0; i < iters; i++) {
+    a0 = fmaf(a0, b, c), a1 = fmaf(a1, b, c), a2 = fmaf(a2, b, c), a3 = fmaf(a3, b, c);
+    a4 = fmaf(a4, b, c), a5 = fmaf(a5, b, c), a6 = fmaf(a6, b, c), a7 = fmaf(a7, b, c);
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+}
+int microbench_fp32(rtf_ctx* ctx, double* tflops) {
+  DevBuf out;
+  const int blocks = ctx->sm_count * 16, threads = 256, iters = 1 << 14;
+  int rc;
+  if ((rc = out.reserve((size_t)blocks * threads * 4))) return rc;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0), cudaEventCreate(&e1);
+  LAUNCH(ctx, k_fp32_peak, blocks, threads, 0, out.as<float>(), iters);
+  cudaEventRecord(e0, ctx->stream);
+  LAUNCH(ctx, k_fp32_peak, blocks, threads, 0, out.as<float>(), iters);
+  cudaEventRecord(e1, ctx->stream);
+  cudaError_t e = cudaEventSynchronize(e1);
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0), cudaEventDestroy(e1);
+  out.release();
+  if (e != cudaSuccess) return cuda_fail(e, "fp32 microbench", __FILE__, __LINE__);
+  *tflops = (double)blocks * threads * (double)iters * 8.0 * 2.0 / (ms * 1e-3) / 1e12;
+  return RTF_OK;
+}
+__global__ void k_l2_read(const uint4* __restrict__ src, size_t n_vec, int reps, uint4* sink) {
+  uint4 acc = make_uint4(0, 0, 0, 0);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (int r = 0; r < reps; r++)
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride) {
+      const uint4 v = __ldg(src + i);
+      acc.x ^= v.x, acc.y ^= v.y, acc.z ^= v.z, acc.w ^= v.w;
+    }
+  if (acc.x == 0x12345678u && acc.y == 0x9abcdef0u) *sink = acc;
+}
+int microbench_l2(rtf_ctx* ctx, double bytes, double* gbs) {
+  DevBuf buf, sink;
+  const size_t n_vec = (size_t)(bytes / 16.0);
+  int rc;
+  if ((rc = buf.reserve(n_vec * 16))) return rc;
+  if ((rc = sink.reserve(64))) return rc;
+  cudaMemsetAsync(buf.p, 1, n_vec * 16, ctx->stream);
+  const int reps = 20;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0), cudaEventCreate(&e1);
+  LAUNCH(ctx, k_l2_read, ctx->sm_count * 8, 512, 0, buf.as<uint4>(), n_vec, 2, sink.as<uint4>());
+  cudaEventRecord(e0, ctx->stream);
+  LAUNCH(ctx, k_l2_read, ctx->sm_count * 8, 512, 0, buf.as<uint4>(), n_vec, reps, sink.as<uint4>());
+  cudaEventRecord(e1, ctx->stream);
+  cudaError_t e = cudaEventSynchronize(e1);
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0), cudaEventDestroy(e1);
+  buf.release(), sink.release();
+  if (e != cudaSuccess) return cuda_fail(e, "l2 microbench", __FILE__, __LINE__);
+  *gbs = (double)n_vec * 16.0 * reps / (ms * 1e-3) / 1e9;
+  return RTF_OK;
+}
+
+}  // namespace rtf

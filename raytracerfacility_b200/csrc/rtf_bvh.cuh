@@ -1,0 +1,115 @@
+// rtf_bvh.cuh — data layout of the acceleration structure + the pure functions of its builder.
+//
+// This replaces the closed-source half of the reference path: optixAccelBuild
+// (/root/reference/src/RayTracerFacility/RayTracer.cu:1528-1584 GAS, :1654-1707 IAS).  Algorithms:
+// Karras HPG'12 (Morton + radix tree), Ylitie/Karras/Laine HPG'17 (80 B 8-wide compressed node).
+//
+// HBM layout (DESIGN.md "Data layout"):
+//   wide node  = 80 B = 5 x 16 B, fetched as five 128-bit loads:
+//       q0 = {p.x, p.y, p.z, e.x | e.y<<8 | e.z<<16 | imask<<24}
+//       q1 = {child_base, tri_base, meta[0..3], meta[4..7]}
+//       q2 = {qlo.x[0..3], qlo.x[4..7], qlo.y[0..3], qlo.y[4..7]}
+//       q3 = {qlo.z[0..3], qlo.z[4..7], qhi.x[0..3], qhi.x[4..7]}
+//       q4 = {qhi.y[0..3], qhi.y[4..7], qhi.z[0..3], qhi.z[4..7]}
+//   triangle   = 48 B = 3 x 16 B: {v0.xyz, prim}, {v1.xyz, inst}, {v2.xyz, flags}
+#pragma once
+#include "rtf_math.cuh"
+
+namespace rtf {
+
+struct __align__(16) Node80 {
+  float p[3];
+  uint8_t e[3];
+  uint8_t imask;
+  uint32_t child_base;
+  uint32_t tri_base;
+  uint8_t meta[8];
+  uint8_t qlo[3][8];
+  uint8_t qhi[3][8];
+};
+static_assert(sizeof(Node80) == 80, "node must be 80 B");
+
+struct __align__(16) Tri48 {
+  float v0[3];
+  uint32_t prim;
+  float v1[3];
+  uint32_t inst;
+  float v2[3];
+  uint32_t flags;
+};
+static_assert(sizeof(Tri48) == 48, "triangle must be 48 B");
+
+enum { TRI_FLAG_ALPHA = 1u };  // material may ignore hits (RayFunctions.cuh:5-23)
+
+struct Box3 {
+  float3 lo, hi;
+};
+
+RTF_HD uint32_t expand10(uint32_t v) {
+  v &= 0x3ffu;
+  v = (v | (v << 16)) & 0x030000FFu;
+  v = (v | (v << 8)) & 0x0300F00Fu;
+  v = (v | (v << 4)) & 0x030C30C3u;
+  v = (v | (v << 2)) & 0x09249249u;
+  return v;
+}
+RTF_HD uint64_t expand21(uint64_t v) {
+  v &= 0x1fffffull;
+  v = (v | (v << 32)) & 0x1f00000000ffffull;
+  v = (v | (v << 16)) & 0x1f0000ff0000ffull;
+  v = (v | (v << 8)) & 0x100f00f00f00f00full;
+  v = (v | (v << 4)) & 0x10c30c30c30c30c3ull;
+  v = (v | (v << 2)) & 0x1249249249249249ull;
+  return v;
+}
+RTF_HD uint32_t quantize_axis(float c, float lo, float inv, float scale, float maxq) {
+  float nx = (c - lo) * inv;
+  float q = fminf(fmaxf(nx * scale, 0.0f), maxq);
+  return (uint32_t)q;
+}
+// 30-bit (10/axis) or 63-bit (21/axis) Morton code of a centroid; x owns the most significant bit.
+RTF_HD uint64_t morton_code(float3 c, float3 lo, float3 inv, int bits) {
+  if (bits == 30) {
+    uint32_t x = quantize_axis(c.x, lo.x, inv.x, 1024.0f, 1023.0f);
+    uint32_t y = quantize_axis(c.y, lo.y, inv.y, 1024.0f, 1023.0f);
+    uint32_t z = quantize_axis(c.z, lo.z, inv.z, 1024.0f, 1023.0f);
+    return (uint64_t)((expand10(x) << 2) | (expand10(y) << 1) | expand10(z));
+  }
+  uint64_t x = quantize_axis(c.x, lo.x, inv.x, 2097152.0f, 2097151.0f);
+  uint64_t y = quantize_axis(c.y, lo.y, inv.y, 2097152.0f, 2097151.0f);
+  uint64_t z = quantize_axis(c.z, lo.z, inv.z, 2097152.0f, 2097151.0f);
+  return (expand21(x) << 2) | (expand21(y) << 1) | expand21(z);
+}
+
+RTF_HD float half_area(const Box3& b) {
+  float3 d = b.hi - b.lo;
+  return (d.x * d.y + d.y * d.z) + d.z * d.x;
+}
+
+// Biased exponent e with 2^(e-127) * 255 >= extent (integer bit operations only, no log2f).
+RTF_HD uint32_t quant_exponent(float extent) {
+  float f = extent / 255.0f;
+  uint32_t bits = f2u(f);
+  uint32_t e = (bits >> 23) & 0xffu;
+  if (bits & 0x7fffffu) e += 1;
+  if (e < 1) e = 1;
+  if (u2f(e << 23) * 255.0f < extent) e += 1;
+  if (e > 254) e = 254;
+  return e;
+}
+
+// Conservative 8-bit quantisation of [lo,hi] against origin p and scale 2^(e-127).
+RTF_HD void quantize_interval(float lo, float hi, float p, uint32_t e, uint8_t& qlo, uint8_t& qhi) {
+  float inv_scale = u2f((254u - e) << 23);
+  float scale = u2f(e << 23);
+  float ql = floorf((lo - p) * inv_scale);
+  float qh = ceilf((hi - p) * inv_scale);
+  ql = fminf(fmaxf(ql, 0.0f), 255.0f);
+  qh = fminf(fmaxf(qh, 0.0f), 255.0f);
+  while (ql > 0.0f && p + ql * scale > lo) ql -= 1.0f;
+  while (qh < 255.0f && p + qh * scale < hi) qh += 1.0f;
+  qlo = (uint8_t)ql;
+  qhi = (uint8_t)qh;
+}
+
+}  // namespace rtf

@@ -1,0 +1,148 @@
+// rtf_internal.h — context, device scene and workspace shared by the translation units of librtf_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/rtf/rtf.h"
+#include "rtf_bvh.cuh"
+
+namespace rtf {
+
+constexpr int kMaxStackDepth = 64;  // wide-BVH depth the traversal stack can hold (checked at commit)
+
+void set_error(const std::string& msg);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define RTF_CUDA(expr)                                                         \
+  do {                                                                         \
+    cudaError_t e_ = (expr);                                                   \
+    if (e_ != cudaSuccess) return ::rtf::cuda_fail(e_, #expr, __FILE__, __LINE__); \
+  } while (0)
+
+// Grow-only device buffer (replaces the reference's CudaBuffer, CUDABuffer.cpp:13-38, which frees and
+// cudaMallocs on every size change and on every entry-point call, CUDAModule.cpp:43-49).
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return RTF_OK;
+    if (p) cudaFree(p);
+    p = nullptr, cap = 0;
+    cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc", __FILE__, __LINE__);
+    cap = bytes;
+    return RTF_OK;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr, cap = 0;
+  }
+  template <class T>
+  T* as() const {
+    return (T*)p;
+  }
+};
+
+struct InstDev {
+  float xform[16];
+  uint64_t handle;  // private component handle (SBT::m_handle, RayTracer.cu:1859)
+  uint32_t mat;
+  uint32_t first_prim;
+  uint32_t n_prims;
+  uint32_t pad_;
+  const rtf_vertex* verts;
+  const uint32_t* tris;
+};
+
+// Everything a kernel needs to trace and shade, passed by value.
+struct DevScene {
+  const uint4* nodes = nullptr;
+  const float4* tris = nullptr;
+  const float* pos9 = nullptr;
+  const float* nrm9 = nullptr;
+  const uint32_t* tri_inst = nullptr;
+  const InstDev* insts = nullptr;
+  const rtf_material* mats = nullptr;
+  const float* inst_alpha = nullptr;
+  uint32_t n_tris = 0, n_nodes = 0, n_insts = 0;
+  int has_alpha = 0;
+};
+
+struct Geometry {
+  std::vector<rtf_vertex> verts;
+  std::vector<uint32_t> tris;
+  uint64_t version = 0;
+  DevBuf d_verts, d_tris;
+  bool uploaded = false;
+};
+struct Instance {
+  uint64_t geom, mat;
+  float xform[16];
+  uint64_t component;
+};
+
+// Intermediate arrays of the builder kept for parity read-back (rtf_debug_read).
+struct BuildArrays {
+  DevBuf morton, sorted_keys, sorted_ids, children, parent, range, boxes, flags, scene_bounds;
+  DevBuf keys_alt, ids_alt, cub_tmp, level_a, level_b, cnt_int, cnt_tri, scan_int, scan_tri, stash;
+};
+
+struct Workspace {  // wavefront queues + path state, sized for `capacity` paths
+  size_t capacity = 0;
+  DevBuf ray_a[2], ray_b[2], path_idx[2], hits, counters;
+  DevBuf thr, acc, dir0w, first_n, first_a, first_p;  // per-path state (SoA float4)
+  DevBuf sort_keys, sort_keys_alt, sort_vals, sort_vals_alt, sort_tmp;
+  DevBuf io;  // staging for AoS entry points
+};
+
+}  // namespace rtf
+
+struct rtf_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  uint64_t launches = 0;
+  int sm_count = 148;
+  std::map<uint64_t, rtf::Geometry> geoms;
+  std::map<uint64_t, rtf_material> mats;
+  std::map<uint64_t, rtf::Instance> insts;
+  // committed state
+  bool ready = false;
+  int morton_bits = 63;
+  int depth = 0;
+  uint32_t n_tris = 0, n_nodes = 0;
+  rtf::DevBuf d_pos9, d_nrm9, d_tri_inst, d_nodes, d_tris48, d_insts, d_mats, d_inst_alpha;
+  rtf::BuildArrays ba;
+  rtf::Workspace ws;
+  rtf::DevScene scene;
+  uint64_t last_rays = 0, last_paths = 0;
+  rtf::DevBuf d_stats;  // {rays u64, paths u64}
+};
+
+struct rtf_camera {
+  rtf_ctx* ctx = nullptr;
+  rtf_camera_props props;
+  rtf::DevBuf color, normal, albedo;
+};
+
+namespace rtf {
+// build.cu
+int build_bvh(rtf_ctx* ctx, int morton_bits);
+// render.cu
+int trace_rays_device(rtf_ctx* ctx, const float4* rays_a, const float4* rays_b, int stride, size_t n, float4* hits,
+                      uint32_t* node_visits, uint32_t* tri_visits);
+int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push, int front,
+                      int back, uint64_t tri_begin, uint64_t tri_end, int s0, int s1, float* d_accum6,
+                      const rtf_illum_sampler* d_probes, uint64_t probe_base);
+int illum_finalize_device(rtf_ctx* ctx, float* d_accum6, uint64_t n, int faces, int samples, rtf_illum_sampler* d_probes);
+int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin, uint64_t ray_end, float* d_t,
+                     uint32_t* d_prim, uint32_t* d_inst);
+int scan_samples_device(rtf_ctx* ctx, rtf_pc_sample* d_samples, size_t n, uint32_t* d_prim);
+int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp);
+int microbench_fp32(rtf_ctx* ctx, double* tflops);
+int microbench_l2(rtf_ctx* ctx, double bytes, double* gbs);
+}  // namespace rtf
