@@ -204,6 +204,13 @@ RTF_API int rtf_remove_instance(rtf_ctx* ctx, uint64_t handle);
  * LBVH -> 8-wide compressed BVH on the device.  morton_bits: 30 or 63 (0 = 63). */
 RTF_API int rtf_commit(rtf_ctx* ctx, int morton_bits);
 RTF_API int rtf_triangle_count(rtf_ctx* ctx, uint64_t* n_triangles);
+/* Device time (ms, CUDA events) of the last rtf_commit per stage:
+ * {flatten, bounds+morton, sort, karras+refit, collapse+encode, total}; n >= 6.  (The reference
+ * has no counterpart: its builds are opaque optixAccelBuild calls, RT.cu:1562-1584.) */
+RTF_API int rtf_build_timings(rtf_ctx* ctx, float* ms_out, int n);
+/* Tuning knobs (not in the reference): "batch_paths" = wavefront batch capacity in paths,
+ * "sort_rays" = 0/1 sort bounce rays by (direction octant, origin cell) before tracing. */
+RTF_API int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value);
 
 /* ---- illumination: CudaModule::EstimateIlluminationRayTracing (CM.hpp:38-41, CM.cpp:39-50)
  *      -> RayTracer::EstimateIllumination (RT.cu:605-756) -> __raygen__IE (IE.cu:30-129) ---- */

@@ -78,6 +78,8 @@ int rtf_destroy(rtf_ctx* ctx) {
                     &ctx->ws.sort_keys, &ctx->ws.sort_keys_alt, &ctx->ws.sort_vals, &ctx->ws.sort_vals_alt,
                     &ctx->ws.sort_tmp, &ctx->ws.io};
   for (DevBuf* b : bufs) b->release();
+  for (cudaEvent_t e : ctx->build_ev)
+    if (e) cudaEventDestroy(e);
   if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return RTF_OK;
@@ -245,6 +247,27 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   for (float a : alpha)
     if (a < 1.0f) s.has_alpha = 1;
   ctx->ready = true;
+  return RTF_OK;
+}
+int rtf_build_timings(rtf_ctx* ctx, float* ms_out, int n) {
+  if (!ctx || !ms_out || n < 6) return RTF_ERR_INVALID;
+  for (int k = 0; k < 6; k++) ms_out[k] = ctx->build_ms[k];
+  return RTF_OK;
+}
+int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value) {
+  if (!ctx || !name) return RTF_ERR_INVALID;
+  if (!strcmp(name, "batch_paths")) {
+    if (value < 1024 || value > ((int64_t)1 << 28)) {
+      set_error("batch_paths must be in [2^10, 2^28]");
+      return RTF_ERR_INVALID;
+    }
+    ctx->batch_paths = (size_t)value;
+  } else if (!strcmp(name, "sort_rays")) {
+    ctx->sort_rays = value != 0;
+  } else {
+    set_error(std::string("unknown option ") + name);
+    return RTF_ERR_INVALID;
+  }
   return RTF_OK;
 }
 int rtf_triangle_count(rtf_ctx* ctx, uint64_t* n) {

@@ -322,9 +322,15 @@ __global__ void k_collapse_emit(CollapseArgs a, const int* __restrict__ level, u
   nodes[level_start + li] = node;
 }
 
+static void mark(rtf_ctx* ctx, int k) {
+  if (!ctx->build_ev[k]) cudaEventCreate(&ctx->build_ev[k]);
+  cudaEventRecord(ctx->build_ev[k], ctx->stream);
+}
+
 int flatten_scene(rtf_ctx* ctx) {
   const uint32_t n = ctx->n_tris;
   if (n == 0) return RTF_OK;
+  mark(ctx, 0);
   LAUNCH(ctx, k_flatten, div_up(n, 256), 256, 0, ctx->scene.insts, ctx->scene.n_insts, n, ctx->d_pos9.as<float>(),
          ctx->d_nrm9.as<float>(), ctx->d_tri_inst.as<uint32_t>());
   RTF_CUDA(cudaGetLastError());
@@ -352,11 +358,13 @@ int build_bvh(rtf_ctx* ctx, int bits) {
 
   int* ob = ba.scene_bounds.as<int>();
   float* fb = ba.scene_bounds.as<float>() + 8;
+  mark(ctx, 1);
   LAUNCH(ctx, k_bounds_init, 1, 32, 0, ob);
   LAUNCH(ctx, k_bounds, min(div_up(n, 256), 148u * 8u), 256, 0, ctx->d_pos9.as<float>(), n, ob);
   LAUNCH(ctx, k_bounds_finish, 1, 32, 0, ob, fb);
   LAUNCH(ctx, k_morton, div_up(n, 256), 256, 0, ctx->d_pos9.as<float>(), n, fb, bits, ba.morton.as<uint64_t>(),
          ba.ids_alt.as<uint32_t>());
+  mark(ctx, 2);
   {  // 4. stable LSD radix sort of (Morton, id) pairs.  cub::DeviceRadixSort for bring-up (library code; a
      //    hand-written onesweep sort is the planned replacement).
     size_t tmp = 0;
@@ -368,6 +376,7 @@ int build_bvh(rtf_ctx* ctx, int bits) {
                                              ba.ids_alt.as<uint32_t>(), ba.sorted_ids.as<uint32_t>(), (int)n, 0, end_bit, st));
     ctx->launches += 8;
   }
+  mark(ctx, 3);
   RTF_CUDA(cudaMemsetAsync(ba.parent.p, 0xff, 4 * (size_t)(2 * n), st));
   if (ni > 0) {
     LAUNCH(ctx, k_karras, div_up(ni, 256), 256, 0, ba.sorted_keys.as<uint64_t>(), (int)n, ba.children.as<int2>(),
@@ -378,6 +387,7 @@ int build_bvh(rtf_ctx* ctx, int bits) {
          ba.children.as<int2>(), ba.parent.as<int>(), ba.boxes.as<float>(), ba.flags.as<uint32_t>());
 
   // ---- collapse ----
+  mark(ctx, 4);
   const size_t max_nodes = (size_t)n / 2 + 64;
   const size_t max_level = (size_t)n / 4 + 64;
   if ((rc = ctx->d_nodes.reserve(80 * max_nodes))) return rc;
@@ -433,6 +443,10 @@ int build_bvh(rtf_ctx* ctx, int bits) {
     int* t = lv_cur;
     lv_cur = lv_next, lv_next = t;
   }
+  mark(ctx, 5);
+  RTF_CUDA(cudaEventSynchronize(ctx->build_ev[5]));
+  for (int k = 0; k < 5; k++) cudaEventElapsedTime(&ctx->build_ms[k], ctx->build_ev[k], ctx->build_ev[k + 1]);
+  cudaEventElapsedTime(&ctx->build_ms[5], ctx->build_ev[0], ctx->build_ev[5]);
   if (tri_cursor != n) {
     set_error("BVH collapse lost triangles");
     return RTF_ERR_LIMIT;

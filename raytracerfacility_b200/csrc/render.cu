@@ -390,15 +390,7 @@ __global__ void k_finalize_illum(float* accum6, uint64_t n, int faces, int sampl
   }
 }
 
-static size_t batch_capacity() {
-  static size_t cap = 0;
-  if (!cap) {
-    const char* e = getenv("RTF_BATCH_PATHS");
-    cap = e ? (size_t)atoll(e) : ((size_t)1 << 22);
-    if (cap < 1024) cap = 1024;
-  }
-  return cap;
-}
+static size_t batch_capacity(const rtf_ctx* ctx) { return ctx->batch_paths < 1024 ? 1024 : ctx->batch_paths; }
 
 static int ensure_workspace(rtf_ctx* ctx, size_t cap, bool camera) {
   Workspace& w = ctx->ws;
@@ -472,7 +464,7 @@ int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp,
   if (tri_end <= tri_begin || s1 <= s0) return RTF_OK;
   const uint32_t sc_ = (uint32_t)(s1 - s0);
   const size_t per_probe = 2 * (size_t)sc_;
-  size_t cap = batch_capacity();
+  size_t cap = batch_capacity(ctx);
   if (cap < per_probe) cap = per_probe;
   int rc;
   if ((rc = ensure_workspace(ctx, cap, false))) return rc;
@@ -712,7 +704,7 @@ int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, cons
     return RTF_ERR_INVALID;
   }
   const uint32_t spp = (uint32_t)rp->samples;
-  size_t cap = batch_capacity();
+  size_t cap = batch_capacity(ctx);
   if (cap < spp) cap = spp;
   int rc;
   if ((rc = ensure_workspace(ctx, cap, true))) return rc;

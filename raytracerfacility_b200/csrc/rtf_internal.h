@@ -121,6 +121,12 @@ struct rtf_ctx {
   rtf::DevScene scene;
   uint64_t last_rays = 0, last_paths = 0;
   rtf::DevBuf d_stats;  // {rays u64, paths u64}
+  // options (rtf_set_option)
+  size_t batch_paths = (size_t)1 << 22;
+  int sort_rays = 1;
+  // build-stage events: flatten | bounds+morton | sort | karras+refit | collapse | end
+  cudaEvent_t build_ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  float build_ms[6] = {0, 0, 0, 0, 0, 0};
 };
 
 struct rtf_camera {

@@ -1,0 +1,138 @@
+"""Multi-GPU sharding of the three entry points: one process per GPU (torch.distributed), BVH replicated,
+work split, at most one collective per job.  The reference is single-GPU (CUDAModule.cpp:25
+`cudaSetDevice(0)`), so this layer is new; it only ever calls the C ABI through module.RayTracer.
+
+* illumination: SAMPLE-sharded (rank r traces samples [r*S/G, (r+1)*S/G) of every triangle), partial sums
+  {sum E, sum D} per triangle, ONE all-reduce(sum) of 6*nTris floats, then finalize (IlluminationEstimation.cu:125-128).
+  Alternative `triangle` mode: contiguous triangle ranges + all-gather, bit-identical to one GPU.
+* LiDAR: contiguous ray ranges, no data-path collective (each rank writes its own slice), optional all-gather.
+* camera: contiguous row bands per rank, all-gather of the float4 bands.
+
+`compute` callbacks make the wiring testable on CPU with the gloo backend (tests inject the oracle there).
+"""
+import numpy as np
+
+
+def split_range(n, world, rank):
+    """Contiguous, balanced [begin, end) of n units for `rank` of `world` (the first n % world ranks get one more)."""
+    base, rem = divmod(int(n), int(world))
+    begin = rank * base + min(rank, rem)
+    return begin, begin + base + (1 if rank < rem else 0)
+
+
+def sample_shard(samples, world, rank):
+    return split_range(samples, world, rank)
+
+
+def init_distributed(backend=None):
+    """Initialise torch.distributed from the torchrun environment; returns (rank, world, local_rank)."""
+    import os
+
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+            dist.init_process_group(backend, device_id=torch.device("cuda", local))
+        else:
+            dist.init_process_group(backend)
+    return rank, world, local
+
+
+def illumination_sample_sharded(n_tris, samples, faces, compute_partial, finalize, all_reduce_sum, world, rank, accum):
+    """accum: zero-initialised 6*n_tris float buffer (torch tensor, device or CPU).
+    compute_partial(s0, s1, accum) adds the raw sums of samples [s0, s1) for all triangles;
+    all_reduce_sum(accum) sums across ranks in place; finalize(accum, faces, samples) normalises in place."""
+    s0, s1 = sample_shard(samples, world, rank)
+    if s1 > s0:
+        compute_partial(s0, s1, accum)
+    if world > 1:
+        all_reduce_sum(accum)
+    finalize(accum, faces, samples)
+    return accum
+
+
+def illumination_triangle_sharded(n_tris, compute_range, all_gather, world, rank):
+    """compute_range(t0, t1) -> finalised (t1-t0, 6) array for its triangle range; all_gather(list-of-sizes, local)
+    returns the concatenation over ranks (bit-identical to a single-GPU run)."""
+    t0, t1 = split_range(n_tris, world, rank)
+    local = compute_range(t0, t1)
+    if world == 1:
+        return local
+    sizes = [split_range(n_tris, world, r) for r in range(world)]
+    return all_gather([e - b for b, e in sizes], local)
+
+
+class DistributedRayTracer:
+    """One RayTracer per rank + the collectives.  Scene calls are replicated (every rank builds the same BVH)."""
+
+    def __init__(self, rt, rank=0, world=1, group=None):
+        self.rt, self.rank, self.world, self.group = rt, rank, world, group
+
+    def estimate_illumination_mesh(self, env, ray_props, seed, push=0.001, front=True, back=True, mode="sample"):
+        """Returns a CUDA float32 tensor (n_tris, 6) = {energy, direction}, identical on all ranks."""
+        import torch
+        import torch.distributed as dist
+        rt = self.rt
+        n = rt.triangle_count
+        faces = int(bool(front)) + int(bool(back))
+        dev = torch.device("cuda", rt.device)
+        if mode == "sample":
+            accum = torch.zeros(n * 6, dtype=torch.float32, device=dev)
+
+            def compute_partial(s0, s1, acc):
+                rt.estimate_illumination_mesh_device(env, ray_props, seed, push, front, back, 0, n, s0, s1, acc.data_ptr())
+
+            def finalize(acc, f, s):
+                rt.illumination_finalize_device(acc.data_ptr(), n, f, s)
+
+            def all_reduce_sum(acc):
+                dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=self.group)
+
+            illumination_sample_sharded(n, ray_props.samples, faces, compute_partial, finalize, all_reduce_sum,
+                                        self.world, self.rank, accum)
+            return accum.view(n, 6)
+        # triangle mode
+        out = torch.zeros(n * 6, dtype=torch.float32, device=dev)
+        t0, t1 = split_range(n, self.world, self.rank)
+        if t1 > t0:
+            rt.estimate_illumination_mesh_device(env, ray_props, seed, push, front, back, t0, t1, 0, ray_props.samples,
+                                                 out.data_ptr())
+            rt.illumination_finalize_device(out.data_ptr() + 24 * t0, t1 - t0, faces, ray_props.samples)
+        if self.world > 1:
+            parts = [out[6 * b:6 * e] for b, e in (split_range(n, self.world, r) for r in range(self.world))]
+            if len({p.numel() for p in parts}) == 1:
+                dist.all_gather(parts, parts[self.rank].clone(), group=self.group)
+            else:
+                for r, p in enumerate(parts):
+                    dist.broadcast(p, src=r, group=self.group)
+        return out.view(n, 6)
+
+    def scan_grid(self, grid, gather=False):
+        """Each rank traces its contiguous ray range into device SoA tensors (t, prim); optional all-gather."""
+        import torch
+        import torch.distributed as dist
+        rt = self.rt
+        total = rt.scan_grid_ray_count(grid)
+        b, e = split_range(total, self.world, self.rank)
+        dev = torch.device("cuda", rt.device)
+        t = torch.empty(e - b, dtype=torch.float32, device=dev)
+        prim = torch.empty(e - b, dtype=torch.int32, device=dev)
+        if e > b:
+            rt.scan_grid_device(grid, b, e, t.data_ptr(), prim.data_ptr())
+        if not gather or self.world == 1:
+            return (b, e), t, prim
+        sizes = [split_range(total, self.world, r) for r in range(self.world)]
+        full_t = torch.empty(total, dtype=torch.float32, device=dev)
+        full_p = torch.empty(total, dtype=torch.int32, device=dev)
+        for r, (rb, re) in enumerate(sizes):
+            if r == self.rank:
+                full_t[rb:re], full_p[rb:re] = t, prim
+            dist.broadcast(full_t[rb:re], src=r, group=self.group)
+            dist.broadcast(full_p[rb:re], src=r, group=self.group)
+        return (0, total), full_t, full_p

@@ -273,3 +273,53 @@ def scene_bounds(sd):
         w = v @ m[:3, :3].T + m[:3, 3]
         lo, hi = np.minimum(lo, w.min(0)), np.maximum(hi, w.max(0))
     return lo, hi
+
+
+# ---- device-side generation of the same ray set (bench: 2^26 rays would take ~a minute in numpy) ------------
+def _s64(x):
+    x &= (1 << 64) - 1
+    return x - (1 << 64) if x >= (1 << 63) else x
+
+
+def _lsr(z, k):
+    return (z >> k) & ((1 << (64 - k)) - 1)
+
+
+def _splitmix64_torch(x):
+    x = x + _s64(0x9E3779B97F4A7C15)
+    z = x
+    z = (z ^ _lsr(z, 30)) * _s64(0xBF58476D1CE4E5B9)
+    z = (z ^ _lsr(z, 27)) * _s64(0x94D049BB133111EB)
+    return z ^ _lsr(z, 31)
+
+
+def hash_uniform_torch(seed, idx, dim):
+    """hash_uniform() with torch int64 tensors (two's-complement wrap == uint64 arithmetic); float64 out."""
+    import torch
+    k = idx * _s64(0x100000001B3) + _s64(dim * 0x9E3779B1) + _s64(seed * 0xD6E8FEB86659FD93)
+    k = _splitmix64_torch(_splitmix64_torch(k))
+    return _lsr(k, 11).to(torch.float64) * (1.0 / 9007199254740992.0)
+
+
+def incoherent_rays_torch(n, lo, hi, seed=3, tmin=0.0, tmax=1e20, start=0, device="cuda", chunk=1 << 22):
+    """incoherent_rays() generated on the device; (n, 8) float32 tensor.  Integer hashing is bit-identical to the
+    numpy version; cos/sin(float64) may differ in the last float32 bit on a vanishing fraction of rays."""
+    import torch
+    out = torch.empty((n, 8), dtype=torch.float32, device=device)
+    lo = [float(x) for x in lo]
+    hi = [float(x) for x in hi]
+    for b in range(0, n, chunk):
+        e = min(n, b + chunk)
+        idx = torch.arange(start + b, start + e, dtype=torch.int64, device=device)
+        o = out[b:e]
+        for d in range(3):
+            o[:, d] = (lo[d] + (hi[d] - lo[d]) * hash_uniform_torch(seed, idx, d)).to(torch.float32)
+        z = 1.0 - 2.0 * hash_uniform_torch(seed, idx, 3)
+        ph = (2 * math.pi) * hash_uniform_torch(seed, idx, 4)
+        r = torch.sqrt(torch.clamp(1.0 - z * z, min=0.0))
+        o[:, 3] = tmin
+        o[:, 4] = (r * torch.cos(ph)).to(torch.float32)
+        o[:, 5] = z.to(torch.float32)
+        o[:, 6] = (r * torch.sin(ph)).to(torch.float32)
+        o[:, 7] = tmax
+    return out

@@ -1,0 +1,102 @@
+"""Generates the committed fixtures in tests/golden/.  Run in the authoring container:
+    make -C oracle ref && python tests/golden/make_golden.py
+
+* lcg_kat.json   — outputs of the REFERENCE's own RNG header
+                   (/root/reference/include/RayTracerFacility/RayTracer/LinearCongruenceGenerator.hpp),
+                   compiled verbatim into oracle/_ref/liblcg_ref.so.  Pins orc::LCG (oracle_math.h).
+* oracle_small.npz — outputs of the CPU oracle on small seeded inputs (hits, visit counts, Morton codes,
+                   irradiance, LiDAR, camera).  The reference has no tests/fixtures for these, so this
+                   file guards the oracle against drift and gives the GPU tests stored vectors to hit as well.
+"""
+import ctypes as C
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+from oracle import pyoracle as orc  # noqa: E402
+from raytracerfacility_b200 import scenes, structs as S  # noqa: E402
+
+LCG_SEEDS = [(0, 0), (1, 0), (0, 1), (12345, 678), (20001, 0x5EED), (0xFFFFFFFF, 0xFFFFFFFF), (1920 * 1080 - 1, 7)]
+
+
+def small_cases():
+    """The seeded inputs shared by make_golden.py and the tests."""
+    soup = scenes.random_soup(2000, seed=7)
+    lo, hi = scenes.scene_bounds(soup)
+    rays = scenes.incoherent_rays(4096, lo - 0.2, hi + 0.2, seed=3)
+    illum_scene = scenes.random_soup(300, seed=11, extent=1.0, size=0.35)
+    env = S.EnvironmentProperties()
+    rp = S.RayProperties(bounces=3, samples=16)
+    grid = scenes.lidar_grid(center=(0.5, 3.0, 0.5), size=(1.6, 0.8), distance=(0.04, 0.04))
+    return dict(soup=soup, rays=rays, illum_scene=illum_scene, env=env, rp=rp, grid=grid)
+
+
+def camera_props(width=16, height=12):
+    """CameraProperties::Set (RayTracer.cu:28-46) for position (0.5,0.5,3), identity rotation, fov 120 (60 effective)."""
+    import math
+    cp = S.CameraProps()
+    cp.accumulate, cp.fov, cp.max_distance, cp.gamma = 0, 120.0, 50.0, 2.2
+    cp.width, cp.height, cp.frame_id, cp.aperture, cp.focal_length = width, height, 0, 0.0, 1.0
+    cp.output_type = S.OUT_COLOR
+    pos = np.array([0.5, 0.5, 3.0])
+    front, up = np.array([0.0, 0, -1]), np.array([0.0, 1, 0])
+    aspect = width / height
+    half = math.radians(cp.fov * 0.5)
+    th = math.tan(half / 2)
+    zn, zf = 0.1, 100.0
+    proj = np.zeros((4, 4))
+    proj[0, 0], proj[1, 1], proj[2, 2], proj[3, 2], proj[2, 3] = 1 / (aspect * th), 1 / th, -(zf + zn) / (zf - zn), -1, -2 * zf * zn / (zf - zn)
+    s = np.cross(front, up)
+    s /= np.linalg.norm(s)
+    u = np.cross(s, front)
+    view = np.eye(4)
+    view[0, :3], view[1, :3], view[2, :3] = s, u, -front
+    view[0, 3], view[1, 3], view[2, 3] = -s @ pos, -u @ pos, front @ pos
+    inv = np.linalg.inv(proj @ view)
+    cp.inverse_projection_view[:] = [float(x) for x in inv.T.reshape(16)]  # column-major
+    cp.from_[:] = [float(x) for x in pos]
+    cp.horizontal[:] = [float(x) for x in (half * aspect * s)]
+    cp.vertical[:] = [float(x) for x in (half * up)]
+    return cp
+
+
+def main():
+    ref = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "liblcg_ref.so"))
+    kat = []
+    for v0, v1 in LCG_SEEDS:
+        out = (C.c_float * 8)()
+        st = C.c_uint32()
+        ref.ref_lcg(C.c_uint32(v0), C.c_uint32(v1), 8, out, C.byref(st))
+        kat.append(dict(v0=v0, v1=v1, state=st.value,
+                        out_bits=[int(np.float32(x).view(np.uint32)) for x in out]))
+    with open(os.path.join(HERE, "lcg_kat.json"), "w") as f:
+        json.dump(dict(source="reference LinearCongruenceGenerator.hpp via oracle/_ref/liblcg_ref.so", kat=kat), f, indent=1)
+
+    c = small_cases()
+    osc = orc.OracleScene(c["soup"], 63)
+    hits, nv, tv = osc.trace(c["rays"], counts=True)
+    morton = osc.debug(S.DBG_MORTON)
+    order = osc.debug(S.DBG_SORTED_IDS)
+    osc30 = orc.OracleScene(c["soup"], 30)
+    ill = orc.OracleScene(c["illum_scene"], 63)
+    irr, st = ill.illum_mesh(c["env"], c["rp"], seed=0x5EED, push=1e-3)
+    t, prim, inst, _ = ill.scan_grid(c["grid"])
+    cp = camera_props()
+    col, nrm, alb, _ = ill.camera(c["env"], S.RayProperties(bounces=2, samples=4), cp)
+    np.savez_compressed(os.path.join(HERE, "oracle_small.npz"), hits=hits.view(np.uint32).reshape(-1, 4), node_visits=nv,
+                        tri_visits=tv, morton63=morton, order63=order, morton30=osc30.debug(S.DBG_MORTON),
+                        order30=osc30.debug(S.DBG_SORTED_IDS), n_nodes=np.array([osc.n_nodes, osc.depth]),
+                        irradiance=irr.view(np.uint32), illum_rays=np.array([st.rays, st.paths]),
+                        lidar_t=t.view(np.uint32), lidar_prim=prim, camera_color=col.view(np.uint32),
+                        camera_normal=nrm.view(np.uint32), camera_albedo=alb.view(np.uint32))
+    print("wrote", os.listdir(HERE))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,94 @@
+"""GPU LBVH builder vs the CPU oracle, stage by stage, bit for bit (through the C ABI's parity read-back).
+Replaces optixAccelBuild (RayTracer.cu:1528-1584, 1654-1707) — closed source, so the oracle is the pin."""
+import numpy as np
+import pytest
+
+from .conftest import assert_bit_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def _compare_all(rt, osc, S):
+    assert rt.triangle_count == osc.n_tris
+    for what, name in [(S.DBG_FLAT_POS, "flat pos"), (S.DBG_FLAT_NRM, "flat nrm"), (S.DBG_FLAT_INST, "flat inst"),
+                       (S.DBG_SCENE_BOUNDS, "scene bounds"), (S.DBG_MORTON, "morton"), (S.DBG_SORTED_IDS, "sorted ids"),
+                       (S.DBG_BIN_CHILDREN, "children"), (S.DBG_BIN_PARENT, "parent"), (S.DBG_BIN_BOXES, "boxes"),
+                       (S.DBG_WIDE_NODES, "wide nodes"), (S.DBG_WIDE_TRIS, "wide tris")]:
+        assert_bit_equal(rt.debug(what), osc.debug(what), name)
+
+
+@pytest.mark.parametrize("n,bits", [(1, 63), (2, 63), (3, 30), (4, 63), (5, 30), (9, 63), (100, 30), (257, 63),
+                                    (5000, 63), (5000, 30), (100000, 63)])
+def test_soup_build_bit_exact(rt, orc, S, scenes, n, bits):
+    sd = scenes.random_soup(n, seed=n, size=0.08 if n < 50000 else 0.02)
+    rt.load_scene(sd, bits)
+    _compare_all(rt, orc.OracleScene(sd, bits), S)
+
+
+def test_duplicates_and_degenerates_bit_exact(rt, orc, S, scenes):
+    sd = scenes.random_soup(64, seed=5, size=0.6)
+    v, t = sd.geometries[1]
+    v = np.concatenate([v, v, v[:3]])
+    t = np.concatenate([t, t + 192, [[384, 384, 384]], [[384, 385, 385]]]).astype(np.uint32)
+    sd.geometries[1] = (v, t)
+    for bits in (30, 63):
+        rt.load_scene(sd, bits)
+        _compare_all(rt, orc.OracleScene(sd, bits), S)
+
+
+@pytest.mark.parametrize("bits", [30, 63])
+def test_sorghum_c1_build_bit_exact(rt, orc, S, scenes, bits):
+    sd = scenes.sorghum_scene(1)
+    rt.load_scene(sd, bits)
+    assert rt.triangle_count == 20002
+    _compare_all(rt, orc.OracleScene(sd, bits), S)
+    tm = rt.build_timings()
+    assert tm["total"] > 0
+
+
+def test_instanced_field_build_bit_exact(rt, orc, S, scenes):
+    sd = scenes.sorghum_scene(6)  # 6 transformed instances of one geometry + ground = 120 002 triangles
+    rt.load_scene(sd, 63)
+    assert rt.triangle_count == 120002
+    _compare_all(rt, orc.OracleScene(sd, 63), S)
+
+
+def test_rebuild_after_scene_edit(rt, orc, S, scenes):
+    sd = scenes.sorghum_scene(3)
+    rt.load_scene(sd, 63)
+    rt.remove_instance(11)
+    del sd.instances[11]
+    rt.build_ias(63)
+    _compare_all(rt, orc.OracleScene(sd, 63), S)
+    with pytest.raises(Exception):
+        rt.remove_instance(11)
+
+
+def test_not_ready_and_bad_arguments(rt, mod, S, scenes):
+    env, rp = S.EnvironmentProperties(), S.RayProperties()
+    rays = np.zeros((4, 8), dtype=np.float32)
+    with pytest.raises(mod.RtfError) as e:  # reference: silent return when there is no AS (RayTracer.cu:610-611)
+        rt.trace_closest(rays)
+    assert e.value.code == mod.ERR_NOT_READY
+    cam = rt.create_camera()
+    cam.resize(8, 8)
+    cam.set((0, 0, 3))
+    assert rt.render_to_camera(env, cam, rp) is False  # RayTracer.cu:248-249
+    cam.destroy()
+    with pytest.raises(mod.RtfError):
+        rt.build_ias(17)
+    sd = scenes.random_soup(4, seed=1)
+    v, t = sd.geometries[1]
+    with pytest.raises(mod.RtfError):
+        rt.set_geometry(1, v, t + 100)  # index out of range
+    rt.set_geometry(1, v, t)
+    rt.set_material(1, sd.materials[1])
+    rt.set_instance(1, 1, 99, scenes.IDENTITY)  # unknown material
+    with pytest.raises(mod.RtfError) as e:
+        rt.build_ias()
+    assert e.value.code == mod.ERR_NOT_FOUND
+    # empty scene: commit succeeds, entry points stay "not ready"
+    rt.remove_instance(1)
+    rt.build_ias()
+    with pytest.raises(mod.RtfError):
+        rt.trace_closest(rays)

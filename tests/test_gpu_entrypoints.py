@@ -1,0 +1,208 @@
+"""The three entry points through the C ABI vs the oracle: illumination estimation (IlluminationEstimation.cu),
+virtual LiDAR (PointCloudScanning.cu, PointCloudScanner.cpp) and camera rendering (CameraRendering.cu).
+Tolerances: hit ids / LiDAR t bit-exact; energies, directions, colours <= 1e-5 relative (north_star)."""
+import os
+
+import numpy as np
+import pytest
+
+from .conftest import GOLDEN, assert_bit_equal
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5  # BASELINE.json north_star: "within 1e-5 relative for the same RNG sequence"
+
+
+def close(a, b, what, rtol=RTOL, atol=0.0):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    err = np.abs(a - b) - (atol + rtol * np.abs(b))
+    assert np.all(err <= 0), f"{what}: max excess {err.max():.3e} at {np.unravel_index(err.argmax(), err.shape)}"
+
+
+def test_golden_small_cases(rt, S):
+    from tests.golden.make_golden import camera_props, small_cases
+    g = np.load(os.path.join(GOLDEN, "oracle_small.npz"))
+    c = small_cases()
+    rt.load_scene(c["illum_scene"], 63)
+    irr = rt.estimate_illumination_mesh(c["env"], c["rp"], seed=0x5EED, push=1e-3)
+    gold = g["irradiance"].view(np.float32)
+    close(irr[:, :3], gold[:, :3], "energy")
+    close(irr[:, 3:], gold[:, 3:], "direction", atol=1e-5)
+    rays, paths = rt.last_job_stats()
+    assert [rays, paths] == g["illum_rays"].tolist()
+    t, prim, inst = rt.scan_grid(c["grid"])
+    assert_bit_equal(t.view(np.uint32), g["lidar_t"], "lidar t")
+    assert np.array_equal(prim, g["lidar_prim"])
+    cam = rt.create_camera()
+    cp = camera_props()
+    cam.resize(cp.width, cp.height)
+    for f, _ in S.CameraProps._fields_:
+        setattr(cam.props, f, getattr(cp, f))
+    assert rt.render_to_camera(c["env"], cam, S.RayProperties(bounces=2, samples=4))
+    close(cam.download(S.OUT_COLOR).reshape(-1, 4), g["camera_color"].view(np.float32), "colour")
+    close(cam.download(S.OUT_NORMAL).reshape(-1, 4), g["camera_normal"].view(np.float32), "normal", atol=1e-6)
+    close(cam.download(S.OUT_ALBEDO).reshape(-1, 4), g["camera_albedo"].view(np.float32), "albedo")
+    cam.destroy()
+
+
+def test_c1_illumination_parity(rt, orc, S, scenes):
+    """BASELINE config 1: 20k-triangle sorghum + ground, sky light, 64 samples/triangle, fixed seed."""
+    sd = scenes.sorghum_scene(1)
+    rt.load_scene(sd, 63)
+    osc = orc.OracleScene(sd, 63)
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=4, samples=64)
+    gpu = rt.estimate_illumination_mesh(env, rp, seed=0x5EED, push=1e-3)
+    cpu, st = osc.illum_mesh(env, rp, seed=0x5EED, push=1e-3)
+    close(gpu[:, :3], cpu[:, :3], "energy")
+    close(gpu[:, 3:], cpu[:, 3:], "direction", atol=1e-5)
+    rays, paths = rt.last_job_stats()
+    assert (rays, paths) == (st.rays, st.paths) and paths == 20002 * 64 * 2
+    # flux integration of TriangleIlluminationEstimator::SampleLightProbeGroup (TriangleIlluminationEstimator.cpp:84-91)
+    assert 0.05 < gpu[:, 0].mean() < 0.5
+
+
+def test_illumination_aos_entry_point(rt, orc, S, scenes, mod):
+    """CudaModule::EstimateIlluminationRayTracing signature: 268 B AoS probes in-out."""
+    sd = scenes.random_soup(700, seed=6, size=0.3)
+    rt.load_scene(sd, 63)
+    osc = orc.OracleScene(sd, 63)
+    env, rp = S.EnvironmentProperties(color=(1.0, 0.8, 0.6)), S.RayProperties(bounces=3, samples=32)
+    probes = mod.probes_from_scene(sd)
+    probes["front_face"][::3] = 0
+    probes["back_face"][::5] = 0
+    ref = probes.copy()
+    rt.estimate_illumination(env, rp, probes, 77, 1e-3)
+    osc.illum_probes(env, rp, ref, 77, 1e-3)
+    both_off = (ref["front_face"] == 0) & (ref["back_face"] == 0)
+    assert both_off.sum() > 10
+    close(probes["energy"], ref["energy"], "energy")
+    live = ~both_off
+    close(probes["direction"][live], ref["direction"][live], "direction", atol=1e-5)
+    assert_bit_equal(probes["a"], ref["a"], "inputs untouched")
+    rt.estimate_illumination(env, rp, probes[:0], 77, 1e-3)  # empty input: no-op (RayTracer.cu:612-615)
+
+
+def test_illumination_sharding_and_batches(rt, S, scenes):
+    """Sample-range partial sums add up; triangle ranges and small batches are bit-identical (multi-GPU sharding)."""
+    sd = scenes.random_soup(900, seed=2, size=0.4)
+    rt.load_scene(sd, 63)
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=2, samples=64)
+    whole = rt.estimate_illumination_mesh(env, rp, 9, normalise=False)
+    a = rt.estimate_illumination_mesh(env, rp, 9, s0=0, s1=32, normalise=False)
+    b = rt.estimate_illumination_mesh(env, rp, 9, s0=32, s1=64, normalise=False)
+    close(a + b, whole, "sample shards", rtol=1e-5, atol=5e-5)
+    c = rt.estimate_illumination_mesh(env, rp, 9, tri_begin=100, tri_end=333, normalise=False)
+    assert_bit_equal(c, whole[100:333], "triangle shard")
+    rt.set_option("batch_paths", 4096)
+    d = rt.estimate_illumination_mesh(env, rp, 9, normalise=False)
+    assert_bit_equal(d, whole, "batch size independence")
+    rt.set_option("sort_rays", 0)
+    e = rt.estimate_illumination_mesh(env, rp, 9, normalise=False)
+    assert_bit_equal(e, whole, "ray sorting does not change results")
+
+
+def test_illumination_materials_alpha_emission_skydome(rt, orc, S, scenes):
+    sd = scenes.random_soup(400, seed=12, size=0.35)
+    sd.materials[1] = S.Material(albedo=(0.8, 0.7, 0.6), metallic=0.4, roughness=0.6, emission=0.2, transmission=0.5)
+    rt.load_scene(sd, 63)
+    osc = orc.OracleScene(sd, 63)
+    rp = S.RayProperties(bounces=3, samples=16)
+    for env in (S.EnvironmentProperties(gamma=2.2, color=(0.9, 0.8, 1.0)),
+                S.EnvironmentProperties(lighting_type=S.ENV_SINGLE_LIGHT_SOURCE, light_size=0.1, sun_direction=(0.3, 0.9, 0.1))):
+        gpu = rt.estimate_illumination_mesh(env, rp, 5)
+        cpu, st = osc.illum_mesh(env, rp, 5, 1e-3)
+        close(gpu[:, :3], cpu[:, :3], f"energy env {env.lighting_type}", rtol=2e-5)
+        assert rt.last_job_stats()[0] == st.rays
+    sky = S.EnvironmentProperties(lighting_type=S.ENV_SKYDOME)  # expf/powf: CUDA vs glibc differ by ulps
+    gpu = rt.estimate_illumination_mesh(sky, rp, 5)
+    cpu, _ = osc.illum_mesh(sky, rp, 5, 1e-3)
+    close(gpu[:, :3], cpu[:, :3], "energy skydome", rtol=1e-4)
+
+
+def test_lidar_grid_and_aos(rt, orc, S, scenes):
+    sd = scenes.sorghum_scene(4)
+    rt.load_scene(sd, 63)
+    osc = orc.OracleScene(sd, 63)
+    grid = scenes.lidar_grid(center=(0.0, 30.0, 0.0), size=(6.0, 5.0), distance=(0.02, 0.02))
+    n = rt.scan_grid_ray_count(grid)
+    assert n == orc.scan_grid_count(grid) == 300 * 250
+    t, prim, inst = rt.scan_grid(grid)
+    ot, oprim, oinst, _ = osc.scan_grid(grid)
+    assert_bit_equal(t, ot, "t")
+    assert np.array_equal(prim, oprim) and np.array_equal(inst, oinst)
+    assert (prim != 0xFFFFFFFF).mean() > 0.5
+    # a ray range (multi-GPU sharding by ray range) is the same slice
+    t2, prim2, _ = rt.scan_grid(grid, 12345, 23456)
+    assert_bit_equal(t2, t[12345:23456], "range t") and np.array_equal(prim2, prim[12345:23456])
+    # CudaModule::SamplePointCloud signature: 112 B AoS in-out
+    rays = orc.scan_grid_rays(grid, 0, n)[::7]
+    smp = np.zeros(len(rays) + 2, dtype=S.PC_SAMPLE_DTYPE)
+    smp["start"][:-2], smp["direction"][:-2] = rays[:, 0:3], rays[:, 4:7]
+    smp["start"][-2:], smp["direction"][-2:] = (0, 50, 0), (0, 1, 0)
+    ref = smp.copy()
+    p = rt.sample_point_cloud(S.EnvironmentProperties(), smp, want_prim_ids=True)
+    op = osc.scan_point_cloud(ref)
+    assert np.array_equal(p, op)
+    assert np.array_equal(smp["hit"], ref["hit"]) and np.array_equal(smp["handle"], ref["handle"])
+    for f in ("position", "normal", "tangent", "color", "tex_coord", "data"):
+        assert_bit_equal(smp["hit_info"][f], ref["hit_info"][f], f"hit_info.{f}")
+    assert smp["hit"][-1] == 0 and smp["handle"][-1] == 0
+
+
+def test_camera_render_parity_and_accumulation(rt, orc, S, scenes):
+    sd = scenes.sorghum_scene(1)
+    rt.load_scene(sd, 63)
+    osc = orc.OracleScene(sd, 63)
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=4, samples=4)
+    cam = rt.create_camera()
+    cam.resize(96, 54)
+    cam.props.accumulate, cam.props.gamma, cam.props.fov = 1, 2.2, 120.0
+    cam.set((0.0, 1.5, 4.0), (0.9950042, -0.0998334, 0.0, 0.0))  # slight downward pitch
+    assert rt.render_to_camera(env, cam, rp) and cam.props.frame_id == 1
+    cp = S.CameraProps.from_buffer_copy(cam.props)
+    cp.frame_id = 0
+    col, nrm, alb, st = osc.camera(env, rp, cp)
+    g = cam.download(S.OUT_COLOR).reshape(-1, 4)
+    close(g, col, "colour frame 0")
+    close(cam.download(S.OUT_NORMAL).reshape(-1, 4), nrm, "normal", atol=1e-6)
+    close(cam.download(S.OUT_ALBEDO).reshape(-1, 4), alb, "albedo")
+    assert rt.last_job_stats() == (st.rays, st.paths)
+    assert g[:, :3].std() > 0.05  # an actual image: plant, ground and sky
+    # progressive accumulation in gamma space (CameraRendering.cu:113-128): frame ids 1 and 2
+    for fid in (1, 2):
+        prev = cam.download(S.OUT_COLOR).reshape(-1, 4)
+        assert rt.render_to_camera(env, cam, rp) and cam.props.frame_id == fid + 1
+        cp.frame_id = fid
+        cp.accumulate = 1
+        col, _, _, _ = osc.camera(env, rp, cp, prev_color=prev)
+        close(cam.download(S.OUT_COLOR).reshape(-1, 4), col, f"colour frame {fid}", rtol=2e-5)
+    # a changed setting resets the accumulation (RayTracer.cu:253-269)
+    rp2 = S.RayProperties(bounces=2, samples=4)
+    assert rt.render_to_camera(env, cam, rp2) and cam.props.frame_id == 1
+    # depth output goes to the albedo buffer (CameraRendering.cu:135-140)
+    cam.props.output_type = S.OUT_DEPTH
+    cam.props.modified = 1
+    assert rt.render_to_camera(env, cam, rp2)
+    cp = S.CameraProps.from_buffer_copy(cam.props)
+    cp.frame_id = 0
+    _, _, alb, _ = osc.camera(env, rp2, cp)
+    close(cam.download(S.OUT_ALBEDO).reshape(-1, 4), alb, "depth", rtol=2e-5)
+    cam.destroy()
+
+
+def test_cuda_module_facade(mod, orc, S, scenes):
+    """The static façade with the reference's names (CUDAModule.hpp:30-45)."""
+    mod.CudaModule.Init()
+    rt = mod.CudaModule.GetRayTracer()
+    sd = scenes.random_soup(200, seed=3, size=0.4)
+    rt.load_scene(sd)
+    osc = orc.OracleScene(sd)
+    probes = mod.probes_from_scene(sd)
+    ref = probes.copy()
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=1, samples=8)
+    mod.CudaModule.EstimateIlluminationRayTracing(env, rp, probes, 1, 0.001)
+    osc.illum_probes(env, rp, ref, 1, 0.001)
+    close(probes["energy"], ref["energy"], "energy")
+    mod.CudaModule.Terminate()
+    with pytest.raises(mod.RtfError):
+        mod.CudaModule.GetRayTracer()

@@ -1,0 +1,129 @@
+"""Pins the oracle's acceleration structure (CPU only).  The reference's BVH lives inside closed-source OptiX
+(RayTracer.cu:1528-1584, 1654-1707; optixTrace call sites IlluminationEstimation.cu:66 ...), so the pin is a
+brute-force all-triangles intersector (same watertight test, no BVH): every BVH hit must equal it bit for bit."""
+import numpy as np
+import pytest
+
+from .conftest import assert_bit_equal
+
+
+def _check_tree(osc, S):
+    n = osc.n_tris
+    morton, order = osc.debug(S.DBG_MORTON), osc.debug(S.DBG_SORTED_IDS)
+    keys = morton[order]
+    assert sorted(order.tolist()) == list(range(n))
+    assert np.all(keys[1:] >= keys[:-1])
+    same = keys[1:] == keys[:-1]
+    assert np.all(order[1:][same] > order[:-1][same])  # stable: ties keep primitive order
+    ch = osc.debug(S.DBG_BIN_CHILDREN).reshape(-1, 2)
+    par = osc.debug(S.DBG_BIN_PARENT)
+    boxes = osc.debug(S.DBG_BIN_BOXES).reshape(-1, 6)
+    ni = n - 1
+    if n > 1:
+        assert par[0] == -1
+        seen = np.zeros(2 * n - 1, dtype=np.int32)
+        for i in range(ni):
+            for c in ch[i]:
+                idx = c if c >= 0 else ni + (~c)
+                assert par[idx] == i
+                seen[idx] += 1
+                assert np.all(boxes[idx, :3] >= boxes[i, :3]) and np.all(boxes[idx, 3:] <= boxes[i, 3:])
+        assert seen[0] == 0 and np.all(seen[1:] == 1)
+    nodes, tris = osc.debug(S.DBG_WIDE_NODES), osc.debug(S.DBG_WIDE_TRIS)
+    assert sorted(tris["prim"].tolist()) == list(range(n))  # every triangle exactly once
+    pos = osc.debug(S.DBG_FLAT_POS).reshape(-1, 3, 3)
+    assert_bit_equal(tris["v0"], pos[tris["prim"], 0], "tri v0")
+    # quantised child boxes contain the triangles they lead to (leaf slots checked directly)
+    for nd in nodes:
+        scale = (nd["e"].astype(np.uint32) << 23).view(np.float32)
+        for s in range(8):
+            meta = int(nd["meta"][s])
+            if meta == 0 or (meta >> 5) == 1 and (meta & 0x1f) >= 24:
+                continue
+            cnt = bin(meta >> 5).count("1")
+            t0 = int(nd["tri_base"]) + (meta & 0x1f)
+            lo = nd["p"] + nd["qlo"][:, s].astype(np.float32) * scale
+            hi = nd["p"] + nd["qhi"][:, s].astype(np.float32) * scale
+            for t in tris[t0:t0 + cnt]:
+                v = np.stack([t["v0"], t["v1"], t["v2"]])
+                assert np.all(v.min(0) >= lo) and np.all(v.max(0) <= hi)
+    # child_base / imask consistency: internal children are contiguous, BFS order
+    n_int = sum(bin(int(nd["imask"])).count("1") for nd in nodes)
+    assert n_int == len(nodes) - 1
+
+
+@pytest.mark.parametrize("n,bits", [(1, 63), (2, 63), (3, 30), (4, 63), (9, 63), (257, 30), (1500, 63)])
+def test_tree_invariants(orc, S, scenes, n, bits):
+    osc = orc.OracleScene(scenes.random_soup(n, seed=n), bits)
+    assert osc.n_tris == n
+    _check_tree(osc, S)
+
+
+def test_duplicate_triangles_and_degenerates(orc, S, scenes):
+    sd = scenes.random_soup(64, seed=5, size=0.6)
+    v, t = sd.geometries[1]
+    v = np.concatenate([v, v, v[:3]])  # duplicates -> equal Morton keys (Karras index tie-break)
+    t = np.concatenate([t, t + 192, [[384, 384, 384]], [[384, 385, 385]]]).astype(np.uint32)  # + degenerate
+    sd.geometries[1] = (v, t)
+    osc = orc.OracleScene(sd, 30)
+    _check_tree(osc, S)
+    lo, hi = scenes.scene_bounds(sd)
+    rays = scenes.incoherent_rays(3000, lo - 0.1, hi + 0.1, seed=9)
+    assert_bit_equal(osc.trace(rays), osc.trace_brute(rays), "dup hits")
+    # equal-t ties resolve to the lower primitive id
+    h = osc.trace(rays)
+    hit = h["prim"] != 0xFFFFFFFF
+    assert hit.sum() > 100 and np.all(h["prim"][hit] < 64)
+
+
+@pytest.mark.parametrize("bits", [30, 63])
+def test_bvh_hits_equal_brute_force_soup(orc, scenes, bits):
+    sd = scenes.random_soup(3000, seed=21, size=0.25)
+    osc = orc.OracleScene(sd, bits)
+    lo, hi = scenes.scene_bounds(sd)
+    rays = scenes.incoherent_rays(20000, lo, hi, seed=4)
+    a, b = osc.trace(rays), osc.trace_brute(rays)
+    assert_bit_equal(a, b, "hits")
+    assert (a["prim"] != 0xFFFFFFFF).mean() > 0.3
+
+
+def test_bvh_hits_equal_brute_force_sorghum(orc, scenes):
+    sd = scenes.sorghum_scene(1)
+    osc = orc.OracleScene(sd, 63)
+    assert osc.n_tris == 20002
+    lo, hi = scenes.scene_bounds(sd)
+    rays = scenes.incoherent_rays(3000, lo, hi, seed=3)
+    a, b = osc.trace(rays), osc.trace_brute(rays)
+    assert_bit_equal(a, b, "hits")
+    # axis-aligned and zero-component directions (safe_dir path), rays starting on the ground plane
+    ax = np.zeros((6, 8), dtype=np.float32)
+    ax[:, 0:3] = (1.9, 1.0, 1.9)
+    ax[:, 7] = 1e20
+    for k in range(6):
+        ax[k, 4 + k % 3] = 1.0 if k < 3 else -1.0
+    assert_bit_equal(osc.trace(ax), osc.trace_brute(ax), "axis rays")
+    h = osc.trace(ax)
+    assert h["prim"][4] in (0, 1) and h["t"][4] == 1.0  # straight down onto the ground (primitives 0,1)
+
+
+def test_tmin_tmax_window(orc, scenes):
+    sd = scenes.sorghum_scene(1)
+    osc = orc.OracleScene(sd, 63)
+    r = np.array([[0.5, 2.0, 0.5, 0.0, 0, -1, 0, 1e20], [0.5, 2.0, 0.5, 0.0, 0, -1, 0, 1.5],
+                  [0.5, 2.0, 0.5, 2.5, 0, -1, 0, 1e20], [0.5, 2.0, 0.5, 2.0, 0, -1, 0, 2.0]], dtype=np.float32)
+    h = osc.trace(r)
+    assert h["t"][0] == 2.0 and h["prim"][0] in (0, 1)
+    assert h["prim"][1] == 0xFFFFFFFF and h["prim"][2] == 0xFFFFFFFF
+    assert h["prim"][3] in (0, 1)  # t == tmin == tmax is accepted
+    assert_bit_equal(h, osc.trace_brute(r), "window")
+
+
+def test_visit_counts_are_deterministic(orc, scenes):
+    sd = scenes.random_soup(2000, seed=7)
+    osc = orc.OracleScene(sd, 63)
+    lo, hi = scenes.scene_bounds(sd)
+    rays = scenes.incoherent_rays(2000, lo, hi, seed=3)
+    _, nv1, tv1 = osc.trace(rays, counts=True, nthreads=1)
+    _, nv2, tv2 = osc.trace(rays, counts=True, nthreads=4)
+    assert np.array_equal(nv1, nv2) and np.array_equal(tv1, tv2)
+    assert nv1.min() >= 1 and tv1.mean() < 40

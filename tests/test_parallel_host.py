@@ -1,0 +1,94 @@
+"""Host-side sharding logic of raytracerfacility_b200.parallel on CPU: world_size-2 gloo processes, with the
+oracle injected as the compute function (tests may use the oracle; the product never does)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from .conftest import ROOT
+
+
+def test_split_range_partitions():
+    from raytracerfacility_b200.parallel import split_range
+    for n in (0, 1, 7, 64, 256, 20002, 10 ** 8):
+        for w in (1, 2, 4, 8):
+            parts = [split_range(n, w, r) for r in range(w)]
+            assert parts[0][0] == 0 and parts[-1][1] == n
+            assert all(parts[i][1] == parts[i + 1][0] for i in range(w - 1))
+            sizes = [e - b for b, e in parts]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    from oracle import pyoracle as orc
+    from raytracerfacility_b200 import parallel, scenes, structs as S
+    r, w, _ = parallel.init_distributed("gloo")
+    assert (r, w) == (rank, world)
+    sd = scenes.random_soup(60, seed=2, size=0.4)
+    osc = orc.OracleScene(sd)
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=2, samples=33)  # odd: ragged sample shards
+    n = osc.n_tris
+
+    def compute_partial(s0, s1, acc):
+        part, _ = osc.illum_mesh(env, rp, 9, 1e-3, s0=s0, s1=s1, normalise=False, nthreads=1)
+        acc += torch.from_numpy(part.reshape(-1))
+
+    def finalize(acc, faces, samples):
+        a = acc.numpy().reshape(-1, 6)
+        cnt = np.float32(faces * samples)
+        a[:, :3] = a[:, :3] / cnt
+        d = a[:, 3:]
+        inv = np.float32(1.0) / np.sqrt((d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2])
+        a[:, 3:] = d * inv[:, None]
+
+    acc = torch.zeros(n * 6, dtype=torch.float32)
+    parallel.illumination_sample_sharded(n, rp.samples, 2, compute_partial, finalize,
+                                         lambda a: dist.all_reduce(a, op=dist.ReduceOp.SUM), world, rank, acc)
+
+    def compute_range(t0, t1):
+        part, _ = osc.illum_mesh(env, rp, 9, 1e-3, tri_begin=t0, tri_end=t1, nthreads=1)
+        return torch.from_numpy(part)
+
+    def all_gather(sizes, local):
+        outs = [torch.empty(s, 6) for s in sizes]
+        for src in range(world):
+            if src == rank:
+                outs[src].copy_(local)
+            dist.broadcast(outs[src], src=src)
+        return torch.cat(outs)
+
+    tri = parallel.illumination_triangle_sharded(n, compute_range, all_gather, world, rank)
+    np.save(os.path.join(out_dir, f"sample_{rank}.npy"), acc.numpy().reshape(-1, 6))
+    np.save(os.path.join(out_dir, f"tri_{rank}.npy"), tri.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_world2_gloo_sharded_illumination(tmp_path, orc, S, scenes):
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    sd = scenes.random_soup(60, seed=2, size=0.4)
+    osc = orc.OracleScene(sd)
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=2, samples=33)
+    single, _ = osc.illum_mesh(env, rp, 9, 1e-3)
+    s0, s1 = np.load(tmp_path / "sample_0.npy"), np.load(tmp_path / "sample_1.npy")
+    assert np.array_equal(s0.view(np.uint32), s1.view(np.uint32))  # all ranks hold the same result
+    assert np.allclose(s0[:, :3], single[:, :3], rtol=1e-5) and np.allclose(s0[:, 3:], single[:, 3:], rtol=1e-5, atol=1e-5)
+    t0, t1 = np.load(tmp_path / "tri_0.npy"), np.load(tmp_path / "tri_1.npy")
+    assert np.array_equal(t0.view(np.uint32), single.view(np.uint32))  # triangle sharding: bit-identical to 1 rank
+    assert np.array_equal(t1.view(np.uint32), single.view(np.uint32))
