@@ -151,7 +151,11 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: librtf_b200 has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    stream = torch.cuda.current_stream()
+    # A dedicated non-default stream shared by torch and the library: rtf_set_stream(NULL) would mean "own stream",
+    # and torch's default stream handle IS NULL — events recorded there would never see the kernels.
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     rt = module.RayTracer(local)
     rt.set_stream(stream.cuda_stream)
 

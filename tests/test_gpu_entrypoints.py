@@ -123,9 +123,9 @@ def test_lidar_grid_and_aos(rt, orc, S, scenes):
     sd = scenes.sorghum_scene(4)
     rt.load_scene(sd, 63)
     osc = orc.OracleScene(sd, 63)
-    grid = scenes.lidar_grid(center=(0.0, 30.0, 0.0), size=(6.0, 5.0), distance=(0.02, 0.02))
+    grid = scenes.lidar_grid(center=(0.0, 30.0, 0.0), size=(2.6, 2.8), distance=(0.02, 0.02))
     n = rt.scan_grid_ray_count(grid)
-    assert n == orc.scan_grid_count(grid) == 300 * 250
+    assert n == orc.scan_grid_count(grid) == 130 * 140
     t, prim, inst = rt.scan_grid(grid)
     ot, oprim, oinst, _ = osc.scan_grid(grid)
     assert_bit_equal(t, ot, "t")
