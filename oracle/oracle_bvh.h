@@ -429,7 +429,8 @@ static inline Hit trace(const BVH& bvh, const Ray& ray, TraceStats* stats = null
   const bool neg[3] = {std::signbit(dx), std::signbit(dy), std::signbit(dz)};
   const float org[3] = {ray.o.x, ray.o.y, ray.o.z};
   const uint32_t oct_inv = (neg[0] ? 0u : 4u) | (neg[1] ? 0u : 2u) | (neg[2] ? 0u : 1u);
-  const float SLACK = 1.00000095367431640625f;  // 1 + 2^-20
+  const float SLACK = 1.00000095367431640625f;    // 1 + 2^-20
+  const float FAR_SLACK = 2.384185791015625e-07f;  // 2^-22
   struct Group {
     uint32_t base, bits;
   };
@@ -448,11 +449,14 @@ static inline Hit trace(const BVH& bvh, const Ray& ray, TraceStats* stats = null
       const uint32_t rel = (uint32_t)__builtin_popcount(hits & ~(0xffffffffu << slot));
       const Node80& nd = bvh.nodes[cur.base + rel];
       if (stats) stats->nodes++;
-      float sc[3], oo[3];
+      float sc[3], oo[3], oof[3];
       for (int a = 0; a < 3; a++) {
         sc[a] = u2f((uint32_t)nd.e[a] << 23) * idir[a];
         oo[a] = (nd.p[a] - org[a]) * idir[a];
+        // far-plane slack relative to the operands that cancel in q*s + o (see rtf_trace.cuh)
+        oof[a] = fmaf(fmaf(fabsf(sc[a]), 256.0f, fabsf(oo[a])), FAR_SLACK, oo[a]);
       }
+      const float best_s = best.t * SLACK;
       uint32_t hitmask = 0;
       for (int s = 0; s < 8; s++) {
         const uint32_t meta = nd.meta[s];
@@ -462,11 +466,11 @@ static inline Hit trace(const BVH& bvh, const Ray& ray, TraceStats* stats = null
           const float qn = (float)(neg[a] ? nd.qhi[a][s] : nd.qlo[a][s]);
           const float qf = (float)(neg[a] ? nd.qlo[a][s] : nd.qhi[a][s]);
           tn[a] = fmaf(qn, sc[a], oo[a]);
-          tf[a] = fmaf(qf, sc[a], oo[a]);
+          tf[a] = fmaf(qf, sc[a], oof[a]);
         }
         const float tnear = fmaxf(fmaxf(tn[0], tn[1]), fmaxf(tn[2], ray.tmin));
-        const float tfar = fminf(fminf(tf[0], tf[1]), fminf(tf[2], best.t));
-        if (tnear <= tfar * SLACK) {
+        const float tfar = fminf(fminf(tf[0], tf[1]), fminf(tf[2], best_s));
+        if (tnear <= tfar) {
           const bool inner = (meta & (meta << 1) & 0x10u) != 0;
           const uint32_t bit_index = (meta ^ (inner ? oct_inv : 0u)) & 0x1fu;
           const uint32_t child_bits = (meta >> 5) & 7u;

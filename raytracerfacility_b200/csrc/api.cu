@@ -73,7 +73,7 @@ int rtf_destroy(rtf_ctx* ctx) {
                     &ctx->ba.scene_bounds, &ctx->ba.keys_alt, &ctx->ba.ids_alt, &ctx->ba.cub_tmp, &ctx->ba.level_a,
                     &ctx->ba.level_b, &ctx->ba.cnt_int, &ctx->ba.cnt_tri, &ctx->ba.scan_int, &ctx->ba.scan_tri,
                     &ctx->ba.stash, &ctx->ws.ray_a[0], &ctx->ws.ray_a[1], &ctx->ws.ray_b[0], &ctx->ws.ray_b[1],
-                    &ctx->ws.path_idx[0], &ctx->ws.path_idx[1], &ctx->ws.hits, &ctx->ws.counters, &ctx->ws.thr,
+                    &ctx->ws.hits, &ctx->ws.counters, &ctx->ws.thr,
                     &ctx->ws.acc, &ctx->ws.dir0w, &ctx->ws.first_n, &ctx->ws.first_a, &ctx->ws.first_p,
                     &ctx->ws.sort_keys, &ctx->ws.sort_keys_alt, &ctx->ws.sort_vals, &ctx->ws.sort_vals_alt,
                     &ctx->ws.sort_tmp, &ctx->ws.io};
@@ -416,7 +416,7 @@ int rtf_scan_grid_trace(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t b, uin
 int rtf_trace_closest_device(rtf_ctx* ctx, const float* dev_rays, size_t n, void* dev_hits) {
   CHECK_CTX(ctx);
   if ((!dev_rays || !dev_hits) && n) return RTF_ERR_INVALID;
-  return trace_rays_device(ctx, (const float4*)dev_rays, (const float4*)dev_rays + 1, 2, n, (float4*)dev_hits, nullptr, nullptr);
+  return trace_rays_device(ctx, (const float4*)dev_rays, n, (float4*)dev_hits, nullptr, nullptr);
 }
 int rtf_trace_closest_counts(rtf_ctx* ctx, const float* rays, size_t n, void* hits, uint32_t* node_visits, uint32_t* tri_visits) {
   CHECK_CTX(ctx);
@@ -432,7 +432,7 @@ int rtf_trace_closest_counts(rtf_ctx* ctx, const float* rays, size_t n, void* hi
   uint32_t* dtv = dn + n;
   const bool counts = node_visits || tri_visits;
   RTF_CUDA(cudaMemcpyAsync(dr, rays, rb, cudaMemcpyHostToDevice, ctx->stream));
-  if ((rc = trace_rays_device(ctx, dr, dr + 1, 2, n, dh, counts ? dn : nullptr, counts ? dtv : nullptr))) return rc;
+  if ((rc = trace_rays_device(ctx, dr, n, dh, counts ? dn : nullptr, counts ? dtv : nullptr))) return rc;
   RTF_CUDA(cudaMemcpyAsync(hits, dh, hb, cudaMemcpyDeviceToHost, ctx->stream));
   if (node_visits) RTF_CUDA(cudaMemcpyAsync(node_visits, dn, cb, cudaMemcpyDeviceToHost, ctx->stream));
   if (tri_visits) RTF_CUDA(cudaMemcpyAsync(tri_visits, dtv, cb, cudaMemcpyDeviceToHost, ctx->stream));

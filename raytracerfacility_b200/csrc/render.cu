@@ -27,46 +27,57 @@ static_assert(kSmemStack + kLocalStack == kMaxStackDepth, "stack split must cove
 
 static inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
 
-constexpr int kTraceBlock = 128;
 constexpr uint32_t kShadowBit = 0x80000000u;
 
 // ============================ raw closest-hit (M1 metric) =========================================
-// Persistent warps pull 32-ray chunks from a global counter; rays are two float4 streams
-// (origin|tmin, direction|tmax) with a stride so the interleaved n x 8 host layout can be used as is.
-template <bool STATS>
-__global__ void __launch_bounds__(kTraceBlock)
-    k_trace_rays(DevScene sc, const float4* __restrict__ ra, const float4* __restrict__ rb, int stride, uint32_t n,
-                 float4* __restrict__ hits, uint32_t* __restrict__ nv, uint32_t* __restrict__ tv, uint32_t* work) {
-  __shared__ uint2 sstack[kSmemStack * kTraceBlock];
-  const int lane = threadIdx.x & 31;
-  AlphaCtx actx{nullptr, 0u, 0ull, 0u};
-  for (;;) {
-    uint32_t base = 0;
-    if (lane == 0) base = atomicAdd(work, 32u);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= n) break;
-    const uint32_t i = base + lane;
-    if (i < n) {
-      const float4 a = __ldg(ra + (size_t)i * stride), b = __ldg(rb + (size_t)i * stride);
-      uint32_t nvis = 0, tvis = 0;
-      const HitRec h = traverse<kSmemStack, STATS>(sc.nodes, sc.tris, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), a.w, b.w,
-                                                   sstack + threadIdx.x, kTraceBlock, 0u, actx, nvis, tvis);
-      hits[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
-      if (STATS) {
-        if (nv) nv[i] = nvis;
-        if (tv) tv[i] = tvis;
-      }
-    }
+// Persistent lanes (rtf_trace.cuh): rays are the interleaved n x 8 float layout {o.xyz, tmin, d.xyz, tmax};
+// a 32-ray tile is one contiguous 1 KB TMA bulk copy.
+struct SrcRays {
+  static constexpr bool kTma = true, kAnyHit = false, kAlpha = false;
+  const float4* rays;
+  float4* hits;
+  uint32_t* nv;
+  uint32_t* tv;
+  uint32_t n;
+  RTF_D void issue(uint32_t base, uint32_t cnt, uint32_t raw_s, uint32_t mbar_s) const {
+    mbar_expect_tx(mbar_s, cnt * 32u);
+    tma_load_1d(raw_s, rays + 2 * (size_t)base, cnt * 32u, mbar_s);
   }
+  RTF_D void fetch(const unsigned char* raw, uint32_t, uint32_t slot, float4& a, float4& b, float& tmin, uint32_t& tag) const {
+    const float4* r = (const float4*)raw;
+    a = r[2 * slot], b = r[2 * slot + 1];
+    tmin = a.w, tag = 0u;
+  }
+  RTF_D bool any_hit(uint32_t) const { return false; }
+  RTF_D bool alpha_pass(uint32_t, uint32_t, uint32_t) const { return true; }
+  RTF_D void store(uint32_t i, uint32_t, const HitRec& h, uint32_t nvis, uint32_t tvis) const {
+    hits[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
+    if (nv) nv[i] = nvis;
+    if (tv) tv[i] = tvis;
+  }
+};
+template <bool STATS>
+__global__ void __launch_bounds__(kTraceBlock) k_trace_rays(DevScene sc, SrcRays src, uint32_t* work) {
+  __shared__ TraceSmem sm;
+  trace_engine<STATS>(sc.nodes, sc.tris, src, work, sm);
 }
 
-int trace_rays_device(rtf_ctx* ctx, const float4* ra, const float4* rb, int stride, size_t n, float4* hits,
-                      uint32_t* nv, uint32_t* tv) {
+static unsigned trace_grid(const rtf_ctx* ctx, size_t n) {
+  const unsigned full = (unsigned)ctx->sm_count * (unsigned)ctx->trace_blocks_per_sm;
+  const unsigned need = div_up(n, kTraceBlock);
+  return need < full ? need : full;
+}
+
+int trace_rays_device(rtf_ctx* ctx, const float4* rays, size_t n, float4* hits, uint32_t* nv, uint32_t* tv) {
   if (!ctx->ready) {
     set_error("no acceleration structure (call rtf_commit)");
     return RTF_ERR_NOT_READY;
   }
   if (n == 0) return RTF_OK;
+  if (((uintptr_t)rays & 15u) || ((uintptr_t)hits & 15u)) {
+    set_error("ray and hit buffers must be 16-byte aligned");
+    return RTF_ERR_INVALID;
+  }
   int rc;
   if ((rc = ctx->ws.counters.reserve(4096))) return rc;
   uint32_t* work = ctx->ws.counters.as<uint32_t>();
@@ -74,13 +85,11 @@ int trace_rays_device(rtf_ctx* ctx, const float4* ra, const float4* rb, int stri
   for (size_t off = 0; off < n; off += chunk) {
     const uint32_t m = (uint32_t)((n - off) < chunk ? (n - off) : chunk);
     RTF_CUDA(cudaMemsetAsync(work, 0, 4, ctx->stream));
-    const unsigned grid = min(div_up(m, kTraceBlock), (unsigned)ctx->sm_count * 8u);
+    SrcRays src{rays + 2 * off, hits + off, nv ? nv + off : nullptr, tv ? tv + off : nullptr, m};
     if (nv || tv)
-      LAUNCH(ctx, k_trace_rays<true>, grid, kTraceBlock, 0, ctx->scene, ra + off * stride, rb + off * stride, stride, m,
-             hits + off, nv ? nv + off : nullptr, tv ? tv + off : nullptr, work);
+      LAUNCH(ctx, k_trace_rays<true>, trace_grid(ctx, m), kTraceBlock, 0, ctx->scene, src, work);
     else
-      LAUNCH(ctx, k_trace_rays<false>, grid, kTraceBlock, 0, ctx->scene, ra + off * stride, rb + off * stride, stride, m,
-             hits + off, nullptr, nullptr, work);
+      LAUNCH(ctx, k_trace_rays<false>, trace_grid(ctx, m), kTraceBlock, 0, ctx->scene, src, work);
   }
   RTF_CUDA(cudaGetLastError());
   return RTF_OK;
@@ -105,9 +114,8 @@ __device__ __forceinline__ uint64_t unit_of(const PathMap& pm, uint32_t p) {
 }
 
 struct Queues {
-  float4* ray_a[2];
-  float4* ray_b[2];
-  uint32_t* path_idx[2];
+  float4* ray_a[2];  // {origin.xyz, path index | kShadowBit (bits)}
+  float4* ray_b[2];  // {direction.xyz, tmax}
   float4* hits;
   uint32_t* count;  // count[k] = rays in wavefront k
   uint32_t* work;   // work[k]  = dynamic-fetch cursor of wavefront k
@@ -135,38 +143,49 @@ __device__ __forceinline__ uint32_t warp_append(bool emit, uint32_t* counter) {
 }
 
 // ---- trace one wavefront -----------------------------------------------------------------------------
+// Queue rays are SoA: a 32-ray tile is two 512 B TMA bulk copies (origins|path, directions|tmax).  tmin is
+// uniform per wavefront (camera primary rays 0, everything else 1e-3: CameraRendering.cu:89, IlluminationEstimation.cu:69,
+// RayFunctions.cuh:77,140), so the .w of the origin stream carries the path index instead.
+struct SrcQueue {
+  static constexpr bool kTma = true, kAnyHit = true, kAlpha = true;
+  const float4* ra;
+  const float4* rb;
+  float4* hits;
+  uint32_t n;
+  float tmin;
+  const float* inst_alpha;  // nullptr: no material can ignore hits
+  PathMap pm;
+  uint32_t seed, bounce;
+  RTF_D void issue(uint32_t base, uint32_t cnt, uint32_t raw_s, uint32_t mbar_s) const {
+    mbar_expect_tx(mbar_s, cnt * 32u);
+    tma_load_1d(raw_s, ra + base, cnt * 16u, mbar_s);
+    tma_load_1d(raw_s + 512u, rb + base, cnt * 16u, mbar_s);
+  }
+  RTF_D void fetch(const unsigned char* raw, uint32_t, uint32_t slot, float4& a, float4& b, float& tmin_, uint32_t& tag) const {
+    const float4* r = (const float4*)raw;
+    a = r[slot], b = r[32 + slot];
+    tmin_ = tmin, tag = __float_as_uint(a.w);
+  }
+  RTF_D bool any_hit(uint32_t tag) const { return (tag & kShadowBit) != 0u; }  // TERMINATE_ON_FIRST_HIT, RayFunctions.cuh:81-83
+  // AnyHitFunc, RayFunctions.cuh:5-23: ignore the candidate if alpha <= rnd; the draw is keyed by (path, bounce, primitive)
+  // so it does not depend on traversal order.  Shadow rays run with DISABLE_ANYHIT.
+  RTF_D bool alpha_pass(uint32_t tag, uint32_t prim, uint32_t inst) const {
+    if (inst_alpha == nullptr || (tag & kShadowBit)) return true;
+    const float alpha = inst_alpha[inst];
+    const float rnd = path_rng(seed, STREAM_ALPHA, unit_of(pm, tag), bounce, prim).x;
+    return !(alpha <= rnd);
+  }
+  RTF_D void store(uint32_t i, uint32_t, const HitRec& h, uint32_t, uint32_t) const {
+    hits[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
+  }
+};
 __global__ void __launch_bounds__(kTraceBlock)
-    k_trace_queue(DevScene sc, Queues q, int qi, int wave, PathMap pm, uint32_t seed, unsigned long long* stats) {
-  __shared__ uint2 sstack[kSmemStack * kTraceBlock];
-  const int lane = threadIdx.x & 31;
+    k_trace_queue(DevScene sc, Queues q, int qi, int wave, float tmin, PathMap pm, uint32_t seed, unsigned long long* stats) {
+  __shared__ TraceSmem sm;
   const uint32_t n = q.count[wave];
   if (blockIdx.x == 0 && threadIdx.x == 0 && stats) atomicAdd(stats, (unsigned long long)n);
-  const float4* __restrict__ ra = q.ray_a[qi];
-  const float4* __restrict__ rb = q.ray_b[qi];
-  const uint32_t* __restrict__ pidx = q.path_idx[qi];
-  for (;;) {
-    uint32_t base = 0;
-    if (lane == 0) base = atomicAdd(q.work + wave, 32u);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= n) break;
-    const uint32_t i = base + lane;
-    if (i < n) {
-      const float4 a = __ldg(ra + i), b = __ldg(rb + i);
-      const uint32_t pi = __ldg(pidx + i);
-      uint32_t flags = 0;
-      AlphaCtx actx{sc.inst_alpha, seed, 0ull, (uint32_t)wave};
-      if (pi & kShadowBit) {
-        flags = TRACE_ANY_HIT;  // DISABLE_ANYHIT | TERMINATE_ON_FIRST_HIT, RayFunctions.cuh:81-83
-      } else if (sc.has_alpha) {
-        flags = TRACE_ALPHA;
-        actx.unit = unit_of(pm, pi);
-      }
-      uint32_t nvis = 0, tvis = 0;
-      const HitRec h = traverse<kSmemStack, false>(sc.nodes, sc.tris, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), a.w, b.w,
-                                                   sstack + threadIdx.x, kTraceBlock, flags, actx, nvis, tvis);
-      q.hits[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
-    }
-  }
+  SrcQueue src{q.ray_a[qi], q.ray_b[qi], q.hits, n, tmin, sc.has_alpha ? sc.inst_alpha : nullptr, pm, seed, (uint32_t)wave};
+  trace_engine<false>(sc.nodes, sc.tris, src, q.work + wave, sm);
 }
 
 // ---- shade one wavefront: ClosestHitFunc (RayFunctions.cuh:25-172) / MissFunc (:260-272), unrolled ------
@@ -182,10 +201,9 @@ __global__ void __launch_bounds__(256)
   if (blockIdx.x * blockDim.x >= n) return;  // whole block idle (uniform exit keeps warp_append safe)
   bool emit = false;
   float4 na = make_float4(0, 0, 0, 0), nb = make_float4(0, 0, 0, 0);
-  uint32_t npi = 0;
   if (i < n) {
     const float4 a = q.ray_a[qi][i], b = q.ray_b[qi][i];
-    const uint32_t pi = q.path_idx[qi][i];
+    const uint32_t pi = __float_as_uint(a.w);
     const uint32_t p = pi & ~kShadowBit;
     const float4 h = q.hits[i];
     const uint32_t prim = __float_as_uint(h.w);
@@ -232,9 +250,8 @@ __global__ void __launch_bounds__(256)
         const float ndl = dot3(sh.normal, nd);
         if (ndl > 0.0f) {
           emit = true;
-          na = make_float4(sh.position.x, sh.position.y, sh.position.z, 1e-3f);
+          na = make_float4(sh.position.x, sh.position.y, sh.position.z, __uint_as_float(p | kShadowBit));
           nb = make_float4(nd.x, nd.y, nd.z, 1e20f);
-          npi = p | kShadowBit;
           ps.thr[p] = make_float4(T.x, T.y, T.z, m.emission);
           ps.aux[p] = make_float4(albedo.x, albedo.y, albedo.z, ndl);
         } else {
@@ -252,9 +269,8 @@ __global__ void __launch_bounds__(256)
         ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
         ps.thr[p] = make_float4(T.x, T.y, T.z, __uint_as_float(hit_count));
         emit = true;
-        na = make_float4(sh.position.x, sh.position.y, sh.position.z, 1e-3f);  // origin not offset, RayFunctions.cuh:138
+        na = make_float4(sh.position.x, sh.position.y, sh.position.z, __uint_as_float(p));  // origin not offset, RayFunctions.cuh:138
         nb = make_float4(nd.x, nd.y, nd.z, 1e20f);
-        npi = p;
       } else {
         acc = acc + T * emis;
         ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
@@ -265,7 +281,6 @@ __global__ void __launch_bounds__(256)
   if (emit) {
     q.ray_a[qi ^ 1][slot] = na;
     q.ray_b[qi ^ 1][slot] = nb;
-    q.path_idx[qi ^ 1][slot] = npi;
   }
 }
 
@@ -320,7 +335,7 @@ __global__ void __launch_bounds__(256) k_gen_illum(DevScene sc, IllumGen g, Queu
       const float3 dir = sample_hemisphere(r.z, r.w, normal);
       const float3 origin = position + normal * g.push;
       emit = true;
-      na = make_float4(origin.x, origin.y, origin.z, 1e-3f);
+      na = make_float4(origin.x, origin.y, origin.z, __uint_as_float(p));
       nb = make_float4(dir.x, dir.y, dir.z, 1e20f);
       d0w = make_float4(dir.x, dir.y, dir.z, fabsf(dot3(normal, dir)));
     }
@@ -332,7 +347,6 @@ __global__ void __launch_bounds__(256) k_gen_illum(DevScene sc, IllumGen g, Queu
   if (emit) {
     q.ray_a[0][slot] = na;
     q.ray_b[0][slot] = nb;
-    q.path_idx[0][slot] = p;
   }
 }
 
@@ -398,7 +412,6 @@ static int ensure_workspace(rtf_ctx* ctx, size_t cap, bool camera) {
   for (int k = 0; k < 2; k++) {
     if ((rc = w.ray_a[k].reserve(16 * cap))) return rc;
     if ((rc = w.ray_b[k].reserve(16 * cap))) return rc;
-    if ((rc = w.path_idx[k].reserve(4 * cap))) return rc;
   }
   if ((rc = w.hits.reserve(16 * cap))) return rc;
   if ((rc = w.counters.reserve(4096))) return rc;
@@ -420,7 +433,6 @@ static void bind(rtf_ctx* ctx, Queues& q, PathState& ps, bool camera) {
   Workspace& w = ctx->ws;
   for (int k = 0; k < 2; k++) {
     q.ray_a[k] = w.ray_a[k].as<float4>(), q.ray_b[k] = w.ray_b[k].as<float4>();
-    q.path_idx[k] = w.path_idx[k].as<uint32_t>();
   }
   q.hits = w.hits.as<float4>();
   q.count = w.counters.as<uint32_t>() + 16;
@@ -440,10 +452,11 @@ static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_
   }
   ShadeParams sp{bounces, seed, camera ? 1 : 0};
   unsigned long long* stats = ctx->d_stats.as<unsigned long long>();
-  const unsigned tgrid = min(div_up(paths, kTraceBlock), (unsigned)ctx->sm_count * 8u);
+  const unsigned tgrid = trace_grid(ctx, paths);
   int qi = 0;
   for (int w = 0; w < waves; w++) {
-    LAUNCH(ctx, k_trace_queue, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, pm, seed, stats);
+    const float tmin = (camera && w == 0) ? 0.0f : 1e-3f;
+    LAUNCH(ctx, k_trace_queue, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
     LAUNCH(ctx, k_shade, div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
     qi ^= 1;
   }
@@ -500,68 +513,76 @@ int illum_finalize_device(rtf_ctx* ctx, float* d_accum6, uint64_t n, int faces, 
 // ============================ LiDAR =================================================================
 // PointCloudScanner::Scan ray grid (PointCloudScanner.cpp:70-92) generated in the kernel, traced
 // (tmin 1e-3, tmax 1e20, any-hit disabled: PointCloudScanning.cu:58-64) and written as SoA.
-__global__ void __launch_bounds__(kTraceBlock)
-    k_scan_grid(DevScene sc, rtf_scan_grid g, uint32_t column, uint32_t row, uint64_t ray_begin, uint32_t n,
-                float* __restrict__ t_out, uint32_t* __restrict__ prim_out, uint32_t* __restrict__ inst_out, uint32_t* work) {
-  __shared__ uint2 sstack[kSmemStack * kTraceBlock];
-  const int lane = threadIdx.x & 31;
-  const int column_start = -(int)(column / 2), row_start = -(int)(row / 2);
-  const float3 center = f3(g.center[0], g.center[1], g.center[2]);
-  const float3 left = f3(g.left[0], g.left[1], g.left[2]), up = f3(g.up[0], g.up[1], g.up[2]);
-  const float3 dir = normalize3(f3(g.direction[0], g.direction[1], g.direction[2]));
-  AlphaCtx actx{nullptr, 0u, 0ull, 0u};
-  for (;;) {
-    uint32_t base = 0;
-    if (lane == 0) base = atomicAdd(work, 32u);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= n) break;
-    const uint32_t k = base + lane;
-    if (k < n) {
-      const uint64_t i = ray_begin + k;
-      const int ci = (int)(i / row), ri = (int)(i % row);
-      const float3 pos = (center + (left * (float)(column_start + ci)) * g.distance[0]) + (up * (float)(row_start + ri)) * g.distance[1];
-      uint32_t nvis = 0, tvis = 0;
-      const HitRec h = traverse<kSmemStack, false>(sc.nodes, sc.tris, pos, dir, 1e-3f, 1e20f, sstack + threadIdx.x,
-                                                   kTraceBlock, 0u, actx, nvis, tvis);
-      if (t_out) t_out[k] = h.t;
-      if (prim_out) prim_out[k] = h.prim;
-      if (inst_out) inst_out[k] = h.prim == 0xFFFFFFFFu ? 0xFFFFFFFFu : __ldg(sc.tri_inst + h.prim);
-    }
+struct SrcGrid {
+  static constexpr bool kTma = false, kAnyHit = false, kAlpha = false;
+  rtf_scan_grid g;
+  uint32_t row;
+  int column_start, row_start;
+  float3 dir;
+  uint64_t ray_begin;
+  uint32_t n;
+  float* t_out;
+  uint32_t* prim_out;
+  uint32_t* inst_out;
+  const uint32_t* tri_inst;
+  RTF_D void fetch(const unsigned char*, uint32_t base, uint32_t slot, float4& a, float4& b, float& tmin, uint32_t& tag) const {
+    const uint64_t i = ray_begin + base + slot;
+    const int ci = (int)(i / row), ri = (int)(i % row);
+    const float3 center = f3(g.center[0], g.center[1], g.center[2]);
+    const float3 left = f3(g.left[0], g.left[1], g.left[2]), up = f3(g.up[0], g.up[1], g.up[2]);
+    const float3 pos = (center + (left * (float)(column_start + ci)) * g.distance[0]) + (up * (float)(row_start + ri)) * g.distance[1];
+    a = make_float4(pos.x, pos.y, pos.z, 0.0f);
+    b = make_float4(dir.x, dir.y, dir.z, 1e20f);
+    tmin = 1e-3f, tag = 0u;
   }
+  RTF_D bool any_hit(uint32_t) const { return false; }
+  RTF_D bool alpha_pass(uint32_t, uint32_t, uint32_t) const { return true; }
+  RTF_D void store(uint32_t k, uint32_t, const HitRec& h, uint32_t, uint32_t) const {
+    if (t_out) t_out[k] = h.t;
+    if (prim_out) prim_out[k] = h.prim;
+    if (inst_out) inst_out[k] = h.prim == 0xFFFFFFFFu ? 0xFFFFFFFFu : __ldg(tri_inst + h.prim);
+  }
+};
+__global__ void __launch_bounds__(kTraceBlock) k_scan_grid(DevScene sc, SrcGrid src, uint32_t* work) {
+  __shared__ TraceSmem sm;
+  trace_engine<false>(sc.nodes, sc.tris, src, work, sm);
 }
-__global__ void __launch_bounds__(kTraceBlock)
-    k_scan_samples(DevScene sc, rtf_pc_sample* samples, uint32_t n, uint32_t* __restrict__ prim_out, uint32_t* work) {
-  __shared__ uint2 sstack[kSmemStack * kTraceBlock];
-  const int lane = threadIdx.x & 31;
-  AlphaCtx actx{nullptr, 0u, 0ull, 0u};
-  for (;;) {
-    uint32_t base = 0;
-    if (lane == 0) base = atomicAdd(work, 32u);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= n) break;
-    const uint32_t k = base + lane;
-    if (k < n) {
-      rtf_pc_sample& sm = samples[k];
-      const float3 d = f3(sm.direction[0], sm.direction[1], sm.direction[2]);
-      const float3 o = f3(sm.start[0], sm.start[1], sm.start[2]);
-      uint32_t nvis = 0, tvis = 0;
-      const HitRec h = traverse<kSmemStack, false>(sc.nodes, sc.tris, o, d, 1e-3f, 1e20f, sstack + threadIdx.x, kTraceBlock,
-                                                   0u, actx, nvis, tvis);
-      if (prim_out) prim_out[k] = h.prim;
-      rtf_hit_info hi;
-      if (h.prim == 0xFFFFFFFFu) {  // __miss__PCS_R (PointCloudScanning.cu:36-40) + HitInfo() defaults
-        sm.hit = 0, sm.handle = 0;
-        for (int c = 0; c < 3; c++) hi.position[c] = hi.normal[c] = hi.tangent[c] = 0.0f;
-        for (int c = 0; c < 4; c++) hi.color[c] = 1.0f, hi.data[c] = 0.0f;
-        hi.tex_coord[0] = hi.tex_coord[1] = 0.0f;
-      } else {
-        uint64_t handle;
-        full_hit_info(sc, h.prim, h.u, h.v, d, hi, handle);
-        sm.hit = 1, sm.handle = handle;
-      }
-      sm.hit_info = hi;
-    }
+// CudaModule::SamplePointCloud's AoS samples (112 B in-out): read in the converged prepare phase, written back with
+// the full HitInfo of __closesthit__PCS_R (PointCloudScanning.cu:15-28).
+struct SrcSamples {
+  static constexpr bool kTma = false, kAnyHit = false, kAlpha = false;
+  DevScene sc;
+  rtf_pc_sample* samples;
+  uint32_t* prim_out;
+  uint32_t n;
+  RTF_D void fetch(const unsigned char*, uint32_t base, uint32_t slot, float4& a, float4& b, float& tmin, uint32_t& tag) const {
+    const rtf_pc_sample& s = samples[base + slot];
+    a = make_float4(s.start[0], s.start[1], s.start[2], 0.0f);
+    b = make_float4(s.direction[0], s.direction[1], s.direction[2], 1e20f);
+    tmin = 1e-3f, tag = 0u;
   }
+  RTF_D bool any_hit(uint32_t) const { return false; }
+  RTF_D bool alpha_pass(uint32_t, uint32_t, uint32_t) const { return true; }
+  RTF_D void store(uint32_t k, uint32_t, const HitRec& h, uint32_t, uint32_t) const {
+    rtf_pc_sample& s = samples[k];
+    if (prim_out) prim_out[k] = h.prim;
+    rtf_hit_info hi;
+    if (h.prim == 0xFFFFFFFFu) {  // __miss__PCS_R (PointCloudScanning.cu:36-40) + HitInfo() defaults
+      s.hit = 0, s.handle = 0;
+      for (int c = 0; c < 3; c++) hi.position[c] = hi.normal[c] = hi.tangent[c] = 0.0f;
+      for (int c = 0; c < 4; c++) hi.color[c] = 1.0f, hi.data[c] = 0.0f;
+      hi.tex_coord[0] = hi.tex_coord[1] = 0.0f;
+    } else {
+      uint64_t handle;
+      full_hit_info(sc, h.prim, h.u, h.v, f3(s.direction[0], s.direction[1], s.direction[2]), hi, handle);
+      s.hit = 1, s.handle = handle;
+    }
+    s.hit_info = hi;
+  }
+};
+__global__ void __launch_bounds__(kTraceBlock) k_scan_samples(DevScene sc, SrcSamples src, uint32_t* work) {
+  __shared__ TraceSmem sm;
+  trace_engine<false>(sc.nodes, sc.tris, src, work, sm);
 }
 
 int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin, uint64_t ray_end, float* d_t,
@@ -583,10 +604,11 @@ int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin
   for (uint64_t off = ray_begin; off < ray_end; off += chunk) {
     const uint32_t m = (uint32_t)((ray_end - off) < chunk ? (ray_end - off) : chunk);
     RTF_CUDA(cudaMemsetAsync(work, 0, 4, ctx->stream));
-    const unsigned g = min(div_up(m, kTraceBlock), (unsigned)ctx->sm_count * 8u);
     const uint64_t o = off - ray_begin;
-    LAUNCH(ctx, k_scan_grid, g, kTraceBlock, 0, ctx->scene, *grid, column, row, off, m, d_t ? d_t + o : nullptr,
-           d_prim ? d_prim + o : nullptr, d_inst ? d_inst + o : nullptr, work);
+    SrcGrid src{*grid, row, -(int)(column / 2), -(int)(row / 2),
+                normalize3(f3(grid->direction[0], grid->direction[1], grid->direction[2])), off, m,
+                d_t ? d_t + o : nullptr, d_prim ? d_prim + o : nullptr, d_inst ? d_inst + o : nullptr, ctx->scene.tri_inst};
+    LAUNCH(ctx, k_scan_grid, trace_grid(ctx, m), kTraceBlock, 0, ctx->scene, src, work);
   }
   RTF_CUDA(cudaGetLastError());
   return RTF_OK;
@@ -601,8 +623,8 @@ int scan_samples_device(rtf_ctx* ctx, rtf_pc_sample* d_samples, size_t n, uint32
   if ((rc = ctx->ws.counters.reserve(4096))) return rc;
   uint32_t* work = ctx->ws.counters.as<uint32_t>();
   RTF_CUDA(cudaMemsetAsync(work, 0, 4, ctx->stream));
-  const unsigned g = min(div_up(n, kTraceBlock), (unsigned)ctx->sm_count * 8u);
-  LAUNCH(ctx, k_scan_samples, g, kTraceBlock, 0, ctx->scene, d_samples, (uint32_t)n, d_prim, work);
+  SrcSamples src{ctx->scene, d_samples, d_prim, (uint32_t)n};
+  LAUNCH(ctx, k_scan_samples, trace_grid(ctx, n), kTraceBlock, 0, ctx->scene, src, work);
   RTF_CUDA(cudaGetLastError());
   return RTF_OK;
 }
@@ -641,7 +663,7 @@ __global__ void __launch_bounds__(256)
     const float3 ap = start + cam.aperture * (hor * sn + ver * cs);
     const float3 dir = normalize3(conv - ap);
     emit = true;
-    na = make_float4(ap.x, ap.y, ap.z, 0.0f);  // tmin 0, CameraRendering.cu:89
+    na = make_float4(ap.x, ap.y, ap.z, __uint_as_float(p));  // tmin 0 (CameraRendering.cu:89) is the wavefront's
     nb = make_float4(dir.x, dir.y, dir.z, 1e20f);
     ps.thr[p] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(0u));
     ps.acc[p] = make_float4(0, 0, 0, 0);
@@ -653,7 +675,6 @@ __global__ void __launch_bounds__(256)
   if (emit) {
     q.ray_a[0][slot] = na;
     q.ray_b[0][slot] = nb;
-    q.path_idx[0][slot] = p;
   }
 }
 // CameraRendering.cu:101-146: per-pixel sums in sample order, progressive accumulation in gamma space.

@@ -93,7 +93,7 @@ struct BuildArrays {
 
 struct Workspace {  // wavefront queues + path state, sized for `capacity` paths
   size_t capacity = 0;
-  DevBuf ray_a[2], ray_b[2], path_idx[2], hits, counters;
+  DevBuf ray_a[2], ray_b[2], hits, counters;
   DevBuf thr, acc, dir0w, first_n, first_a, first_p;  // per-path state (SoA float4)
   DevBuf sort_keys, sort_keys_alt, sort_vals, sort_vals_alt, sort_tmp;
   DevBuf io;  // staging for AoS entry points
@@ -107,6 +107,7 @@ struct rtf_ctx {
   bool own_stream = false;
   uint64_t launches = 0;
   int sm_count = 148;
+  int trace_blocks_per_sm = 8;  // resident trace blocks per SM (occupancy query at rtf_create)
   std::map<uint64_t, rtf::Geometry> geoms;
   std::map<uint64_t, rtf_material> mats;
   std::map<uint64_t, rtf::Instance> insts;
@@ -139,8 +140,7 @@ namespace rtf {
 // build.cu
 int build_bvh(rtf_ctx* ctx, int morton_bits);
 // render.cu
-int trace_rays_device(rtf_ctx* ctx, const float4* rays_a, const float4* rays_b, int stride, size_t n, float4* hits,
-                      uint32_t* node_visits, uint32_t* tri_visits);
+int trace_rays_device(rtf_ctx* ctx, const float4* rays, size_t n, float4* hits, uint32_t* node_visits, uint32_t* tri_visits);
 int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push, int front,
                       int back, uint64_t tri_begin, uint64_t tri_end, int s0, int s1, float* d_accum6,
                       const rtf_illum_sampler* d_probes, uint64_t probe_base);

@@ -11,7 +11,16 @@
 // * Ray/triangle: Woop/Benthin/Wald JCGT'13 watertight test, without back-face culling; the axis
 //   permutation is folded into a per-ray 3x3 shear matrix (no per-triangle selects).  The closest hit
 //   resolves equal t to the lower primitive id, so the result does not depend on the BVH at all.
-// * Traversal stack: entries [0, SMEM_STACK) live in shared memory, laid out [entry][thread] so a warp's
+// * Execution model ("persistent lanes"): a warp owns 32 traversal slots.  A lane whose ray has
+//   finished takes the next ray from the warp's pool in shared memory in the SAME loop iteration, so
+//   the node/triangle code always runs with (almost) all 32 lanes busy — incoherent rays have a
+//   heavy-tailed visit count (mean 11, max > 100 nodes) and a warp that waited for its slowest lane
+//   ran at 11 % SIMT utilisation (profiles/r1_trace_baseline.md).
+// * Ray pool: rays are claimed in tiles of 32 from a global cursor.  Lane 0 brings the NEXT tile into
+//   shared memory with a TMA bulk copy (cp.async.bulk + mbarrier complete_tx) while the current one is
+//   traversed; when the pool runs dry the whole warp — converged, 32 lanes — turns the raw tile into
+//   traversal-ready records (reciprocal direction, shear constants) and goes back to traversing.
+// * Traversal stack: entries [0, kSmemStack) live in shared memory, laid out [entry][thread] so a warp's
 //   accesses hit 32 consecutive 8-byte words; deeper entries spill to local memory.
 #pragma once
 #include "rtf_bvh.cuh"
@@ -23,173 +32,304 @@ struct HitRec {
   uint32_t prim;  // 0xFFFFFFFF = miss
 };
 
-struct AlphaCtx {          // stochastic alpha test = AnyHitFunc, RayFunctions.cuh:5-23
-  const float* inst_alpha; // per instance: 1 - transmission (Default material), else 1
-  uint32_t seed;
-  uint64_t unit;
-  uint32_t bounce;
-};
-
-constexpr int kSmemStack = 12;   // entries per thread in shared memory
-constexpr int kLocalStack = 52;  // spill entries in local memory (kSmemStack + kLocalStack = kMaxStackDepth)
-constexpr float kBoxSlack = 1.00000095367431640625f;  // 1 + 2^-20: absorbs rounding of the slab test
+constexpr int kSmemStack = 8;    // entries per thread in shared memory
+constexpr int kLocalStack = 56;  // spill entries in local memory (kSmemStack + kLocalStack = kMaxStackDepth)
+constexpr float kBoxSlack = 1.00000095367431640625f;  // 1 + 2^-20 on the current best t
+constexpr float kFarSlack = 2.384185791015625e-07f;   // 2^-22 of the slab operands, added to the far planes
+constexpr int kTraceBlock = 128;
+constexpr int kTraceWarps = kTraceBlock / 32;
+constexpr int kRawTileBytes = 1024;  // 32 rays x 32 B
 
 RTF_D float safe_dir(float d) {
   const float ooeps = __uint_as_float(0x17800000u);  // 2^-80
   return fabsf(d) < ooeps ? copysignf(ooeps, d) : d;
 }
 RTF_D uint32_t extract_byte(uint32_t w, int j) { return (w >> (8 * j)) & 0xffu; }
+// float(byte j of w), exact.  PRMT builds 0x4B0000bb = 2^23 + b, one FADD removes the bias: both run on the
+// full-rate ALU/FMA pipes, whereas I2F.U8 is a quarter-rate XU instruction (48 of them per node made XU the
+// busiest pipe of the first version, profiles/r1_trace_baseline.md).
+RTF_D float byte_to_float(uint32_t w, int j) {
+  return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7540u + (uint32_t)j)) - 8388608.0f;
+}
 
-enum { TRACE_ANY_HIT = 1u, TRACE_ALPHA = 2u };
+// ---- TMA 1-D bulk copy + mbarrier (PTX; SASS: UBLKCP / SYNCS) -------------------------------------------
+RTF_D uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+RTF_D void mbar_init(uint32_t mbar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+RTF_D void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+RTF_D void tma_load_1d(uint32_t dst_smem, const void* src_gmem, uint32_t bytes, uint32_t mbar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_smem),
+               "l"(src_gmem), "r"(bytes), "r"(mbar)
+               : "memory");
+}
+RTF_D void mbar_wait(uint32_t mbar, uint32_t parity) {
+  uint32_t ok = 0;
+  do {
+    asm volatile(
+        "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+        : "=r"(ok)
+        : "r"(mbar), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
 
-template <int SMEM_STACK, bool STATS>
-RTF_D HitRec traverse(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const float3 o, const float3 d,
-                      const float tmin, const float tmax, uint2* __restrict__ sstack, const int sstride,
-                      const uint32_t flags, const AlphaCtx& actx, uint32_t& nvis, uint32_t& tvis) {
-  HitRec best;
-  best.t = tmax, best.u = 0.0f, best.v = 0.0f, best.prim = 0xFFFFFFFFu;
+// Shared memory of one trace block (static, 21 KB): per warp a raw TMA tile, a pool of prepared rays and
+// an mbarrier; per thread kSmemStack stack entries.
+struct __align__(128) TraceSmem {
+  unsigned char raw[kTraceWarps][kRawTileBytes];
+  float4 pool[kTraceWarps][4][32];
+  uint2 stack[kSmemStack * kTraceBlock];
+  unsigned long long mbar[kTraceWarps];
+};
 
-  // ---- per-ray constants -------------------------------------------------------------------
-  const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
-  const int kz = (ax >= ay && ax >= az) ? 0 : (ay >= az ? 1 : 2);
-  // shear matrix rows (mx, my, mz): kx = kz+1, ky = kz+2 (mod 3)
-  float3 mx, my, mz;
-  {
-    const float dz = kz == 0 ? d.x : (kz == 1 ? d.y : d.z);
-    const float dx = kz == 0 ? d.y : (kz == 1 ? d.z : d.x);
-    const float dy = kz == 0 ? d.z : (kz == 1 ? d.x : d.y);
-    const float Sz = 1.0f / dz;
-    const float Sx = dx * Sz, Sy = dy * Sz;
-    if (kz == 0) {  // kx = y, ky = z
-      mx = f3(-Sx, 1.0f, 0.0f), my = f3(-Sy, 0.0f, 1.0f), mz = f3(Sz, 0.0f, 0.0f);
-    } else if (kz == 1) {  // kx = z, ky = x
-      mx = f3(0.0f, -Sx, 1.0f), my = f3(1.0f, -Sy, 0.0f), mz = f3(0.0f, Sz, 0.0f);
-    } else {  // kx = x, ky = y
-      mx = f3(1.0f, 0.0f, -Sx), my = f3(0.0f, 1.0f, -Sy), mz = f3(0.0f, 0.0f, Sz);
-    }
+// A ray source/sink ("Src") provides:
+//   static constexpr bool kTma     — tiles arrive by TMA bulk copy (issue()) or are read/generated in fetch()
+//   static constexpr bool kAnyHit  — rays may be first-hit rays (any_hit(tag))
+//   static constexpr bool kAlpha   — stochastic alpha test may reject candidates (alpha_pass())
+//   uint32_t n                     — rays in this launch
+//   void issue(base, cnt, raw_smem_u32, mbar_u32)            (lane 0; kTma only)
+//   void fetch(raw, base, slot, a, b, tmin, tag)              a = {o.xyz, *}, b = {d.xyz, tmax}
+//   void store(index, tag, hit, node_visits, tri_visits)
+template <bool STATS, class Src>
+RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const Src& src,
+                        uint32_t* __restrict__ work, TraceSmem& sm) {
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const uint32_t n = src.n;
+  const unsigned char* raw = sm.raw[warp];
+  float4(*pool)[32] = sm.pool[warp];
+  uint2* sstack = sm.stack + threadIdx.x;
+  const uint32_t raw_s = smem_u32(raw), mbar_s = smem_u32(&sm.mbar[warp]);
+  uint32_t parity = 0;
+
+  if constexpr (Src::kTma) {
+    if (lane == 0) mbar_init(mbar_s, 1);
+    __syncwarp();
   }
-  const float sdx = safe_dir(d.x), sdy = safe_dir(d.y), sdz = safe_dir(d.z);
-  const float idx = 1.0f / sdx, idy = 1.0f / sdy, idz = 1.0f / sdz;
-  const bool negx = sdx < 0.0f, negy = sdy < 0.0f, negz = sdz < 0.0f;
-  const uint32_t oct_inv = (negx ? 0u : 4u) | (negy ? 0u : 2u) | (negz ? 0u : 1u);
-  const uint32_t oct_inv4 = oct_inv * 0x01010101u;
+  uint32_t next_base = 0;  // tile in flight (>= n: none left)
+  if (lane == 0) next_base = atomicAdd(work, 32u);
+  next_base = __shfl_sync(0xffffffffu, next_base, 0);
+  if constexpr (Src::kTma) {
+    if (lane == 0 && next_base < n) src.issue(next_base, min(32u, n - next_base), raw_s, mbar_s);
+  }
+  uint32_t pool_base = 0, pool_pos = 0, pool_cnt = 0;
 
+  // ---- per-lane traversal slot ----
+  bool have = false;
+  float3 o = f3(0, 0, 0), mx = f3(0, 0, 0), my = f3(0, 0, 0), mz = f3(0, 0, 0);
+  float tmin = 0, idx = 0, idy = 0, idz = 0;
+  bool negx = false, negy = false, negz = false;
+  uint32_t oct_inv = 0, oct_inv4 = 0, tag = 0, ridx = 0, nvis = 0, tvis = 0;
+  HitRec best;
+  best.t = 0, best.u = 0, best.v = 0, best.prim = 0xFFFFFFFFu;
   int sp = 0;
   uint2 lstack[kLocalStack];
-  uint2 cur = make_uint2(0u, 0x80000000u);
+  uint2 cur = make_uint2(0u, 0u);
 
   for (;;) {
-    uint2 tg;
-    {
-      const uint32_t hits = cur.y;
-      const uint32_t off = 31u - (uint32_t)__clz((int)hits);
-      cur.y &= ~(1u << off);
-      if (cur.y & 0xff000000u) {
-        if (sp < SMEM_STACK)
-          sstack[sp * sstride] = cur;
-        else
-          lstack[sp - SMEM_STACK] = cur;
-        sp++;
+    unsigned idle = __ballot_sync(0xffffffffu, !have);
+    if (idle) {
+      for (;;) {
+        if (pool_pos >= pool_cnt) {
+          if (next_base >= n) break;
+          // ---- whole warp, converged: turn tile `next_base` into traversal-ready records ----
+          const uint32_t base = next_base, cnt = min(32u, n - base);
+          if constexpr (Src::kTma) {
+            mbar_wait(mbar_s, parity);
+            parity ^= 1u;
+          }
+          float4 a = make_float4(0, 0, 0, 0), b = make_float4(0, 0, 1, 0);
+          float r_tmin = 0;
+          uint32_t r_tag = 0;
+          if ((uint32_t)lane < cnt) src.fetch(raw, base, (uint32_t)lane, a, b, r_tmin, r_tag);
+          __syncwarp();  // raw tile and old pool records are dead from here on
+          if (lane == 0) next_base = atomicAdd(work, 32u);
+          next_base = __shfl_sync(0xffffffffu, next_base, 0);
+          if constexpr (Src::kTma) {
+    if (lane == 0 && next_base < n) src.issue(next_base, min(32u, n - next_base), raw_s, mbar_s);
+  }
+          if ((uint32_t)lane < cnt) {
+            const float3 d = f3(b.x, b.y, b.z);
+            const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+            const int kz = (ax >= ay && ax >= az) ? 0 : (ay >= az ? 1 : 2);
+            const float dz = kz == 0 ? d.x : (kz == 1 ? d.y : d.z);
+            const float dx = kz == 0 ? d.y : (kz == 1 ? d.z : d.x);
+            const float dy = kz == 0 ? d.z : (kz == 1 ? d.x : d.y);
+            const float Sz = 1.0f / dz;
+            const float Sx = dx * Sz, Sy = dy * Sz;
+            const float sdx = safe_dir(d.x), sdy = safe_dir(d.y), sdz = safe_dir(d.z);
+            pool[0][lane] = make_float4(a.x, a.y, a.z, r_tmin);
+            pool[1][lane] = make_float4(1.0f / sdx, 1.0f / sdy, 1.0f / sdz, b.w);
+            pool[2][lane] = make_float4(Sx, Sy, Sz, __int_as_float(kz));
+            pool[3][lane] = make_float4(__uint_as_float(r_tag), 0.0f, 0.0f, 0.0f);
+          }
+          __syncwarp();
+          pool_base = base, pool_pos = 0, pool_cnt = cnt;
+        }
+        const uint32_t slot = pool_pos + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+        if (!have && slot < pool_cnt) {
+          const float4 q0 = pool[0][slot], q1 = pool[1][slot], q2 = pool[2][slot];
+          tag = __float_as_uint(pool[3][slot].x);
+          ridx = pool_base + slot;
+          o = f3(q0.x, q0.y, q0.z), tmin = q0.w;
+          idx = q1.x, idy = q1.y, idz = q1.z;
+          best.t = q1.w, best.u = 0.0f, best.v = 0.0f, best.prim = 0xFFFFFFFFu;
+          const int kz = __float_as_int(q2.w);
+          const float Sx = q2.x, Sy = q2.y, Sz = q2.z;
+          // shear matrix rows (mx, my, mz): kx = kz+1, ky = kz+2 (mod 3)
+          if (kz == 0) {  // kx = y, ky = z
+            mx = f3(-Sx, 1.0f, 0.0f), my = f3(-Sy, 0.0f, 1.0f), mz = f3(Sz, 0.0f, 0.0f);
+          } else if (kz == 1) {  // kx = z, ky = x
+            mx = f3(0.0f, -Sx, 1.0f), my = f3(1.0f, -Sy, 0.0f), mz = f3(0.0f, Sz, 0.0f);
+          } else {  // kx = x, ky = y
+            mx = f3(1.0f, 0.0f, -Sx), my = f3(0.0f, 1.0f, -Sy), mz = f3(0.0f, 0.0f, Sz);
+          }
+          negx = idx < 0.0f, negy = idy < 0.0f, negz = idz < 0.0f;
+          oct_inv = (negx ? 0u : 4u) | (negy ? 0u : 2u) | (negz ? 0u : 1u);
+          oct_inv4 = oct_inv * 0x01010101u;
+          cur = make_uint2(0u, 0x80000000u);
+          sp = 0, nvis = 0, tvis = 0;
+          have = true;
+        }
+        pool_pos = min(pool_pos + (uint32_t)__popc(idle), pool_cnt);
+        idle = __ballot_sync(0xffffffffu, !have);
+        if (!idle) break;
       }
-      const uint32_t slot = (off - 24u) ^ oct_inv;
-      const uint32_t rel = (uint32_t)__popc(hits & ~(0xffffffffu << slot));
-      const uint4* np = nodes + (size_t)(cur.x + rel) * 5;
-      const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
-      if (STATS) nvis++;
-      const float sx = __uint_as_float((n0.w & 0xffu) << 23) * idx;
-      const float sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idy;
-      const float sz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * idz;
-      const float ox = (__uint_as_float(n0.x) - o.x) * idx;
-      const float oy = (__uint_as_float(n0.y) - o.y) * idy;
-      const float oz = (__uint_as_float(n0.z) - o.z) * idz;
-      uint32_t hitmask = 0;
+      if (idle == 0xffffffffu) break;  // pool dry, no tile left, nobody traversing
+    }
+    if (have) {
+      bool finished = false;
+      uint2 tg;
+      {
+        const uint32_t hits = cur.y;
+        const uint32_t off = 31u - (uint32_t)__clz((int)hits);
+        cur.y &= ~(1u << off);
+        if (cur.y & 0xff000000u) {
+          if (sp < kSmemStack)
+            sstack[sp * kTraceBlock] = cur;
+          else
+            lstack[sp - kSmemStack] = cur;
+          sp++;
+        }
+        const uint32_t cslot = (off - 24u) ^ oct_inv;
+        const uint32_t rel = (uint32_t)__popc(hits & ~(0xffffffffu << cslot));
+        const uint4* np = nodes + (size_t)(cur.x + rel) * 5;
+        const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+        if (STATS) nvis++;
+        const float sx = __uint_as_float((n0.w & 0xffu) << 23) * idx;
+        const float sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idy;
+        const float sz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * idz;
+        const float ox = (__uint_as_float(n0.x) - o.x) * idx;
+        const float oy = (__uint_as_float(n0.y) - o.y) * idy;
+        const float oz = (__uint_as_float(n0.z) - o.z) * idz;
+        // far planes get a slack relative to the magnitude of the operands that cancel in q*s + o (2^-22 of
+        // |o| + 256|s|): this is the rounding-error bound of the slab arithmetic, and it keeps a ray that runs
+        // exactly inside a box face (axis-parallel, origin on the face) from being culled.
+        const float oxf = fmaf(fmaf(fabsf(sx), 256.0f, fabsf(ox)), kFarSlack, ox);
+        const float oyf = fmaf(fmaf(fabsf(sy), 256.0f, fabsf(oy)), kFarSlack, oy);
+        const float ozf = fmaf(fmaf(fabsf(sz), 256.0f, fabsf(oz)), kFarSlack, oz);
+        const float best_s = best.t * kBoxSlack;  // equal-t candidates behind a rounded box entry stay reachable
+        uint32_t hitmask = 0;
 #pragma unroll
-      for (int half = 0; half < 2; half++) {
-        const uint32_t meta4 = half ? n1.w : n1.z;
-        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-        const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
-        const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
-        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-        const uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
-        const uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
-        const uint32_t nx = negx ? qhix : qlox, fx = negx ? qlox : qhix;
-        const uint32_t ny = negy ? qhiy : qloy, fy = negy ? qloy : qhiy;
-        const uint32_t nz = negz ? qhiz : qloz, fz = negz ? qloz : qhiz;
+        for (int half = 0; half < 2; half++) {
+          const uint32_t meta4 = half ? n1.w : n1.z;
+          const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+          const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
+          const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
+          const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+          const uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
+          const uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
+          const uint32_t nx = negx ? qhix : qlox, fx = negx ? qlox : qhix;
+          const uint32_t ny = negy ? qhiy : qloy, fy = negy ? qloy : qhiy;
+          const uint32_t nz = negz ? qhiz : qloz, fz = negz ? qloz : qhiz;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-          const float tnx = fmaf((float)extract_byte(nx, j), sx, ox);
-          const float tny = fmaf((float)extract_byte(ny, j), sy, oy);
-          const float tnz = fmaf((float)extract_byte(nz, j), sz, oz);
-          const float tfx = fmaf((float)extract_byte(fx, j), sx, ox);
-          const float tfy = fmaf((float)extract_byte(fy, j), sy, oy);
-          const float tfz = fmaf((float)extract_byte(fz, j), sz, oz);
-          const float tnear = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
-          const float tfar = fminf(fminf(tfx, tfy), fminf(tfz, best.t));
-          if (tnear <= tfar * kBoxSlack) {
-            const uint32_t cb = extract_byte(child_bits4, j);
-            const uint32_t bi = extract_byte(bit_index4, j);
-            hitmask |= cb << bi;
+          for (int j = 0; j < 4; j++) {
+            const float tnx = fmaf(byte_to_float(nx, j), sx, ox);
+            const float tny = fmaf(byte_to_float(ny, j), sy, oy);
+            const float tnz = fmaf(byte_to_float(nz, j), sz, oz);
+            const float tfx = fmaf(byte_to_float(fx, j), sx, oxf);
+            const float tfy = fmaf(byte_to_float(fy, j), sy, oyf);
+            const float tfz = fmaf(byte_to_float(fz, j), sz, ozf);
+            const float tnear = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
+            const float tfar = fminf(fminf(tfx, tfy), fminf(tfz, best_s));
+            if (tnear <= tfar) {
+              const uint32_t cb = extract_byte(child_bits4, j);
+              const uint32_t bi = extract_byte(bit_index4, j);
+              hitmask |= cb << bi;
+            }
+          }
+        }
+        cur.x = n1.x;
+        cur.y = (hitmask & 0xff000000u) | (n0.w >> 24);
+        tg.x = n1.y;
+        tg.y = hitmask & 0x00ffffffu;
+      }
+      while (tg.y) {
+        const uint32_t ti = 31u - (uint32_t)__clz((int)tg.y);
+        tg.y &= ~(1u << ti);
+        const float4* tp = tris + (size_t)(tg.x + ti) * 3;
+        const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+        if (STATS) tvis++;
+        const float3 A = f3(t0.x - o.x, t0.y - o.y, t0.z - o.z);
+        const float3 B = f3(t1.x - o.x, t1.y - o.y, t1.z - o.z);
+        const float3 C = f3(t2.x - o.x, t2.y - o.y, t2.z - o.z);
+        const float Ax = fmaf(mx.z, A.z, fmaf(mx.y, A.y, mx.x * A.x));
+        const float Ay = fmaf(my.z, A.z, fmaf(my.y, A.y, my.x * A.x));
+        const float Bx = fmaf(mx.z, B.z, fmaf(mx.y, B.y, mx.x * B.x));
+        const float By = fmaf(my.z, B.z, fmaf(my.y, B.y, my.x * B.x));
+        const float Cx = fmaf(mx.z, C.z, fmaf(mx.y, C.y, mx.x * C.x));
+        const float Cy = fmaf(my.z, C.z, fmaf(my.y, C.y, my.x * C.x));
+        float U = Cx * By - Cy * Bx;
+        float V = Ax * Cy - Ay * Cx;
+        float W = Bx * Ay - By * Ax;
+        if (U == 0.0f || V == 0.0f || W == 0.0f) {
+          U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+          V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+          W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+        }
+        if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) continue;
+        const float det = (U + V) + W;
+        if (det == 0.0f) continue;
+        const float Az = fmaf(mz.z, A.z, fmaf(mz.y, A.y, mz.x * A.x));
+        const float Bz = fmaf(mz.z, B.z, fmaf(mz.y, B.y, mz.x * B.x));
+        const float Cz = fmaf(mz.z, C.z, fmaf(mz.y, C.y, mz.x * C.x));
+        const float T = fmaf(U, Az, fmaf(V, Bz, W * Cz));
+        const float rcp = 1.0f / det;
+        const float t = T * rcp;
+        const uint32_t prim = __float_as_uint(t0.w);
+        if (!(t >= tmin)) continue;
+        if (t > best.t) continue;
+        if (t == best.t && prim >= best.prim) continue;
+        if constexpr (Src::kAlpha) {
+          if (__float_as_uint(t2.w) & TRI_FLAG_ALPHA)
+            if (!src.alpha_pass(tag, prim, __float_as_uint(t1.w))) continue;
+        }
+        best.t = t, best.u = V * rcp, best.v = W * rcp, best.prim = prim;
+        if constexpr (Src::kAnyHit) {
+          if (src.any_hit(tag)) {
+            finished = true;
+            break;
           }
         }
       }
-      cur.x = n1.x;
-      cur.y = (hitmask & 0xff000000u) | (n0.w >> 24);
-      tg.x = n1.y;
-      tg.y = hitmask & 0x00ffffffu;
-    }
-    while (tg.y) {
-      const uint32_t ti = 31u - (uint32_t)__clz((int)tg.y);
-      tg.y &= ~(1u << ti);
-      const float4* tp = tris + (size_t)(tg.x + ti) * 3;
-      const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
-      if (STATS) tvis++;
-      const float3 A = f3(t0.x - o.x, t0.y - o.y, t0.z - o.z);
-      const float3 B = f3(t1.x - o.x, t1.y - o.y, t1.z - o.z);
-      const float3 C = f3(t2.x - o.x, t2.y - o.y, t2.z - o.z);
-      const float Ax = fmaf(mx.z, A.z, fmaf(mx.y, A.y, mx.x * A.x));
-      const float Ay = fmaf(my.z, A.z, fmaf(my.y, A.y, my.x * A.x));
-      const float Bx = fmaf(mx.z, B.z, fmaf(mx.y, B.y, mx.x * B.x));
-      const float By = fmaf(my.z, B.z, fmaf(my.y, B.y, my.x * B.x));
-      const float Cx = fmaf(mx.z, C.z, fmaf(mx.y, C.y, mx.x * C.x));
-      const float Cy = fmaf(my.z, C.z, fmaf(my.y, C.y, my.x * C.x));
-      float U = Cx * By - Cy * Bx;
-      float V = Ax * Cy - Ay * Cx;
-      float W = Bx * Ay - By * Ax;
-      if (U == 0.0f || V == 0.0f || W == 0.0f) {
-        U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
-        V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
-        W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
-      }
-      if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) continue;
-      const float det = (U + V) + W;
-      if (det == 0.0f) continue;
-      const float Az = fmaf(mz.z, A.z, fmaf(mz.y, A.y, mz.x * A.x));
-      const float Bz = fmaf(mz.z, B.z, fmaf(mz.y, B.y, mz.x * B.x));
-      const float Cz = fmaf(mz.z, C.z, fmaf(mz.y, C.y, mz.x * C.x));
-      const float T = fmaf(U, Az, fmaf(V, Bz, W * Cz));
-      const float rcp = 1.0f / det;
-      const float t = T * rcp;
-      const uint32_t prim = __float_as_uint(t0.w);
-      if (!(t >= tmin)) continue;
-      if (t > best.t) continue;
-      if (t == best.t && prim >= best.prim) continue;
-      if (flags & TRACE_ALPHA) {
-        if (__float_as_uint(t2.w) & TRI_FLAG_ALPHA) {
-          const float alpha = actx.inst_alpha[__float_as_uint(t1.w)];
-          const float rnd = path_rng(actx.seed, STREAM_ALPHA, actx.unit, actx.bounce, prim).x;
-          if (alpha <= rnd) continue;
+      if (!finished && (cur.y & 0xff000000u) == 0) {
+        if (sp == 0) {
+          finished = true;
+        } else {
+          sp--;
+          cur = sp < kSmemStack ? sstack[sp * kTraceBlock] : lstack[sp - kSmemStack];
         }
       }
-      best.t = t, best.u = V * rcp, best.v = W * rcp, best.prim = prim;
-      if (flags & TRACE_ANY_HIT) return best;
-    }
-    if ((cur.y & 0xff000000u) == 0) {
-      if (sp == 0) break;
-      sp--;
-      cur = sp < SMEM_STACK ? sstack[sp * sstride] : lstack[sp - SMEM_STACK];
+      if (finished) {
+        src.store(ridx, tag, best, nvis, tvis);
+        have = false;
+      }
     }
   }
-  return best;
 }
 
 }  // namespace rtf

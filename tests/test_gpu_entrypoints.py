@@ -132,8 +132,8 @@ def test_lidar_grid_and_aos(rt, orc, S, scenes):
     assert np.array_equal(prim, oprim) and np.array_equal(inst, oinst)
     assert (prim != 0xFFFFFFFF).mean() > 0.5
     # a ray range (multi-GPU sharding by ray range) is the same slice
-    t2, prim2, _ = rt.scan_grid(grid, 12345, 23456)
-    assert_bit_equal(t2, t[12345:23456], "range t") and np.array_equal(prim2, prim[12345:23456])
+    t2, prim2, _ = rt.scan_grid(grid, 2345, 13456)
+    assert_bit_equal(t2, t[2345:13456], "range t") and np.array_equal(prim2, prim[2345:13456])
     # CudaModule::SamplePointCloud signature: 112 B AoS in-out
     rays = orc.scan_grid_rays(grid, 0, n)[::7]
     smp = np.zeros(len(rays) + 2, dtype=S.PC_SAMPLE_DTYPE)

@@ -104,6 +104,16 @@ def test_bvh_hits_equal_brute_force_sorghum(orc, scenes):
     assert_bit_equal(osc.trace(ax), osc.trace_brute(ax), "axis rays")
     h = osc.trace(ax)
     assert h["prim"][4] in (0, 1) and h["t"][4] == 1.0  # straight down onto the ground (primitives 0,1)
+    # axis-parallel rays running exactly inside a face of the scene box (the ground's edges and corners):
+    # the brute-force intersector hits the boundary triangles, so the box test must not cull them
+    face = []
+    for x in (-2.0, 2.0):
+        for z in (-2.0, 0.3, 2.0):
+            face += [[x, 1.0, z, 0.0, 0, -1, 0, 1e20], [x, 1.0, z, 0.0, -0.0, -1, -0.0, 1e20], [z, 1.0, x, 0.0, 0, -1, 0, 1e20]]
+    face = np.array(face, dtype=np.float32)
+    hf = osc.trace(face)
+    assert_bit_equal(hf, osc.trace_brute(face), "on-face rays")
+    assert (hf["prim"] != 0xFFFFFFFF).all()
 
 
 def test_tmin_tmax_window(orc, scenes):
