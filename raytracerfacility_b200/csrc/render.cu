@@ -28,6 +28,14 @@ static_assert(kSmemStack + kLocalStack == kMaxStackDepth, "stack split must cove
 static inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
 
 constexpr uint32_t kShadowBit = 0x80000000u;
+// resident blocks per SM the register allocator must allow: 8 x 128 threads = 64 registers (measured 3118 vs 3017
+// Mrays/s at 80 registers / 6 blocks); the queue kernel carries the path map and keeps 72.
+#ifndef RTF_TRACE_MIN_BLOCKS
+#define RTF_TRACE_MIN_BLOCKS 8
+#endif
+#ifndef RTF_QUEUE_MIN_BLOCKS
+#define RTF_QUEUE_MIN_BLOCKS 7
+#endif
 
 // ============================ raw closest-hit (M1 metric) =========================================
 // Persistent lanes (rtf_trace.cuh): rays are the interleaved n x 8 float layout {o.xyz, tmin, d.xyz, tmax};
@@ -57,7 +65,7 @@ struct SrcRays {
   }
 };
 template <bool STATS>
-__global__ void __launch_bounds__(kTraceBlock) k_trace_rays(DevScene sc, SrcRays src, uint32_t* work) {
+__global__ void __launch_bounds__(kTraceBlock, RTF_TRACE_MIN_BLOCKS) k_trace_rays(DevScene sc, SrcRays src, uint32_t* work) {
   __shared__ TraceSmem sm;
   trace_engine<STATS>(sc.nodes, sc.tris, src, work, sm);
 }
@@ -179,7 +187,7 @@ struct SrcQueue {
     hits[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
   }
 };
-__global__ void __launch_bounds__(kTraceBlock)
+__global__ void __launch_bounds__(kTraceBlock, RTF_QUEUE_MIN_BLOCKS)
     k_trace_queue(DevScene sc, Queues q, int qi, int wave, float tmin, PathMap pm, uint32_t seed, unsigned long long* stats) {
   __shared__ TraceSmem sm;
   const uint32_t n = q.count[wave];

@@ -48,9 +48,13 @@ RTF_D uint32_t extract_byte(uint32_t w, int j) { return (w >> (8 * j)) & 0xffu; 
 // float(byte j of w), exact.  PRMT builds 0x4B0000bb = 2^23 + b, one FADD removes the bias: both run on the
 // full-rate ALU/FMA pipes, whereas I2F.U8 is a quarter-rate XU instruction (48 of them per node made XU the
 // busiest pipe of the first version, profiles/r1_trace_baseline.md).
-RTF_D float byte_to_float(uint32_t w, int j) {
-  return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7540u + (uint32_t)j)) - 8388608.0f;
+RTF_D float byte_to_float(uint32_t w, int j, uint32_t magic /* 0x4B000000, kept in a register */) {
+  return __uint_as_float(__byte_perm(w, magic, 0x7540u + (uint32_t)j)) - 8388608.0f;
 }
+// The bias constant must stay in ONE register so that the selector becomes PRMT's immediate; given a literal, ptxas
+// encodes the constant as the immediate and re-materialises the selector with a MOV per PRMT (48 per node).  It is
+// therefore derived from a run-time value the compiler cannot fold (n < 2^31 always).
+RTF_D uint32_t prmt_magic(uint32_t n) { return 0x4B000000u | (n >> 31); }
 
 // ---- TMA 1-D bulk copy + mbarrier (PTX; SASS: UBLKCP / SYNCS) -------------------------------------------
 RTF_D uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -105,6 +109,7 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
   uint2* sstack = sm.stack + threadIdx.x;
   const uint32_t raw_s = smem_u32(raw), mbar_s = smem_u32(&sm.mbar[warp]);
   uint32_t parity = 0;
+  const uint32_t magic = prmt_magic(src.n);
 
   if constexpr (Src::kTma) {
     if (lane == 0) mbar_init(mbar_s, 1);
@@ -129,6 +134,7 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
   int sp = 0;
   uint2 lstack[kLocalStack];
   uint2 cur = make_uint2(0u, 0u);
+  uint2 tg = make_uint2(0u, 0u);  // pending leaf triangles of the node visited last: {base, hit bits}
 
   for (;;) {
     unsigned idle = __ballot_sync(0xffffffffu, !have);
@@ -192,6 +198,7 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
           oct_inv = (negx ? 0u : 4u) | (negy ? 0u : 2u) | (negz ? 0u : 1u);
           oct_inv4 = oct_inv * 0x01010101u;
           cur = make_uint2(0u, 0x80000000u);
+          tg = make_uint2(0u, 0u);
           sp = 0, nvis = 0, tvis = 0;
           have = true;
         }
@@ -201,10 +208,13 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
       }
       if (idle == 0xffffffffu) break;  // pool dry, no tile left, nobody traversing
     }
+    // One iteration = (a) a node visit for the lanes with no pending triangle, then (b) at most ONE triangle test per
+    // lane.  A lane whose node produced several leaf hits keeps them in `tg` and skips (a) until they are done, so its
+    // own sequence (node, all its triangles, next node) is unchanged — but the warp no longer waits, at 8 % utilisation,
+    // for the one lane that hit ten triangles (profiles/r1_trace_persistent.md).
     if (have) {
       bool finished = false;
-      uint2 tg;
-      {
+      if (tg.y == 0u) {
         const uint32_t hits = cur.y;
         const uint32_t off = 31u - (uint32_t)__clz((int)hits);
         cur.y &= ~(1u << off);
@@ -248,12 +258,12 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
           const uint32_t nz = negz ? qhiz : qloz, fz = negz ? qloz : qhiz;
 #pragma unroll
           for (int j = 0; j < 4; j++) {
-            const float tnx = fmaf(byte_to_float(nx, j), sx, ox);
-            const float tny = fmaf(byte_to_float(ny, j), sy, oy);
-            const float tnz = fmaf(byte_to_float(nz, j), sz, oz);
-            const float tfx = fmaf(byte_to_float(fx, j), sx, oxf);
-            const float tfy = fmaf(byte_to_float(fy, j), sy, oyf);
-            const float tfz = fmaf(byte_to_float(fz, j), sz, ozf);
+            const float tnx = fmaf(byte_to_float(nx, j, magic), sx, ox);
+            const float tny = fmaf(byte_to_float(ny, j, magic), sy, oy);
+            const float tnz = fmaf(byte_to_float(nz, j, magic), sz, oz);
+            const float tfx = fmaf(byte_to_float(fx, j, magic), sx, oxf);
+            const float tfy = fmaf(byte_to_float(fy, j, magic), sy, oyf);
+            const float tfz = fmaf(byte_to_float(fz, j, magic), sz, ozf);
             const float tnear = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
             const float tfar = fminf(fminf(tfx, tfy), fminf(tfz, best_s));
             if (tnear <= tfar) {
@@ -268,7 +278,8 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
         tg.x = n1.y;
         tg.y = hitmask & 0x00ffffffu;
       }
-      while (tg.y) {
+      do {
+        if (tg.y == 0u) break;
         const uint32_t ti = 31u - (uint32_t)__clz((int)tg.y);
         tg.y &= ~(1u << ti);
         const float4* tp = tris + (size_t)(tg.x + ti) * 3;
@@ -291,9 +302,9 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
           V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
           W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
         }
-        if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) continue;
+        if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) break;
         const float det = (U + V) + W;
-        if (det == 0.0f) continue;
+        if (det == 0.0f) break;
         const float Az = fmaf(mz.z, A.z, fmaf(mz.y, A.y, mz.x * A.x));
         const float Bz = fmaf(mz.z, B.z, fmaf(mz.y, B.y, mz.x * B.x));
         const float Cz = fmaf(mz.z, C.z, fmaf(mz.y, C.y, mz.x * C.x));
@@ -301,22 +312,19 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
         const float rcp = 1.0f / det;
         const float t = T * rcp;
         const uint32_t prim = __float_as_uint(t0.w);
-        if (!(t >= tmin)) continue;
-        if (t > best.t) continue;
-        if (t == best.t && prim >= best.prim) continue;
+        if (!(t >= tmin)) break;
+        if (t > best.t) break;
+        if (t == best.t && prim >= best.prim) break;
         if constexpr (Src::kAlpha) {
           if (__float_as_uint(t2.w) & TRI_FLAG_ALPHA)
-            if (!src.alpha_pass(tag, prim, __float_as_uint(t1.w))) continue;
+            if (!src.alpha_pass(tag, prim, __float_as_uint(t1.w))) break;
         }
         best.t = t, best.u = V * rcp, best.v = W * rcp, best.prim = prim;
         if constexpr (Src::kAnyHit) {
-          if (src.any_hit(tag)) {
-            finished = true;
-            break;
-          }
+          if (src.any_hit(tag)) finished = true;
         }
-      }
-      if (!finished && (cur.y & 0xff000000u) == 0) {
+      } while (false);
+      if (!finished && tg.y == 0u && (cur.y & 0xff000000u) == 0) {
         if (sp == 0) {
           finished = true;
         } else {

@@ -18,7 +18,7 @@ import numpy as np
 from . import structs as S
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librtf_b200.so")
+LIB_PATH = os.environ.get("RTF_B200_LIB", os.path.join(_HERE, "librtf_b200.so"))  # env override: developer A/B builds
 
 OK, ERR_INVALID, ERR_CUDA, ERR_NOT_READY, ERR_NOT_FOUND, ERR_LIMIT = 0, -1, -2, -3, -4, -5
 MISS = 0xFFFFFFFF

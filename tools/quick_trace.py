@@ -1,0 +1,64 @@
+#!/usr/bin/env python
+"""Developer loop: time k_trace_rays on the C2 scene and check a sub-sample bit for bit against the CPU oracle.
+    python tools/quick_trace.py [--plants 50] [--log2-rays 26] [--reps 5] [--check 131072]"""
+import argparse
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--plants", type=int, default=50)
+    ap.add_argument("--log2-rays", type=int, default=26)
+    ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--check", type=int, default=1 << 17)
+    args = ap.parse_args()
+    import torch
+
+    from raytracerfacility_b200 import module, scenes
+    dev = torch.device("cuda", 0)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    rt = module.RayTracer(0)
+    rt.set_stream(stream.cuda_stream)
+    sd = scenes.sorghum_scene(args.plants)
+    rt.load_scene(sd, 63)
+    lo, hi = scenes.scene_bounds(sd)
+    n = 1 << args.log2_rays
+    rays = scenes.incoherent_rays_torch(n, lo, hi, seed=3, device=dev)
+    hits = torch.empty((n, 4), dtype=torch.float32, device=dev)
+    for _ in range(3):
+        rt.trace_closest_device(rays.data_ptr(), n, hits.data_ptr())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(stream)
+    for _ in range(args.reps):
+        rt.trace_closest_device(rays.data_ptr(), n, hits.data_ptr())
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.reps
+    print(f"k_trace_rays: {ms:.3f} ms for 2^{args.log2_rays} rays = {n / ms / 1e3:.1f} Mrays/s", flush=True)
+    if args.check:
+        from oracle import pyoracle as orc
+        osc = orc.OracleScene(sd, 63)
+        m = args.check
+        sub = rays[:m].cpu().numpy()
+        gh, gnv, gtv = rt.trace_closest(sub, counts=True)
+        oh, onv, otv = osc.trace(sub, counts=True)
+        ok_h = np.array_equal(gh.view(np.uint32), oh.view(np.uint32))
+        ok_d = np.array_equal(hits[:m].cpu().numpy().view(np.uint32).reshape(-1), gh.view(np.uint32).reshape(-1))
+        ok_c = np.array_equal(gnv, onv) and np.array_equal(gtv, otv)
+        print(f"parity on {m} rays: hits bit-exact={ok_h} device-path==host-path={ok_d} visit counts equal={ok_c} "
+              f"(mean nodes {gnv.mean():.2f}, tris {gtv.mean():.2f})")
+        if not (ok_h and ok_d and ok_c):
+            sys.exit(1)
+    rt.destroy()
+
+
+if __name__ == "__main__":
+    main()
