@@ -80,6 +80,13 @@ int rtf_destroy(rtf_ctx* ctx) {
   for (DevBuf* b : bufs) b->release();
   for (cudaEvent_t e : ctx->build_ev)
     if (e) cudaEventDestroy(e);
+  if (ctx->pipe.init) {
+    for (int k = 0; k < 2; k++) {
+      cudaEventDestroy(ctx->pipe.ev_in[k]), cudaEventDestroy(ctx->pipe.ev_done[k]), cudaEventDestroy(ctx->pipe.ev_out[k]);
+      ctx->pipe.rays[k].release(), ctx->pipe.hits[k].release();
+    }
+    cudaStreamDestroy(ctx->pipe.in), cudaStreamDestroy(ctx->pipe.out);
+  }
   if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return RTF_OK;
@@ -262,6 +269,12 @@ int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value) {
       return RTF_ERR_INVALID;
     }
     ctx->batch_paths = (size_t)value;
+  } else if (!strcmp(name, "pipe_chunk_rays")) {
+    if (value < 1024 || value > ((int64_t)1 << 28)) {
+      set_error("pipe_chunk_rays must be in [2^10, 2^28]");
+      return RTF_ERR_INVALID;
+    }
+    ctx->pipe_chunk_rays = (size_t)value;
   } else if (!strcmp(name, "sort_rays")) {
     ctx->sort_rays = value != 0;
   } else {
@@ -439,8 +452,54 @@ int rtf_trace_closest_counts(rtf_ctx* ctx, const float* rays, size_t n, void* hi
   RTF_CUDA(cudaStreamSynchronize(ctx->stream));
   return RTF_OK;
 }
+static int pipe_init(rtf_ctx* ctx) {
+  HostPipe& p = ctx->pipe;
+  if (p.init) return RTF_OK;
+  RTF_CUDA(cudaStreamCreateWithFlags(&p.in, cudaStreamNonBlocking));
+  RTF_CUDA(cudaStreamCreateWithFlags(&p.out, cudaStreamNonBlocking));
+  for (int k = 0; k < 2; k++) {
+    RTF_CUDA(cudaEventCreateWithFlags(&p.ev_in[k], cudaEventDisableTiming));
+    RTF_CUDA(cudaEventCreateWithFlags(&p.ev_done[k], cudaEventDisableTiming));
+    RTF_CUDA(cudaEventCreateWithFlags(&p.ev_out[k], cudaEventDisableTiming));
+  }
+  p.init = true;
+  return RTF_OK;
+}
+// Host rays in, host hits out.  Large batches run as a three-stage pipeline over chunks: H2D of chunk i+1 (copy-in
+// stream), traversal of chunk i (context stream) and D2H of chunk i-1 (copy-out stream) overlap; PCIe is full duplex,
+// so the job is bounded by the larger of the two copy directions instead of their sum plus the kernel.  Pinned host
+// buffers give true overlap; pageable ones still work (the runtime stages them).
 int rtf_trace_closest(rtf_ctx* ctx, const float* rays, size_t n, void* hits) {
-  return rtf_trace_closest_counts(ctx, rays, n, hits, nullptr, nullptr);
+  CHECK_CTX(ctx);
+  if ((!rays || !hits) && n) return RTF_ERR_INVALID;
+  if (!ctx->ready) return not_ready();
+  if (n == 0) return RTF_OK;
+  const size_t chunk = ctx->pipe_chunk_rays;
+  if (n <= chunk) return rtf_trace_closest_counts(ctx, rays, n, hits, nullptr, nullptr);
+  int rc;
+  if ((rc = pipe_init(ctx))) return rc;
+  HostPipe& p = ctx->pipe;
+  for (int k = 0; k < 2; k++)
+    if ((rc = p.rays[k].reserve(chunk * 32)) || (rc = p.hits[k].reserve(chunk * 16))) return rc;
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));  // earlier work of the caller on the context stream
+  size_t i = 0;
+  for (size_t off = 0; off < n; off += chunk, i++) {
+    const size_t m = (n - off) < chunk ? (n - off) : chunk;
+    const int b = (int)(i & 1);
+    if (i >= 2) RTF_CUDA(cudaStreamWaitEvent(p.in, p.ev_done[b], 0));  // chunk i-2 no longer reads rays[b]
+    RTF_CUDA(cudaMemcpyAsync(p.rays[b].p, rays + off * 8, m * 32, cudaMemcpyHostToDevice, p.in));
+    RTF_CUDA(cudaEventRecord(p.ev_in[b], p.in));
+    RTF_CUDA(cudaStreamWaitEvent(ctx->stream, p.ev_in[b], 0));
+    if (i >= 2) RTF_CUDA(cudaStreamWaitEvent(ctx->stream, p.ev_out[b], 0));  // hits[b] of chunk i-2 has left the device
+    if ((rc = trace_rays_device(ctx, p.rays[b].as<float4>(), m, p.hits[b].as<float4>(), nullptr, nullptr))) return rc;
+    RTF_CUDA(cudaEventRecord(p.ev_done[b], ctx->stream));
+    RTF_CUDA(cudaStreamWaitEvent(p.out, p.ev_done[b], 0));
+    RTF_CUDA(cudaMemcpyAsync((char*)hits + off * 16, p.hits[b].p, m * 16, cudaMemcpyDeviceToHost, p.out));
+    RTF_CUDA(cudaEventRecord(p.ev_out[b], p.out));
+  }
+  RTF_CUDA(cudaStreamSynchronize(p.out));
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+  return RTF_OK;
 }
 
 // ---- camera -------------------------------------------------------------------------------------------------------

@@ -788,14 +788,21 @@ int microbench_fp32(rtf_ctx* ctx, double* tflops) {
   *tflops = (double)blocks * threads * (double)iters * 8.0 * 2.0 / (ms * 1e-3) / 1e12;
   return RTF_OK;
 }
+// L2 -> SM read bandwidth.  Every repetition rotates the index space by a large odd offset, so the lines a block reads
+// in repetition r were last touched by OTHER SMs: the 228 KB L1 of an SM never holds them and each 128-bit load is an
+// L2 hit (footprint <= ~96 MB of the 126 MB L2).
 __global__ void k_l2_read(const uint4* __restrict__ src, size_t n_vec, int reps, uint4* sink) {
   uint4 acc = make_uint4(0, 0, 0, 0);
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (int r = 0; r < reps; r++)
+  for (int r = 0; r < reps; r++) {
+    const size_t shift = ((size_t)r * 2654435761ull) % n_vec;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride) {
-      const uint4 v = __ldg(src + i);
+      size_t j = i + shift;
+      if (j >= n_vec) j -= n_vec;
+      const uint4 v = __ldg(src + j);
       acc.x ^= v.x, acc.y ^= v.y, acc.z ^= v.z, acc.w ^= v.w;
     }
+  }
   if (acc.x == 0x12345678u && acc.y == 0x9abcdef0u) *sink = acc;
 }
 int microbench_l2(rtf_ctx* ctx, double bytes, double* gbs) {

@@ -99,6 +99,16 @@ struct Workspace {  // wavefront queues + path state, sized for `capacity` paths
   DevBuf io;  // staging for AoS entry points
 };
 
+// Double-buffered host<->device pipeline of the host-buffer entry points (upload chunk i+1 and download chunk i-1
+// while chunk i is traced).  The reference uploads, launches, synchronises and downloads serially
+// (CUDAModule.cpp:43-49, 57-63).
+struct HostPipe {
+  bool init = false;
+  cudaStream_t in = nullptr, out = nullptr;
+  cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+  DevBuf rays[2], hits[2];
+};
+
 }  // namespace rtf
 
 struct rtf_ctx {
@@ -119,11 +129,13 @@ struct rtf_ctx {
   rtf::DevBuf d_pos9, d_nrm9, d_tri_inst, d_nodes, d_tris48, d_insts, d_mats, d_inst_alpha;
   rtf::BuildArrays ba;
   rtf::Workspace ws;
+  rtf::HostPipe pipe;
+  size_t pipe_chunk_rays = (size_t)1 << 22;  // option "pipe_chunk_rays"
   rtf::DevScene scene;
   uint64_t last_rays = 0, last_paths = 0;
   rtf::DevBuf d_stats;  // {rays u64, paths u64}
   // options (rtf_set_option)
-  size_t batch_paths = (size_t)1 << 22;
+  size_t batch_paths = (size_t)1 << 24;  // 2^24 paths: ~3 GB of queues + path state; +12..20 % over 2^22 (fewer, fuller waves)
   int sort_rays = 1;
   // build-stage events: flatten | bounds+morton | sort | karras+refit | collapse | end
   cudaEvent_t build_ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};

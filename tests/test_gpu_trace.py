@@ -114,3 +114,19 @@ def test_field_1m_triangles_properties(rt, orc, S, scenes):
     osc = orc.OracleScene(sd, 63)
     sub = rays[::64]
     assert_bit_equal(hits[::64], osc.trace(sub), "sub-sample vs oracle")
+
+
+def test_host_pipeline_chunks(rt, orc, scenes):
+    """rtf_trace_closest with host buffers larger than one pipeline chunk: H2D / trace / D2H overlap over chunks,
+    ragged last chunk; result identical to the single-shot path and to the oracle."""
+    sd = scenes.sorghum_scene(1)
+    rt.load_scene(sd, 63)
+    osc = orc.OracleScene(sd, 63)
+    lo, hi = scenes.scene_bounds(sd)
+    rays = scenes.incoherent_rays(4096 * 5 + 777, lo, hi, seed=21)
+    rt.set_option("pipe_chunk_rays", 4096)
+    piped = rt.trace_closest(rays)
+    rt.set_option("pipe_chunk_rays", 1 << 22)
+    single = rt.trace_closest(rays)
+    assert_bit_equal(piped, single, "pipelined vs single shot")
+    assert_bit_equal(piped, osc.trace(rays), "pipelined vs oracle")

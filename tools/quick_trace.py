@@ -17,6 +17,7 @@ def main():
     ap.add_argument("--log2-rays", type=int, default=26)
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--check", type=int, default=1 << 17)
+    ap.add_argument("--sort", type=int, default=0, help="sort the rays by (octant, origin cell of 2^SORT per axis) first")
     args = ap.parse_args()
     import torch
 
@@ -31,6 +32,19 @@ def main():
     lo, hi = scenes.scene_bounds(sd)
     n = 1 << args.log2_rays
     rays = scenes.incoherent_rays_torch(n, lo, hi, seed=3, device=dev)
+    if args.sort:
+        g = 1 << args.sort
+        lo_t = torch.tensor(lo, dtype=torch.float32, device=dev)
+        ext = torch.tensor(hi - lo, dtype=torch.float32, device=dev)
+        cell = ((rays[:, 0:3] - lo_t) / ext * g).clamp(0, g - 1).to(torch.int64)
+        key = torch.zeros(n, dtype=torch.int64, device=dev)
+        for b in range(args.sort):
+            for a in range(3):
+                key |= ((cell[:, a] >> b) & 1) << (3 * b + (2 - a))
+        octant = ((rays[:, 4] < 0).to(torch.int64) << 2) | ((rays[:, 5] < 0).to(torch.int64) << 1) | (rays[:, 6] < 0).to(torch.int64)
+        key |= octant << (3 * args.sort)
+        rays = rays[torch.argsort(key)].contiguous()
+        del key, cell, octant
     hits = torch.empty((n, 4), dtype=torch.float32, device=dev)
     for _ in range(3):
         rt.trace_closest_device(rays.data_ptr(), n, hits.data_ptr())
