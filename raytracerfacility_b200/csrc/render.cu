@@ -29,12 +29,12 @@ static inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1
 
 constexpr uint32_t kShadowBit = 0x80000000u;
 // resident blocks per SM the register allocator must allow: 8 x 128 threads = 64 registers (measured 3118 vs 3017
-// Mrays/s at 80 registers / 6 blocks); the queue kernel carries the path map and keeps 72.
+// Mrays/s at 80 registers / 6 blocks); the queue kernel with stochastic alpha carries the path map and RNG keys: 80 registers / 6 blocks (spilling at 72 cost 12 %).
 #ifndef RTF_TRACE_MIN_BLOCKS
 #define RTF_TRACE_MIN_BLOCKS 8
 #endif
 #ifndef RTF_QUEUE_MIN_BLOCKS
-#define RTF_QUEUE_MIN_BLOCKS 7
+#define RTF_QUEUE_MIN_BLOCKS 6
 #endif
 
 // ============================ raw closest-hit (M1 metric) =========================================
@@ -154,8 +154,9 @@ __device__ __forceinline__ uint32_t warp_append(bool emit, uint32_t* counter) {
 // Queue rays are SoA: a 32-ray tile is two 512 B TMA bulk copies (origins|path, directions|tmax).  tmin is
 // uniform per wavefront (camera primary rays 0, everything else 1e-3: CameraRendering.cu:89, IlluminationEstimation.cu:69,
 // RayFunctions.cuh:77,140), so the .w of the origin stream carries the path index instead.
+template <bool ALPHA>
 struct SrcQueue {
-  static constexpr bool kTma = true, kAnyHit = true, kAlpha = true;
+  static constexpr bool kTma = true, kAnyHit = true, kAlpha = ALPHA;
   const float4* ra;
   const float4* rb;
   float4* hits;
@@ -187,12 +188,14 @@ struct SrcQueue {
     hits[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
   }
 };
-__global__ void __launch_bounds__(kTraceBlock, RTF_QUEUE_MIN_BLOCKS)
+// ALPHA = some material can ignore hits (transmission > 0): only then does the kernel carry the path map and RNG keys.
+template <bool ALPHA>
+__global__ void __launch_bounds__(kTraceBlock, ALPHA ? RTF_QUEUE_MIN_BLOCKS : RTF_QUEUE_MIN_BLOCKS + 1)
     k_trace_queue(DevScene sc, Queues q, int qi, int wave, float tmin, PathMap pm, uint32_t seed, unsigned long long* stats) {
   __shared__ TraceSmem sm;
   const uint32_t n = q.count[wave];
   if (blockIdx.x == 0 && threadIdx.x == 0 && stats) atomicAdd(stats, (unsigned long long)n);
-  SrcQueue src{q.ray_a[qi], q.ray_b[qi], q.hits, n, tmin, sc.has_alpha ? sc.inst_alpha : nullptr, pm, seed, (uint32_t)wave};
+  SrcQueue<ALPHA> src{q.ray_a[qi], q.ray_b[qi], q.hits, n, tmin, ALPHA ? sc.inst_alpha : nullptr, pm, seed, (uint32_t)wave};
   trace_engine<false>(sc.nodes, sc.tris, src, q.work + wave, sm);
 }
 
@@ -464,7 +467,10 @@ static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_
   int qi = 0;
   for (int w = 0; w < waves; w++) {
     const float tmin = (camera && w == 0) ? 0.0f : 1e-3f;
-    LAUNCH(ctx, k_trace_queue, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
+    if (ctx->scene.has_alpha)
+      LAUNCH(ctx, k_trace_queue<true>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
+    else
+      LAUNCH(ctx, k_trace_queue<false>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
     LAUNCH(ctx, k_shade, div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
     qi ^= 1;
   }

@@ -39,6 +39,10 @@ constexpr float kFarSlack = 2.384185791015625e-07f;   // 2^-22 of the slab opera
 constexpr int kTraceBlock = 128;
 constexpr int kTraceWarps = kTraceBlock / 32;
 constexpr int kRawTileBytes = 1024;  // 32 rays x 32 B
+#ifndef RTF_NODE_QUORUM
+#define RTF_NODE_QUORUM 24
+#endif
+constexpr int kNodeQuorum = RTF_NODE_QUORUM;  // lanes that must be ready before the warp runs a node visit
 
 RTF_D float safe_dir(float d) {
   const float ooeps = __uint_as_float(0x17800000u);  // 2^-80
@@ -81,11 +85,11 @@ RTF_D void mbar_wait(uint32_t mbar, uint32_t parity) {
   } while (!ok);
 }
 
-// Shared memory of one trace block (static, 21 KB): per warp a raw TMA tile, a pool of prepared rays and
+// Shared memory of one trace block (static, 23 KB): per warp a raw TMA tile, a pool of prepared rays and
 // an mbarrier; per thread kSmemStack stack entries.
 struct __align__(128) TraceSmem {
   unsigned char raw[kTraceWarps][kRawTileBytes];
-  float4 pool[kTraceWarps][4][32];
+  float4 pool[kTraceWarps][5][32];
   uint2 stack[kSmemStack * kTraceBlock];
   unsigned long long mbar[kTraceWarps];
 };
@@ -168,32 +172,33 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
             const float Sz = 1.0f / dz;
             const float Sx = dx * Sz, Sy = dy * Sz;
             const float sdx = safe_dir(d.x), sdy = safe_dir(d.y), sdz = safe_dir(d.z);
+            // shear matrix rows (mx, my, mz): kx = kz+1, ky = kz+2 (mod 3) — built here, at 32/32 lanes
+            float3 rx, ry, rz;
+            if (kz == 0) {  // kx = y, ky = z
+              rx = f3(-Sx, 1.0f, 0.0f), ry = f3(-Sy, 0.0f, 1.0f), rz = f3(Sz, 0.0f, 0.0f);
+            } else if (kz == 1) {  // kx = z, ky = x
+              rx = f3(0.0f, -Sx, 1.0f), ry = f3(1.0f, -Sy, 0.0f), rz = f3(0.0f, Sz, 0.0f);
+            } else {  // kx = x, ky = y
+              rx = f3(1.0f, 0.0f, -Sx), ry = f3(0.0f, 1.0f, -Sy), rz = f3(0.0f, 0.0f, Sz);
+            }
             pool[0][lane] = make_float4(a.x, a.y, a.z, r_tmin);
             pool[1][lane] = make_float4(1.0f / sdx, 1.0f / sdy, 1.0f / sdz, b.w);
-            pool[2][lane] = make_float4(Sx, Sy, Sz, __int_as_float(kz));
-            pool[3][lane] = make_float4(__uint_as_float(r_tag), 0.0f, 0.0f, 0.0f);
+            pool[2][lane] = make_float4(rx.x, rx.y, rx.z, ry.x);
+            pool[3][lane] = make_float4(ry.y, ry.z, rz.x, rz.y);
+            pool[4][lane] = make_float4(rz.z, __uint_as_float(r_tag), 0.0f, 0.0f);
           }
           __syncwarp();
           pool_base = base, pool_pos = 0, pool_cnt = cnt;
         }
         const uint32_t slot = pool_pos + (uint32_t)__popc(idle & ((1u << lane) - 1u));
         if (!have && slot < pool_cnt) {
-          const float4 q0 = pool[0][slot], q1 = pool[1][slot], q2 = pool[2][slot];
-          tag = __float_as_uint(pool[3][slot].x);
+          const float4 q0 = pool[0][slot], q1 = pool[1][slot], q2 = pool[2][slot], q3 = pool[3][slot], q4 = pool[4][slot];
+          tag = __float_as_uint(q4.y);
           ridx = pool_base + slot;
           o = f3(q0.x, q0.y, q0.z), tmin = q0.w;
           idx = q1.x, idy = q1.y, idz = q1.z;
           best.t = q1.w, best.u = 0.0f, best.v = 0.0f, best.prim = 0xFFFFFFFFu;
-          const int kz = __float_as_int(q2.w);
-          const float Sx = q2.x, Sy = q2.y, Sz = q2.z;
-          // shear matrix rows (mx, my, mz): kx = kz+1, ky = kz+2 (mod 3)
-          if (kz == 0) {  // kx = y, ky = z
-            mx = f3(-Sx, 1.0f, 0.0f), my = f3(-Sy, 0.0f, 1.0f), mz = f3(Sz, 0.0f, 0.0f);
-          } else if (kz == 1) {  // kx = z, ky = x
-            mx = f3(0.0f, -Sx, 1.0f), my = f3(1.0f, -Sy, 0.0f), mz = f3(0.0f, Sz, 0.0f);
-          } else {  // kx = x, ky = y
-            mx = f3(1.0f, 0.0f, -Sx), my = f3(0.0f, 1.0f, -Sy), mz = f3(0.0f, 0.0f, Sz);
-          }
+          mx = f3(q2.x, q2.y, q2.z), my = f3(q2.w, q3.x, q3.y), mz = f3(q3.z, q3.w, q4.x);
           negx = idx < 0.0f, negy = idy < 0.0f, negz = idz < 0.0f;
           oct_inv = (negx ? 0u : 4u) | (negy ? 0u : 2u) | (negz ? 0u : 1u);
           oct_inv4 = oct_inv * 0x01010101u;
@@ -211,10 +216,16 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
     // One iteration = (a) a node visit for the lanes with no pending triangle, then (b) at most ONE triangle test per
     // lane.  A lane whose node produced several leaf hits keeps them in `tg` and skips (a) until they are done, so its
     // own sequence (node, all its triangles, next node) is unchanged — but the warp no longer waits, at 8 % utilisation,
-    // for the one lane that hit ten triangles (profiles/r1_trace_persistent.md).
+    // for the one lane that hit ten triangles.  (a) is the expensive phase (~300 instructions): it only runs when at
+    // least kNodeQuorum lanes want it or nobody has a triangle to test, so it executes with a well-filled warp while
+    // the triangle-bound lanes catch up (profiles/r1_trace_persistent.md).
+    const unsigned want_node = __ballot_sync(0xffffffffu, have && tg.y == 0u);
+    const unsigned want_tri = __ballot_sync(0xffffffffu, have && tg.y != 0u);
+    const bool run_node = __popc(want_node) >= kNodeQuorum || want_tri == 0u;
     if (have) {
       bool finished = false;
-      if (tg.y == 0u) {
+      const bool did_node = run_node && tg.y == 0u;
+      if (did_node) {
         const uint32_t hits = cur.y;
         const uint32_t off = 31u - (uint32_t)__clz((int)hits);
         cur.y &= ~(1u << off);
@@ -278,8 +289,10 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
         tg.x = n1.y;
         tg.y = hitmask & 0x00ffffffu;
       }
+      bool tested = false;
       do {
         if (tg.y == 0u) break;
+        tested = true;
         const uint32_t ti = 31u - (uint32_t)__clz((int)tg.y);
         tg.y &= ~(1u << ti);
         const float4* tp = tris + (size_t)(tg.x + ti) * 3;
@@ -324,7 +337,7 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
           if (src.any_hit(tag)) finished = true;
         }
       } while (false);
-      if (!finished && tg.y == 0u && (cur.y & 0xff000000u) == 0) {
+      if (!finished && tg.y == 0u && (cur.y & 0xff000000u) == 0 && (did_node || tested)) {
         if (sp == 0) {
           finished = true;
         } else {
