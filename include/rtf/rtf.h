@@ -209,7 +209,9 @@ RTF_API int rtf_triangle_count(rtf_ctx* ctx, uint64_t* n_triangles);
  * has no counterpart: its builds are opaque optixAccelBuild calls, RT.cu:1562-1584.) */
 RTF_API int rtf_build_timings(rtf_ctx* ctx, float* ms_out, int n);
 /* Tuning knobs (not in the reference): "batch_paths" = wavefront batch capacity in paths,
- * "sort_rays" = 0/1 sort bounce rays by (direction octant, origin cell) before tracing. */
+ * "sort_rays" = 0/1 sort bounce rays by (direction octant, origin cell) before tracing,
+ * "presplit" = most references a long thin triangle may be cut into before the Morton sort
+ * (default 8, 1 = off; applies at the next rtf_commit; hits do not depend on it). */
 RTF_API int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value);
 
 /* ---- illumination: CudaModule::EstimateIlluminationRayTracing (CM.hpp:38-41, CM.cpp:39-50)
@@ -277,17 +279,19 @@ RTF_API int rtf_camera_device_buffer(rtf_camera* cam, int which, float** dev_rgb
 
 /* ---- build-stage readback for parity tests (tests/ compares each with the oracle) --------- */
 enum {
-  RTF_DBG_MORTON = 0,       /* u64 per triangle (unsorted order)                 */
-  RTF_DBG_SORTED_IDS = 1,   /* u32 per triangle                                  */
+  RTF_DBG_MORTON = 0,       /* u64 per triangle reference (unsorted order)       */
+  RTF_DBG_SORTED_IDS = 1,   /* u32 per triangle reference: sorted position -> reference */
   RTF_DBG_BIN_CHILDREN = 2, /* 2 x i32 per internal binary node (>=0 internal, <0 = ~leaf) */
   RTF_DBG_BIN_PARENT = 3,   /* i32 per binary node: internals [0,n-1) then leaves [n-1, 2n-1) */
   RTF_DBG_BIN_BOXES = 4,    /* 6 floats per binary node, same numbering            */
   RTF_DBG_WIDE_NODES = 5,   /* 80 B per wide node                                */
-  RTF_DBG_WIDE_TRIS = 6,    /* 48 B per triangle, BVH order                      */
+  RTF_DBG_WIDE_TRIS = 6,    /* 48 B per triangle reference, BVH order            */
   RTF_DBG_FLAT_POS = 7,     /* 9 floats per triangle, commit order               */
   RTF_DBG_FLAT_NRM = 8,     /* 9 floats per triangle, commit order               */
   RTF_DBG_FLAT_INST = 9,    /* u32 per triangle                                  */
-  RTF_DBG_SCENE_BOUNDS = 10 /* 6 floats                                          */
+  RTF_DBG_SCENE_BOUNDS = 10, /* 6 floats                                         */
+  RTF_DBG_REF_TRI = 11,     /* u32 per triangle reference: its triangle          */
+  RTF_DBG_REF_BOX = 12      /* 6 floats per triangle reference: clipped bounds   */
 };
 RTF_API int rtf_debug_size(rtf_ctx* ctx, int what, uint64_t* bytes);
 RTF_API int rtf_debug_read(rtf_ctx* ctx, int what, void* host_out, uint64_t bytes);

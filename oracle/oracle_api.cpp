@@ -85,7 +85,8 @@ ORC_API int orc_scene_add_instance(Scene* s, int geom, int mat, const float* xfo
   s->insts.push_back(in);
   return (int)s->insts.size() - 1;
 }
-ORC_API void orc_scene_commit(Scene* s, int bits) { commit(*s, bits == 30 ? 30 : 63); }
+ORC_API void orc_scene_commit(Scene* s, int bits, int presplit) { commit(*s, bits == 30 ? 30 : 63, presplit < 1 ? 1 : presplit); }
+ORC_API uint64_t orc_scene_nrefs(Scene* s) { return s->bvh.nref; }
 ORC_API uint64_t orc_scene_ntris(Scene* s) { return s->tri_inst.size(); }
 ORC_API uint64_t orc_scene_nnodes(Scene* s) { return s->bvh.nodes.size(); }
 ORC_API int orc_scene_depth(Scene* s) { return s->bvh.depth; }
@@ -104,6 +105,8 @@ static const void* dbg_ptr(Scene* s, int what, uint64_t* bytes) {
     case RTF_DBG_FLAT_NRM: *bytes = s->nrm9.size() * 4; return s->nrm9.data();
     case RTF_DBG_FLAT_INST: *bytes = s->tri_inst.size() * 4; return s->tri_inst.data();
     case RTF_DBG_SCENE_BOUNDS: *bytes = 24; return &b.scene;
+    case RTF_DBG_REF_TRI: *bytes = b.ref_tri.size() * 4; return b.ref_tri.data();
+    case RTF_DBG_REF_BOX: *bytes = b.ref_box.size() * 24; return b.ref_box.data();
   }
   *bytes = 0;
   return nullptr;

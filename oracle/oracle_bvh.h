@@ -49,11 +49,15 @@ struct Box {
 };
 
 struct BVH {
-  uint32_t n = 0;
+  uint32_t n = 0;     // triangles
+  uint32_t nref = 0;  // triangle references (>= n when long triangles are pre-split, see split_refs)
   int bits = 63;
   Box scene;
-  std::vector<uint64_t> morton;      // per triangle, unsorted
-  std::vector<uint32_t> order;       // sorted position -> triangle
+  std::vector<uint32_t> ref_first;   // per triangle: index of its first reference (n + 1 entries)
+  std::vector<uint32_t> ref_tri;     // per reference: its triangle
+  std::vector<Box> ref_box;          // per reference: bounds of the triangle clipped to the reference's slab
+  std::vector<uint64_t> morton;      // per reference, unsorted
+  std::vector<uint32_t> order;       // sorted position -> reference
   std::vector<int32_t> children;     // 2 per internal binary node; >=0 internal index, <0 = ~leaf position
   std::vector<int32_t> parent;       // per binary node (internals [0,n-1), leaves [n-1,2n-1)); root = -1
   std::vector<uint32_t> range_first; // per internal node
@@ -129,20 +133,107 @@ static inline uint32_t quant_exponent(float extent) {
   return e;
 }
 
-static inline void build(BVH& bvh, uint32_t n, const float* pos9, const uint32_t* tri_inst, int bits) {
-  bvh.n = n;
+
+// ---- triangle references (pre-splitting) -------------------------------------------------------
+// Long thin triangles that run diagonally (sorghum leaves are 2 mm x 45 mm slivers) have boxes far larger than
+// themselves; a ray then tests dozens of triangles it cannot hit.  Before the Morton sort such a triangle is cut
+// into k slabs along the longest axis of its box ("early split clipping", Ernst & Greiner 2007); every slab becomes
+// one REFERENCE with the bounds of the clipped triangle.  References of one triangle all point to the same 48 B
+// triangle record, so the intersection result does not change (equal t resolves to the lower primitive id).
+struct SplitPlan {
+  int k, axis;
+};
+constexpr float kSplitGain = 0.5f;  // k = floor(gain * box half-area / (2 * triangle area)), >= 2 to split
+static inline SplitPlan split_plan(V3 a, V3 b, V3 c, int max_split) {
+  SplitPlan sp{1, 0};
+  const V3 lo = vmin(vmin(a, b), c), hi = vmax(vmax(a, b), c);
+  const V3 e = hi - lo;
+  sp.axis = (e.x >= e.y && e.x >= e.z) ? 0 : (e.y >= e.z ? 1 : 2);
+  if (max_split <= 1) return sp;
+  const V3 ab = b - a, ac = c - a;
+  const V3 n = v3(ab.y * ac.z - ab.z * ac.y, ab.z * ac.x - ab.x * ac.z, ab.x * ac.y - ab.y * ac.x);
+  const float area2 = sqrtf((n.x * n.x + n.y * n.y) + n.z * n.z);  // twice the triangle's area
+  const float ha = (e.x * e.y + e.y * e.z) + e.z * e.x;
+  if (!(area2 > 0.0f) || !(ha < INFINITY)) return sp;
+  const float r = (ha / area2) * kSplitGain;  // a flat box tight around the triangle has half-area == area2
+  if (!(r >= 2.0f)) return sp;
+  sp.k = r >= (float)max_split ? max_split : (int)r;
+  return sp;
+}
+// Bounds of triangle (a,b,c) clipped to slab j of k along `axis`.  Planes: lo + j*(ext/k); the same float value
+// closes slab j-1 and opens slab j, so the slabs tile the box without gaps.  Clipped edge points are rounded, hence
+// the other two axes are padded by 2^-21 of the box magnitude and clamped to the triangle's own box.
+static inline Box split_slab_box(V3 a, V3 b, V3 c, int axis, int k, int j) {
+  const float A[3][3] = {{a.x, a.y, a.z}, {b.x, b.y, b.z}, {c.x, c.y, c.z}};
+  float lo[3], hi[3];
+  for (int d = 0; d < 3; d++) {
+    lo[d] = fminf(fminf(A[0][d], A[1][d]), A[2][d]);
+    hi[d] = fmaxf(fmaxf(A[0][d], A[1][d]), A[2][d]);
+  }
+  if (k <= 1) return Box{v3(lo[0], lo[1], lo[2]), v3(hi[0], hi[1], hi[2])};
+  const float w = (hi[axis] - lo[axis]) / (float)k;
+  const float x0 = j == 0 ? lo[axis] : fminf(lo[axis] + (float)j * w, hi[axis]);
+  const float x1 = j == k - 1 ? hi[axis] : fminf(lo[axis] + (float)(j + 1) * w, hi[axis]);
+  float blo[3] = {INFINITY, INFINITY, INFINITY}, bhi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int v = 0; v < 3; v++) {
+    if (A[v][axis] >= x0 && A[v][axis] <= x1)
+      for (int d = 0; d < 3; d++) blo[d] = fminf(blo[d], A[v][d]), bhi[d] = fmaxf(bhi[d], A[v][d]);
+  }
+  for (int ed = 0; ed < 3; ed++) {
+    const float* P = A[ed];
+    const float* Q = A[(ed + 1) % 3];
+    if (P[axis] > Q[axis]) {
+      const float* T = P;
+      P = Q, Q = T;
+    }
+    for (int s = 0; s < 2; s++) {
+      const float xp = s ? x1 : x0;
+      if (P[axis] < xp && xp < Q[axis]) {
+        const float t = (xp - P[axis]) / (Q[axis] - P[axis]);
+        for (int d = 0; d < 3; d++) {
+          const float v = fmaf(Q[d] - P[d], t, P[d]);
+          blo[d] = fminf(blo[d], v), bhi[d] = fmaxf(bhi[d], v);
+        }
+      }
+    }
+  }
+  for (int d = 0; d < 3; d++) {
+    if (d == axis) {
+      blo[d] = x0, bhi[d] = x1;
+    } else {
+      const float pad = fmaxf(fabsf(lo[d]), fabsf(hi[d])) * 4.76837158203125e-07f;  // 2^-21
+      blo[d] = fmaxf(blo[d] - pad, lo[d]);
+      bhi[d] = fminf(bhi[d] + pad, hi[d]);
+      if (!(blo[d] <= bhi[d])) blo[d] = lo[d], bhi[d] = hi[d];  // empty slab (cannot happen for a valid triangle)
+    }
+  }
+  return Box{v3(blo[0], blo[1], blo[2]), v3(bhi[0], bhi[1], bhi[2])};
+}
+
+static inline void build(BVH& bvh, uint32_t ntri, const float* pos9, const uint32_t* tri_inst, int bits,
+                         int max_split = 1) {
+  bvh.n = ntri;
   bvh.bits = bits;
   const float INF = INFINITY;
   Box sc{v3(INF, INF, INF), v3(-INF, -INF, -INF)};
-  std::vector<Box> tbox(n);
-  for (uint32_t t = 0; t < n; t++) {
+  bvh.ref_first.assign((size_t)ntri + 1, 0);
+  bvh.ref_tri.clear();
+  bvh.ref_box.clear();
+  for (uint32_t t = 0; t < ntri; t++) {
     const float* p = pos9 + 9 * (size_t)t;
     V3 a = v3(p[0], p[1], p[2]), b = v3(p[3], p[4], p[5]), c = v3(p[6], p[7], p[8]);
-    tbox[t].lo = vmin(vmin(a, b), c);
-    tbox[t].hi = vmax(vmax(a, b), c);
-    sc.lo = vmin(sc.lo, tbox[t].lo);
-    sc.hi = vmax(sc.hi, tbox[t].hi);
+    const SplitPlan sp = split_plan(a, b, c, max_split);
+    bvh.ref_first[t] = (uint32_t)bvh.ref_tri.size();
+    for (int j = 0; j < sp.k; j++) {
+      bvh.ref_tri.push_back(t);
+      bvh.ref_box.push_back(split_slab_box(a, b, c, sp.axis, sp.k, j));
+    }
+    sc.lo = vmin(sc.lo, vmin(vmin(a, b), c));
+    sc.hi = vmax(sc.hi, vmax(vmax(a, b), c));
   }
+  bvh.ref_first[ntri] = (uint32_t)bvh.ref_tri.size();
+  const uint32_t n = bvh.nref = (uint32_t)bvh.ref_tri.size();
+  const std::vector<Box>& tbox = bvh.ref_box;
   bvh.scene = sc;
   V3 ext = sc.hi - sc.lo;
   V3 inv = v3(ext.x > 0 ? 1.0f / ext.x : 0.0f, ext.y > 0 ? 1.0f / ext.y : 0.0f, ext.z > 0 ? 1.0f / ext.z : 0.0f);
@@ -311,7 +402,7 @@ static inline void build(BVH& bvh, uint32_t n, const float* pos9, const uint32_t
           node.meta[s] = (uint8_t)((unary << 5) | tri_off);
           uint32_t first = bin_first(c);
           for (uint32_t j = 0; j < cnt; j++) {
-            uint32_t prim = bvh.order[first + j];
+            uint32_t prim = bvh.ref_tri[bvh.order[first + j]];
             Tri48& T = bvh.tris[tri_cursor + tri_off + j];
             const float* p = pos9 + 9 * (size_t)prim;
             T.v0[0] = p[0], T.v0[1] = p[1], T.v0[2] = p[2];
@@ -398,7 +489,7 @@ static inline bool intersect_tri(const Ray& ray, const RayPrep& rp, const Tri48&
 static inline Hit trace_brute(const BVH& bvh, const Ray& ray) {
   Hit best{ray.tmax, 0.0f, 0.0f, 0xFFFFFFFFu};
   RayPrep rp = prep_ray(ray.d);
-  for (uint32_t i = 0; i < bvh.n; i++) intersect_tri(ray, rp, bvh.tris[i], best);
+  for (uint32_t i = 0; i < bvh.nref; i++) intersect_tri(ray, rp, bvh.tris[i], best);
   return best;
 }
 

@@ -65,9 +65,9 @@ static inline void flatten(Scene& sc) {
     }
   }
 }
-static inline void commit(Scene& sc, int bits) {
+static inline void commit(Scene& sc, int bits, int max_split = 1) {
   flatten(sc);
-  build(sc.bvh, (uint32_t)sc.tri_inst.size(), sc.pos9.data(), sc.tri_inst.data(), bits);
+  build(sc.bvh, (uint32_t)sc.tri_inst.size(), sc.pos9.data(), sc.tri_inst.data(), bits, max_split);
   sc.committed = true;
 }
 

@@ -91,7 +91,7 @@ def env_light(env, pos, d):
 class OracleScene:
     """CPU oracle scene built from a scenes.SceneDesc (instances in ascending handle order)."""
 
-    def __init__(self, desc, morton_bits=63):
+    def __init__(self, desc, morton_bits=63, presplit=S.DEFAULT_PRESPLIT):
         L = lib()
         self.h = C.c_void_p(L.orc_scene_create())
         gmap, mmap = {}, {}
@@ -107,7 +107,7 @@ class OracleScene:
             g, m, x, comp = desc.instances[ih]
             x = np.ascontiguousarray(x, dtype=np.float32)
             L.orc_scene_add_instance(self.h, gmap[g], mmap[m], _p(x), C.c_uint64(comp))
-        L.orc_scene_commit(self.h, morton_bits)
+        L.orc_scene_commit(self.h, int(morton_bits), int(presplit))
         self.n_tris = int(L.orc_scene_ntris(self.h))
         self.n_nodes = int(L.orc_scene_nnodes(self.h))
         self.depth = int(L.orc_scene_depth(self.h))

@@ -275,6 +275,12 @@ int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value) {
       return RTF_ERR_INVALID;
     }
     ctx->pipe_chunk_rays = (size_t)value;
+  } else if (!strcmp(name, "presplit")) {
+    if (value < 1 || value > 64) {
+      set_error("presplit must be in [1, 64]");
+      return RTF_ERR_INVALID;
+    }
+    ctx->presplit = (int)value;  // takes effect at the next rtf_commit
   } else if (!strcmp(name, "sort_rays")) {
     ctx->sort_rays = value != 0;
   } else {
@@ -678,8 +684,10 @@ int rtf_camera_download(rtf_camera* cam, int which, float* host) {
 
 // ---- parity read-back ----------------------------------------------------------------------------------------------
 static const void* dbg_ptr(rtf_ctx* c, int what, uint64_t* bytes) {
-  const uint64_t n = c->n_tris, ni = n ? n - 1 : 0;
+  const uint64_t nt = c->n_tris, n = c->n_refs, ni = n ? n - 1 : 0;  // n: triangle references
   switch (what) {
+    case RTF_DBG_REF_TRI: *bytes = n * 4; return c->ba.ref_tri.p;
+    case RTF_DBG_REF_BOX: *bytes = n * 24; return c->ba.ref_box.p;
     case RTF_DBG_MORTON: *bytes = n * 8; return c->ba.morton.p;
     case RTF_DBG_SORTED_IDS: *bytes = n * 4; return c->ba.sorted_ids.p;
     case RTF_DBG_BIN_CHILDREN: *bytes = ni * 8; return c->ba.children.p;
@@ -687,9 +695,9 @@ static const void* dbg_ptr(rtf_ctx* c, int what, uint64_t* bytes) {
     case RTF_DBG_BIN_BOXES: *bytes = (n ? 2 * n - 1 : 0) * 24; return c->ba.boxes.p;
     case RTF_DBG_WIDE_NODES: *bytes = (uint64_t)c->n_nodes * 80; return c->d_nodes.p;
     case RTF_DBG_WIDE_TRIS: *bytes = n * 48; return c->d_tris48.p;
-    case RTF_DBG_FLAT_POS: *bytes = n * 36; return c->d_pos9.p;
-    case RTF_DBG_FLAT_NRM: *bytes = n * 36; return c->d_nrm9.p;
-    case RTF_DBG_FLAT_INST: *bytes = n * 4; return c->d_tri_inst.p;
+    case RTF_DBG_FLAT_POS: *bytes = nt * 36; return c->d_pos9.p;
+    case RTF_DBG_FLAT_NRM: *bytes = nt * 36; return c->d_nrm9.p;
+    case RTF_DBG_FLAT_INST: *bytes = nt * 4; return c->d_tri_inst.p;
     case RTF_DBG_SCENE_BOUNDS: *bytes = 24; return c->ba.scene_bounds.p ? (char*)c->ba.scene_bounds.p + 32 : nullptr;
   }
   *bytes = 0;
@@ -723,6 +731,7 @@ int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* nodes, uint64_t n_nodes, cons
   ctx->n_nodes = (uint32_t)n_nodes, ctx->depth = depth;
   ctx->scene.n_nodes = (uint32_t)n_nodes;
   if (!ctx->ready) ctx->n_tris = (uint32_t)n_tris, ctx->scene.n_tris = (uint32_t)n_tris;
+  ctx->n_refs = (uint32_t)n_tris;
   ctx->ready = true;
   return RTF_OK;
 }

@@ -9,7 +9,6 @@
 // Every stage is an integer or exactly-rounded float computation, so tests compare each array bit for
 // bit with the CPU oracle (Morton codes, sorted order, radix-tree links, boxes, wide nodes, triangles).
 #include <cub/device/device_radix_sort.cuh>
-#include <cub/device/device_scan.cuh>
 
 #include "rtf_internal.h"
 
@@ -71,6 +70,122 @@ __device__ __forceinline__ Box3 tri_box(const float* __restrict__ pos9, uint32_t
   return bx;
 }
 
+// ---- exclusive prefix sum of u32, single pass with decoupled look-back (Merrill & Garland 2016) -----------------
+// Tiles of 2048 elements are taken in arrival order (atomic ticket), so a tile only ever waits for tiles that are
+// already running.  Tile state = one 64-bit word {flag, value}: flag 1 = tile aggregate, 2 = inclusive prefix.
+// out[n] receives the grand total (callers size `out` for n + 1 elements).
+constexpr int kScanBlock = 256, kScanItems = 8, kScanTile = kScanBlock * kScanItems;
+__global__ void __launch_bounds__(kScanBlock) k_scan_u32(const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
+                                                         uint32_t n, unsigned long long* state /* [0]=ticket, [1+tile] */) {
+  __shared__ uint32_t s_tile, s_warp[kScanBlock / 32], s_prefix;
+  if (threadIdx.x == 0) s_tile = (uint32_t)atomicAdd(state, 1ull);
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  volatile unsigned long long* desc = state + 1;
+  const uint32_t base = tile * kScanTile + threadIdx.x * kScanItems;
+  uint32_t v[kScanItems], sum = 0;
+#pragma unroll
+  for (int k = 0; k < kScanItems; k++) {
+    v[k] = base + k < n ? in[base + k] : 0u;
+    sum += v[k];
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t incl = sum;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+    if (lane >= off) incl += t;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  uint32_t warp_off = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < kScanBlock / 32; w++) {
+    if (w < warp) warp_off += s_warp[w];
+    total += s_warp[w];
+  }
+  if (warp == 0) {
+    uint32_t prefix = 0;
+    if (tile == 0) {
+      if (lane == 0) desc[0] = (2ull << 32) | total;
+    } else {
+      if (lane == 0) desc[tile] = (1ull << 32) | total;
+      int look = (int)tile - 1;
+      for (;;) {
+        const int idx = look - lane;
+        unsigned long long d = idx >= 0 ? desc[idx] : (2ull << 32);
+        while (__any_sync(0xffffffffu, (d >> 32) == 0ull)) d = idx >= 0 ? desc[idx] : (2ull << 32);
+        const unsigned done = __ballot_sync(0xffffffffu, (d >> 32) == 2ull);
+        const int first_done = done ? __ffs((int)done) - 1 : 32;  // nearest predecessor holding an inclusive prefix
+        uint32_t contrib = lane <= first_done ? (uint32_t)d : 0u;
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, off);
+        prefix += contrib;
+        if (done) break;
+        look -= 32;
+      }
+      if (lane == 0) desc[tile] = (2ull << 32) | (unsigned long long)(prefix + total);
+    }
+    if (lane == 0) s_prefix = prefix;
+  }
+  __syncthreads();
+  uint32_t run = s_prefix + warp_off + (incl - sum);
+#pragma unroll
+  for (int k = 0; k < kScanItems; k++) {
+    if (base + k < n) out[base + k] = run;
+    run += v[k];
+    if (base + k + 1 == n) out[n] = run;
+  }
+}
+static int exclusive_scan_u32(rtf_ctx* ctx, const uint32_t* in, uint32_t* out, uint32_t n, DevBuf& state) {
+  const uint32_t tiles = n ? (n + kScanTile - 1) / kScanTile : 0;
+  if (tiles == 0) {
+    RTF_CUDA(cudaMemsetAsync(out, 0, 4, ctx->stream));
+    return RTF_OK;
+  }
+  int rc;
+  if ((rc = state.reserve(8 * ((size_t)tiles + 1)))) return rc;
+  RTF_CUDA(cudaMemsetAsync(state.p, 0, 8 * ((size_t)tiles + 1), ctx->stream));
+  k_scan_u32<<<tiles, kScanBlock, 0, ctx->stream>>>(in, out, n, state.as<unsigned long long>());
+  ctx->launches++;
+  RTF_CUDA(cudaGetLastError());
+  return RTF_OK;
+}
+
+// ---- 2b. triangle references: count, (scan), emit ------------------------------------------------------------------
+__device__ __forceinline__ void load_tri(const float* __restrict__ pos9, uint32_t t, float3& a, float3& b, float3& c) {
+  const float* p = pos9 + 9 * (size_t)t;
+  a = f3(p[0], p[1], p[2]), b = f3(p[3], p[4], p[5]), c = f3(p[6], p[7], p[8]);
+}
+__global__ void k_split_count(const float* __restrict__ pos9, uint32_t n, int max_split, uint32_t* __restrict__ cnt) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  float3 a, b, c;
+  load_tri(pos9, t, a, b, c);
+  cnt[t] = (uint32_t)split_plan(a, b, c, max_split).k;
+}
+__global__ void k_split_emit(const float* __restrict__ pos9, uint32_t n, int max_split, const uint32_t* __restrict__ first,
+                             uint32_t* __restrict__ ref_tri, float* __restrict__ ref_box) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  float3 a, b, c;
+  load_tri(pos9, t, a, b, c);
+  const SplitPlan sp = split_plan(a, b, c, max_split);
+  const uint32_t r0 = first[t];
+  for (int j = 0; j < sp.k; j++) {
+    const Box3 bx = split_slab_box(a, b, c, sp.axis, sp.k, j);
+    ref_tri[r0 + j] = t;
+    float* o = ref_box + 6 * (size_t)(r0 + j);
+    o[0] = bx.lo.x, o[1] = bx.lo.y, o[2] = bx.lo.z, o[3] = bx.hi.x, o[4] = bx.hi.y, o[5] = bx.hi.z;
+  }
+}
+__device__ __forceinline__ Box3 ref_box_load(const float* __restrict__ ref_box, uint32_t r) {
+  const float* b = ref_box + 6 * (size_t)r;
+  Box3 bx;
+  bx.lo = f3(b[0], b[1], b[2]), bx.hi = f3(b[3], b[4], b[5]);
+  return bx;
+}
+
 __global__ void k_bounds_init(int* ob) {
   if (threadIdx.x < 3) ob[threadIdx.x] = float_to_ordered(INFINITY);
   else if (threadIdx.x < 6) ob[threadIdx.x] = float_to_ordered(-INFINITY);
@@ -101,14 +216,14 @@ __global__ void k_bounds_finish(const int* ob, float* fb) {
 }
 
 // ---- 3. Morton codes ---------------------------------------------------------------------------
-__global__ void k_morton(const float* __restrict__ pos9, uint32_t n, const float* __restrict__ fb, int bits,
+__global__ void k_morton(const float* __restrict__ ref_box, uint32_t n, const float* __restrict__ fb, int bits,
                          uint64_t* __restrict__ keys, uint32_t* __restrict__ ids) {
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n) return;
   const float3 lo = f3(fb[0], fb[1], fb[2]), hi = f3(fb[3], fb[4], fb[5]);
   const float3 ext = hi - lo;
   const float3 inv = f3(ext.x > 0 ? 1.0f / ext.x : 0.0f, ext.y > 0 ? 1.0f / ext.y : 0.0f, ext.z > 0 ? 1.0f / ext.z : 0.0f);
-  const Box3 b = tri_box(pos9, t);
+  const Box3 b = ref_box_load(ref_box, t);
   const float3 c = (b.lo + b.hi) * 0.5f;
   keys[t] = morton_code(c, lo, inv, bits);
   ids[t] = t;
@@ -153,13 +268,13 @@ __global__ void k_karras(const uint64_t* __restrict__ keys, int n, int2* __restr
 
 // ---- 6. bottom-up refit: second arriver at a node merges its children (boxes: 6 floats per node,
 //         internals [0,n-1), leaves [n-1,2n-1)) -----------------------------------------------------
-__global__ void k_refit(const float* __restrict__ pos9, const uint32_t* __restrict__ sorted_ids, int n,
+__global__ void k_refit(const float* __restrict__ ref_box, const uint32_t* __restrict__ sorted_ids, int n,
                         const int2* __restrict__ children, const int* __restrict__ parent, float* boxes,
                         uint32_t* __restrict__ flags) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
   const int ni = n - 1;
-  const Box3 b = tri_box(pos9, sorted_ids[k]);
+  const Box3 b = ref_box_load(ref_box, sorted_ids[k]);
   float* bo = boxes + 6 * (size_t)(ni + k);
   bo[0] = b.lo.x, bo[1] = b.lo.y, bo[2] = b.lo.z, bo[3] = b.hi.x, bo[4] = b.hi.y, bo[5] = b.hi.z;
   int node = parent[ni + k];
@@ -268,7 +383,7 @@ __global__ void k_collapse_emit(CollapseArgs a, const int* __restrict__ level, u
                                 uint32_t level_start, uint32_t next_start, uint32_t tri_cursor, int* __restrict__ next_level,
                                 Node80* __restrict__ nodes, Tri48* __restrict__ tris, const float* __restrict__ pos9,
                                 const uint32_t* __restrict__ tri_inst, const uint32_t* __restrict__ sorted_ids,
-                                const float* __restrict__ inst_alpha) {
+                                const uint32_t* __restrict__ ref_tri, const float* __restrict__ inst_alpha) {
   const uint32_t li = blockIdx.x * blockDim.x + threadIdx.x;
   if (li >= level_n) return;
   const int ni = a.n - 1;
@@ -305,7 +420,7 @@ __global__ void k_collapse_emit(CollapseArgs a, const int* __restrict__ level, u
       node.meta[s] = (uint8_t)((unary << 5) | tri_off);
       const uint32_t first = c >= 0 ? a.range[c].x : (uint32_t)~c;
       for (uint32_t j = 0; j < cnt; j++) {
-        const uint32_t prim = sorted_ids[first + j];
+        const uint32_t prim = ref_tri[sorted_ids[first + j]];
         const float* p = pos9 + 9 * (size_t)prim;
         Tri48 T;
         T.v0[0] = p[0], T.v0[1] = p[1], T.v0[2] = p[2];
@@ -338,31 +453,47 @@ int flatten_scene(rtf_ctx* ctx) {
 }
 
 int build_bvh(rtf_ctx* ctx, int bits) {
-  const uint32_t n = ctx->n_tris;
+  const uint32_t nt = ctx->n_tris;
   BuildArrays& ba = ctx->ba;
   cudaStream_t st = ctx->stream;
-  ctx->n_nodes = 0, ctx->depth = 0;
-  if (n == 0) return RTF_OK;
-  const int ni = (int)n - 1;
+  ctx->n_nodes = 0, ctx->depth = 0, ctx->n_refs = 0;
+  if (nt == 0) return RTF_OK;
   int rc;
   if ((rc = ba.scene_bounds.reserve(64))) return rc;
+  int* ob = ba.scene_bounds.as<int>();
+  float* fb = ba.scene_bounds.as<float>() + 8;
+  mark(ctx, 1);
+  LAUNCH(ctx, k_bounds_init, 1, 32, 0, ob);
+  LAUNCH(ctx, k_bounds, min(div_up(nt, 256), 148u * 8u), 256, 0, ctx->d_pos9.as<float>(), nt, ob);
+  LAUNCH(ctx, k_bounds_finish, 1, 32, 0, ob, fb);
+  // triangle references: count -> scan -> emit (one reference per triangle when presplit <= 1)
+  if ((rc = ba.ref_cnt.reserve(4 * (size_t)nt))) return rc;
+  if ((rc = ba.ref_first.reserve(4 * ((size_t)nt + 1)))) return rc;
+  LAUNCH(ctx, k_split_count, div_up(nt, 256), 256, 0, ctx->d_pos9.as<float>(), nt, ctx->presplit, ba.ref_cnt.as<uint32_t>());
+  if ((rc = exclusive_scan_u32(ctx, ba.ref_cnt.as<uint32_t>(), ba.ref_first.as<uint32_t>(), nt, ba.scan_state))) return rc;
+  uint32_t n = 0;
+  RTF_CUDA(cudaMemcpyAsync(&n, ba.ref_first.as<uint32_t>() + nt, 4, cudaMemcpyDeviceToHost, st));
+  RTF_CUDA(cudaStreamSynchronize(st));
+  if (n < nt || (uint64_t)n > 0x7fffffffull) {
+    set_error("triangle reference count out of range");
+    return RTF_ERR_LIMIT;
+  }
+  ctx->n_refs = n;
+  const int ni = (int)n - 1;
+  if ((rc = ba.ref_tri.reserve(4 * (size_t)n))) return rc;
+  if ((rc = ba.ref_box.reserve(24 * (size_t)n))) return rc;
   if ((rc = ba.morton.reserve(8 * (size_t)n))) return rc;
   if ((rc = ba.sorted_keys.reserve(8 * (size_t)n))) return rc;
   if ((rc = ba.sorted_ids.reserve(4 * (size_t)n))) return rc;
   if ((rc = ba.ids_alt.reserve(4 * (size_t)n))) return rc;
   if ((rc = ba.children.reserve(8 * (size_t)n))) return rc;
-  if ((rc = ba.parent.reserve(4 * (size_t)(2 * n)))) return rc;
+  if ((rc = ba.parent.reserve(4 * (size_t)(2 * (size_t)n)))) return rc;
   if ((rc = ba.range.reserve(8 * (size_t)n))) return rc;
-  if ((rc = ba.boxes.reserve(24 * (size_t)(2 * n)))) return rc;
+  if ((rc = ba.boxes.reserve(24 * (size_t)(2 * (size_t)n)))) return rc;
   if ((rc = ba.flags.reserve(4 * (size_t)n))) return rc;
-
-  int* ob = ba.scene_bounds.as<int>();
-  float* fb = ba.scene_bounds.as<float>() + 8;
-  mark(ctx, 1);
-  LAUNCH(ctx, k_bounds_init, 1, 32, 0, ob);
-  LAUNCH(ctx, k_bounds, min(div_up(n, 256), 148u * 8u), 256, 0, ctx->d_pos9.as<float>(), n, ob);
-  LAUNCH(ctx, k_bounds_finish, 1, 32, 0, ob, fb);
-  LAUNCH(ctx, k_morton, div_up(n, 256), 256, 0, ctx->d_pos9.as<float>(), n, fb, bits, ba.morton.as<uint64_t>(),
+  LAUNCH(ctx, k_split_emit, div_up(nt, 256), 256, 0, ctx->d_pos9.as<float>(), nt, ctx->presplit, ba.ref_first.as<uint32_t>(),
+         ba.ref_tri.as<uint32_t>(), ba.ref_box.as<float>());
+  LAUNCH(ctx, k_morton, div_up(n, 256), 256, 0, ba.ref_box.as<float>(), n, fb, bits, ba.morton.as<uint64_t>(),
          ba.ids_alt.as<uint32_t>());
   mark(ctx, 2);
   {  // 4. stable LSD radix sort of (Morton, id) pairs.  cub::DeviceRadixSort for bring-up (library code; a
@@ -377,13 +508,13 @@ int build_bvh(rtf_ctx* ctx, int bits) {
     ctx->launches += 8;
   }
   mark(ctx, 3);
-  RTF_CUDA(cudaMemsetAsync(ba.parent.p, 0xff, 4 * (size_t)(2 * n), st));
+  RTF_CUDA(cudaMemsetAsync(ba.parent.p, 0xff, 4 * (size_t)(2 * (size_t)n), st));
   if (ni > 0) {
     LAUNCH(ctx, k_karras, div_up(ni, 256), 256, 0, ba.sorted_keys.as<uint64_t>(), (int)n, ba.children.as<int2>(),
            ba.parent.as<int>(), ba.range.as<uint2>());
     RTF_CUDA(cudaMemsetAsync(ba.flags.p, 0, 4 * (size_t)n, st));
   }
-  LAUNCH(ctx, k_refit, div_up(n, 256), 256, 0, ctx->d_pos9.as<float>(), ba.sorted_ids.as<uint32_t>(), (int)n,
+  LAUNCH(ctx, k_refit, div_up(n, 256), 256, 0, ba.ref_box.as<float>(), ba.sorted_ids.as<uint32_t>(), (int)n,
          ba.children.as<int2>(), ba.parent.as<int>(), ba.boxes.as<float>(), ba.flags.as<uint32_t>());
 
   // ---- collapse ----
@@ -399,9 +530,6 @@ int build_bvh(rtf_ctx* ctx, int bits) {
   if ((rc = ba.scan_int.reserve(4 * (max_level + 1)))) return rc;
   if ((rc = ba.scan_tri.reserve(4 * (max_level + 1)))) return rc;
   if ((rc = ba.stash.reserve(32 * max_level))) return rc;
-  size_t scan_tmp = 0;
-  cub::DeviceScan::ExclusiveSum(nullptr, scan_tmp, ba.cnt_int.as<uint32_t>(), ba.scan_int.as<uint32_t>(), (int)max_level + 1, st);
-  if ((rc = ba.keys_alt.reserve(scan_tmp))) return rc;
 
   CollapseArgs ca{ba.children.as<int2>(), ba.range.as<uint2>(), ba.boxes.as<float>(), (int)n};
   int root = n == 1 ? ~0 : 0;
@@ -418,21 +546,14 @@ int build_bvh(rtf_ctx* ctx, int bits) {
     }
     LAUNCH(ctx, k_collapse_plan, div_up(level_n, 128), 128, 0, ca, lv_cur, level_n, ba.stash.as<int>(),
            ba.cnt_int.as<uint32_t>(), ba.cnt_tri.as<uint32_t>());
-    // one extra element so the exclusive scan also yields the level totals
-    RTF_CUDA(cudaMemsetAsync(ba.cnt_int.as<uint32_t>() + level_n, 0, 4, st));
-    RTF_CUDA(cudaMemsetAsync(ba.cnt_tri.as<uint32_t>() + level_n, 0, 4, st));
-    size_t tmp = scan_tmp;
-    RTF_CUDA(cub::DeviceScan::ExclusiveSum(ba.keys_alt.p, tmp, ba.cnt_int.as<uint32_t>(), ba.scan_int.as<uint32_t>(),
-                                           (int)level_n + 1, st));
-    tmp = scan_tmp;
-    RTF_CUDA(cub::DeviceScan::ExclusiveSum(ba.keys_alt.p, tmp, ba.cnt_tri.as<uint32_t>(), ba.scan_tri.as<uint32_t>(),
-                                           (int)level_n + 1, st));
-    ctx->launches += 2;
+    // exclusive scans; element [level_n] of each output receives the level total
+    if ((rc = exclusive_scan_u32(ctx, ba.cnt_int.as<uint32_t>(), ba.scan_int.as<uint32_t>(), level_n, ba.scan_state))) return rc;
+    if ((rc = exclusive_scan_u32(ctx, ba.cnt_tri.as<uint32_t>(), ba.scan_tri.as<uint32_t>(), level_n, ba.scan_state))) return rc;
     const uint32_t next_start = level_start + level_n;
     LAUNCH(ctx, k_collapse_emit, div_up(level_n, 128), 128, 0, ca, lv_cur, level_n, ba.stash.as<int>(),
            ba.scan_int.as<uint32_t>(), ba.scan_tri.as<uint32_t>(), level_start, next_start, tri_cursor, lv_next,
            ctx->d_nodes.as<Node80>(), ctx->d_tris48.as<Tri48>(), ctx->d_pos9.as<float>(), ctx->d_tri_inst.as<uint32_t>(),
-           ba.sorted_ids.as<uint32_t>(), ctx->d_inst_alpha.as<float>());
+           ba.sorted_ids.as<uint32_t>(), ba.ref_tri.as<uint32_t>(), ctx->d_inst_alpha.as<float>());
     uint32_t totals[2];
     RTF_CUDA(cudaMemcpyAsync(&totals[0], ba.scan_int.as<uint32_t>() + level_n, 4, cudaMemcpyDeviceToHost, st));
     RTF_CUDA(cudaMemcpyAsync(&totals[1], ba.scan_tri.as<uint32_t>() + level_n, 4, cudaMemcpyDeviceToHost, st));

@@ -112,4 +112,105 @@ RTF_HD void quantize_interval(float lo, float hi, float p, uint32_t e, uint8_t& 
   qhi = (uint8_t)qh;
 }
 
+// ---- triangle references (pre-splitting) -----------------------------------------------------------------------
+// Sorghum leaves are 2 mm x 45 mm slivers that run diagonally: a triangle's box is tens of times larger than the
+// triangle, and a ray tests dozens of triangles it cannot hit (30 per illumination ray on the C2 field).  Before the
+// Morton sort such a triangle is cut into k slabs along the longest axis of its box (early split clipping, Ernst &
+// Greiner 2007); each slab becomes one REFERENCE whose box bounds the clipped triangle.  All references of a triangle
+// carry the same 48 B triangle record, so hits do not change (equal t resolves to the lower primitive id).
+constexpr float kSplitGain = 0.5f;  // k = floor(gain * box half-area / (2 * triangle area)), >= 2 to split
+struct SplitPlan {
+  int k, axis;
+};
+RTF_HD SplitPlan split_plan(float3 a, float3 b, float3 c, int max_split) {
+  SplitPlan sp;
+  sp.k = 1;
+  const float3 lo = min3(min3(a, b), c), hi = max3(max3(a, b), c);
+  const float3 e = hi - lo;
+  sp.axis = (e.x >= e.y && e.x >= e.z) ? 0 : (e.y >= e.z ? 1 : 2);
+  if (max_split <= 1) return sp;
+  const float3 ab = b - a, ac = c - a;
+  const float3 n = f3(ab.y * ac.z - ab.z * ac.y, ab.z * ac.x - ab.x * ac.z, ab.x * ac.y - ab.y * ac.x);
+  const float area2 = sqrtf((n.x * n.x + n.y * n.y) + n.z * n.z);
+  const float ha = (e.x * e.y + e.y * e.z) + e.z * e.x;
+  if (!(area2 > 0.0f) || !(ha < INFINITY)) return sp;
+  const float r = (ha / area2) * kSplitGain;
+  if (!(r >= 2.0f)) return sp;
+  sp.k = r >= (float)max_split ? max_split : (int)r;
+  return sp;
+}
+// Box of triangle (a,b,c) clipped to slab j of k along `axis`.  Plane j = lo + j*(ext/k): the same float closes slab
+// j-1 and opens slab j.  Clipped edge points are rounded, so the other two axes get 2^-21 of padding, clamped to the
+// triangle's own box.
+RTF_HD Box3 split_slab_box(float3 a, float3 b, float3 c, int axis, int k, int j) {
+  const float A[3][3] = {{a.x, a.y, a.z}, {b.x, b.y, b.z}, {c.x, c.y, c.z}};
+  float lo[3], hi[3];
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    lo[d] = fminf(fminf(A[0][d], A[1][d]), A[2][d]);
+    hi[d] = fmaxf(fmaxf(A[0][d], A[1][d]), A[2][d]);
+  }
+  Box3 out;
+  if (k <= 1) {
+    out.lo = f3(lo[0], lo[1], lo[2]), out.hi = f3(hi[0], hi[1], hi[2]);
+    return out;
+  }
+  const float lo_a = axis == 0 ? lo[0] : (axis == 1 ? lo[1] : lo[2]);
+  const float hi_a = axis == 0 ? hi[0] : (axis == 1 ? hi[1] : hi[2]);
+  const float w = (hi_a - lo_a) / (float)k;
+  const float x0 = j == 0 ? lo_a : fminf(lo_a + (float)j * w, hi_a);
+  const float x1 = j == k - 1 ? hi_a : fminf(lo_a + (float)(j + 1) * w, hi_a);
+  float blo[3] = {INFINITY, INFINITY, INFINITY}, bhi[3] = {-INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+  for (int v = 0; v < 3; v++) {
+    const float va = axis == 0 ? A[v][0] : (axis == 1 ? A[v][1] : A[v][2]);
+    if (va >= x0 && va <= x1) {
+#pragma unroll
+      for (int d = 0; d < 3; d++) blo[d] = fminf(blo[d], A[v][d]), bhi[d] = fmaxf(bhi[d], A[v][d]);
+    }
+  }
+#pragma unroll
+  for (int ed = 0; ed < 3; ed++) {
+    float P[3], Q[3];
+#pragma unroll
+    for (int d = 0; d < 3; d++) P[d] = A[ed][d], Q[d] = A[(ed + 1) % 3][d];
+    float pa = axis == 0 ? P[0] : (axis == 1 ? P[1] : P[2]);
+    float qa = axis == 0 ? Q[0] : (axis == 1 ? Q[1] : Q[2]);
+    if (pa > qa) {
+#pragma unroll
+      for (int d = 0; d < 3; d++) {
+        const float t = P[d];
+        P[d] = Q[d], Q[d] = t;
+      }
+      const float t = pa;
+      pa = qa, qa = t;
+    }
+#pragma unroll
+    for (int s = 0; s < 2; s++) {
+      const float xp = s ? x1 : x0;
+      if (pa < xp && xp < qa) {
+        const float t = (xp - pa) / (qa - pa);
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+          const float v = fmaf(Q[d] - P[d], t, P[d]);
+          blo[d] = fminf(blo[d], v), bhi[d] = fmaxf(bhi[d], v);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    if (d == axis) {
+      blo[d] = x0, bhi[d] = x1;
+    } else {
+      const float pad = fmaxf(fabsf(lo[d]), fabsf(hi[d])) * 4.76837158203125e-07f;  // 2^-21
+      blo[d] = fmaxf(blo[d] - pad, lo[d]);
+      bhi[d] = fminf(bhi[d] + pad, hi[d]);
+      if (!(blo[d] <= bhi[d])) blo[d] = lo[d], bhi[d] = hi[d];
+    }
+  }
+  out.lo = f3(blo[0], blo[1], blo[2]), out.hi = f3(bhi[0], bhi[1], bhi[2]);
+  return out;
+}
+
 }  // namespace rtf

@@ -89,6 +89,7 @@ struct Instance {
 struct BuildArrays {
   DevBuf morton, sorted_keys, sorted_ids, children, parent, range, boxes, flags, scene_bounds;
   DevBuf keys_alt, ids_alt, cub_tmp, level_a, level_b, cnt_int, cnt_tri, scan_int, scan_tri, stash;
+  DevBuf ref_cnt, ref_first, ref_tri, ref_box, scan_state;  // triangle references (pre-splitting)
 };
 
 struct Workspace {  // wavefront queues + path state, sized for `capacity` paths
@@ -126,6 +127,8 @@ struct rtf_ctx {
   int morton_bits = 63;
   int depth = 0;
   uint32_t n_tris = 0, n_nodes = 0;
+  uint32_t n_refs = 0;  // triangle references in the BVH (>= n_tris when long triangles are pre-split)
+  int presplit = 8;     // option "presplit": most references one triangle may be cut into (1 = off)
   rtf::DevBuf d_pos9, d_nrm9, d_tri_inst, d_nodes, d_tris48, d_insts, d_mats, d_inst_alpha;
   rtf::BuildArrays ba;
   rtf::Workspace ws;

@@ -169,13 +169,15 @@ class RayTracer:
 
     commit = build_ias
 
-    def load_scene(self, desc, morton_bits=63):
+    def load_scene(self, desc, morton_bits=63, presplit=None):
         for gh, (v, t) in desc.geometries.items():
             self.set_geometry(gh, v, t)
         for mh, m in desc.materials.items():
             self.set_material(mh, m)
         for ih, (g, m, x, comp) in desc.instances.items():
             self.set_instance(ih, g, m, x, comp)
+        if presplit is not None:
+            self.set_option("presplit", presplit)
         self.build_ias(morton_bits)
 
     @property

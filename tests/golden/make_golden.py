@@ -79,12 +79,12 @@ def main():
         json.dump(dict(source="reference LinearCongruenceGenerator.hpp via oracle/_ref/liblcg_ref.so", kat=kat), f, indent=1)
 
     c = small_cases()
-    osc = orc.OracleScene(c["soup"], 63)
+    osc = orc.OracleScene(c["soup"], 63, presplit=1)
     hits, nv, tv = osc.trace(c["rays"], counts=True)
     morton = osc.debug(S.DBG_MORTON)
     order = osc.debug(S.DBG_SORTED_IDS)
-    osc30 = orc.OracleScene(c["soup"], 30)
-    ill = orc.OracleScene(c["illum_scene"], 63)
+    osc30 = orc.OracleScene(c["soup"], 30, presplit=1)
+    ill = orc.OracleScene(c["illum_scene"], 63, presplit=1)
     irr, st = ill.illum_mesh(c["env"], c["rp"], seed=0x5EED, push=1e-3)
     t, prim, inst, _ = ill.scan_grid(c["grid"])
     cp = camera_props()

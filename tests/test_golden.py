@@ -11,14 +11,18 @@ def test_oracle_reproduces_golden(orc, S):
     from tests.golden.make_golden import camera_props, small_cases
     g = np.load(os.path.join(GOLDEN, "oracle_small.npz"))
     c = small_cases()
-    osc = orc.OracleScene(c["soup"], 63)
+    osc = orc.OracleScene(c["soup"], 63, presplit=1)
     hits, nv, tv = osc.trace(c["rays"], counts=True)
     assert_bit_equal(hits.view(np.uint32).reshape(-1, 4), g["hits"], "hits")
     assert np.array_equal(nv, g["node_visits"]) and np.array_equal(tv, g["tri_visits"])
     assert np.array_equal(osc.debug(S.DBG_MORTON), g["morton63"])
     assert np.array_equal(osc.debug(S.DBG_SORTED_IDS), g["order63"])
     assert [osc.n_nodes, osc.depth] == g["n_nodes"].tolist()
-    o30 = orc.OracleScene(c["soup"], 30)
+    # pre-split references change the BVH, never the hits: the fixtures were made without splitting
+    split = orc.OracleScene(c["soup"], 63, presplit=8)
+    assert len(split.debug(S.DBG_REF_TRI)) > split.n_tris
+    assert_bit_equal(split.trace(c["rays"]).view(np.uint32).reshape(-1, 4), g["hits"], "hits (presplit 8)")
+    o30 = orc.OracleScene(c["soup"], 30, presplit=1)
     assert np.array_equal(o30.debug(S.DBG_MORTON), g["morton30"]) and np.array_equal(o30.debug(S.DBG_SORTED_IDS), g["order30"])
     ill = orc.OracleScene(c["illum_scene"], 63)
     irr, st = ill.illum_mesh(c["env"], c["rp"], seed=0x5EED, push=1e-3)

@@ -11,7 +11,8 @@ pytestmark = pytest.mark.gpu
 def _compare_all(rt, osc, S):
     assert rt.triangle_count == osc.n_tris
     for what, name in [(S.DBG_FLAT_POS, "flat pos"), (S.DBG_FLAT_NRM, "flat nrm"), (S.DBG_FLAT_INST, "flat inst"),
-                       (S.DBG_SCENE_BOUNDS, "scene bounds"), (S.DBG_MORTON, "morton"), (S.DBG_SORTED_IDS, "sorted ids"),
+                       (S.DBG_SCENE_BOUNDS, "scene bounds"), (S.DBG_REF_TRI, "reference triangles"),
+                       (S.DBG_REF_BOX, "reference boxes"), (S.DBG_MORTON, "morton"), (S.DBG_SORTED_IDS, "sorted ids"),
                        (S.DBG_BIN_CHILDREN, "children"), (S.DBG_BIN_PARENT, "parent"), (S.DBG_BIN_BOXES, "boxes"),
                        (S.DBG_WIDE_NODES, "wide nodes"), (S.DBG_WIDE_TRIS, "wide tris")]:
         assert_bit_equal(rt.debug(what), osc.debug(what), name)
@@ -19,10 +20,11 @@ def _compare_all(rt, osc, S):
 
 @pytest.mark.parametrize("n,bits", [(1, 63), (2, 63), (3, 30), (4, 63), (5, 30), (9, 63), (100, 30), (257, 63),
                                     (5000, 63), (5000, 30), (100000, 63)])
-def test_soup_build_bit_exact(rt, orc, S, scenes, n, bits):
+@pytest.mark.parametrize("presplit", [1, 8])
+def test_soup_build_bit_exact(rt, orc, S, scenes, n, bits, presplit):
     sd = scenes.random_soup(n, seed=n, size=0.08 if n < 50000 else 0.02)
-    rt.load_scene(sd, bits)
-    _compare_all(rt, orc.OracleScene(sd, bits), S)
+    rt.load_scene(sd, bits, presplit=presplit)
+    _compare_all(rt, orc.OracleScene(sd, bits, presplit=presplit), S)
 
 
 def test_duplicates_and_degenerates_bit_exact(rt, orc, S, scenes):
@@ -36,12 +38,16 @@ def test_duplicates_and_degenerates_bit_exact(rt, orc, S, scenes):
         _compare_all(rt, orc.OracleScene(sd, bits), S)
 
 
-@pytest.mark.parametrize("bits", [30, 63])
-def test_sorghum_c1_build_bit_exact(rt, orc, S, scenes, bits):
+@pytest.mark.parametrize("bits,presplit", [(30, None), (63, None), (63, 1), (63, 3), (63, 32)])
+def test_sorghum_c1_build_bit_exact(rt, orc, S, scenes, bits, presplit):
+    """Sliver-heavy scene: the pre-split references (count, order, clipped boxes) and everything built on them."""
     sd = scenes.sorghum_scene(1)
-    rt.load_scene(sd, bits)
+    rt.load_scene(sd, bits, presplit=presplit)
     assert rt.triangle_count == 20002
-    _compare_all(rt, orc.OracleScene(sd, bits), S)
+    osc = orc.OracleScene(sd, bits, presplit=S.DEFAULT_PRESPLIT if presplit is None else presplit)
+    n_ref = len(rt.debug(S.DBG_REF_TRI))
+    assert n_ref == 20002 if presplit == 1 else n_ref > 2 * 20002
+    _compare_all(rt, osc, S)
     tm = rt.build_timings()
     assert tm["total"] > 0
 

@@ -13,11 +13,13 @@ def test_golden_hits(rt, S):
     from tests.golden.make_golden import small_cases
     g = np.load(os.path.join(GOLDEN, "oracle_small.npz"))
     c = small_cases()
-    rt.load_scene(c["soup"], 63)
+    rt.load_scene(c["soup"], 63, presplit=1)  # the fixture's visit counts belong to the unsplit BVH
     hits, nv, tv = rt.trace_closest(c["rays"], counts=True)
     assert_bit_equal(hits.view(np.uint32).reshape(-1, 4), g["hits"], "hits vs golden")
     assert np.array_equal(nv, g["node_visits"]) and np.array_equal(tv, g["tri_visits"])
     assert_bit_equal(rt.trace_closest(c["rays"]), hits, "stats-free kernel")
+    rt.load_scene(c["soup"], 63, presplit=8)  # pre-split references change the BVH, never the hits
+    assert_bit_equal(rt.trace_closest(c["rays"]).view(np.uint32).reshape(-1, 4), g["hits"], "hits vs golden (presplit 8)")
 
 
 def test_oracle_bvh_uploaded(rt, orc, S, scenes):

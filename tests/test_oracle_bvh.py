@@ -7,8 +7,34 @@ import pytest
 from .conftest import assert_bit_equal
 
 
+def _check_refs(osc, S):
+    """Triangle references: every triangle owns >= 1 consecutive references whose boxes tile it."""
+    ref_tri = osc.debug(S.DBG_REF_TRI)
+    ref_box = osc.debug(S.DBG_REF_BOX).reshape(-1, 6)
+    pos = osc.debug(S.DBG_FLAT_POS).reshape(-1, 3, 3).astype(np.float64)
+    assert np.all(np.diff(ref_tri.astype(np.int64)) >= 0) and set(ref_tri.tolist()) == set(range(osc.n_tris))
+    tlo, thi = pos.min(1), pos.max(1)
+    assert np.all(ref_box[:, :3] >= tlo[ref_tri]) and np.all(ref_box[:, 3:] <= thi[ref_tri])
+    assert np.all(ref_box[:, :3] <= ref_box[:, 3:])
+    # random points of each triangle lie in at least one of its reference boxes
+    rng = np.random.default_rng(1)
+    first = np.searchsorted(ref_tri, np.arange(osc.n_tris))
+    last = np.searchsorted(ref_tri, np.arange(osc.n_tris), side="right")
+    for t in rng.integers(0, osc.n_tris, size=min(osc.n_tris, 400)):
+        a, b = rng.random(24), rng.random(24)
+        flip = a + b > 1
+        a[flip], b[flip] = 1 - a[flip], 1 - b[flip]
+        pts = (1 - a - b)[:, None] * pos[t, 0] + a[:, None] * pos[t, 1] + b[:, None] * pos[t, 2]
+        bx = ref_box[first[t]:last[t]].astype(np.float64)
+        tol = 1e-6 * np.maximum(1.0, np.abs(pts).max())
+        inside = np.all(pts[:, None, :] >= bx[None, :, :3] - tol, axis=2) & np.all(pts[:, None, :] <= bx[None, :, 3:] + tol, axis=2)
+        assert inside.any(axis=1).all(), f"triangle {t}: point outside all {len(bx)} reference boxes"
+    return ref_tri, ref_box
+
+
 def _check_tree(osc, S):
-    n = osc.n_tris
+    ref_tri, ref_box = _check_refs(osc, S)
+    n = len(ref_tri)
     morton, order = osc.debug(S.DBG_MORTON), osc.debug(S.DBG_SORTED_IDS)
     keys = morton[order]
     assert sorted(order.tolist()) == list(range(n))
@@ -30,7 +56,7 @@ def _check_tree(osc, S):
                 assert np.all(boxes[idx, :3] >= boxes[i, :3]) and np.all(boxes[idx, 3:] <= boxes[i, 3:])
         assert seen[0] == 0 and np.all(seen[1:] == 1)
     nodes, tris = osc.debug(S.DBG_WIDE_NODES), osc.debug(S.DBG_WIDE_TRIS)
-    assert sorted(tris["prim"].tolist()) == list(range(n))  # every triangle exactly once
+    assert sorted(tris["prim"].tolist()) == ref_tri.tolist()  # every reference exactly once
     pos = osc.debug(S.DBG_FLAT_POS).reshape(-1, 3, 3)
     assert_bit_equal(tris["v0"], pos[tris["prim"], 0], "tri v0")
     # quantised child boxes contain the triangles they lead to (leaf slots checked directly)
@@ -44,19 +70,38 @@ def _check_tree(osc, S):
             t0 = int(nd["tri_base"]) + (meta & 0x1f)
             lo = nd["p"] + nd["qlo"][:, s].astype(np.float32) * scale
             hi = nd["p"] + nd["qhi"][:, s].astype(np.float32) * scale
-            for t in tris[t0:t0 + cnt]:
-                v = np.stack([t["v0"], t["v1"], t["v2"]])
-                assert np.all(v.min(0) >= lo) and np.all(v.max(0) <= hi)
+            for t in tris[t0:t0 + cnt]:  # the slot holds (at least) one reference box of each of its triangles
+                rb = ref_box[ref_tri == t["prim"]]
+                assert (np.all(rb[:, :3] >= lo, axis=1) & np.all(rb[:, 3:] <= hi, axis=1)).any()
     # child_base / imask consistency: internal children are contiguous, BFS order
     n_int = sum(bin(int(nd["imask"])).count("1") for nd in nodes)
     assert n_int == len(nodes) - 1
 
 
 @pytest.mark.parametrize("n,bits", [(1, 63), (2, 63), (3, 30), (4, 63), (9, 63), (257, 30), (1500, 63)])
-def test_tree_invariants(orc, S, scenes, n, bits):
-    osc = orc.OracleScene(scenes.random_soup(n, seed=n), bits)
+@pytest.mark.parametrize("presplit", [1, 8])
+def test_tree_invariants(orc, S, scenes, n, bits, presplit):
+    osc = orc.OracleScene(scenes.random_soup(n, seed=n), bits, presplit=presplit)
     assert osc.n_tris == n
+    assert (len(osc.debug(S.DBG_REF_TRI)) == n) if presplit == 1 else (len(osc.debug(S.DBG_REF_TRI)) >= n)
     _check_tree(osc, S)
+
+
+def test_presplit_cuts_slivers_and_keeps_hits(orc, S, scenes):
+    """Sorghum leaves are diagonal slivers: pre-splitting multiplies their references, divides the triangle tests per
+    ray, and leaves every hit bit-identical (to the unsplit BVH and to brute force)."""
+    sd = scenes.sorghum_scene(1)
+    plain, split = orc.OracleScene(sd, 63, presplit=1), orc.OracleScene(sd, 63, presplit=8)
+    _check_refs(split, S)
+    n_ref = len(split.debug(S.DBG_REF_TRI))
+    assert 2 * plain.n_tris < n_ref <= 8 * plain.n_tris
+    lo, hi = scenes.scene_bounds(sd)
+    rays = scenes.incoherent_rays(20000, lo, hi, seed=5)
+    h0, _, tv0 = plain.trace(rays, counts=True)
+    h1, _, tv1 = split.trace(rays, counts=True)
+    assert_bit_equal(h0, h1, "hits with and without pre-splitting")
+    assert_bit_equal(h1[:2000], split.trace_brute(rays[:2000]), "hits vs brute force")
+    assert tv1.mean() < 0.8 * tv0.mean()
 
 
 def test_duplicate_triangles_and_degenerates(orc, S, scenes):

@@ -16,6 +16,7 @@ def main():
     ap.add_argument("--tris", type=int, default=0)
     ap.add_argument("--batch-log2", type=int, default=0)
     ap.add_argument("--reps", type=int, default=2)
+    ap.add_argument("--oracle-bvh", type=int, default=0, help="build the BVH with the CPU oracle and upload it (experiments)")
     args = ap.parse_args()
     import torch
 
@@ -29,6 +30,13 @@ def main():
         rt.set_option("batch_paths", 1 << args.batch_log2)
     sd = scenes.sorghum_scene(args.plants)
     rt.load_scene(sd, 63)
+    if args.oracle_bvh:
+        from oracle import pyoracle as _orc
+        from raytracerfacility_b200 import structs as _S
+        _o = _orc.OracleScene(sd, 63)
+        _nodes, _tris = _o.debug(_S.DBG_WIDE_NODES), _o.debug(_S.DBG_WIDE_TRIS)
+        print(f"oracle BVH: {len(_nodes)} nodes, {len(_tris)} triangle refs, depth {_o.depth}", flush=True)
+        rt.debug_upload_bvh(_nodes, _tris, _o.depth)
     n = args.tris or rt.triangle_count
     env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=4, samples=args.samples)
     acc = torch.zeros(rt.triangle_count * 6, dtype=torch.float32, device=dev)

@@ -18,6 +18,7 @@ def main():
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--check", type=int, default=1 << 17)
     ap.add_argument("--sort", type=int, default=0, help="sort the rays by (octant, origin cell of 2^SORT per axis) first")
+    ap.add_argument("--oracle-bvh", type=int, default=0, help="build the BVH with the CPU oracle and upload it (experiments)")
     args = ap.parse_args()
     import torch
 
@@ -29,6 +30,13 @@ def main():
     rt.set_stream(stream.cuda_stream)
     sd = scenes.sorghum_scene(args.plants)
     rt.load_scene(sd, 63)
+    if args.oracle_bvh:
+        from oracle import pyoracle as _orc
+        from raytracerfacility_b200 import structs as _S
+        _o = _orc.OracleScene(sd, 63)
+        _nodes, _tris = _o.debug(_S.DBG_WIDE_NODES), _o.debug(_S.DBG_WIDE_TRIS)
+        print(f"oracle BVH: {len(_nodes)} nodes, {len(_tris)} triangle refs, depth {_o.depth}", flush=True)
+        rt.debug_upload_bvh(_nodes, _tris, _o.depth)
     lo, hi = scenes.scene_bounds(sd)
     n = 1 << args.log2_rays
     rays = scenes.incoherent_rays_torch(n, lo, hi, seed=3, device=dev)
