@@ -540,12 +540,16 @@ static inline Hit trace(const BVH& bvh, const Ray& ray, TraceStats* stats = null
       const uint32_t rel = (uint32_t)__builtin_popcount(hits & ~(0xffffffffu << slot));
       const Node80& nd = bvh.nodes[cur.base + rel];
       if (stats) stats->nodes++;
+      // Plane distance t = q*s + o with the byte q turned into the float 1 + q*2^-15 (one byte-permute on the GPU,
+      // no int->float conversion): t = (1 + q*2^-15) * (s*2^15) + (o - s*2^15).  Near planes are pulled in and far planes
+      // pushed out by 2^-22 of the operands that cancel, which bounds the rounding error (see rtf_trace.cuh).
       float sc[3], oo[3], oof[3];
       for (int a = 0; a < 3; a++) {
-        sc[a] = u2f((uint32_t)nd.e[a] << 23) * idir[a];
-        oo[a] = (nd.p[a] - org[a]) * idir[a];
-        // far-plane slack relative to the operands that cancel in q*s + o (see rtf_trace.cuh)
-        oof[a] = fmaf(fmaf(fabsf(sc[a]), 256.0f, fabsf(oo[a])), FAR_SLACK, oo[a]);
+        sc[a] = (u2f((uint32_t)nd.e[a] << 23) * idir[a]) * 32768.0f;
+        const float o = (nd.p[a] - org[a]) * idir[a];
+        const float m = fabsf(o) + fabsf(sc[a]);
+        oo[a] = fmaf(m, -FAR_SLACK, o) - sc[a];
+        oof[a] = fmaf(m, FAR_SLACK, o) - sc[a];
       }
       const float best_s = best.t * SLACK;
       uint32_t hitmask = 0;
@@ -554,8 +558,8 @@ static inline Hit trace(const BVH& bvh, const Ray& ray, TraceStats* stats = null
         if (meta == 0) continue;
         float tn[3], tf[3];
         for (int a = 0; a < 3; a++) {
-          const float qn = (float)(neg[a] ? nd.qhi[a][s] : nd.qlo[a][s]);
-          const float qf = (float)(neg[a] ? nd.qlo[a][s] : nd.qhi[a][s]);
+          const float qn = u2f(0x3F800000u | ((uint32_t)(neg[a] ? nd.qhi[a][s] : nd.qlo[a][s]) << 8));
+          const float qf = u2f(0x3F800000u | ((uint32_t)(neg[a] ? nd.qlo[a][s] : nd.qhi[a][s]) << 8));
           tn[a] = fmaf(qn, sc[a], oo[a]);
           tf[a] = fmaf(qf, sc[a], oof[a]);
         }

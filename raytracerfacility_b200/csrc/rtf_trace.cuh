@@ -35,7 +35,7 @@ struct HitRec {
 constexpr int kSmemStack = 8;    // entries per thread in shared memory
 constexpr int kLocalStack = 56;  // spill entries in local memory (kSmemStack + kLocalStack = kMaxStackDepth)
 constexpr float kBoxSlack = 1.00000095367431640625f;  // 1 + 2^-20 on the current best t
-constexpr float kFarSlack = 2.384185791015625e-07f;   // 2^-22 of the slab operands, added to the far planes
+constexpr float kFarSlack = 2.384185791015625e-07f;   // 2^-22 of the slab operands: near planes pulled in, far pushed out
 constexpr int kTraceBlock = 128;
 constexpr int kTraceWarps = kTraceBlock / 32;
 constexpr int kRawTileBytes = 1024;  // 32 rays x 32 B
@@ -49,16 +49,17 @@ RTF_D float safe_dir(float d) {
   return fabsf(d) < ooeps ? copysignf(ooeps, d) : d;
 }
 RTF_D uint32_t extract_byte(uint32_t w, int j) { return (w >> (8 * j)) & 0xffu; }
-// float(byte j of w), exact.  PRMT builds 0x4B0000bb = 2^23 + b, one FADD removes the bias: both run on the
-// full-rate ALU/FMA pipes, whereas I2F.U8 is a quarter-rate XU instruction (48 of them per node made XU the
-// busiest pipe of the first version, profiles/r1_trace_baseline.md).
-RTF_D float byte_to_float(uint32_t w, int j, uint32_t magic /* 0x4B000000, kept in a register */) {
-  return __uint_as_float(__byte_perm(w, magic, 0x7540u + (uint32_t)j)) - 8388608.0f;
+// Byte j of w as the float 1 + b*2^-15 (bits 0x3F80bb00), exact, ONE PRMT on the full-rate ALU pipe.  The plane
+// distance q*s + o is evaluated as (1 + q*2^-15) * (s*2^15) + (o - s*2^15): the bias is folded into the per-node
+// constants, so a child costs 6 PRMT + 6 FFMA.  (History: I2F.U8 is a quarter-rate XU instruction — 48 per node made
+// XU the busiest pipe of the first version; PRMT to 2^23 + b needed an FADD per byte to remove the bias.)
+RTF_D float byte_to_float(uint32_t w, int j, uint32_t magic /* 0x3F800000, kept in a register */) {
+  return __uint_as_float(__byte_perm(w, magic, 0x7604u + ((uint32_t)j << 4)));
 }
 // The bias constant must stay in ONE register so that the selector becomes PRMT's immediate; given a literal, ptxas
 // encodes the constant as the immediate and re-materialises the selector with a MOV per PRMT (48 per node).  It is
 // therefore derived from a run-time value the compiler cannot fold (n < 2^31 always).
-RTF_D uint32_t prmt_magic(uint32_t n) { return 0x4B000000u | (n >> 31); }
+RTF_D uint32_t prmt_magic(uint32_t n) { return 0x3F800000u | (n >> 31); }
 
 // ---- TMA 1-D bulk copy + mbarrier (PTX; SASS: UBLKCP / SYNCS) -------------------------------------------
 RTF_D uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -241,18 +242,21 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
         const uint4* np = nodes + (size_t)(cur.x + rel) * 5;
         const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
         if (STATS) nvis++;
-        const float sx = __uint_as_float((n0.w & 0xffu) << 23) * idx;
-        const float sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idy;
-        const float sz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * idz;
-        const float ox = (__uint_as_float(n0.x) - o.x) * idx;
-        const float oy = (__uint_as_float(n0.y) - o.y) * idy;
-        const float oz = (__uint_as_float(n0.z) - o.z) * idz;
-        // far planes get a slack relative to the magnitude of the operands that cancel in q*s + o (2^-22 of
-        // |o| + 256|s|): this is the rounding-error bound of the slab arithmetic, and it keeps a ray that runs
-        // exactly inside a box face (axis-parallel, origin on the face) from being culled.
-        const float oxf = fmaf(fmaf(fabsf(sx), 256.0f, fabsf(ox)), kFarSlack, ox);
-        const float oyf = fmaf(fmaf(fabsf(sy), 256.0f, fabsf(oy)), kFarSlack, oy);
-        const float ozf = fmaf(fmaf(fabsf(sz), 256.0f, fabsf(oz)), kFarSlack, oz);
+        // s = 2^e / d scaled by 2^15, o = (p - origin) / d with the bias s*2^15 taken off (see byte_to_float)
+        const float sx = (__uint_as_float((n0.w & 0xffu) << 23) * idx) * 32768.0f;
+        const float sy = (__uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idy) * 32768.0f;
+        const float sz = (__uint_as_float(((n0.w >> 16) & 0xffu) << 23) * idz) * 32768.0f;
+        const float ox0 = (__uint_as_float(n0.x) - o.x) * idx;
+        const float oy0 = (__uint_as_float(n0.y) - o.y) * idy;
+        const float oz0 = (__uint_as_float(n0.z) - o.z) * idz;
+        // Near planes are pulled in and far planes pushed out by 2^-22 of the operands that cancel (|o| + 2^15|s|):
+        // this bounds the rounding error of the slab arithmetic (the box test is conservative, also against the
+        // current best t), and it keeps a ray that runs exactly inside a box face (axis-parallel, origin on the
+        // face) from being culled.  2^-22 * 2^15 |s| is 1/128 of a quantisation step.
+        const float mgx = fabsf(ox0) + fabsf(sx), mgy = fabsf(oy0) + fabsf(sy), mgz = fabsf(oz0) + fabsf(sz);
+        const float ox = fmaf(mgx, -kFarSlack, ox0) - sx, oxf = fmaf(mgx, kFarSlack, ox0) - sx;
+        const float oy = fmaf(mgy, -kFarSlack, oy0) - sy, oyf = fmaf(mgy, kFarSlack, oy0) - sy;
+        const float oz = fmaf(mgz, -kFarSlack, oz0) - sz, ozf = fmaf(mgz, kFarSlack, oz0) - sz;
         const float best_s = best.t * kBoxSlack;  // equal-t candidates behind a rounded box entry stay reachable
         uint32_t hitmask = 0;
 #pragma unroll
