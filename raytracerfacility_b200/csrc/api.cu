@@ -70,7 +70,8 @@ int rtf_destroy(rtf_ctx* ctx) {
   DevBuf* bufs[] = {&ctx->d_pos9, &ctx->d_nrm9, &ctx->d_tri_inst, &ctx->d_nodes, &ctx->d_tris48, &ctx->d_insts, &ctx->d_mats,
                     &ctx->d_inst_alpha, &ctx->d_stats, &ctx->ba.morton, &ctx->ba.sorted_keys, &ctx->ba.sorted_ids,
                     &ctx->ba.children, &ctx->ba.parent, &ctx->ba.range, &ctx->ba.boxes, &ctx->ba.flags,
-                    &ctx->ba.scene_bounds, &ctx->ba.keys_alt, &ctx->ba.ids_alt, &ctx->ba.cub_tmp, &ctx->ba.level_a,
+                    &ctx->ba.scene_bounds, &ctx->ba.keys_alt, &ctx->ba.ids_alt, &ctx->ba.ref_cnt, &ctx->ba.ref_first,
+                    &ctx->ba.ref_tri, &ctx->ba.ref_box, &ctx->ba.scan_state, &ctx->ba.sort_hist, &ctx->ba.sort_status, &ctx->ba.level_a,
                     &ctx->ba.level_b, &ctx->ba.cnt_int, &ctx->ba.cnt_tri, &ctx->ba.scan_int, &ctx->ba.scan_tri,
                     &ctx->ba.stash, &ctx->ws.ray_a[0], &ctx->ws.ray_a[1], &ctx->ws.ray_b[0], &ctx->ws.ray_b[1],
                     &ctx->ws.hits, &ctx->ws.counters, &ctx->ws.thr,

@@ -1,4 +1,5 @@
-// build.cu — device LBVH builder: flatten -> bounds -> Morton 30/63 -> radix sort -> Karras radix tree ->
+// build.cu — device LBVH builder: flatten -> bounds -> pre-split references -> Morton 30/63 -> radix sort
+// (rtf_sort.cuh) -> Karras radix tree ->
 // refit -> breadth-first greedy surface-area collapse to 8-wide -> quantised 80 B node encode.
 //
 // Replaces RayTracedGeometry::BuildGAS + RayTracer::BuildIAS of the reference
@@ -8,9 +9,10 @@
 //
 // Every stage is an integer or exactly-rounded float computation, so tests compare each array bit for
 // bit with the CPU oracle (Morton codes, sorted order, radix-tree links, boxes, wide nodes, triangles).
-#include <cub/device/device_radix_sort.cuh>
+#include <algorithm>
 
 #include "rtf_internal.h"
+#include "rtf_sort.cuh"
 
 namespace rtf {
 
@@ -217,7 +219,7 @@ __global__ void k_bounds_finish(const int* ob, float* fb) {
 
 // ---- 3. Morton codes ---------------------------------------------------------------------------
 __global__ void k_morton(const float* __restrict__ ref_box, uint32_t n, const float* __restrict__ fb, int bits,
-                         uint64_t* __restrict__ keys, uint32_t* __restrict__ ids) {
+                         uint64_t* __restrict__ keys) {
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n) return;
   const float3 lo = f3(fb[0], fb[1], fb[2]), hi = f3(fb[3], fb[4], fb[5]);
@@ -226,7 +228,6 @@ __global__ void k_morton(const float* __restrict__ ref_box, uint32_t n, const fl
   const Box3 b = ref_box_load(ref_box, t);
   const float3 c = (b.lo + b.hi) * 0.5f;
   keys[t] = morton_code(c, lo, inv, bits);
-  ids[t] = t;
 }
 
 // ---- 5. Karras 2012 radix tree -------------------------------------------------------------------
@@ -493,20 +494,14 @@ int build_bvh(rtf_ctx* ctx, int bits) {
   if ((rc = ba.flags.reserve(4 * (size_t)n))) return rc;
   LAUNCH(ctx, k_split_emit, div_up(nt, 256), 256, 0, ctx->d_pos9.as<float>(), nt, ctx->presplit, ba.ref_first.as<uint32_t>(),
          ba.ref_tri.as<uint32_t>(), ba.ref_box.as<float>());
-  LAUNCH(ctx, k_morton, div_up(n, 256), 256, 0, ba.ref_box.as<float>(), n, fb, bits, ba.morton.as<uint64_t>(),
-         ba.ids_alt.as<uint32_t>());
+  LAUNCH(ctx, k_morton, div_up(n, 256), 256, 0, ba.ref_box.as<float>(), n, fb, bits, ba.morton.as<uint64_t>());
   mark(ctx, 2);
-  {  // 4. stable LSD radix sort of (Morton, id) pairs.  cub::DeviceRadixSort for bring-up (library code; a
-     //    hand-written onesweep sort is the planned replacement).
-    size_t tmp = 0;
-    const int end_bit = bits == 30 ? 30 : 63;
-    cub::DeviceRadixSort::SortPairs(nullptr, tmp, ba.morton.as<uint64_t>(), ba.sorted_keys.as<uint64_t>(),
-                                    ba.ids_alt.as<uint32_t>(), ba.sorted_ids.as<uint32_t>(), (int)n, 0, end_bit, st);
-    if ((rc = ba.cub_tmp.reserve(tmp))) return rc;
-    RTF_CUDA(cub::DeviceRadixSort::SortPairs(ba.cub_tmp.p, tmp, ba.morton.as<uint64_t>(), ba.sorted_keys.as<uint64_t>(),
-                                             ba.ids_alt.as<uint32_t>(), ba.sorted_ids.as<uint32_t>(), (int)n, 0, end_bit, st));
-    ctx->launches += 8;
-  }
+  // 4. stable LSD radix sort of (Morton code, reference id) pairs, 8-bit digits (rtf_sort.cuh); ids start as 0..n-1
+  if ((rc = ba.keys_alt.reserve(8 * (size_t)n))) return rc;
+  if ((rc = radix_sort_pairs<uint64_t>(ctx, ba.morton.as<uint64_t>(), ba.sorted_keys.as<uint64_t>(), ba.keys_alt.as<uint64_t>(),
+                                       nullptr, ba.sorted_ids.as<uint32_t>(), ba.ids_alt.as<uint32_t>(), n, 0,
+                                       bits == 30 ? 30 : 63, ba.sort_hist, ba.sort_status)))
+    return rc;
   mark(ctx, 3);
   RTF_CUDA(cudaMemsetAsync(ba.parent.p, 0xff, 4 * (size_t)(2 * (size_t)n), st));
   if (ni > 0) {

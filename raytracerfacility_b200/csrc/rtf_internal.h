@@ -88,8 +88,9 @@ struct Instance {
 // Intermediate arrays of the builder kept for parity read-back (rtf_debug_read).
 struct BuildArrays {
   DevBuf morton, sorted_keys, sorted_ids, children, parent, range, boxes, flags, scene_bounds;
-  DevBuf keys_alt, ids_alt, cub_tmp, level_a, level_b, cnt_int, cnt_tri, scan_int, scan_tri, stash;
+  DevBuf keys_alt, ids_alt, level_a, level_b, cnt_int, cnt_tri, scan_int, scan_tri, stash;
   DevBuf ref_cnt, ref_first, ref_tri, ref_box, scan_state;  // triangle references (pre-splitting)
+  DevBuf sort_hist, sort_status;                            // radix sort scratch (rtf_sort.cuh)
 };
 
 struct Workspace {  // wavefront queues + path state, sized for `capacity` paths
