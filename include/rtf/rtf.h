@@ -89,8 +89,9 @@ typedef struct rtf_pc_sample {
 enum { RTF_ENV_SCENE = 0, RTF_ENV_SKYDOME = 1, RTF_ENV_SINGLE_LIGHT_SOURCE = 2 };
 
 /* EnvironmentProperties, RT.hpp:103-151.  Numeric fields keep the reference order; the
- * GL cube-map id + cudaTextureObject_t[6] become six optional device pointers to
- * float4 face images (cube map without GL: SURVEY §8 N2, not wired in this round). */
+ * GL cube-map id keeps its meaning "non-zero = sample the cube map" (Env.cuh:153-158); the six
+ * faces are linear-memory images registered with rtf_set_environment_map (no GL on this path);
+ * the cudaTextureObject_t[6] slot is kept for layout and ignored. */
 typedef struct rtf_env {
   int32_t lighting_type;
   float skylight_intensity;
@@ -99,7 +100,7 @@ typedef struct rtf_env {
   float gamma;
   float sun_direction[3];
   float color[3];
-  uint32_t environmental_map_id; /* must be 0 in this round */
+  uint32_t environmental_map_id; /* != 0: Scene lighting samples the cube map (rtf_set_environment_map) */
   uint64_t environmental_maps[6];
   struct {
     float earth_radius;
@@ -213,6 +214,76 @@ RTF_API int rtf_build_timings(rtf_ctx* ctx, float* ms_out, int n);
  * "presplit" = most references a long thin triangle may be cut into before the Morton sort
  * (default 8, 1 = off; applies at the next rtf_commit; hits do not depend on it). */
 RTF_API int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value);
+
+/* ---- images in linear memory ---------------------------------------------------------------
+ * Replace the GL texture ids of RayTracedMaterial (RT.hpp:254-263; bound by BindTexture,
+ * RT.cu:2233-2256) and the cube-map faces of EnvironmentProperties (RT.hpp:112-113; RT.cu:270-347).
+ * Sampling restates tex2D<float4> under the reference's descriptor (cudaAddressModeWrap,
+ * cudaFilterModeLinear, normalizedCoords, RT.cu:2246-2252) with full float weights (the texture
+ * unit keeps 8 fractional bits).  Texels: width*height float4, row-major, row 0 at v = 0.
+ * Changes take effect at the next rtf_commit. */
+RTF_API int rtf_set_texture(rtf_ctx* ctx, uint64_t handle, int width, int height, const float* rgba);
+RTF_API int rtf_remove_texture(rtf_ctx* ctx, uint64_t handle);
+/* RayTracedMaterial::m_albedoTexture / m_normalTexture / m_metallicTexture / m_roughnessTexture
+ * (RT.hpp:254-263; SurfaceMaterial::GetAlbedo/GetRoughness/GetMetallic/ApplyNormalTexture,
+ * RDD.hpp:248-281).  0 = none. */
+RTF_API int rtf_set_material_textures(rtf_ctx* ctx, uint64_t material_handle, uint64_t albedo, uint64_t normal,
+                                      uint64_t metallic, uint64_t roughness);
+/* Cube map of the Scene lighting type: six texture handles in the order +X -X +Y -Y +Z -Z
+ * (SampleCubeMap's faceIndex, RTU.cuh:54-80); NULL clears it. */
+RTF_API int rtf_set_environment_map(rtf_ctx* ctx, const uint64_t face_textures[6]);
+/* Test hooks: n bilinear samples of a texture (uv: 2 floats each -> rgba: 4 floats each); n
+ * evaluations of CalculateEnvironmentalLight (Env.cuh:147-175) for {position.xyz, direction.xyz}
+ * -> rgb.  Host buffers. */
+RTF_API int rtf_sample_texture(rtf_ctx* ctx, uint64_t handle, size_t n, const float* uv, float* rgba_out);
+RTF_API int rtf_sample_environment(rtf_ctx* ctx, const rtf_env* env, size_t n, const float* pos_dir6, float* rgb_out);
+
+/* ---- compressed BTF material (MLVQ), CompressedBTF.hpp / BTFBase.cuh:13-81 ------------------
+ * The 13 tables of CompressedBTF::ImportFromFolder (CompressedBTF.cpp:339-377) as host arrays,
+ * row-major, with the row/column counts the loader reads from each file's header. */
+typedef struct rtf_btf_desc {
+  int32_t use_cos_beta;   /* SharedCoordinates::m_useCosBeta */
+  int32_t num_beta, num_alpha, num_theta, num_phi;
+  int32_t code_btf_flag;  /* SharedCoordinates::m_codeBtfFlag (12th parameterisation int, CompressedBTF.cpp:197) */
+  int32_t hdr;            /* BTFBase::m_hdr / SharedCoordinates::m_hdrFlag */
+  float hdr_value, multiplier, tex_coord_multiplier, gamma; /* BTFBase.cuh:19-24 */
+  int32_t rows_offset, cols_offset;       /* PDF6D::m_rowsOffset / m_colsOffset */
+  int32_t pdf6_rows, pdf6_cols;           /* <mat>_PDF6Dslices.txt / _PDF6Dscale.txt */
+  int32_t n_pdf1d;                        /* all_PDF1Dslice.txt: n_pdf1d x num_beta floats */
+  int32_t n_colors, n_channels;           /* all_colors.txt */
+  int32_t n_index_slices;                 /* all_indexAB.txt: x num_beta ints */
+  int32_t n_pdf2d_color;                  /* all_PDF2Dcolours.txt: x num_alpha ints */
+  int32_t n_pdf2d_lum;                    /* all_PDF2Dslices.txt / all_PDF2Dscale.txt: x num_alpha */
+  int32_t n_pdf2d, pdf2d_slice_len;       /* all_PDF2Dindices.txt: n_pdf2d x 2 {luminance, colour} */
+  int32_t n_pdf3d;                        /* all_PDF3Dslices.txt / _PDF3Dscale.txt: x num_theta */
+  int32_t n_pdf4d;                        /* all_PDF4Dslices.txt / _PDF4Dscale.txt: x num_phi */
+  const int32_t* pdf6_slices;
+  const float* pdf6_scales;
+  const float* pdf1d_basis;
+  const float* colors;
+  const int32_t* index_ab;
+  const int32_t* pdf2d_colors;
+  const int32_t* pdf2d_slices;
+  const float* pdf2d_scales;
+  const int32_t* pdf2d_indices;
+  const float* pdf3d_scales;
+  const int32_t* pdf3d_slices;
+  const float* pdf4d_scales;
+  const int32_t* pdf4d_slices;
+} rtf_btf_desc;
+/* Validates every index table against the sizes (the reference only asserts) and uploads. */
+RTF_API int rtf_set_btf(rtf_ctx* ctx, uint64_t handle, const rtf_btf_desc* desc);
+/* CompressedBTF::ImportFromFolder (CompressedBTF.cpp:74-390): all_materialInfo.txt,
+ * <material>_materialInfo.txt and the 13 "rows cols min max" ASCII tables. */
+RTF_API int rtf_btf_import_folder(rtf_ctx* ctx, uint64_t handle, const char* folder);
+RTF_API int rtf_remove_btf(rtf_ctx* ctx, uint64_t handle);
+/* A material of type RTF_MAT_COMPRESSED_BTF shades with this table set (SBT::m_material ->
+ * SurfaceCompressedBTF, RT.cu:1888-1894). */
+RTF_API int rtf_set_material_btf(rtf_ctx* ctx, uint64_t material_handle, uint64_t btf_handle);
+/* Test hook = SurfaceCompressedBTF::GetValue (RDD.hpp:329-354) for n host-side queries:
+ * tex_coord 2, view_dir 3 (direction of the incoming ray), illum_dir 3, normal 3, tangent 3 -> rgb 3. */
+RTF_API int rtf_btf_eval(rtf_ctx* ctx, uint64_t btf_handle, size_t n, const float* tex_coord, const float* view_dir,
+                         const float* illum_dir, const float* normal, const float* tangent, float* rgb_out);
 
 /* ---- illumination: CudaModule::EstimateIlluminationRayTracing (CM.hpp:38-41, CM.cpp:39-50)
  *      -> RayTracer::EstimateIllumination (RT.cu:605-756) -> __raygen__IE (IE.cu:30-129) ---- */

@@ -324,3 +324,59 @@ ORC_API void orc_camera(Scene* s, const rtf_env* env, const rtf_ray_props* rp, c
     for (auto& x : per) stats->rays += x.rays, stats->nodes += x.nodes, stats->tris += x.tris, stats->paths += x.paths;
   }
 }
+
+// ---- textures, cube map, compressed BTF (oracle_btf.h) ----------------------------------------------------------
+ORC_API int orc_scene_add_texture(Scene* s, int w, int h, const float* rgba) {
+  Texture t;
+  t.w = w, t.h = h;
+  t.rgba.assign(rgba, rgba + 4 * (size_t)w * h);
+  s->textures.push_back(std::move(t));
+  return (int)s->textures.size() - 1;
+}
+ORC_API void orc_scene_set_material_textures(Scene* s, int mat, int albedo, int normal, int metallic, int roughness) {
+  if (s->mat_extra.size() < s->mats.size()) s->mat_extra.resize(s->mats.size());
+  MatExtra& mx = s->mat_extra[mat];
+  mx.tex[0] = albedo, mx.tex[1] = normal, mx.tex[2] = metallic, mx.tex[3] = roughness;
+}
+ORC_API void orc_scene_set_environment_map(Scene* s, const int* faces6) {
+  for (int k = 0; k < 6; k++) s->env_faces[k] = faces6 ? faces6[k] : -1;
+}
+ORC_API int orc_scene_add_btf(Scene* s, const rtf_btf_desc* d) {
+  s->btfs.emplace_back();
+  btf_assign(s->btfs.back(), *d);
+  return (int)s->btfs.size() - 1;
+}
+ORC_API void orc_scene_set_material_btf(Scene* s, int mat, int btf) {
+  if (s->mat_extra.size() < s->mats.size()) s->mat_extra.resize(s->mats.size());
+  s->mat_extra[mat].btf = btf;
+}
+ORC_API void orc_sample_texture(Scene* s, int tex, uint64_t n, const float* uv, float* rgba) {
+  for (uint64_t i = 0; i < n; i++) tex2d(s->textures[tex], uv[2 * i], uv[2 * i + 1], rgba + 4 * i);
+}
+ORC_API void orc_sample_environment(Scene* s, const rtf_env* env, uint64_t n, const float* pd6, float* rgb) {
+  for (uint64_t i = 0; i < n; i++) {
+    const float* q = pd6 + 6 * i;
+    V3 c = env_light(v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), *env, s);
+    rgb[3 * i] = c.x, rgb[3 * i + 1] = c.y, rgb[3 * i + 2] = c.z;
+  }
+}
+ORC_API void orc_btf_eval(Scene* s, int btf, uint64_t n, const float* tc, const float* view, const float* illum,
+                          const float* normal, const float* tangent, float* rgb, int nthreads) {
+  const BTF* b = &s->btfs[btf];
+  parallel_for(n, nthreads, [=](int, uint64_t b0, uint64_t e0) {
+    for (uint64_t i = b0; i < e0; i++) {
+      V3 c = btf_get_value(*b, tc[2 * i], tc[2 * i + 1], v3(view[3 * i], view[3 * i + 1], view[3 * i + 2]),
+                           v3(illum[3 * i], illum[3 * i + 1], illum[3 * i + 2]),
+                           v3(normal[3 * i], normal[3 * i + 1], normal[3 * i + 2]),
+                           v3(tangent[3 * i], tangent[3 * i + 1], tangent[3 * i + 2]));
+      rgb[3 * i] = c.x, rgb[3 * i + 1] = c.y, rgb[3 * i + 2] = c.z;
+    }
+  });
+}
+ORC_API void orc_btf_beta_angles(Scene* s, int btf, float* out) {
+  const BTF& b = s->btfs[btf];
+  for (size_t i = 0; i < b.beta_angles.size(); i++) out[i] = b.beta_angles[i];
+}
+ORC_API void orc_inverse_trig(int n, const float* y, const float* x, float* atan2_out, float* asin_out, float* acos_out) {
+  for (int i = 0; i < n; i++) atan2_out[i] = atan2p(y[i], x[i]), asin_out[i] = asinp(y[i]), acos_out[i] = acosp(y[i]);
+}

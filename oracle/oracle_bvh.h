@@ -499,7 +499,7 @@ struct TraceStats {
 
 // Optional per-candidate filter (the any-hit program, RF.cuh:5-23): return false to ignore the hit.
 struct NoFilter {
-  bool operator()(const Tri48&) const { return true; }
+  bool operator()(const Tri48&, const Hit&) const { return true; }
 };
 
 static inline float safe_dir(float d) {
@@ -583,7 +583,7 @@ static inline Hit trace(const BVH& bvh, const Ray& ray, TraceStats* stats = null
       const Tri48& tri = bvh.tris[tg.base + ti];
       if (stats) stats->tris++;
       Hit cand = best;
-      if (intersect_tri(ray, rp, tri, cand) && filter(tri)) {
+      if (intersect_tri(ray, rp, tri, cand) && filter(tri, cand)) {
         best = cand;
         if (any_hit) return best;
       }

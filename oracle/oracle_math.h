@@ -140,4 +140,38 @@ static inline void sincos2pi(float u, float* s, float* c) {
   *s = ss, *c = cc;
 }
 
+// ---- portable inverse trigonometry: only + - * / sqrt, identical on host and device ----------------
+// Stand in for acosf/asin/atan2 of the BTF angle code (RDD.hpp:307-313, SharedCoordinates.cuh:131-165).  atan on
+// [0,1] after Cephes' atanf: reduce above tan(pi/8) with (x-1)/(x+1), then an odd degree-9 polynomial (abs error
+// ~2e-7, i.e. the last place or two of libm, and reproducible).
+static inline float atan01(float a) {  // a in [0,1]
+  float off = 0.0f;
+  if (a > 0.4142135679721832275390625f) {
+    a = (a - 1.0f) / (a + 1.0f);
+    off = 0.785398185253143310546875f;
+  }
+  const float z = a * a;
+  float p = 8.05374449538e-2f;
+  p = p * z - 1.38776856032e-1f;
+  p = p * z + 1.99777106478e-1f;
+  p = p * z - 3.33329491539e-1f;
+  return off + (a + a * (z * p));
+}
+static inline float atan2p(float y, float x) {
+  if (y != y || x != x) return NAN;
+  const float ax = fabsf(x), ay = fabsf(y);
+  const float hi = ax > ay ? ax : ay, lo = ax > ay ? ay : ax;
+  float r = hi > 0.0f ? atan01(lo / hi) : 0.0f;
+  if (ay > ax) r = 1.57079637050628662109375f - r;
+  if (x < 0.0f) r = 3.1415927410125732421875f - r;
+  return y < 0.0f ? -r : r;
+}
+static inline float asinp(float v) { return atan2p(v, sqrtf((1.0f - v) * (1.0f + v))); }
+static inline float acosp(float v) { return atan2p(sqrtf((1.0f - v) * (1.0f + v)), v); }
+// sin / cos of an angle in radians through the 2*pi*u polynomial above
+static inline void sincos_rad(float a, float* s, float* c) { sincos2pi(a * 0.15915493667125701904296875f, s, c); }
+static inline float radiansf(float d) { return d * 0.01745329238474369049072265625f; }
+static inline float degreesf(float r) { return r * 57.295780181884765625f; }
+static inline float modf_glm(float x, float y) { return x - y * floorf(x / y); }  // glm::mod
+
 }  // namespace orc

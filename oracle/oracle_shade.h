@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "../include/rtf/rtf.h"
+#include "oracle_btf.h"
 #include "oracle_bvh.h"
 
 namespace orc {
@@ -35,9 +36,18 @@ struct Instance {
   uint32_t first_prim;
 };
 
+// RayTracedMaterial's texture ids (RT.hpp:254-263) and its BTF (RT.cu:1888-1894), as indices into the scene tables.
+struct MatExtra {
+  int tex[4] = {-1, -1, -1, -1};  // albedo, normal, metallic, roughness
+  int btf = -1;
+};
 struct Scene {
   std::vector<Geometry> geoms;
   std::vector<rtf_material> mats;
+  std::vector<MatExtra> mat_extra;  // parallel to mats (resized on demand)
+  std::vector<Texture> textures;
+  std::vector<BTF> btfs;
+  int env_faces[6] = {-1, -1, -1, -1, -1, -1};  // cube map of the Scene lighting type (+X -X +Y -Y +Z -Z)
   std::vector<Instance> insts;
   // flattened, commit order (global primitive id)
   std::vector<float> pos9, nrm9;
@@ -172,11 +182,20 @@ static inline V3 nishita_sky(V3 position, V3 dir, const rtf_env& env) {  // Env.
   }
   return ((sumR * betaR) * phaseR + (sumM * betaM) * phaseM) * 20.0f;
 }
-static inline V3 env_light(V3 position, V3 dir, const rtf_env& env) {  // Env.cuh:147-175
+static inline V3 env_light(V3 position, V3 dir, const rtf_env& env, const Scene* sc = nullptr) {  // Env.cuh:147-175
   V3 c = v3(1, 1, 1);
   V3 col = v3(env.color[0], env.color[1], env.color[2]);
   switch (env.lighting_type) {
-    case RTF_ENV_SCENE: c = col * env.skylight_intensity; break;  // cube map: not wired (N2)
+    case RTF_ENV_SCENE:
+      if (env.environmental_map_id != 0 && sc && sc->env_faces[0] >= 0) {
+        const Texture* faces[6];
+        for (int k = 0; k < 6; k++) faces[k] = &sc->textures[sc->env_faces[k]];
+        float t[4];
+        sample_cube_map(faces, dir, t);
+        col = v3(t[0], t[1], t[2]);
+      }
+      c = col * env.skylight_intensity;
+      break;
     case RTF_ENV_SKYDOME: c = nishita_sky(position, dir, env) * env.skylight_intensity; break;
     case RTF_ENV_SINGLE_LIGHT_SOURCE: c = col * env.skylight_intensity; break;
   }
@@ -230,17 +249,57 @@ static inline void full_hit_info(const Scene& sc, const Hit& h, V3 ray_dir, rtf_
   out.data[2] = pick->tangent_padding, out.data[3] = pick->tex_coord_padding[0];
 }
 
-// any-hit alpha test (RF.cuh:5-23): Default material only, alpha = 1 - transmission (RDD.hpp:250).
+// Interpolated vertex attributes of a hit (TriangularMesh::GetHitInfo, RDD.hpp:127-164; tangent through
+// SBT::GetHitInfo, RDD.hpp:379) for the materials that read them.
+struct HitAttrs {
+  float u, v;   // texture coordinate
+  V3 tangent;   // normalize(M * t)
+  V3 color;     // colour of the dominant-barycentric vertex
+};
+static inline HitAttrs hit_attrs(const Scene& sc, uint32_t prim, float bu, float bv, uint32_t inst) {
+  const Instance& in = sc.insts[inst];
+  const Geometry& g = sc.geoms[in.geom];
+  const uint32_t lt = prim - in.first_prim;
+  const rtf_vertex& vx = g.verts[g.tris[3 * lt]];
+  const rtf_vertex& vy = g.verts[g.tris[3 * lt + 1]];
+  const rtf_vertex& vz = g.verts[g.tris[3 * lt + 2]];
+  const float z = (1.0f - bu) - bv;
+  HitAttrs a;
+  V3 tg = (z * v3(vx.tangent[0], vx.tangent[1], vx.tangent[2]) + bu * v3(vy.tangent[0], vy.tangent[1], vy.tangent[2])) +
+          bv * v3(vz.tangent[0], vz.tangent[1], vz.tangent[2]);
+  a.tangent = normalize(mat4_mul_point(in.xform, tg, 0.0f));
+  a.u = (z * vx.tex_coord[0] + bu * vy.tex_coord[0]) + bv * vz.tex_coord[0];
+  a.v = (z * vx.tex_coord[1] + bu * vy.tex_coord[1]) + bv * vz.tex_coord[1];
+  const rtf_vertex* pick = (bu > z && bu > bv) ? &vx : (bv > z ? &vy : &vz);  // RDD.hpp:150-160 (as written)
+  a.color = v3(pick->color[0], pick->color[1], pick->color[2]);
+  return a;
+}
+static inline const MatExtra& mat_extra(const Scene& sc, uint32_t mat) {
+  static const MatExtra none;
+  return mat < sc.mat_extra.size() ? sc.mat_extra[mat] : none;
+}
+
+// any-hit alpha test (RF.cuh:5-23): Default material only; alpha = albedo texture's w, else 1 - transmission
+// (SurfaceMaterial::GetAlbedo, RDD.hpp:248-254).
 struct AlphaFilter {
   const Scene* sc;
   uint32_t seed;
   uint64_t unit;
   uint32_t bounce;
-  bool operator()(const Tri48& tri) const {
-    const rtf_material& m = sc->mats[sc->insts[tri.inst].mat];
+  bool operator()(const Tri48& tri, const Hit& cand) const {
+    const uint32_t mi = sc->insts[tri.inst].mat;
+    const rtf_material& m = sc->mats[mi];
     if (m.material_type != RTF_MAT_DEFAULT) return true;
     float alpha = 1.0f - m.transmission;
-    if (alpha >= 1.0f) return true;
+    const int at = mat_extra(*sc, mi).tex[0];
+    if (at >= 0) {
+      const HitAttrs a = hit_attrs(*sc, tri.prim, cand.u, cand.v, tri.inst);
+      float t[4];
+      tex2d(sc->textures[at], a.u, a.v, t);
+      alpha = t[3];
+    } else if (alpha >= 1.0f) {
+      return true;
+    }
     float r[4];
     path_rng(seed, STREAM_ALPHA, unit, bounce, tri.prim, r);
     return !(alpha <= r[0]);
@@ -253,8 +312,9 @@ struct PathResult {
   uint32_t rays;
 };
 
-// __closesthit__*_R -> ClosestHitFunc (RF.cuh:25-172, non-BTF branch), __miss__*_R -> MissFunc
-// (RF.cuh:260-272), unrolled.  `o,d,tmin` is the primary ray; returns radiance + first-hit records.
+// __closesthit__*_R -> ClosestHitFunc (RF.cuh:25-258: surface materials :44-172, compressed BTF :172-258),
+// __miss__*_R -> MissFunc (RF.cuh:260-272), unrolled.  `o,d,tmin` is the primary ray; returns radiance + first-hit
+// records.
 static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bounces, uint32_t seed, uint64_t unit,
                                     V3 o, V3 d, float tmin, TraceStats* stats) {
   PathResult pr;
@@ -263,40 +323,114 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
   pr.rays = 0;
   V3 T = v3(1, 1, 1), acc = v3(0, 0, 0);
   uint32_t hit_count = 0;
+  bool any_hit_enabled = true;  // BTF bounce rays run with OPTIX_RAY_FLAG_DISABLE_ANYHIT (RF.cuh:239)
   for (;;) {
     Ray ray{o, tmin, d, 1e20f};
-    AlphaFilter flt{&sc, seed, unit, hit_count};
-    Hit h = trace(sc.bvh, ray, stats, false, flt);
+    Hit h;
+    if (any_hit_enabled) {
+      AlphaFilter flt{&sc, seed, unit, hit_count};
+      h = trace(sc.bvh, ray, stats, false, flt);
+    } else {
+      h = trace(sc.bvh, ray, stats, false);
+    }
+    any_hit_enabled = true;
     pr.rays++;
     if (h.prim == 0xFFFFFFFFu) {
-      V3 L = env_light(o, d, env);
+      V3 L = env_light(o, d, env, &sc);
       acc = acc + T * L;
       if (hit_count == 0) pr.albedo = L;  // MissFunc: m_albedo = m_energy = env colour
       break;
     }
     hit_count++;
     SurfaceHit sh = surface_hit(sc, h, d);
-    const rtf_material& m = sc.mats[sc.insts[sh.inst].mat];
+    const uint32_t mi = sc.insts[sh.inst].mat;
+    const rtf_material& m = sc.mats[mi];
+    const MatExtra& mx = mat_extra(sc, mi);
+    const bool rich = m.material_type != RTF_MAT_DEFAULT || mx.tex[0] >= 0 || mx.tex[1] >= 0 || mx.tex[2] >= 0 || mx.tex[3] >= 0;
+    HitAttrs at{0.0f, 0.0f, v3(0, 0, 0), v3(0, 0, 0)};
+    if (rich) at = hit_attrs(sc, h.prim, h.u, h.v, sh.inst);
+    float r[4];
+    if (m.material_type == RTF_MAT_COMPRESSED_BTF) {  // RF.cuh:172-258
+      const BTF& btf = sc.btfs[mx.btf];
+      V3 btf_color = v3(0, 0, 0);  // the reference leaves it uninitialised past the bounce limit: 0 here
+      bool go_on = false;
+      if ((int)hit_count <= bounces) {
+        path_rng(seed, STREAM_PATH, unit, hit_count, 0, r);
+        if (env.lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE) {  // RF.cuh:180-218
+          V3 sun = v3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
+          V3 nd = sample_lobe(r[0], r[1], sun, 1.0f - env.light_size);
+          btf_color = btf_get_value(btf, at.u, at.v, d, nd, sh.normal, at.tangent);
+          V3 col = v3(env.color[0], env.color[1], env.color[2]);
+          acc = acc + T * ((col * env.ambient_light_intensity) * btf_color);
+          float ndl = dot(sh.normal, nd);
+          if (ndl > 0.0f) {
+            Ray sr{sh.position + sh.normal * 1e-3f, 1e-3f, nd, 1e20f};
+            Hit sh2 = trace(sc.bvh, sr, stats, true);
+            pr.rays++;
+            if (sh2.prim == 0xFFFFFFFFu) {
+              V3 L = env_light(sr.o, nd, env, &sc);
+              acc = acc + T * ((L * ndl) * btf_color);
+            }
+          }
+        } else {  // RF.cuh:219-246
+          V3 refl = reflect(d, sh.normal);
+          V3 nd = sample_lobe(r[0], r[1], refl, 0.0f);
+          btf_color = btf_get_value(btf, at.u, at.v, d, nd, sh.normal, at.tangent);
+          T = T * btf_color;
+          o = sh.position + sh.normal * 1e-3f, d = nd, tmin = 1e-3f;
+          any_hit_enabled = false;
+          go_on = true;
+        }
+      }
+      if (hit_count == 1) pr.normal = sh.normal, pr.albedo = btf_color, pr.position = sh.position, pr.first_hit = true;
+      if (go_on) continue;
+      break;
+    }
+    // ---- surface materials, RF.cuh:44-172 ----
+    V3 normal = sh.normal;
+    if (mx.tex[1] >= 0) {  // ApplyNormalTexture, RDD.hpp:268-281
+      float t[4];
+      tex2d(sc.textures[mx.tex[1]], at.u, at.v, t);
+      V3 B = cross(normal, at.tangent);
+      V3 tn = v3(t[0] * 2.0f - 1.0f, t[1] * 2.0f - 1.0f, t[2] * 2.0f - 1.0f);
+      normal = normalize((at.tangent * tn.x + B * tn.y) + normal * tn.z);
+    }
     float metallic = m.metallic, roughness = m.roughness;
+    if (mx.tex[2] >= 0) {
+      float t[4];
+      tex2d(sc.textures[mx.tex[2]], at.u, at.v, t);
+      metallic = t[0];
+    }
+    if (mx.tex[3] >= 0) {
+      float t[4];
+      tex2d(sc.textures[mx.tex[3]], at.u, at.v, t);
+      roughness = t[0];
+    }
     V3 albedo = v3(m.albedo_color[0], m.albedo_color[1], m.albedo_color[2]);
-    if (hit_count == 1) pr.normal = sh.normal, pr.albedo = albedo, pr.position = sh.position, pr.first_hit = true;
+    if (m.material_type != RTF_MAT_DEFAULT) {
+      albedo = at.color;  // VertexColor: hitInfo.m_color (RF.cuh:55-57)
+    } else if (mx.tex[0] >= 0) {
+      float t[4];
+      tex2d(sc.textures[mx.tex[0]], at.u, at.v, t);
+      albedo = v3(t[0], t[1], t[2]);
+    }
+    if (hit_count == 1) pr.normal = normal, pr.albedo = albedo, pr.position = sh.position, pr.first_hit = true;
     float f = 1.0f;
     if (metallic >= 0.0f) f = (metallic + 2) / (metallic + 1);
     V3 emis = m.emission * albedo;
-    float r[4];
     if (env.lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE) {  // RF.cuh:61-92
       path_rng(seed, STREAM_PATH, unit, hit_count, 0, r);
       V3 sun = v3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
       V3 nd = sample_lobe(r[0], r[1], sun, 1.0f - env.light_size);
       V3 col = v3(env.color[0], env.color[1], env.color[2]);
       acc = acc + T * ((col * env.ambient_light_intensity) * albedo);
-      float ndl = dot(sh.normal, nd);
+      float ndl = dot(normal, nd);
       if (ndl > 0.0f) {
         Ray sr{sh.position, 1e-3f, nd, 1e20f};
         Hit sh2 = trace(sc.bvh, sr, stats, true);
         pr.rays++;
         if (sh2.prim == 0xFFFFFFFFu) {
-          V3 L = env_light(sh.position, nd, env);
+          V3 L = env_light(sh.position, nd, env, &sc);
           acc = acc + T * ((L * ndl) * albedo);
         }
       }
@@ -304,9 +438,9 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
       break;
     } else if ((int)hit_count <= bounces) {  // RF.cuh:93-161 (BSSRDF branch off: subsurfaceFactor == 0 only)
       path_rng(seed, STREAM_PATH, unit, hit_count, 0, r);
-      V3 refl = reflect(d, sh.normal);
+      V3 refl = reflect(d, normal);
       V3 nd = sample_lobe(r[0], r[1], refl, metallic);
-      float k = clampf(fabsf(dot(sh.normal, nd)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
+      float k = clampf(fabsf(dot(normal, nd)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
       V3 wgt = ((1.0f - m.subsurface_factor) * albedo) * k;
       acc = acc + T * emis;
       T = T * wgt;

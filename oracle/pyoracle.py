@@ -17,7 +17,7 @@ from raytracerfacility_b200 import structs as S  # noqa: E402  (POD layouts only
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("oracle_api.cpp", "oracle_shade.h", "oracle_bvh.h", "oracle_math.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_api.cpp", "oracle_shade.h", "oracle_bvh.h", "oracle_btf.h", "oracle_math.h")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
     return so
@@ -82,6 +82,14 @@ def sample_lobe(r0, r1, n, alpha):
     return np.array(out[:], dtype=np.float32)
 
 
+def inverse_trig(y, x):
+    """Portable atan2(y, x), asin(y), acos(y) of oracle_math.h."""
+    y, x = np.ascontiguousarray(y, dtype=np.float32), np.ascontiguousarray(x, dtype=np.float32)
+    a, s, c = np.empty_like(y), np.empty_like(y), np.empty_like(y)
+    lib().orc_inverse_trig(len(y), _p(y), _p(x), _p(a), _p(s), _p(c))
+    return a, s, c
+
+
 def env_light(env, pos, d):
     out = (C.c_float * 3)()
     lib().orc_env_light(C.byref(env), (C.c_float * 3)(*pos), (C.c_float * 3)(*d), out)
@@ -107,6 +115,22 @@ class OracleScene:
             g, m, x, comp = desc.instances[ih]
             x = np.ascontiguousarray(x, dtype=np.float32)
             L.orc_scene_add_instance(self.h, gmap[g], mmap[m], _p(x), C.c_uint64(comp))
+        # images, cube map, compressed BTF (oracle_btf.h)
+        self.tex_index, self.btf_index, self.mat_index = {}, {}, mmap
+        for th in sorted(getattr(desc, "textures", {})):
+            img = np.ascontiguousarray(desc.textures[th], dtype=np.float32)
+            self.tex_index[th] = L.orc_scene_add_texture(self.h, int(img.shape[1]), int(img.shape[0]), _p(img))
+        for mh, tex in getattr(desc, "material_textures", {}).items():
+            ids = [self.tex_index[t] if t else -1 for t in tex]
+            L.orc_scene_set_material_textures(self.h, mmap[mh], *ids)
+        for bh in sorted(getattr(desc, "btfs", {})):
+            d = desc.btfs[bh].desc()
+            self.btf_index[bh] = L.orc_scene_add_btf(self.h, C.byref(d))
+        for mh, bh in getattr(desc, "material_btf", {}).items():
+            L.orc_scene_set_material_btf(self.h, mmap[mh], self.btf_index[bh])
+        if getattr(desc, "env_map", None) is not None:
+            faces = (C.c_int * 6)(*[self.tex_index[t] for t in desc.env_map])
+            L.orc_scene_set_environment_map(self.h, faces)
         L.orc_scene_commit(self.h, int(morton_bits), int(presplit))
         self.n_tris = int(L.orc_scene_ntris(self.h))
         self.n_nodes = int(L.orc_scene_nnodes(self.h))
@@ -119,6 +143,31 @@ class OracleScene:
                 self.h = None
         except Exception:
             pass
+
+    def sample_texture(self, handle, uv):
+        uv = np.ascontiguousarray(uv, dtype=np.float32).reshape(-1, 2)
+        out = np.empty((len(uv), 4), dtype=np.float32)
+        lib().orc_sample_texture(self.h, self.tex_index[handle], C.c_uint64(len(uv)), _p(uv), _p(out))
+        return out
+
+    def sample_environment(self, env, pos_dir):
+        pd = np.ascontiguousarray(pos_dir, dtype=np.float32).reshape(-1, 6)
+        out = np.empty((len(pd), 3), dtype=np.float32)
+        lib().orc_sample_environment(self.h, C.byref(env), C.c_uint64(len(pd)), _p(pd), _p(out))
+        return out
+
+    def btf_eval(self, btf, tex_coord, view_dir, illum_dir, normal, tangent, nthreads=0):
+        a = [np.ascontiguousarray(x, dtype=np.float32) for x in (tex_coord, view_dir, illum_dir, normal, tangent)]
+        n = len(a[0])
+        out = np.empty((n, 3), dtype=np.float32)
+        lib().orc_btf_eval(self.h, self.btf_index[btf], C.c_uint64(n), _p(a[0]), _p(a[1]), _p(a[2]), _p(a[3]), _p(a[4]),
+                           _p(out), int(nthreads))
+        return out
+
+    def btf_beta_angles(self, btf, n):
+        out = np.empty(n, dtype=np.float32)
+        lib().orc_btf_beta_angles(self.h, self.btf_index[btf], _p(out))
+        return out
 
     def debug(self, what):
         L = lib()

@@ -79,6 +79,8 @@ int rtf_destroy(rtf_ctx* ctx) {
                     &ctx->ws.sort_keys, &ctx->ws.sort_keys_alt, &ctx->ws.sort_vals, &ctx->ws.sort_vals_alt,
                     &ctx->ws.sort_tmp, &ctx->ws.io};
   for (DevBuf* b : bufs) b->release();
+  ctx->d_btfs.release(), ctx->d_env_faces.release();
+  release_material_tables(ctx);
   for (cudaEvent_t e : ctx->build_ev)
     if (e) cudaEventDestroy(e);
   if (ctx->pipe.init) {
@@ -132,8 +134,8 @@ int rtf_set_geometry(rtf_ctx* ctx, uint64_t handle, const void* vertices, size_t
 int rtf_set_material(rtf_ctx* ctx, uint64_t handle, const rtf_material* material) {
   CHECK_CTX(ctx);
   if (!material) return RTF_ERR_INVALID;
-  if (material->material_type == RTF_MAT_COMPRESSED_BTF) {
-    set_error("CompressedBTF materials are a 'next' row (SURVEY N1), not built in this round");
+  if (material->material_type < RTF_MAT_DEFAULT || material->material_type > RTF_MAT_COMPRESSED_BTF) {
+    set_error("rtf_set_material: unknown material_type");
     return RTF_ERR_INVALID;
   }
   ctx->mats[handle] = *material;
@@ -158,6 +160,7 @@ int rtf_remove_geometry(rtf_ctx* ctx, uint64_t handle) {
 }
 int rtf_remove_material(rtf_ctx* ctx, uint64_t handle) {
   CHECK_CTX(ctx);
+  ctx->mat_links.erase(handle);
   return ctx->mats.erase(handle) ? RTF_OK : RTF_ERR_NOT_FOUND;
 }
 int rtf_remove_instance(rtf_ctx* ctx, uint64_t handle) {
@@ -177,8 +180,9 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   cudaStream_t st = ctx->stream;
   // materials -> dense table
   std::map<uint64_t, uint32_t> mat_index;
-  std::vector<rtf_material> mats;
-  for (auto& m : ctx->mats) mat_index[m.first] = (uint32_t)mats.size(), mats.push_back(m.second);
+  std::vector<DevMaterial> mats;
+  std::vector<DevBTF> btfs;
+  if ((rc = resolve_materials(ctx, mat_index, mats, btfs))) return rc;
   // instances in ascending handle order = global primitive numbering
   std::vector<InstDev> insts;
   std::vector<float> alpha;
@@ -211,8 +215,12 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
     if (d.n_prims == 0) continue;  // nothing to trace; keeps first_prim strictly increasing
     first += d.n_prims;
     insts.push_back(d);
-    const rtf_material& mm = mats[d.mat];
-    alpha.push_back(mm.material_type == RTF_MAT_DEFAULT ? 1.0f - mm.transmission : 1.0f);  // RayDataDefinations.hpp:250
+    const DevMaterial& mm = mats[d.mat];
+    // any-hit alpha (RF.cuh:13-19, RDD.hpp:248-254): Default material only; the albedo texture's w when there is one
+    // (flagged as -1: looked up per candidate hit), else 1 - transmission
+    float al = 1.0f;
+    if (mm.m.material_type == RTF_MAT_DEFAULT) al = mm.tex[MAT_TEX_ALBEDO].texels ? -1.0f : 1.0f - mm.m.transmission;
+    alpha.push_back(al);
   }
   if (first >= 0xFFFFFFF0ull) {
     set_error("more than 2^32 triangles");
@@ -224,10 +232,15 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
     return RTF_OK;
   }
   if ((rc = ctx->d_insts.reserve(insts.size() * sizeof(InstDev)))) return rc;
-  if ((rc = ctx->d_mats.reserve(mats.size() * sizeof(rtf_material)))) return rc;
+  if ((rc = ctx->d_mats.reserve(mats.size() * sizeof(DevMaterial)))) return rc;
+  if ((rc = ctx->d_btfs.reserve((btfs.size() + 1) * sizeof(DevBTF)))) return rc;
+  if (!btfs.empty())
+    RTF_CUDA(cudaMemcpyAsync(ctx->d_btfs.p, btfs.data(), btfs.size() * sizeof(DevBTF), cudaMemcpyHostToDevice, st));
+  const DevTexture* env_faces = nullptr;
+  if ((rc = resolve_environment_map(ctx, &env_faces))) return rc;
   if ((rc = ctx->d_inst_alpha.reserve(alpha.size() * 4))) return rc;
   RTF_CUDA(cudaMemcpyAsync(ctx->d_insts.p, insts.data(), insts.size() * sizeof(InstDev), cudaMemcpyHostToDevice, st));
-  RTF_CUDA(cudaMemcpyAsync(ctx->d_mats.p, mats.data(), mats.size() * sizeof(rtf_material), cudaMemcpyHostToDevice, st));
+  RTF_CUDA(cudaMemcpyAsync(ctx->d_mats.p, mats.data(), mats.size() * sizeof(DevMaterial), cudaMemcpyHostToDevice, st));
   RTF_CUDA(cudaMemcpyAsync(ctx->d_inst_alpha.p, alpha.data(), alpha.size() * 4, cudaMemcpyHostToDevice, st));
   if ((rc = ctx->d_pos9.reserve(36 * (size_t)first))) return rc;
   if ((rc = ctx->d_nrm9.reserve(36 * (size_t)first))) return rc;
@@ -249,11 +262,12 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   DevScene& s = ctx->scene;
   s.nodes = ctx->d_nodes.as<uint4>(), s.tris = ctx->d_tris48.as<float4>();
   s.pos9 = ctx->d_pos9.as<float>(), s.nrm9 = ctx->d_nrm9.as<float>(), s.tri_inst = ctx->d_tri_inst.as<uint32_t>();
-  s.mats = ctx->d_mats.as<rtf_material>(), s.inst_alpha = ctx->d_inst_alpha.as<float>();
+  s.mats = ctx->d_mats.as<DevMaterial>(), s.inst_alpha = ctx->d_inst_alpha.as<float>();
+  s.btfs = ctx->d_btfs.as<DevBTF>(), s.env_faces = env_faces;
   s.n_tris = ctx->n_tris, s.n_nodes = ctx->n_nodes;
   s.has_alpha = 0;
   for (float a : alpha)
-    if (a < 1.0f) s.has_alpha = 1;
+    if (a < 1.0f) s.has_alpha = 1;  // includes the "textured alpha" marker (-1)
   ctx->ready = true;
   return RTF_OK;
 }

@@ -27,7 +27,9 @@ static_assert(kSmemStack + kLocalStack == kMaxStackDepth, "stack split must cove
 
 static inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
 
-constexpr uint32_t kShadowBit = 0x80000000u;
+constexpr uint32_t kShadowBit = 0x80000000u;   // first-hit ray (TERMINATE_ON_FIRST_HIT | DISABLE_ANYHIT | DISABLE_CLOSESTHIT)
+constexpr uint32_t kNoAnyHitBit = 0x40000000u; // closest-hit ray traced with OPTIX_RAY_FLAG_DISABLE_ANYHIT (BTF bounce, RF.cuh:239)
+constexpr uint32_t kPathMask = ~(kShadowBit | kNoAnyHitBit);  // path index inside the batch (batch_paths <= 2^28)
 // resident blocks per SM the register allocator must allow: 8 x 128 threads = 64 registers (measured 3118 vs 3017
 // Mrays/s at 80 registers / 6 blocks); the queue kernel with stochastic alpha carries the path map and RNG keys: 80 registers / 6 blocks (spilling at 72 cost 12 %).
 #ifndef RTF_TRACE_MIN_BLOCKS
@@ -57,7 +59,7 @@ struct SrcRays {
     tmin = a.w, tag = 0u;
   }
   RTF_D bool any_hit(uint32_t) const { return false; }
-  RTF_D bool alpha_pass(uint32_t, uint32_t, uint32_t) const { return true; }
+  RTF_D bool alpha_pass(uint32_t, uint32_t, uint32_t, float, float) const { return true; }
   RTF_D void store(uint32_t i, uint32_t, const HitRec& h, uint32_t nvis, uint32_t tvis) const {
     hits[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
     if (nv) nv[i] = nvis;
@@ -163,6 +165,7 @@ struct SrcQueue {
   uint32_t n;
   float tmin;
   const float* inst_alpha;  // nullptr: no material can ignore hits
+  DevScene sc;              // alpha from an albedo texture needs the hit's texture coordinate (ALPHA variant only)
   PathMap pm;
   uint32_t seed, bounce;
   RTF_D void issue(uint32_t base, uint32_t cnt, uint32_t raw_s, uint32_t mbar_s) const {
@@ -177,11 +180,15 @@ struct SrcQueue {
   }
   RTF_D bool any_hit(uint32_t tag) const { return (tag & kShadowBit) != 0u; }  // TERMINATE_ON_FIRST_HIT, RayFunctions.cuh:81-83
   // AnyHitFunc, RayFunctions.cuh:5-23: ignore the candidate if alpha <= rnd; the draw is keyed by (path, bounce, primitive)
-  // so it does not depend on traversal order.  Shadow rays run with DISABLE_ANYHIT.
-  RTF_D bool alpha_pass(uint32_t tag, uint32_t prim, uint32_t inst) const {
-    if (inst_alpha == nullptr || (tag & kShadowBit)) return true;
-    const float alpha = inst_alpha[inst];
-    const float rnd = path_rng(seed, STREAM_ALPHA, unit_of(pm, tag), bounce, prim).x;
+  // so it does not depend on traversal order.  Shadow rays and BTF bounce rays run with DISABLE_ANYHIT.
+  RTF_D bool alpha_pass(uint32_t tag, uint32_t prim, uint32_t inst, float bu, float bv) const {
+    if (inst_alpha == nullptr || (tag & (kShadowBit | kNoAnyHitBit))) return true;
+    float alpha = inst_alpha[inst];
+    if (alpha < 0.0f) {  // SurfaceMaterial::GetAlbedo(texCoord).w, RDD.hpp:248-254
+      const HitAttrs at = hit_attrs(sc, prim, bu, bv, inst);
+      alpha = tex2d(sc.mats[sc.insts[inst].mat].tex[MAT_TEX_ALBEDO], at.u, at.v).w;
+    }
+    const float rnd = path_rng(seed, STREAM_ALPHA, unit_of(pm, tag & kPathMask), bounce, prim).x;
     return !(alpha <= rnd);
   }
   RTF_D void store(uint32_t i, uint32_t, const HitRec& h, uint32_t, uint32_t) const {
@@ -195,7 +202,7 @@ __global__ void __launch_bounds__(kTraceBlock, ALPHA ? RTF_QUEUE_MIN_BLOCKS : RT
   __shared__ TraceSmem sm;
   const uint32_t n = q.count[wave];
   if (blockIdx.x == 0 && threadIdx.x == 0 && stats) atomicAdd(stats, (unsigned long long)n);
-  SrcQueue<ALPHA> src{q.ray_a[qi], q.ray_b[qi], q.hits, n, tmin, ALPHA ? sc.inst_alpha : nullptr, pm, seed, (uint32_t)wave};
+  SrcQueue<ALPHA> src{q.ray_a[qi], q.ray_b[qi], q.hits, n, tmin, ALPHA ? sc.inst_alpha : nullptr, sc, pm, seed, (uint32_t)wave};
   trace_engine<false>(sc.nodes, sc.tris, src, q.work + wave, sm);
 }
 
@@ -215,7 +222,7 @@ __global__ void __launch_bounds__(256)
   if (i < n) {
     const float4 a = q.ray_a[qi][i], b = q.ray_b[qi][i];
     const uint32_t pi = __float_as_uint(a.w);
-    const uint32_t p = pi & ~kShadowBit;
+    const uint32_t p = pi & kPathMask;
     const float4 h = q.hits[i];
     const uint32_t prim = __float_as_uint(h.w);
     const float3 o = f3(a.x, a.y, a.z), d = f3(b.x, b.y, b.z);
@@ -223,68 +230,127 @@ __global__ void __launch_bounds__(256)
     float3 T = f3(thr4.x, thr4.y, thr4.z);
     const float4 acc4 = ps.acc[p];
     float3 acc = f3(acc4.x, acc4.y, acc4.z);
-    if (pi & kShadowBit) {  // shadow ray result, RayFunctions.cuh:70-92
+    if (pi & kShadowBit) {  // shadow ray result, RayFunctions.cuh:70-92 (BTF: :193-217)
       const float4 ax = ps.aux[p];
       const float3 albedo = f3(ax.x, ax.y, ax.z);
       if (prim == 0xFFFFFFFFu) {
-        const float3 L = env_light(o, d, env);
+        const float3 L = env_light(o, d, env, sc.env_faces);
         acc = acc + T * ((L * ax.w) * albedo);
       }
       acc = acc + T * (thr4.w * albedo);
       ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
     } else if (prim == 0xFFFFFFFFu) {  // MissFunc
-      const float3 L = env_light(o, d, env);
+      const float3 L = env_light(o, d, env, sc.env_faces);
       acc = acc + T * L;
       ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
       if (sp.camera && __float_as_uint(thr4.w) == 0u) ps.first_a[p] = make_float4(L.x, L.y, L.z, 0.0f);
     } else {
       const uint32_t hit_count = __float_as_uint(thr4.w) + 1u;
       const SurfaceHit sh = surface_hit(sc, prim, h.y, h.z, d);
-      const rtf_material& m = sc.mats[sc.insts[sh.inst].mat];
-      const float metallic = m.metallic, roughness = m.roughness;
-      const float3 albedo = f3(m.albedo_color[0], m.albedo_color[1], m.albedo_color[2]);
-      if (sp.camera && hit_count == 1u) {
-        ps.first_n[p] = make_float4(sh.normal.x, sh.normal.y, sh.normal.z, 0.0f);
-        ps.first_a[p] = make_float4(albedo.x, albedo.y, albedo.z, 0.0f);
-        ps.first_p[p] = make_float4(sh.position.x, sh.position.y, sh.position.z, 1.0f);
-      }
-      float f = 1.0f;
-      if (metallic >= 0.0f) f = (metallic + 2) / (metallic + 1);
-      const float3 emis = m.emission * albedo;
+      const DevMaterial& dm = sc.mats[sc.insts[sh.inst].mat];
+      const rtf_material& m = dm.m;
+      HitAttrs at;
+      at.u = 0.0f, at.v = 0.0f, at.tangent = f3(0, 0, 0), at.color = f3(0, 0, 0);
+      if (dm.rich) at = hit_attrs(sc, prim, h.y, h.z, sh.inst);
       const uint64_t unit = unit_of(pm, p);
-      if (env.lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE) {  // RayFunctions.cuh:61-92
-        const float4 r = path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
-        const float3 sun = f3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
-        const float3 nd = sample_lobe(r.x, r.y, sun, 1.0f - env.light_size);
-        const float3 col = f3(env.color[0], env.color[1], env.color[2]);
-        acc = acc + T * ((col * env.ambient_light_intensity) * albedo);
-        const float ndl = dot3(sh.normal, nd);
-        if (ndl > 0.0f) {
+      if (m.material_type == RTF_MAT_COMPRESSED_BTF) {  // RayFunctions.cuh:172-258
+        const DevBTF& btf = sc.btfs[dm.btf];
+        float3 btf_color = f3(0, 0, 0);  // the reference leaves it uninitialised past the bounce limit: 0 here
+        if ((int)hit_count <= sp.bounces) {
+          const float4 r = path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
+          if (env.lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE) {  // :180-218
+            const float3 sun = f3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
+            const float3 nd = sample_lobe(r.x, r.y, sun, 1.0f - env.light_size);
+            btf_color = btf_get_value(btf, at.u, at.v, d, nd, sh.normal, at.tangent);
+            const float3 col = f3(env.color[0], env.color[1], env.color[2]);
+            acc = acc + T * ((col * env.ambient_light_intensity) * btf_color);
+            const float ndl = dot3(sh.normal, nd);
+            if (ndl > 0.0f) {
+              const float3 so = sh.position + sh.normal * 1e-3f;
+              emit = true;
+              na = make_float4(so.x, so.y, so.z, __uint_as_float(p | kShadowBit));
+              nb = make_float4(nd.x, nd.y, nd.z, 1e20f);
+              ps.thr[p] = make_float4(T.x, T.y, T.z, 0.0f);  // no emission term on this branch
+              ps.aux[p] = make_float4(btf_color.x, btf_color.y, btf_color.z, ndl);
+            }
+            ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
+          } else {  // :219-246
+            const float3 refl = reflect3(d, sh.normal);
+            const float3 nd = sample_lobe(r.x, r.y, refl, 0.0f);
+            btf_color = btf_get_value(btf, at.u, at.v, d, nd, sh.normal, at.tangent);
+            T = T * btf_color;
+            const float3 so = sh.position + sh.normal * 1e-3f;
+            ps.thr[p] = make_float4(T.x, T.y, T.z, __uint_as_float(hit_count));
+            emit = true;
+            na = make_float4(so.x, so.y, so.z, __uint_as_float(p | kNoAnyHitBit));
+            nb = make_float4(nd.x, nd.y, nd.z, 1e20f);
+          }
+        }
+        if (sp.camera && hit_count == 1u) {
+          ps.first_n[p] = make_float4(sh.normal.x, sh.normal.y, sh.normal.z, 0.0f);
+          ps.first_a[p] = make_float4(btf_color.x, btf_color.y, btf_color.z, 0.0f);
+          ps.first_p[p] = make_float4(sh.position.x, sh.position.y, sh.position.z, 1.0f);
+        }
+      } else {  // surface materials, RayFunctions.cuh:44-172
+        float3 normal = sh.normal;
+        if (dm.tex[MAT_TEX_NORMAL].texels) {  // ApplyNormalTexture, RDD.hpp:268-281
+          const float4 t = tex2d(dm.tex[MAT_TEX_NORMAL], at.u, at.v);
+          const float3 B = cross3(normal, at.tangent);
+          const float3 tn = f3(t.x * 2.0f - 1.0f, t.y * 2.0f - 1.0f, t.z * 2.0f - 1.0f);
+          normal = normalize3((at.tangent * tn.x + B * tn.y) + normal * tn.z);
+        }
+        float metallic = m.metallic, roughness = m.roughness;
+        if (dm.tex[MAT_TEX_METALLIC].texels) metallic = tex2d(dm.tex[MAT_TEX_METALLIC], at.u, at.v).x;
+        if (dm.tex[MAT_TEX_ROUGHNESS].texels) roughness = tex2d(dm.tex[MAT_TEX_ROUGHNESS], at.u, at.v).x;
+        float3 albedo = f3(m.albedo_color[0], m.albedo_color[1], m.albedo_color[2]);
+        if (m.material_type != RTF_MAT_DEFAULT) {
+          albedo = at.color;  // VertexColor: hitInfo.m_color, RayFunctions.cuh:55-57
+        } else if (dm.tex[MAT_TEX_ALBEDO].texels) {
+          const float4 t = tex2d(dm.tex[MAT_TEX_ALBEDO], at.u, at.v);
+          albedo = f3(t.x, t.y, t.z);
+        }
+        if (sp.camera && hit_count == 1u) {
+          ps.first_n[p] = make_float4(normal.x, normal.y, normal.z, 0.0f);
+          ps.first_a[p] = make_float4(albedo.x, albedo.y, albedo.z, 0.0f);
+          ps.first_p[p] = make_float4(sh.position.x, sh.position.y, sh.position.z, 1.0f);
+        }
+        float f = 1.0f;
+        if (metallic >= 0.0f) f = (metallic + 2) / (metallic + 1);
+        const float3 emis = m.emission * albedo;
+        if (env.lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE) {  // RayFunctions.cuh:61-92
+          const float4 r = path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
+          const float3 sun = f3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
+          const float3 nd = sample_lobe(r.x, r.y, sun, 1.0f - env.light_size);
+          const float3 col = f3(env.color[0], env.color[1], env.color[2]);
+          acc = acc + T * ((col * env.ambient_light_intensity) * albedo);
+          const float ndl = dot3(normal, nd);
+          if (ndl > 0.0f) {
+            emit = true;
+            na = make_float4(sh.position.x, sh.position.y, sh.position.z, __uint_as_float(p | kShadowBit));
+            nb = make_float4(nd.x, nd.y, nd.z, 1e20f);
+            ps.thr[p] = make_float4(T.x, T.y, T.z, m.emission);
+            ps.aux[p] = make_float4(albedo.x, albedo.y, albedo.z, ndl);
+          } else {
+            acc = acc + T * emis;
+          }
+          ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
+        } else if ((int)hit_count <= sp.bounces) {  // RayFunctions.cuh:93-161, BSSRDF branch off (factor 0)
+          const float4 r = path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
+          const float3 refl = reflect3(d, normal);
+          const float3 nd = sample_lobe(r.x, r.y, refl, metallic);  // BRDF(), BSDF.cuh:6-13
+          const float k = clampf(fabsf(dot3(normal, nd)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
+          const float3 wgt = ((1.0f - m.subsurface_factor) * albedo) * k;
+          acc = acc + T * emis;
+          T = T * wgt;
+          ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
+          ps.thr[p] = make_float4(T.x, T.y, T.z, __uint_as_float(hit_count));
           emit = true;
-          na = make_float4(sh.position.x, sh.position.y, sh.position.z, __uint_as_float(p | kShadowBit));
+          na = make_float4(sh.position.x, sh.position.y, sh.position.z, __uint_as_float(p));  // origin not offset, RayFunctions.cuh:138
           nb = make_float4(nd.x, nd.y, nd.z, 1e20f);
-          ps.thr[p] = make_float4(T.x, T.y, T.z, m.emission);
-          ps.aux[p] = make_float4(albedo.x, albedo.y, albedo.z, ndl);
         } else {
           acc = acc + T * emis;
+          ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
         }
-        ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
-      } else if ((int)hit_count <= sp.bounces) {  // RayFunctions.cuh:93-161, BSSRDF branch off (factor 0)
-        const float4 r = path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
-        const float3 refl = reflect3(d, sh.normal);
-        const float3 nd = sample_lobe(r.x, r.y, refl, metallic);  // BRDF(), BSDF.cuh:6-13
-        const float k = clampf(fabsf(dot3(sh.normal, nd)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
-        const float3 wgt = ((1.0f - m.subsurface_factor) * albedo) * k;
-        acc = acc + T * emis;
-        T = T * wgt;
-        ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
-        ps.thr[p] = make_float4(T.x, T.y, T.z, __uint_as_float(hit_count));
-        emit = true;
-        na = make_float4(sh.position.x, sh.position.y, sh.position.z, __uint_as_float(p));  // origin not offset, RayFunctions.cuh:138
-        nb = make_float4(nd.x, nd.y, nd.z, 1e20f);
-      } else {
-        acc = acc + T * emis;
-        ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
       }
     }
   }
@@ -484,8 +550,8 @@ int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp,
     set_error("no acceleration structure (call rtf_commit)");
     return RTF_ERR_NOT_READY;
   }
-  if (env->environmental_map_id != 0) {
-    set_error("cube-map environment is not wired in this round (SURVEY N2)");
+  if (env->environmental_map_id != 0 && env->lighting_type == RTF_ENV_SCENE && ctx->scene.env_faces == nullptr) {
+    set_error("environmental_map_id != 0 but no cube map is registered (rtf_set_environment_map, then rtf_commit)");
     return RTF_ERR_INVALID;
   }
   if (tri_end <= tri_begin || s1 <= s0) return RTF_OK;
@@ -550,7 +616,7 @@ struct SrcGrid {
     tmin = 1e-3f, tag = 0u;
   }
   RTF_D bool any_hit(uint32_t) const { return false; }
-  RTF_D bool alpha_pass(uint32_t, uint32_t, uint32_t) const { return true; }
+  RTF_D bool alpha_pass(uint32_t, uint32_t, uint32_t, float, float) const { return true; }
   RTF_D void store(uint32_t k, uint32_t, const HitRec& h, uint32_t, uint32_t) const {
     if (t_out) t_out[k] = h.t;
     if (prim_out) prim_out[k] = h.prim;
@@ -576,7 +642,7 @@ struct SrcSamples {
     tmin = 1e-3f, tag = 0u;
   }
   RTF_D bool any_hit(uint32_t) const { return false; }
-  RTF_D bool alpha_pass(uint32_t, uint32_t, uint32_t) const { return true; }
+  RTF_D bool alpha_pass(uint32_t, uint32_t, uint32_t, float, float) const { return true; }
   RTF_D void store(uint32_t k, uint32_t, const HitRec& h, uint32_t, uint32_t) const {
     rtf_pc_sample& s = samples[k];
     if (prim_out) prim_out[k] = h.prim;
@@ -734,8 +800,8 @@ int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, cons
   const rtf_camera_props& cp = cam->props;
   const uint64_t n_pixels = (uint64_t)cp.width * (uint64_t)cp.height;
   if (n_pixels == 0 || rp->samples <= 0) return RTF_OK;
-  if (env->environmental_map_id != 0) {
-    set_error("cube-map environment is not wired in this round (SURVEY N2)");
+  if (env->environmental_map_id != 0 && env->lighting_type == RTF_ENV_SCENE && ctx->scene.env_faces == nullptr) {
+    set_error("environmental_map_id != 0 but no cube map is registered (rtf_set_environment_map, then rtf_commit)");
     return RTF_ERR_INVALID;
   }
   const uint32_t spp = (uint32_t)rp->samples;

@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "../../include/rtf/rtf.h"
+#include "rtf_btf.cuh"
 #include "rtf_bvh.cuh"
 
 namespace rtf {
@@ -58,6 +59,16 @@ struct InstDev {
   const uint32_t* tris;
 };
 
+// A material as the kernels see it: the MaterialProperties fields + the texture / BTF tables it points at
+// (RayTracedMaterial, RT.hpp:247-269 -> SurfaceMaterial / SurfaceCompressedBTF, RDD.hpp:240-354).
+enum { MAT_TEX_ALBEDO = 0, MAT_TEX_NORMAL = 1, MAT_TEX_METALLIC = 2, MAT_TEX_ROUGHNESS = 3 };
+struct DevMaterial {
+  rtf_material m;
+  DevTexture tex[4];  // texels == nullptr: constant from m
+  int btf;            // index into DevScene::btfs (material_type == RTF_MAT_COMPRESSED_BTF), else -1
+  int rich;           // shading needs interpolated vertex attributes (texture coordinate, tangent, vertex colour)
+};
+
 // Everything a kernel needs to trace and shade, passed by value.
 struct DevScene {
   const uint4* nodes = nullptr;
@@ -66,8 +77,10 @@ struct DevScene {
   const float* nrm9 = nullptr;
   const uint32_t* tri_inst = nullptr;
   const InstDev* insts = nullptr;
-  const rtf_material* mats = nullptr;
-  const float* inst_alpha = nullptr;
+  const DevMaterial* mats = nullptr;
+  const DevBTF* btfs = nullptr;
+  const DevTexture* env_faces = nullptr;  // 6 cube-map faces, or nullptr
+  const float* inst_alpha = nullptr;      // per instance: constant alpha, or < 0 = alpha comes from the albedo texture
   uint32_t n_tris = 0, n_nodes = 0, n_insts = 0;
   int has_alpha = 0;
 };
@@ -78,6 +91,21 @@ struct Geometry {
   uint64_t version = 0;
   DevBuf d_verts, d_tris;
   bool uploaded = false;
+};
+struct Texture {
+  int w = 0, h = 0;
+  DevBuf texels;
+};
+struct MaterialLinks {  // handles; 0 = none
+  uint64_t tex[4] = {0, 0, 0, 0};
+  uint64_t btf = 0;
+};
+struct BTFTables {
+  rtf_btf_desc desc;  // scalars only (pointers are dead after rtf_set_btf)
+  DevBuf pdf6_slices, pdf6_scales, pdf1d_basis, colors, index_ab, pdf2d_colors, pdf2d_slices, pdf2d_scales, pdf2d_indices,
+      pdf3d_scales, pdf3d_slices, pdf4d_scales, pdf4d_slices, beta_angles;
+  DevBTF dev() const;
+  void release();
 };
 struct Instance {
   uint64_t geom, mat;
@@ -123,6 +151,11 @@ struct rtf_ctx {
   std::map<uint64_t, rtf::Geometry> geoms;
   std::map<uint64_t, rtf_material> mats;
   std::map<uint64_t, rtf::Instance> insts;
+  std::map<uint64_t, rtf::Texture> textures;
+  std::map<uint64_t, rtf::MaterialLinks> mat_links;
+  std::map<uint64_t, rtf::BTFTables> btfs;
+  uint64_t env_map[6] = {0, 0, 0, 0, 0, 0};
+  bool has_env_map = false;
   // committed state
   bool ready = false;
   int morton_bits = 63;
@@ -130,7 +163,7 @@ struct rtf_ctx {
   uint32_t n_tris = 0, n_nodes = 0;
   uint32_t n_refs = 0;  // triangle references in the BVH (>= n_tris when long triangles are pre-split)
   int presplit = 8;     // option "presplit": most references one triangle may be cut into (1 = off)
-  rtf::DevBuf d_pos9, d_nrm9, d_tri_inst, d_nodes, d_tris48, d_insts, d_mats, d_inst_alpha;
+  rtf::DevBuf d_pos9, d_nrm9, d_tri_inst, d_nodes, d_tris48, d_insts, d_mats, d_inst_alpha, d_btfs, d_env_faces;
   rtf::BuildArrays ba;
   rtf::Workspace ws;
   rtf::HostPipe pipe;
@@ -155,6 +188,11 @@ struct rtf_camera {
 namespace rtf {
 // build.cu
 int build_bvh(rtf_ctx* ctx, int morton_bits);
+// materials.cu
+int resolve_materials(rtf_ctx* ctx, std::map<uint64_t, uint32_t>& mat_index, std::vector<DevMaterial>& mats,
+                      std::vector<DevBTF>& btfs);
+int resolve_environment_map(rtf_ctx* ctx, const DevTexture** dev_faces);
+void release_material_tables(rtf_ctx* ctx);
 // render.cu
 int trace_rays_device(rtf_ctx* ctx, const float4* rays, size_t n, float4* hits, uint32_t* node_visits, uint32_t* tri_visits);
 int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push, int front,
@@ -165,6 +203,9 @@ int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin
                      uint32_t* d_prim, uint32_t* d_inst);
 int scan_samples_device(rtf_ctx* ctx, rtf_pc_sample* d_samples, size_t n, uint32_t* d_prim);
 int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp);
+int sample_texture_device(rtf_ctx* ctx, const DevTexture& tex, size_t n, const float* d_uv, float* d_rgba);
+int sample_environment_device(rtf_ctx* ctx, const rtf_env* env, size_t n, const float* d_pos_dir6, float* d_rgb);
+int btf_eval_device(rtf_ctx* ctx, const DevBTF& btf, size_t n, const float* d_in14, float* d_rgb);
 int microbench_fp32(rtf_ctx* ctx, double* tflops);
 int microbench_l2(rtf_ctx* ctx, double bytes, double* gbs);
 }  // namespace rtf

@@ -86,12 +86,19 @@ RTF_HD float3 nishita_sky(float3 position, float3 dir, const rtf_env& env) {
   }
   return ((sumR * betaR) * phaseR + (sumM * betaM) * phaseM) * 20.0f;
 }
-// CalculateEnvironmentalLight, Environment.cuh:147-175 (cube map: SURVEY §8 N2, not wired)
-RTF_HD float3 env_light(float3 position, float3 dir, const rtf_env& env) {
+// CalculateEnvironmentalLight, Environment.cuh:147-175.  env_faces: the six cube-map faces (rtf_set_environment_map) or
+// nullptr; sampled when m_environmentalMapId != 0 (Env.cuh:153-158).
+RTF_D float3 env_light(float3 position, float3 dir, const rtf_env& env, const DevTexture* env_faces) {
   float3 c = f3(1, 1, 1);
   float3 col = f3(env.color[0], env.color[1], env.color[2]);
   switch (env.lighting_type) {
-    case RTF_ENV_SCENE: c = col * env.skylight_intensity; break;
+    case RTF_ENV_SCENE:
+      if (env.environmental_map_id != 0 && env_faces != nullptr) {
+        const float4 t = sample_cube_map(env_faces, dir);
+        col = f3(t.x, t.y, t.z);
+      }
+      c = col * env.skylight_intensity;
+      break;
     case RTF_ENV_SKYDOME: c = nishita_sky(position, dir, env) * env.skylight_intensity; break;
     case RTF_ENV_SINGLE_LIGHT_SOURCE: c = col * env.skylight_intensity; break;
   }
@@ -123,6 +130,33 @@ RTF_D SurfaceHit surface_hit(const DevScene& sc, uint32_t prim, float u, float v
   s.normal = nn;
   s.inst = __ldg(sc.tri_inst + prim);
   return s;
+}
+// Interpolated vertex attributes for the materials that read them (TriangularMesh::GetHitInfo, RDD.hpp:127-164;
+// tangent through SBT::GetHitInfo, RDD.hpp:379).
+struct HitAttrs {
+  float u, v;      // texture coordinate
+  float3 tangent;  // normalize(M * t)
+  float3 color;    // colour of the dominant-barycentric vertex (RDD.hpp:150-160, as written)
+};
+RTF_D HitAttrs hit_attrs(const DevScene& sc, uint32_t prim, float bu, float bv, uint32_t inst) {
+  const InstDev& in = sc.insts[inst];
+  const uint32_t lt = prim - in.first_prim;
+  const rtf_vertex& vx = in.verts[in.tris[3 * lt]];
+  const rtf_vertex& vy = in.verts[in.tris[3 * lt + 1]];
+  const rtf_vertex& vz = in.verts[in.tris[3 * lt + 2]];
+  const float z = (1.0f - bu) - bv;
+  HitAttrs a;
+  float3 tg = (z * f3(vx.tangent[0], vx.tangent[1], vx.tangent[2]) + bu * f3(vy.tangent[0], vy.tangent[1], vy.tangent[2])) +
+              bv * f3(vz.tangent[0], vz.tangent[1], vz.tangent[2]);
+  float m[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) m[k] = in.xform[k];
+  a.tangent = normalize3(mat4_mul(m, tg, 0.0f));
+  a.u = (z * vx.tex_coord[0] + bu * vy.tex_coord[0]) + bv * vz.tex_coord[0];
+  a.v = (z * vx.tex_coord[1] + bu * vy.tex_coord[1]) + bv * vz.tex_coord[1];
+  const rtf_vertex* pick = (bu > z && bu > bv) ? &vx : (bv > z ? &vy : &vz);
+  a.color = f3(pick->color[0], pick->color[1], pick->color[2]);
+  return a;
 }
 // Full HitInfo as __closesthit__PCS_R writes it (PointCloudScanning.cu:15-28).
 RTF_D void full_hit_info(const DevScene& sc, uint32_t prim, float u, float v, float3 ray_dir, rtf_hit_info& out,

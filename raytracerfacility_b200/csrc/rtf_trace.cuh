@@ -98,7 +98,7 @@ struct __align__(128) TraceSmem {
 // A ray source/sink ("Src") provides:
 //   static constexpr bool kTma     — tiles arrive by TMA bulk copy (issue()) or are read/generated in fetch()
 //   static constexpr bool kAnyHit  — rays may be first-hit rays (any_hit(tag))
-//   static constexpr bool kAlpha   — stochastic alpha test may reject candidates (alpha_pass())
+//   static constexpr bool kAlpha   — stochastic alpha test may reject candidates (alpha_pass(tag, prim, inst, u, v))
 //   uint32_t n                     — rays in this launch
 //   void issue(base, cnt, raw_smem_u32, mbar_u32)            (lane 0; kTma only)
 //   void fetch(raw, base, slot, a, b, tmin, tag)              a = {o.xyz, *}, b = {d.xyz, tmax}
@@ -332,11 +332,12 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
         if (!(t >= tmin)) break;
         if (t > best.t) break;
         if (t == best.t && prim >= best.prim) break;
+        const float bu = V * rcp, bv = W * rcp;
         if constexpr (Src::kAlpha) {
           if (__float_as_uint(t2.w) & TRI_FLAG_ALPHA)
-            if (!src.alpha_pass(tag, prim, __float_as_uint(t1.w))) break;
+            if (!src.alpha_pass(tag, prim, __float_as_uint(t1.w), bu, bv)) break;
         }
-        best.t = t, best.u = V * rcp, best.v = W * rcp, best.prim = prim;
+        best.t = t, best.u = bu, best.v = bv, best.prim = prim;
         if constexpr (Src::kAnyHit) {
           if (src.any_hit(tag)) finished = true;
         }

@@ -34,6 +34,9 @@ EXPORTS = [
     "rtf_camera_create", "rtf_camera_destroy", "rtf_camera_get_props", "rtf_camera_resize", "rtf_camera_set",
     "rtf_render_camera", "rtf_camera_download", "rtf_camera_device_buffer", "rtf_debug_size", "rtf_debug_read",
     "rtf_debug_upload_bvh", "rtf_microbench_fp32", "rtf_microbench_l2", "rtf_build_timings", "rtf_set_option",
+    "rtf_set_texture", "rtf_remove_texture", "rtf_set_material_textures", "rtf_set_environment_map", "rtf_sample_texture",
+    "rtf_sample_environment", "rtf_set_btf", "rtf_btf_import_folder", "rtf_remove_btf", "rtf_set_material_btf",
+    "rtf_btf_eval",
 ]
 
 
@@ -149,6 +152,61 @@ class RayTracer:
     def set_material(self, handle, material):
         _check(lib().rtf_set_material(self.h, C.c_uint64(handle), C.byref(material)))
 
+    # ---- images in linear memory + compressed BTF (the GL texture ids / CompressedBTF assets of the reference) ----
+    def set_texture(self, handle, rgba):
+        """rgba: (height, width, 4) float32."""
+        t = np.ascontiguousarray(rgba, dtype=np.float32)
+        assert t.ndim == 3 and t.shape[2] == 4
+        _check(lib().rtf_set_texture(self.h, C.c_uint64(handle), int(t.shape[1]), int(t.shape[0]), _p(t)))
+
+    def remove_texture(self, handle):
+        _check(lib().rtf_remove_texture(self.h, C.c_uint64(handle)))
+
+    def set_material_textures(self, material, albedo=0, normal=0, metallic=0, roughness=0):
+        _check(lib().rtf_set_material_textures(self.h, C.c_uint64(material), C.c_uint64(albedo), C.c_uint64(normal),
+                                               C.c_uint64(metallic), C.c_uint64(roughness)))
+
+    def set_environment_map(self, faces):
+        """faces: six texture handles (+X -X +Y -Y +Z -Z) or None."""
+        arr = (C.c_uint64 * 6)(*faces) if faces is not None else None
+        _check(lib().rtf_set_environment_map(self.h, arr))
+
+    def sample_texture(self, handle, uv):
+        uv = np.ascontiguousarray(uv, dtype=np.float32).reshape(-1, 2)
+        out = np.empty((len(uv), 4), dtype=np.float32)
+        _check(lib().rtf_sample_texture(self.h, C.c_uint64(handle), C.c_size_t(len(uv)), _p(uv), _p(out)))
+        return out
+
+    def sample_environment(self, env, pos_dir):
+        pd = np.ascontiguousarray(pos_dir, dtype=np.float32).reshape(-1, 6)
+        out = np.empty((len(pd), 3), dtype=np.float32)
+        _check(lib().rtf_sample_environment(self.h, C.byref(env), C.c_size_t(len(pd)), _p(pd), _p(out)))
+        return out
+
+    def set_btf(self, handle, tables):
+        """tables: structs.BTFTables."""
+        d = tables.desc()
+        _check(lib().rtf_set_btf(self.h, C.c_uint64(handle), C.byref(d)))
+
+    def btf_import_folder(self, handle, folder):
+        """CompressedBTF::ImportFromFolder (CompressedBTF.cpp:74-390)."""
+        _check(lib().rtf_btf_import_folder(self.h, C.c_uint64(handle), str(folder).encode()))
+
+    def remove_btf(self, handle):
+        _check(lib().rtf_remove_btf(self.h, C.c_uint64(handle)))
+
+    def set_material_btf(self, material, btf):
+        _check(lib().rtf_set_material_btf(self.h, C.c_uint64(material), C.c_uint64(btf)))
+
+    def btf_eval(self, btf, tex_coord, view_dir, illum_dir, normal, tangent):
+        """SurfaceCompressedBTF::GetValue (RayDataDefinations.hpp:329-354) for n queries -> (n, 3) rgb."""
+        a = [np.ascontiguousarray(x, dtype=np.float32) for x in (tex_coord, view_dir, illum_dir, normal, tangent)]
+        n = len(a[0])
+        out = np.empty((n, 3), dtype=np.float32)
+        _check(lib().rtf_btf_eval(self.h, C.c_uint64(btf), C.c_size_t(n), _p(a[0]), _p(a[1]), _p(a[2]), _p(a[3]), _p(a[4]),
+                                  _p(out)))
+        return out
+
     def set_instance(self, handle, geometry, material, transform, component_handle=0):
         x = np.ascontiguousarray(transform, dtype=np.float32).reshape(16)
         _check(lib().rtf_set_instance(self.h, C.c_uint64(handle), C.c_uint64(geometry), C.c_uint64(material), _p(x),
@@ -176,6 +234,15 @@ class RayTracer:
             self.set_material(mh, m)
         for ih, (g, m, x, comp) in desc.instances.items():
             self.set_instance(ih, g, m, x, comp)
+        for th, img in getattr(desc, "textures", {}).items():
+            self.set_texture(th, img)
+        for mh, tex in getattr(desc, "material_textures", {}).items():
+            self.set_material_textures(mh, *tex)
+        for bh, tables in getattr(desc, "btfs", {}).items():
+            self.set_btf(bh, tables)
+        for mh, bh in getattr(desc, "material_btf", {}).items():
+            self.set_material_btf(mh, bh)
+        self.set_environment_map(getattr(desc, "env_map", None))
         if presplit is not None:
             self.set_option("presplit", presplit)
         self.build_ias(morton_bits)

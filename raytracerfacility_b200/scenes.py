@@ -21,6 +21,11 @@ class SceneDesc:
     geometries: dict = field(default_factory=dict)
     materials: dict = field(default_factory=dict)
     instances: dict = field(default_factory=dict)
+    textures: dict = field(default_factory=dict)           # handle -> (h, w, 4) float32
+    material_textures: dict = field(default_factory=dict)  # material -> (albedo, normal, metallic, roughness) handles, 0 = none
+    btfs: dict = field(default_factory=dict)               # handle -> structs.BTFTables
+    material_btf: dict = field(default_factory=dict)       # material -> btf handle
+    env_map: object = None                                 # six texture handles (+X -X +Y -Y +Z -Z) or None
 
     def triangle_count(self):
         return sum(len(self.geometries[g][1]) for (g, _, _, _) in self.instances.values())
@@ -323,3 +328,150 @@ def incoherent_rays_torch(n, lo, hi, seed=3, tmin=0.0, tmax=1e20, start=0, devic
         o[:, 6] = (r * torch.sin(ph)).to(torch.float32)
         o[:, 7] = tmax
     return out
+
+
+# ---- synthetic material inputs (the reference ships no textures and no BTF database) -----------------
+def checker_texture(width, height, seed=5, cells=8, alpha=None):
+    """Smooth-ish seeded RGBA image: a checker modulated by hashed per-cell colours.  (h, w, 4) float32."""
+    y, x = np.mgrid[0:height, 0:width]
+    cx, cy = (x * cells // width).astype(np.uint64), (y * cells // height).astype(np.uint64)
+    cell = cy * np.uint64(cells) + cx
+    img = np.stack([hash_uniform(seed, cell, k) for k in range(3)], axis=-1)
+    img = 0.15 + 0.8 * img * (0.6 + 0.4 * ((cx + cy) % np.uint64(2))[..., None].astype(np.float64))
+    a = np.ones((height, width, 1)) if alpha is None else np.clip(alpha, 0, 1).reshape(height, width, 1)
+    return np.concatenate([img, a], axis=-1).astype(np.float32)
+
+
+def synthetic_btf(seed=4, num_beta=13, num_alpha=7, num_theta=7, num_phi=16, texels=(256, 256), n_pdf1d=4096,
+                  n_colors=512, n_index=1024, n_pdf2d_color=512, n_pdf2d_lum=1024, n_pdf2d=2048, n_pdf3d=1024,
+                  n_pdf4d=512, **params):
+    """Random but valid MLVQ database honouring the loader's table shapes (CompressedBTF.cpp:339-377): every index
+    table points inside the table below it; luminance slices are smooth positive curves; scales are near 1."""
+    from . import structs as S
+
+    def u(shape, salt):
+        n = int(np.prod(shape))
+        return hash_uniform(seed, np.arange(n, dtype=np.uint64), salt).reshape(shape)
+
+    def idx(shape, hi, salt, base=0):
+        return (np.minimum((u(shape, salt) * hi).astype(np.int64), hi - 1) + base).astype(np.int32)
+
+    beta = np.linspace(-1.0, 1.0, num_beta)
+    amp, width = 40.0 + 160.0 * u((n_pdf1d, 1), 1), 0.3 + 1.2 * u((n_pdf1d, 1), 2)
+    centre = 0.6 * (u((n_pdf1d, 1), 3) - 0.5)
+    pdf1d = amp * np.exp(-((beta[None, :] - centre) / width) ** 2) + 8.0 * u((n_pdf1d, num_beta), 4)
+    tables = dict(
+        pdf1d_basis=pdf1d,
+        colors=np.concatenate([90.0 + 70.0 * u((n_colors, 1), 5), 100.0 + 60.0 * u((n_colors, 1), 6)], axis=1),  # Cb, Cr
+        index_ab=idx((n_index, num_beta), n_colors, 7),
+        pdf2d_colors=idx((n_pdf2d_color, num_alpha), n_index, 8),
+        pdf2d_slices=idx((n_pdf2d_lum, num_alpha), n_pdf1d, 9),
+        pdf2d_scales=0.7 + 0.6 * u((n_pdf2d_lum, num_alpha), 10),
+        pdf2d_indices=np.stack([idx((n_pdf2d,), n_pdf2d_lum, 11), idx((n_pdf2d,), n_pdf2d_color, 12)], axis=1),
+        pdf3d_slices=idx((n_pdf3d, num_theta), n_pdf2d, 13),
+        pdf3d_scales=0.8 + 0.4 * u((n_pdf3d, num_theta), 14),
+        pdf4d_slices=idx((n_pdf4d, num_phi), n_pdf3d, 15),
+        pdf4d_scales=0.8 + 0.4 * u((n_pdf4d, num_phi), 16),
+        pdf6_slices=idx(texels, n_pdf4d, 17, base=1),  # 1-based (PDF6D.cuh:88)
+        pdf6_scales=0.8 + 0.4 * u(texels, 18),
+    )
+    return S.BTFTables(tables, **params)
+
+
+def write_btf_folder(folder, btf, material="synth"):
+    """Writes a BTFTables database in the reference's on-disk folder format (all_materialInfo.txt,
+    <material>_materialInfo.txt, 13 'rows cols min max' ASCII tables; CompressedBTF.cpp:7-50, 109-228, 284-377)."""
+    import os
+    os.makedirs(folder, exist_ok=True)
+    t, p = btf.t, btf.params
+    nb, na = t["pdf1d_basis"].shape[1], t["pdf2d_slices"].shape[1]
+    nt, nph = t["pdf3d_slices"].shape[1], t["pdf4d_slices"].shape[1]
+    hdr_value = p["hdr_value"] if p["hdr"] else 1.0
+    info = f"{material} in out tmp {p['rows_offset']} {p['cols_offset']} {t['pdf6_slices'].shape[0]} {t['pdf6_slices'].shape[1]} {hdr_value:.9g}\n"
+    with open(os.path.join(folder, "all_materialInfo.txt"), "w") as f:
+        f.write("synthetic_btf_base\n1\n1\n1\n0\n0\n")          # name, loadMaterials, maxMaterials, allInOne, 34view, compact
+        f.write("3\n81\n81\n256\n")                              # ncolour nview nillu tileSize
+        f.write(f"{p['use_cos_beta']} {nb} 0 {na} 0 {nt} 0 {nph} 0 0 0 {p['code_btf_flag']}\n")
+        f.write("0 0 0 0 0 0 0 0 0 0\n0 0 0 0 0 0 0 0 0 0\n")
+        f.write("0 0.1 0.1 0.1 0.1 0.1 0.1 0.1 0.1 0.1 0.1 0.1\n")
+        f.write(info)
+    with open(os.path.join(folder, f"{material}_materialInfo.txt"), "w") as f:
+        f.write(info)
+    names = {"pdf6_slices": f"{material}_PDF6Dslices.txt", "pdf6_scales": f"{material}_PDF6Dscale.txt",
+             "pdf1d_basis": "all_PDF1Dslice.txt", "colors": "all_colors.txt", "index_ab": "all_indexAB.txt",
+             "pdf2d_colors": "all_PDF2Dcolours.txt", "pdf2d_slices": "all_PDF2Dslices.txt",
+             "pdf2d_scales": "all_PDF2Dscale.txt", "pdf2d_indices": "all_PDF2Dindices.txt",
+             "pdf3d_scales": "all_PDF3Dscale.txt", "pdf3d_slices": "all_PDF3Dslices.txt",
+             "pdf4d_scales": "all_PDF4Dscale.txt", "pdf4d_slices": "all_PDF4Dslices.txt"}
+    for k, fn in names.items():
+        a = t[k]
+        with open(os.path.join(folder, fn), "w") as f:
+            if a.dtype.kind == "i":
+                f.write(f"{a.shape[0]} {a.shape[1]} {int(a.min())} {int(a.max())}\n")
+                for row in a:
+                    f.write(" ".join(str(int(v)) for v in row) + " \n")
+            else:
+                f.write(f"{a.shape[0]} {a.shape[1]} {float(a.min()):.9g} {float(a.max()):.9g}\n")
+                for row in a:
+                    f.write(" ".join(f"{float(v):.9g}" for v in row) + " \n")
+
+
+def _quad(cx, cy, cz, ex, ez, tilt_deg=0.0, uv_scale=1.0, n=4, seed=0):
+    """n x n grid quad centred at (cx,cy,cz), half extents (ex, ez), tilted about x; uv in [0, uv_scale]; per-vertex
+    hashed colours; analytic tangent = d(position)/du."""
+    g = np.linspace(-1.0, 1.0, n + 1)
+    u, v = np.meshgrid(g, g, indexing="xy")
+    t = math.radians(tilt_deg)
+    px, py, pz = u * ex, -v * ez * math.sin(t), v * ez * math.cos(t)
+    pos = np.stack([px.ravel() + cx, py.ravel() + cy, pz.ravel() + cz], axis=1)
+    nrm = np.tile(np.array([0.0, math.cos(t), math.sin(t)]), (len(pos), 1))
+    tan = np.tile(np.array([1.0, 0.0, 0.0]), (len(pos), 1))
+    uv = np.stack([(u.ravel() + 1) / 2 * uv_scale, (v.ravel() + 1) / 2 * uv_scale], axis=1)
+    idx = np.arange(len(pos), dtype=np.uint64)
+    col = np.stack([hash_uniform(seed, idx, k) for k in range(3)] + [np.ones(len(pos))], axis=1)
+    verts = make_vertices(pos, nrm, uv=uv, tangent=tan)
+    verts["color"] = col.astype(np.float32)
+    tris = []
+    for j in range(n):
+        for i in range(n):
+            a = j * (n + 1) + i
+            tris += [[a, a + n + 2, a + 1], [a, a + n + 1, a + n + 2]]
+    return verts, np.array(tris, dtype=np.uint32)
+
+
+def materials_scene(seed=9, btf=None):
+    """Small scene exercising every material input: textured Default (albedo + normal + metallic + roughness maps, uv
+    beyond [0,1] for the wrap mode), VertexColor, CompressedBTF, and a Default material whose albedo texture carries
+    alpha < 1 (stochastic any-hit).  Textures 1..5, BTF 1, cube map faces 11..16."""
+    from . import structs as S
+    sd = SceneDesc()
+    sd.geometries[1] = _quad(0.0, 0.0, 0.0, 1.5, 1.5, uv_scale=3.0, n=6, seed=seed)           # ground
+    sd.geometries[2] = _quad(-0.5, 0.45, 0.1, 0.45, 0.45, tilt_deg=25.0, n=5, seed=seed + 1)    # vertex colours
+    sd.geometries[3] = _quad(0.55, 0.5, -0.2, 0.5, 0.5, tilt_deg=-20.0, uv_scale=2.0, n=5, seed=seed + 2)  # BTF
+    sd.geometries[4] = _quad(0.0, 0.95, 0.0, 0.9, 0.9, uv_scale=1.0, n=3, seed=seed + 3)       # alpha-textured canopy
+    sd.materials[1] = Material(albedo=(0.8, 0.8, 0.8), metallic=0.2, roughness=0.7)
+    sd.materials[2] = Material(albedo=(0.1, 0.1, 0.1), metallic=0.0, roughness=1.0, material_type=S.MAT_VERTEX_COLOR)
+    sd.materials[3] = Material(material_type=S.MAT_COMPRESSED_BTF)
+    sd.materials[4] = Material(albedo=(0.2, 0.7, 0.3), metallic=0.0, roughness=0.9, emission=0.05)
+    for k in (1, 2, 3, 4):
+        sd.instances[k] = (k, k, IDENTITY.copy(), 100 + k)
+    sd.textures[1] = checker_texture(32, 16, seed=seed)
+    nm = checker_texture(16, 16, seed=seed + 1)
+    nm[..., 0:2] = 0.5 + 0.3 * (nm[..., 0:2] - 0.5)
+    nm[..., 2] = 0.9
+    sd.textures[2] = nm
+    sd.textures[3] = checker_texture(8, 8, seed=seed + 2, cells=4)
+    sd.textures[4] = checker_texture(8, 4, seed=seed + 3, cells=4)
+    yy, xx = np.mgrid[0:16, 0:16]
+    alpha = 0.15 + 0.8 * hash_uniform(seed + 4, (yy * 16 + xx).astype(np.uint64), 0)
+    sd.textures[5] = checker_texture(16, 16, seed=seed + 5, alpha=alpha)
+    sd.material_textures[1] = (1, 2, 3, 4)
+    sd.material_textures[4] = (5, 0, 0, 0)
+    sd.btfs[1] = btf if btf is not None else synthetic_btf(seed=4, texels=(32, 32), n_pdf1d=256, n_colors=64, n_index=128,
+                                                            n_pdf2d_color=64, n_pdf2d_lum=128, n_pdf2d=256, n_pdf3d=128,
+                                                            n_pdf4d=64)
+    sd.material_btf[3] = 1
+    for k in range(6):
+        sd.textures[11 + k] = checker_texture(8, 8, seed=seed + 20 + k, cells=4)
+    sd.env_map = [11, 12, 13, 14, 15, 16]
+    return sd

@@ -142,3 +142,59 @@ DBG_DTYPES = {DBG_REF_TRI: np.dtype("<u4"), DBG_REF_BOX: np.dtype("<f4"),
               DBG_BIN_PARENT: np.dtype("<i4"), DBG_BIN_BOXES: np.dtype("<f4"), DBG_WIDE_NODES: NODE_DTYPE,
               DBG_WIDE_TRIS: TRI_DTYPE, DBG_FLAT_POS: np.dtype("<f4"), DBG_FLAT_NRM: np.dtype("<f4"),
               DBG_FLAT_INST: np.dtype("<u4"), DBG_SCENE_BOUNDS: np.dtype("<f4")}
+
+
+class BTFDesc(C.Structure):
+    """rtf_btf_desc (include/rtf/rtf.h): scalars + host pointers to the 13 tables of CompressedBTF::ImportFromFolder
+    (/root/reference/src/RayTracerFacility/MLVQ/CompressedBTF.cpp:339-377)."""
+    _fields_ = [("use_cos_beta", i32), ("num_beta", i32), ("num_alpha", i32), ("num_theta", i32), ("num_phi", i32),
+                ("code_btf_flag", i32), ("hdr", i32), ("hdr_value", f32), ("multiplier", f32),
+                ("tex_coord_multiplier", f32), ("gamma", f32), ("rows_offset", i32), ("cols_offset", i32),
+                ("pdf6_rows", i32), ("pdf6_cols", i32), ("n_pdf1d", i32), ("n_colors", i32), ("n_channels", i32),
+                ("n_index_slices", i32), ("n_pdf2d_color", i32), ("n_pdf2d_lum", i32), ("n_pdf2d", i32),
+                ("pdf2d_slice_len", i32), ("n_pdf3d", i32), ("n_pdf4d", i32),
+                ("pdf6_slices", C.c_void_p), ("pdf6_scales", C.c_void_p), ("pdf1d_basis", C.c_void_p),
+                ("colors", C.c_void_p), ("index_ab", C.c_void_p), ("pdf2d_colors", C.c_void_p),
+                ("pdf2d_slices", C.c_void_p), ("pdf2d_scales", C.c_void_p), ("pdf2d_indices", C.c_void_p),
+                ("pdf3d_scales", C.c_void_p), ("pdf3d_slices", C.c_void_p), ("pdf4d_scales", C.c_void_p),
+                ("pdf4d_slices", C.c_void_p)]
+
+
+BTF_INT_TABLES = ("pdf6_slices", "index_ab", "pdf2d_colors", "pdf2d_slices", "pdf2d_indices", "pdf3d_slices", "pdf4d_slices")
+BTF_FLOAT_TABLES = ("pdf6_scales", "pdf1d_basis", "colors", "pdf2d_scales", "pdf3d_scales", "pdf4d_scales")
+
+
+class BTFTables:
+    """A compressed-BTF database as numpy tables (2-D, row-major) + scalar parameters; desc() builds the ABI record
+    (the arrays stay referenced by this object)."""
+
+    def __init__(self, tables, use_cos_beta=True, code_btf_flag=0, hdr=False, hdr_value=1.0, multiplier=1.0,
+                 tex_coord_multiplier=1.0, gamma=2.2, rows_offset=0, cols_offset=0):
+        self.t = {}
+        for k in BTF_INT_TABLES:
+            self.t[k] = np.ascontiguousarray(tables[k], dtype=np.int32)
+        for k in BTF_FLOAT_TABLES:
+            self.t[k] = np.ascontiguousarray(tables[k], dtype=np.float32)
+        self.params = dict(use_cos_beta=int(use_cos_beta), code_btf_flag=int(code_btf_flag), hdr=int(hdr),
+                           hdr_value=float(hdr_value), multiplier=float(multiplier),
+                           tex_coord_multiplier=float(tex_coord_multiplier), gamma=float(gamma),
+                           rows_offset=int(rows_offset), cols_offset=int(cols_offset))
+
+    def desc(self):
+        t, d = self.t, BTFDesc()
+        for k, v in self.params.items():
+            setattr(d, k, v)
+        d.num_beta, d.num_alpha = t["pdf1d_basis"].shape[1], t["pdf2d_slices"].shape[1]
+        d.num_theta, d.num_phi = t["pdf3d_slices"].shape[1], t["pdf4d_slices"].shape[1]
+        d.pdf6_rows, d.pdf6_cols = t["pdf6_slices"].shape
+        d.n_pdf1d = t["pdf1d_basis"].shape[0]
+        d.n_colors, d.n_channels = t["colors"].shape
+        d.n_index_slices = t["index_ab"].shape[0]
+        d.n_pdf2d_color = t["pdf2d_colors"].shape[0]
+        d.n_pdf2d_lum = t["pdf2d_slices"].shape[0]
+        d.n_pdf2d, d.pdf2d_slice_len = t["pdf2d_indices"].shape
+        d.n_pdf3d = t["pdf3d_slices"].shape[0]
+        d.n_pdf4d = t["pdf4d_slices"].shape[0]
+        for k in BTF_INT_TABLES + BTF_FLOAT_TABLES:
+            setattr(d, k, t[k].ctypes.data)
+        return d
