@@ -344,6 +344,12 @@ RTF_API int rtf_camera_resize(rtf_camera* cam, int width, int height);   /* Came
 RTF_API int rtf_camera_set(rtf_camera* cam, const float position[3], const float rotation_wxyz[4]);
 /* returns 1 rendered / 0 no acceleration structure (bool of the reference) or <0 error */
 RTF_API int rtf_render_camera(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* ray_props);
+/* Same call restricted to image rows [row_begin, row_end): pixels keep their global index, so their
+ * RNG streams and values are those of the full-frame render; rows outside the band keep their
+ * previous contents.  This is how image bands are split across GPUs (the reference is single-GPU,
+ * CUDAModule.cpp:25). */
+RTF_API int rtf_render_camera_rows(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* ray_props,
+                                   int row_begin, int row_end);
 /* which: RTF_OUT_COLOR / NORMAL / ALBEDO(also depth when output_type == DEPTH); host float4 per pixel */
 RTF_API int rtf_camera_download(rtf_camera* cam, int which, float* host_rgba);
 RTF_API int rtf_camera_device_buffer(rtf_camera* cam, int which, float** dev_rgba);

@@ -661,12 +661,16 @@ struct CamLast {
 };
 static std::map<rtf_ctx*, CamLast> g_cam_last;  // m_cameraRenderingLaunchParams.m_rayTracerProperties, RayTracer.cu:259-266
 
-int rtf_render_camera(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp) {
-  CHECK_CTX(ctx);
+static int render_camera_rows(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, int row_begin,
+                              int row_end) {
   if (!env || !cam || !rp) return RTF_ERR_INVALID;
   rtf_camera_props& p = cam->props;
   if (p.width == 0 || p.height == 0) return 1;  // RayTracer.cu:246-247
   if (!ctx->ready) return 0;                    // RayTracer.cu:248-249
+  if (row_begin < 0 || row_end > p.height || row_begin > row_end) {
+    set_error("rtf_render_camera_rows: bad row range");
+    return RTF_ERR_INVALID;
+  }
   CamLast& last = g_cam_last[ctx];
   bool changed = p.modified != 0;
   p.modified = 0;
@@ -674,12 +678,22 @@ int rtf_render_camera(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const r
   if (!last.valid || last.rp.bounces != rp->bounces || last.rp.samples != rp->samples) last.rp = *rp, changed = true;
   last.valid = true;
   if (!p.accumulate || changed) p.frame_id = 0;  // RayTracer.cu:266-269
-  int rc = render_camera_device(ctx, env, cam, rp);  // launch sees the frame id before the increment (RayTracer.cu:349-352)
+  // the launch sees the frame id before the increment (RayTracer.cu:349-352)
+  int rc = render_camera_device(ctx, env, cam, rp, (uint64_t)row_begin * p.width, (uint64_t)row_end * p.width);
   if (rc) return rc;
   p.frame_id++;
   RTF_CUDA(cudaStreamSynchronize(ctx->stream));
   if ((rc = fetch_stats(ctx))) return rc;
   return 1;
+}
+int rtf_render_camera(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp) {
+  CHECK_CTX(ctx);
+  return render_camera_rows(ctx, env, cam, rp, 0, cam ? cam->props.height : 0);
+}
+int rtf_render_camera_rows(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, int row_begin,
+                           int row_end) {
+  CHECK_CTX(ctx);
+  return render_camera_rows(ctx, env, cam, rp, row_begin, row_end);
 }
 int rtf_camera_device_buffer(rtf_camera* cam, int which, float** dev) {
   if (!cam || !dev) return RTF_ERR_INVALID;

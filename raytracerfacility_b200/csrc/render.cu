@@ -796,10 +796,14 @@ __global__ void __launch_bounds__(256)
   normal[pixel] = make_float4(pn.x, pn.y, pn.z, 1.0f);
 }
 
-int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp) {
+int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, uint64_t px_begin,
+                         uint64_t px_end) {
   const rtf_camera_props& cp = cam->props;
-  const uint64_t n_pixels = (uint64_t)cp.width * (uint64_t)cp.height;
-  if (n_pixels == 0 || rp->samples <= 0) return RTF_OK;
+  const uint64_t all_pixels = (uint64_t)cp.width * (uint64_t)cp.height;
+  if (px_end > all_pixels) px_end = all_pixels;
+  ctx->last_paths = 0;
+  if (px_begin >= px_end || rp->samples <= 0) return RTF_OK;
+  const uint64_t n_pixels = px_end;  // the loop below runs over [px_begin, px_end)
   if (env->environmental_map_id != 0 && env->lighting_type == RTF_ENV_SCENE && ctx->scene.env_faces == nullptr) {
     set_error("environmental_map_id != 0 but no cube map is registered (rtf_set_environment_map, then rtf_commit)");
     return RTF_ERR_INVALID;
@@ -814,7 +818,7 @@ int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, cons
   bind(ctx, q, ps, true);
   const uint64_t px_per_batch = cap / spp;
   RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, ctx->stream));
-  for (uint64_t p0 = 0; p0 < n_pixels; p0 += px_per_batch) {
+  for (uint64_t p0 = px_begin; p0 < n_pixels; p0 += px_per_batch) {
     const uint32_t np = (uint32_t)((n_pixels - p0) < px_per_batch ? (n_pixels - p0) : px_per_batch);
     const size_t paths = (size_t)np * spp;
     RTF_CUDA(cudaMemsetAsync(ctx->ws.counters.p, 0, 4096, ctx->stream));
@@ -825,7 +829,7 @@ int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, cons
            cam->normal.as<float4>(), cam->albedo.as<float4>());
   }
   RTF_CUDA(cudaGetLastError());
-  ctx->last_paths = n_pixels * spp;
+  ctx->last_paths = (px_end - px_begin) * spp;
   return RTF_OK;
 }
 

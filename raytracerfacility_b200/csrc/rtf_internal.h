@@ -202,7 +202,8 @@ int illum_finalize_device(rtf_ctx* ctx, float* d_accum6, uint64_t n, int faces, 
 int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin, uint64_t ray_end, float* d_t,
                      uint32_t* d_prim, uint32_t* d_inst);
 int scan_samples_device(rtf_ctx* ctx, rtf_pc_sample* d_samples, size_t n, uint32_t* d_prim);
-int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp);
+int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, uint64_t px_begin,
+                         uint64_t px_end);
 int sample_texture_device(rtf_ctx* ctx, const DevTexture& tex, size_t n, const float* d_uv, float* d_rgba);
 int sample_environment_device(rtf_ctx* ctx, const rtf_env* env, size_t n, const float* d_pos_dir6, float* d_rgb);
 int btf_eval_device(rtf_ctx* ctx, const DevBTF& btf, size_t n, const float* d_in14, float* d_rgb);

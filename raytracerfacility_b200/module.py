@@ -32,7 +32,7 @@ EXPORTS = [
     "rtf_last_job_stats", "rtf_scan_point_cloud", "rtf_scan_grid_ray_count", "rtf_scan_grid_trace",
     "rtf_scan_grid_trace_device", "rtf_trace_closest", "rtf_trace_closest_device", "rtf_trace_closest_counts",
     "rtf_camera_create", "rtf_camera_destroy", "rtf_camera_get_props", "rtf_camera_resize", "rtf_camera_set",
-    "rtf_render_camera", "rtf_camera_download", "rtf_camera_device_buffer", "rtf_debug_size", "rtf_debug_read",
+    "rtf_render_camera", "rtf_render_camera_rows", "rtf_camera_download", "rtf_camera_device_buffer", "rtf_debug_size", "rtf_debug_read",
     "rtf_debug_upload_bvh", "rtf_microbench_fp32", "rtf_microbench_l2", "rtf_build_timings", "rtf_set_option",
     "rtf_set_texture", "rtf_remove_texture", "rtf_set_material_textures", "rtf_set_environment_map", "rtf_sample_texture",
     "rtf_sample_environment", "rtf_set_btf", "rtf_btf_import_folder", "rtf_remove_btf", "rtf_set_material_btf",
@@ -343,6 +343,12 @@ class RayTracer:
     def render_to_camera(self, env, camera, ray_props):
         """Returns True when a frame was rendered, False when there is no acceleration structure."""
         return _check(lib().rtf_render_camera(self.h, C.byref(env), camera.h, C.byref(ray_props))) == 1
+
+    def render_to_camera_rows(self, env, camera, ray_props, row_begin, row_end):
+        """RenderToCamera for the image rows [row_begin, row_end) only (multi-GPU bands); same pixel values as the
+        full-frame call."""
+        return _check(lib().rtf_render_camera_rows(self.h, C.byref(env), camera.h, C.byref(ray_props), int(row_begin),
+                                                   int(row_end))) == 1
 
     # ---- parity read-back ----
     def debug(self, what):

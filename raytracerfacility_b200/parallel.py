@@ -136,3 +136,82 @@ class DistributedRayTracer:
             dist.broadcast(full_t[rb:re], src=r, group=self.group)
             dist.broadcast(full_p[rb:re], src=r, group=self.group)
         return (0, total), full_t, full_p
+
+
+# ---- camera: interleaved row bands (load balance: sky rows are cheap, canopy rows are not) + ONE all-gather --------
+BAND_ROWS = 8
+
+
+def camera_bands(height, world, rank, band_rows=BAND_ROWS):
+    """Row ranges [(r0, r1), ...] rendered by `rank`: bands of `band_rows` rows dealt round-robin."""
+    n_bands = (int(height) + band_rows - 1) // band_rows
+    return [(b * band_rows, min((b + 1) * band_rows, int(height))) for b in range(rank, n_bands, world)]
+
+
+def image_bands_sharded(height, width, channels, render_rows, all_gather_into, world, rank, frame, band_rows=BAND_ROWS):
+    """frame: (height, width, channels) float32 tensor that render_rows(r0, r1) fills for its rows (in place).
+    all_gather_into(out, local) gathers equal-size tensors from all ranks into out[world, ...].  Returns the full frame,
+    identical on all ranks and bit-identical to a single-rank render (pixels keep their global RNG streams)."""
+    import torch
+    for r0, r1 in camera_bands(height, world, rank, band_rows):
+        render_rows(r0, r1)
+    if world == 1:
+        return frame
+    n_bands = (height + band_rows - 1) // band_rows
+    k = (n_bands + world - 1) // world  # bands per rank, padded
+    local = torch.zeros((k, band_rows, width, channels), dtype=frame.dtype, device=frame.device)
+    for j, (r0, r1) in enumerate(camera_bands(height, world, rank, band_rows)):
+        local[j, :r1 - r0] = frame[r0:r1]
+    gathered = torch.empty((world, k, band_rows, width, channels), dtype=frame.dtype, device=frame.device)
+    all_gather_into(gathered, local)
+    # band b = j * world + r lives at gathered[r, j]
+    full = gathered.permute(1, 0, 2, 3, 4).reshape(k * world * band_rows, width, channels)
+    frame.copy_(full[:height])
+    return frame
+
+
+class _DeviceArray:
+    """Zero-copy torch view of a raw device pointer (__cuda_array_interface__)."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+def _camera_frame_tensor(camera, which, device):
+    import torch
+    h, w = camera.props.height, camera.props.width
+    return torch.as_tensor(_DeviceArray(camera.device_buffer(which), (h, w, 4)), device=device)
+
+
+def render_to_camera_sharded(drt, env, camera, ray_props, outputs=(0,)):
+    """DistributedRayTracer camera render: every rank renders its interleaved row bands into its own camera buffers,
+    then one all-gather per requested output (structs.OUT_COLOR / OUT_NORMAL / OUT_ALBEDO) completes the frame on all
+    ranks.  Progressive accumulation state stays rank-local per band."""
+    import torch
+    import torch.distributed as dist
+    rt = drt.rt
+    dev = torch.device("cuda", rt.device)
+    h, w = camera.props.height, camera.props.width
+    bands = camera_bands(h, drt.world, drt.rank)
+    frame_id, modified = camera.props.frame_id, camera.props.modified
+    ok = True
+    for i, (r0, r1) in enumerate(bands):
+        # every band of one frame must see the same frame id / modified flag (the C call advances them per call)
+        camera.props.modified = modified if i == 0 else 0
+        if i > 0:
+            camera.props.frame_id = first_frame_id
+        ok = rt.render_to_camera_rows(env, camera, ray_props, r0, r1) and ok
+        if i == 0:
+            first_frame_id = camera.props.frame_id - 1
+    if not bands:
+        rt.render_to_camera_rows(env, camera, ray_props, 0, 0)
+    if drt.world > 1:
+        for which in outputs:
+            frame = _camera_frame_tensor(camera, which, dev)
+            image_bands_sharded(h, w, 4, lambda r0, r1: None,
+                                lambda out, local: dist.all_gather_into_tensor(out, local, group=drt.group), drt.world,
+                                drt.rank, frame)
+    return ok
+
+
+DistributedRayTracer.render_to_camera = render_to_camera_sharded

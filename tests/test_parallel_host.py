@@ -92,3 +92,47 @@ def test_world2_gloo_sharded_illumination(tmp_path, orc, S, scenes):
     t0, t1 = np.load(tmp_path / "tri_0.npy"), np.load(tmp_path / "tri_1.npy")
     assert np.array_equal(t0.view(np.uint32), single.view(np.uint32))  # triangle sharding: bit-identical to 1 rank
     assert np.array_equal(t1.view(np.uint32), single.view(np.uint32))
+
+
+def _camera_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    from oracle import pyoracle as orc
+    from raytracerfacility_b200 import parallel, scenes, structs as S
+    from tests.golden.make_golden import camera_props
+    parallel.init_distributed("gloo")
+    osc = orc.OracleScene(scenes.random_soup(300, seed=11, extent=1.0, size=0.35))
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=2, samples=2)
+    cp = camera_props(20, 27)  # 27 rows: 4 bands of 8 rows (the last one ragged), dealt round-robin over 2 ranks
+    frame = torch.zeros((27, 20, 4), dtype=torch.float32)
+
+    def render_rows(r0, r1):
+        col, _, _, _ = osc.camera(env, rp, cp, pixel_begin=r0 * 20, pixel_end=r1 * 20, nthreads=1)
+        frame[r0:r1] = torch.from_numpy(col.reshape(r1 - r0, 20, 4))
+
+    def all_gather_into(out, local):  # gloo: list form (NCCL uses all_gather_into_tensor in the product)
+        parts = [torch.empty_like(local) for _ in range(world)]
+        dist.all_gather(parts, local)
+        out.copy_(torch.stack(parts))
+
+    parallel.image_bands_sharded(27, 20, 4, render_rows, all_gather_into, world, rank, frame)
+    np.save(os.path.join(out_dir, f"cam_{rank}.npy"), frame.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_world2_gloo_camera_bands(tmp_path, orc, S, scenes):
+    from raytracerfacility_b200.parallel import camera_bands
+    from tests.golden.make_golden import camera_props
+    for h in (1, 8, 27, 1080, 2160):
+        for w in (1, 2, 4, 8):
+            rows = sorted(r for k in range(w) for b in camera_bands(h, w, k) for r in range(*b))
+            assert rows == list(range(h))  # every row rendered exactly once
+    world = 2
+    mp.spawn(_camera_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    osc = orc.OracleScene(scenes.random_soup(300, seed=11, extent=1.0, size=0.35))
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=2, samples=2)
+    col, _, _, _ = osc.camera(env, rp, camera_props(20, 27))
+    c0, c1 = np.load(tmp_path / "cam_0.npy"), np.load(tmp_path / "cam_1.npy")
+    assert np.array_equal(c0.view(np.uint32), c1.view(np.uint32))
+    assert np.array_equal(c0.reshape(-1, 4).view(np.uint32), col.view(np.uint32))  # bit-identical to one rank
