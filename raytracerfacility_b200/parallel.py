@@ -170,6 +170,11 @@ def image_bands_sharded(height, width, channels, render_rows, all_gather_into, w
     return frame
 
 
+def default_band_rows(height, world):
+    """16 bands per rank: enough interleaving to balance sky against canopy, few enough calls to keep batches large."""
+    return int(height) if world == 1 else max(BAND_ROWS, int(height) // (16 * world))
+
+
 class _DeviceArray:
     """Zero-copy torch view of a raw device pointer (__cuda_array_interface__)."""
 
@@ -192,8 +197,9 @@ def render_to_camera_sharded(drt, env, camera, ray_props, outputs=(0,)):
     rt = drt.rt
     dev = torch.device("cuda", rt.device)
     h, w = camera.props.height, camera.props.width
-    bands = camera_bands(h, drt.world, drt.rank)
-    frame_id, modified = camera.props.frame_id, camera.props.modified
+    band_rows = default_band_rows(h, drt.world)
+    bands = camera_bands(h, drt.world, drt.rank, band_rows)
+    modified = camera.props.modified
     ok = True
     for i, (r0, r1) in enumerate(bands):
         # every band of one frame must see the same frame id / modified flag (the C call advances them per call)
@@ -210,7 +216,7 @@ def render_to_camera_sharded(drt, env, camera, ray_props, outputs=(0,)):
             frame = _camera_frame_tensor(camera, which, dev)
             image_bands_sharded(h, w, 4, lambda r0, r1: None,
                                 lambda out, local: dist.all_gather_into_tensor(out, local, group=drt.group), drt.world,
-                                drt.rank, frame)
+                                drt.rank, frame, band_rows)
     return ok
 
 
