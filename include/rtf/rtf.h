@@ -171,8 +171,10 @@ typedef struct rtf_scan_grid {
   float distance[2];  /* m_distance */
 } rtf_scan_grid;
 
-/* BRDF model.  RTF_BRDF_REFERENCE = mirror-lobe of BSDF.cuh:6-13 + RF.cuh:152-161. */
-enum { RTF_BRDF_REFERENCE = 0 };
+/* BRDF model of the surface materials, rtf_set_option(ctx, "brdf", ...).  RTF_BRDF_REFERENCE = mirror lobe of
+ * BSDF.cuh:6-13 + RF.cuh:152-161 (the reference's only model).  RTF_BRDF_LAMBERT_GGX (BASELINE config 2) = importance-
+ * sampled Lambert + GGX (Schlick Fresnel, Smith G); a new capability, checked against its own closed forms only. */
+enum { RTF_BRDF_REFERENCE = 0, RTF_BRDF_LAMBERT_GGX = 1 };
 
 typedef struct rtf_ctx rtf_ctx;
 typedef struct rtf_camera rtf_camera;
@@ -212,7 +214,8 @@ RTF_API int rtf_build_timings(rtf_ctx* ctx, float* ms_out, int n);
 /* Tuning knobs (not in the reference): "batch_paths" = wavefront batch capacity in paths,
  * "sort_rays" = 0/1 sort bounce rays by (direction octant, origin cell) before tracing,
  * "presplit" = most references a long thin triangle may be cut into before the Morton sort
- * (default 8, 1 = off; applies at the next rtf_commit; hits do not depend on it). */
+ * (default 8, 1 = off; applies at the next rtf_commit; hits do not depend on it),
+ * "brdf" = RTF_BRDF_REFERENCE (default) or RTF_BRDF_LAMBERT_GGX. */
 RTF_API int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value);
 
 /* ---- images in linear memory ---------------------------------------------------------------

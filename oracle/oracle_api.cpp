@@ -87,6 +87,7 @@ ORC_API int orc_scene_add_instance(Scene* s, int geom, int mat, const float* xfo
 }
 ORC_API void orc_scene_commit(Scene* s, int bits, int presplit) { commit(*s, bits == 30 ? 30 : 63, presplit < 1 ? 1 : presplit); }
 ORC_API uint64_t orc_scene_nrefs(Scene* s) { return s->bvh.nref; }
+ORC_API void orc_scene_set_brdf(Scene* s, int brdf) { s->brdf = brdf; }
 ORC_API uint64_t orc_scene_ntris(Scene* s) { return s->tri_inst.size(); }
 ORC_API uint64_t orc_scene_nnodes(Scene* s) { return s->bvh.nodes.size(); }
 ORC_API int orc_scene_depth(Scene* s) { return s->bvh.depth; }
@@ -379,4 +380,14 @@ ORC_API void orc_btf_beta_angles(Scene* s, int btf, float* out) {
 }
 ORC_API void orc_inverse_trig(int n, const float* y, const float* x, float* atan2_out, float* asin_out, float* acos_out) {
   for (int i = 0; i < n; i++) atan2_out[i] = atan2p(y[i], x[i]), asin_out[i] = asinp(y[i]), acos_out[i] = acosp(y[i]);
+}
+ORC_API void orc_sample_lambert_ggx(int n, const float* albedo3, float metallic, float roughness, const float* normal3,
+                                    const float* view3, const float* r3, float* weight3, float* dir3) {
+  for (int i = 0; i < n; i++) {
+    V3 l;
+    V3 w = sample_lambert_ggx(v3(albedo3[0], albedo3[1], albedo3[2]), metallic, roughness, v3(normal3[0], normal3[1], normal3[2]),
+                              v3(view3[0], view3[1], view3[2]), r3[3 * i], r3[3 * i + 1], r3[3 * i + 2], l);
+    weight3[3 * i] = w.x, weight3[3 * i + 1] = w.y, weight3[3 * i + 2] = w.z;
+    dir3[3 * i] = l.x, dir3[3 * i + 1] = l.y, dir3[3 * i + 2] = l.z;
+  }
 }

@@ -48,6 +48,7 @@ struct Scene {
   std::vector<Texture> textures;
   std::vector<BTF> btfs;
   int env_faces[6] = {-1, -1, -1, -1, -1, -1};  // cube map of the Scene lighting type (+X -X +Y -Y +Z -Z)
+  int brdf = RTF_BRDF_REFERENCE;                // option "brdf"
   std::vector<Instance> insts;
   // flattened, commit order (global primitive id)
   std::vector<float> pos9, nrm9;
@@ -204,6 +205,62 @@ static inline V3 env_light(V3 position, V3 dir, const rtf_env& env, const Scene*
     c = v3(powf(c.x, ig), powf(c.y, ig), powf(c.z, ig));
   }
   return vmax(v3(0, 0, 0), c);
+}
+
+// Lambert + GGX importance sampling (option "brdf" = RTF_BRDF_LAMBERT_GGX, BASELINE config 2).  Not in the reference (its
+// only BRDF is the mirror lobe, BSDF.cuh:6-13): cosine-weighted Lambert with albedo*(1-metallic)*0.96, GGX visible-normal
+// sampling, Schlick Fresnel with F0 = mix(0.04, albedo, metallic), separable Smith G, p_spec = (1 + metallic)/2.
+// Validated against its own closed forms in tests/ (nothing in the reference to compare with).
+static inline V3 sample_lambert_ggx(V3 albedo, float metallic, float roughness, V3 n, V3 v, float r0, float r1, float r2,
+                                    V3& l) {
+  const float p_spec = 0.5f + 0.5f * clampf(metallic, 0.0f, 1.0f);
+  const float nv = dot(n, v);
+  if (r2 >= p_spec) {
+    l = to_world(n, sqrtf(1.0f - r0), r1);
+    const float k = ((1.0f - metallic) * 0.96f) / (1.0f - p_spec);
+    return albedo * k;
+  }
+  // specular lobe: GGX distribution of visible normals (Heitz 2018) — the weight F * G1(l) never exceeds 1
+  if (!(nv > 0.0f)) return v3(0.0f, 0.0f, 0.0f);
+  const float a = fmaxf(roughness * roughness, 1e-3f), a2 = a * a;
+  V3 helper = v3(1.0f, 0.0f, 0.0f);
+  if (fabsf(n.x) > 0.99f) helper = v3(0.0f, 0.0f, 1.0f);
+  const V3 tx = normalize(cross(n, helper)), ty = normalize(cross(n, tx));
+  const float vx = dot(v, tx), vy = dot(v, ty);
+  // stretch the view vector, build an orthonormal basis around it
+  const float sx = a * vx, sy = a * vy;
+  const float inv_len = 1.0f / sqrtf((sx * sx + sy * sy) + nv * nv);
+  const float hx = sx * inv_len, hy = sy * inv_len, hz = nv * inv_len;
+  const float lensq = hx * hx + hy * hy;
+  float t1x = 1.0f, t1y = 0.0f;
+  if (lensq > 0.0f) {
+    const float il = 1.0f / sqrtf(lensq);
+    t1x = -hy * il, t1y = hx * il;
+  }
+  const float t2x = -hz * t1y, t2y = hz * t1x, t2z = hx * t1y - hy * t1x;  // cross(Vh, T1)
+  // sample the projected disk, warp the half that faces away
+  const float rr = sqrtf(r0);
+  float sn, cs;
+  sincos2pi(r1, &sn, &cs);
+  const float p1 = rr * cs;
+  float p2 = rr * sn;
+  const float sw = 0.5f * (1.0f + hz);
+  p2 = (1.0f - sw) * sqrtf(fmaxf(0.0f, 1.0f - p1 * p1)) + sw * p2;
+  const float p3 = sqrtf(fmaxf(0.0f, (1.0f - p1 * p1) - p2 * p2));
+  const float nhx = (p1 * t1x + p2 * t2x) + p3 * hx, nhy = (p1 * t1y + p2 * t2y) + p3 * hy, nhz = p2 * t2z + p3 * hz;
+  // unstretch
+  const float ex = a * nhx, ey = a * nhy, ez = fmaxf(0.0f, nhz);
+  const float ie = 1.0f / sqrtf((ex * ex + ey * ey) + ez * ez);
+  const V3 h = (tx * (ex * ie) + ty * (ey * ie)) + n * (ez * ie);
+  const float vh = dot(v, h);
+  l = (2.0f * vh) * h - v;
+  const float nl = dot(n, l);
+  if (!(nl > 0.0f) || !(vh > 0.0f)) return v3(0.0f, 0.0f, 0.0f);
+  const float g1l = (2.0f * nl) / (nl + sqrtf(a2 + (1.0f - a2) * (nl * nl)));
+  const float m = 1.0f - vh, m2 = m * m, m5 = (m2 * m2) * m;
+  const V3 f0 = v3(0.04f, 0.04f, 0.04f) * (1.0f - metallic) + albedo * metallic;
+  const V3 fr = f0 + (v3(1.0f, 1.0f, 1.0f) - f0) * m5;
+  return fr * (g1l / p_spec);
 }
 
 // ---- hit reconstruction: RDD.hpp:127-164 (TriangularMesh::GetHitInfo) + :364-382 (SBT::GetHitInfo) ----
@@ -438,11 +495,18 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
       break;
     } else if ((int)hit_count <= bounces) {  // RF.cuh:93-161 (BSSRDF branch off: subsurfaceFactor == 0 only)
       path_rng(seed, STREAM_PATH, unit, hit_count, 0, r);
-      V3 refl = reflect(d, normal);
-      V3 nd = sample_lobe(r[0], r[1], refl, metallic);
-      float k = clampf(fabsf(dot(normal, nd)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
-      V3 wgt = ((1.0f - m.subsurface_factor) * albedo) * k;
-      acc = acc + T * emis;
+      V3 nd, wgt;
+      if (sc.brdf == RTF_BRDF_LAMBERT_GGX) {
+        wgt = sample_lambert_ggx(albedo, metallic, roughness, normal, neg(d), r[0], r[1], r[2], nd);
+        acc = acc + T * emis;
+        if (wgt.x == 0.0f && wgt.y == 0.0f && wgt.z == 0.0f) break;  // absorbed
+      } else {
+        V3 refl = reflect(d, normal);
+        nd = sample_lobe(r[0], r[1], refl, metallic);
+        float k = clampf(fabsf(dot(normal, nd)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
+        wgt = ((1.0f - m.subsurface_factor) * albedo) * k;
+        acc = acc + T * emis;
+      }
       T = T * wgt;
       o = sh.position, d = nd, tmin = 1e-3f;
       continue;

@@ -82,6 +82,15 @@ def sample_lobe(r0, r1, n, alpha):
     return np.array(out[:], dtype=np.float32)
 
 
+def sample_lambert_ggx(albedo, metallic, roughness, normal, view, r3):
+    """(weights, directions) of oracle_shade.h's sample_lambert_ggx for n triples of uniforms."""
+    r3 = np.ascontiguousarray(r3, dtype=np.float32).reshape(-1, 3)
+    a, nrm, v = (np.ascontiguousarray(x, dtype=np.float32) for x in (albedo, normal, view))
+    w, d = np.empty_like(r3), np.empty_like(r3)
+    lib().orc_sample_lambert_ggx(len(r3), _p(a), C.c_float(metallic), C.c_float(roughness), _p(nrm), _p(v), _p(r3), _p(w), _p(d))
+    return w, d
+
+
 def inverse_trig(y, x):
     """Portable atan2(y, x), asin(y), acos(y) of oracle_math.h."""
     y, x = np.ascontiguousarray(y, dtype=np.float32), np.ascontiguousarray(x, dtype=np.float32)
@@ -143,6 +152,9 @@ class OracleScene:
                 self.h = None
         except Exception:
             pass
+
+    def set_brdf(self, brdf):
+        lib().orc_scene_set_brdf(self.h, int(brdf))
 
     def sample_texture(self, handle, uv):
         uv = np.ascontiguousarray(uv, dtype=np.float32).reshape(-1, 2)

@@ -296,6 +296,12 @@ int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value) {
       return RTF_ERR_INVALID;
     }
     ctx->presplit = (int)value;  // takes effect at the next rtf_commit
+  } else if (!strcmp(name, "brdf")) {
+    if (value != RTF_BRDF_REFERENCE && value != RTF_BRDF_LAMBERT_GGX) {
+      set_error("brdf must be RTF_BRDF_REFERENCE (0) or RTF_BRDF_LAMBERT_GGX (1)");
+      return RTF_ERR_INVALID;
+    }
+    ctx->brdf = (int)value;
   } else if (!strcmp(name, "sort_rays")) {
     ctx->sort_rays = value != 0;
   } else {

@@ -211,6 +211,7 @@ struct ShadeParams {
   int bounces;
   uint32_t seed;
   int camera;
+  int brdf;  // RTF_BRDF_REFERENCE / RTF_BRDF_LAMBERT_GGX
 };
 __global__ void __launch_bounds__(256)
     k_shade(DevScene sc, rtf_env env, ShadeParams sp, PathMap pm, Queues q, int qi, int wave, PathState ps) {
@@ -336,17 +337,24 @@ __global__ void __launch_bounds__(256)
           ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
         } else if ((int)hit_count <= sp.bounces) {  // RayFunctions.cuh:93-161, BSSRDF branch off (factor 0)
           const float4 r = path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
-          const float3 refl = reflect3(d, normal);
-          const float3 nd = sample_lobe(r.x, r.y, refl, metallic);  // BRDF(), BSDF.cuh:6-13
-          const float k = clampf(fabsf(dot3(normal, nd)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
-          const float3 wgt = ((1.0f - m.subsurface_factor) * albedo) * k;
+          float3 nd, wgt;
+          if (sp.brdf == RTF_BRDF_LAMBERT_GGX) {
+            wgt = sample_lambert_ggx(albedo, metallic, roughness, normal, neg3(d), r.x, r.y, r.z, nd);
+          } else {
+            const float3 refl = reflect3(d, normal);
+            nd = sample_lobe(r.x, r.y, refl, metallic);  // BRDF(), BSDF.cuh:6-13
+            const float k = clampf(fabsf(dot3(normal, nd)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
+            wgt = ((1.0f - m.subsurface_factor) * albedo) * k;
+          }
           acc = acc + T * emis;
-          T = T * wgt;
           ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
-          ps.thr[p] = make_float4(T.x, T.y, T.z, __uint_as_float(hit_count));
-          emit = true;
-          na = make_float4(sh.position.x, sh.position.y, sh.position.z, __uint_as_float(p));  // origin not offset, RayFunctions.cuh:138
-          nb = make_float4(nd.x, nd.y, nd.z, 1e20f);
+          if (!(wgt.x == 0.0f && wgt.y == 0.0f && wgt.z == 0.0f)) {  // (only the GGX lobe can absorb a sample)
+            T = T * wgt;
+            ps.thr[p] = make_float4(T.x, T.y, T.z, __uint_as_float(hit_count));
+            emit = true;
+            na = make_float4(sh.position.x, sh.position.y, sh.position.z, __uint_as_float(p));  // origin not offset, RayFunctions.cuh:138
+            nb = make_float4(nd.x, nd.y, nd.z, 1e20f);
+          }
         } else {
           acc = acc + T * emis;
           ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
@@ -527,7 +535,7 @@ static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_
     set_error("too many bounces");
     return RTF_ERR_INVALID;
   }
-  ShadeParams sp{bounces, seed, camera ? 1 : 0};
+  ShadeParams sp{bounces, seed, camera ? 1 : 0, ctx->brdf};
   unsigned long long* stats = ctx->d_stats.as<unsigned long long>();
   const unsigned tgrid = trace_grid(ctx, paths);
   int qi = 0;

@@ -174,6 +174,7 @@ struct rtf_ctx {
   // options (rtf_set_option)
   size_t batch_paths = (size_t)1 << 24;  // 2^24 paths: ~3 GB of queues + path state; +12..20 % over 2^22 (fewer, fuller waves)
   int sort_rays = 1;
+  int brdf = RTF_BRDF_REFERENCE;  // option "brdf"
   // build-stage events: flatten | bounds+morton | sort | karras+refit | collapse | end
   cudaEvent_t build_ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   float build_ms[6] = {0, 0, 0, 0, 0, 0};

@@ -157,4 +157,63 @@ RTF_HD float3 sample_lobe(float r0, float r1, float3 n, float alpha) {
   return to_world(n, cos_theta, r1);
 }
 
+// ---- Lambert + GGX importance sampling (option "brdf" = RTF_BRDF_LAMBERT_GGX; BASELINE config 2) ----------------------
+// Not in the reference (its only BRDF is the mirror lobe above, BSDF.cuh:6-13): diffuse = cosine-weighted Lambert with
+// albedo*(1-metallic)*0.96, specular = GGX microfacet (Trowbridge-Reitz, visible-normal sampling, Schlick Fresnel
+// with F0 = mix(0.04, albedo, metallic), separable Smith G), lobe chosen with probability p_spec = (1 + metallic)/2.
+// Only + - * / sqrt and the portable sincos: bit-identical on host and device.  r = three uniforms (direction 2, lobe 1);
+// v = direction towards the viewer (= -ray direction), n = shading normal facing v.  Returns the path weight
+// f*cos/pdf (0 = absorbed) and the new direction in `l`.
+RTF_HD float3 sample_lambert_ggx(float3 albedo, float metallic, float roughness, float3 n, float3 v, float r0, float r1,
+                                 float r2, float3& l) {
+  const float p_spec = 0.5f + 0.5f * clampf(metallic, 0.0f, 1.0f);
+  const float nv = dot3(n, v);
+  if (r2 >= p_spec) {  // diffuse lobe: cos(theta) = sqrt(1 - r0)
+    l = to_world(n, sqrtf(1.0f - r0), r1);
+    const float k = ((1.0f - metallic) * 0.96f) / (1.0f - p_spec);
+    return albedo * k;
+  }
+  // specular lobe: GGX distribution of visible normals (Heitz 2018) — the weight F * G1(l) never exceeds 1
+  if (!(nv > 0.0f)) return f3(0.0f, 0.0f, 0.0f);
+  const float a = fmaxf(roughness * roughness, 1e-3f), a2 = a * a;
+  float3 helper = f3(1.0f, 0.0f, 0.0f);
+  if (fabsf(n.x) > 0.99f) helper = f3(0.0f, 0.0f, 1.0f);
+  const float3 tx = normalize3(cross3(n, helper)), ty = normalize3(cross3(n, tx));
+  const float vx = dot3(v, tx), vy = dot3(v, ty);
+  // stretch the view vector, build an orthonormal basis around it
+  const float sx = a * vx, sy = a * vy;
+  const float inv_len = 1.0f / sqrtf((sx * sx + sy * sy) + nv * nv);
+  const float hx = sx * inv_len, hy = sy * inv_len, hz = nv * inv_len;
+  const float lensq = hx * hx + hy * hy;
+  float t1x = 1.0f, t1y = 0.0f;
+  if (lensq > 0.0f) {
+    const float il = 1.0f / sqrtf(lensq);
+    t1x = -hy * il, t1y = hx * il;
+  }
+  const float t2x = -hz * t1y, t2y = hz * t1x, t2z = hx * t1y - hy * t1x;  // cross(Vh, T1)
+  // sample the projected disk, warp the half that faces away
+  const float rr = sqrtf(r0);
+  float sn, cs;
+  sincos2pi(r1, sn, cs);
+  const float p1 = rr * cs;
+  float p2 = rr * sn;
+  const float sw = 0.5f * (1.0f + hz);
+  p2 = (1.0f - sw) * sqrtf(fmaxf(0.0f, 1.0f - p1 * p1)) + sw * p2;
+  const float p3 = sqrtf(fmaxf(0.0f, (1.0f - p1 * p1) - p2 * p2));
+  const float nhx = (p1 * t1x + p2 * t2x) + p3 * hx, nhy = (p1 * t1y + p2 * t2y) + p3 * hy, nhz = p2 * t2z + p3 * hz;
+  // unstretch
+  const float ex = a * nhx, ey = a * nhy, ez = fmaxf(0.0f, nhz);
+  const float ie = 1.0f / sqrtf((ex * ex + ey * ey) + ez * ez);
+  const float3 h = (tx * (ex * ie) + ty * (ey * ie)) + n * (ez * ie);
+  const float vh = dot3(v, h);
+  l = (2.0f * vh) * h - v;
+  const float nl = dot3(n, l);
+  if (!(nl > 0.0f) || !(vh > 0.0f)) return f3(0.0f, 0.0f, 0.0f);
+  const float g1l = (2.0f * nl) / (nl + sqrtf(a2 + (1.0f - a2) * (nl * nl)));
+  const float m = 1.0f - vh, m2 = m * m, m5 = (m2 * m2) * m;
+  const float3 f0 = f3(0.04f, 0.04f, 0.04f) * (1.0f - metallic) + albedo * metallic;
+  const float3 fr = f0 + (f3(1.0f, 1.0f, 1.0f) - f0) * m5;
+  return fr * (g1l / p_spec);
+}
+
 }  // namespace rtf

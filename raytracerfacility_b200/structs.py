@@ -42,6 +42,7 @@ class Atmosphere(C.Structure):
 ENV_SCENE, ENV_SKYDOME, ENV_SINGLE_LIGHT_SOURCE = 0, 1, 2
 MAT_DEFAULT, MAT_VERTEX_COLOR, MAT_COMPRESSED_BTF = 0, 1, 2
 OUT_COLOR, OUT_NORMAL, OUT_ALBEDO, OUT_DEPTH = 0, 1, 2, 3
+BRDF_REFERENCE, BRDF_LAMBERT_GGX = 0, 1
 
 
 class EnvironmentProperties(C.Structure):

@@ -142,3 +142,35 @@ def test_single_light_source_shadow_ray(orc, S, scenes):
     # triangle subtends most of it); misses see the sun colour 1.0.  Energy within (0.55*0.5*frac, ...] -> loose bounds
     e = probes["energy"][0, 0]
     assert 0.2 < e < 0.5
+
+
+def test_lambert_ggx_closed_forms(orc):
+    """The Lambert+GGX sampler (option brdf = 1; not in the reference, BASELINE config 2 names it): closed forms of its
+    two lobes."""
+    n, v = np.array([0, 1, 0], np.float32), np.array([0.6, 0.8, 0.0], np.float32)
+    rng = np.random.default_rng(3)
+    r = rng.random((200000, 3)).astype(np.float32)
+    alb = np.array([0.8, 0.5, 0.3], np.float32)
+    # dielectric: half the samples go to each lobe; the diffuse weight is the constant albedo * 0.96 / (1 - p_spec)
+    w, d = orc.sample_lambert_ggx(alb, 0.0, 0.6, n, v, r)
+    diff = r[:, 2] >= 0.5
+    assert np.allclose(w[diff], alb * np.float32(1.92), rtol=1e-6)
+    assert np.all(d[diff][:, 1] >= 0) and abs(d[diff][:, 1].mean() - 2.0 / 3.0) < 5e-3  # cosine-weighted: E[cos] = 2/3
+    assert np.allclose(np.linalg.norm(d[diff], axis=1), 1.0, atol=1e-5)
+    spec = ~diff
+    assert np.all(w[spec] >= 0) and w[spec].mean() < 0.3  # F0 = 0.04: a dielectric's specular albedo is small
+    # perfect conductor, white: the visible-normal sampler's weight is F * G1(l) <= 1 — no sample ever creates energy —
+    # and single-scatter GGX keeps most of the energy at low roughness
+    for rough, lo in ((0.15, 0.93), (0.5, 0.75), (1.0, 0.3)):
+        w, d = orc.sample_lambert_ggx(np.ones(3, np.float32), 1.0, rough, n, v, r)
+        assert w.max() <= 1.0 + 1e-6 and w.min() >= 0.0
+        mean = w[:, 0].mean()
+        assert lo < mean <= 1.0, (rough, mean)
+        assert np.all(d[w[:, 0] > 0][:, 1] > 0)  # reflected directions stay above the surface
+    # roughness -> 0: the sampled direction is the mirror direction
+    w, d = orc.sample_lambert_ggx(np.ones(3, np.float32), 1.0, 0.0, n, v, r[:1000])
+    mirror = 2 * (v @ n) * n - v
+    assert np.percentile(np.abs(d - mirror).max(1), 95) < 1e-2 and np.allclose(w, 1.0, atol=1e-2)
+    # grazing view below the surface is absorbed, not reflected
+    w, _ = orc.sample_lambert_ggx(np.ones(3, np.float32), 1.0, 0.5, n, np.array([0.8, -0.6, 0.0], np.float32), r[:100])
+    assert np.all(w == 0)
