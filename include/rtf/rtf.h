@@ -195,6 +195,38 @@ RTF_API uint64_t rtf_launch_count(rtf_ctx* ctx);
 RTF_API int rtf_set_geometry(rtf_ctx* ctx, uint64_t handle, const void* vertices, size_t n_vertices,
                              size_t vertex_stride_bytes, const uint32_t* triangles, size_t n_triangles,
                              uint64_t version);
+/* RendererType::Instanced geometry (RT.hpp:277-292): one mesh drawn under n_instances matrices.  The
+ * device pre-kernel restates CopyVerticesInstancedKernel (RT.cu:1148-1175): vertex k of instance i =
+ * {position = M_i*(p,1), N = normalize(M_i*(n,0)), T = normalize(M_i*(t,0)) then
+ * T = normalize(T - dot(T,N)*N), texCoord and colour copied, the instance colour in the four padding
+ * floats (position/normal/tangent padding, tex_coord_padding[0] -> HitInfo::m_data) and the instance index
+ * in tex_coord_padding[1]}; triangle j of instance i = mesh triangle j + i*n_vertices (RT.cu:1477-1487).
+ * The resulting geometry has n_instances*n_triangles triangles and is referenced by rtf_set_instance
+ * like any other.  matrices: 16 floats each, column-major; colors: 4 floats each, NULL = (1,1,1,1).
+ * Waived quirk: the reference's index vector is resize(N) THEN push_back (RT.cu:1477-1483), so its
+ * first N triples are the degenerate triangle (0,0,0) — they can never be hit (zero determinant)
+ * and are not emitted here, i.e. primitive numbering starts at the first real triangle. */
+RTF_API int rtf_set_geometry_instanced(rtf_ctx* ctx, uint64_t handle, const void* vertices, size_t n_vertices,
+                                       size_t vertex_stride_bytes, const uint32_t* triangles, size_t n_triangles,
+                                       const float* matrices, const float* colors, size_t n_instances,
+                                       uint64_t version);
+/* RendererType::Skinned geometry: device pre-kernel restating CopySkinnedVerticesKernel
+ * (RT.cu:1194-1247): boneTransform = sum_k bone[id_k]*w_k over the up-to-8 influences (the first always,
+ * the others when their id != -1), then the same position / N / T arithmetic as above; paddings,
+ * texCoord and colour copied.  rtf_skinned_vertex is UniEngine::SkinnedVertex (layout inferred, 144 B). */
+typedef struct rtf_skinned_vertex {
+  rtf_vertex v;
+  int32_t bone_id[4];
+  float weight[4];
+  int32_t bone_id2[4];
+  float weight2[4];
+} rtf_skinned_vertex;
+RTF_API int rtf_set_geometry_skinned(rtf_ctx* ctx, uint64_t handle, const void* skinned_vertices, size_t n_vertices,
+                                     size_t vertex_stride_bytes, const uint32_t* triangles, size_t n_triangles,
+                                     const float* bone_matrices, size_t n_bones, uint64_t version);
+/* Test hook: the baked (device-resident) vertices / indices of an instanced or skinned geometry. */
+RTF_API int rtf_geometry_read_baked(rtf_ctx* ctx, uint64_t handle, rtf_vertex* vertices_out, size_t n_vertices,
+                                    uint32_t* triangles_out, size_t n_triangles);
 RTF_API int rtf_set_material(rtf_ctx* ctx, uint64_t handle, const rtf_material* material);
 RTF_API int rtf_set_instance(rtf_ctx* ctx, uint64_t handle, uint64_t geometry_handle, uint64_t material_handle,
                              const float transform[16] /* column-major glm::mat4 m_globalTransform */,
@@ -312,6 +344,24 @@ RTF_API int rtf_estimate_illumination_mesh_device(rtf_ctx* ctx, const rtf_env* e
 /* energy = sum/(faces*samples); direction = normalize(D) over a device accumulator (IE.cu:125-128). */
 RTF_API int rtf_illumination_finalize_device(rtf_ctx* ctx, float* dev_accum6, uint64_t n_triangles, int faces,
                                              int samples);
+/* TriangleIlluminationEstimator::PrepareLightProbeGroup (TriangleIlluminationEstimator.cpp:94-139) on the
+ * device: the 268 B probes of committed triangles [tri_begin, tri_end) — the three mesh vertices with
+ * position = M*(p,1) and normal = M*(n,0), direction = energy = 0, the two face flags as given (the
+ * caller maps Material::m_drawSettings cull modes to them, :120-135). */
+RTF_API int rtf_prepare_light_probes(rtf_ctx* ctx, uint64_t tri_begin, uint64_t tri_end, int front_face,
+                                     int back_face, rtf_illum_sampler* probes_out /* host */);
+/* TriangleIlluminationEstimator::SampleLightProbeGroup's flux integration (:84-92):
+ * out8 = {totalFlux.xyz = sum energy*GetArea() (Heron, RT.hpp:204-210), totalArea (a two-sided probe
+ * counts twice, :124), averageFlux.xyz = totalFlux/totalArea, 0}.  The reference adds 10^7 floats
+ * serially on the host; here the terms are added in double by a fixed-shape tree (1024-term tiles:
+ * 4 strided terms per thread, xor butterfly, 8 warp sums in order; tiles reduced the same way), so the
+ * result does not depend on the GPU count or batch size and the oracle reproduces it bit for bit.
+ * rtf_illumination_flux: host probes (as returned by rtf_estimate_illumination).
+ * rtf_illumination_flux_mesh_device: finalised device array of 6 floats per committed triangle (the
+ * mesh-range entry point's output), areas from the committed world-space triangles. */
+RTF_API int rtf_illumination_flux(rtf_ctx* ctx, const rtf_illum_sampler* probes /* host */, size_t n, float* out8);
+RTF_API int rtf_illumination_flux_mesh_device(rtf_ctx* ctx, const float* dev_energy6, uint64_t tri_begin,
+                                              uint64_t tri_end, int front_face, int back_face, float* out8);
 /* Statistics of the last illumination / render call: rays traced, paths started. */
 RTF_API int rtf_last_job_stats(rtf_ctx* ctx, uint64_t* rays_traced, uint64_t* paths);
 

@@ -8,6 +8,7 @@
 #include <thread>
 #include <vector>
 
+#include "oracle_prebake.h"
 #include "oracle_shade.h"
 
 using namespace orc;
@@ -390,4 +391,23 @@ ORC_API void orc_sample_lambert_ggx(int n, const float* albedo3, float metallic,
     weight3[3 * i] = w.x, weight3[3 * i + 1] = w.y, weight3[3 * i + 2] = w.z;
     dir3[3 * i] = l.x, dir3[3 * i + 1] = l.y, dir3[3 * i + 2] = l.z;
   }
+}
+
+// ---- geometry pre-kernels, light probes, flux (oracle_prebake.h) -----------------------------------------
+ORC_API void orc_bake_instanced(const void* verts, uint64_t nv, uint64_t stride, const uint32_t* tris, uint64_t nt,
+                                const float* matrices, const float* colors, uint64_t n_inst, rtf_vertex* out_v, uint32_t* out_t) {
+  std::vector<rtf_vertex> packed(nv);
+  for (uint64_t i = 0; i < nv; i++) memcpy(&packed[i], (const char*)verts + i * stride, sizeof(rtf_vertex));
+  bake_instanced(packed.data(), nv, tris, nt, matrices, colors, n_inst, out_v, out_t);
+}
+ORC_API int orc_bake_skinned(const void* sverts, uint64_t nv, uint64_t stride, const float* bones, uint64_t n_bones,
+                             rtf_vertex* out_v) {
+  return bake_skinned((const unsigned char*)sverts, stride, nv, bones, n_bones, out_v);
+}
+ORC_API void orc_make_probes(Scene* s, uint64_t tri_begin, uint64_t tri_end, int front, int back, rtf_illum_sampler* out) {
+  make_probes(*s, tri_begin, tri_end, front, back, out);
+}
+ORC_API void orc_flux_probes(const rtf_illum_sampler* probes, uint64_t n, float* out8) { flux_probes(probes, n, out8); }
+ORC_API void orc_flux_mesh(Scene* s, const float* energy6, uint64_t tri_begin, uint64_t tri_end, int faces, float* out8) {
+  flux_mesh(*s, energy6, tri_begin, tri_end, faces, out8);
 }

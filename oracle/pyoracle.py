@@ -17,7 +17,7 @@ from raytracerfacility_b200 import structs as S  # noqa: E402  (POD layouts only
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("oracle_api.cpp", "oracle_shade.h", "oracle_bvh.h", "oracle_btf.h", "oracle_math.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_api.cpp", "oracle_prebake.h", "oracle_shade.h", "oracle_bvh.h", "oracle_btf.h", "oracle_math.h")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
     return so
@@ -217,6 +217,20 @@ class OracleScene:
                              int(normalise), _p(out), C.byref(st), nthreads)
         return out, st
 
+    def make_probes(self, tri_begin=0, tri_end=None, front=True, back=True):
+        tri_end = self.n_tris if tri_end is None else tri_end
+        out = np.zeros(max(0, tri_end - tri_begin), dtype=S.ILLUM_SAMPLER_DTYPE)
+        lib().orc_make_probes(self.h, C.c_uint64(tri_begin), C.c_uint64(tri_end), int(front), int(back), _p(out))
+        return out
+
+    def flux_mesh(self, energy6, tri_begin=0, tri_end=None, front=True, back=True):
+        tri_end = self.n_tris if tri_end is None else tri_end
+        e = np.ascontiguousarray(energy6, dtype=np.float32)
+        assert e.shape == (self.n_tris, 6)
+        out = np.zeros(8, dtype=np.float32)
+        lib().orc_flux_mesh(self.h, _p(e), C.c_uint64(tri_begin), C.c_uint64(tri_end), int(front) + int(back), _p(out))
+        return out
+
     def illum_probes(self, env, rp, probes, seed, push, nthreads=0):
         assert probes.dtype == S.ILLUM_SAMPLER_DTYPE and probes.flags.c_contiguous
         st = S.JobStats()
@@ -253,6 +267,35 @@ class OracleScene:
                          C.c_uint64(pixel_end), C.c_uint64(stride), _p(prev_color), _p(color), _p(normal), _p(albedo),
                          C.byref(st), nthreads)
         return color, normal, albedo, st
+
+
+def bake_instanced(vertices, triangles, matrices, colors=None):
+    v = np.ascontiguousarray(vertices)
+    t = np.ascontiguousarray(triangles, dtype=np.uint32).reshape(-1, 3)
+    m = np.ascontiguousarray(matrices, dtype=np.float32).reshape(-1, 16)
+    c = None if colors is None else np.ascontiguousarray(colors, dtype=np.float32).reshape(-1, 4)
+    ov = np.zeros(len(v) * len(m), dtype=S.VERTEX_DTYPE)
+    ot = np.zeros((len(t) * len(m), 3), dtype=np.uint32)
+    lib().orc_bake_instanced(_p(v), C.c_uint64(len(v)), C.c_uint64(80), _p(t), C.c_uint64(len(t)), _p(m), _p(c),
+                             C.c_uint64(len(m)), _p(ov), _p(ot))
+    return ov, ot
+
+
+def bake_skinned(skinned_vertices, bone_matrices):
+    v = np.ascontiguousarray(skinned_vertices)
+    assert v.dtype == S.SKINNED_VERTEX_DTYPE
+    b = np.ascontiguousarray(bone_matrices, dtype=np.float32).reshape(-1, 16)
+    ov = np.zeros(len(v), dtype=S.VERTEX_DTYPE)
+    rc = lib().orc_bake_skinned(_p(v), C.c_uint64(len(v)), C.c_uint64(144), _p(b), C.c_uint64(len(b)), _p(ov))
+    if rc:
+        raise ValueError("bone index out of range")
+    return ov
+
+
+def flux_probes(probes):
+    out = np.zeros(8, dtype=np.float32)
+    lib().orc_flux_probes(_p(probes), C.c_uint64(len(probes)), _p(out))
+    return out
 
 
 def scan_grid_count(grid):

@@ -128,7 +128,72 @@ int rtf_set_geometry(rtf_ctx* ctx, uint64_t handle, const void* vertices, size_t
   for (size_t i = 0; i < n_vertices; i++) memcpy(&g.verts[i], (const char*)vertices + i * stride, sizeof(rtf_vertex));
   g.tris.assign(triangles, triangles + 3 * n_triangles);
   g.version = version;
-  g.uploaded = false;
+  g.uploaded = false, g.baked = false;
+  g.n_verts = n_vertices, g.n_tris = n_triangles;
+  return RTF_OK;
+}
+int rtf_set_geometry_instanced(rtf_ctx* ctx, uint64_t handle, const void* vertices, size_t n_vertices, size_t stride,
+                               const uint32_t* triangles, size_t n_triangles, const float* matrices, const float* colors,
+                               size_t n_instances, uint64_t version) {
+  CHECK_CTX(ctx);
+  if ((!vertices && n_vertices) || (!triangles && n_triangles) || stride < sizeof(rtf_vertex) || (!matrices && n_instances)) {
+    set_error("rtf_set_geometry_instanced: bad arguments (vertex stride must be >= 80)");
+    return RTF_ERR_INVALID;
+  }
+  for (size_t i = 0; i < 3 * n_triangles; i++)
+    if (triangles[i] >= n_vertices) {
+      set_error("rtf_set_geometry_instanced: triangle index out of range");
+      return RTF_ERR_INVALID;
+    }
+  if ((uint64_t)n_vertices * n_instances >= 0xFFFFFFF0ull || (uint64_t)n_triangles * n_instances * 3 >= 0xFFFFFFF0ull) {
+    set_error("rtf_set_geometry_instanced: more than 2^32 baked vertices or indices");
+    return RTF_ERR_LIMIT;
+  }
+  std::vector<rtf_vertex> packed(n_vertices);
+  for (size_t i = 0; i < n_vertices; i++) memcpy(&packed[i], (const char*)vertices + i * stride, sizeof(rtf_vertex));
+  if (ctx->geoms.count(handle)) ctx->ready = false;  // the committed scene may point at the arrays re-baked below
+  Geometry& g = ctx->geoms[handle];
+  g.verts.clear(), g.tris.clear();
+  g.version = version;
+  g.uploaded = false, g.baked = false, g.n_verts = g.n_tris = 0;
+  return bake_instanced(ctx, g, packed.data(), n_vertices, triangles, n_triangles, matrices, colors, n_instances);
+}
+int rtf_set_geometry_skinned(rtf_ctx* ctx, uint64_t handle, const void* skinned_vertices, size_t n_vertices, size_t stride,
+                             const uint32_t* triangles, size_t n_triangles, const float* bone_matrices, size_t n_bones,
+                             uint64_t version) {
+  CHECK_CTX(ctx);
+  if ((!skinned_vertices && n_vertices) || (!triangles && n_triangles) || stride < sizeof(rtf_skinned_vertex) ||
+      (stride & 3) || (!bone_matrices && n_bones)) {
+    set_error("rtf_set_geometry_skinned: bad arguments (vertex stride must be a multiple of 4 and >= 144)");
+    return RTF_ERR_INVALID;
+  }
+  for (size_t i = 0; i < 3 * n_triangles; i++)
+    if (triangles[i] >= n_vertices) {
+      set_error("rtf_set_geometry_skinned: triangle index out of range");
+      return RTF_ERR_INVALID;
+    }
+  if (ctx->geoms.count(handle)) ctx->ready = false;  // the committed scene may point at the arrays re-baked below
+  Geometry& g = ctx->geoms[handle];
+  g.verts.clear(), g.tris.clear();
+  g.version = version;
+  g.uploaded = false, g.baked = false, g.n_verts = g.n_tris = 0;
+  return bake_skinned(ctx, g, skinned_vertices, n_vertices, stride, triangles, n_triangles, bone_matrices, n_bones);
+}
+int rtf_geometry_read_baked(rtf_ctx* ctx, uint64_t handle, rtf_vertex* verts_out, size_t n_vertices, uint32_t* tris_out,
+                            size_t n_triangles) {
+  CHECK_CTX(ctx);
+  auto it = ctx->geoms.find(handle);
+  if (it == ctx->geoms.end()) return RTF_ERR_NOT_FOUND;
+  const Geometry& g = it->second;
+  if (!g.baked || n_vertices != g.n_verts || n_triangles != g.n_tris) {
+    set_error("rtf_geometry_read_baked: not a baked geometry, or counts differ");
+    return RTF_ERR_INVALID;
+  }
+  if (verts_out && n_vertices)
+    RTF_CUDA(cudaMemcpyAsync(verts_out, g.d_verts.p, n_vertices * sizeof(rtf_vertex), cudaMemcpyDeviceToHost, ctx->stream));
+  if (tris_out && n_triangles)
+    RTF_CUDA(cudaMemcpyAsync(tris_out, g.d_tris.p, 12 * n_triangles, cudaMemcpyDeviceToHost, ctx->stream));
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
   return RTF_OK;
 }
 int rtf_set_material(rtf_ctx* ctx, uint64_t handle, const rtf_material* material) {
@@ -208,7 +273,7 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
     d.handle = in.component;
     d.mat = m->second;
     d.first_prim = (uint32_t)first;
-    d.n_prims = (uint32_t)(geo.tris.size() / 3);
+    d.n_prims = (uint32_t)geo.n_tris;
     d.pad_ = 0;
     d.verts = geo.d_verts.as<rtf_vertex>();
     d.tris = geo.d_tris.as<uint32_t>();
@@ -388,6 +453,41 @@ int rtf_estimate_illumination_mesh(rtf_ctx* ctx, const rtf_env* env, const rtf_r
   RTF_CUDA(cudaMemcpyAsync(out6, d_acc, n * 24, cudaMemcpyDeviceToHost, ctx->stream));
   RTF_CUDA(cudaStreamSynchronize(ctx->stream));
   return fetch_stats(ctx);
+}
+int rtf_prepare_light_probes(rtf_ctx* ctx, uint64_t tri_begin, uint64_t tri_end, int front, int back, rtf_illum_sampler* out) {
+  CHECK_CTX(ctx);
+  if (!ctx->ready) return not_ready();
+  if (tri_end > ctx->n_tris || tri_begin > tri_end || (!out && tri_end > tri_begin)) {
+    set_error("triangle range out of bounds");
+    return RTF_ERR_INVALID;
+  }
+  const uint64_t n = tri_end - tri_begin;
+  if (n == 0) return RTF_OK;
+  int rc;
+  if ((rc = ctx->ws.io.reserve(n * sizeof(rtf_illum_sampler)))) return rc;
+  if ((rc = make_probes_device(ctx, tri_begin, tri_end, front, back, ctx->ws.io.as<rtf_illum_sampler>()))) return rc;
+  RTF_CUDA(cudaMemcpyAsync(out, ctx->ws.io.p, n * sizeof(rtf_illum_sampler), cudaMemcpyDeviceToHost, ctx->stream));
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+  return RTF_OK;
+}
+int rtf_illumination_flux(rtf_ctx* ctx, const rtf_illum_sampler* probes, size_t n, float* out8) {
+  CHECK_CTX(ctx);
+  if (!out8 || (!probes && n)) return RTF_ERR_INVALID;
+  int rc;
+  if ((rc = ctx->ws.io.reserve(n * sizeof(rtf_illum_sampler) + 16))) return rc;
+  if (n) RTF_CUDA(cudaMemcpyAsync(ctx->ws.io.p, probes, n * sizeof(rtf_illum_sampler), cudaMemcpyHostToDevice, ctx->stream));
+  return flux_probes_device(ctx, ctx->ws.io.as<rtf_illum_sampler>(), n, out8);
+}
+int rtf_illumination_flux_mesh_device(rtf_ctx* ctx, const float* dev_energy6, uint64_t tri_begin, uint64_t tri_end, int front,
+                                      int back, float* out8) {
+  CHECK_CTX(ctx);
+  if (!out8 || !dev_energy6) return RTF_ERR_INVALID;
+  if (!ctx->ready) return not_ready();
+  if (tri_end > ctx->n_tris || tri_begin > tri_end) {
+    set_error("triangle range out of bounds");
+    return RTF_ERR_INVALID;
+  }
+  return flux_mesh_device(ctx, dev_energy6, tri_begin, tri_end, (front ? 1 : 0) + (back ? 1 : 0), out8);
 }
 int rtf_last_job_stats(rtf_ctx* ctx, uint64_t* rays, uint64_t* paths) {
   CHECK_CTX(ctx);

@@ -91,6 +91,8 @@ struct Geometry {
   uint64_t version = 0;
   DevBuf d_verts, d_tris;
   bool uploaded = false;
+  bool baked = false;            // instanced / skinned: d_verts and d_tris were produced on the device (prebake.cu)
+  size_t n_verts = 0, n_tris = 0;  // counts of the device arrays
 };
 struct Texture {
   int w = 0, h = 0;
@@ -187,6 +189,14 @@ struct rtf_camera {
 };
 
 namespace rtf {
+// prebake.cu
+int bake_instanced(rtf_ctx* ctx, Geometry& g, const rtf_vertex* verts, size_t nv, const uint32_t* tris, size_t nt,
+                   const float* matrices, const float* colors, size_t n_inst);
+int bake_skinned(rtf_ctx* ctx, Geometry& g, const void* sverts, size_t nv, size_t stride, const uint32_t* tris, size_t nt,
+                 const float* bones, size_t n_bones);
+int make_probes_device(rtf_ctx* ctx, uint64_t tri_begin, uint64_t tri_end, int front, int back, rtf_illum_sampler* d_out);
+int flux_probes_device(rtf_ctx* ctx, const rtf_illum_sampler* d_probes, uint64_t n, float* out8_host);
+int flux_mesh_device(rtf_ctx* ctx, const float* d_energy6, uint64_t tri_begin, uint64_t tri_end, int faces, float* out8_host);
 // build.cu
 int build_bvh(rtf_ctx* ctx, int morton_bits);
 // materials.cu

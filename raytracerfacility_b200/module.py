@@ -36,7 +36,8 @@ EXPORTS = [
     "rtf_debug_upload_bvh", "rtf_microbench_fp32", "rtf_microbench_l2", "rtf_build_timings", "rtf_set_option",
     "rtf_set_texture", "rtf_remove_texture", "rtf_set_material_textures", "rtf_set_environment_map", "rtf_sample_texture",
     "rtf_sample_environment", "rtf_set_btf", "rtf_btf_import_folder", "rtf_remove_btf", "rtf_set_material_btf",
-    "rtf_btf_eval",
+    "rtf_btf_eval", "rtf_set_geometry_instanced", "rtf_set_geometry_skinned", "rtf_geometry_read_baked",
+    "rtf_prepare_light_probes", "rtf_illumination_flux", "rtf_illumination_flux_mesh_device",
 ]
 
 
@@ -148,6 +149,35 @@ class RayTracer:
         t = np.ascontiguousarray(triangles, dtype=np.uint32).reshape(-1, 3)
         _check(lib().rtf_set_geometry(self.h, C.c_uint64(handle), _p(v), C.c_size_t(len(v)), C.c_size_t(80), _p(t),
                                       C.c_size_t(len(t)), C.c_uint64(version)))
+
+    def set_geometry_instanced(self, handle, vertices, triangles, matrices, colors=None, version=0):
+        """RendererType::Instanced geometry: device bake of CopyVerticesInstancedKernel (RayTracer.cu:1148-1175)."""
+        v = np.ascontiguousarray(vertices)
+        assert v.dtype == S.VERTEX_DTYPE
+        t = np.ascontiguousarray(triangles, dtype=np.uint32).reshape(-1, 3)
+        m = np.ascontiguousarray(matrices, dtype=np.float32).reshape(-1, 16)
+        c = None if colors is None else np.ascontiguousarray(colors, dtype=np.float32).reshape(-1, 4)
+        assert c is None or len(c) == len(m)
+        _check(lib().rtf_set_geometry_instanced(self.h, C.c_uint64(handle), _p(v), C.c_size_t(len(v)), C.c_size_t(80),
+                                                _p(t), C.c_size_t(len(t)), _p(m), _p(c), C.c_size_t(len(m)),
+                                                C.c_uint64(version)))
+
+    def set_geometry_skinned(self, handle, skinned_vertices, triangles, bone_matrices, version=0):
+        """RendererType::Skinned geometry: device bake of CopySkinnedVerticesKernel (RayTracer.cu:1194-1247)."""
+        v = np.ascontiguousarray(skinned_vertices)
+        assert v.dtype == S.SKINNED_VERTEX_DTYPE
+        t = np.ascontiguousarray(triangles, dtype=np.uint32).reshape(-1, 3)
+        b = np.ascontiguousarray(bone_matrices, dtype=np.float32).reshape(-1, 16)
+        _check(lib().rtf_set_geometry_skinned(self.h, C.c_uint64(handle), _p(v), C.c_size_t(len(v)), C.c_size_t(144),
+                                              _p(t), C.c_size_t(len(t)), _p(b), C.c_size_t(len(b)),
+                                              C.c_uint64(version)))
+
+    def read_baked_geometry(self, handle, n_vertices, n_triangles):
+        v = np.zeros(n_vertices, dtype=S.VERTEX_DTYPE)
+        t = np.zeros((n_triangles, 3), dtype=np.uint32)
+        _check(lib().rtf_geometry_read_baked(self.h, C.c_uint64(handle), _p(v), C.c_size_t(n_vertices), _p(t),
+                                             C.c_size_t(n_triangles)))
+        return v, t
 
     def set_material(self, handle, material):
         _check(lib().rtf_set_material(self.h, C.c_uint64(handle), C.byref(material)))
@@ -288,6 +318,27 @@ class RayTracer:
     def illumination_finalize_device(self, dev_accum6_ptr, n_triangles, faces, samples):
         _check(lib().rtf_illumination_finalize_device(self.h, C.c_void_p(dev_accum6_ptr), C.c_uint64(n_triangles),
                                                       int(faces), int(samples)))
+
+    def prepare_light_probes(self, tri_begin=0, tri_end=None, front=True, back=True):
+        """TriangleIlluminationEstimator::PrepareLightProbeGroup on the device."""
+        tri_end = self.triangle_count if tri_end is None else tri_end
+        out = np.zeros(max(0, tri_end - tri_begin), dtype=S.ILLUM_SAMPLER_DTYPE)
+        _check(lib().rtf_prepare_light_probes(self.h, C.c_uint64(tri_begin), C.c_uint64(tri_end), int(front), int(back),
+                                              _p(out)))
+        return out
+
+    def illumination_flux(self, probes):
+        """SampleLightProbeGroup's flux integration: {totalFlux[3], totalArea, averageFlux[3], 0}."""
+        assert probes.dtype == S.ILLUM_SAMPLER_DTYPE and probes.flags.c_contiguous
+        out = np.zeros(8, dtype=np.float32)
+        _check(lib().rtf_illumination_flux(self.h, _p(probes), C.c_size_t(len(probes)), _p(out)))
+        return out
+
+    def illumination_flux_mesh_device(self, dev_energy6_ptr, tri_begin, tri_end, front=True, back=True):
+        out = np.zeros(8, dtype=np.float32)
+        _check(lib().rtf_illumination_flux_mesh_device(self.h, C.c_void_p(dev_energy6_ptr), C.c_uint64(tri_begin),
+                                                       C.c_uint64(tri_end), int(front), int(back), _p(out)))
+        return out
 
     def last_job_stats(self):
         r, p = C.c_uint64(), C.c_uint64()

@@ -131,7 +131,10 @@ NODE_DTYPE = np.dtype([("p", "<f4", 3), ("e", "u1", 3), ("imask", "u1"), ("child
                        ("meta", "u1", 8), ("qlo", "u1", (3, 8)), ("qhi", "u1", (3, 8))])
 TRI_DTYPE = np.dtype([("v0", "<f4", 3), ("prim", "<u4"), ("v1", "<f4", 3), ("inst", "<u4"), ("v2", "<f4", 3),
                       ("flags", "<u4")])
-assert VERTEX_DTYPE.itemsize == 80 and ILLUM_SAMPLER_DTYPE.itemsize == 268
+# UniEngine::SkinnedVertex (layout inferred from CopySkinnedVerticesKernel, RayTracer.cu:1194-1247): 144 B
+SKINNED_VERTEX_DTYPE = np.dtype([("v", VERTEX_DTYPE), ("bone_id", "<i4", 4), ("weight", "<f4", 4), ("bone_id2", "<i4", 4),
+                                 ("weight2", "<f4", 4)])
+assert VERTEX_DTYPE.itemsize == 80 and ILLUM_SAMPLER_DTYPE.itemsize == 268 and SKINNED_VERTEX_DTYPE.itemsize == 144
 assert PC_SAMPLE_DTYPE.itemsize == 112 and NODE_DTYPE.itemsize == 80 and TRI_DTYPE.itemsize == 48
 
 DBG_MORTON, DBG_SORTED_IDS, DBG_BIN_CHILDREN, DBG_BIN_PARENT, DBG_BIN_BOXES = 0, 1, 2, 3, 4
