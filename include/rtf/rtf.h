@@ -124,7 +124,15 @@ typedef struct rtf_ray_props {
 enum { RTF_MAT_DEFAULT = 0, RTF_MAT_VERTEX_COLOR = 1, RTF_MAT_COMPRESSED_BTF = 2 };
 
 /* The MaterialProperties fields the path reads (RF.cuh:97-98,122-123,152,170; RDD.hpp:250-264)
- * + RayTracedMaterial::m_materialType (RT.hpp:248). */
+ * + RayTracedMaterial::m_materialType (RT.hpp:248).
+ * BSSRDF (RF.cuh:97-133, BSSDF.cuh:42-89): with subsurface_factor > 0 and subsurface_radius[0] > 0 the
+ * FIRST hit of a path probes the same object (private component handle) from a disk of that radius
+ * above the surface; if the drawn record lies within the radius, a second radiance path leaves the
+ * surface there (weight factor*subsurface_color*k), traced BEFORE the ordinary bounce, and — as in the
+ * reference, whose two paths share PerRayData::m_hitCount — the bounce path continues from the hit
+ * count the subsurface path ended with.  Deviation (documented in csrc/rtf_sss.cuh): the reference's
+ * record set depends on the order in which OptiX reports any-hit candidates; here it is the up-to-four
+ * nearest same-handle intersections, which is a function of the scene alone. */
 typedef struct rtf_material {
   int32_t material_type;
   float albedo_color[3];
@@ -429,6 +437,11 @@ RTF_API int rtf_debug_read(rtf_ctx* ctx, int what, void* host_out, uint64_t byte
 RTF_API int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* wide_nodes, uint64_t n_nodes, const void* wide_tris,
                                  uint64_t n_tris, int depth);
 /* microbenchmarks for the roofline denominators BASELINE.md asks the builder to measure */
+/* Test hook: the BSSRDF spatial probe (SSAnyHit / BSSRDF, BSSDF.cuh:18-89) on its own.  rays: n x
+ * {o.xyz, tmin, d.xyz, tmax}; handles: the private component handle each probe is restricted to;
+ * out17: per probe {n_records, prim[4], t[4], u[4], v[4]} (float bits) = the up-to-four nearest
+ * same-handle intersections in [tmin, tmax], ascending (t, prim).  See rtf_material.subsurface_*. */
+RTF_API int rtf_sss_probe(rtf_ctx* ctx, const float* rays, const uint64_t* handles, size_t n, uint32_t* out17);
 RTF_API int rtf_microbench_fp32(rtf_ctx* ctx, double* tflops);
 RTF_API int rtf_microbench_l2(rtf_ctx* ctx, double bytes_footprint, double* gbs);
 

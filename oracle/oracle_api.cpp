@@ -411,3 +411,21 @@ ORC_API void orc_flux_probes(const rtf_illum_sampler* probes, uint64_t n, float*
 ORC_API void orc_flux_mesh(Scene* s, const float* energy6, uint64_t tri_begin, uint64_t tri_end, int faces, float* out8) {
   flux_mesh(*s, energy6, tri_begin, tri_end, faces, out8);
 }
+
+// ---- BSSRDF spatial probe (oracle_sss.h) -------------------------------------------------------------------
+ORC_API void orc_sss_probe(Scene* s, const float* rays, const uint64_t* handles, uint64_t n, uint32_t* out17, int brute) {
+  auto handle_of = [&](uint32_t inst) { return s->insts[inst].handle; };
+  for (uint64_t i = 0; i < n; i++) {
+    const float* r = rays + 8 * i;
+    const V3 o = v3(r[0], r[1], r[2]), d = v3(r[4], r[5], r[6]);
+    const SSRecords rec = brute ? ss_probe_brute(s->bvh, o, d, r[3], r[7], handles[i], handle_of)
+                                : ss_probe(s->bvh, o, d, r[3], r[7], handles[i], handle_of);
+    uint32_t* out = out17 + 17 * i;
+    out[0] = (uint32_t)rec.n;
+    for (int k = 0; k < 4; k++) out[1 + k] = rec.prim[k], out[5 + k] = f2u(rec.t[k]), out[9 + k] = f2u(rec.u[k]), out[13 + k] = f2u(rec.v[k]);
+  }
+}
+ORC_API void orc_rotate_about(const float* v, float u_turns, const float* axis, float* out) {
+  const V3 r = rotate_about(v3(v[0], v[1], v[2]), u_turns, v3(axis[0], axis[1], axis[2]));
+  out[0] = r.x, out[1] = r.y, out[2] = r.z;
+}

@@ -98,7 +98,7 @@ static inline void philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], u
 static inline float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
 
 // RNG streams (key[1])
-enum { STREAM_PATH = 0, STREAM_ALPHA = 1, STREAM_CAMERA = 2 };
+enum { STREAM_PATH = 0, STREAM_ALPHA = 1, STREAM_CAMERA = 2, STREAM_SSS = 3 };
 
 static inline void path_rng(uint32_t seed, uint32_t stream, uint64_t unit, uint32_t bounce, uint32_t extra,
                             float r[4]) {

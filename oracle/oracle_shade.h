@@ -22,6 +22,7 @@
 #include "../include/rtf/rtf.h"
 #include "oracle_btf.h"
 #include "oracle_bvh.h"
+#include "oracle_sss.h"
 
 namespace orc {
 
@@ -381,6 +382,20 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
   V3 T = v3(1, 1, 1), acc = v3(0, 0, 0);
   uint32_t hit_count = 0;
   bool any_hit_enabled = true;  // BTF bounce rays run with OPTIX_RAY_FLAG_DISABLE_ANYHIT (RF.cuh:239)
+  // BSSRDF (RF.cuh:97-133): the first hit may start TWO radiance paths, the subsurface one first.  Both share
+  // PerRayData::m_hitCount, which is never reset: the ordinary bounce path is traced after the subsurface path has
+  // returned and starts from the hit count the subsurface path ended with.
+  struct {
+    bool on = false;
+    V3 o, d, T;
+  } pend;
+  auto resume = [&]() -> bool {
+    if (!pend.on) return false;
+    pend.on = false;
+    o = pend.o, d = pend.d, T = pend.T, tmin = 1e-3f;
+    any_hit_enabled = true;
+    return true;
+  };
   for (;;) {
     Ray ray{o, tmin, d, 1e20f};
     Hit h;
@@ -396,6 +411,7 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
       V3 L = env_light(o, d, env, &sc);
       acc = acc + T * L;
       if (hit_count == 0) pr.albedo = L;  // MissFunc: m_albedo = m_energy = env colour
+      if (resume()) continue;
       break;
     }
     hit_count++;
@@ -441,6 +457,7 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
       }
       if (hit_count == 1) pr.normal = sh.normal, pr.albedo = btf_color, pr.position = sh.position, pr.first_hit = true;
       if (go_on) continue;
+      if (resume()) continue;
       break;
     }
     // ---- surface materials, RF.cuh:44-172 ----
@@ -493,25 +510,76 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
       }
       acc = acc + T * emis;
       break;
-    } else if ((int)hit_count <= bounces) {  // RF.cuh:93-161 (BSSRDF branch off: subsurfaceFactor == 0 only)
+    } else if ((int)hit_count <= bounces) {  // RF.cuh:93-161
+      // ---- BSSRDF, RF.cuh:97-133 + BSSDF.cuh:42-89 ----
+      bool need_sample = false;
+      V3 ss_o = v3(0, 0, 0), ss_d = v3(0, 0, 0), ss_w = v3(0, 0, 0);
+      if (hit_count <= 1 && m.subsurface_factor > 0.0f && m.subsurface_radius[0] > 0.0f) {
+        const float radius = m.subsurface_radius[0];
+        float rs[4], rb[4];
+        path_rng(seed, STREAM_SSS, unit, hit_count, 0, rs);
+        path_rng(seed, STREAM_SSS, unit, hit_count, 1, rb);
+        const V3 disk_center = sh.position + (radius * normal) * 0.5f;
+        const float disk_radius = radius * sqrtf(rs[0]);
+        const float distance = sqrtf(radius * radius - disk_radius * disk_radius);
+        const V3 sample_pos = disk_center + disk_radius * rotate_about(v3(normal.y, normal.z, normal.x), rs[1], normal);
+        const uint64_t handle = sc.insts[sh.inst].handle;
+        const SSRecords rec = ss_probe(sc.bvh, sample_pos, neg(normal), distance, radius + distance, handle,
+                                       [&](uint32_t inst) { return sc.insts[inst].handle; });
+        if (rec.n > 0) {
+          int index = (int)(rs[2] * (float)rec.n);
+          index = index < 0 ? 0 : (index > rec.n - 1 ? rec.n - 1 : index);
+          Hit rh{rec.t[index], rec.u[index], rec.v[index], rec.prim[index]};
+          const SurfaceHit so = surface_hit(sc, rh, v3(0, 0, 0));  // GetHitInfo(rayDirection, false): no flip
+          V3 out_n = so.normal;
+          const uint32_t omi = sc.insts[so.inst].mat;
+          const MatExtra& omx = mat_extra(sc, omi);
+          if (omx.tex[1] >= 0) {  // ApplyNormalTexture of the record's own material (BSSDF.cuh:31-32)
+            const HitAttrs oa = hit_attrs(sc, rh.prim, rh.u, rh.v, so.inst);
+            float t[4];
+            tex2d(sc.textures[omx.tex[1]], oa.u, oa.v, t);
+            V3 B = cross(out_n, oa.tangent);
+            V3 tn = v3(t[0] * 2.0f - 1.0f, t[1] * 2.0f - 1.0f, t[2] * 2.0f - 1.0f);
+            out_n = normalize((oa.tangent * tn.x + B * tn.y) + out_n * tn.z);
+          }
+          if (length(sh.position - so.position) <= radius) {
+            ss_o = so.position + out_n * 0.01f;
+            ss_d = sample_lobe(rb[0], rb[1], reflect(neg(out_n), out_n), metallic);  // BRDF(metallic, rnd, -n, n)
+            const float k2 = clampf(fabsf(dot(out_n, ss_d)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
+            ss_w = (m.subsurface_factor * v3(m.subsurface_color[0], m.subsurface_color[1], m.subsurface_color[2])) * k2;
+            need_sample = true;
+          }
+        }
+      }
       path_rng(seed, STREAM_PATH, unit, hit_count, 0, r);
       V3 nd, wgt;
+      bool absorbed = false;
       if (sc.brdf == RTF_BRDF_LAMBERT_GGX) {
         wgt = sample_lambert_ggx(albedo, metallic, roughness, normal, neg(d), r[0], r[1], r[2], nd);
-        acc = acc + T * emis;
-        if (wgt.x == 0.0f && wgt.y == 0.0f && wgt.z == 0.0f) break;  // absorbed
       } else {
         V3 refl = reflect(d, normal);
         nd = sample_lobe(r[0], r[1], refl, metallic);
         float k = clampf(fabsf(dot(normal, nd)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
         wgt = ((1.0f - m.subsurface_factor) * albedo) * k;
-        acc = acc + T * emis;
+      }
+      absorbed = wgt.x == 0.0f && wgt.y == 0.0f && wgt.z == 0.0f;  // a zero-weight ray is not traced (result unchanged)
+      acc = acc + T * emis;
+      if (need_sample) {  // subsurface path first; the bounce waits for it
+        if (!absorbed) pend.on = true, pend.o = sh.position, pend.d = nd, pend.T = T * wgt;
+        T = T * ss_w;
+        o = ss_o, d = ss_d, tmin = 1e-3f;
+        continue;
+      }
+      if (absorbed) {
+        if (resume()) continue;
+        break;
       }
       T = T * wgt;
       o = sh.position, d = nd, tmin = 1e-3f;
       continue;
     } else {
       acc = acc + T * emis;
+      if (resume()) continue;
       break;
     }
   }

@@ -17,7 +17,7 @@ from raytracerfacility_b200 import structs as S  # noqa: E402  (POD layouts only
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("oracle_api.cpp", "oracle_prebake.h", "oracle_shade.h", "oracle_bvh.h", "oracle_btf.h", "oracle_math.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_api.cpp", "oracle_sss.h", "oracle_prebake.h", "oracle_shade.h", "oracle_bvh.h", "oracle_btf.h", "oracle_math.h")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
     return so
@@ -231,6 +231,14 @@ class OracleScene:
         lib().orc_flux_mesh(self.h, _p(e), C.c_uint64(tri_begin), C.c_uint64(tri_end), int(front) + int(back), _p(out))
         return out
 
+    def sss_probe(self, rays, handles, brute=False):
+        """BSSDF.cuh:18-89 spatial probe: per ray {n, prim[4], t[4], u[4], v[4]} (uint32 view)."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+        handles = np.ascontiguousarray(handles, dtype=np.uint64)
+        out = np.zeros((len(rays), 17), dtype=np.uint32)
+        lib().orc_sss_probe(self.h, _p(rays), _p(handles), C.c_uint64(len(rays)), _p(out), int(brute))
+        return out
+
     def illum_probes(self, env, rp, probes, seed, push, nthreads=0):
         assert probes.dtype == S.ILLUM_SAMPLER_DTYPE and probes.flags.c_contiguous
         st = S.JobStats()
@@ -296,6 +304,12 @@ def flux_probes(probes):
     out = np.zeros(8, dtype=np.float32)
     lib().orc_flux_probes(_p(probes), C.c_uint64(len(probes)), _p(out))
     return out
+
+
+def rotate_about(v, u_turns, axis):
+    out = (C.c_float * 3)()
+    lib().orc_rotate_about((C.c_float * 3)(*v), C.c_float(u_turns), (C.c_float * 3)(*axis), out)
+    return np.array(list(out), dtype=np.float32)
 
 
 def scan_grid_count(grid):

@@ -77,7 +77,7 @@ int rtf_destroy(rtf_ctx* ctx) {
                     &ctx->ws.hits, &ctx->ws.counters, &ctx->ws.thr,
                     &ctx->ws.acc, &ctx->ws.dir0w, &ctx->ws.first_n, &ctx->ws.first_a, &ctx->ws.first_p,
                     &ctx->ws.sort_keys, &ctx->ws.sort_keys_alt, &ctx->ws.sort_vals, &ctx->ws.sort_vals_alt,
-                    &ctx->ws.sort_tmp, &ctx->ws.io};
+                    &ctx->ws.sort_tmp, &ctx->ws.io, &ctx->ws.pend_o, &ctx->ws.pend_d, &ctx->ws.pend_t};
   for (DevBuf* b : bufs) b->release();
   ctx->d_btfs.release(), ctx->d_env_faces.release();
   release_material_tables(ctx);
@@ -333,6 +333,10 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   s.has_alpha = 0;
   for (float a : alpha)
     if (a < 1.0f) s.has_alpha = 1;  // includes the "textured alpha" marker (-1)
+  s.has_sss = 0;
+  for (const DevMaterial& dm : mats)
+    if (dm.m.material_type != RTF_MAT_COMPRESSED_BTF && dm.m.subsurface_factor > 0.0f && dm.m.subsurface_radius[0] > 0.0f)
+      s.has_sss = 1;
   ctx->ready = true;
   return RTF_OK;
 }
@@ -868,6 +872,25 @@ int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* nodes, uint64_t n_nodes, cons
   if (!ctx->ready) ctx->n_tris = (uint32_t)n_tris, ctx->scene.n_tris = (uint32_t)n_tris;
   ctx->n_refs = (uint32_t)n_tris;
   ctx->ready = true;
+  return RTF_OK;
+}
+int rtf_sss_probe(rtf_ctx* ctx, const float* rays, const uint64_t* handles, size_t n, uint32_t* out17) {
+  CHECK_CTX(ctx);
+  if ((!rays || !handles || !out17) && n) return RTF_ERR_INVALID;
+  if (!ctx->ready) return not_ready();
+  if (n == 0) return RTF_OK;
+  int rc;
+  const size_t rb = n * 32, hb = n * 8, ob = n * 68;
+  if ((rc = ctx->ws.io.reserve(rb + hb + ob + 512))) return rc;
+  char* base = ctx->ws.io.as<char>();
+  float4* d_rays = (float4*)base;
+  unsigned long long* d_h = (unsigned long long*)(base + ((rb + 255) & ~(size_t)255));
+  uint32_t* d_out = (uint32_t*)((char*)d_h + ((hb + 255) & ~(size_t)255));
+  RTF_CUDA(cudaMemcpyAsync(d_rays, rays, rb, cudaMemcpyHostToDevice, ctx->stream));
+  RTF_CUDA(cudaMemcpyAsync(d_h, handles, hb, cudaMemcpyHostToDevice, ctx->stream));
+  if ((rc = ss_probe_device(ctx, d_rays, d_h, n, d_out))) return rc;
+  RTF_CUDA(cudaMemcpyAsync(out17, d_out, ob, cudaMemcpyDeviceToHost, ctx->stream));
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
   return RTF_OK;
 }
 int rtf_microbench_fp32(rtf_ctx* ctx, double* tflops) {

@@ -14,6 +14,7 @@
 #include "rtf_internal.h"
 #include "rtf_shade.cuh"
 #include "rtf_trace.cuh"
+#include "rtf_sss.cuh"
 
 namespace rtf {
 
@@ -138,6 +139,10 @@ struct PathState {
   float4* first_n;  // camera: first-hit normal
   float4* first_a;  // camera: first-hit albedo (or miss colour)
   float4* first_p;  // camera: first-hit position, w = 1 if there was a first hit
+  // BSSRDF (scenes with a subsurface material only): the bounce ray that waits for the subsurface path to end
+  float4* pend_o;  // origin.xyz, w = 1 while pending
+  float4* pend_d;  // direction.xyz
+  float4* pend_t;  // throughput.xyz of the bounce path
 };
 
 // warp-aggregated append: one atomicAdd per warp (ballot + popc), slots keep lane order.
@@ -213,6 +218,9 @@ struct ShadeParams {
   int camera;
   int brdf;  // RTF_BRDF_REFERENCE / RTF_BRDF_LAMBERT_GGX
 };
+// SSS = some material has subsurfaceFactor > 0: the kernel carries the BSSRDF spatial probe (rtf_sss.cuh) and the
+// pending-bounce state.
+template <bool SSS>
 __global__ void __launch_bounds__(256)
     k_shade(DevScene sc, rtf_env env, ShadeParams sp, PathMap pm, Queues q, int qi, int wave, PathState ps) {
   const uint32_t n = q.count[wave];
@@ -231,6 +239,7 @@ __global__ void __launch_bounds__(256)
     float3 T = f3(thr4.x, thr4.y, thr4.z);
     const float4 acc4 = ps.acc[p];
     float3 acc = f3(acc4.x, acc4.y, acc4.z);
+    uint32_t count_now = __float_as_uint(thr4.w);  // PerRayData::m_hitCount after this event
     if (pi & kShadowBit) {  // shadow ray result, RayFunctions.cuh:70-92 (BTF: :193-217)
       const float4 ax = ps.aux[p];
       const float3 albedo = f3(ax.x, ax.y, ax.z);
@@ -247,6 +256,7 @@ __global__ void __launch_bounds__(256)
       if (sp.camera && __float_as_uint(thr4.w) == 0u) ps.first_a[p] = make_float4(L.x, L.y, L.z, 0.0f);
     } else {
       const uint32_t hit_count = __float_as_uint(thr4.w) + 1u;
+      count_now = hit_count;
       const SurfaceHit sh = surface_hit(sc, prim, h.y, h.z, d);
       const DevMaterial& dm = sc.mats[sc.insts[sh.inst].mat];
       const rtf_material& m = dm.m;
@@ -335,7 +345,50 @@ __global__ void __launch_bounds__(256)
             acc = acc + T * emis;
           }
           ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
-        } else if ((int)hit_count <= sp.bounces) {  // RayFunctions.cuh:93-161, BSSRDF branch off (factor 0)
+        } else if ((int)hit_count <= sp.bounces) {  // RayFunctions.cuh:93-161
+          bool need_sample = false;  // BSSRDF, RayFunctions.cuh:97-133 + BSSDF.cuh:42-89
+          float3 ss_o = f3(0, 0, 0), ss_d = f3(0, 0, 0), ss_w = f3(0, 0, 0);
+          if constexpr (SSS) {
+            if (hit_count <= 1u && m.subsurface_factor > 0.0f && m.subsurface_radius[0] > 0.0f) {
+              const float radius = m.subsurface_radius[0];
+              const float4 rs = path_rng(sp.seed, STREAM_SSS, unit, hit_count, 0u);
+              const float4 rb = path_rng(sp.seed, STREAM_SSS, unit, hit_count, 1u);
+              const float3 disk_center = sh.position + (radius * normal) * 0.5f;
+              const float disk_radius = radius * sqrtf(rs.x);
+              const float distance = sqrtf(radius * radius - disk_radius * disk_radius);
+              const float3 sample_pos =
+                  disk_center + disk_radius * rotate_about(f3(normal.y, normal.z, normal.x), rs.y, normal);
+              SSRecords rec;
+              ss_probe(sc, sample_pos, neg3(normal), distance, radius + distance, sc.insts[sh.inst].handle, rec);
+              if (rec.n > 0) {
+                int index = (int)(rs.z * (float)rec.n);
+                index = index < 0 ? 0 : (index > rec.n - 1 ? rec.n - 1 : index);
+                float rt = 0, ru = 0, rv = 0;
+                uint32_t rprim = 0;
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                  if (k == index) rt = rec.t[k], ru = rec.u[k], rv = rec.v[k], rprim = rec.prim[k];
+                (void)rt;
+                const SurfaceHit so = surface_hit(sc, rprim, ru, rv, f3(0, 0, 0));  // GetHitInfo(rayDirection, false): no flip
+                float3 out_n = so.normal;
+                const DevMaterial& om = sc.mats[sc.insts[so.inst].mat];
+                if (om.tex[MAT_TEX_NORMAL].texels) {  // ApplyNormalTexture of the record's own material, BSSDF.cuh:31-32
+                  const HitAttrs oa = hit_attrs(sc, rprim, ru, rv, so.inst);
+                  const float4 t = tex2d(om.tex[MAT_TEX_NORMAL], oa.u, oa.v);
+                  const float3 B = cross3(out_n, oa.tangent);
+                  const float3 tn = f3(t.x * 2.0f - 1.0f, t.y * 2.0f - 1.0f, t.z * 2.0f - 1.0f);
+                  out_n = normalize3((oa.tangent * tn.x + B * tn.y) + out_n * tn.z);
+                }
+                if (length3(sh.position - so.position) <= radius) {
+                  ss_o = so.position + out_n * 0.01f;
+                  ss_d = sample_lobe(rb.x, rb.y, reflect3(neg3(out_n), out_n), metallic);  // BRDF(metallic, rnd, -n, n)
+                  const float k2 = clampf(fabsf(dot3(out_n, ss_d)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
+                  ss_w = (m.subsurface_factor * f3(m.subsurface_color[0], m.subsurface_color[1], m.subsurface_color[2])) * k2;
+                  need_sample = true;
+                }
+              }
+            }
+          }
           const float4 r = path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
           float3 nd, wgt;
           if (sp.brdf == RTF_BRDF_LAMBERT_GGX) {
@@ -348,7 +401,20 @@ __global__ void __launch_bounds__(256)
           }
           acc = acc + T * emis;
           ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
-          if (!(wgt.x == 0.0f && wgt.y == 0.0f && wgt.z == 0.0f)) {  // (only the GGX lobe can absorb a sample)
+          const bool absorbed = wgt.x == 0.0f && wgt.y == 0.0f && wgt.z == 0.0f;  // (only the GGX lobe can absorb a sample)
+          if (SSS && need_sample) {  // the subsurface path runs first; the bounce waits for it (shared m_hitCount)
+            if (!absorbed) {
+              const float3 tb = T * wgt;
+              ps.pend_o[p] = make_float4(sh.position.x, sh.position.y, sh.position.z, 1.0f);
+              ps.pend_d[p] = make_float4(nd.x, nd.y, nd.z, 0.0f);
+              ps.pend_t[p] = make_float4(tb.x, tb.y, tb.z, 0.0f);
+            }
+            T = T * ss_w;
+            ps.thr[p] = make_float4(T.x, T.y, T.z, __uint_as_float(hit_count));
+            emit = true;
+            na = make_float4(ss_o.x, ss_o.y, ss_o.z, __uint_as_float(p));
+            nb = make_float4(ss_d.x, ss_d.y, ss_d.z, 1e20f);
+          } else if (!absorbed) {
             T = T * wgt;
             ps.thr[p] = make_float4(T.x, T.y, T.z, __uint_as_float(hit_count));
             emit = true;
@@ -358,6 +424,19 @@ __global__ void __launch_bounds__(256)
         } else {
           acc = acc + T * emis;
           ps.acc[p] = make_float4(acc.x, acc.y, acc.z, 0.0f);
+        }
+      }
+    }
+    if constexpr (SSS) {  // a path that ended here resumes with its waiting bounce ray, hit count carried over
+      if (!emit && !(pi & kShadowBit)) {
+        const float4 po = ps.pend_o[p];
+        if (po.w != 0.0f) {
+          const float4 pd = ps.pend_d[p], pt = ps.pend_t[p];
+          ps.pend_o[p] = make_float4(0, 0, 0, 0);
+          ps.thr[p] = make_float4(pt.x, pt.y, pt.z, __uint_as_float(count_now));
+          emit = true;
+          na = make_float4(po.x, po.y, po.z, __uint_as_float(p));
+          nb = make_float4(pd.x, pd.y, pd.z, 1e20f);
         }
       }
     }
@@ -509,6 +588,11 @@ static int ensure_workspace(rtf_ctx* ctx, size_t cap, bool camera) {
     if ((rc = w.first_p.reserve(16 * cap))) return rc;
     if ((rc = w.sort_keys.reserve(16 * cap))) return rc;  // aux for camera + single light
   }
+  if (ctx->scene.has_sss) {
+    if ((rc = w.pend_o.reserve(16 * cap))) return rc;
+    if ((rc = w.pend_d.reserve(16 * cap))) return rc;
+    if ((rc = w.pend_t.reserve(16 * cap))) return rc;
+  }
   if ((rc = ctx->d_stats.reserve(64))) return rc;
   w.capacity = cap;
   return RTF_OK;
@@ -525,12 +609,17 @@ static void bind(rtf_ctx* ctx, Queues& q, PathState& ps, bool camera) {
   ps.thr = w.thr.as<float4>(), ps.acc = w.acc.as<float4>(), ps.dir0w = w.dir0w.as<float4>();
   ps.first_n = w.first_n.as<float4>(), ps.first_a = w.first_a.as<float4>(), ps.first_p = w.first_p.as<float4>();
   ps.aux = camera ? w.sort_keys.as<float4>() : w.first_n.as<float4>();
+  ps.pend_o = w.pend_o.as<float4>(), ps.pend_d = w.pend_d.as<float4>(), ps.pend_t = w.pend_t.as<float4>();
 }
 
 // Runs the trace/shade loop for the wavefronts of one batch (no host synchronisation inside).
 static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_t seed, const PathMap& pm, size_t paths,
                           Queues& q, PathState& ps, bool camera) {
-  const int waves = env->lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE ? 2 : bounces + 1;
+  // BSSRDF: the subsurface path and the waiting bounce path share one hit counter, so together they add at most one ray
+  // to the longest chain (primary + `bounces` hits + the resumed ray).
+  const bool sss = ctx->scene.has_sss && env->lighting_type != RTF_ENV_SINGLE_LIGHT_SOURCE;
+  const int waves = env->lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE ? 2 : bounces + 1 + (sss ? 1 : 0);
+  if (sss) RTF_CUDA(cudaMemsetAsync(ps.pend_o, 0, 16 * paths, ctx->stream));
   if (waves + 1 > 60) {
     set_error("too many bounces");
     return RTF_ERR_INVALID;
@@ -545,7 +634,10 @@ static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_
       LAUNCH(ctx, k_trace_queue<true>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
     else
       LAUNCH(ctx, k_trace_queue<false>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
-    LAUNCH(ctx, k_shade, div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
+    if (sss)
+      LAUNCH(ctx, k_shade<true>, div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
+    else
+      LAUNCH(ctx, k_shade<false>, div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
     qi ^= 1;
   }
   return RTF_OK;
@@ -838,6 +930,29 @@ int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, cons
   }
   RTF_CUDA(cudaGetLastError());
   ctx->last_paths = (px_end - px_begin) * spp;
+  return RTF_OK;
+}
+
+// ---- test hook: the BSSRDF spatial probe on its own (rtf_sss.cuh) ----------------------------------------------------
+__global__ void k_ss_probe_test(DevScene sc, const float4* __restrict__ rays, const unsigned long long* __restrict__ handles,
+                                uint32_t n, uint32_t* __restrict__ out17) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 a = rays[2 * i], b = rays[2 * i + 1];
+  SSRecords rec;
+  ss_probe(sc, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), a.w, b.w, handles[i], rec);
+  uint32_t* o = out17 + 17 * (size_t)i;
+  o[0] = (uint32_t)rec.n;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    o[1 + k] = rec.prim[k], o[5 + k] = __float_as_uint(rec.t[k]);
+    o[9 + k] = __float_as_uint(rec.u[k]), o[13 + k] = __float_as_uint(rec.v[k]);
+  }
+}
+int ss_probe_device(rtf_ctx* ctx, const float4* d_rays, const unsigned long long* d_handles, size_t n, uint32_t* d_out17) {
+  if (n == 0) return RTF_OK;
+  LAUNCH(ctx, k_ss_probe_test, div_up(n, 128), 128, 0, ctx->scene, d_rays, d_handles, (uint32_t)n, d_out17);
+  RTF_CUDA(cudaGetLastError());
   return RTF_OK;
 }
 

@@ -83,6 +83,7 @@ struct DevScene {
   const float* inst_alpha = nullptr;      // per instance: constant alpha, or < 0 = alpha comes from the albedo texture
   uint32_t n_tris = 0, n_nodes = 0, n_insts = 0;
   int has_alpha = 0;
+  int has_sss = 0;  // some material has subsurfaceFactor > 0 and subsurfaceRadius.x > 0 (BSSRDF, RF.cuh:97-133)
 };
 
 struct Geometry {
@@ -127,6 +128,7 @@ struct Workspace {  // wavefront queues + path state, sized for `capacity` paths
   size_t capacity = 0;
   DevBuf ray_a[2], ray_b[2], hits, counters;
   DevBuf thr, acc, dir0w, first_n, first_a, first_p;  // per-path state (SoA float4)
+  DevBuf pend_o, pend_d, pend_t;                      // BSSRDF: bounce ray waiting for the subsurface path
   DevBuf sort_keys, sort_keys_alt, sort_vals, sort_vals_alt, sort_tmp;
   DevBuf io;  // staging for AoS entry points
 };
@@ -218,6 +220,7 @@ int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, cons
 int sample_texture_device(rtf_ctx* ctx, const DevTexture& tex, size_t n, const float* d_uv, float* d_rgba);
 int sample_environment_device(rtf_ctx* ctx, const rtf_env* env, size_t n, const float* d_pos_dir6, float* d_rgb);
 int btf_eval_device(rtf_ctx* ctx, const DevBTF& btf, size_t n, const float* d_in14, float* d_rgb);
+int ss_probe_device(rtf_ctx* ctx, const float4* d_rays, const unsigned long long* d_handles, size_t n, uint32_t* d_out17);
 int microbench_fp32(rtf_ctx* ctx, double* tflops);
 int microbench_l2(rtf_ctx* ctx, double bytes, double* gbs);
 }  // namespace rtf

@@ -104,7 +104,7 @@ RTF_HD uint4 philox4x32_10(uint4 c, uint2 k) {
 // 24-bit uniform in [0,1): same granularity as LinearCongruenceGenerator.hpp:32
 RTF_HD float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
 
-enum { STREAM_PATH = 0, STREAM_ALPHA = 1, STREAM_CAMERA = 2 };
+enum { STREAM_PATH = 0, STREAM_ALPHA = 1, STREAM_CAMERA = 2, STREAM_SSS = 3 };
 
 RTF_HD float4 path_rng(uint32_t seed, uint32_t stream, uint64_t unit, uint32_t bounce, uint32_t extra) {
   uint4 o = philox4x32_10(make_uint4((uint32_t)unit, (uint32_t)(unit >> 32), bounce, extra), make_uint2(seed, stream));

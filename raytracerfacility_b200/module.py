@@ -37,7 +37,7 @@ EXPORTS = [
     "rtf_set_texture", "rtf_remove_texture", "rtf_set_material_textures", "rtf_set_environment_map", "rtf_sample_texture",
     "rtf_sample_environment", "rtf_set_btf", "rtf_btf_import_folder", "rtf_remove_btf", "rtf_set_material_btf",
     "rtf_btf_eval", "rtf_set_geometry_instanced", "rtf_set_geometry_skinned", "rtf_geometry_read_baked",
-    "rtf_prepare_light_probes", "rtf_illumination_flux", "rtf_illumination_flux_mesh_device",
+    "rtf_prepare_light_probes", "rtf_illumination_flux", "rtf_illumination_flux_mesh_device", "rtf_sss_probe",
 ]
 
 
@@ -338,6 +338,14 @@ class RayTracer:
         out = np.zeros(8, dtype=np.float32)
         _check(lib().rtf_illumination_flux_mesh_device(self.h, C.c_void_p(dev_energy6_ptr), C.c_uint64(tri_begin),
                                                        C.c_uint64(tri_end), int(front), int(back), _p(out)))
+        return out
+
+    def sss_probe(self, rays, handles):
+        """Test hook: BSSRDF spatial probe (BSSDF.cuh:18-89); per ray {n, prim[4], t[4], u[4], v[4]} (uint32 view)."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+        handles = np.ascontiguousarray(handles, dtype=np.uint64)
+        out = np.zeros((len(rays), 17), dtype=np.uint32)
+        _check(lib().rtf_sss_probe(self.h, _p(rays), _p(handles), C.c_size_t(len(rays)), _p(out)))
         return out
 
     def last_job_stats(self):
