@@ -247,6 +247,13 @@ RTF_API int rtf_remove_instance(rtf_ctx* ctx, uint64_t handle);
  * LBVH -> 8-wide compressed BVH on the device.  morton_bits: 30 or 63 (0 = 63). */
 RTF_API int rtf_commit(rtf_ctx* ctx, int morton_bits);
 RTF_API int rtf_triangle_count(rtf_ctx* ctx, uint64_t* n_triangles);
+/* Scene-sync diffing (the reference's m_updateFlag / m_version bookkeeping, RayTracerLayer.cpp:47-92,
+ * RT.hpp:305-327, done on this side of the ABI): rtf_set_geometry with a non-zero version equal to the
+ * stored one, and rtf_set_material / rtf_set_instance with identical contents, are no-ops; rtf_commit
+ * rebuilds the BVH only if a geometry, an instance or "presplit" changed, re-resolves the material-side
+ * tables only (materials, textures, BTFs, cube map — microseconds) if nothing else did, and returns at once
+ * if nothing changed.  out4 = {full builds, material-only commits, skipped commits, skipped geometry uploads}. */
+RTF_API int rtf_commit_stats(rtf_ctx* ctx, uint64_t* out4);
 /* Device time (ms, CUDA events) of the last rtf_commit per stage:
  * {flatten, bounds+morton, sort, karras+refit, collapse+encode, total}; n >= 6.  (The reference
  * has no counterpart: its builds are opaque optixAccelBuild calls, RT.cu:1562-1584.) */

@@ -123,6 +123,15 @@ int rtf_set_geometry(rtf_ctx* ctx, uint64_t handle, const void* vertices, size_t
       set_error("rtf_set_geometry: triangle index out of range");
       return RTF_ERR_INVALID;
     }
+  {  // unchanged version: nothing to do (the caller-side check of RayTracerLayer.cpp:60-75, done here)
+    auto it = ctx->geoms.find(handle);
+    if (it != ctx->geoms.end() && version != 0 && it->second.version == version && !it->second.baked &&
+        it->second.n_verts == n_vertices && it->second.n_tris == n_triangles) {
+      ctx->geometry_uploads_skipped++;
+      return RTF_OK;
+    }
+  }
+  ctx->geom_dirty = true;
   Geometry& g = ctx->geoms[handle];
   g.verts.resize(n_vertices);
   for (size_t i = 0; i < n_vertices; i++) memcpy(&g.verts[i], (const char*)vertices + i * stride, sizeof(rtf_vertex));
@@ -151,6 +160,7 @@ int rtf_set_geometry_instanced(rtf_ctx* ctx, uint64_t handle, const void* vertic
   }
   std::vector<rtf_vertex> packed(n_vertices);
   for (size_t i = 0; i < n_vertices; i++) memcpy(&packed[i], (const char*)vertices + i * stride, sizeof(rtf_vertex));
+  ctx->geom_dirty = true;
   if (ctx->geoms.count(handle)) ctx->ready = false;  // the committed scene may point at the arrays re-baked below
   Geometry& g = ctx->geoms[handle];
   g.verts.clear(), g.tris.clear();
@@ -172,6 +182,7 @@ int rtf_set_geometry_skinned(rtf_ctx* ctx, uint64_t handle, const void* skinned_
       set_error("rtf_set_geometry_skinned: triangle index out of range");
       return RTF_ERR_INVALID;
     }
+  ctx->geom_dirty = true;
   if (ctx->geoms.count(handle)) ctx->ready = false;  // the committed scene may point at the arrays re-baked below
   Geometry& g = ctx->geoms[handle];
   g.verts.clear(), g.tris.clear();
@@ -203,15 +214,23 @@ int rtf_set_material(rtf_ctx* ctx, uint64_t handle, const rtf_material* material
     set_error("rtf_set_material: unknown material_type");
     return RTF_ERR_INVALID;
   }
+  auto mit = ctx->mats.find(handle);
+  if (mit != ctx->mats.end() && !memcmp(&mit->second, material, sizeof(rtf_material))) return RTF_OK;  // unchanged
   ctx->mats[handle] = *material;
+  ctx->mat_dirty = true;
   return RTF_OK;
 }
 int rtf_set_instance(rtf_ctx* ctx, uint64_t handle, uint64_t geom, uint64_t mat, const float xform[16], uint64_t comp) {
   CHECK_CTX(ctx);
   if (!xform) return RTF_ERR_INVALID;
+  auto iit = ctx->insts.find(handle);
+  if (iit != ctx->insts.end() && iit->second.geom == geom && iit->second.mat == mat && iit->second.component == comp &&
+      !memcmp(iit->second.xform, xform, 64))
+    return RTF_OK;  // unchanged (RayTracedInstance::m_version check, RayTracerLayer.cpp:76-92)
   Instance& in = ctx->insts[handle];
   in.geom = geom, in.mat = mat, in.component = comp;
   memcpy(in.xform, xform, 64);
+  ctx->geom_dirty = true;
   return RTF_OK;
 }
 int rtf_remove_geometry(rtf_ctx* ctx, uint64_t handle) {
@@ -221,26 +240,39 @@ int rtf_remove_geometry(rtf_ctx* ctx, uint64_t handle) {
   cudaStreamSynchronize(ctx->stream);
   it->second.d_verts.release(), it->second.d_tris.release();
   ctx->geoms.erase(it);
+  ctx->geom_dirty = true;
+  ctx->ready = false;  // the committed scene may point at the released arrays
   return RTF_OK;
 }
 int rtf_remove_material(rtf_ctx* ctx, uint64_t handle) {
   CHECK_CTX(ctx);
   ctx->mat_links.erase(handle);
+  ctx->mat_dirty = true;
   return ctx->mats.erase(handle) ? RTF_OK : RTF_ERR_NOT_FOUND;
 }
 int rtf_remove_instance(rtf_ctx* ctx, uint64_t handle) {
   CHECK_CTX(ctx);
+  ctx->geom_dirty = true;
   return ctx->insts.erase(handle) ? RTF_OK : RTF_ERR_NOT_FOUND;
 }
 
 int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   CHECK_CTX(ctx);
-  ctx->ready = false;
   if (morton_bits == 0) morton_bits = 63;
   if (morton_bits != 30 && morton_bits != 63) {
     set_error("morton_bits must be 30 or 63");
     return RTF_ERR_INVALID;
   }
+  // Scene-sync diffing: nothing changed -> nothing to do (the reference only calls BuildIAS when an update flag was
+  // raised, RayTracerLayer.cpp:394-400); only material-side tables changed -> they are re-resolved below and the BVH
+  // stays, unless an instance's "may ignore hits" class changed (it is baked into the triangle records).
+  const bool was_ready = ctx->ready && ctx->morton_bits == morton_bits && ctx->n_tris > 0;
+  if (was_ready && !ctx->geom_dirty && !ctx->mat_dirty) {
+    ctx->commits_skipped++;
+    return RTF_OK;
+  }
+  const bool keep_bvh_if_possible = was_ready && !ctx->geom_dirty;
+  ctx->ready = false;
   int rc;
   cudaStream_t st = ctx->stream;
   // materials -> dense table
@@ -291,9 +323,13 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
     set_error("more than 2^32 triangles");
     return RTF_ERR_LIMIT;
   }
+  std::vector<uint8_t> alpha_class(alpha.size());
+  for (size_t k = 0; k < alpha.size(); k++) alpha_class[k] = alpha[k] < 1.0f ? 1 : 0;
+  const bool keep_bvh = keep_bvh_if_possible && first == ctx->n_tris && alpha_class == ctx->alpha_class;
   ctx->n_tris = (uint32_t)first;
   ctx->scene = DevScene();
   if (first == 0) {  // reference: no acceleration structure -> entry points report "not ready"
+    ctx->geom_dirty = true;
     return RTF_OK;
   }
   if ((rc = ctx->d_insts.reserve(insts.size() * sizeof(InstDev)))) return rc;
@@ -312,9 +348,14 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   if ((rc = ctx->d_tri_inst.reserve(4 * (size_t)first))) return rc;
   ctx->scene.n_insts = (uint32_t)insts.size();
   ctx->scene.insts = ctx->d_insts.as<InstDev>();
+  if (keep_bvh) {
+    RTF_CUDA(cudaStreamSynchronize(st));  // host vectors above die at return
+    ctx->commits_materials++;
+  } else {
   if ((rc = flatten_scene(ctx))) return rc;
   RTF_CUDA(cudaStreamSynchronize(st));  // host vectors above die at return
   if ((rc = build_bvh(ctx, morton_bits))) return rc;
+  ctx->commits_full++;
   {  // shrink the node array to its final size (collapse allocated the n/2 worst case)
     DevBuf exact;
     if ((rc = exact.reserve(80 * (size_t)ctx->n_nodes))) return rc;
@@ -323,6 +364,9 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
     ctx->d_nodes.release();
     ctx->d_nodes = exact;
   }
+  }
+  ctx->alpha_class = alpha_class;
+  ctx->geom_dirty = false, ctx->mat_dirty = false;
   ctx->morton_bits = morton_bits;
   DevScene& s = ctx->scene;
   s.nodes = ctx->d_nodes.as<uint4>(), s.tris = ctx->d_tris48.as<float4>();
@@ -338,6 +382,12 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
     if (dm.m.material_type != RTF_MAT_COMPRESSED_BTF && dm.m.subsurface_factor > 0.0f && dm.m.subsurface_radius[0] > 0.0f)
       s.has_sss = 1;
   ctx->ready = true;
+  return RTF_OK;
+}
+int rtf_commit_stats(rtf_ctx* ctx, uint64_t* out4) {
+  if (!ctx || !out4) return RTF_ERR_INVALID;
+  out4[0] = ctx->commits_full, out4[1] = ctx->commits_materials, out4[2] = ctx->commits_skipped;
+  out4[3] = ctx->geometry_uploads_skipped;
   return RTF_OK;
 }
 int rtf_build_timings(rtf_ctx* ctx, float* ms_out, int n) {
@@ -364,6 +414,7 @@ int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value) {
       set_error("presplit must be in [1, 64]");
       return RTF_ERR_INVALID;
     }
+    if (ctx->presplit != (int)value) ctx->geom_dirty = true;
     ctx->presplit = (int)value;  // takes effect at the next rtf_commit
   } else if (!strcmp(name, "brdf")) {
     if (value != RTF_BRDF_REFERENCE && value != RTF_BRDF_LAMBERT_GGX) {

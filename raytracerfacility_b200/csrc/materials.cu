@@ -183,6 +183,7 @@ static bool parse_table(const std::string& path, int& rows, int& cols, std::vect
 extern "C" {
 
 int rtf_set_texture(rtf_ctx* ctx, uint64_t handle, int width, int height, const float* rgba) {
+  if (ctx) ctx->mat_dirty = true;
   CHECK_CTX(ctx);
   if (handle == 0 || width < 1 || height < 1 || !rgba || (size_t)width * height > ((size_t)1 << 28)) {
     set_error("rtf_set_texture: bad handle, size or pixels");
@@ -196,6 +197,7 @@ int rtf_set_texture(rtf_ctx* ctx, uint64_t handle, int width, int height, const 
   return RTF_OK;
 }
 int rtf_remove_texture(rtf_ctx* ctx, uint64_t handle) {
+  if (ctx) ctx->mat_dirty = true;
   CHECK_CTX(ctx);
   auto it = ctx->textures.find(handle);
   if (it == ctx->textures.end()) return RTF_ERR_NOT_FOUND;
@@ -207,6 +209,7 @@ int rtf_remove_texture(rtf_ctx* ctx, uint64_t handle) {
 }
 int rtf_set_material_textures(rtf_ctx* ctx, uint64_t material, uint64_t albedo, uint64_t normal, uint64_t metallic,
                               uint64_t roughness) {
+  if (ctx) ctx->mat_dirty = true;
   CHECK_CTX(ctx);
   MaterialLinks& l = ctx->mat_links[material];
   l.tex[MAT_TEX_ALBEDO] = albedo, l.tex[MAT_TEX_NORMAL] = normal, l.tex[MAT_TEX_METALLIC] = metallic;
@@ -214,6 +217,7 @@ int rtf_set_material_textures(rtf_ctx* ctx, uint64_t material, uint64_t albedo, 
   return RTF_OK;
 }
 int rtf_set_environment_map(rtf_ctx* ctx, const uint64_t faces[6]) {
+  if (ctx) ctx->mat_dirty = true;
   CHECK_CTX(ctx);
   ctx->has_env_map = faces != nullptr;
   for (int k = 0; k < 6; k++) ctx->env_map[k] = faces ? faces[k] : 0;
@@ -261,6 +265,7 @@ int rtf_sample_environment(rtf_ctx* ctx, const rtf_env* env, size_t n, const flo
 }
 
 int rtf_set_btf(rtf_ctx* ctx, uint64_t handle, const rtf_btf_desc* d) {
+  if (ctx) ctx->mat_dirty = true;
   CHECK_CTX(ctx);
   if (handle == 0 || !d) return RTF_ERR_INVALID;
   if (d->num_beta < 3 || (d->num_beta & 1) == 0 || d->num_alpha < 2 || d->num_theta < 2 || d->num_phi < 1 || d->pdf6_rows < 1 ||
@@ -329,6 +334,7 @@ int rtf_set_btf(rtf_ctx* ctx, uint64_t handle, const rtf_btf_desc* d) {
   return RTF_OK;
 }
 int rtf_remove_btf(rtf_ctx* ctx, uint64_t handle) {
+  if (ctx) ctx->mat_dirty = true;
   CHECK_CTX(ctx);
   auto it = ctx->btfs.find(handle);
   if (it == ctx->btfs.end()) return RTF_ERR_NOT_FOUND;
@@ -339,6 +345,7 @@ int rtf_remove_btf(rtf_ctx* ctx, uint64_t handle) {
   return RTF_OK;
 }
 int rtf_set_material_btf(rtf_ctx* ctx, uint64_t material, uint64_t btf) {
+  if (ctx) ctx->mat_dirty = true;
   CHECK_CTX(ctx);
   ctx->mat_links[material].btf = btf;
   return RTF_OK;

@@ -160,6 +160,12 @@ struct rtf_ctx {
   std::map<uint64_t, rtf::BTFTables> btfs;
   uint64_t env_map[6] = {0, 0, 0, 0, 0, 0};
   bool has_env_map = false;
+  // scene-sync diffing (the reference's m_updateFlag / m_version bookkeeping, RayTracerLayer.cpp:47-92, RT.hpp:305-327):
+  // geom_dirty = a geometry or instance changed since the last commit (BVH rebuild); mat_dirty = only material-side
+  // tables changed (materials, textures, BTFs, cube map: re-resolved without touching the BVH)
+  bool geom_dirty = true, mat_dirty = true;
+  std::vector<uint8_t> alpha_class;  // per committed instance: may ignore hits (decides TRI_FLAG_ALPHA in the BVH)
+  uint64_t commits_full = 0, commits_materials = 0, commits_skipped = 0, geometry_uploads_skipped = 0;
   // committed state
   bool ready = false;
   int morton_bits = 63;

@@ -38,6 +38,7 @@ EXPORTS = [
     "rtf_sample_environment", "rtf_set_btf", "rtf_btf_import_folder", "rtf_remove_btf", "rtf_set_material_btf",
     "rtf_btf_eval", "rtf_set_geometry_instanced", "rtf_set_geometry_skinned", "rtf_geometry_read_baked",
     "rtf_prepare_light_probes", "rtf_illumination_flux", "rtf_illumination_flux_mesh_device", "rtf_sss_probe",
+    "rtf_commit_stats",
 ]
 
 
@@ -276,6 +277,12 @@ class RayTracer:
         if presplit is not None:
             self.set_option("presplit", presplit)
         self.build_ias(morton_bits)
+
+    def commit_stats(self):
+        """{full builds, material-only commits, skipped commits, skipped geometry uploads} (scene-sync diffing)."""
+        out = (C.c_uint64 * 4)()
+        _check(lib().rtf_commit_stats(self.h, out))
+        return dict(zip(("full", "materials", "skipped", "uploads_skipped"), [int(x) for x in out]))
 
     @property
     def triangle_count(self):

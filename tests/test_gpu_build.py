@@ -98,3 +98,67 @@ def test_not_ready_and_bad_arguments(rt, mod, S, scenes):
     rt.build_ias()
     with pytest.raises(mod.RtfError):
         rt.trace_closest(rays)
+
+
+def test_scene_sync_diffing(rt, orc, S, scenes):
+    """rtf_commit rebuilds only what changed (RayTracerLayer.cpp:47-92 update flags): identical re-submission -> skipped,
+    material-side change -> tables only (BVH bits untouched), geometry / instance / alpha-class change -> full build."""
+    sd = scenes.sorghum_scene(1)
+    for gh, (v, t) in sd.geometries.items():
+        rt.set_geometry(gh, v, t, version=7)
+    for mh, m in sd.materials.items():
+        rt.set_material(mh, m)
+    for ih, (g, m, x, comp) in sd.instances.items():
+        rt.set_instance(ih, g, m, x, comp)
+    rt.build_ias(63)
+    nodes0 = rt.debug(S.DBG_WIDE_NODES).copy()
+    assert rt.commit_stats() == {"full": 1, "materials": 0, "skipped": 0, "uploads_skipped": 0}
+    # the same scene again, same versions
+    for gh, (v, t) in sd.geometries.items():
+        rt.set_geometry(gh, v, t, version=7)
+    for mh, m in sd.materials.items():
+        rt.set_material(mh, m)
+    for ih, (g, m, x, comp) in sd.instances.items():
+        rt.set_instance(ih, g, m, x, comp)
+    rt.build_ias(63)
+    assert rt.commit_stats() == {"full": 1, "materials": 0, "skipped": 1, "uploads_skipped": len(sd.geometries)}
+    # albedo change: tables only, and the new albedo is what the shading sees
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=2, samples=8)
+    before = rt.estimate_illumination_mesh(env, rp, seed=3, tri_begin=0, tri_end=500)
+    mh = sorted(sd.materials)[0]
+    sd.materials[mh].albedo_color[:] = (0.05, 0.05, 0.05)
+    for h, m in sd.materials.items():
+        rt.set_material(h, m)
+    rt.build_ias(63)
+    assert rt.commit_stats()["materials"] == 1 and rt.commit_stats()["full"] == 1
+    assert np.array_equal(rt.debug(S.DBG_WIDE_NODES), nodes0)
+    after = rt.estimate_illumination_mesh(env, rp, seed=3, tri_begin=0, tri_end=500)
+    osc = orc.OracleScene(sd, 63)
+    cpu, _ = osc.illum_mesh(env, rp, seed=3, push=1e-3, tri_begin=0, tri_end=500)
+    assert np.abs(after[:, :3] - before[:, :3]).max() > 1e-3
+    assert np.allclose(after[:, :3], cpu[:, :3], rtol=1e-5, atol=0)
+    # transmission > 0 changes the any-hit class baked into the triangle records -> full build
+    sd.materials[mh].transmission = 0.5
+    rt.set_material(mh, sd.materials[mh])
+    rt.build_ias(63)
+    assert rt.commit_stats()["full"] == 2
+    gt = rt.debug(S.DBG_WIDE_TRIS)
+    mat_of_inst = [sd.instances[ih][1] for ih in sorted(sd.instances)]
+    want = np.array([1 if mat_of_inst[i] == mh else 0 for i in gt["inst"]], dtype=np.uint32)
+    assert np.array_equal(gt["flags"], want) and want.any()  # TRI_FLAG_ALPHA follows the new class (the oracle keeps 0)
+    # a moved instance -> full build, same bits as a fresh oracle build
+    ih = sorted(sd.instances)[-1]
+    g, m, x, comp = sd.instances[ih]
+    x = x.copy()
+    x[12] += 0.25
+    sd.instances[ih] = (g, m, x, comp)
+    rt.set_instance(ih, g, m, x, comp)
+    rt.build_ias(63)
+    assert rt.commit_stats()["full"] == 3
+    osc = orc.OracleScene(sd, 63)
+    assert np.array_equal(rt.debug(S.DBG_WIDE_NODES).view(np.uint8), osc.debug(S.DBG_WIDE_NODES).view(np.uint8))
+    # new geometry version -> upload + full build
+    for gh, (v, t) in sd.geometries.items():
+        rt.set_geometry(gh, v, t, version=8)
+    rt.build_ias(63)
+    assert rt.commit_stats()["full"] == 4
