@@ -179,6 +179,22 @@ def main():
     t0 = time.perf_counter()
     rt.load_scene(sd, 63)
     build_wall = time.perf_counter() - t0
+    first_build = rt.build_timings()
+    # steady-state rebuild (dynamic scenes; buffers already allocated): move one instance, commit, move it back, commit —
+    # the second commit rebuilds exactly the benchmark scene and is the one reported.
+    ih = max(sd.instances)
+    g_, m_, x_, c_ = sd.instances[ih]
+    x_moved = x_.copy()
+    x_moved[12] += 0.125
+    rt.set_instance(ih, g_, m_, x_moved, c_)
+    rt.build_ias(63)
+    rt.set_instance(ih, g_, m_, x_, c_)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    rt.build_ias(63)
+    torch.cuda.synchronize()
+    rebuild_wall = time.perf_counter() - t0
+    rebuild = dict(rt.build_timings(), wall_ms=rebuild_wall * 1e3)
     n_tris = rt.triangle_count
     lo, hi = scenes.scene_bounds(sd)
     n = 1 << args.log2_rays
@@ -265,7 +281,7 @@ def main():
            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 16,
                    "api": "rtf_trace_closest (host rays in, host hits out, pinned)"},
            "gpu_launches": launches, "clocks": clk, "roofline": roofline,
-           "build": dict(rt.build_timings(), wall_s_incl_upload=build_wall)}
+           "build": dict(first_build, wall_s_incl_upload=build_wall), "rebuild": rebuild}
 
     if not args.no_extras:
         # ---- illumination estimation, sample-sharded + one all-reduce --------------------------------------
