@@ -105,3 +105,33 @@ def test_light_probes_and_flux(rt, orc, mod, S, scenes):
     sub = rt.illumination_flux_mesh_device(d.data_ptr(), 1234, 9999, front=True, back=False)
     assert_bit_equal(sub, osc.flux_mesh(e6, 1234, 9999, True, False), "mesh flux, sub-range")
     assert rt.illumination_flux(pr[:0])[3] == 0
+
+
+def test_prebake_edge_cases(rt, mod, S, scenes):
+    v, t = small_mesh(scenes)
+    # not committed yet: probes need an acceleration structure (reference: silent return, RayTracer.cu:610-611)
+    with pytest.raises(mod.RtfError) as ei:
+        rt.prepare_light_probes(0, 0)
+    assert ei.value.code == mod.ERR_NOT_READY
+    # zero instances -> a geometry with no triangles: its scene instance contributes nothing
+    rt.set_geometry_instanced(9, v, t, np.zeros((0, 16), dtype=np.float32))
+    rt.set_geometry(1, v, t)
+    rt.set_material(1, S.Material())
+    rt.set_instance(1, 9, 1, scenes.IDENTITY.copy(), 5)
+    rt.set_instance(2, 1, 1, scenes.IDENTITY.copy(), 6)
+    rt.build_ias(63)
+    assert rt.triangle_count == len(t)
+    assert len(rt.prepare_light_probes(3, 3)) == 0
+    with pytest.raises(mod.RtfError):
+        rt.prepare_light_probes(0, len(t) + 1)
+    # bad index, bad stride
+    bad = t.copy()
+    bad[0, 0] = len(v)
+    with pytest.raises(mod.RtfError, match="out of range"):
+        rt.set_geometry_instanced(9, v, bad, scenes.IDENTITY.copy().reshape(1, 16))
+    # single-term flux = energy * area (two faces count the area twice)
+    pr = rt.prepare_light_probes(0, 1)
+    pr["energy"] = (2.0, 0.0, 1.0)
+    out = rt.illumination_flux(pr)
+    a = mod.probe_area(pr)[0]
+    assert out[3] == np.float32(2) * a and out[0] == np.float32(2) * a and out[4] == np.float32(1.0)
