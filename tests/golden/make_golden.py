@@ -7,6 +7,7 @@
 * oracle_small.npz — outputs of the CPU oracle on small seeded inputs (hits, visit counts, Morton codes,
                    irradiance, LiDAR, camera).  The reference has no tests/fixtures for these, so this
                    file guards the oracle against drift and gives the GPU tests stored vectors to hit as well.
+* oracle_extra.npz — the same for the BSSRDF probe / irradiance, the instanced and skinned pre-kernels, light probes, flux.
 """
 import ctypes as C
 import json
@@ -35,6 +36,42 @@ def small_cases():
     rp = S.RayProperties(bounces=3, samples=16)
     grid = scenes.lidar_grid(center=(0.5, 3.0, 0.5), size=(1.6, 0.8), distance=(0.04, 0.04))
     return dict(soup=soup, rays=rays, illum_scene=illum_scene, env=env, rp=rp, grid=grid)
+
+
+def extra_cases():
+    """Seeded inputs of oracle_extra.npz: BSSRDF scene + probe rays, instanced / skinned bake, flux."""
+    sss_scene = scenes.random_soup(300, seed=11, extent=1.0, size=0.35)
+    m = sss_scene.materials[1]
+    m.subsurface_factor = 0.5
+    m.subsurface_color[:] = (0.9, 0.4, 0.2)
+    m.subsurface_radius[:] = (0.08, 0.0, 0.0)
+    lo, hi = scenes.scene_bounds(sss_scene)
+    probe_rays = scenes.incoherent_rays(512, lo, hi, seed=13)
+    probe_rays[:, 3] = 0.01
+    probe_rays[:, 7] = 0.6
+    mesh = scenes.random_soup(24, seed=17, size=0.4)
+    v, t = mesh.geometries[1]
+    v = v.copy()
+    v["tangent"] = np.roll(v["normal"], 1, axis=1) + np.float32(0.25)
+    k = np.arange(5, dtype=np.float64)
+    mats = np.zeros((5, 4, 4))
+    c, sn, sc = np.cos(0.7 * k), np.sin(0.7 * k), 0.6 + 0.2 * k
+    mats[:, 0, 0], mats[:, 0, 2], mats[:, 2, 0], mats[:, 2, 2] = c * sc, sn * sc, -sn * sc, c * sc
+    mats[:, 1, 1], mats[:, 3, 3] = sc, 1.0
+    mats[:, 0, 3], mats[:, 1, 3], mats[:, 2, 3] = 0.3 * k, -0.1 * k, 0.05 * k * k
+    mats = np.ascontiguousarray(mats.transpose(0, 2, 1)).astype(np.float32).reshape(5, 16)  # column-major
+    cols = scenes.hash_uniform(19, np.arange(20), 1).reshape(5, 4).astype(np.float32)
+    sv = np.zeros(len(v), dtype=S.SKINNED_VERTEX_DTYPE)
+    sv["v"] = v
+    i = np.arange(len(v))
+    sv["bone_id"], sv["bone_id2"] = -1, -1
+    sv["bone_id"][:, 0] = i % 5
+    sv["bone_id"][:, 2] = np.where(i % 2 == 0, (i + 1) % 5, -1)
+    sv["bone_id2"][:, 1] = np.where(i % 3 == 0, (i + 2) % 5, -1)
+    w = scenes.hash_uniform(23, np.arange(len(v) * 8), 2).reshape(-1, 8).astype(np.float32)
+    sv["weight"], sv["weight2"] = w[:, :4], w[:, 4:]
+    return dict(sss_scene=sss_scene, probe_rays=probe_rays, handle=101, verts=v, tris=t, mats=mats, cols=cols, skinned=sv,
+                env=S.EnvironmentProperties(color=(0.9, 1.0, 0.8)), rp=S.RayProperties(bounces=3, samples=16))
 
 
 def camera_props(width=16, height=12):
@@ -95,7 +132,24 @@ def main():
                         irradiance=irr.view(np.uint32), illum_rays=np.array([st.rays, st.paths]),
                         lidar_t=t.view(np.uint32), lidar_prim=prim, camera_color=col.view(np.uint32),
                         camera_normal=nrm.view(np.uint32), camera_albedo=alb.view(np.uint32))
+    write_extra()
     print("wrote", os.listdir(HERE))
+
+
+def write_extra():
+    """oracle_extra.npz — BSSRDF (probe records, irradiance), pre-kernels, light probes and flux from the CPU oracle."""
+    x = extra_cases()
+    osc = orc.OracleScene(x["sss_scene"], 63)
+    rec = osc.sss_probe(x["probe_rays"], np.full(len(x["probe_rays"]), x["handle"], dtype=np.uint64))
+    irr, st = osc.illum_mesh(x["env"], x["rp"], seed=0xABCD, push=1e-3)
+    bv, bt = orc.bake_instanced(x["verts"], x["tris"], x["mats"], x["cols"])
+    sk = orc.bake_skinned(x["skinned"], x["mats"])
+    pr = osc.make_probes(front=True, back=True)
+    pr["energy"] = irr[:, :3]
+    flux = orc.flux_probes(pr)
+    np.savez_compressed(os.path.join(HERE, "oracle_extra.npz"), sss_records=rec, sss_irradiance=irr.view(np.uint32),
+                        sss_rays=np.array([st.rays, st.paths]), bake_instanced=bv.view(np.uint8), bake_tris=bt,
+                        bake_skinned=sk.view(np.uint8), probes=pr.view(np.uint8), flux=flux.view(np.uint32))
 
 
 if __name__ == "__main__":

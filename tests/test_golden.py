@@ -35,3 +35,24 @@ def test_oracle_reproduces_golden(orc, S):
     assert_bit_equal(col.view(np.uint32), g["camera_color"], "camera colour")
     assert_bit_equal(nrm.view(np.uint32), g["camera_normal"], "camera normal")
     assert_bit_equal(alb.view(np.uint32), g["camera_albedo"], "camera albedo")
+
+
+def test_oracle_reproduces_extra_golden(orc, S):
+    """BSSRDF probe / irradiance, instanced and skinned pre-kernels, light probes and flux vs tests/golden/oracle_extra.npz."""
+    from tests.golden.make_golden import extra_cases
+    g = np.load(os.path.join(GOLDEN, "oracle_extra.npz"))
+    x = extra_cases()
+    osc = orc.OracleScene(x["sss_scene"], 63)
+    hs = np.full(len(x["probe_rays"]), x["handle"], dtype=np.uint64)
+    assert np.array_equal(osc.sss_probe(x["probe_rays"], hs), g["sss_records"])
+    assert np.array_equal(osc.sss_probe(x["probe_rays"], hs, brute=True), g["sss_records"])
+    irr, st = osc.illum_mesh(x["env"], x["rp"], seed=0xABCD, push=1e-3)
+    assert_bit_equal(irr.view(np.uint32), g["sss_irradiance"], "BSSRDF irradiance")
+    assert [st.rays, st.paths] == g["sss_rays"].tolist()
+    bv, bt = orc.bake_instanced(x["verts"], x["tris"], x["mats"], x["cols"])
+    assert np.array_equal(bv.view(np.uint8), g["bake_instanced"]) and np.array_equal(bt, g["bake_tris"])
+    assert np.array_equal(orc.bake_skinned(x["skinned"], x["mats"]).view(np.uint8), g["bake_skinned"])
+    pr = osc.make_probes(front=True, back=True)
+    pr["energy"] = irr[:, :3]
+    assert np.array_equal(pr.view(np.uint8), g["probes"])
+    assert_bit_equal(orc.flux_probes(pr).view(np.uint32), g["flux"], "flux")

@@ -79,3 +79,34 @@ def test_illumination_and_camera_parity(rt, orc, S, scenes, brdf):
     close(cam.download(S.OUT_ALBEDO).reshape(-1, 4), alb, "albedo")
     assert rt.last_job_stats() == (cst.rays, cst.paths)
     cam.destroy()
+
+
+def test_extra_golden_fixtures(rt, S):
+    """CUDA path vs the committed fixtures (tests/golden/oracle_extra.npz): probe records and pre-kernels bit for bit,
+    irradiance <= 1e-5, flux bit for bit on the fixture's probes."""
+    import os
+
+    from tests.golden.make_golden import extra_cases
+
+    from .conftest import GOLDEN
+    g = np.load(os.path.join(GOLDEN, "oracle_extra.npz"))
+    x = extra_cases()
+    rt.load_scene(x["sss_scene"], 63)
+    hs = np.full(len(x["probe_rays"]), x["handle"], dtype=np.uint64)
+    assert np.array_equal(rt.sss_probe(x["probe_rays"], hs), g["sss_records"])
+    irr = rt.estimate_illumination_mesh(x["env"], x["rp"], seed=0xABCD, push=1e-3)
+    gold = g["sss_irradiance"].view(np.float32)
+    close(irr[:, :3], gold[:, :3], "energy")
+    close(irr[:, 3:], gold[:, 3:], "direction", atol=1e-5)
+    assert list(rt.last_job_stats()) == g["sss_rays"].tolist()
+    pr = np.ascontiguousarray(g["probes"]).view(S.ILLUM_SAMPLER_DTYPE)
+    assert rt.illumination_flux(pr).view(np.uint32).tolist() == g["flux"].tolist()
+    got = rt.prepare_light_probes()
+    got["energy"] = pr["energy"]
+    assert got.tobytes() == pr.tobytes()
+    rt.set_geometry_instanced(50, x["verts"], x["tris"], x["mats"], x["cols"])
+    bv, bt = rt.read_baked_geometry(50, len(x["verts"]) * 5, len(x["tris"]) * 5)
+    assert np.array_equal(bv.view(np.uint8), g["bake_instanced"]) and np.array_equal(bt, g["bake_tris"])
+    rt.set_geometry_skinned(51, x["skinned"], x["tris"], x["mats"])
+    sk, _ = rt.read_baked_geometry(51, len(x["verts"]), len(x["tris"]))
+    assert np.array_equal(sk.view(np.uint8), g["bake_skinned"])
