@@ -77,7 +77,7 @@ int rtf_destroy(rtf_ctx* ctx) {
                     &ctx->ws.hits, &ctx->ws.counters, &ctx->ws.thr,
                     &ctx->ws.acc, &ctx->ws.dir0w, &ctx->ws.first_n, &ctx->ws.first_a, &ctx->ws.first_p,
                     &ctx->ws.sort_keys, &ctx->ws.sort_keys_alt, &ctx->ws.sort_vals, &ctx->ws.sort_vals_alt,
-                    &ctx->ws.sort_tmp, &ctx->ws.io, &ctx->ws.pend_o, &ctx->ws.pend_d, &ctx->ws.pend_t};
+                    &ctx->ws.sort_tmp, &ctx->ws.io, &ctx->ws.pend_o, &ctx->ws.pend_d, &ctx->ws.pend_t, &ctx->ws.sort_kin};
   for (DevBuf* b : bufs) b->release();
   ctx->d_btfs.release(), ctx->d_env_faces.release();
   release_material_tables(ctx);

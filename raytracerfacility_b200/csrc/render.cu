@@ -15,6 +15,7 @@
 #include "rtf_shade.cuh"
 #include "rtf_trace.cuh"
 #include "rtf_sss.cuh"
+#include "rtf_sort.cuh"
 
 namespace rtf {
 
@@ -568,6 +569,56 @@ __global__ void k_finalize_illum(float* accum6, uint64_t n, int faces, int sampl
   }
 }
 
+// ---- ray sort between wavefronts (option "sort_rays"): key = direction octant (3 b) | Morton code of the origin's cell in a
+//      64^3 grid over the scene box (18 b); empty queue slots get bit 21 and sort behind every ray.  The sorted order only
+//      changes which lanes trace which rays: per-path state is addressed by the path index the ray carries, so results are
+//      bit-identical with the option on or off. ---------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_ray_sort_keys(const float4* __restrict__ ra, const float4* __restrict__ rb,
+                                                       const uint32_t* __restrict__ count, uint32_t n_max,
+                                                       const float* __restrict__ fb, uint32_t* __restrict__ keys) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_max) return;
+  uint32_t key = 1u << 21;
+  if (i < *count) {
+    const float4 a = ra[i], b = rb[i];
+    const float3 lo = f3(fb[0], fb[1], fb[2]), hi = f3(fb[3], fb[4], fb[5]);
+    const float3 ext = hi - lo;
+    const float3 inv = f3(ext.x > 0 ? 64.0f / ext.x : 0.0f, ext.y > 0 ? 64.0f / ext.y : 0.0f, ext.z > 0 ? 64.0f / ext.z : 0.0f);
+    const uint32_t cx = (uint32_t)fminf(fmaxf((a.x - lo.x) * inv.x, 0.0f), 63.0f);
+    const uint32_t cy = (uint32_t)fminf(fmaxf((a.y - lo.y) * inv.y, 0.0f), 63.0f);
+    const uint32_t cz = (uint32_t)fminf(fmaxf((a.z - lo.z) * inv.z, 0.0f), 63.0f);
+    const uint32_t oct = (b.x < 0.0f ? 4u : 0u) | (b.y < 0.0f ? 2u : 0u) | (b.z < 0.0f ? 1u : 0u);
+    key = (oct << 18) | (expand10(cx) << 2) | (expand10(cy) << 1) | expand10(cz);
+  }
+  keys[i] = key;
+}
+__global__ void __launch_bounds__(256) k_ray_gather(const float4* __restrict__ ra, const float4* __restrict__ rb,
+                                                    const uint32_t* __restrict__ perm, const uint32_t* __restrict__ count,
+                                                    uint32_t n_max, float4* __restrict__ oa, float4* __restrict__ ob) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_max || i >= *count) return;
+  const uint32_t src = perm[i];
+  oa[i] = ra[src], ob[i] = rb[src];
+}
+// Sorts the rays of wavefront `wave` (in queue qi) into queue qi^1, which is free at that moment.
+static int sort_wavefront(rtf_ctx* ctx, Queues& q, int qi, int wave, size_t paths) {
+  Workspace& w = ctx->ws;
+  int rc;
+  const uint32_t n = (uint32_t)paths;
+  if ((rc = w.sort_kin.reserve(4 * paths)) || (rc = w.sort_keys_alt.reserve(4 * paths)) || (rc = w.sort_tmp.reserve(4 * paths)) ||
+      (rc = w.sort_vals.reserve(4 * paths)) || (rc = w.sort_vals_alt.reserve(4 * paths)))
+    return rc;
+  LAUNCH(ctx, k_ray_sort_keys, div_up(paths, 256), 256, 0, q.ray_a[qi], q.ray_b[qi], q.count + wave, n,
+         ctx->ba.scene_bounds.as<float>() + 8, w.sort_kin.as<uint32_t>());
+  if ((rc = radix_sort_pairs<uint32_t>(ctx, w.sort_kin.as<uint32_t>(), w.sort_keys_alt.as<uint32_t>(), w.sort_tmp.as<uint32_t>(),
+                                       nullptr, w.sort_vals.as<uint32_t>(), w.sort_vals_alt.as<uint32_t>(), n, 0, 22,
+                                       ctx->ba.sort_hist, ctx->ba.sort_status)))
+    return rc;
+  LAUNCH(ctx, k_ray_gather, div_up(paths, 256), 256, 0, q.ray_a[qi], q.ray_b[qi], w.sort_vals.as<uint32_t>(), q.count + wave, n,
+         q.ray_a[qi ^ 1], q.ray_b[qi ^ 1]);
+  return RTF_OK;
+}
+
 static size_t batch_capacity(const rtf_ctx* ctx) { return ctx->batch_paths < 1024 ? 1024 : ctx->batch_paths; }
 
 static int ensure_workspace(rtf_ctx* ctx, size_t cap, bool camera) {
@@ -630,6 +681,11 @@ static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_
   int qi = 0;
   for (int w = 0; w < waves; w++) {
     const float tmin = (camera && w == 0) ? 0.0f : 1e-3f;
+    if (ctx->sort_rays && w >= 1) {  // bounce rays leave the surfaces in random directions: restore some coherence
+      int rc;
+      if ((rc = sort_wavefront(ctx, q, qi, w, paths))) return rc;
+      qi ^= 1;
+    }
     if (ctx->scene.has_alpha)
       LAUNCH(ctx, k_trace_queue<true>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
     else

@@ -129,7 +129,7 @@ struct Workspace {  // wavefront queues + path state, sized for `capacity` paths
   DevBuf ray_a[2], ray_b[2], hits, counters;
   DevBuf thr, acc, dir0w, first_n, first_a, first_p;  // per-path state (SoA float4)
   DevBuf pend_o, pend_d, pend_t;                      // BSSRDF: bounce ray waiting for the subsurface path
-  DevBuf sort_keys, sort_keys_alt, sort_vals, sort_vals_alt, sort_tmp;
+  DevBuf sort_keys, sort_keys_alt, sort_vals, sort_vals_alt, sort_tmp, sort_kin;
   DevBuf io;  // staging for AoS entry points
 };
 
@@ -183,7 +183,7 @@ struct rtf_ctx {
   rtf::DevBuf d_stats;  // {rays u64, paths u64}
   // options (rtf_set_option)
   size_t batch_paths = (size_t)1 << 24;  // 2^24 paths: ~3 GB of queues + path state; +12..20 % over 2^22 (fewer, fuller waves)
-  int sort_rays = 1;
+  int sort_rays = 0;  // option "sort_rays": sort bounce rays by (octant, origin cell) before tracing (measured: DESIGN.md)
   int brdf = RTF_BRDF_REFERENCE;  // option "brdf"
   // build-stage events: flatten | bounds+morton | sort | karras+refit | collapse | end
   cudaEvent_t build_ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};

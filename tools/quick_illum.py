@@ -16,6 +16,7 @@ def main():
     ap.add_argument("--tris", type=int, default=0)
     ap.add_argument("--batch-log2", type=int, default=0)
     ap.add_argument("--reps", type=int, default=2)
+    ap.add_argument("--sort-rays", type=int, default=0, help="option sort_rays: sort bounce rays by (octant, origin cell)")
     ap.add_argument("--oracle-bvh", type=int, default=0, help="build the BVH with the CPU oracle and upload it (experiments)")
     args = ap.parse_args()
     import torch
@@ -28,6 +29,7 @@ def main():
     rt.set_stream(stream.cuda_stream)
     if args.batch_log2:
         rt.set_option("batch_paths", 1 << args.batch_log2)
+    rt.set_option("sort_rays", args.sort_rays)
     sd = scenes.sorghum_scene(args.plants)
     rt.load_scene(sd, 63)
     if args.oracle_bvh:
