@@ -24,6 +24,28 @@ def sample_shard(samples, world, rank):
     return split_range(samples, world, rank)
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Pin this process to the CPU cores NVML reports as local to GPU `local_rank` (first-touch then places pinned host
+    buffers on that NUMA node).  With several ranks feeding their GPUs from host memory (the host-buffer entry points)
+    this keeps the H2D / D2H traffic off the inter-socket link.  Best effort: returns the core list, or None."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        cores = [64 * w + b for w, mask in enumerate(words) for b in range(64) if (int(mask) >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cores = [c for c in cores if c in allowed]
+        if cores:
+            os.sched_setaffinity(0, cores)
+            return cores
+    except Exception:
+        pass
+    return None
+
+
 def init_distributed(backend=None):
     """Initialise torch.distributed from the torchrun environment; returns (rank, world, local_rank)."""
     import os
@@ -33,6 +55,8 @@ def init_distributed(backend=None):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and torch.cuda.is_available():
+        bind_to_gpu_numa_node(local)
     if world > 1 and not dist.is_initialized():
         if backend is None:
             backend = "nccl" if torch.cuda.is_available() else "gloo"
