@@ -18,6 +18,7 @@ def main():
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--sort-rays", type=int, default=0, help="option sort_rays: sort bounce rays by (octant, origin cell)")
     ap.add_argument("--oracle-bvh", type=int, default=0, help="build the BVH with the CPU oracle and upload it (experiments)")
+    ap.add_argument("--presplit", type=int, default=0, help="option presplit (0 = library default)")
     args = ap.parse_args()
     import torch
 
@@ -31,7 +32,7 @@ def main():
         rt.set_option("batch_paths", 1 << args.batch_log2)
     rt.set_option("sort_rays", args.sort_rays)
     sd = scenes.sorghum_scene(args.plants)
-    rt.load_scene(sd, 63)
+    rt.load_scene(sd, 63, presplit=args.presplit or None)
     if args.oracle_bvh:
         from oracle import pyoracle as _orc
         from raytracerfacility_b200 import structs as _S

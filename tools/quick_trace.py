@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--check", type=int, default=1 << 17)
     ap.add_argument("--sort", type=int, default=0, help="sort the rays by (octant, origin cell of 2^SORT per axis) first")
     ap.add_argument("--oracle-bvh", type=int, default=0, help="build the BVH with the CPU oracle and upload it (experiments)")
+    ap.add_argument("--presplit", type=int, default=0, help="option presplit (0 = library default)")
     args = ap.parse_args()
     import torch
 
@@ -29,7 +30,7 @@ def main():
     rt = module.RayTracer(0)
     rt.set_stream(stream.cuda_stream)
     sd = scenes.sorghum_scene(args.plants)
-    rt.load_scene(sd, 63)
+    rt.load_scene(sd, 63, presplit=args.presplit or None)
     if args.oracle_bvh:
         from oracle import pyoracle as _orc
         from raytracerfacility_b200 import structs as _S
