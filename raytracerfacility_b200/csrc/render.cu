@@ -221,8 +221,11 @@ struct ShadeParams {
 };
 // SSS = some material has subsurfaceFactor > 0: the kernel carries the BSSRDF spatial probe (rtf_sss.cuh) and the
 // pending-bounce state.
+#ifndef RTF_SHADE_MIN_BLOCKS
+#define RTF_SHADE_MIN_BLOCKS 3
+#endif
 template <bool SSS>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, SSS ? 1 : RTF_SHADE_MIN_BLOCKS)
     k_shade(DevScene sc, rtf_env env, ShadeParams sp, PathMap pm, Queues q, int qi, int wave, PathState ps) {
   const uint32_t n = q.count[wave];
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
