@@ -381,6 +381,8 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
   pr.rays = 0;
   V3 T = v3(1, 1, 1), acc = v3(0, 0, 0);
   uint32_t hit_count = 0;
+  uint32_t wave = 0;  // radiance rays traced so far on this path = the wavefront index the GPU traces this ray in; keys the
+                      // any-hit draws (equal to hit_count except after a BSSRDF resume, where two rays share a hit count)
   bool any_hit_enabled = true;  // BTF bounce rays run with OPTIX_RAY_FLAG_DISABLE_ANYHIT (RF.cuh:239)
   // BSSRDF (RF.cuh:97-133): the first hit may start TWO radiance paths, the subsurface one first.  Both share
   // PerRayData::m_hitCount, which is never reset: the ordinary bounce path is traced after the subsurface path has
@@ -400,11 +402,12 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
     Ray ray{o, tmin, d, 1e20f};
     Hit h;
     if (any_hit_enabled) {
-      AlphaFilter flt{&sc, seed, unit, hit_count};
+      AlphaFilter flt{&sc, seed, unit, wave};
       h = trace(sc.bvh, ray, stats, false, flt);
     } else {
       h = trace(sc.bvh, ray, stats, false);
     }
+    wave++;
     any_hit_enabled = true;
     pr.rays++;
     if (h.prim == 0xFFFFFFFFu) {
