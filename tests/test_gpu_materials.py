@@ -256,3 +256,26 @@ def test_subsurface_with_all_material_kinds(rt, orc, scenes, S):
     small = rt.estimate_illumination_mesh(env, rp, seed=0xC0DE, push=1e-3)
     cpu, _ = osc.illum_mesh(env, rp, seed=0xC0DE, push=1e-3)
     _close(small[:, :3], cpu[:, :3], "irradiance (2048-path batches)", atol=1e-6)
+
+
+def test_subsurface_switched_on_by_a_material_only_commit_and_ray_sort(rt, orc, scenes, S):
+    """has_sss flips in a material-only commit (BVH kept); the ray-sort option leaves the BSSRDF + any-hit result alone."""
+    sd = scenes.materials_scene()
+    rt.load_scene(sd)
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=3, samples=8)
+    plain = rt.estimate_illumination_mesh(env, rp, seed=11, push=1e-3)
+    m = sd.materials[1]
+    m.subsurface_factor, m.subsurface_radius[0] = 0.6, 0.3
+    rt.set_material(1, m)
+    rt.build_ias(63)
+    st = rt.commit_stats()
+    assert st["materials"] == 1 and st["full"] == 1
+    osc = orc.OracleScene(sd)
+    cpu, cst = osc.illum_mesh(env, rp, seed=11, push=1e-3)
+    on = rt.estimate_illumination_mesh(env, rp, seed=11, push=1e-3)
+    _close(on[:, :3], cpu[:, :3], "irradiance after the material-only commit", atol=1e-6)
+    assert rt.last_job_stats() == (cst.rays, cst.paths)
+    assert np.abs(on[:, :3] - plain[:, :3]).max() > 1e-3
+    rt.set_option("sort_rays", 1)
+    srt = rt.estimate_illumination_mesh(env, rp, seed=11, push=1e-3)
+    assert np.array_equal(srt.view(np.uint32), on.view(np.uint32)) and rt.last_job_stats() == (cst.rays, cst.paths)
