@@ -252,8 +252,14 @@ RTF_API int rtf_triangle_count(rtf_ctx* ctx, uint64_t* n_triangles);
  * stored one, and rtf_set_material / rtf_set_instance with identical contents, are no-ops; rtf_commit
  * rebuilds the BVH only if a geometry, an instance or "presplit" changed, re-resolves the material-side
  * tables only (materials, textures, BTFs, cube map — microseconds) if nothing else did, and returns at once
- * if nothing changed.  out4 = {full builds, material-only commits, skipped commits, skipped geometry uploads}. */
-RTF_API int rtf_commit_stats(rtf_ctx* ctx, uint64_t* out4);
+ * if nothing changed.  With option "refit" = 1, a commit in which only vertex positions or instance transforms
+ * moved (same geometries, instances and triangle counts) takes the REFIT path: the sorted reference order
+ * and the radix tree of the last full build are reused, reference boxes, node boxes, the 8-wide collapse
+ * and the triangle records are recomputed (no bounds / split planning / Morton / sort / Karras).  Hits do
+ * not depend on the tree; its quality decays as the scene deforms, so rebuild fully from time to time
+ * (any topology change does).  out5 = {full builds, material-only commits, skipped commits, skipped
+ * geometry uploads, refits}. */
+RTF_API int rtf_commit_stats(rtf_ctx* ctx, uint64_t* out5);
 /* Device time (ms, CUDA events) of the last rtf_commit per stage:
  * {flatten, bounds+morton, sort, karras+refit, collapse+encode, total}; n >= 6.  (The reference
  * has no counterpart: its builds are opaque optixAccelBuild calls, RT.cu:1562-1584.) */
@@ -263,7 +269,8 @@ RTF_API int rtf_build_timings(rtf_ctx* ctx, float* ms_out, int n);
  * measured slower than the unsorted persistent-lane traversal; results are bit-identical),
  * "presplit" = most references a long thin triangle may be cut into before the Morton sort
  * (default 8, 1 = off; applies at the next rtf_commit; hits do not depend on it),
- * "brdf" = RTF_BRDF_REFERENCE (default) or RTF_BRDF_LAMBERT_GGX. */
+ * "brdf" = RTF_BRDF_REFERENCE (default) or RTF_BRDF_LAMBERT_GGX,
+ * "refit" = 0/1 allow the refit path of rtf_commit (see rtf_commit_stats; default 0). */
 RTF_API int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value);
 
 /* ---- images in linear memory ---------------------------------------------------------------

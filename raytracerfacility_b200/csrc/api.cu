@@ -132,6 +132,10 @@ int rtf_set_geometry(rtf_ctx* ctx, uint64_t handle, const void* vertices, size_t
     }
   }
   ctx->geom_dirty = true;
+  {
+    auto it = ctx->geoms.find(handle);
+    if (it == ctx->geoms.end() || it->second.baked || it->second.n_tris != n_triangles) ctx->topo_dirty = true;
+  }
   Geometry& g = ctx->geoms[handle];
   g.verts.resize(n_vertices);
   for (size_t i = 0; i < n_vertices; i++) memcpy(&g.verts[i], (const char*)vertices + i * stride, sizeof(rtf_vertex));
@@ -160,7 +164,7 @@ int rtf_set_geometry_instanced(rtf_ctx* ctx, uint64_t handle, const void* vertic
   }
   std::vector<rtf_vertex> packed(n_vertices);
   for (size_t i = 0; i < n_vertices; i++) memcpy(&packed[i], (const char*)vertices + i * stride, sizeof(rtf_vertex));
-  ctx->geom_dirty = true;
+  ctx->geom_dirty = true, ctx->topo_dirty = true;
   if (ctx->geoms.count(handle)) ctx->ready = false;  // the committed scene may point at the arrays re-baked below
   Geometry& g = ctx->geoms[handle];
   g.verts.clear(), g.tris.clear();
@@ -182,7 +186,7 @@ int rtf_set_geometry_skinned(rtf_ctx* ctx, uint64_t handle, const void* skinned_
       set_error("rtf_set_geometry_skinned: triangle index out of range");
       return RTF_ERR_INVALID;
     }
-  ctx->geom_dirty = true;
+  ctx->geom_dirty = true, ctx->topo_dirty = true;
   if (ctx->geoms.count(handle)) ctx->ready = false;  // the committed scene may point at the arrays re-baked below
   Geometry& g = ctx->geoms[handle];
   g.verts.clear(), g.tris.clear();
@@ -227,6 +231,7 @@ int rtf_set_instance(rtf_ctx* ctx, uint64_t handle, uint64_t geom, uint64_t mat,
   if (iit != ctx->insts.end() && iit->second.geom == geom && iit->second.mat == mat && iit->second.component == comp &&
       !memcmp(iit->second.xform, xform, 64))
     return RTF_OK;  // unchanged (RayTracedInstance::m_version check, RayTracerLayer.cpp:76-92)
+  if (iit == ctx->insts.end() || iit->second.geom != geom || iit->second.mat != mat) ctx->topo_dirty = true;
   Instance& in = ctx->insts[handle];
   in.geom = geom, in.mat = mat, in.component = comp;
   memcpy(in.xform, xform, 64);
@@ -240,7 +245,7 @@ int rtf_remove_geometry(rtf_ctx* ctx, uint64_t handle) {
   cudaStreamSynchronize(ctx->stream);
   it->second.d_verts.release(), it->second.d_tris.release();
   ctx->geoms.erase(it);
-  ctx->geom_dirty = true;
+  ctx->geom_dirty = true, ctx->topo_dirty = true;
   ctx->ready = false;  // the committed scene may point at the released arrays
   return RTF_OK;
 }
@@ -252,7 +257,7 @@ int rtf_remove_material(rtf_ctx* ctx, uint64_t handle) {
 }
 int rtf_remove_instance(rtf_ctx* ctx, uint64_t handle) {
   CHECK_CTX(ctx);
-  ctx->geom_dirty = true;
+  ctx->geom_dirty = true, ctx->topo_dirty = true;
   return ctx->insts.erase(handle) ? RTF_OK : RTF_ERR_NOT_FOUND;
 }
 
@@ -272,6 +277,8 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
     return RTF_OK;
   }
   const bool keep_bvh_if_possible = was_ready && !ctx->geom_dirty;
+  const bool refit_if_possible = was_ready && ctx->geom_dirty && !ctx->topo_dirty && ctx->refit && ctx->n_refs > 0;
+  const uint32_t old_tris = ctx->n_tris;
   ctx->ready = false;
   int rc;
   cudaStream_t st = ctx->stream;
@@ -354,8 +361,13 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   } else {
   if ((rc = flatten_scene(ctx))) return rc;
   RTF_CUDA(cudaStreamSynchronize(st));  // host vectors above die at return
-  if ((rc = build_bvh(ctx, morton_bits))) return rc;
-  ctx->commits_full++;
+  if (refit_if_possible && first == old_tris && alpha_class == ctx->alpha_class) {
+    if ((rc = refit_bvh(ctx))) return rc;
+    ctx->commits_refit++;
+  } else {
+    if ((rc = build_bvh(ctx, morton_bits))) return rc;
+    ctx->commits_full++;
+  }
   {  // shrink the node array to its final size (collapse allocated the n/2 worst case)
     DevBuf exact;
     if ((rc = exact.reserve(80 * (size_t)ctx->n_nodes))) return rc;
@@ -366,7 +378,7 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   }
   }
   ctx->alpha_class = alpha_class;
-  ctx->geom_dirty = false, ctx->mat_dirty = false;
+  ctx->geom_dirty = false, ctx->mat_dirty = false, ctx->topo_dirty = false;
   ctx->morton_bits = morton_bits;
   DevScene& s = ctx->scene;
   s.nodes = ctx->d_nodes.as<uint4>(), s.tris = ctx->d_tris48.as<float4>();
@@ -384,10 +396,10 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   ctx->ready = true;
   return RTF_OK;
 }
-int rtf_commit_stats(rtf_ctx* ctx, uint64_t* out4) {
-  if (!ctx || !out4) return RTF_ERR_INVALID;
-  out4[0] = ctx->commits_full, out4[1] = ctx->commits_materials, out4[2] = ctx->commits_skipped;
-  out4[3] = ctx->geometry_uploads_skipped;
+int rtf_commit_stats(rtf_ctx* ctx, uint64_t* out5) {
+  if (!ctx || !out5) return RTF_ERR_INVALID;
+  out5[0] = ctx->commits_full, out5[1] = ctx->commits_materials, out5[2] = ctx->commits_skipped;
+  out5[3] = ctx->geometry_uploads_skipped, out5[4] = ctx->commits_refit;
   return RTF_OK;
 }
 int rtf_build_timings(rtf_ctx* ctx, float* ms_out, int n) {
@@ -414,7 +426,7 @@ int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value) {
       set_error("presplit must be in [1, 64]");
       return RTF_ERR_INVALID;
     }
-    if (ctx->presplit != (int)value) ctx->geom_dirty = true;
+    if (ctx->presplit != (int)value) ctx->geom_dirty = true, ctx->topo_dirty = true;
     ctx->presplit = (int)value;  // takes effect at the next rtf_commit
   } else if (!strcmp(name, "brdf")) {
     if (value != RTF_BRDF_REFERENCE && value != RTF_BRDF_LAMBERT_GGX) {
@@ -422,6 +434,8 @@ int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value) {
       return RTF_ERR_INVALID;
     }
     ctx->brdf = (int)value;
+  } else if (!strcmp(name, "refit")) {
+    ctx->refit = value != 0;
   } else if (!strcmp(name, "sort_rays")) {
     ctx->sort_rays = value != 0;
   } else {

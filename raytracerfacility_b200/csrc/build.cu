@@ -181,6 +181,23 @@ __global__ void k_split_emit(const float* __restrict__ pos9, uint32_t n, int max
     o[0] = bx.lo.x, o[1] = bx.lo.y, o[2] = bx.lo.z, o[3] = bx.hi.x, o[4] = bx.hi.y, o[5] = bx.hi.z;
   }
 }
+// Refit: the reference counts of the last build are kept (first[t+1] - first[t] slabs per triangle), only the boxes are
+// recomputed from the moved vertices; the slab axis is the longest axis of the triangle's current box.
+__global__ void k_split_emit_fixed(const float* __restrict__ pos9, uint32_t n, const uint32_t* __restrict__ first,
+                                   float* __restrict__ ref_box) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  float3 a, b, c;
+  load_tri(pos9, t, a, b, c);
+  const int axis = split_plan(a, b, c, 1).axis;
+  const uint32_t r0 = first[t];
+  const int k = (int)(first[t + 1] - r0);
+  for (int j = 0; j < k; j++) {
+    const Box3 bx = split_slab_box(a, b, c, axis, k, j);
+    float* o = ref_box + 6 * (size_t)(r0 + j);
+    o[0] = bx.lo.x, o[1] = bx.lo.y, o[2] = bx.lo.z, o[3] = bx.hi.x, o[4] = bx.hi.y, o[5] = bx.hi.z;
+  }
+}
 __device__ __forceinline__ Box3 ref_box_load(const float* __restrict__ ref_box, uint32_t r) {
   const float* b = ref_box + 6 * (size_t)r;
   Box3 bx;
@@ -453,6 +470,28 @@ int flatten_scene(rtf_ctx* ctx) {
   return RTF_OK;
 }
 
+static int collapse_encode(rtf_ctx* ctx, uint32_t n);
+
+// Fast path for moved geometry with unchanged topology (option "refit"): the sorted reference order and the radix tree of
+// the last build are reused; reference boxes, node boxes, the 8-wide collapse and the triangle records are recomputed.
+// Skips bounds, split planning, Morton codes, the radix sort and the Karras tree.  The tree keeps the shape it had for the
+// old positions, so its quality decays as the scene deforms; hits do not depend on it.
+int refit_bvh(rtf_ctx* ctx) {
+  const uint32_t nt = ctx->n_tris, n = ctx->n_refs;
+  BuildArrays& ba = ctx->ba;
+  if (nt == 0 || n == 0) return RTF_ERR_NOT_READY;
+  mark(ctx, 1);
+  LAUNCH(ctx, k_split_emit_fixed, div_up(nt, 256), 256, 0, ctx->d_pos9.as<float>(), nt, ba.ref_first.as<uint32_t>(),
+         ba.ref_box.as<float>());
+  mark(ctx, 2);
+  mark(ctx, 3);
+  if (n > 1) RTF_CUDA(cudaMemsetAsync(ba.flags.p, 0, 4 * (size_t)n, ctx->stream));
+  LAUNCH(ctx, k_refit, div_up(n, 256), 256, 0, ba.ref_box.as<float>(), ba.sorted_ids.as<uint32_t>(), (int)n,
+         ba.children.as<int2>(), ba.parent.as<int>(), ba.boxes.as<float>(), ba.flags.as<uint32_t>());
+  ctx->n_nodes = 0, ctx->depth = 0;
+  return collapse_encode(ctx, n);
+}
+
 int build_bvh(rtf_ctx* ctx, int bits) {
   const uint32_t nt = ctx->n_tris;
   BuildArrays& ba = ctx->ba;
@@ -511,7 +550,14 @@ int build_bvh(rtf_ctx* ctx, int bits) {
   }
   LAUNCH(ctx, k_refit, div_up(n, 256), 256, 0, ba.ref_box.as<float>(), ba.sorted_ids.as<uint32_t>(), (int)n,
          ba.children.as<int2>(), ba.parent.as<int>(), ba.boxes.as<float>(), ba.flags.as<uint32_t>());
+  return collapse_encode(ctx, n);
+}
 
+// Radix tree + node boxes -> 8-wide compressed nodes and BVH-ordered triangle records (shared by build and refit).
+static int collapse_encode(rtf_ctx* ctx, uint32_t n) {
+  BuildArrays& ba = ctx->ba;
+  cudaStream_t st = ctx->stream;
+  int rc;
   // ---- collapse ----
   mark(ctx, 4);
   const size_t max_nodes = (size_t)n / 2 + 64;

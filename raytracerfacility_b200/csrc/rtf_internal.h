@@ -164,6 +164,10 @@ struct rtf_ctx {
   // geom_dirty = a geometry or instance changed since the last commit (BVH rebuild); mat_dirty = only material-side
   // tables changed (materials, textures, BTFs, cube map: re-resolved without touching the BVH)
   bool geom_dirty = true, mat_dirty = true;
+  bool topo_dirty = true;  // a geometry / instance appeared, vanished or changed its triangle count, or "presplit" changed
+                           // (geom_dirty && !topo_dirty = vertices or transforms moved: candidates for the refit path)
+  int refit = 0;           // option "refit"
+  uint64_t commits_refit = 0;
   std::vector<uint8_t> alpha_class;  // per committed instance: may ignore hits (decides TRI_FLAG_ALPHA in the BVH)
   uint64_t commits_full = 0, commits_materials = 0, commits_skipped = 0, geometry_uploads_skipped = 0;
   // committed state
@@ -207,6 +211,7 @@ int flux_probes_device(rtf_ctx* ctx, const rtf_illum_sampler* d_probes, uint64_t
 int flux_mesh_device(rtf_ctx* ctx, const float* d_energy6, uint64_t tri_begin, uint64_t tri_end, int faces, float* out8_host);
 // build.cu
 int build_bvh(rtf_ctx* ctx, int morton_bits);
+int refit_bvh(rtf_ctx* ctx);
 // materials.cu
 int resolve_materials(rtf_ctx* ctx, std::map<uint64_t, uint32_t>& mat_index, std::vector<DevMaterial>& mats,
                       std::vector<DevBTF>& btfs);

@@ -280,9 +280,9 @@ class RayTracer:
 
     def commit_stats(self):
         """{full builds, material-only commits, skipped commits, skipped geometry uploads} (scene-sync diffing)."""
-        out = (C.c_uint64 * 4)()
+        out = (C.c_uint64 * 5)()
         _check(lib().rtf_commit_stats(self.h, out))
-        return dict(zip(("full", "materials", "skipped", "uploads_skipped"), [int(x) for x in out]))
+        return dict(zip(("full", "materials", "skipped", "uploads_skipped", "refits"), [int(x) for x in out]))
 
     @property
     def triangle_count(self):

@@ -112,7 +112,7 @@ def test_scene_sync_diffing(rt, orc, S, scenes):
         rt.set_instance(ih, g, m, x, comp)
     rt.build_ias(63)
     nodes0 = rt.debug(S.DBG_WIDE_NODES).copy()
-    assert rt.commit_stats() == {"full": 1, "materials": 0, "skipped": 0, "uploads_skipped": 0}
+    assert rt.commit_stats() == {"full": 1, "materials": 0, "skipped": 0, "uploads_skipped": 0, "refits": 0}
     # the same scene again, same versions
     for gh, (v, t) in sd.geometries.items():
         rt.set_geometry(gh, v, t, version=7)
@@ -121,7 +121,7 @@ def test_scene_sync_diffing(rt, orc, S, scenes):
     for ih, (g, m, x, comp) in sd.instances.items():
         rt.set_instance(ih, g, m, x, comp)
     rt.build_ias(63)
-    assert rt.commit_stats() == {"full": 1, "materials": 0, "skipped": 1, "uploads_skipped": len(sd.geometries)}
+    assert rt.commit_stats() == {"full": 1, "materials": 0, "skipped": 1, "uploads_skipped": len(sd.geometries), "refits": 0}
     # albedo change: tables only, and the new albedo is what the shading sees
     env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=2, samples=8)
     before = rt.estimate_illumination_mesh(env, rp, seed=3, tri_begin=0, tri_end=500)
@@ -162,3 +162,63 @@ def test_scene_sync_diffing(rt, orc, S, scenes):
         rt.set_geometry(gh, v, t, version=8)
     rt.build_ias(63)
     assert rt.commit_stats()["full"] == 4
+
+
+def test_refit_path(rt, orc, S, scenes):
+    """Option "refit": moved instances / vertices with unchanged topology reuse the sorted order and the radix tree of the
+    last full build.  Hits, LiDAR and irradiance equal a fresh oracle build of the moved scene (they do not depend on
+    the tree); a topology change falls back to the full build."""
+    rt.set_option("refit", 1)
+    sd = scenes.sorghum_scene(2)
+    rt.load_scene(sd, 63)
+    assert rt.commit_stats()["full"] == 1
+    lo, hi = scenes.scene_bounds(sd)
+    rays = scenes.incoherent_rays(1 << 15, lo - 0.3, hi + 0.3, seed=12)
+
+    def check(tag):
+        osc = orc.OracleScene(sd, 63)
+        assert_bit_equal(rt.trace_closest(rays).view(np.uint32), osc.trace(rays).view(np.uint32), f"hits ({tag})")
+        env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=3, samples=8)
+        gpu = rt.estimate_illumination_mesh(env, rp, seed=5, push=1e-3, tri_begin=0, tri_end=2000)
+        cpu, st = osc.illum_mesh(env, rp, seed=5, push=1e-3, tri_begin=0, tri_end=2000)
+        assert np.allclose(gpu[:, :3], cpu[:, :3], rtol=1e-5, atol=0), tag
+        assert rt.last_job_stats() == (st.rays, st.paths), tag
+
+    # 1. an instance is moved, turned and scaled (the planned slab counts of its triangles would differ now)
+    ih = max(sd.instances)
+    g, m, x, comp = sd.instances[ih]
+    c, s_ = np.cos(0.9), np.sin(0.9)
+    x2 = np.array([[1.3 * c, 0, 1.3 * s_, 0.4], [0, 1.3, 0, 0.05], [-1.3 * s_, 0, 1.3 * c, -0.3], [0, 0, 0, 1]], dtype=np.float32)
+    sd.instances[ih] = (g, m, np.ascontiguousarray(x2.T).reshape(16), comp)
+    rt.set_instance(ih, *sd.instances[ih])
+    rt.build_ias(63)
+    st = rt.commit_stats()
+    assert (st["full"], st["refits"]) == (1, 1)
+    check("moved instance")
+    # 2. vertex animation: same triangle count, new positions
+    gh = sd.instances[ih][0]
+    v, t = sd.geometries[gh]
+    v = v.copy()
+    v["position"][:, 0] += (0.05 * np.sin(7.0 * v["position"][:, 1])).astype(np.float32)
+    sd.geometries[gh] = (v, t)
+    rt.set_geometry(gh, v, t, version=2)
+    rt.build_ias(63)
+    st = rt.commit_stats()
+    assert (st["full"], st["refits"]) == (1, 2)
+    check("moved vertices")
+    # 3. refit off -> full build of the same scene gives the oracle's nodes again
+    rt.set_option("refit", 0)
+    rt.set_instance(ih, g, m, x, comp)
+    sd.instances[ih] = (g, m, x, comp)
+    rt.build_ias(63)
+    assert rt.commit_stats()["full"] == 2
+    osc = orc.OracleScene(sd, 63)
+    assert np.array_equal(rt.debug(S.DBG_WIDE_NODES).view(np.uint8), osc.debug(S.DBG_WIDE_NODES).view(np.uint8))
+    # 4. topology change with refit on -> full build
+    rt.set_option("refit", 1)
+    sd.instances[ih + 1] = (g, m, scenes.IDENTITY.copy(), 4711)
+    rt.set_instance(ih + 1, *sd.instances[ih + 1])
+    rt.build_ias(63)
+    st = rt.commit_stats()
+    assert (st["full"], st["refits"]) == (3, 2)
+    check("added instance")
