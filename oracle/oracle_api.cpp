@@ -375,6 +375,15 @@ ORC_API void orc_btf_eval(Scene* s, int btf, uint64_t n, const float* tc, const 
     }
   });
 }
+// BTFBase::GetValueDeg layer: q6 = {u, v, illumTheta, illumPhi, viewTheta, viewPhi} (degrees)
+ORC_API void orc_btf_value_deg(Scene* s, int btf, uint64_t n, const float* q6, float* rgb) {
+  const BTF& b = s->btfs[btf];
+  for (uint64_t i = 0; i < n; i++) {
+    const float* q = q6 + 6 * i;
+    V3 c = btf_value_deg(b, q[0], q[1], q[2], q[3], q[4], q[5]);
+    rgb[3 * i] = c.x, rgb[3 * i + 1] = c.y, rgb[3 * i + 2] = c.z;
+  }
+}
 ORC_API void orc_btf_beta_angles(Scene* s, int btf, float* out) {
   const BTF& b = s->btfs[btf];
   for (size_t i = 0; i < b.beta_angles.size(); i++) out[i] = b.beta_angles[i];

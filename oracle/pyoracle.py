@@ -176,6 +176,13 @@ class OracleScene:
                            _p(out), int(nthreads))
         return out
 
+    def btf_value_deg(self, btf, q6):
+        """BTFBase::GetValueDeg layer: rows {u, v, illumTheta, illumPhi, viewTheta, viewPhi} in degrees -> rgb."""
+        q = np.ascontiguousarray(q6, dtype=np.float32).reshape(-1, 6)
+        out = np.empty((len(q), 3), dtype=np.float32)
+        lib().orc_btf_value_deg(self.h, self.btf_index[btf], C.c_uint64(len(q)), _p(q), _p(out))
+        return out
+
     def btf_beta_angles(self, btf, n):
         out = np.empty(n, dtype=np.float32)
         lib().orc_btf_beta_angles(self.h, self.btf_index[btf], _p(out))
@@ -303,6 +310,27 @@ def bake_skinned(skinned_vertices, bone_matrices):
 def flux_probes(probes):
     out = np.zeros(8, dtype=np.float32)
     lib().orc_flux_probes(_p(probes), C.c_uint64(len(probes)), _p(out))
+    return out
+
+
+def ref_btf_lib():
+    """oracle/_ref/libbtf_ref.so = the reference's own MLVQ headers compiled on the host (make -C oracle ref; exists only
+    where /root/reference does).  None when absent."""
+    so = os.path.join(_HERE, "_ref", "libbtf_ref.so")
+    return C.CDLL(so) if os.path.exists(so) else None
+
+
+def ref_btf_value_deg(tables, beta_angles, q6):
+    """The REFERENCE's BTFBase::GetValueDeg on a structs.BTFTables set."""
+    L = ref_btf_lib()
+    if L is None:
+        raise FileNotFoundError("oracle/_ref/libbtf_ref.so (make -C oracle ref)")
+    q = np.ascontiguousarray(q6, dtype=np.float32).reshape(-1, 6)
+    ba = np.ascontiguousarray(beta_angles, dtype=np.float32)
+    d = tables.desc()
+    out = np.empty((len(q), 3), dtype=np.float32)
+    rc = L.ref_btf_value_deg(C.byref(d), _p(ba), C.c_uint64(len(q)), _p(q), _p(out))
+    assert rc == 0
     return out
 
 

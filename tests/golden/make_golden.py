@@ -7,6 +7,8 @@
 * oracle_small.npz — outputs of the CPU oracle on small seeded inputs (hits, visit counts, Morton codes,
                    irradiance, LiDAR, camera).  The reference has no tests/fixtures for these, so this
                    file guards the oracle against drift and gives the GPU tests stored vectors to hit as well.
+* btf_ref.npz    — outputs of the REFERENCE's own compressed-BTF evaluator (include/RayTracerFacility/MLVQ/*.cuh compiled
+                   unmodified into oracle/_ref/libbtf_ref.so against oracle/ref_stubs).  Pins orc::btf_value_deg.
 * oracle_extra.npz — the same for the BSSRDF probe / irradiance, the instanced and skinned pre-kernels, light probes, flux.
 """
 import ctypes as C
@@ -74,6 +76,24 @@ def extra_cases():
                 env=S.EnvironmentProperties(color=(0.9, 1.0, 0.8)), rp=S.RayProperties(bounces=3, samples=16))
 
 
+BTF_REF_VARIANTS = [dict(), dict(use_cos_beta=0), dict(hdr=1, hdr_value=2.5, multiplier=2.5), dict(code_btf_flag=1),
+                    dict(gamma=1.0, tex_coord_multiplier=2.5, rows_offset=3, cols_offset=7)]
+
+
+def btf_ref_cases():
+    """Seeded inputs of btf_ref.npz: small synthetic MLVQ databases (one per parameter variant) and GetValueDeg queries
+    {u, v, illumTheta, illumPhi, viewTheta, viewPhi}; the first half stays below 80 degrees, the second half covers the
+    whole range including theta > 90 (black) and grazing angles."""
+    n = 4096
+    idx = np.arange(n)
+    h = lambda d: scenes.hash_uniform(31, idx, d)  # noqa: E731
+    tmax = np.where(idx < n // 2, 80.0, 95.0)
+    q = np.stack([h(0) * 3 - 1, h(1) * 3 - 1, h(2) * tmax, h(3) * 360, h(4) * tmax, h(5) * 360], 1).astype(np.float32)
+    small = dict(seed=6, texels=(32, 32), n_pdf1d=256, n_colors=64, n_index=128, n_pdf2d_color=64, n_pdf2d_lum=128,
+                 n_pdf2d=256, n_pdf3d=128, n_pdf4d=64)
+    return [scenes.synthetic_btf(**small, **kw) for kw in BTF_REF_VARIANTS], q
+
+
 def camera_props(width=16, height=12):
     """CameraProperties::Set (RayTracer.cu:28-46) for position (0.5,0.5,3), identity rotation, fov 120 (60 effective)."""
     import math
@@ -133,7 +153,20 @@ def main():
                         lidar_t=t.view(np.uint32), lidar_prim=prim, camera_color=col.view(np.uint32),
                         camera_normal=nrm.view(np.uint32), camera_albedo=alb.view(np.uint32))
     write_extra()
+    write_btf_ref()
     print("wrote", os.listdir(HERE))
+
+
+def write_btf_ref():
+    """btf_ref.npz — outputs of the REFERENCE's own compressed-BTF evaluator (MLVQ/*.cuh compiled unmodified into
+    oracle/_ref/libbtf_ref.so, `make -C oracle ref`) for the queries of btf_ref_cases()."""
+    btfs, q = btf_ref_cases()
+    out = {}
+    for k, btf in enumerate(btfs):
+        osc = orc.OracleScene(scenes.materials_scene(btf=btf))
+        beta = osc.btf_beta_angles(1, btf.desc().num_beta)
+        out[f"rgb{k}"] = orc.ref_btf_value_deg(btf, beta, q).view(np.uint32)
+    np.savez_compressed(os.path.join(HERE, "btf_ref.npz"), **out)
 
 
 def write_extra():
