@@ -57,6 +57,20 @@ ORC_API void orc_sample_lobe(float r0, float r1, const float* n, float alpha, fl
   V3 d = sample_lobe(r0, r1, v3(n[0], n[1], n[2]), alpha);
   out[0] = d.x, out[1] = d.y, out[2] = d.z;
 }
+ORC_API void orc_reflect(const float* i, const float* n, float* out) {
+  V3 d = reflect(v3(i[0], i[1], i[2]), v3(n[0], n[1], n[2]));
+  out[0] = d.x, out[1] = d.y, out[2] = d.z;
+}
+ORC_API void orc_tangent_space(const float* n, float* out9) {
+  V3 nn = v3(n[0], n[1], n[2]), t, b;
+  tangent_space(nn, t, b);
+  out9[0] = t.x, out9[1] = t.y, out9[2] = t.z, out9[3] = b.x, out9[4] = b.y, out9[5] = b.z;
+  out9[6] = nn.x, out9[7] = nn.y, out9[8] = nn.z;
+}
+ORC_API int orc_cube_map_lookup(const float* d, float* uv) { return cube_map_lookup(v3(d[0], d[1], d[2]), uv[0], uv[1]); }
+ORC_API int orc_ray_sphere(const float* o, const float* d, float radius, float* t01) {
+  return ray_sphere(v3(o[0], o[1], o[2]), v3(d[0], d[1], d[2]), radius, t01[0], t01[1]) ? 1 : 0;
+}
 ORC_API void orc_env_light(const rtf_env* env, const float* pos, const float* dir, float* out) {
   V3 c = env_light(v3(pos[0], pos[1], pos[2]), v3(dir[0], dir[1], dir[2]), *env);
   out[0] = c.x, out[1] = c.y, out[2] = c.z;

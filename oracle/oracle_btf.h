@@ -45,9 +45,9 @@ static inline void tex2d(const Texture& t, float u, float v, float out[4]) {
   for (int k = 0; k < 4; k++) out[k] = ((w00 * t00[k] + w10 * t10[k]) + w01 * t01[k]) + w11 * t11[k];
 }
 // SampleCubeMap, RTU.cuh:54-80.  faces: +X -X +Y -Y +Z -Z.
-static inline void sample_cube_map(const Texture* const faces[6], V3 d, float out[4]) {
+static inline int cube_map_lookup(V3 d, float& u, float& v) {
   const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
-  float ma, u, v;
+  float ma;
   int face;
   if (az >= ax && az >= ay) {
     face = d.z < 0.0f ? 5 : 4;
@@ -62,7 +62,13 @@ static inline void sample_cube_map(const Texture* const faces[6], V3 d, float ou
     ma = 0.5f / ax;
     u = d.x < 0.0f ? d.z : -d.z, v = -d.y;
   }
-  tex2d(*faces[face], u * ma + 0.5f, v * ma + 0.5f, out);
+  u = u * ma + 0.5f, v = v * ma + 0.5f;
+  return face;
+}
+static inline void sample_cube_map(const Texture* const faces[6], V3 d, float out[4]) {
+  float u, v;
+  const int face = cube_map_lookup(d, u, v);
+  tex2d(*faces[face], u, v, out);
 }
 
 // ---- compressed BTF ------------------------------------------------------------------------------------------------

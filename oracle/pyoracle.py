@@ -334,6 +334,99 @@ def ref_btf_value_deg(tables, beta_angles, q6):
     return out
 
 
+def ref_env_lib():
+    """oracle/_ref/libenv_ref.so = the reference's own RayTracerUtilities.cuh / Environment.cuh / BSDF.cuh compiled on the
+    host (make -C oracle ref; exists only where /root/reference does).  None when absent."""
+    so = os.path.join(_HERE, "_ref", "libenv_ref.so")
+    if not os.path.exists(so):
+        return None
+    L = C.CDLL(so)
+    L.ref_cie_sky.restype = C.c_float
+    return L
+
+
+def _f3(v):
+    return (C.c_float * 3)(*[float(x) for x in v])
+
+
+class RefEnv:
+    """The REFERENCE's helpers (ref_env_driver.cpp).  Samplers return (uniforms consumed, result)."""
+
+    def __init__(self):
+        self.L = ref_env_lib()
+        if self.L is None:
+            raise FileNotFoundError("oracle/_ref/libenv_ref.so (make -C oracle ref)")
+
+    def reflect(self, i, n):
+        out = (C.c_float * 3)()
+        self.L.ref_reflect(_f3(i), _f3(n), out)
+        return np.array(out[:], dtype=np.float32)
+
+    def tangent_space(self, n):
+        out = (C.c_float * 9)()
+        self.L.ref_tangent_space(_f3(n), out)
+        return np.array(out[:], dtype=np.float32).reshape(3, 3)
+
+    def sample_hemisphere(self, v0, v1, n):
+        r, out = (C.c_float * 2)(), (C.c_float * 3)()
+        self.L.ref_sample_hemisphere(C.c_uint(v0), C.c_uint(v1), _f3(n), r, out)
+        return np.array(r[:], dtype=np.float32), np.array(out[:], dtype=np.float32)
+
+    def sample_lobe(self, v0, v1, n, alpha):
+        r, out = (C.c_float * 2)(), (C.c_float * 3)()
+        self.L.ref_sample_lobe(C.c_uint(v0), C.c_uint(v1), _f3(n), C.c_float(alpha), r, out)
+        return np.array(r[:], dtype=np.float32), np.array(out[:], dtype=np.float32)
+
+    def brdf(self, metallic, v0, v1, in_dir, normal):
+        r, out = (C.c_float * 2)(), (C.c_float * 3)()
+        self.L.ref_brdf(C.c_float(metallic), C.c_uint(v0), C.c_uint(v1), _f3(in_dir), _f3(normal), r, out)
+        return np.array(r[:], dtype=np.float32), np.array(out[:], dtype=np.float32)
+
+    def cube_map_lookup(self, d):
+        face, uv = C.c_int(), (C.c_float * 2)()
+        self.L.ref_cube_map_lookup(_f3(d), C.byref(face), uv)
+        return face.value, np.array(uv[:], dtype=np.float32)
+
+    def ray_sphere(self, o, d, radius):
+        t = (C.c_float * 2)()
+        ok = self.L.ref_ray_sphere(_f3(o), _f3(d), C.c_float(radius), t)
+        return bool(ok), np.array(t[:], dtype=np.float32)
+
+    def nishita_sky(self, env, pos, d):
+        out = (C.c_float * 3)()
+        self.L.ref_nishita_sky(C.byref(env), _f3(pos), _f3(d), out)
+        return np.array(out[:], dtype=np.float32)
+
+    def env_light(self, env, pos, d):
+        out = (C.c_float * 3)()
+        self.L.ref_env_light(C.byref(env), _f3(pos), _f3(d), out)
+        return np.array(out[:], dtype=np.float32)
+
+
+def reflect(i, n):
+    out = (C.c_float * 3)()
+    lib().orc_reflect(_f3(i), _f3(n), out)
+    return np.array(out[:], dtype=np.float32)
+
+
+def tangent_space(n):
+    out = (C.c_float * 9)()
+    lib().orc_tangent_space(_f3(n), out)
+    return np.array(out[:], dtype=np.float32).reshape(3, 3)
+
+
+def cube_map_lookup(d):
+    uv = (C.c_float * 2)()
+    face = lib().orc_cube_map_lookup(_f3(d), uv)
+    return int(face), np.array(uv[:], dtype=np.float32)
+
+
+def ray_sphere(o, d, radius):
+    t = (C.c_float * 2)()
+    ok = lib().orc_ray_sphere(_f3(o), _f3(d), C.c_float(radius), t)
+    return bool(ok), np.array(t[:], dtype=np.float32)
+
+
 def rotate_about(v, u_turns, axis):
     out = (C.c_float * 3)()
     lib().orc_rotate_about((C.c_float * 3)(*v), C.c_float(u_turns), (C.c_float * 3)(*axis), out)

@@ -1,7 +1,8 @@
 // oracle/ref_stubs/glm/glm.hpp — TEST INFRASTRUCTURE ONLY.
 // A minimal stand-in for the parts of glm (absent from this image) that the reference's MLVQ headers use
 // (include/RayTracerFacility/MLVQ/*.cuh: vec2, vec3, clamp, isnan, sin, cos, asin, radians, degrees, mod, pow), written
-// from glm's documented semantics so that those headers compile UNMODIFIED on the host into oracle/_ref/libbtf_ref.so.
+// from glm's documented semantics so that those headers compile UNMODIFIED on the host into oracle/_ref/libbtf_ref.so
+// (and, with the additions at the end, RayTracer/{RayTracerUtilities,Environment,BSDF}.cuh into oracle/_ref/libenv_ref.so).
 // Not a copy of glm; scalar functions forward to <cmath> exactly as glm's do.
 #pragma once
 #include <cmath>
@@ -55,4 +56,71 @@ inline float pow(float a, float b) { return std::pow(a, b); }
 inline vec3 pow(const vec3& a, const vec3& b) { return vec3(std::pow(a.x, b.x), std::pow(a.y, b.y), std::pow(a.z, b.z)); }
 template <class T>
 inline T pi() { return T(3.14159265358979323846264338327950288); }
+
+// ---- additions for RayTracer/{RayTracer.hpp, RayTracerUtilities.cuh, Environment.cuh, BSDF.cuh} ------------------------
+// Operation order follows glm's scalar (non-SIMD) code paths: dot = (x*x' + y*y') + z*z'; cross, normalize = v *
+// inversesqrt(dot(v, v)) with inversesqrt(x) = 1 / sqrt(x); length = sqrt(dot(v, v)); mat3 * vec3 = columns scaled and
+// summed left to right; angle(x, y) = acos(clamp(dot(x, y), -1, 1)).
+typedef unsigned int uint;
+struct ivec2 {
+  int x, y;
+  ivec2() : x(0), y(0) {}
+  ivec2(int a, int b) : x(a), y(b) {}
+};
+struct uvec3 {
+  unsigned x, y, z;
+  uvec3() : x(0), y(0), z(0) {}
+  uvec3(unsigned a, unsigned b, unsigned c) : x(a), y(b), z(c) {}
+};
+struct vec4 {
+  float x, y, z, w;
+  vec4() : x(0), y(0), z(0), w(0) {}
+  vec4(float a, float b, float c, float d) : x(a), y(b), z(c), w(d) {}
+  explicit vec4(float a) : x(a), y(a), z(a), w(a) {}
+  vec4(const vec3& v, float d) : x(v.x), y(v.y), z(v.z), w(d) {}
+};
+struct quat {
+  float x, y, z, w;
+  quat() : x(0), y(0), z(0), w(1) {}
+};
+struct mat4 {
+  vec4 c[4];
+  mat4() {}
+  explicit mat4(float d) { c[0].x = d, c[1].y = d, c[2].z = d, c[3].w = d; }
+  vec4& operator[](int i) { return c[i]; }
+  const vec4& operator[](int i) const { return c[i]; }
+};
+struct mat3x3 {
+  vec3 c[3];
+  mat3x3() {}
+  mat3x3(const vec3& a, const vec3& b, const vec3& d) { c[0] = a, c[1] = b, c[2] = d; }
+  vec3& operator[](int i) { return c[i]; }
+  const vec3& operator[](int i) const { return c[i]; }
+};
+typedef mat3x3 mat3;
+inline bool operator==(const vec3& a, const vec3& b) { return a.x == b.x && a.y == b.y && a.z == b.z; }
+inline bool operator!=(const vec3& a, const vec3& b) { return !(a == b); }
+inline vec2 operator+(const vec2& a, const vec2& b) { return vec2(a.x + b.x, a.y + b.y); }
+inline vec3 operator*(const mat3x3& m, const vec3& v) {
+  return vec3(m[0].x * v.x + m[1].x * v.y + m[2].x * v.z, m[0].y * v.x + m[1].y * v.y + m[2].y * v.z,
+              m[0].z * v.x + m[1].z * v.y + m[2].z * v.z);
+}
+inline float sqrt(float v) { return std::sqrt(v); }
+inline float exp(float v) { return std::exp(v); }
+inline float abs(float v) { return std::fabs(v); }
+inline float max(float a, float b) { return a < b ? b : a; }
+inline float min(float a, float b) { return b < a ? b : a; }
+inline vec3 max(const vec3& a, const vec3& b) { return vec3(max(a.x, b.x), max(a.y, b.y), max(a.z, b.z)); }
+inline float dot(const vec3& a, const vec3& b) {
+  const vec3 t(a * b);
+  return t.x + t.y + t.z;
+}
+inline vec3 cross(const vec3& x, const vec3& y) {
+  return vec3(x.y * y.z - y.y * x.z, x.z * y.x - y.z * x.x, x.x * y.y - y.x * x.y);
+}
+inline float inversesqrt(float v) { return 1.0f / std::sqrt(v); }
+inline vec3 normalize(const vec3& v) { return v * inversesqrt(dot(v, v)); }
+inline float length(const vec3& v) { return std::sqrt(dot(v, v)); }
+inline float distance(const vec3& a, const vec3& b) { return length(b - a); }
+inline float angle(const vec3& x, const vec3& y) { return std::acos(clamp(dot(x, y), -1.0f, 1.0f)); }
 }  // namespace glm

@@ -7,6 +7,9 @@
 * oracle_small.npz — outputs of the CPU oracle on small seeded inputs (hits, visit counts, Morton codes,
                    irradiance, LiDAR, camera).  The reference has no tests/fixtures for these, so this
                    file guards the oracle against drift and gives the GPU tests stored vectors to hit as well.
+* env_ref.npz    — outputs of the REFERENCE's own sampling helpers, sky model and environment lookup (RayTracer/
+                   {RayTracerUtilities,Environment,BSDF}.cuh compiled unmodified into oracle/_ref/libenv_ref.so).  Pins
+                   orc::reflect / tangent_space / sample_hemisphere / sample_lobe / cube_map_lookup / nishita_sky / env_light.
 * btf_ref.npz    — outputs of the REFERENCE's own compressed-BTF evaluator (include/RayTracerFacility/MLVQ/*.cuh compiled
                    unmodified into oracle/_ref/libbtf_ref.so against oracle/ref_stubs).  Pins orc::btf_value_deg.
 * oracle_extra.npz — the same for the BSSRDF probe / irradiance, the instanced and skinned pre-kernels, light probes, flux.
@@ -94,6 +97,48 @@ def btf_ref_cases():
     return [scenes.synthetic_btf(**small, **kw) for kw in BTF_REF_VARIANTS], q
 
 
+def env_ref_cases():
+    """Seeded inputs of env_ref.npz.  `vec`: n unit normals (the first rows hit GetTangentSpace's |n.x| > 0.99 switch from
+    both sides), unit incident directions, unnormalised cube-map directions (with exact ties between the axes), LCG seeds
+    and lobe widths; `sky`: Skydome environments (sun, intensity, gamma, sample counts) with positions and directions;
+    `flat`: Scene / SingleLightSource environments."""
+    n = 1024
+    idx = np.arange(n)
+    h = lambda s, d: scenes.hash_uniform(s, idx, d).astype(np.float64)  # noqa: E731
+
+    def sphere(s):
+        z, ph = 2 * h(s, 0) - 1, 2 * np.pi * h(s, 1)
+        r = np.sqrt(1 - z * z)
+        return np.stack([r * np.cos(ph), r * np.sin(ph), z], 1).astype(np.float32)
+
+    normal, incident = sphere(41), sphere(42)
+    normal[:6] = [[1, 0, 0], [-1, 0, 0], [0.9900001, 0.14106695, 0], [0.99, 0.14106736, 0], [0, 1, 0], [0, 0, -1]]
+    cube = ((np.stack([h(43, 0), h(43, 1), h(43, 2)], 1) * 2 - 1) * 3).astype(np.float32)
+    cube[:8] = [[1, 1, 1], [-1, 1, 1], [1, -1, -1], [2, 2, 1], [2, 1, 2], [1, 2, 2], [-2, 0, 2], [0, -3, 0]]
+    seeds = np.stack([(h(44, 0) * 2 ** 31).astype(np.uint32), (h(44, 1) * 2 ** 31).astype(np.uint32)], 1)
+    alpha = h(45, 0).astype(np.float32)
+    alpha[:3] = [0.0, 1.0, 0.5]
+    vec = dict(normal=normal, incident=incident, cube=cube, seeds=seeds, alpha=alpha)
+
+    sun = sphere(46) * np.float32([1, 0.5, 1]) + np.float32([0, 0.6, 0])
+    sun /= np.linalg.norm(sun, axis=1, keepdims=True)
+    sun[0] = [0, 1, 0]
+    pos = np.stack([(h(47, 0) - 0.5) * 400, h(47, 1) * 120, (h(47, 2) - 0.5) * 400], 1).astype(np.float32)
+    sky = dict(sun=sun.astype(np.float32), dir=sphere(48), pos=pos, intensity=(0.5 + 2.5 * h(49, 0)).astype(np.float32),
+               gamma=np.float32([1.0, 2.2, 0.7])[idx % 3], small=(idx % 7 == 0))
+    flat = [dict(lighting_type=lt, color=(0.3, 0.9, 1.7), skylight_intensity=1.3, gamma=g)
+            for lt in (S.ENV_SCENE, S.ENV_SINGLE_LIGHT_SOURCE) for g in (1.0, 2.2)]
+    return vec, sky, flat
+
+
+def sky_env(sky, k):
+    env = S.EnvironmentProperties(lighting_type=S.ENV_SKYDOME, sun_direction=tuple(float(x) for x in sky["sun"][k]),
+                                  skylight_intensity=float(sky["intensity"][k]), gamma=float(sky["gamma"][k]))
+    if sky["small"][k]:
+        env.atmosphere.num_samples, env.atmosphere.num_samples_light = 8, 4
+    return env
+
+
 def camera_props(width=16, height=12):
     """CameraProperties::Set (RayTracer.cu:28-46) for position (0.5,0.5,3), identity rotation, fov 120 (60 effective)."""
     import math
@@ -154,7 +199,36 @@ def main():
                         camera_normal=nrm.view(np.uint32), camera_albedo=alb.view(np.uint32))
     write_extra()
     write_btf_ref()
+    write_env_ref()
     print("wrote", os.listdir(HERE))
+
+
+def write_env_ref():
+    """env_ref.npz — outputs of the REFERENCE's own helpers (oracle/ref_env_driver.cpp -> oracle/_ref/libenv_ref.so,
+    `make -C oracle ref`) for env_ref_cases().  Floats are stored as their bit patterns."""
+    R = orc.RefEnv()
+    vec, sky, flat = env_ref_cases()
+    n = len(vec["normal"])
+    u32 = lambda rows: np.asarray(rows, dtype=np.float32).view(np.uint32)  # noqa: E731
+    out = dict(reflect=u32([R.reflect(vec["incident"][k], vec["normal"][k]) for k in range(n)]),
+               tangent=u32([R.tangent_space(vec["normal"][k]).reshape(9) for k in range(n)]))
+    hemi = [R.sample_hemisphere(int(a), int(b), vec["normal"][k]) for k, (a, b) in enumerate(vec["seeds"])]
+    lobe = [R.sample_lobe(int(a), int(b), vec["normal"][k], float(vec["alpha"][k])) for k, (a, b) in enumerate(vec["seeds"])]
+    brdf = [R.brdf(float(vec["alpha"][k]), int(a), int(b), vec["incident"][k], vec["normal"][k])
+            for k, (a, b) in enumerate(vec["seeds"])]
+    out["uniforms"] = u32([r for r, _ in hemi])
+    assert all(np.array_equal(r, r2) and np.array_equal(r, r3) for (r, _), (r2, _), (r3, _) in zip(hemi, lobe, brdf))
+    out["hemisphere"], out["lobe"], out["brdf"] = (u32([d for _, d in x]) for x in (hemi, lobe, brdf))
+    cube = [R.cube_map_lookup(d) for d in vec["cube"]]
+    out["cube_face"] = np.array([f for f, _ in cube], dtype=np.int32)
+    out["cube_uv"] = u32([uv for _, uv in cube])
+    out["sky"] = u32([R.env_light(sky_env(sky, k), sky["pos"][k], sky["dir"][k]) for k in range(n)])
+    out["sky_raw"] = u32([R.nishita_sky(sky_env(sky, k), sky["pos"][k], sky["dir"][k]) for k in range(n)])
+    out["flat"] = u32([R.env_light(S.EnvironmentProperties(**kw), (0, 0, 0), (0, 1, 0)) for kw in flat])
+    # the inputs travel with the outputs (the tests read them from here, not from env_ref_cases())
+    out.update({f"in_{k}": v for k, v in vec.items()})
+    out.update({f"in_sky_{k}": v for k, v in sky.items()})
+    np.savez_compressed(os.path.join(HERE, "env_ref.npz"), **out)
 
 
 def write_btf_ref():

@@ -62,6 +62,33 @@ def test_cube_map_environment_bit_exact(rt, orc, scenes, S):
     assert_bit_equal(rt.sample_environment(env, pd), osc.sample_environment(env, pd), "constant sky")
 
 
+def test_skydome_environment_against_the_reference_code(rt, scenes, S):
+    """The device's environment lookup against tests/golden/env_ref.npz = outputs of the REFERENCE's own
+    CalculateEnvironmentalLight / NishitaSkyIncidentLight (Environment.cuh compiled on the host,
+    oracle/ref_env_driver.cpp) — no oracle in between.  The sky integrates 16 x 8 expf terms and ends in a powf:
+    CUDA's and glibc's differ by ulps, so 1e-5 relative (+1e-7 of the brightest channel for the dark ones); unlit
+    directions are exactly black in both; the Scene / SingleLightSource colours are bit-equal at gamma 1."""
+    import os
+    from .golden.make_golden import env_ref_cases, sky_env
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "env_ref.npz"))
+    sky = {n[len("in_sky_"):]: g[n] for n in g.files if n.startswith("in_sky_")}
+    ref = g["sky"].view(np.float32)
+    rt.load_scene(scenes.materials_scene())
+    n = len(ref)
+    got = np.concatenate([rt.sample_environment(sky_env(sky, k), np.concatenate([sky["pos"][k], sky["dir"][k]])[None])
+                          for k in range(n)])
+    assert np.array_equal(got == 0, ref == 0)
+    _close(got, ref, "skydome vs reference code", atol=1e-7 * float(ref.max()))
+    flat = env_ref_cases()[2]
+    got = np.concatenate([rt.sample_environment(S.EnvironmentProperties(**kw), np.float32([[0, 0, 0, 0, 1, 0]]))
+                          for kw in flat])
+    ref = g["flat"].view(np.float32)
+    for k, kw in enumerate(flat):
+        if kw["gamma"] == 1.0:
+            assert_bit_equal(got[k], ref[k], "flat environment")
+    _close(got, ref, "flat environment with gamma")
+
+
 @pytest.mark.parametrize("params", [dict(), dict(use_cos_beta=False), dict(code_btf_flag=1),
                                     dict(tex_coord_multiplier=2.5, rows_offset=3, cols_offset=7, gamma=1.0),
                                     dict(hdr=True, hdr_value=1.5, multiplier=1.5)])
