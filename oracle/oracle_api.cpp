@@ -202,6 +202,37 @@ ORC_API void orc_illum_mesh(Scene* s, const rtf_env* env, const rtf_ray_props* r
     for (auto& x : per) stats->rays += x.rays, stats->nodes += x.nodes, stats->tris += x.tris, stats->paths += x.paths;
   }
 }
+// orc_illum_probes with the REFERENCE's random stream: one LCG per probe seeded (probe index, seed) as __raygen__IE does
+// (IE.cu:47), drawn sequentially in the reference's order.  Test mode only (see t_seq_rng, oracle_math.h): compared with
+// the reference's own device programs run on the host (ref_ie_driver.cpp).  No BSSRDF materials (the repo's BSSRDF
+// reorders the two first-hit paths); single thread.
+ORC_API int orc_illum_probes_lcg(Scene* s, const rtf_env* env, const rtf_ray_props* rp, rtf_illum_sampler* probes, uint64_t n,
+                                 uint32_t seed, float push, uint64_t* rays_out) {
+  for (const rtf_material& m : s->mats)
+    if (m.subsurface_factor > 0.0f && m.subsurface_radius[0] > 0.0f) return -1;
+  uint64_t rays = 0;
+  for (uint64_t i = 0; i < n; i++) {
+    rtf_illum_sampler& pr = probes[i];
+    V3 P[3] = {v3(pr.a.position[0], pr.a.position[1], pr.a.position[2]), v3(pr.b.position[0], pr.b.position[1], pr.b.position[2]),
+               v3(pr.c.position[0], pr.c.position[1], pr.c.position[2])};
+    V3 N[3] = {v3(pr.a.normal[0], pr.a.normal[1], pr.a.normal[2]), v3(pr.b.normal[0], pr.b.normal[1], pr.b.normal[2]),
+               v3(pr.c.normal[0], pr.c.normal[1], pr.c.normal[2])};
+    LCG g;
+    g.init((uint32_t)i, seed);
+    t_seq_rng = &g;
+    float o6[6];
+    bool f = pr.front_face != 0, bk = pr.back_face != 0;
+    illum_probe(*s, *env, *rp, seed, push, i, P, N, f, bk, 0, rp->samples, o6, &rays, nullptr);
+    t_seq_rng = nullptr;
+    int faces = (f ? 1 : 0) + (bk ? 1 : 0);
+    if (faces * rp->samples != 0) {
+      illum_finalize(o6, faces, rp->samples);
+      for (int k = 0; k < 3; k++) pr.energy[k] = o6[k], pr.direction[k] = o6[3 + k];
+    }
+  }
+  if (rays_out) *rays_out = rays;
+  return 0;
+}
 // CudaModule::EstimateIlluminationRayTracing semantics over the 268 B AoS (CUDAModule.cpp:39-50).
 ORC_API void orc_illum_probes(Scene* s, const rtf_env* env, const rtf_ray_props* rp, rtf_illum_sampler* probes, uint64_t n,
                               uint32_t seed, float push, JobStats* stats, int nthreads) {
@@ -339,6 +370,28 @@ ORC_API void orc_camera(Scene* s, const rtf_env* env, const rtf_ray_props* rp, c
     *stats = JobStats{0, 0, 0, 0};
     for (auto& x : per) stats->rays += x.rays, stats->nodes += x.nodes, stats->tris += x.tris, stats->paths += x.paths;
   }
+}
+
+// orc_camera over the whole frame with the REFERENCE's random stream: one LCG per pixel seeded (ix + width * iy, frame id)
+// as __raygen__CR does (CR.cu:42-44), drawn sequentially.  Test mode only (see orc_illum_probes_lcg).  color is in-out.
+ORC_API int orc_camera_lcg(Scene* s, const rtf_env* env, const rtf_ray_props* rp, const rtf_camera_props* cam, float* color,
+                           float* normal, float* albedo, uint64_t* rays_out) {
+  for (const rtf_material& m : s->mats)
+    if (m.subsurface_factor > 0.0f && m.subsurface_radius[0] > 0.0f) return -1;
+  uint64_t rays = 0;
+  for (int iy = 0; iy < cam->height; iy++)
+    for (int ix = 0; ix < cam->width; ix++) {
+      const size_t k = (size_t)ix + (size_t)cam->width * (size_t)iy;
+      LCG g;
+      g.init((uint32_t)((float)ix + (float)cam->width * (float)iy), (uint32_t)cam->frame_id);
+      t_seq_rng = &g;
+      PixelOut po = camera_pixel(*s, *env, *rp, *cam, ix, iy, &rays, nullptr);
+      t_seq_rng = nullptr;
+      float prev[4] = {color[4 * k], color[4 * k + 1], color[4 * k + 2], color[4 * k + 3]};
+      camera_resolve(*cam, po, prev, color + 4 * k, normal + 4 * k, albedo + 4 * k);
+    }
+  if (rays_out) *rays_out = rays;
+  return 0;
 }
 
 // ---- textures, cube map, compressed BTF (oracle_btf.h) ----------------------------------------------------------

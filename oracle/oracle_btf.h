@@ -73,7 +73,7 @@ static inline void sample_cube_map(const Texture* const faces[6], V3 d, float ou
 
 // ---- compressed BTF ------------------------------------------------------------------------------------------------
 struct BTF {
-  rtf_btf_desc d;  // scalars; the pointers below point into the vectors
+  rtf_btf_desc d;  // scalars only: its pointers are the caller's and may dangle; the tables live in the vectors below
   std::vector<int32_t> pdf6_slices, index_ab, pdf2d_colors, pdf2d_slices, pdf2d_indices, pdf3d_slices, pdf4d_slices;
   std::vector<float> pdf6_scales, pdf1d_basis, colors, pdf2d_scales, pdf3d_scales, pdf4d_scales, beta_angles;
 };

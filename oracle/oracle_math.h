@@ -109,6 +109,20 @@ static inline void path_rng(uint32_t seed, uint32_t stream, uint64_t unit, uint3
   r[0] = u01(o[0]), r[1] = u01(o[1]), r[2] = u01(o[2]), r[3] = u01(o[3]);
 }
 
+// Sequential source, used by ONE test mode only (orc_illum_probes_lcg, pinning against the reference's own device
+// programs run on the host, ref_ie_driver.cpp): while set for the calling thread, path_draws() serves the next `n`
+// numbers of the reference's LCG in call order — the reference's per-thread stream (IE.cu:47) — instead of the keyed
+// Philox draws.  The product never draws this way.
+static thread_local LCG* t_seq_rng = nullptr;
+static inline void path_draws(uint32_t seed, uint32_t stream, uint64_t unit, uint32_t bounce, uint32_t extra, float r[4],
+                              int n) {
+  if (t_seq_rng) {
+    for (int k = 0; k < 4; k++) r[k] = k < n ? t_seq_rng->next() : 0.0f;
+    return;
+  }
+  path_rng(seed, stream, unit, bounce, extra, r);
+}
+
 // ---- portable sin/cos of 2*pi*u, u in [0,1]: only + * fma, identical on host and device -----
 // Stands in for glm::sin/glm::cos(2*pi*rnd) of RTU.cuh:127-131,139-143 and CR.cu:75-79; max abs
 // error ~1.2e-7, so results agree with libm to the last place or two while being reproducible.

@@ -94,7 +94,12 @@ static inline void tangent_space(V3 n, V3& t, V3& b) {  // RTU.cuh:110-120
 static inline V3 to_world(V3 n, float cos_theta, float r_phi) {
   float sin_theta = sqrtf(fmaxf(0.0f, 1.0f - cos_theta * cos_theta));
   float s, c;
-  sincos2pi(r_phi, &s, &c);
+  if (t_seq_rng) {  // test mode (oracle_math.h): the reference's own libm calls, glm::cos / glm::sin(2 pi u), RTU.cuh:127-131
+    const float phi = 2.0f * 3.14159265358979323846264338327950288f * r_phi;
+    c = cosf(phi), s = sinf(phi);
+  } else {
+    sincos2pi(r_phi, &s, &c);
+  }
   V3 l = v3(c * sin_theta, s * sin_theta, cos_theta);
   V3 t, b;
   tangent_space(n, t, b);
@@ -355,11 +360,11 @@ struct AlphaFilter {
       float t[4];
       tex2d(sc->textures[at], a.u, a.v, t);
       alpha = t[3];
-    } else if (alpha >= 1.0f) {
-      return true;
+    } else if (alpha >= 1.0f && !t_seq_rng) {
+      return true;  // 1 <= rnd never holds; the reference still draws (RF.cuh:19), which only a sequential source sees
     }
     float r[4];
-    path_rng(seed, STREAM_ALPHA, unit, bounce, tri.prim, r);
+    path_draws(seed, STREAM_ALPHA, unit, bounce, tri.prim, r, 1);
     return !(alpha <= r[0]);
   }
 };
@@ -389,7 +394,7 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
   // returned and starts from the hit count the subsurface path ended with.
   struct {
     bool on = false;
-    V3 o, d, T;
+    V3 o = v3(0, 0, 0), d = v3(0, 0, 0), T = v3(0, 0, 0);
   } pend;
   auto resume = [&]() -> bool {
     if (!pend.on) return false;
@@ -431,7 +436,7 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
       V3 btf_color = v3(0, 0, 0);  // the reference leaves it uninitialised past the bounce limit: 0 here
       bool go_on = false;
       if ((int)hit_count <= bounces) {
-        path_rng(seed, STREAM_PATH, unit, hit_count, 0, r);
+        path_draws(seed, STREAM_PATH, unit, hit_count, 0, r, 2);
         if (env.lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE) {  // RF.cuh:180-218
           V3 sun = v3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
           V3 nd = sample_lobe(r[0], r[1], sun, 1.0f - env.light_size);
@@ -496,7 +501,7 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
     if (metallic >= 0.0f) f = (metallic + 2) / (metallic + 1);
     V3 emis = m.emission * albedo;
     if (env.lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE) {  // RF.cuh:61-92
-      path_rng(seed, STREAM_PATH, unit, hit_count, 0, r);
+      path_draws(seed, STREAM_PATH, unit, hit_count, 0, r, 2);
       V3 sun = v3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
       V3 nd = sample_lobe(r[0], r[1], sun, 1.0f - env.light_size);
       V3 col = v3(env.color[0], env.color[1], env.color[2]);
@@ -554,7 +559,7 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
           }
         }
       }
-      path_rng(seed, STREAM_PATH, unit, hit_count, 0, r);
+      path_draws(seed, STREAM_PATH, unit, hit_count, 0, r, sc.brdf == RTF_BRDF_LAMBERT_GGX ? 3 : 2);
       V3 nd, wgt;
       bool absorbed = false;
       if (sc.brdf == RTF_BRDF_LAMBERT_GGX) {
@@ -620,7 +625,7 @@ static inline void illum_probe(const Scene& sc, const rtf_env& env, const rtf_ra
     for (int s = s0; s < s1; s++) {
       uint64_t unit = (probe_id * 2 + (uint64_t)face) * (uint64_t)rp.samples + (uint64_t)s;
       float r[4];
-      path_rng(seed, STREAM_PATH, unit, 0, 0, r);
+      path_draws(seed, STREAM_PATH, unit, 0, 0, r, 4);
       float a = r[0], b = r[1];
       float w = (1.0f - a) - b;
       V3 position = (w * P[0] + a * P[1]) + b * P[2];
@@ -667,7 +672,14 @@ static inline PixelOut camera_pixel(const Scene& sc, const rtf_env& env, const r
   for (int s = 0; s < rp.samples; s++) {
     uint64_t unit = pixel * (uint64_t)rp.samples + (uint64_t)s;
     float r[4];
-    path_rng(seed, STREAM_CAMERA, unit, 0, 0, r);
+    if (t_seq_rng) {
+      // test mode (oracle_math.h): CR.cu:60-61 draws both jitters inside one constructor call, glm::vec2(f(rnd()), f(rnd())),
+      // whose argument order the language leaves open; g++, which compiles the reference's program for the host run
+      // (ref_optix_driver.cpp), evaluates the second argument first.  Then the aperture angle (CR.cu:75).
+      r[1] = t_seq_rng->next(), r[0] = t_seq_rng->next(), r[2] = t_seq_rng->next(), r[3] = 0.0f;
+    } else {
+      path_rng(seed, STREAM_CAMERA, unit, 0, 0, r);
+    }
     float sx = (((float)ix + r[0]) - halfX) / halfX;
     float sy = (((float)iy + r[1]) - halfY) / halfY;
     float st[4], en[4];
@@ -680,7 +692,12 @@ static inline PixelOut camera_pixel(const Scene& sc, const rtf_env& env, const r
     V3 pdir = normalize(end - start);
     V3 conv = start + pdir * cam.focal_length;
     float sn, cs;
-    sincos2pi(r[2], &sn, &cs);
+    if (t_seq_rng) {  // test mode (oracle_math.h): the reference's own libm calls, CR.cu:75-79
+      const float angle = r[2] * 3.1415927f * 2.0f;
+      sn = sinf(angle), cs = cosf(angle);
+    } else {
+      sincos2pi(r[2], &sn, &cs);
+    }
     V3 ap = start + cam.aperture * (hor * sn + ver * cs);
     V3 dir = normalize(conv - ap);
     PathResult pr = trace_path(sc, env, rp.bounces, seed, unit, ap, dir, 0.0f, stats);

@@ -253,6 +253,29 @@ class OracleScene:
                                C.c_uint32(seed), C.c_float(push), C.byref(st), nthreads)
         return st
 
+    def illum_probes_lcg(self, env, rp, probes, seed, push):
+        """illum_probes() drawing from the reference's LCG in the reference's order (test mode, oracle_math.h
+        t_seq_rng).  Returns the number of rays traced."""
+        assert probes.dtype == S.ILLUM_SAMPLER_DTYPE and probes.flags.c_contiguous
+        rays = C.c_uint64()
+        rc = lib().orc_illum_probes_lcg(self.h, C.byref(env), C.byref(rp), _p(probes), C.c_uint64(len(probes)),
+                                        C.c_uint32(seed), C.c_float(push), C.byref(rays))
+        assert rc == 0, "BSSRDF materials are not supported in this mode"
+        return rays.value
+
+    def ref_illum_probes(self, env, rp, probes, seed, push):
+        """The REFERENCE's own __raygen__IE / closest-hit / any-hit / miss programs run on the host over this scene
+        (oracle/ref_ie_driver.cpp -> oracle/_ref/libie_ref.so).  Returns the number of rays traced."""
+        L = ref_ie_lib()
+        if L is None:
+            raise FileNotFoundError("oracle/_ref/libie_ref.so (make -C oracle ref)")
+        assert probes.dtype == S.ILLUM_SAMPLER_DTYPE and probes.flags.c_contiguous
+        rays = C.c_uint64()
+        rc = L.ref_ie_run(self.h, C.byref(env), C.byref(rp), _p(probes), C.c_uint64(len(probes)),
+                          C.c_uint32(seed), C.c_float(push), C.byref(rays))
+        assert rc == 0, "scene holds materials the host run of the reference does not set up"
+        return rays.value
+
     def scan_point_cloud(self, samples, nthreads=0):
         assert samples.dtype == S.PC_SAMPLE_DTYPE and samples.flags.c_contiguous
         prim = np.empty(len(samples), dtype=np.uint32)
@@ -271,6 +294,39 @@ class OracleScene:
                             _p(t), _p(prim), _p(inst), C.byref(st), nthreads)
         return t, prim, inst, st
 
+    def camera_lcg(self, env, rp, cam, prev_color=None):
+        """camera() over the whole frame drawing from the reference's LCG in the reference's order (test mode)."""
+        n = cam.width * cam.height
+        color = np.zeros((n, 4), dtype=np.float32) if prev_color is None else np.array(prev_color, dtype=np.float32).reshape(n, 4)
+        normal, albedo = np.empty((n, 4), dtype=np.float32), np.empty((n, 4), dtype=np.float32)
+        rays = C.c_uint64()
+        rc = lib().orc_camera_lcg(self.h, C.byref(env), C.byref(rp), C.byref(cam), _p(color), _p(normal), _p(albedo),
+                                  C.byref(rays))
+        assert rc == 0
+        return color, normal, albedo, rays.value
+
+    def ref_camera(self, env, rp, cam, prev_color=None):
+        """The REFERENCE's own __raygen__CR / closest-hit / any-hit / miss programs run on the host over this scene."""
+        L = ref_cr_lib()
+        if L is None:
+            raise FileNotFoundError("oracle/_ref/libcr_ref.so (make -C oracle ref)")
+        n = cam.width * cam.height
+        color = np.zeros((n, 4), dtype=np.float32) if prev_color is None else np.array(prev_color, dtype=np.float32).reshape(n, 4)
+        normal, albedo = np.empty((n, 4), dtype=np.float32), np.empty((n, 4), dtype=np.float32)
+        rays = C.c_uint64()
+        rc = L.ref_cr_run(self.h, C.byref(env), C.byref(rp), C.byref(cam), _p(color), _p(normal), _p(albedo), C.byref(rays))
+        assert rc == 0
+        return color, normal, albedo, rays.value
+
+    def ref_scan_point_cloud(self, samples):
+        """The REFERENCE's own __raygen__PCS / closest-hit / miss programs run on the host over this scene (in place)."""
+        L = ref_pcs_lib()
+        if L is None:
+            raise FileNotFoundError("oracle/_ref/libpcs_ref.so (make -C oracle ref)")
+        assert samples.dtype == S.PC_SAMPLE_DTYPE and samples.flags.c_contiguous
+        rc = L.ref_pcs_run(self.h, _p(samples), C.c_uint64(len(samples)))
+        assert rc == 0
+
     def camera(self, env, rp, cam, pixel_begin=0, pixel_end=None, stride=1, prev_color=None, nthreads=0):
         pixel_end = cam.width * cam.height if pixel_end is None else pixel_end
         cnt = max(0, (pixel_end - pixel_begin + stride - 1) // stride)
@@ -282,6 +338,21 @@ class OracleScene:
                          C.c_uint64(pixel_end), C.c_uint64(stride), _p(prev_color), _p(color), _p(normal), _p(albedo),
                          C.byref(st), nthreads)
         return color, normal, albedo, st
+
+
+def _ref_lib(name):
+    so = os.path.join(_HERE, "_ref", name)
+    return C.CDLL(so) if os.path.exists(so) else None
+
+
+def ref_pcs_lib():
+    """oracle/_ref/libpcs_ref.so: the reference's PointCloudScanning.cu programs on the host (see ref_ie_lib)."""
+    return _ref_lib("libpcs_ref.so")
+
+
+def ref_cr_lib():
+    """oracle/_ref/libcr_ref.so: the reference's CameraRendering.cu programs on the host (see ref_ie_lib)."""
+    return _ref_lib("libcr_ref.so")
 
 
 def bake_instanced(vertices, triangles, matrices, colors=None):
@@ -332,6 +403,13 @@ def ref_btf_value_deg(tables, beta_angles, q6):
     rc = L.ref_btf_value_deg(C.byref(d), _p(ba), C.c_uint64(len(q)), _p(q), _p(out))
     assert rc == 0
     return out
+
+
+def ref_ie_lib():
+    """oracle/_ref/libie_ref.so = the reference's own illumination-estimation device programs compiled on the host over
+    an emulation of the OptiX intrinsics (make -C oracle ref; exists only where /root/reference does).  None when absent."""
+    so = os.path.join(_HERE, "_ref", "libie_ref.so")
+    return C.CDLL(so) if os.path.exists(so) else None
 
 
 def ref_env_lib():

@@ -20,9 +20,11 @@ struct vec2 {
 inline vec2 operator*(const vec2& a, float s) { return vec2(a.x * s, a.y * s); }
 inline vec2 operator*(float s, const vec2& a) { return vec2(a.x * s, a.y * s); }
 
+struct vec4;
 struct vec3 {
   float x, y, z;
   vec3() : x(0), y(0), z(0) {}
+  vec3(const vec4& v);  // glm's vec<3>(vec<4>) is implicit unless GLM_FORCE_EXPLICIT_CTOR
   vec3(float a, float b, float c) : x(a), y(b), z(c) {}
   explicit vec3(float a) : x(a), y(a), z(a) {}
   vec3(int a, int b, int c) : x((float)a), y((float)b), z((float)c) {}
@@ -78,7 +80,17 @@ struct vec4 {
   vec4(float a, float b, float c, float d) : x(a), y(b), z(c), w(d) {}
   explicit vec4(float a) : x(a), y(a), z(a), w(a) {}
   vec4(const vec3& v, float d) : x(v.x), y(v.y), z(v.z), w(d) {}
+  float& operator[](int i) { return (&x)[i]; }
+  const float& operator[](int i) const { return (&x)[i]; }
+  vec4& operator/=(float s) { x /= s, y /= s, z /= s, w /= s; return *this; }
 };
+inline vec3::vec3(const vec4& v) : x(v.x), y(v.y), z(v.z) {}
+inline vec4 operator+(const vec4& a, const vec4& b) { return vec4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+inline vec4 operator-(const vec4& a, const vec4& b) { return vec4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w); }
+inline vec4 operator*(const vec4& a, const vec4& b) { return vec4(a.x * b.x, a.y * b.y, a.z * b.z, a.w * b.w); }
+inline vec4 operator*(const vec4& a, float s) { return vec4(a.x * s, a.y * s, a.z * s, a.w * s); }
+inline vec4 operator*(float s, const vec4& a) { return vec4(s * a.x, s * a.y, s * a.z, s * a.w); }
+inline vec4 operator/(const vec4& a, float s) { return vec4(a.x / s, a.y / s, a.z / s, a.w / s); }
 struct quat {
   float x, y, z, w;
   quat() : x(0), y(0), z(0), w(1) {}
@@ -98,6 +110,8 @@ struct mat3x3 {
   const vec3& operator[](int i) const { return c[i]; }
 };
 typedef mat3x3 mat3;
+// mat4 * vec4, glm/detail/type_mat4x4.inl: (m[0] * x + m[1] * y) + (m[2] * z + m[3] * w)
+inline vec4 operator*(const mat4& m, const vec4& v) { return (m[0] * v.x + m[1] * v.y) + (m[2] * v.z + m[3] * v.w); }
 inline bool operator==(const vec3& a, const vec3& b) { return a.x == b.x && a.y == b.y && a.z == b.z; }
 inline bool operator!=(const vec3& a, const vec3& b) { return !(a == b); }
 inline vec2 operator+(const vec2& a, const vec2& b) { return vec2(a.x + b.x, a.y + b.y); }
@@ -123,4 +137,17 @@ inline vec3 normalize(const vec3& v) { return v * inversesqrt(dot(v, v)); }
 inline float length(const vec3& v) { return std::sqrt(dot(v, v)); }
 inline float distance(const vec3& a, const vec3& b) { return length(b - a); }
 inline float angle(const vec3& x, const vec3& y) { return std::acos(clamp(dot(x, y), -1.0f, 1.0f)); }
+inline int clamp(int v, int lo, int hi) { return v < lo ? lo : (hi < v ? hi : v); }
+// gtx/rotate_vector.hpp: rotate(v, angle, normal) = mat3(rotate(mat4(1), angle, normal)) * v, with the rotation matrix
+// of gtc/matrix_transform (c + t_i * a_i on the diagonal, t_i * a_j +- s * a_k off it, t = (1 - c) * axis).
+inline vec3 rotate(const vec3& v, float angle, const vec3& normal) {
+  const float c = std::cos(angle), s = std::sin(angle);
+  const vec3 a(normalize(normal));
+  const vec3 t((1.0f - c) * a);
+  mat3x3 r;
+  r[0] = vec3(c + t.x * a.x, t.x * a.y + s * a.z, t.x * a.z - s * a.y);
+  r[1] = vec3(t.y * a.x - s * a.z, c + t.y * a.y, t.y * a.z + s * a.x);
+  r[2] = vec3(t.z * a.x + s * a.y, t.z * a.y - s * a.x, c + t.z * a.z);
+  return r * v;
+}
 }  // namespace glm

@@ -10,6 +10,11 @@
 * env_ref.npz    — outputs of the REFERENCE's own sampling helpers, sky model and environment lookup (RayTracer/
                    {RayTracerUtilities,Environment,BSDF}.cuh compiled unmodified into oracle/_ref/libenv_ref.so).  Pins
                    orc::reflect / tangent_space / sample_hemisphere / sample_lobe / cube_map_lookup / nishita_sky / env_light.
+* programs_ref.npz — outputs of the REFERENCE's own device programs of the three entry points (ptx/{IlluminationEstimation,
+                   PointCloudScanning,CameraRendering}.cu + RayFunctions.cuh + RayDataDefinations.hpp, compiled unmodified over a
+                   host emulation of the OptiX intrinsics: oracle/ref_optix_driver.cpp), tracing through the oracle's BVH
+                   and drawing from the reference's own LCG.  Pins orc::illum_probe / trace_path / camera_pixel /
+                   camera_resolve / full_hit_info (run with the same LCG stream: orc_*_lcg).
 * btf_ref.npz    — outputs of the REFERENCE's own compressed-BTF evaluator (include/RayTracerFacility/MLVQ/*.cuh compiled
                    unmodified into oracle/_ref/libbtf_ref.so against oracle/ref_stubs).  Pins orc::btf_value_deg.
 * oracle_extra.npz — the same for the BSSRDF probe / irradiance, the instanced and skinned pre-kernels, light probes, flux.
@@ -139,6 +144,54 @@ def sky_env(sky, k):
     return env
 
 
+def programs_ref_scenes():
+    """Scenes of programs_ref.npz: `plants` (Default materials, every instance under its own transform), `mixed`
+    (materials_scene without the BTF quad: textures, normal / metallic / roughness maps, vertex colours, alpha-textured
+    canopy, emission, a transmissive material, cube map; identity transforms) and `btf` (materials_scene as it is)."""
+    mixed = scenes.materials_scene()
+    mixed.materials[3] = scenes.Material(albedo=(0.5, 0.4, 0.9), metallic=0.6, roughness=0.3, transmission=0.4)
+    del mixed.material_btf[3]
+    return dict(plants=scenes.sorghum_scene(n_plants=2, seed=2), mixed=mixed, btf=scenes.materials_scene())
+
+
+PROGRAMS_ENVS = dict(
+    scene=dict(),
+    skydome=dict(lighting_type=S.ENV_SKYDOME, sun_direction=(0.3, 0.8, 0.52)),
+    sun=dict(lighting_type=S.ENV_SINGLE_LIGHT_SOURCE, sun_direction=(0.3, 0.8, 0.52), light_size=0.1, color=(1.0, 0.9, 0.7)),
+    cube=dict(environmental_map_id=3, skylight_intensity=1.7, gamma=2.2))
+# (scene, environment, bounces, samples) of the illumination-estimation cases; seed 7, push 1e-3, first 400 probes
+PROGRAMS_IE = [(sc, e, b, n) for sc, envs in (("plants", ("scene", "skydome", "sun")), ("mixed", ("scene", "skydome", "sun", "cube")),
+                                               ("btf", ("scene", "sun"))) for e in envs for b, n in ((1, 1), (4, 8))]
+# (environment, bounces, samples, output type, accumulate) of the camera cases on `mixed`, 32 x 24, aperture 0.02
+PROGRAMS_CR = [("scene", 1, 1, S.OUT_COLOR, 0), ("scene", 3, 4, S.OUT_DEPTH, 0), ("skydome", 1, 1, S.OUT_COLOR, 0),
+               ("skydome", 3, 4, S.OUT_COLOR, 1), ("cube", 2, 2, S.OUT_COLOR, 0)]
+
+
+def programs_camera(accumulate):
+    cam = camera_props(32, 24)
+    cam.aperture, cam.focal_length = 0.02, 2.5
+    if accumulate:
+        cam.accumulate, cam.frame_id = 1, 3
+    return cam
+
+
+def programs_prev_color():
+    return scenes.hash_uniform(77, np.arange(32 * 24 * 4), 0).astype(np.float32).reshape(-1, 4)
+
+
+def programs_pc_samples(sd, n=2000):
+    lo, hi = scenes.scene_bounds(sd)
+    idx = np.arange(n)
+    h = lambda d: scenes.hash_uniform(55, idx, d)  # noqa: E731
+    o = np.stack([lo[k] - 0.2 + (hi[k] - lo[k] + 0.4) * h(k) for k in range(3)], 1)
+    t = np.stack([lo[k] + (hi[k] - lo[k]) * h(3 + k) for k in range(3)], 1)
+    d = t - o
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    smp = np.zeros(n, dtype=S.PC_SAMPLE_DTYPE)
+    smp["start"], smp["direction"] = o.astype(np.float32), d.astype(np.float32)
+    return smp
+
+
 def camera_props(width=16, height=12):
     """CameraProperties::Set (RayTracer.cu:28-46) for position (0.5,0.5,3), identity rotation, fov 120 (60 effective)."""
     import math
@@ -200,6 +253,7 @@ def main():
     write_extra()
     write_btf_ref()
     write_env_ref()
+    write_programs_ref()
     print("wrote", os.listdir(HERE))
 
 
@@ -229,6 +283,32 @@ def write_env_ref():
     out.update({f"in_{k}": v for k, v in vec.items()})
     out.update({f"in_sky_{k}": v for k, v in sky.items()})
     np.savez_compressed(os.path.join(HERE, "env_ref.npz"), **out)
+
+
+def write_programs_ref():
+    """programs_ref.npz — see the module docstring; needs oracle/_ref/lib{ie,pcs,cr}_ref.so (`make -C oracle ref`)."""
+    out = {}
+    oscs = {k: orc.OracleScene(sd) for k, sd in programs_ref_scenes().items()}
+    for sc, e, b, n in PROGRAMS_IE:
+        osc = oscs[sc]
+        pr = osc.make_probes(0, min(400, osc.n_tris))
+        rays = osc.ref_illum_probes(S.EnvironmentProperties(**PROGRAMS_ENVS[e]), S.RayProperties(b, n), pr, 7, 1e-3)
+        key = f"ie_{sc}_{e}_{b}_{n}"
+        out[key] = np.concatenate([pr["energy"], pr["direction"]], 1).view(np.uint32)
+        out[key + "_rays"] = np.array([rays])
+    for k, (e, b, n, ot, acc) in enumerate(PROGRAMS_CR):
+        cam = programs_camera(acc)
+        cam.output_type = ot
+        c, nm, al, rays = oscs["mixed"].ref_camera(S.EnvironmentProperties(**PROGRAMS_ENVS[e]), S.RayProperties(b, n), cam,
+                                                   programs_prev_color() if acc else None)
+        out[f"cr_{k}"] = np.concatenate([c, nm, al], 1).view(np.uint32)
+        out[f"cr_{k}_rays"] = np.array([rays])
+    for sc in ("plants", "mixed"):
+        smp = programs_pc_samples(programs_ref_scenes()[sc])
+        out[f"pcs_{sc}_in"] = smp.copy().view(np.uint8)
+        oscs[sc].ref_scan_point_cloud(smp)
+        out[f"pcs_{sc}"] = smp.view(np.uint8)
+    np.savez_compressed(os.path.join(HERE, "programs_ref.npz"), **out)
 
 
 def write_btf_ref():
