@@ -32,7 +32,7 @@ static void parallel_for(uint64_t n, int nthreads, F fn) {
   for (auto& x : th) x.join();
 }
 
-ORC_API const char* orc_version() { return "rtf-oracle 0.1 (parity unpinned by the reference: it has no tests; pinned by brute force + closed forms)"; }
+ORC_API const char* orc_version() { return "rtf-oracle 0.2 (shading, helpers, RNG, BTF pinned by the reference's own code compiled on the host; traversal unpinned by the reference: OptiX is closed, pinned by brute force)"; }
 ORC_API int orc_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
 
 // ---- primitives -----------------------------------------------------------------------------

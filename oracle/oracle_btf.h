@@ -9,9 +9,10 @@
 //   RayTracer/RayDataDefinations.hpp:286-354  SurfaceCompressedBTF::ComputeAngles / GetValue
 //   RayTracer/RayDataDefinations.hpp:240-284  SurfaceMaterial texture look-ups
 //   RayTracer/RayTracerUtilities.cuh:54-80    SampleCubeMap
-// PARITY PINNING: the reference ships no BTF database, no textures and no tests, so these functions are
-// pinned by closed forms in tests/ (constant tables -> constant colour, Hermite end points, texel centres, cube-map
-// face axes) — "parity unpinned" by reference vectors.
+// PARITY PINNING: btf_value_deg and everything below it are pinned by the reference's own MLVQ headers compiled on the
+// host (ref_btf_driver.cpp, tests/golden/btf_ref.npz); the cube-map addressing by RayTracerUtilities.cuh compiled on the
+// host (ref_env_driver.cpp, tests/golden/env_ref.npz).  Texture filtering has no reference source (it is hardware):
+// pinned by closed forms in tests/ (texel centres, wrap periodicity).
 // Departures: sin/cos/asin/acos/atan2 use the portable polynomials of oracle_math.h (reproducible on host and device);
 // texture filtering uses full float weights (tex2D keeps 8 fractional bits).
 #pragma once
