@@ -275,17 +275,25 @@ struct SurfaceHit {
   uint32_t inst;
 };
 static inline SurfaceHit surface_hit(const Scene& sc, const Hit& h, V3 ray_dir) {
+  // TriangularMesh::GetHitInfo interpolates the OBJECT-space vertices (RDD.hpp:127-149); SBT::GetHitInfo then transforms:
+  // normal = normalize(M * (n, 0)), faced against the ray, position = M * (p, 1) (RDD.hpp:375-380).
   SurfaceHit s;
-  const float* p = &sc.pos9[9 * (size_t)h.prim];
-  const float* n = &sc.nrm9[9 * (size_t)h.prim];
+  s.inst = sc.tri_inst[h.prim];
+  const Instance& in = sc.insts[s.inst];
+  const Geometry& g = sc.geoms[in.geom];
+  const uint32_t lt = h.prim - in.first_prim;
+  const rtf_vertex& vx = g.verts[g.tris[3 * lt]];
+  const rtf_vertex& vy = g.verts[g.tris[3 * lt + 1]];
+  const rtf_vertex& vz = g.verts[g.tris[3 * lt + 2]];
   float w0 = (1.0f - h.u) - h.v;
-  V3 p0 = v3(p[0], p[1], p[2]), p1 = v3(p[3], p[4], p[5]), p2 = v3(p[6], p[7], p[8]);
-  V3 n0 = v3(n[0], n[1], n[2]), n1 = v3(n[3], n[4], n[5]), n2 = v3(n[6], n[7], n[8]);
-  s.position = (w0 * p0 + h.u * p1) + h.v * p2;
-  V3 nn = normalize((w0 * n0 + h.u * n1) + h.v * n2);
+  V3 pl = (w0 * v3(vx.position[0], vx.position[1], vx.position[2]) + h.u * v3(vy.position[0], vy.position[1], vy.position[2])) +
+          h.v * v3(vz.position[0], vz.position[1], vz.position[2]);
+  V3 nl = (w0 * v3(vx.normal[0], vx.normal[1], vx.normal[2]) + h.u * v3(vy.normal[0], vy.normal[1], vy.normal[2])) +
+          h.v * v3(vz.normal[0], vz.normal[1], vz.normal[2]);
+  V3 nn = normalize(mat4_mul_point(in.xform, nl, 0.0f));
   if (dot(ray_dir, nn) > 0.0f) nn = neg(nn);
   s.normal = nn;
-  s.inst = sc.tri_inst[h.prim];
+  s.position = mat4_mul_point(in.xform, pl, 1.0f);
   return s;
 }
 // Full HitInfo as written by __closesthit__PCS_R (PCS.cu:15-28).

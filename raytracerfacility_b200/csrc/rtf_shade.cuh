@@ -109,26 +109,35 @@ RTF_D float3 env_light(float3 position, float3 dir, const rtf_env& env, const De
   return max3(f3(0, 0, 0), c);
 }
 
-// ---- hit reconstruction: TriangularMesh::GetHitInfo (RayDataDefinations.hpp:127-164) on world-space
-//      vertices + SBT::GetHitInfo's normalise-and-face-the-ray (RayDataDefinations.hpp:375-378) -------
+// ---- hit reconstruction: TriangularMesh::GetHitInfo (RayDataDefinations.hpp:127-149) interpolates the OBJECT-space
+//      vertices; SBT::GetHitInfo (RayDataDefinations.hpp:375-380) then transforms: normal = normalize(M * (n, 0)), faced
+//      against the ray, position = M * (p, 1).  Same association as the reference, so the result is bit-equal to it under
+//      any instance transform (interpolating pre-transformed vertices would differ by an ulp). -------
 struct SurfaceHit {
   float3 position, normal;
   uint32_t inst;
 };
 RTF_D SurfaceHit surface_hit(const DevScene& sc, uint32_t prim, float u, float v, float3 ray_dir) {
-  const float* p = sc.pos9 + 9 * (size_t)prim;
-  const float* n = sc.nrm9 + 9 * (size_t)prim;
-  const float w0 = (1.0f - u) - v;
-  const float3 p0 = f3(__ldg(p + 0), __ldg(p + 1), __ldg(p + 2)), p1 = f3(__ldg(p + 3), __ldg(p + 4), __ldg(p + 5)),
-               p2 = f3(__ldg(p + 6), __ldg(p + 7), __ldg(p + 8));
-  const float3 n0 = f3(__ldg(n + 0), __ldg(n + 1), __ldg(n + 2)), n1 = f3(__ldg(n + 3), __ldg(n + 4), __ldg(n + 5)),
-               n2 = f3(__ldg(n + 6), __ldg(n + 7), __ldg(n + 8));
   SurfaceHit s;
-  s.position = (w0 * p0 + u * p1) + v * p2;
-  float3 nn = normalize3((w0 * n0 + u * n1) + v * n2);
+  s.inst = __ldg(sc.tri_inst + prim);
+  const InstDev& in = sc.insts[s.inst];
+  const uint32_t lt = prim - in.first_prim;
+  const uint32_t i0 = __ldg(in.tris + 3 * lt), i1 = __ldg(in.tris + 3 * lt + 1), i2 = __ldg(in.tris + 3 * lt + 2);
+  // position|padding and normal|padding are the first two 16 B quads of the 80 B vertex
+  const float4* q0 = reinterpret_cast<const float4*>(in.verts + i0);
+  const float4* q1 = reinterpret_cast<const float4*>(in.verts + i1);
+  const float4* q2 = reinterpret_cast<const float4*>(in.verts + i2);
+  const float4 a0 = __ldg(q0), b0 = __ldg(q0 + 1), a1 = __ldg(q1), b1 = __ldg(q1 + 1), a2 = __ldg(q2), b2 = __ldg(q2 + 1);
+  const float w0 = (1.0f - u) - v;
+  const float3 pl = (w0 * f3(a0.x, a0.y, a0.z) + u * f3(a1.x, a1.y, a1.z)) + v * f3(a2.x, a2.y, a2.z);
+  const float3 nl = (w0 * f3(b0.x, b0.y, b0.z) + u * f3(b1.x, b1.y, b1.z)) + v * f3(b2.x, b2.y, b2.z);
+  float m[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) m[k] = in.xform[k];
+  float3 nn = normalize3(mat4_mul(m, nl, 0.0f));
   if (dot3(ray_dir, nn) > 0.0f) nn = neg3(nn);
   s.normal = nn;
-  s.inst = __ldg(sc.tri_inst + prim);
+  s.position = mat4_mul(m, pl, 1.0f);
   return s;
 }
 // Interpolated vertex attributes for the materials that read them (TriangularMesh::GetHitInfo, RDD.hpp:127-164;

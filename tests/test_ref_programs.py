@@ -15,10 +15,9 @@ the LiDAR hit record, the BTF shading branch — and the order of the draws.  Wh
 the keyed Philox draws of the product (instead of the LCG stream), the 4-nearest BSSRDF probe, and OptiX's traversal.
 
 Bars, with the reason for each residue:
-  * `mixed` scene (identity transforms): 1 sample x 1 bounce bit-equal; more bounces / samples 1e-6 of the largest channel
-    (the oracle unrolls the reference's recursion into a throughput loop and sums samples in a fixed tree);
-  * `plants` scene (every instance under a transform): 1e-5 — the oracle interpolates world-space vertices where the
-    reference interpolates object-space ones and transforms the result (1 ulp in the hit position and normal);
+  * `mixed` and `plants` scenes (the latter with every instance under its own transform): 1 sample x 1 bounce bit-equal;
+    more bounces / samples 1e-6 of the largest channel (the oracle unrolls the reference's recursion into a throughput
+    loop and sums samples in a fixed tree);
   * `btf` scene: 90 % of the probes to 1e-5, all to 2e-2 — the portable trigonometry of the BTF evaluator (pinned on its
     own in test_golden.py) at grazing angles, carried through the bounces;
   * ray counts equal in every case (same any-hit and shadow-ray decisions).
@@ -64,13 +63,11 @@ def test_illumination_programs(orc, S, ref, oscs):
         assert want[:, :3].max() > 0.05, key  # lit
         err = _rel(got[:, :3], want[:, :3])
         equal = (got[:, :3].view(np.uint32) == want[:, :3].view(np.uint32)).all(1).mean()
-        if sc == "mixed":
+        if sc in ("mixed", "plants"):
             if (b, n) == (1, 1):
                 assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), key
             else:
                 assert err.max() <= 1e-6, (key, err.max())
-        elif sc == "plants":
-            assert err.max() <= 1e-5 and equal >= (0.8 if (b, n) == (1, 1) else 0.0), (key, err.max(), equal)
         else:
             assert np.percentile(err.max(1), 90) <= 1e-5 and err.max() <= 2e-2, (key, err.max())
             if (b, n) == (1, 1):
@@ -117,14 +114,7 @@ def test_point_cloud_programs(orc, S, ref, oscs):
         oscs[sc].scan_point_cloud(smp)
         assert np.array_equal(smp["hit"], want["hit"]) and np.array_equal(smp["handle"], want["handle"]), sc
         assert 0.2 < want["hit"].mean() < 0.95, sc
-        for f in ("tangent", "color", "tex_coord", "data"):
-            assert np.array_equal(smp["hit_info"][f].view(np.uint32), want["hit_info"][f].view(np.uint32)), (sc, f)
-        if sc == "mixed":  # identity transforms: the whole 120 B record
-            assert smp.tobytes() == want.tobytes()
-        else:  # world-space vs object-space interpolation: 1 ulp
-            for f in ("position", "normal"):
-                assert np.abs(smp["hit_info"][f] - want["hit_info"][f]).max() <= 5e-7, (sc, f)
-                assert (smp["hit_info"][f].view(np.uint32) == want["hit_info"][f].view(np.uint32)).mean() > 0.9, (sc, f)
+        assert smp.tobytes() == want.tobytes(), sc  # the whole 120 B record, with or without instance transforms
         if orc.ref_pcs_lib() is not None:
             live = ref[f"pcs_{sc}_in"].view(S.PC_SAMPLE_DTYPE).copy()
             oscs[sc].ref_scan_point_cloud(live)
