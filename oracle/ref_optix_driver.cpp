@@ -266,7 +266,7 @@ REF_API int ref_ie_run(const orc::Scene* sc, const rtf_env* env, const rtf_ray_p
 }
 #endif
 #ifdef REF_ENTRY_PCS
-// __raygen__PCS over `n` point-cloud samples (in-out, the reference's 120 B records).
+// __raygen__PCS over `n` point-cloud samples (in-out, the reference's 112 B records).
 REF_API int ref_pcs_run(const orc::Scene* sc, rtf_pc_sample* samples, unsigned long long n) {
   using namespace emu;
   if (setup_scene(sc) != 0) return -1;

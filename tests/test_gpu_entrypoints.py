@@ -153,7 +153,7 @@ def test_point_cloud_against_the_reference_programs(mod, S):
     """The device's SamplePointCloud against tests/golden/programs_ref.npz = what the REFERENCE's own __raygen__PCS /
     __closesthit__PCS_R / __miss__PCS_R programs (ptx/PointCloudScanning.cu, RayDataDefinations.hpp) write when compiled
     unmodified for the host (oracle/ref_optix_driver.cpp) — no oracle in between, and no random numbers on this path.
-    The whole 120 B record byte for byte, with or without instance transforms."""
+    The whole 112 B record byte for byte, with or without instance transforms."""
     import os
     from .golden import make_golden as G
     ref = np.load(os.path.join(os.path.dirname(__file__), "golden", "programs_ref.npz"))

@@ -114,7 +114,7 @@ def test_point_cloud_programs(orc, S, ref, oscs):
         oscs[sc].scan_point_cloud(smp)
         assert np.array_equal(smp["hit"], want["hit"]) and np.array_equal(smp["handle"], want["handle"]), sc
         assert 0.2 < want["hit"].mean() < 0.95, sc
-        assert smp.tobytes() == want.tobytes(), sc  # the whole 120 B record, with or without instance transforms
+        assert smp.tobytes() == want.tobytes(), sc  # the whole 112 B record, with or without instance transforms
         if orc.ref_pcs_lib() is not None:
             live = ref[f"pcs_{sc}_in"].view(S.PC_SAMPLE_DTYPE).copy()
             oscs[sc].ref_scan_point_cloud(live)
