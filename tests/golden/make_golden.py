@@ -15,6 +15,10 @@
                    host emulation of the OptiX intrinsics: oracle/ref_optix_driver.cpp), tracing through the oracle's BVH
                    and drawing from the reference's own LCG.  Pins orc::illum_probe / trace_path / camera_pixel /
                    camera_resolve / full_hit_info (run with the same LCG stream: orc_*_lcg).
+* c1_ref.npz     — BASELINE config 1 (20k-triangle sorghum + ground, sky light, 64 samples per triangle and face, 4 bounces)
+                   run through the REFERENCE's own illumination programs on the host (as programs_ref.npz) with two seeds:
+                   the per-triangle energies of both runs.  Their difference is the Monte-Carlo noise of the reference's
+                   own estimator, against which the GPU's (keyed Philox draws) is tested statistically.
 * btf_ref.npz    — outputs of the REFERENCE's own compressed-BTF evaluator (include/RayTracerFacility/MLVQ/*.cuh compiled
                    unmodified into oracle/_ref/libbtf_ref.so against oracle/ref_stubs).  Pins orc::btf_value_deg.
 * oracle_extra.npz — the same for the BSSRDF probe / irradiance, the instanced and skinned pre-kernels, light probes, flux.
@@ -254,6 +258,7 @@ def main():
     write_btf_ref()
     write_env_ref()
     write_programs_ref()
+    write_c1_ref()
     print("wrote", os.listdir(HERE))
 
 
@@ -309,6 +314,21 @@ def write_programs_ref():
         oscs[sc].ref_scan_point_cloud(smp)
         out[f"pcs_{sc}"] = smp.view(np.uint8)
     np.savez_compressed(os.path.join(HERE, "programs_ref.npz"), **out)
+
+
+C1_SEEDS = (11, 12)
+
+
+def write_c1_ref():
+    """c1_ref.npz — see the module docstring; half a minute of single-thread CPU."""
+    osc = orc.OracleScene(scenes.sorghum_scene(1))
+    env, rp = S.EnvironmentProperties(), S.RayProperties(4, 64)
+    out = {}
+    for name, seed in zip("ab", C1_SEEDS):
+        pr = osc.make_probes()
+        out["rays_" + name] = np.array([osc.ref_illum_probes(env, rp, pr, seed, 1e-3)])
+        out["energy_" + name] = pr["energy"].copy()
+    np.savez_compressed(os.path.join(HERE, "c1_ref.npz"), **out)
 
 
 def write_btf_ref():

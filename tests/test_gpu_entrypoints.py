@@ -170,6 +170,18 @@ def test_point_cloud_against_the_reference_programs(mod, S):
         assert smp.tobytes() == want.tobytes(), name
 
 
+def test_config1_statistics_against_the_reference_programs(rt, S, scenes):
+    """BASELINE config 1 on the device against tests/golden/c1_ref.npz = the REFERENCE's own illumination programs run on
+    the host with the reference's own LCG under two seeds: the device's estimate (keyed Philox draws) must be
+    statistically indistinguishable from them (tests/test_ref_programs.py: c1_statistics)."""
+    import os
+    from .test_ref_programs import c1_statistics
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "c1_ref.npz"))
+    rt.load_scene(scenes.sorghum_scene(1))
+    e = rt.estimate_illumination_mesh(S.EnvironmentProperties(), S.RayProperties(bounces=4, samples=64), 5)
+    c1_statistics(e[:, :3], rt.last_job_stats()[0], g)
+
+
 def test_camera_render_parity_and_accumulation(rt, orc, S, scenes):
     sd = scenes.sorghum_scene(1)
     rt.load_scene(sd, 63)

@@ -119,3 +119,30 @@ def test_point_cloud_programs(orc, S, ref, oscs):
             live = ref[f"pcs_{sc}_in"].view(S.PC_SAMPLE_DTYPE).copy()
             oscs[sc].ref_scan_point_cloud(live)
             assert live.tobytes() == want.tobytes(), sc
+
+
+def c1_statistics(energy, rays, g):
+    """BASELINE config 1 against the reference's own programs run with the reference's own LCG under two seeds (a, b):
+    a different random stream must be statistically indistinguishable from them.  RMS per-triangle difference to run a
+    within 7 % of the a-b RMS (the reference estimator's own Monte-Carlo noise, 60006 values), mean difference per channel
+    within 4 sigma of zero, rays traced within 0.3 %."""
+    a, b = g["energy_a"], g["energy_b"]
+    n = len(a)
+    assert energy.shape == a.shape
+    noise = np.sqrt(((a - b) ** 2).mean())
+    assert 0.02 < noise < 0.05
+    for other in (a, b):
+        rms = np.sqrt(((energy - other) ** 2).mean())
+        assert 0.93 <= rms / noise <= 1.07, (rms, noise)
+        assert np.abs((energy - other).mean(0)).max() <= 4.0 * noise / np.sqrt(n), (energy - other).mean(0)
+    assert abs(rays - int(g["rays_a"][0])) <= 3e-3 * int(g["rays_a"][0]), rays
+    # and per triangle: the largest deviations are what the noise predicts (no triangle is systematically off)
+    z = np.abs(energy - 0.5 * (a + b)).max(1)
+    assert (z > 6 * noise).mean() < 2e-3, (z > 6 * noise).mean()
+
+
+def test_config1_statistics_against_the_reference_programs(orc, S, scenes):
+    g = np.load(os.path.join(GOLDEN, "c1_ref.npz"))
+    osc = orc.OracleScene(scenes.sorghum_scene(1))
+    e, st = osc.illum_mesh(S.EnvironmentProperties(), S.RayProperties(4, 64), seed=5, push=1e-3)
+    c1_statistics(e[:, :3], st.rays, g)
