@@ -352,6 +352,20 @@ def main():
                 _, onv, otv = osc.trace(np_rays[:mc], counts=True)
                 out["cpu_baseline"] = {"value": m / cdt / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
                                        "sample": f"first {m} rays of rank 0's M1 batch, all host threads"}
+                # the illumination leg next to the reference's OWN device programs run on one host core (compiled
+                # unmodified over a host emulation of the OptiX intrinsics, oracle/ref_optix_driver.cpp; the tracer behind
+                # optixTrace is the oracle's), bounded sample
+                if orc.ref_ie_lib() is not None:
+                    kt = min(n_tris, 2000)
+                    pr = osc.make_probes(0, kt)
+                    t0 = time.perf_counter()
+                    rrays = osc.ref_illum_probes(env, rp, pr, 0x5EED, 1e-3)
+                    rdt = time.perf_counter() - t0
+                    out["illum"]["cpu_baseline"] = {
+                        "value": kt * rp.samples * 2 / rdt, "unit": "triangle-samples/s", "cores": 1, "kind": "reference",
+                        "Mrays/s": rrays / rdt / 1e6,
+                        "sample": f"first {kt} triangles of the same job through the reference's own __raygen__IE / "
+                                  "closest-hit / any-hit / miss programs on the host, one thread"}
                 out["parity"] = {"hits_bit_exact_on_sample": same, "sample_rays": m,
                                  "visit_counts_equal": bool(np.array_equal(onv, nv[:mc]) and np.array_equal(otv, tv[:mc])),
                                  "visit_count_rays": mc}
