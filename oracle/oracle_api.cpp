@@ -204,12 +204,11 @@ ORC_API void orc_illum_mesh(Scene* s, const rtf_env* env, const rtf_ray_props* r
 }
 // orc_illum_probes with the REFERENCE's random stream: one LCG per probe seeded (probe index, seed) as __raygen__IE does
 // (IE.cu:47), drawn sequentially in the reference's order.  Test mode only (see t_seq_rng, oracle_math.h): compared with
-// the reference's own device programs run on the host (ref_ie_driver.cpp).  No BSSRDF materials (the repo's BSSRDF
-// reorders the two first-hit paths); single thread.
+// the reference's own device programs run on the host (ref_optix_driver.cpp).  BSSRDF materials: the draws are made at
+// the reference's positions (oracle_shade.h, `deferred`), but the spatial probe itself is the repo's (4 nearest), which
+// equals the reference's only where at most one same-handle surface lies in the probe's range.  Single thread.
 ORC_API int orc_illum_probes_lcg(Scene* s, const rtf_env* env, const rtf_ray_props* rp, rtf_illum_sampler* probes, uint64_t n,
                                  uint32_t seed, float push, uint64_t* rays_out) {
-  for (const rtf_material& m : s->mats)
-    if (m.subsurface_factor > 0.0f && m.subsurface_radius[0] > 0.0f) return -1;
   uint64_t rays = 0;
   for (uint64_t i = 0; i < n; i++) {
     rtf_illum_sampler& pr = probes[i];

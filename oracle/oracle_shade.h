@@ -403,10 +403,23 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
   struct {
     bool on = false;
     V3 o = v3(0, 0, 0), d = v3(0, 0, 0), T = v3(0, 0, 0);
+    // test mode (t_seq_rng) only: the reference draws the ordinary bounce AFTER the subsurface path has returned
+    // (RF.cuh:134-136), so with a sequential stream the draw is made at resume time from what is kept here
+    bool deferred = false;
+    V3 normal = v3(0, 0, 0), d_in = v3(0, 0, 0), base = v3(0, 0, 0);  // base = (1 - subsurface_factor) * albedo
+    float metallic = 0.0f, roughness = 0.0f, f = 0.0f;
   } pend;
   auto resume = [&]() -> bool {
     if (!pend.on) return false;
     pend.on = false;
+    if (pend.deferred) {
+      pend.deferred = false;
+      float rr[4];
+      path_draws(seed, STREAM_PATH, unit, 0, 0, rr, 2);
+      const V3 nd = sample_lobe(rr[0], rr[1], reflect(pend.d_in, pend.normal), pend.metallic);
+      const float k = clampf(fabsf(dot(pend.normal, nd)) * pend.roughness + (1.0f - pend.roughness) * pend.f, 0.0f, 1.0f);
+      pend.d = nd, pend.T = pend.T * (pend.base * k);
+    }
     o = pend.o, d = pend.d, T = pend.T, tmin = 1e-3f;
     any_hit_enabled = true;
     return true;
@@ -533,8 +546,7 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
       if (hit_count <= 1 && m.subsurface_factor > 0.0f && m.subsurface_radius[0] > 0.0f) {
         const float radius = m.subsurface_radius[0];
         float rs[4], rb[4];
-        path_rng(seed, STREAM_SSS, unit, hit_count, 0, rs);
-        path_rng(seed, STREAM_SSS, unit, hit_count, 1, rb);
+        path_draws(seed, STREAM_SSS, unit, hit_count, 0, rs, 2);  // disk radius, rotation angle (BSSDF.cuh:51-54)
         const V3 disk_center = sh.position + (radius * normal) * 0.5f;
         const float disk_radius = radius * sqrtf(rs[0]);
         const float distance = sqrtf(radius * radius - disk_radius * disk_radius);
@@ -543,6 +555,10 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
         const SSRecords rec = ss_probe(sc.bvh, sample_pos, neg(normal), distance, radius + distance, handle,
                                        [&](uint32_t inst) { return sc.insts[inst].handle; });
         if (rec.n > 0) {
+          if (t_seq_rng) {  // the reference picks the record with a COPY of the generator (BSSDF.cuh:58,77): the number
+            LCG copy = *t_seq_rng;  // the main stream hands out next, not consumed
+            rs[2] = copy.next();
+          }
           int index = (int)(rs[2] * (float)rec.n);
           index = index < 0 ? 0 : (index > rec.n - 1 ? rec.n - 1 : index);
           Hit rh{rec.t[index], rec.u[index], rec.v[index], rec.prim[index]};
@@ -560,12 +576,22 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
           }
           if (length(sh.position - so.position) <= radius) {
             ss_o = so.position + out_n * 0.01f;
+            path_draws(seed, STREAM_SSS, unit, hit_count, 1, rb, 2);
             ss_d = sample_lobe(rb[0], rb[1], reflect(neg(out_n), out_n), metallic);  // BRDF(metallic, rnd, -n, n)
             const float k2 = clampf(fabsf(dot(out_n, ss_d)) * roughness + (1.0f - roughness) * f, 0.0f, 1.0f);
             ss_w = (m.subsurface_factor * v3(m.subsurface_color[0], m.subsurface_color[1], m.subsurface_color[2])) * k2;
             need_sample = true;
           }
         }
+      }
+      if (t_seq_rng && need_sample) {  // test mode: subsurface path first, the bounce is drawn when it resumes
+        acc = acc + T * emis;
+        pend.on = true, pend.deferred = true, pend.o = sh.position, pend.T = T;
+        pend.normal = normal, pend.d_in = d, pend.base = (1.0f - m.subsurface_factor) * albedo;
+        pend.metallic = metallic, pend.roughness = roughness, pend.f = f;
+        T = T * ss_w;
+        o = ss_o, d = ss_d, tmin = 1e-3f;
+        continue;
       }
       path_draws(seed, STREAM_PATH, unit, hit_count, 0, r, sc.brdf == RTF_BRDF_LAMBERT_GGX ? 3 : 2);
       V3 nd, wgt;

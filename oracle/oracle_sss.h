@@ -64,7 +64,12 @@ static inline SSRecords ss_probe_brute(const BVH& bvh, V3 o, V3 d, float tmin, f
 // glm::rotate(v, angle, normal) (glm/gtx/rotate_vector.hpp -> glm/ext/matrix_transform.inl), angle = 2*pi*u.
 static inline V3 rotate_about(V3 v, float u_turns, V3 axis_in) {
   float s, c;
-  sincos2pi(u_turns, &s, &c);
+  if (t_seq_rng) {  // test mode (oracle_math.h): the reference's own libm calls on 2 pi u (BSSDF.cuh:54)
+    const float a = 2.0f * 3.14159265358979323846264338327950288f * u_turns;
+    c = cosf(a), s = sinf(a);
+  } else {
+    sincos2pi(u_turns, &s, &c);
+  }
   const V3 axis = normalize(axis_in);
   const V3 temp = (1.0f - c) * axis;
   const V3 c0 = v3(c + temp.x * axis.x, temp.x * axis.y + s * axis.z, temp.x * axis.z - s * axis.y);

@@ -70,8 +70,14 @@ float2 optixGetTriangleBarycentrics() { return emu::g.bary; }
 float optixGetCurveParameter() { return 0.0f; }
 float3 optixTransformPointFromWorldToObjectSpace(float3 p) { return p; }
 CUdeviceptr optixGetSbtDataPointer() { return (CUdeviceptr)emu::g.sbt; }
-void optixIgnoreIntersection() { emu::g.ignore = true; }
-void optixTerminateRay() {}
+// On the device neither of these returns to the any-hit program: emulated by unwinding out of it.
+struct IgnoreIntersection {};
+struct TerminateRay {};
+void optixIgnoreIntersection() {
+  emu::g.ignore = true;
+  throw IgnoreIntersection();
+}
+void optixTerminateRay() { throw TerminateRay(); }
 template <>
 float4 tex2D<float4>(cudaTextureObject_t tex, float u, float v) {
   float t[4];
@@ -157,15 +163,22 @@ void optixTrace(OptixTraversableHandle, float3 origin, float3 direction, float t
   const RayCtx saved = g;
   const bool radiance = sbt_offset == (unsigned)RayType::Radiance;
   const orc::Ray ray{orc::v3(origin.x, origin.y, origin.z), tmin, orc::v3(direction.x, direction.y, direction.z), tmax};
-  g_rays++;
+  if (radiance) g_rays++;  // the spatial-sampling probes of the BSSRDF are not counted as rays (neither does the oracle)
   orc::Hit h;
   if (flags & OPTIX_RAY_FLAG_DISABLE_ANYHIT) {
     h = orc::trace(sc.bvh, ray, nullptr, (flags & OPTIX_RAY_FLAG_TERMINATE_ON_FIRST_HIT) != 0);
   } else {
     const unsigned q0 = p0, q1 = p1;
+    bool terminated = false;  // optixTerminateRay: the current hit is kept, nothing further is reported
     h = orc::trace(sc.bvh, ray, nullptr, false, [&](const orc::Tri48& tri, const orc::Hit& cand) {
+      if (terminated) return false;
       set_hit(origin, direction, q0, q1, tri.inst, tri.prim, cand.t, cand.u, cand.v);
-      g_prog.anyhit[radiance ? 0 : 1]();
+      try {
+        g_prog.anyhit[radiance ? 0 : 1]();
+      } catch (const IgnoreIntersection&) {
+      } catch (const TerminateRay&) {
+        terminated = true;
+      }
       return !g.ignore;
     });
   }

@@ -151,11 +151,22 @@ def sky_env(sky, k):
 def programs_ref_scenes():
     """Scenes of programs_ref.npz: `plants` (Default materials, every instance under its own transform), `mixed`
     (materials_scene without the BTF quad: textures, normal / metallic / roughness maps, vertex colours, alpha-textured
-    canopy, emission, a transmissive material, cube map; identity transforms) and `btf` (materials_scene as it is)."""
+    canopy, emission, a transmissive material, cube map; identity transforms), `btf` (materials_scene as it is) and `sss`
+    (below)."""
     mixed = scenes.materials_scene()
     mixed.materials[3] = scenes.Material(albedo=(0.5, 0.4, 0.9), metallic=0.6, roughness=0.3, transmission=0.4)
     del mixed.material_btf[3]
-    return dict(plants=scenes.sorghum_scene(n_plants=2, seed=2), mixed=mixed, btf=scenes.materials_scene())
+    # `sss`: `mixed` with a subsurface ground (one flat sheet per handle, so the BSSRDF's spatial probe can only ever
+    # find the sheet itself — at most one record, the case in which the repo's 4-nearest probe and the reference's
+    # traversal-order collection coincide): BSSRDF sampling arithmetic, normal map at the exit point, draw order
+    sss = scenes.materials_scene()
+    sss.materials[3] = mixed.materials[3]
+    del sss.material_btf[3]
+    g = sss.materials[1]
+    g.subsurface_factor = 0.5
+    g.subsurface_color[:] = (0.9, 0.5, 0.3)
+    g.subsurface_radius[:] = (0.05, 0.0, 0.0)
+    return dict(plants=scenes.sorghum_scene(n_plants=2, seed=2), mixed=mixed, btf=scenes.materials_scene(), sss=sss)
 
 
 PROGRAMS_ENVS = dict(
@@ -165,7 +176,8 @@ PROGRAMS_ENVS = dict(
     cube=dict(environmental_map_id=3, skylight_intensity=1.7, gamma=2.2))
 # (scene, environment, bounces, samples) of the illumination-estimation cases; seed 7, push 1e-3, first 400 probes
 PROGRAMS_IE = [(sc, e, b, n) for sc, envs in (("plants", ("scene", "skydome", "sun")), ("mixed", ("scene", "skydome", "sun", "cube")),
-                                               ("btf", ("scene", "sun"))) for e in envs for b, n in ((1, 1), (4, 8))]
+                                               ("btf", ("scene", "sun")), ("sss", ("scene", "skydome", "cube")))
+               for e in envs for b, n in ((1, 1), (4, 8))]
 # (environment, bounces, samples, output type, accumulate) of the camera cases on `mixed`, 32 x 24, aperture 0.02
 PROGRAMS_CR = [("scene", 1, 1, S.OUT_COLOR, 0), ("scene", 3, 4, S.OUT_DEPTH, 0), ("skydome", 1, 1, S.OUT_COLOR, 0),
                ("skydome", 3, 4, S.OUT_COLOR, 1), ("cube", 2, 2, S.OUT_COLOR, 0)]

@@ -12,12 +12,17 @@ compared.  What that pins: everything the reference's programs compute — probe
 textures and normal maps, vertex colours, the alpha any-hit, emission, the mirror-lobe bounce and its weight, the
 three lighting types, sky model and cube map, the bounce limit, camera rays with depth of field, accumulation and gamma,
 the LiDAR hit record, the BTF shading branch — and the order of the draws.  What it leaves to the documented departures:
-the keyed Philox draws of the product (instead of the LCG stream), the 4-nearest BSSRDF probe, and OptiX's traversal.
+the keyed Philox draws of the product (instead of the LCG stream), which records the BSSRDF probe collects when several
+same-handle surfaces lie in its range (the reference's depend on OptiX's traversal order), and OptiX's traversal.
 
 Bars, with the reason for each residue:
   * `mixed` and `plants` scenes (the latter with every instance under its own transform): 1 sample x 1 bounce bit-equal;
     more bounces / samples 1e-6 of the largest channel (the oracle unrolls the reference's recursion into a throughput
     loop and sums samples in a fixed tree);
+  * `sss` scene (subsurface ground that is a single sheet, so the BSSRDF probe finds at most one record — where the repo's
+    order-independent 4-nearest probe and the reference's traversal-order collection coincide): same bars; pins the
+    BSSRDF sampling arithmetic, the exit-point normal map, the record pick drawn from a COPY of the generator
+    (BSSDF.cuh:58,77) and the order subsurface path -> ordinary bounce;
   * `btf` scene: 90 % of the probes to 1e-5, all to 2e-2 — the portable trigonometry of the BTF evaluator (pinned on its
     own in test_golden.py) at grazing angles, carried through the bounces;
   * ray counts equal in every case (same any-hit and shadow-ray decisions).
@@ -63,7 +68,7 @@ def test_illumination_programs(orc, S, ref, oscs):
         assert want[:, :3].max() > 0.05, key  # lit
         err = _rel(got[:, :3], want[:, :3])
         equal = (got[:, :3].view(np.uint32) == want[:, :3].view(np.uint32)).all(1).mean()
-        if sc in ("mixed", "plants"):
+        if sc in ("mixed", "plants", "sss"):
             if (b, n) == (1, 1):
                 assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), key
             else:
@@ -81,7 +86,7 @@ def test_illumination_programs(orc, S, ref, oscs):
             live = osc.make_probes(0, min(400, osc.n_tris))
             assert osc.ref_illum_probes(env, rp, live, 7, 1e-3) == rays
             assert np.array_equal(np.concatenate([live["energy"], live["direction"]], 1).view(np.uint32), ref[key]), key
-    assert len(seen) == 9
+    assert len(seen) == 12
 
 
 def test_camera_programs(orc, S, ref, oscs):
