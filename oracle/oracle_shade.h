@@ -555,11 +555,17 @@ static inline PathResult trace_path(const Scene& sc, const rtf_env& env, int bou
         const SSRecords rec = ss_probe(sc.bvh, sample_pos, neg(normal), distance, radius + distance, handle,
                                        [&](uint32_t inst) { return sc.insts[inst].handle; });
         if (rec.n > 0) {
-          if (t_seq_rng) {  // the reference picks the record with a COPY of the generator (BSSDF.cuh:58,77): the number
-            LCG copy = *t_seq_rng;  // the main stream hands out next, not consumed
-            rs[2] = copy.next();
+          // The reference picks the record with a COPY of the generator (BSSDF.cuh:58,77), which leaves the main stream
+          // where it was: the pick is the very number the exit lobe's first draw returns afterwards (BSSDF.cuh:83).
+          float pick;
+          if (t_seq_rng) {
+            LCG copy = *t_seq_rng;
+            pick = copy.next();
+          } else {
+            path_rng(seed, STREAM_SSS, unit, hit_count, 1, rb);
+            pick = rb[0];
           }
-          int index = (int)(rs[2] * (float)rec.n);
+          int index = (int)(pick * (float)rec.n);
           index = index < 0 ? 0 : (index > rec.n - 1 ? rec.n - 1 : index);
           Hit rh{rec.t[index], rec.u[index], rec.v[index], rec.prim[index]};
           const SurfaceHit so = surface_hit(sc, rh, v3(0, 0, 0));  // GetHitInfo(rayDirection, false): no flip

@@ -365,7 +365,9 @@ __global__ void __launch_bounds__(256, SSS ? 1 : RTF_SHADE_MIN_BLOCKS)
               SSRecords rec;
               ss_probe(sc, sample_pos, neg3(normal), distance, radius + distance, sc.insts[sh.inst].handle, rec);
               if (rec.n > 0) {
-                int index = (int)(rs.z * (float)rec.n);
+                // the reference picks the record with a COPY of its generator (BSSDF.cuh:58,77): the pick is the same
+                // number as the exit lobe's first draw (BSSDF.cuh:83)
+                int index = (int)(rb.x * (float)rec.n);
                 index = index < 0 ? 0 : (index > rec.n - 1 ? rec.n - 1 : index);
                 float rt = 0, ru = 0, rv = 0;
                 uint32_t rprim = 0;

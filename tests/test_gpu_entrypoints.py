@@ -157,9 +157,9 @@ def test_point_cloud_against_the_reference_programs(mod, S):
     import os
     from .golden import make_golden as G
     ref = np.load(os.path.join(os.path.dirname(__file__), "golden", "programs_ref.npz"))
-    for name, sd in G.programs_ref_scenes().items():
-        if name == "btf":
-            continue
+    all_scenes = G.programs_ref_scenes()
+    for name in ("plants", "mixed"):
+        sd = all_scenes[name]
         rt = mod.RayTracer(0)  # one context per scene
         rt.load_scene(sd)
         smp = ref[f"pcs_{name}_in"].view(S.PC_SAMPLE_DTYPE).copy()
