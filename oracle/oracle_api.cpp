@@ -375,8 +375,6 @@ ORC_API void orc_camera(Scene* s, const rtf_env* env, const rtf_ray_props* rp, c
 // as __raygen__CR does (CR.cu:42-44), drawn sequentially.  Test mode only (see orc_illum_probes_lcg).  color is in-out.
 ORC_API int orc_camera_lcg(Scene* s, const rtf_env* env, const rtf_ray_props* rp, const rtf_camera_props* cam, float* color,
                            float* normal, float* albedo, uint64_t* rays_out) {
-  for (const rtf_material& m : s->mats)
-    if (m.subsurface_factor > 0.0f && m.subsurface_radius[0] > 0.0f) return -1;
   uint64_t rays = 0;
   for (int iy = 0; iy < cam->height; iy++)
     for (int ix = 0; ix < cam->width; ix++) {
