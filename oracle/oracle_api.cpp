@@ -43,6 +43,12 @@ ORC_API void orc_lcg(uint32_t v0, uint32_t v1, int n, float* out, uint32_t* stat
   if (state_after_init) *state_after_init = g.state;
   for (int i = 0; i < n; i++) out[i] = g.next();
 }
+// Test switch, see g_libm_trig in oracle_math.h.  Returns the previous value.
+ORC_API int orc_set_libm_trig(int on) {
+  const int was = g_libm_trig;
+  g_libm_trig = on;
+  return was;
+}
 ORC_API void orc_sincos2pi(int n, const float* u, float* s, float* c) {
   for (int i = 0; i < n; i++) sincos2pi(u[i], &s[i], &c[i]);
 }
@@ -219,10 +225,12 @@ ORC_API int orc_illum_probes_lcg(Scene* s, const rtf_env* env, const rtf_ray_pro
     LCG g;
     g.init((uint32_t)i, seed);
     t_seq_rng = &g;
+    g_libm_trig = 1;  // the BTF evaluator's angles through libm too, as the reference computes them
     float o6[6];
     bool f = pr.front_face != 0, bk = pr.back_face != 0;
     illum_probe(*s, *env, *rp, seed, push, i, P, N, f, bk, 0, rp->samples, o6, &rays, nullptr);
     t_seq_rng = nullptr;
+    g_libm_trig = 0;
     int faces = (f ? 1 : 0) + (bk ? 1 : 0);
     if (faces * rp->samples != 0) {
       illum_finalize(o6, faces, rp->samples);
@@ -382,8 +390,10 @@ ORC_API int orc_camera_lcg(Scene* s, const rtf_env* env, const rtf_ray_props* rp
       LCG g;
       g.init((uint32_t)((float)ix + (float)cam->width * (float)iy), (uint32_t)cam->frame_id);
       t_seq_rng = &g;
+      g_libm_trig = 1;
       PixelOut po = camera_pixel(*s, *env, *rp, *cam, ix, iy, &rays, nullptr);
       t_seq_rng = nullptr;
+      g_libm_trig = 0;
       float prev[4] = {color[4 * k], color[4 * k + 1], color[4 * k + 2], color[4 * k + 3]};
       camera_resolve(*cam, po, prev, color + 4 * k, normal + 4 * k, albedo + 4 * k);
     }

@@ -171,7 +171,13 @@ static inline float atan01(float a) {  // a in [0,1]
   p = p * z - 3.33329491539e-1f;
   return off + (a + a * (z * p));
 }
+// Test switch (orc_set_libm_trig): the inverse functions and sincos_rad below call libm, as the reference's glm::asin /
+// acosf / atan2 / glm::sin / glm::cos do, instead of the portable polynomials — used to show that the restatements that
+// sit on top of them (compressed BTF) equal the reference's own code bit for bit once the trigonometry is the same.
+// The product always uses the portable forms (identical on host and device).
+static int g_libm_trig = 0;
 static inline float atan2p(float y, float x) {
+  if (g_libm_trig) return atan2f(y, x);
   if (y != y || x != x) return NAN;
   const float ax = fabsf(x), ay = fabsf(y);
   const float hi = ax > ay ? ax : ay, lo = ax > ay ? ay : ax;
@@ -180,10 +186,16 @@ static inline float atan2p(float y, float x) {
   if (x < 0.0f) r = 3.1415927410125732421875f - r;
   return y < 0.0f ? -r : r;
 }
-static inline float asinp(float v) { return atan2p(v, sqrtf((1.0f - v) * (1.0f + v))); }
-static inline float acosp(float v) { return atan2p(sqrtf((1.0f - v) * (1.0f + v)), v); }
+static inline float asinp(float v) { return g_libm_trig ? asinf(v) : atan2p(v, sqrtf((1.0f - v) * (1.0f + v))); }
+static inline float acosp(float v) { return g_libm_trig ? acosf(v) : atan2p(sqrtf((1.0f - v) * (1.0f + v)), v); }
 // sin / cos of an angle in radians through the 2*pi*u polynomial above
-static inline void sincos_rad(float a, float* s, float* c) { sincos2pi(a * 0.15915493667125701904296875f, s, c); }
+static inline void sincos_rad(float a, float* s, float* c) {
+  if (g_libm_trig) {
+    *s = sinf(a), *c = cosf(a);
+    return;
+  }
+  sincos2pi(a * 0.15915493667125701904296875f, s, c);
+}
 static inline float radiansf(float d) { return d * 0.01745329238474369049072265625f; }
 static inline float degreesf(float r) { return r * 57.295780181884765625f; }
 static inline float modf_glm(float x, float y) { return x - y * floorf(x / y); }  // glm::mod

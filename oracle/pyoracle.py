@@ -226,6 +226,7 @@ class OracleScene:
 
     def make_probes(self, tri_begin=0, tri_end=None, front=True, back=True):
         tri_end = self.n_tris if tri_end is None else tri_end
+        assert 0 <= tri_begin and tri_end <= self.n_tris
         out = np.zeros(max(0, tri_end - tri_begin), dtype=S.ILLUM_SAMPLER_DTYPE)
         lib().orc_make_probes(self.h, C.c_uint64(tri_begin), C.c_uint64(tri_end), int(front), int(back), _p(out))
         return out
@@ -410,6 +411,17 @@ def ref_ie_lib():
     an emulation of the OptiX intrinsics (make -C oracle ref; exists only where /root/reference does).  None when absent."""
     so = os.path.join(_HERE, "_ref", "libie_ref.so")
     return C.CDLL(so) if os.path.exists(so) else None
+
+
+class libm_trig:
+    """Context manager: the oracle's asin / acos / atan2 / sin / cos call libm, as the reference's code does, instead of
+    the portable polynomials (test switch g_libm_trig, oracle_math.h)."""
+
+    def __enter__(self):
+        self.was = lib().orc_set_libm_trig(1)
+
+    def __exit__(self, *a):
+        lib().orc_set_libm_trig(self.was)
 
 
 def ref_env_lib():

@@ -7,6 +7,11 @@
 #pragma once
 #include <cmath>
 #include <cstdio>
+// The reference calls cos / sin / asin / abs / sqrt UNQUALIFIED on floats in places (e.g. SharedCoordinates.cuh:134-146).
+// In CUDA device code those resolve to the float overloads; under g++ they do so only when the C++ <math.h> wrapper has
+// brought std::'s overloads into the global namespace — with <cmath> alone they would silently run in double.
+#include <math.h>
+#include <stdlib.h>
 
 namespace glm {
 struct vec2 {

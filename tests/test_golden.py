@@ -88,6 +88,11 @@ def test_btf_restatement_matches_the_reference_evaluator(orc, scenes):
         assert (err[low] <= 1e-5).mean() >= 0.995, k
         assert (err <= 1e-4).mean() >= 0.99, k
         assert ref[ok].max() > 1.0, k  # real values, not zeros
+        # with the trigonometry taken from libm, as the reference's code takes it, the restatement is the reference's
+        # evaluator bit for bit: table look-ups, index arithmetic, interpolation weights, colour conversion
+        with orc.libm_trig():
+            exact = osc.btf_value_deg(1, q)
+        assert np.array_equal(exact[ok].view(np.uint32), g[f"rgb{k}"][ok]), k
         # when the reference library is present (authoring container) the fixture is what it produces now
         if orc.ref_btf_lib() is not None:
             live = orc.ref_btf_value_deg(btf, osc.btf_beta_angles(1, btf.desc().num_beta), q)

@@ -16,15 +16,17 @@ the keyed Philox draws of the product (instead of the LCG stream), which records
 same-handle surfaces lie in its range (the reference's depend on OptiX's traversal order), and OptiX's traversal.
 
 Bars, with the reason for each residue:
-  * `mixed` and `plants` scenes (the latter with every instance under its own transform): 1 sample x 1 bounce bit-equal;
+  * `mixed` and `plants` scenes (the latter with every instance under its own transform): 1 sample x 1 bounce bit-equal
+    (all six floats of every probe);
     more bounces / samples 1e-6 of the largest channel (the oracle unrolls the reference's recursion into a throughput
     loop and sums samples in a fixed tree);
   * `sss` scene (subsurface ground that is a single sheet, so the BSSRDF probe finds at most one record — where the repo's
     order-independent 4-nearest probe and the reference's traversal-order collection coincide): same bars; pins the
     BSSRDF sampling arithmetic, the exit-point normal map, the record pick drawn from a COPY of the generator
     (BSSDF.cuh:58,77) and the order subsurface path -> ordinary bounce;
-  * `btf` scene: 90 % of the probes to 1e-5, all to 2e-2 — the portable trigonometry of the BTF evaluator (pinned on its
-    own in test_golden.py) at grazing angles, carried through the bounces;
+  * `btf` scene: same bars.  In these test modes the oracle's BTF evaluator takes its angles through libm as the
+    reference's does (`g_libm_trig`); with its portable trigonometry the evaluator alone agrees to 2e-4 of a query's
+    largest channel below 80 degrees (test_golden.py), which multi-bounce BTF paths amplify;
   * ray counts equal in every case (same any-hit and shadow-ray decisions).
 """
 import os
@@ -68,18 +70,13 @@ def test_illumination_programs(orc, S, ref, oscs):
         assert want[:, :3].max() > 0.05, key  # lit
         err = _rel(got[:, :3], want[:, :3])
         equal = (got[:, :3].view(np.uint32) == want[:, :3].view(np.uint32)).all(1).mean()
-        if sc in ("mixed", "plants", "sss"):
-            if (b, n) == (1, 1):
-                assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), key
-            else:
-                assert err.max() <= 1e-6, (key, err.max())
+        if (b, n) == (1, 1):
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), key
         else:
-            assert np.percentile(err.max(1), 90) <= 1e-5 and err.max() <= 2e-2, (key, err.max())
-            if (b, n) == (1, 1):
-                assert equal >= 0.9, (key, equal)
+            assert err.max() <= 1e-6, (key, err.max(), equal)
         ok = ~np.isnan(want[:, 3:]).any(1)
         derr = np.abs(got[ok, 3:] - want[ok, 3:]).max(1)
-        assert np.percentile(derr, 90) <= 1e-5 and derr.max() <= (2e-2 if sc == "btf" else 2e-4), (key, derr.max())
+        assert np.percentile(derr, 90) <= 1e-5 and derr.max() <= 2e-4, (key, derr.max())
         seen.add((sc, e))
         # when the reference library is present (authoring container) the fixture is what it produces now
         if orc.ref_ie_lib() is not None and (b, n) == (1, 1):
