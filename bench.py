@@ -50,8 +50,60 @@ def workload_name(args, n_tris):
 
 
 # ---------------------------------------------------------------------------------------------------------
+class NvmlSampler:
+    """SM clock / throttle reasons / power of one GPU sampled through NVML from a thread of this process every 2 ms: the
+    timed region is shorter than nvidia-smi's start-up plus its 100 ms loop.  Same quantities as the recipe's
+    nvidia-smi line (clocks.sm, clocks.max.sm, power.draw, clocks_event_reasons.*)."""
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
+
+    def __init__(self, gpu_index):
+        import threading
+
+        import pynvml as nv
+        import torch
+        nv.nvmlInit()
+        self.nv = nv
+        try:
+            uuid = str(torch.cuda.get_device_properties(gpu_index).uuid)
+            self.h = nv.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        except Exception:
+            self.h = nv.nvmlDeviceGetHandleByIndex(gpu_index)
+        self.mx = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
+        self.sm, self.pw, self.bits, self.run = [], [], 0, True
+        self.t = threading.Thread(target=self.loop, daemon=True)
+        self.t.start()
+
+    def loop(self):
+        nv = self.nv
+        while self.run:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                self.pw.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+                self.bits |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def stop(self):
+        self.run = False
+        self.t.join(timeout=2)
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "source": "nvml"}
+        if self.sm:
+            out.update(sm_mhz=float(np.median(self.sm)), sm_max_mhz=self.mx, power_w_max=float(max(self.pw)) if self.pw else None,
+                       reasons=sorted(n for b, n in self.REASONS if self.bits & b), samples=len(self.sm))
+        return out
+
+
+def clock_sampler(gpu_index):
+    try:
+        return NvmlSampler(gpu_index)
+    except Exception:
+        return ClockSampler(gpu_index)
+
+
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe); fallback when NVML cannot
+    be used from this process."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -221,7 +273,7 @@ def main():
     for _ in range(max(3, args.warmup)):
         rt.trace_closest_device(rays.data_ptr(), n, hits.data_ptr())
     barrier()
-    clocks = ClockSampler(local)
+    clocks = clock_sampler(local)
     l0 = rt.launch_count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
