@@ -70,3 +70,19 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 txt = open(os.path.join(dp, f), errors="ignore").read()
                 assert "pyoracle" not in txt and "liboracle" not in txt and "oracle_" not in txt, f
+
+
+def test_header_is_plain_c_and_cxx(tmp_path):
+    """include/rtf/rtf.h is the drop-in boundary: it must compile as C99 and as C++11 with nothing but the standard
+    headers (no torch, no CUDA types in the signatures)."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "t.c"
+    src.write_text("#include <rtf/rtf.h>\nint main(void) { rtf_env e; (void)e; return (int)sizeof(rtf_illum_sampler) - 268; }\n")
+    inc = os.path.join(root, "include")
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", inc, "-fsyntax-only", str(src)])
+    subprocess.check_call(["g++", "-std=c++11", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", inc, "-fsyntax-only", "-x", "c++",
+                           str(src)])
+    text = open(os.path.join(inc, "rtf", "rtf.h")).read()
+    includes = re.findall(r"#\s*include\s*[<\"]([^>\"]+)", text)
+    assert set(includes) <= {"stddef.h", "stdint.h"}, includes
