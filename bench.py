@@ -180,6 +180,21 @@ def reference_arm(args):
     dt = time.perf_counter() - t0
     v = n * args.steps / dt / 1e6
     sample = f"first {n} rays of the M1 set per step ({args.steps} steps), all {cores} host threads"
+    # informational: the same rays through the reference's OWN closest-hit path for raw rays — __raygen__PCS /
+    # __closesthit__PCS_R / __miss__PCS_R compiled unmodified for the host (oracle/ref_optix_driver.cpp; the tracer behind
+    # optixTrace is the oracle's), one thread
+    ref_prog = None
+    if orc.ref_pcs_lib() is not None:
+        from raytracerfacility_b200 import structs as S
+        k = min(n, 1 << 18)
+        smp = np.zeros(k, dtype=S.PC_SAMPLE_DTYPE)
+        smp["start"], smp["direction"] = rays[:k, 0:3], rays[:k, 4:7]
+        t0 = time.perf_counter()
+        osc.ref_scan_point_cloud(smp)
+        rdt = time.perf_counter() - t0
+        ref_prog = {"value": k / rdt / 1e6, "unit": UNIT, "cores": 1, "kind": "reference",
+                    "sample": f"first {k} rays through the reference's PointCloudScanning programs on the host, one thread",
+                    "hit_rate": float(smp["hit"].mean())}
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -187,7 +202,7 @@ def reference_arm(args):
         "config": {"workload": workload_name(args, osc.n_tris), "note": "bounded sample: " + sample},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}))
+        "reference_programs": ref_prog, "gpu_launches": 0}))
 
 
 # ---------------------------------------------------------------------------------------------------------
