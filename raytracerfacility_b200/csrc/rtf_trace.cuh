@@ -32,8 +32,11 @@ struct HitRec {
   uint32_t prim;  // 0xFFFFFFFF = miss
 };
 
-constexpr int kSmemStack = 8;    // entries per thread in shared memory
-constexpr int kLocalStack = 56;  // spill entries in local memory (kSmemStack + kLocalStack = kMaxStackDepth)
+#ifndef RTF_SMEM_STACK
+#define RTF_SMEM_STACK 8
+#endif
+constexpr int kSmemStack = RTF_SMEM_STACK;        // entries per thread in shared memory
+constexpr int kLocalStack = 64 - RTF_SMEM_STACK;  // spill entries in local memory (kSmemStack + kLocalStack = kMaxStackDepth)
 constexpr float kBoxSlack = 1.00000095367431640625f;  // 1 + 2^-20 on the current best t
 constexpr float kFarSlack = 2.384185791015625e-07f;   // 2^-22 of the slab operands: near planes pulled in, far pushed out
 constexpr int kTraceBlock = 128;
