@@ -192,7 +192,11 @@ RTF_API int rtf_create(int device, rtf_ctx** out);
 RTF_API int rtf_destroy(rtf_ctx* ctx);
 RTF_API const char* rtf_last_error(void);
 RTF_API const char* rtf_version(void);
-/* Use an externally owned CUDA stream (e.g. torch's current stream) for all work. NULL = own stream. */
+/* Use an externally owned CUDA stream for all work.  NULL = a private non-blocking stream of the context (NOT the legacy
+ * default stream: torch's default stream handle is NULL too — pass a real stream to share one).  Stream contract: every
+ * *_device entry point only ENQUEUES on the context's stream; a caller that reads or overwrites the buffers from another
+ * stream (a collective, a zero-fill) must order the two itself (share the stream, or events).  Host-buffer entry points
+ * block until their results are in host memory. */
 RTF_API int rtf_set_stream(rtf_ctx* ctx, void* cuda_stream);
 /* Number of kernel launches issued by the context so far (bench.py's gpu_launches claim). */
 RTF_API uint64_t rtf_launch_count(rtf_ctx* ctx);
@@ -395,6 +399,9 @@ RTF_API int rtf_scan_point_cloud(rtf_ctx* ctx, const rtf_env* env, rtf_pc_sample
 /* PointCloudScanner::Scan's ray grid (PCS.cpp:70-92) generated on the device; rays
  * [ray_begin, ray_end) of the column*row grid; SoA outputs (host, each nullable):
  * t (float, <0 = miss... see hit), prim_id (0xFFFFFFFF = miss), inst_id. */
+/* column = uint(size.x / distance.x), row = uint(size.y / distance.y) (PCS.cpp:71-75).  RTF_ERR_INVALID unless both
+ * distances are > 0, both sizes >= 0, all finite and the quotients below 2^32 (the reference converts unchecked). */
+RTF_API int rtf_scan_grid_dims(const rtf_scan_grid* grid, uint32_t* column, uint32_t* row);
 RTF_API int rtf_scan_grid_ray_count(const rtf_scan_grid* grid, uint64_t* n_rays);
 RTF_API int rtf_scan_grid_trace(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin, uint64_t ray_end,
                           float* t_out, uint32_t* prim_id_out, uint32_t* inst_id_out);
@@ -438,19 +445,20 @@ enum {
   RTF_DBG_BIN_PARENT = 3,   /* i32 per binary node: internals [0,n-1) then leaves [n-1, 2n-1) */
   RTF_DBG_BIN_BOXES = 4,    /* 6 floats per binary node, same numbering            */
   RTF_DBG_WIDE_NODES = 5,   /* 80 B per wide node                                */
-  RTF_DBG_WIDE_TRIS = 6,    /* 48 B per triangle reference, BVH order            */
+  RTF_DBG_WIDE_TRIS = 6,    /* 48 B per triangle, primitive order                */
   RTF_DBG_FLAT_POS = 7,     /* 9 floats per triangle, commit order               */
   RTF_DBG_FLAT_NRM = 8,     /* 9 floats per triangle, commit order               */
   RTF_DBG_FLAT_INST = 9,    /* u32 per triangle                                  */
   RTF_DBG_SCENE_BOUNDS = 10, /* 6 floats                                         */
   RTF_DBG_REF_TRI = 11,     /* u32 per triangle reference: its triangle          */
-  RTF_DBG_REF_BOX = 12      /* 6 floats per triangle reference: clipped bounds   */
+  RTF_DBG_REF_BOX = 12,     /* 6 floats per triangle reference: clipped bounds   */
+  RTF_DBG_TRI_IDX = 13      /* u32 per triangle reference, BVH (leaf-slot) order: its triangle */
 };
 RTF_API int rtf_debug_size(rtf_ctx* ctx, int what, uint64_t* bytes);
 RTF_API int rtf_debug_read(rtf_ctx* ctx, int what, void* host_out, uint64_t bytes);
 /* Upload a BVH built elsewhere (the oracle, in tests) so traversal can be checked in isolation. */
 RTF_API int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* wide_nodes, uint64_t n_nodes, const void* wide_tris,
-                                 uint64_t n_tris, int depth);
+                                 uint64_t n_tris, const uint32_t* tri_idx, uint64_t n_refs, int depth);
 /* microbenchmarks for the roofline denominators BASELINE.md asks the builder to measure */
 /* Test hook: the BSSRDF spatial probe (SSAnyHit / BSSRDF, BSSDF.cuh:18-89) on its own.  rays: n x
  * {o.xyz, tmin, d.xyz, tmax}; handles: the private component handle each probe is restricted to;

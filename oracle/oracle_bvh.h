@@ -44,6 +44,23 @@ struct Tri48 {
 };
 static_assert(sizeof(Tri48) == 48, "triangle must be 48 B");
 
+// Node meta (8 bytes, little-endian words w0 = meta[0..3], w1 = meta[4..7]):
+//   w0 bits 0..23 = VALID: bit 3s+j set iff slot s is a leaf slot holding more than j triangles (j = 0..2)
+//   w1 bits 0..7  = imask (copy), bits 8..23 = CNT: 2-bit field s = triangles of leaf slot s (0 for inner / empty slots)
+// The triangles of a node's leaf slots lie consecutively from tri_base in slot order, so triangle j of slot s is
+// tri_base + (sum of the CNT fields below s) + j.  The traversal keeps its pending triangles as the 24-bit mask
+// "bit 3s+j" — a fixed position per slot, so the node visit needs no per-child variable shift.
+static inline void node_meta_store(Node80& nd, uint32_t valid, uint32_t cnt16) {
+  const uint32_t w0 = valid & 0xffffffu, w1 = (uint32_t)nd.imask | ((cnt16 & 0xffffu) << 8);
+  for (int k = 0; k < 4; k++) nd.meta[k] = (uint8_t)(w0 >> (8 * k)), nd.meta[4 + k] = (uint8_t)(w1 >> (8 * k));
+}
+static inline uint32_t node_meta_w0(const Node80& nd) {
+  return (uint32_t)nd.meta[0] | ((uint32_t)nd.meta[1] << 8) | ((uint32_t)nd.meta[2] << 16) | ((uint32_t)nd.meta[3] << 24);
+}
+static inline uint32_t node_meta_w1(const Node80& nd) {
+  return (uint32_t)nd.meta[4] | ((uint32_t)nd.meta[5] << 8) | ((uint32_t)nd.meta[6] << 16) | ((uint32_t)nd.meta[7] << 24);
+}
+
 struct Box {
   V3 lo, hi;
 };
@@ -64,7 +81,8 @@ struct BVH {
   std::vector<uint32_t> range_last;
   std::vector<Box> boxes;            // per binary node
   std::vector<Node80> nodes;         // wide nodes, BFS order
-  std::vector<Tri48> tris;           // BVH order
+  std::vector<Tri48> tris;           // one record per triangle, primitive order (shared by all its references)
+  std::vector<uint32_t> tri_idx;     // per triangle reference, BVH (leaf-slot) order: its triangle
   int depth = 0;                     // number of wide levels
 };
 
@@ -302,7 +320,20 @@ static inline void build(BVH& bvh, uint32_t ntri, const float* pos9, const uint3
   }
   // ---- greedy surface-area collapse to 8-wide, breadth first ----
   bvh.nodes.clear();
-  bvh.tris.assign(n, Tri48{});
+  // triangle records: ONE per triangle in primitive order; the leaf slots hold 4-byte indices into it (tri_idx), so a
+  // triangle cut into k references costs 48 + 4k bytes, not 48k (1 M-triangle field: 120 MB of BVH instead of 277 MB)
+  bvh.tris.assign(ntri, Tri48{});
+  for (uint32_t prim = 0; prim < ntri; prim++) {
+    Tri48& T = bvh.tris[prim];
+    const float* p = pos9 + 9 * (size_t)prim;
+    T.v0[0] = p[0], T.v0[1] = p[1], T.v0[2] = p[2];
+    T.v1[0] = p[3], T.v1[1] = p[4], T.v1[2] = p[5];
+    T.v2[0] = p[6], T.v2[1] = p[7], T.v2[2] = p[8];
+    T.prim = prim;
+    T.inst = tri_inst ? tri_inst[prim] : 0;
+    T.flags = 0;
+  }
+  bvh.tri_idx.assign(N, 0u);
   bvh.depth = 0;
   if (N == 0) return;
   auto bin_box = [&](int c) -> const Box& { return bvh.boxes[c >= 0 ? c : ni + ~c]; };
@@ -373,7 +404,7 @@ static inline void build(BVH& bvh, uint32_t ntri, const float* pos9, const uint3
       for (int a = 0; a < 3; a++) node.e[a] = (uint8_t)e[a];
       node.child_base = next_start + (uint32_t)next.size();
       node.tri_base = tri_cursor;
-      uint32_t tri_off = 0;
+      uint32_t tri_off = 0, valid = 0, cnt16 = 0;
       for (int s = 0; s < 8; s++) {
         int i = child_in_slot[s];
         if (i < 0) continue;
@@ -395,27 +426,19 @@ static inline void build(BVH& bvh, uint32_t ntri, const float* pos9, const uint3
         uint32_t cnt = bin_count(c);
         if (c >= 0 && cnt > 3) {
           node.imask |= (uint8_t)(1u << s);
-          node.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
           next.push_back(c);
         } else {
-          uint32_t unary = cnt == 1 ? 1u : (cnt == 2 ? 3u : 7u);
-          node.meta[s] = (uint8_t)((unary << 5) | tri_off);
+          // leaf slot s: `cnt` (1..3) triangles, stored consecutively in slot order; bit 3s+j of the valid mask says
+          // "slot s holds more than j triangles", the 2-bit field s of the count word is cnt (node_meta below)
+          valid |= (cnt == 1 ? 1u : (cnt == 2 ? 3u : 7u)) << (3 * s);
+          cnt16 |= cnt << (2 * s);
           uint32_t first = bin_first(c);
-          for (uint32_t j = 0; j < cnt; j++) {
-            uint32_t prim = bvh.ref_tri[bvh.order[first + j]];
-            Tri48& T = bvh.tris[tri_cursor + tri_off + j];
-            const float* p = pos9 + 9 * (size_t)prim;
-            T.v0[0] = p[0], T.v0[1] = p[1], T.v0[2] = p[2];
-            T.v1[0] = p[3], T.v1[1] = p[4], T.v1[2] = p[5];
-            T.v2[0] = p[6], T.v2[1] = p[7], T.v2[2] = p[8];
-            T.prim = prim;
-            T.inst = tri_inst ? tri_inst[prim] : 0;
-            T.flags = 0;
-          }
+          for (uint32_t j = 0; j < cnt; j++) bvh.tri_idx[tri_cursor + tri_off + j] = bvh.ref_tri[bvh.order[first + j]];
           tri_off += cnt;
         }
       }
       tri_cursor += tri_off;
+      node_meta_store(node, valid, cnt16);
       bvh.nodes.push_back(node);
     }
     level.swap(next);
@@ -489,7 +512,7 @@ static inline bool intersect_tri(const Ray& ray, const RayPrep& rp, const Tri48&
 static inline Hit trace_brute(const BVH& bvh, const Ray& ray) {
   Hit best{ray.tmax, 0.0f, 0.0f, 0xFFFFFFFFu};
   RayPrep rp = prep_ray(ray.d);
-  for (uint32_t i = 0; i < bvh.nref; i++) intersect_tri(ray, rp, bvh.tris[i], best);
+  for (uint32_t i = 0; i < bvh.n; i++) intersect_tri(ray, rp, bvh.tris[i], best);
   return best;
 }
 
@@ -502,6 +525,8 @@ struct NoFilter {
   bool operator()(const Tri48&, const Hit&) const { return true; }
 };
 
+// Sign bit of an IEEE result; a NaN counts as non-negative (the GPU's arithmetic returns the canonical NaN 0x7fffffff).
+static inline bool sign_neg(float d) { return d != d ? false : std::signbit(d); }
 static inline float safe_dir(float d) {
   const float ooeps = u2f(0x17800000u);  // 2^-80
   return fabsf(d) < ooeps ? copysignf(ooeps, d) : d;
@@ -552,10 +577,10 @@ static inline Hit trace(const BVH& bvh, const Ray& ray, TraceStats* stats = null
         oof[a] = fmaf(m, FAR_SLACK, o) - sc[a];
       }
       const float best_s = best.t * SLACK;
-      uint32_t hitmask = 0;
+      // A child is entered iff none of (tfar - tnear), (best_s - tnear), (tfar - tmin) is negative — the slab test
+      // max(tnear, tmin) <= min(tfar, best_s) written as three sign bits (the GPU gathers them with funnel shifts).
+      uint32_t hit8 = 0;
       for (int s = 0; s < 8; s++) {
-        const uint32_t meta = nd.meta[s];
-        if (meta == 0) continue;
         float tn[3], tf[3];
         for (int a = 0; a < 3; a++) {
           const float qn = u2f(0x3F800000u | ((uint32_t)(neg[a] ? nd.qhi[a][s] : nd.qlo[a][s]) << 8));
@@ -563,24 +588,31 @@ static inline Hit trace(const BVH& bvh, const Ray& ray, TraceStats* stats = null
           tn[a] = fmaf(qn, sc[a], oo[a]);
           tf[a] = fmaf(qf, sc[a], oof[a]);
         }
-        const float tnear = fmaxf(fmaxf(tn[0], tn[1]), fmaxf(tn[2], ray.tmin));
-        const float tfar = fminf(fminf(tf[0], tf[1]), fminf(tf[2], best_s));
-        if (tnear <= tfar) {
-          const bool inner = (meta & (meta << 1) & 0x10u) != 0;
-          const uint32_t bit_index = (meta ^ (inner ? oct_inv : 0u)) & 0x1fu;
-          const uint32_t child_bits = (meta >> 5) & 7u;
-          hitmask |= child_bits << bit_index;
-        }
+        const float tnear = fmaxf(fmaxf(tn[0], tn[1]), tn[2]);
+        const float tfar = fminf(fminf(tf[0], tf[1]), tf[2]);
+        if (!(sign_neg(tfar - tnear) || sign_neg(best_s - tnear) || sign_neg(tfar - ray.tmin))) hit8 |= 1u << s;
       }
+      // inner children: hit bit of slot s moves to priority (s ^ oct_inv); leaf slots: bits 3s..3s+2 of the valid mask
+      const uint32_t w0 = node_meta_w0(nd), w1 = node_meta_w1(nd);
+      const uint32_t inner = hit8 & nd.imask;
+      uint32_t perm = 0;
+      for (int s = 0; s < 8; s++)
+        if (inner & (1u << s)) perm |= 1u << (s ^ oct_inv);
+      uint32_t spread = 0;
+      for (int s = 0; s < 8; s++)
+        if (hit8 & (1u << s)) spread |= 7u << (3 * s);
       cur.base = nd.child_base;
-      cur.bits = (hitmask & 0xff000000u) | nd.imask;
+      cur.bits = (perm << 24) | w1;
       tg.base = nd.tri_base;
-      tg.bits = hitmask & 0x00ffffffu;
+      tg.bits = spread & w0;
     }
     while (tg.bits) {
-      const uint32_t ti = 31u - (uint32_t)__builtin_clz(tg.bits);
-      tg.bits &= ~(1u << ti);
-      const Tri48& tri = bvh.tris[tg.base + ti];
+      const uint32_t pos = 31u - (uint32_t)__builtin_clz(tg.bits);
+      tg.bits &= ~(1u << pos);
+      const uint32_t ts = pos / 3u, tj = pos - 3u * ts;
+      uint32_t before = 0;  // triangles of the leaf slots below ts (2-bit count fields of cur.bits, bits 8..23)
+      for (uint32_t s = 0; s < ts; s++) before += (cur.bits >> (8 + 2 * s)) & 3u;
+      const Tri48& tri = bvh.tris[bvh.tri_idx[tg.base + before + tj]];
       if (stats) stats->tris++;
       Hit cand = best;
       if (intersect_tri(ray, rp, tri, cand) && filter(tri, cand)) {

@@ -72,8 +72,7 @@ int rtf_destroy(rtf_ctx* ctx) {
                     &ctx->ba.children, &ctx->ba.parent, &ctx->ba.range, &ctx->ba.boxes, &ctx->ba.flags,
                     &ctx->ba.scene_bounds, &ctx->ba.keys_alt, &ctx->ba.ids_alt, &ctx->ba.ref_cnt, &ctx->ba.ref_first,
                     &ctx->ba.ref_tri, &ctx->ba.ref_box, &ctx->ba.scan_state, &ctx->ba.sort_hist, &ctx->ba.sort_status, &ctx->ba.level_a,
-                    &ctx->ba.level_b, &ctx->ba.cnt_int, &ctx->ba.cnt_tri, &ctx->ba.scan_int, &ctx->ba.scan_tri,
-                    &ctx->ba.stash, &ctx->ws.ray_a[0], &ctx->ws.ray_a[1], &ctx->ws.ray_b[0], &ctx->ws.ray_b[1],
+                    &ctx->ba.level_b, &ctx->ba.collapse_state, &ctx->d_tri_idx, &ctx->ws.ray_a[0], &ctx->ws.ray_a[1], &ctx->ws.ray_b[0], &ctx->ws.ray_b[1],
                     &ctx->ws.hits, &ctx->ws.counters, &ctx->ws.thr,
                     &ctx->ws.acc, &ctx->ws.dir0w, &ctx->ws.first_n, &ctx->ws.first_a, &ctx->ws.first_p,
                     &ctx->ws.sort_keys, &ctx->ws.sort_keys_alt, &ctx->ws.sort_vals, &ctx->ws.sort_vals_alt,
@@ -165,7 +164,7 @@ int rtf_set_geometry_instanced(rtf_ctx* ctx, uint64_t handle, const void* vertic
   std::vector<rtf_vertex> packed(n_vertices);
   for (size_t i = 0; i < n_vertices; i++) memcpy(&packed[i], (const char*)vertices + i * stride, sizeof(rtf_vertex));
   ctx->geom_dirty = true, ctx->topo_dirty = true;
-  if (ctx->geoms.count(handle)) ctx->ready = false;  // the committed scene may point at the arrays re-baked below
+  if (ctx->geoms.count(handle)) ctx->ready = false, ctx->bvh_ok = false;  // the committed scene may point at the arrays re-baked below
   Geometry& g = ctx->geoms[handle];
   g.verts.clear(), g.tris.clear();
   g.version = version;
@@ -187,7 +186,7 @@ int rtf_set_geometry_skinned(rtf_ctx* ctx, uint64_t handle, const void* skinned_
       return RTF_ERR_INVALID;
     }
   ctx->geom_dirty = true, ctx->topo_dirty = true;
-  if (ctx->geoms.count(handle)) ctx->ready = false;  // the committed scene may point at the arrays re-baked below
+  if (ctx->geoms.count(handle)) ctx->ready = false, ctx->bvh_ok = false;  // the committed scene may point at the arrays re-baked below
   Geometry& g = ctx->geoms[handle];
   g.verts.clear(), g.tris.clear();
   g.version = version;
@@ -246,7 +245,7 @@ int rtf_remove_geometry(rtf_ctx* ctx, uint64_t handle) {
   it->second.d_verts.release(), it->second.d_tris.release();
   ctx->geoms.erase(it);
   ctx->geom_dirty = true, ctx->topo_dirty = true;
-  ctx->ready = false;  // the committed scene may point at the released arrays
+  ctx->ready = false, ctx->bvh_ok = false;  // the committed scene may point at the released arrays
   return RTF_OK;
 }
 int rtf_remove_material(rtf_ctx* ctx, uint64_t handle) {
@@ -271,15 +270,15 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   // Scene-sync diffing: nothing changed -> nothing to do (the reference only calls BuildIAS when an update flag was
   // raised, RayTracerLayer.cpp:394-400); only material-side tables changed -> they are re-resolved below and the BVH
   // stays, unless an instance's "may ignore hits" class changed (it is baked into the triangle records).
-  const bool was_ready = ctx->ready && ctx->morton_bits == morton_bits && ctx->n_tris > 0;
-  if (was_ready && !ctx->geom_dirty && !ctx->mat_dirty) {
+  const bool was_ready = (ctx->ready || ctx->bvh_ok) && ctx->morton_bits == morton_bits && ctx->n_tris > 0;
+  if (ctx->ready && was_ready && !ctx->geom_dirty && !ctx->mat_dirty) {
     ctx->commits_skipped++;
     return RTF_OK;
   }
   const bool keep_bvh_if_possible = was_ready && !ctx->geom_dirty;
   const bool refit_if_possible = was_ready && ctx->geom_dirty && !ctx->topo_dirty && ctx->refit && ctx->n_refs > 0;
   const uint32_t old_tris = ctx->n_tris;
-  ctx->ready = false;
+  ctx->ready = false, ctx->bvh_ok = false;
   int rc;
   cudaStream_t st = ctx->stream;
   // materials -> dense table
@@ -381,7 +380,7 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   ctx->geom_dirty = false, ctx->mat_dirty = false, ctx->topo_dirty = false;
   ctx->morton_bits = morton_bits;
   DevScene& s = ctx->scene;
-  s.nodes = ctx->d_nodes.as<uint4>(), s.tris = ctx->d_tris48.as<float4>();
+  s.nodes = ctx->d_nodes.as<uint4>(), s.tris = ctx->d_tris48.as<float4>(), s.tri_idx = ctx->d_tri_idx.as<uint32_t>();
   s.pos9 = ctx->d_pos9.as<float>(), s.nrm9 = ctx->d_nrm9.as<float>(), s.tri_inst = ctx->d_tri_inst.as<uint32_t>();
   s.mats = ctx->d_mats.as<DevMaterial>(), s.inst_alpha = ctx->d_inst_alpha.as<float>();
   s.btfs = ctx->d_btfs.as<DevBTF>(), s.env_faces = env_faces;
@@ -393,7 +392,8 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   for (const DevMaterial& dm : mats)
     if (dm.m.material_type != RTF_MAT_COMPRESSED_BTF && dm.m.subsurface_factor > 0.0f && dm.m.subsurface_radius[0] > 0.0f)
       s.has_sss = 1;
-  ctx->ready = true;
+  ctx->ready = true, ctx->bvh_ok = true;
+  ctx->epoch++;
   return RTF_OK;
 }
 int rtf_commit_stats(rtf_ctx* ctx, uint64_t* out5) {
@@ -591,14 +591,35 @@ int rtf_scan_point_cloud(rtf_ctx* ctx, const rtf_env* env, rtf_pc_sample* sample
   RTF_CUDA(cudaStreamSynchronize(ctx->stream));
   return RTF_OK;
 }
+// column = uint(size.x / distance.x), row = uint(size.y / distance.y) (PointCloudScanner.cpp:71-75); the float -> unsigned
+// conversion is only defined for finite quotients in [0, 2^32)
+int rtf_scan_grid_dims(const rtf_scan_grid* g, uint32_t* column, uint32_t* row) {
+  if (!g || !column || !row) return RTF_ERR_INVALID;
+  for (int k = 0; k < 2; k++) {
+    const float q = g->size[k] / g->distance[k];
+    if (!(g->distance[k] > 0.0f) || !(g->size[k] >= 0.0f) || !(q < 4294967296.0f)) {
+      set_error("scan grid: distance must be > 0, size >= 0, both finite, and size / distance < 2^32");
+      return RTF_ERR_INVALID;
+    }
+  }
+  *column = (uint32_t)(g->size[0] / g->distance[0]);
+  *row = (uint32_t)(g->size[1] / g->distance[1]);
+  return RTF_OK;
+}
 int rtf_scan_grid_ray_count(const rtf_scan_grid* g, uint64_t* n) {
   if (!g || !n) return RTF_ERR_INVALID;
-  *n = (uint64_t)(uint32_t)(g->size[0] / g->distance[0]) * (uint64_t)(uint32_t)(g->size[1] / g->distance[1]);
+  uint32_t column = 0, row = 0;
+  int rc = rtf_scan_grid_dims(g, &column, &row);
+  if (rc) return rc;
+  *n = (uint64_t)column * (uint64_t)row;
   return RTF_OK;
 }
 int rtf_scan_grid_trace_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t b, uint64_t e, float* dev_t, uint32_t* dev_prim) {
   CHECK_CTX(ctx);
-  if (!grid) return RTF_ERR_INVALID;
+  if (!grid || (!dev_t && !dev_prim)) {
+    set_error("rtf_scan_grid_trace_device: null grid, or no output array");
+    return RTF_ERR_INVALID;
+  }
   return scan_grid_device(ctx, grid, b, e, dev_t, dev_prim, nullptr);
 }
 int rtf_scan_grid_trace(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t b, uint64_t e, float* t_out, uint32_t* prim_out,
@@ -829,13 +850,6 @@ int rtf_camera_set(rtf_camera* cam, const float position[3], const float q[4]) {
   return RTF_OK;
 }
 
-struct CamLast {
-  rtf_env env;
-  rtf_ray_props rp;
-  bool valid = false;
-};
-static std::map<rtf_ctx*, CamLast> g_cam_last;  // m_cameraRenderingLaunchParams.m_rayTracerProperties, RayTracer.cu:259-266
-
 static int render_camera_rows(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, int row_begin,
                               int row_end) {
   if (!env || !cam || !rp) return RTF_ERR_INVALID;
@@ -846,12 +860,14 @@ static int render_camera_rows(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam,
     set_error("rtf_render_camera_rows: bad row range");
     return RTF_ERR_INVALID;
   }
-  CamLast& last = g_cam_last[ctx];
   bool changed = p.modified != 0;
   p.modified = 0;
-  if (!last.valid || memcmp(&last.env, env, sizeof(rtf_env)) != 0) last.env = *env, changed = true;
-  if (!last.valid || last.rp.bounces != rp->bounces || last.rp.samples != rp->samples) last.rp = *rp, changed = true;
-  last.valid = true;
+  if (!ctx->cam_last_valid || memcmp(&ctx->cam_last_env, env, sizeof(rtf_env)) != 0) ctx->cam_last_env = *env, changed = true;
+  if (!ctx->cam_last_valid || ctx->cam_last_rp.bounces != rp->bounces || ctx->cam_last_rp.samples != rp->samples)
+    ctx->cam_last_rp = *rp, changed = true;
+  // m_requireUpdate: BuildIAS / an SBT update restarts the accumulation (RayTracer.cu:254, RayTracerLayer.cpp:382-389)
+  if (ctx->cam_last_epoch != ctx->epoch) ctx->cam_last_epoch = ctx->epoch, changed = true;
+  ctx->cam_last_valid = true;
   if (!p.accumulate || changed) p.frame_id = 0;  // RayTracer.cu:266-269
   // the launch sees the frame id before the increment (RayTracer.cu:349-352)
   int rc = render_camera_device(ctx, env, cam, rp, (uint64_t)row_begin * p.width, (uint64_t)row_end * p.width);
@@ -898,7 +914,8 @@ static const void* dbg_ptr(rtf_ctx* c, int what, uint64_t* bytes) {
     case RTF_DBG_BIN_PARENT: *bytes = (n ? 2 * n - 1 : 0) * 4; return c->ba.parent.p;
     case RTF_DBG_BIN_BOXES: *bytes = (n ? 2 * n - 1 : 0) * 24; return c->ba.boxes.p;
     case RTF_DBG_WIDE_NODES: *bytes = (uint64_t)c->n_nodes * 80; return c->d_nodes.p;
-    case RTF_DBG_WIDE_TRIS: *bytes = n * 48; return c->d_tris48.p;
+    case RTF_DBG_WIDE_TRIS: *bytes = nt * 48; return c->d_tris48.p;
+    case RTF_DBG_TRI_IDX: *bytes = n * 4; return c->d_tri_idx.p;
     case RTF_DBG_FLAT_POS: *bytes = nt * 36; return c->d_pos9.p;
     case RTF_DBG_FLAT_NRM: *bytes = nt * 36; return c->d_nrm9.p;
     case RTF_DBG_FLAT_INST: *bytes = nt * 4; return c->d_tri_inst.p;
@@ -923,19 +940,24 @@ int rtf_debug_read(rtf_ctx* ctx, int what, void* out, uint64_t bytes) {
   }
   return RTF_OK;
 }
-int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* nodes, uint64_t n_nodes, const void* tris, uint64_t n_tris, int depth) {
+int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* nodes, uint64_t n_nodes, const void* tris, uint64_t n_tris,
+                         const uint32_t* tri_idx, uint64_t n_refs, int depth) {
   CHECK_CTX(ctx);
-  if (!nodes || !tris || depth > kMaxStackDepth) return RTF_ERR_INVALID;
+  if (!nodes || !tris || !tri_idx || depth > kMaxStackDepth) return RTF_ERR_INVALID;
   int rc;
   RTF_CUDA(cudaStreamSynchronize(ctx->stream));
-  if ((rc = ctx->d_nodes.reserve(n_nodes * 80)) || (rc = ctx->d_tris48.reserve(n_tris * 48))) return rc;
+  if ((rc = ctx->d_nodes.reserve(n_nodes * 80)) || (rc = ctx->d_tris48.reserve(n_tris * 48)) ||
+      (rc = ctx->d_tri_idx.reserve(n_refs * 4)))
+    return rc;
   RTF_CUDA(cudaMemcpy(ctx->d_nodes.p, nodes, n_nodes * 80, cudaMemcpyHostToDevice));
   RTF_CUDA(cudaMemcpy(ctx->d_tris48.p, tris, n_tris * 48, cudaMemcpyHostToDevice));
+  RTF_CUDA(cudaMemcpy(ctx->d_tri_idx.p, tri_idx, n_refs * 4, cudaMemcpyHostToDevice));
   ctx->scene.nodes = ctx->d_nodes.as<uint4>(), ctx->scene.tris = ctx->d_tris48.as<float4>();
+  ctx->scene.tri_idx = ctx->d_tri_idx.as<uint32_t>();
   ctx->n_nodes = (uint32_t)n_nodes, ctx->depth = depth;
   ctx->scene.n_nodes = (uint32_t)n_nodes;
   if (!ctx->ready) ctx->n_tris = (uint32_t)n_tris, ctx->scene.n_tris = (uint32_t)n_tris;
-  ctx->n_refs = (uint32_t)n_tris;
+  ctx->n_refs = (uint32_t)n_refs;
   ctx->ready = true;
   return RTF_OK;
 }

@@ -309,7 +309,14 @@ __global__ void k_refit(const float* __restrict__ ref_box, const uint32_t* __res
   }
 }
 
-// ---- 7. collapse to 8-wide, one breadth-first level per launch pair ---------------------------------
+// ---- 7. collapse to 8-wide: ONE persistent cooperative kernel for all breadth-first levels ----------------------------
+// The node layout is breadth first (a node's internal children are consecutive in the next level, its triangles
+// consecutive in the index array), so a level needs the exclusive prefix sums of its nodes' child and triangle counts.
+// Each block takes 128-node tiles of the current level in ticket order: greedy expansion + slot assignment per node
+// (registers only), a block scan, a decoupled look-back over the tile descriptors of the level (Merrill & Garland), then
+// the nodes are encoded and the next level's roots written — one pass per level, no intermediate arrays.  Levels are
+// separated by a grid barrier; the level sizes never leave the device (the previous version ran four launches per level
+// and read two counters back to the host after each: 2.5 ms of a 4.8 ms build were that).
 struct CollapseArgs {
   const int2* children;
   const uint2* range;
@@ -323,15 +330,31 @@ __device__ __forceinline__ Box3 load_box(const float* __restrict__ boxes, int ni
   return r;
 }
 constexpr int kEmptySlot = 0x7fffffff;
+constexpr int kCollapseBlock = 128;
+constexpr int kCollapseLevels = kMaxStackDepth + 2;
+struct CollapseLevel {
+  uint32_t n, start, tri_cursor, desc_base;
+};
+__device__ __forceinline__ CollapseLevel level_load(const CollapseLevel* p) {  // written by another block: volatile reads
+  const volatile uint32_t* v = (const volatile uint32_t*)p;
+  CollapseLevel l;
+  l.n = v[0], l.start = v[1], l.tri_cursor = v[2], l.desc_base = v[3];
+  return l;
+}
+__device__ __forceinline__ void level_store(CollapseLevel* p, const CollapseLevel& l) {
+  volatile uint32_t* v = (volatile uint32_t*)p;
+  v[0] = l.n, v[1] = l.start, v[2] = l.tri_cursor, v[3] = l.desc_base;
+}
+struct CollapseState {  // device memory, zeroed before the launch except level[0]
+  CollapseLevel level[kCollapseLevels];
+  uint32_t ticket[kCollapseLevels];
+  uint32_t depth, n_nodes, n_tris, error;
+};
 
-// Pass A: greedy expansion by largest half-area + greedy octant slot assignment; stash the binary child
-// of every slot and count internal children / leaf triangles.
-__global__ void k_collapse_plan(CollapseArgs a, const int* __restrict__ level, uint32_t level_n, int* __restrict__ stash,
-                                uint32_t* __restrict__ cnt_int, uint32_t* __restrict__ cnt_tri) {
-  const uint32_t li = blockIdx.x * blockDim.x + threadIdx.x;
-  if (li >= level_n) return;
+// Greedy expansion by largest half-area + greedy octant slot assignment of binary subtree R: the binary child of every
+// slot (kEmptySlot: none), the number of internal children and of leaf triangles.
+__device__ __forceinline__ void collapse_plan(const CollapseArgs& a, int R, int (&slot_child)[8], uint32_t& ci, uint32_t& ct) {
   const int ni = a.n - 1;
-  const int R = level[li];
   int ch[8];
   int nc;
   if (R < 0) {
@@ -377,7 +400,7 @@ __global__ void k_collapse_plan(CollapseArgs a, const int* __restrict__ level, u
     slot_of[bi] = bs;
     child_in_slot[bs] = bi;
   }
-  uint32_t ci = 0, ct = 0;
+  ci = 0, ct = 0;
   for (int s = 0; s < 8; s++) {
     const int i = child_in_slot[s];
     int c = kEmptySlot;
@@ -389,23 +412,16 @@ __global__ void k_collapse_plan(CollapseArgs a, const int* __restrict__ level, u
       else
         ct += cnt;
     }
-    stash[8 * (size_t)li + s] = c;
+    slot_child[s] = c;
   }
-  cnt_int[li] = ci;
-  cnt_tri[li] = ct;
 }
 
-// Pass B: encode the node, emit its triangles and the next level's roots.
-__global__ void k_collapse_emit(CollapseArgs a, const int* __restrict__ level, uint32_t level_n, const int* __restrict__ stash,
-                                const uint32_t* __restrict__ scan_int, const uint32_t* __restrict__ scan_tri,
-                                uint32_t level_start, uint32_t next_start, uint32_t tri_cursor, int* __restrict__ next_level,
-                                Node80* __restrict__ nodes, Tri48* __restrict__ tris, const float* __restrict__ pos9,
-                                const uint32_t* __restrict__ tri_inst, const uint32_t* __restrict__ sorted_ids,
-                                const uint32_t* __restrict__ ref_tri, const float* __restrict__ inst_alpha) {
-  const uint32_t li = blockIdx.x * blockDim.x + threadIdx.x;
-  if (li >= level_n) return;
+// Encode node R (80 B), write its internal children into the next level and, per triangle slot, the SORTED POSITION of
+// the reference it holds (k_tri_index turns those into triangle ids with coalesced accesses).
+__device__ __forceinline__ void collapse_emit(const CollapseArgs& a, int R, const int (&slot_child)[8], uint32_t child_base,
+                                              uint32_t tri_base, int* __restrict__ next_level_at, Node80* __restrict__ out,
+                                              uint32_t* __restrict__ slot_pos) {
   const int ni = a.n - 1;
-  const int R = level[li];
   const Box3 nb = load_box(a.boxes, ni, R);
   Node80 node;
   node.p[0] = nb.lo.x, node.p[1] = nb.lo.y, node.p[2] = nb.lo.z;
@@ -413,13 +429,11 @@ __global__ void k_collapse_emit(CollapseArgs a, const int* __restrict__ level, u
   const uint32_t e[3] = {quant_exponent(ext.x), quant_exponent(ext.y), quant_exponent(ext.z)};
   node.e[0] = (uint8_t)e[0], node.e[1] = (uint8_t)e[1], node.e[2] = (uint8_t)e[2];
   node.imask = 0;
-  const uint32_t child_off = scan_int[li];
-  node.child_base = next_start + child_off;
-  node.tri_base = tri_cursor + scan_tri[li];
-  uint32_t tri_off = 0, int_off = 0;
+  node.child_base = child_base;
+  node.tri_base = tri_base;
+  uint32_t tri_off = 0, int_off = 0, valid = 0, cnt16 = 0;
   for (int s = 0; s < 8; s++) {
-    const int c = stash[8 * (size_t)li + s];
-    node.meta[s] = 0;
+    const int c = slot_child[s];
     node.qlo[0][s] = node.qlo[1][s] = node.qlo[2][s] = 0;
     node.qhi[0][s] = node.qhi[1][s] = node.qhi[2][s] = 0;
     if (c == kEmptySlot) continue;
@@ -430,29 +444,153 @@ __global__ void k_collapse_emit(CollapseArgs a, const int* __restrict__ level, u
     const uint32_t cnt = c >= 0 ? (a.range[c].y - a.range[c].x + 1u) : 1u;
     if (c >= 0 && cnt > 3u) {
       node.imask |= (uint8_t)(1u << s);
-      node.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
-      next_level[child_off + int_off] = c;
-      int_off++;
+      next_level_at[int_off++] = c;
     } else {
-      const uint32_t unary = cnt == 1u ? 1u : (cnt == 2u ? 3u : 7u);
-      node.meta[s] = (uint8_t)((unary << 5) | tri_off);
+      valid |= (cnt == 1u ? 1u : (cnt == 2u ? 3u : 7u)) << (3 * s);
+      cnt16 |= cnt << (2 * s);
       const uint32_t first = c >= 0 ? a.range[c].x : (uint32_t)~c;
-      for (uint32_t j = 0; j < cnt; j++) {
-        const uint32_t prim = ref_tri[sorted_ids[first + j]];
-        const float* p = pos9 + 9 * (size_t)prim;
-        Tri48 T;
-        T.v0[0] = p[0], T.v0[1] = p[1], T.v0[2] = p[2];
-        T.v1[0] = p[3], T.v1[1] = p[4], T.v1[2] = p[5];
-        T.v2[0] = p[6], T.v2[1] = p[7], T.v2[2] = p[8];
-        T.prim = prim;
-        T.inst = tri_inst[prim];
-        T.flags = (inst_alpha && inst_alpha[T.inst] < 1.0f) ? (uint32_t)TRI_FLAG_ALPHA : 0u;
-        tris[node.tri_base + tri_off + j] = T;
-      }
+      for (uint32_t j = 0; j < cnt; j++) slot_pos[tri_base + tri_off + j] = first + j;
       tri_off += cnt;
     }
   }
-  nodes[level_start + li] = node;
+  node_meta_store(node, valid, cnt16);
+  *out = node;
+}
+
+// Tile descriptor of the look-back: bits 62..63 = state (1 aggregate, 2 inclusive prefix), bits 32..61 = internal
+// children, bits 0..31 = triangles (references <= 2^31, nodes < 2^30: the fields cannot carry into each other).
+__global__ void __launch_bounds__(kCollapseBlock)
+    k_collapse(CollapseArgs a, CollapseState* cs, unsigned long long* desc_all, int* lv_a, int* lv_b, Node80* __restrict__ nodes,
+               uint32_t* __restrict__ slot_pos, uint32_t max_nodes, uint32_t max_level, unsigned* gbar) {
+  __shared__ uint32_t s_tile;
+  __shared__ unsigned long long s_warp[kCollapseBlock / 32], s_prefix;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int L = 0;
+  for (;; L++) {
+    if (L >= kCollapseLevels - 1) {
+      if (blockIdx.x == 0 && threadIdx.x == 0) cs->error = 2u;  // deeper than the traversal stack can hold
+      break;
+    }
+    const CollapseLevel lv = level_load(&cs->level[L]);
+    if (lv.n == 0) break;
+    if ((size_t)lv.start + lv.n > max_nodes || lv.n > max_level) {
+      if (blockIdx.x == 0 && threadIdx.x == 0) cs->error = 1u;  // node budget exceeded (same decision in every block)
+      break;
+    }
+    const int* level = (L & 1) ? lv_b : lv_a;
+    int* next = (L & 1) ? lv_a : lv_b;
+    volatile unsigned long long* desc = desc_all + lv.desc_base;
+    const uint32_t tiles = (lv.n + kCollapseBlock - 1) / kCollapseBlock;
+    for (;;) {
+      __syncthreads();
+      if (threadIdx.x == 0) s_tile = atomicAdd(&cs->ticket[L], 1u);
+      __syncthreads();
+      const uint32_t tile = s_tile;
+      if (tile >= tiles) break;
+      const uint32_t li = tile * kCollapseBlock + threadIdx.x;
+      const bool active = li < lv.n;
+      int slot_child[8];
+      uint32_t ci = 0, ct = 0;
+      int R = 0;
+      if (active) {
+        R = level[li];
+        collapse_plan(a, R, slot_child, ci, ct);
+      }
+      const unsigned long long mine = ((unsigned long long)ci << 32) | ct;
+      unsigned long long incl = mine;
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += t;
+      }
+      if (lane == 31) s_warp[warp] = incl;
+      __syncthreads();
+      unsigned long long warp_off = 0, total = 0;
+#pragma unroll
+      for (int w = 0; w < kCollapseBlock / 32; w++) {
+        if (w < warp) warp_off += s_warp[w];
+        total += s_warp[w];
+      }
+      if (warp == 0) {
+        unsigned long long prefix = 0;
+        if (tile == 0) {
+          if (lane == 0) desc[0] = (2ull << 62) | total;
+        } else {
+          if (lane == 0) desc[tile] = (1ull << 62) | total;
+          int look = (int)tile - 1;
+          for (;;) {
+            const int idx = look - lane;
+            unsigned long long d = idx >= 0 ? desc[idx] : (2ull << 62);
+            while (__any_sync(0xffffffffu, (d >> 62) == 0ull)) d = idx >= 0 ? desc[idx] : (2ull << 62);
+            const unsigned done = __ballot_sync(0xffffffffu, (d >> 62) == 2ull);
+            const int first_done = done ? __ffs((int)done) - 1 : 32;
+            unsigned long long contrib = lane <= first_done ? (d & 0x3fffffffffffffffull) : 0ull;
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, off);
+            prefix += contrib;
+            if (done) break;
+            look -= 32;
+          }
+          if (lane == 0) desc[tile] = (2ull << 62) | (prefix + total);
+        }
+        if (lane == 0) {
+          s_prefix = prefix;
+          if (tile == tiles - 1) {  // the level's totals: the next level's size and cursors
+            const unsigned long long all = prefix + total;
+            CollapseLevel nx;
+            nx.n = (uint32_t)(all >> 32), nx.start = lv.start + lv.n, nx.tri_cursor = lv.tri_cursor + (uint32_t)all;
+            nx.desc_base = lv.desc_base + tiles;
+            level_store(&cs->level[L + 1], nx);
+          }
+        }
+      }
+      __syncthreads();
+      if (active) {
+        const unsigned long long excl = s_prefix + warp_off + (incl - mine);
+        const uint32_t child_off = (uint32_t)(excl >> 32), tri_off = (uint32_t)excl;
+        collapse_emit(a, R, slot_child, lv.start + lv.n + child_off, lv.tri_cursor + tri_off, next + child_off,
+                      nodes + lv.start + li, slot_pos);
+      }
+    }
+    // grid barrier between levels (all blocks are resident: cooperative launch): generation counter
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned target = (unsigned)(L + 1) * gridDim.x;
+      atomicAdd(gbar, 1u);
+      while (*(volatile unsigned*)gbar < target) {
+      }
+      __threadfence();
+    }
+    __syncthreads();
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const CollapseLevel lv = level_load(&cs->level[L]);
+    cs->depth = (uint32_t)L, cs->n_nodes = lv.start, cs->n_tris = lv.tri_cursor;
+  }
+}
+
+// Triangle ids of the leaf slots (4 B per reference, BVH order) from the sorted positions the collapse left there.
+__global__ void k_tri_index(uint32_t n, const uint32_t* __restrict__ sorted_ids, const uint32_t* __restrict__ ref_tri,
+                            uint32_t* __restrict__ slot_pos_to_prim) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  slot_pos_to_prim[i] = ref_tri[sorted_ids[slot_pos_to_prim[i]]];
+}
+// One 48 B record per TRIANGLE in primitive order, shared by all references of the triangle (rtf_bvh.cuh).
+__global__ void k_tri_records(uint32_t nt, const float* __restrict__ pos9, const uint32_t* __restrict__ tri_inst,
+                              const float* __restrict__ inst_alpha, Tri48* __restrict__ tris) {
+  const uint32_t prim = blockIdx.x * blockDim.x + threadIdx.x;
+  if (prim >= nt) return;
+  const float* p = pos9 + 9 * (size_t)prim;
+  Tri48 T;
+  T.v0[0] = p[0], T.v0[1] = p[1], T.v0[2] = p[2];
+  T.v1[0] = p[3], T.v1[1] = p[4], T.v1[2] = p[5];
+  T.v2[0] = p[6], T.v2[1] = p[7], T.v2[2] = p[8];
+  T.prim = prim;
+  T.inst = tri_inst[prim];
+  T.flags = (inst_alpha && inst_alpha[T.inst] < 1.0f) ? (uint32_t)TRI_FLAG_ALPHA : 0u;
+  tris[prim] = T;
 }
 
 static void mark(rtf_ctx* ctx, int k) {
@@ -504,7 +642,7 @@ int build_bvh(rtf_ctx* ctx, int bits) {
   float* fb = ba.scene_bounds.as<float>() + 8;
   mark(ctx, 1);
   LAUNCH(ctx, k_bounds_init, 1, 32, 0, ob);
-  LAUNCH(ctx, k_bounds, min(div_up(nt, 256), 148u * 8u), 256, 0, ctx->d_pos9.as<float>(), nt, ob);
+  LAUNCH(ctx, k_bounds, min(div_up(nt, 256), (unsigned)ctx->sm_count * 8u), 256, 0, ctx->d_pos9.as<float>(), nt, ob);
   LAUNCH(ctx, k_bounds_finish, 1, 32, 0, ob, fb);
   // triangle references: count -> scan -> emit (one reference per triangle when presplit <= 1)
   if ((rc = ba.ref_cnt.reserve(4 * (size_t)nt))) return rc;
@@ -553,72 +691,74 @@ int build_bvh(rtf_ctx* ctx, int bits) {
   return collapse_encode(ctx, n);
 }
 
-// Radix tree + node boxes -> 8-wide compressed nodes and BVH-ordered triangle records (shared by build and refit).
+// Radix tree + node boxes -> 8-wide compressed nodes, leaf-slot triangle indices and the per-triangle records (shared by
+// build and refit).  One cooperative launch + two streaming kernels; the only host synchronisation is the one at the end
+// that reads {depth, nodes, triangles, error} back.
 static int collapse_encode(rtf_ctx* ctx, uint32_t n) {
   BuildArrays& ba = ctx->ba;
   cudaStream_t st = ctx->stream;
+  const uint32_t nt = ctx->n_tris;
   int rc;
-  // ---- collapse ----
   mark(ctx, 4);
   const size_t max_nodes = (size_t)n / 2 + 64;
   const size_t max_level = (size_t)n / 4 + 64;
+  const size_t max_tiles = max_nodes / kCollapseBlock + kCollapseLevels + 2;
   if ((rc = ctx->d_nodes.reserve(80 * max_nodes))) return rc;
-  if ((rc = ctx->d_tris48.reserve(48 * (size_t)n))) return rc;
+  if ((rc = ctx->d_tri_idx.reserve(4 * (size_t)n))) return rc;
+  if ((rc = ctx->d_tris48.reserve(48 * (size_t)nt))) return rc;
   if ((rc = ba.level_a.reserve(4 * max_level))) return rc;
   if ((rc = ba.level_b.reserve(4 * max_level))) return rc;
-  if ((rc = ba.cnt_int.reserve(4 * (max_level + 1)))) return rc;
-  if ((rc = ba.cnt_tri.reserve(4 * (max_level + 1)))) return rc;
-  if ((rc = ba.scan_int.reserve(4 * (max_level + 1)))) return rc;
-  if ((rc = ba.scan_tri.reserve(4 * (max_level + 1)))) return rc;
-  if ((rc = ba.stash.reserve(32 * max_level))) return rc;
-
-  CollapseArgs ca{ba.children.as<int2>(), ba.range.as<uint2>(), ba.boxes.as<float>(), (int)n};
-  int root = n == 1 ? ~0 : 0;
+  if ((rc = ba.collapse_state.reserve(sizeof(CollapseState) + 64))) return rc;
+  if ((rc = ba.scan_state.reserve(8 * max_tiles))) return rc;
+  CollapseState* cs = ba.collapse_state.as<CollapseState>();
+  unsigned* gbar = (unsigned*)((char*)ba.collapse_state.p + sizeof(CollapseState));
+  RTF_CUDA(cudaMemsetAsync(ba.collapse_state.p, 0, sizeof(CollapseState) + 64, st));
+  RTF_CUDA(cudaMemsetAsync(ba.scan_state.p, 0, 8 * max_tiles, st));
+  const CollapseLevel l0{1u, 0u, 0u, 0u};
+  const int root = n == 1 ? ~0 : 0;
+  RTF_CUDA(cudaMemcpyAsync(&cs->level[0], &l0, sizeof(l0), cudaMemcpyHostToDevice, st));
   RTF_CUDA(cudaMemcpyAsync(ba.level_a.p, &root, 4, cudaMemcpyHostToDevice, st));
-  int* lv_cur = ba.level_a.as<int>();
-  int* lv_next = ba.level_b.as<int>();
-  uint32_t level_n = 1, level_start = 0, tri_cursor = 0;
-  int depth = 0;
-  while (level_n > 0) {
-    depth++;
-    if ((size_t)level_start + level_n > max_nodes || level_n > max_level) {
-      set_error("BVH collapse exceeded its node budget");
-      return RTF_ERR_LIMIT;
-    }
-    LAUNCH(ctx, k_collapse_plan, div_up(level_n, 128), 128, 0, ca, lv_cur, level_n, ba.stash.as<int>(),
-           ba.cnt_int.as<uint32_t>(), ba.cnt_tri.as<uint32_t>());
-    // exclusive scans; element [level_n] of each output receives the level total
-    if ((rc = exclusive_scan_u32(ctx, ba.cnt_int.as<uint32_t>(), ba.scan_int.as<uint32_t>(), level_n, ba.scan_state))) return rc;
-    if ((rc = exclusive_scan_u32(ctx, ba.cnt_tri.as<uint32_t>(), ba.scan_tri.as<uint32_t>(), level_n, ba.scan_state))) return rc;
-    const uint32_t next_start = level_start + level_n;
-    LAUNCH(ctx, k_collapse_emit, div_up(level_n, 128), 128, 0, ca, lv_cur, level_n, ba.stash.as<int>(),
-           ba.scan_int.as<uint32_t>(), ba.scan_tri.as<uint32_t>(), level_start, next_start, tri_cursor, lv_next,
-           ctx->d_nodes.as<Node80>(), ctx->d_tris48.as<Tri48>(), ctx->d_pos9.as<float>(), ctx->d_tri_inst.as<uint32_t>(),
-           ba.sorted_ids.as<uint32_t>(), ba.ref_tri.as<uint32_t>(), ctx->d_inst_alpha.as<float>());
-    uint32_t totals[2];
-    RTF_CUDA(cudaMemcpyAsync(&totals[0], ba.scan_int.as<uint32_t>() + level_n, 4, cudaMemcpyDeviceToHost, st));
-    RTF_CUDA(cudaMemcpyAsync(&totals[1], ba.scan_tri.as<uint32_t>() + level_n, 4, cudaMemcpyDeviceToHost, st));
-    RTF_CUDA(cudaStreamSynchronize(st));
-    level_start = next_start;
-    tri_cursor += totals[1];
-    level_n = totals[0];
-    int* t = lv_cur;
-    lv_cur = lv_next, lv_next = t;
+  if (ctx->collapse_blocks == 0) {
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_collapse, kCollapseBlock, 0) != cudaSuccess || nb < 1) nb = 1;
+    ctx->collapse_blocks = nb;
   }
+  CollapseArgs ca{ba.children.as<int2>(), ba.range.as<uint2>(), ba.boxes.as<float>(), (int)n};
+  unsigned long long* desc = ba.scan_state.as<unsigned long long>();
+  int* lva = ba.level_a.as<int>();
+  int* lvb = ba.level_b.as<int>();
+  Node80* nodes = ctx->d_nodes.as<Node80>();
+  uint32_t* slot_pos = ctx->d_tri_idx.as<uint32_t>();
+  uint32_t mn = (uint32_t)max_nodes, ml = (uint32_t)max_level;
+  const unsigned want = div_up(max_level, kCollapseBlock);
+  const unsigned full = (unsigned)ctx->sm_count * (unsigned)ctx->collapse_blocks;
+  void* args[] = {&ca, &cs, &desc, &lva, &lvb, &nodes, &slot_pos, &mn, &ml, &gbar};
+  RTF_CUDA(cudaLaunchCooperativeKernel((const void*)k_collapse, dim3(want < full ? want : full), dim3(kCollapseBlock), args, 0, st));
+  ctx->launches++;
+  LAUNCH(ctx, k_tri_index, div_up(n, 256), 256, 0, n, ba.sorted_ids.as<uint32_t>(), ba.ref_tri.as<uint32_t>(), slot_pos);
+  LAUNCH(ctx, k_tri_records, div_up(nt, 256), 256, 0, nt, ctx->d_pos9.as<float>(), ctx->d_tri_inst.as<uint32_t>(),
+         ctx->d_inst_alpha.as<float>(), ctx->d_tris48.as<Tri48>());
   mark(ctx, 5);
+  uint32_t res[4] = {0, 0, 0, 0};  // depth, nodes, triangle slots, error
+  RTF_CUDA(cudaMemcpyAsync(res, &cs->depth, 16, cudaMemcpyDeviceToHost, st));
   RTF_CUDA(cudaEventSynchronize(ctx->build_ev[5]));
+  RTF_CUDA(cudaStreamSynchronize(st));
   for (int k = 0; k < 5; k++) cudaEventElapsedTime(&ctx->build_ms[k], ctx->build_ev[k], ctx->build_ev[k + 1]);
   cudaEventElapsedTime(&ctx->build_ms[5], ctx->build_ev[0], ctx->build_ev[5]);
-  if (tri_cursor != n) {
-    set_error("BVH collapse lost triangles");
+  if (res[3] == 1u) {
+    set_error("BVH collapse exceeded its node budget");
     return RTF_ERR_LIMIT;
   }
-  ctx->n_nodes = level_start;
-  ctx->depth = depth;
-  if (depth > kMaxStackDepth) {
+  if (res[3] == 2u || (int)res[0] > kMaxStackDepth) {
     set_error("BVH deeper than the traversal stack");
     return RTF_ERR_LIMIT;
   }
+  if (res[2] != n) {
+    set_error("BVH collapse lost triangles");
+    return RTF_ERR_LIMIT;
+  }
+  ctx->n_nodes = res[1];
+  ctx->depth = (int)res[0];
   return RTF_OK;
 }
 

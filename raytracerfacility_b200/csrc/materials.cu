@@ -189,6 +189,12 @@ int rtf_set_texture(rtf_ctx* ctx, uint64_t handle, int width, int height, const 
     set_error("rtf_set_texture: bad handle, size or pixels");
     return RTF_ERR_INVALID;
   }
+  // An existing handle may back the committed material / cube-map tables (old pointer and size): uploading over it, or
+  // re-allocating it, would leave them dangling until the next commit.  Same guard as rtf_remove_texture.
+  if (ctx->textures.count(handle)) {
+    RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->ready = false;
+  }
   Texture& t = ctx->textures[handle];
   t.w = width, t.h = height;
   int rc;
@@ -297,6 +303,7 @@ int rtf_set_btf(rtf_ctx* ctx, uint64_t handle, const rtf_btf_desc* d) {
     return RTF_ERR_INVALID;
   }
   cudaStreamSynchronize(ctx->stream);
+  if (ctx->btfs.count(handle)) ctx->ready = false;  // the committed DevBTF table points at the arrays replaced below
   BTFTables& b = ctx->btfs[handle];
   b.desc = *d;
   // CompressedBTF.cpp:162-186: beta angles (degrees) of the 1-D slices

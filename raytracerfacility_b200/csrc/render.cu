@@ -71,11 +71,20 @@ struct SrcRays {
 template <bool STATS>
 __global__ void __launch_bounds__(kTraceBlock, RTF_TRACE_MIN_BLOCKS) k_trace_rays(DevScene sc, SrcRays src, uint32_t* work) {
   __shared__ TraceSmem sm;
-  trace_engine<STATS>(sc.nodes, sc.tris, src, work, sm);
+  trace_engine<STATS>(sc.nodes, sc.tris, sc.tri_idx, src, work, sm);
 }
 
-static unsigned trace_grid(const rtf_ctx* ctx, size_t n) {
-  const unsigned full = (unsigned)ctx->sm_count * (unsigned)ctx->trace_blocks_per_sm;
+// Persistent-lane kernels run one resident wave: SMs x the blocks of THIS kernel variant that fit on an SM (its register
+// count and launch bounds differ per variant), asked of the runtime at the variant's first launch.
+enum { TK_RAYS = 0, TK_RAYS_STATS, TK_QUEUE, TK_QUEUE_ALPHA, TK_GRID, TK_SAMPLES };
+template <class Kernel>
+static unsigned trace_grid(rtf_ctx* ctx, int which, Kernel kernel, size_t n) {
+  if (ctx->trace_blocks[which] == 0) {
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, kTraceBlock, 0) != cudaSuccess || nb < 1) nb = 1;
+    ctx->trace_blocks[which] = nb;
+  }
+  const unsigned full = (unsigned)ctx->sm_count * (unsigned)ctx->trace_blocks[which];
   const unsigned need = div_up(n, kTraceBlock);
   return need < full ? need : full;
 }
@@ -99,9 +108,9 @@ int trace_rays_device(rtf_ctx* ctx, const float4* rays, size_t n, float4* hits, 
     RTF_CUDA(cudaMemsetAsync(work, 0, 4, ctx->stream));
     SrcRays src{rays + 2 * off, hits + off, nv ? nv + off : nullptr, tv ? tv + off : nullptr, m};
     if (nv || tv)
-      LAUNCH(ctx, k_trace_rays<true>, trace_grid(ctx, m), kTraceBlock, 0, ctx->scene, src, work);
+      LAUNCH(ctx, k_trace_rays<true>, trace_grid(ctx, TK_RAYS_STATS, k_trace_rays<true>, m), kTraceBlock, 0, ctx->scene, src, work);
     else
-      LAUNCH(ctx, k_trace_rays<false>, trace_grid(ctx, m), kTraceBlock, 0, ctx->scene, src, work);
+      LAUNCH(ctx, k_trace_rays<false>, trace_grid(ctx, TK_RAYS, k_trace_rays<false>, m), kTraceBlock, 0, ctx->scene, src, work);
   }
   RTF_CUDA(cudaGetLastError());
   return RTF_OK;
@@ -209,7 +218,7 @@ __global__ void __launch_bounds__(kTraceBlock, ALPHA ? RTF_QUEUE_MIN_BLOCKS : RT
   const uint32_t n = q.count[wave];
   if (blockIdx.x == 0 && threadIdx.x == 0 && stats) atomicAdd(stats, (unsigned long long)n);
   SrcQueue<ALPHA> src{q.ray_a[qi], q.ray_b[qi], q.hits, n, tmin, ALPHA ? sc.inst_alpha : nullptr, sc, pm, seed, (uint32_t)wave};
-  trace_engine<false>(sc.nodes, sc.tris, src, q.work + wave, sm);
+  trace_engine<false>(sc.nodes, sc.tris, sc.tri_idx, src, q.work + wave, sm);
 }
 
 // ---- shade one wavefront: ClosestHitFunc (RayFunctions.cuh:25-172) / MissFunc (:260-272), unrolled ------
@@ -682,7 +691,8 @@ static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_
   }
   ShadeParams sp{bounces, seed, camera ? 1 : 0, ctx->brdf};
   unsigned long long* stats = ctx->d_stats.as<unsigned long long>();
-  const unsigned tgrid = trace_grid(ctx, paths);
+  const unsigned tgrid = ctx->scene.has_alpha ? trace_grid(ctx, TK_QUEUE_ALPHA, k_trace_queue<true>, paths)
+                                              : trace_grid(ctx, TK_QUEUE, k_trace_queue<false>, paths);
   int qi = 0;
   for (int w = 0; w < waves; w++) {
     const float tmin = (camera && w == 0) ? 0.0f : 1e-3f;
@@ -786,7 +796,7 @@ struct SrcGrid {
 };
 __global__ void __launch_bounds__(kTraceBlock) k_scan_grid(DevScene sc, SrcGrid src, uint32_t* work) {
   __shared__ TraceSmem sm;
-  trace_engine<false>(sc.nodes, sc.tris, src, work, sm);
+  trace_engine<false>(sc.nodes, sc.tris, sc.tri_idx, src, work, sm);
 }
 // CudaModule::SamplePointCloud's AoS samples (112 B in-out): read in the converged prepare phase, written back with
 // the full HitInfo of __closesthit__PCS_R (PointCloudScanning.cu:15-28).
@@ -823,7 +833,7 @@ struct SrcSamples {
 };
 __global__ void __launch_bounds__(kTraceBlock) k_scan_samples(DevScene sc, SrcSamples src, uint32_t* work) {
   __shared__ TraceSmem sm;
-  trace_engine<false>(sc.nodes, sc.tris, src, work, sm);
+  trace_engine<false>(sc.nodes, sc.tris, sc.tri_idx, src, work, sm);
 }
 
 int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin, uint64_t ray_end, float* d_t,
@@ -832,13 +842,14 @@ int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin
     set_error("no acceleration structure (call rtf_commit)");
     return RTF_ERR_NOT_READY;
   }
-  const uint32_t column = (uint32_t)(grid->size[0] / grid->distance[0]);
-  const uint32_t row = (uint32_t)(grid->size[1] / grid->distance[1]);
+  uint32_t column = 0, row = 0;
+  int rc;
+  if ((rc = rtf_scan_grid_dims(grid, &column, &row))) return rc;
   if (ray_end > (uint64_t)column * row || ray_end < ray_begin) {
     set_error("ray range outside the scan grid");
     return RTF_ERR_INVALID;
   }
-  int rc;
+  if (ray_end == ray_begin) return RTF_OK;
   if ((rc = ctx->ws.counters.reserve(4096))) return rc;
   uint32_t* work = ctx->ws.counters.as<uint32_t>();
   const uint64_t chunk = 1ull << 30;
@@ -849,7 +860,7 @@ int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin
     SrcGrid src{*grid, row, -(int)(column / 2), -(int)(row / 2),
                 normalize3(f3(grid->direction[0], grid->direction[1], grid->direction[2])), off, m,
                 d_t ? d_t + o : nullptr, d_prim ? d_prim + o : nullptr, d_inst ? d_inst + o : nullptr, ctx->scene.tri_inst};
-    LAUNCH(ctx, k_scan_grid, trace_grid(ctx, m), kTraceBlock, 0, ctx->scene, src, work);
+    LAUNCH(ctx, k_scan_grid, trace_grid(ctx, TK_GRID, k_scan_grid, m), kTraceBlock, 0, ctx->scene, src, work);
   }
   RTF_CUDA(cudaGetLastError());
   return RTF_OK;
@@ -865,7 +876,7 @@ int scan_samples_device(rtf_ctx* ctx, rtf_pc_sample* d_samples, size_t n, uint32
   uint32_t* work = ctx->ws.counters.as<uint32_t>();
   RTF_CUDA(cudaMemsetAsync(work, 0, 4, ctx->stream));
   SrcSamples src{ctx->scene, d_samples, d_prim, (uint32_t)n};
-  LAUNCH(ctx, k_scan_samples, trace_grid(ctx, n), kTraceBlock, 0, ctx->scene, src, work);
+  LAUNCH(ctx, k_scan_samples, trace_grid(ctx, TK_SAMPLES, k_scan_samples, n), kTraceBlock, 0, ctx->scene, src, work);
   RTF_CUDA(cudaGetLastError());
   return RTF_OK;
 }

@@ -7,7 +7,7 @@
 // HBM layout (DESIGN.md "Data layout"):
 //   wide node  = 80 B = 5 x 16 B, fetched as five 128-bit loads:
 //       q0 = {p.x, p.y, p.z, e.x | e.y<<8 | e.z<<16 | imask<<24}
-//       q1 = {child_base, tri_base, meta[0..3], meta[4..7]}
+//       q1 = {child_base, tri_base, VALID (24 bits), imask | CNT << 8}   (node_meta_store below)
 //       q2 = {qlo.x[0..3], qlo.x[4..7], qlo.y[0..3], qlo.y[4..7]}
 //       q3 = {qlo.z[0..3], qlo.z[4..7], qhi.x[0..3], qhi.x[4..7]}
 //       q4 = {qhi.y[0..3], qhi.y[4..7], qhi.z[0..3], qhi.z[4..7]}
@@ -38,6 +38,17 @@ struct __align__(16) Tri48 {
   uint32_t flags;
 };
 static_assert(sizeof(Tri48) == 48, "triangle must be 48 B");
+
+// Node meta words: w0 bits 0..23 = VALID, bit 3s+j set iff slot s is a leaf slot holding more than j triangles;
+// w1 = imask | CNT << 8, CNT = eight 2-bit fields, field s = triangles of leaf slot s (0 for inner / empty slots).
+// A node's leaf triangles lie consecutively from tri_base in slot order: triangle j of slot s is
+// tri_base + (sum of the CNT fields below s) + j.  The traversal keeps pending triangles as the mask "bit 3s+j" — a fixed
+// position per slot, so a node visit needs no per-child variable shift (rtf_trace.cuh).
+RTF_HD void node_meta_store(Node80& nd, uint32_t valid, uint32_t cnt16) {
+  const uint32_t w0 = valid & 0xffffffu, w1 = (uint32_t)nd.imask | ((cnt16 & 0xffffu) << 8);
+#pragma unroll
+  for (int k = 0; k < 4; k++) nd.meta[k] = (uint8_t)(w0 >> (8 * k)), nd.meta[4 + k] = (uint8_t)(w1 >> (8 * k));
+}
 
 enum { TRI_FLAG_ALPHA = 1u };  // material may ignore hits (RayFunctions.cuh:5-23)
 

@@ -72,7 +72,8 @@ struct DevMaterial {
 // Everything a kernel needs to trace and shade, passed by value.
 struct DevScene {
   const uint4* nodes = nullptr;
-  const float4* tris = nullptr;
+  const float4* tris = nullptr;        // one 48 B record per triangle, primitive order
+  const uint32_t* tri_idx = nullptr;   // per triangle reference (leaf-slot order): its triangle
   const float* pos9 = nullptr;
   const float* nrm9 = nullptr;
   const uint32_t* tri_inst = nullptr;
@@ -119,9 +120,10 @@ struct Instance {
 // Intermediate arrays of the builder kept for parity read-back (rtf_debug_read).
 struct BuildArrays {
   DevBuf morton, sorted_keys, sorted_ids, children, parent, range, boxes, flags, scene_bounds;
-  DevBuf keys_alt, ids_alt, level_a, level_b, cnt_int, cnt_tri, scan_int, scan_tri, stash;
+  DevBuf keys_alt, ids_alt, level_a, level_b;
   DevBuf ref_cnt, ref_first, ref_tri, ref_box, scan_state;  // triangle references (pre-splitting)
   DevBuf sort_hist, sort_status;                            // radix sort scratch (rtf_sort.cuh)
+  DevBuf collapse_state;                                    // level table + tickets + grid barrier of k_collapse
 };
 
 struct Workspace {  // wavefront queues + path state, sized for `capacity` paths
@@ -151,7 +153,8 @@ struct rtf_ctx {
   bool own_stream = false;
   uint64_t launches = 0;
   int sm_count = 148;
-  int trace_blocks_per_sm = 8;  // resident trace blocks per SM (occupancy query at rtf_create)
+  int trace_blocks[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // resident blocks per SM of each trace-kernel variant (occupancy query
+                                                   // at its first launch, render.cu trace_grid)
   std::map<uint64_t, rtf::Geometry> geoms;
   std::map<uint64_t, rtf_material> mats;
   std::map<uint64_t, rtf::Instance> insts;
@@ -172,11 +175,16 @@ struct rtf_ctx {
   uint64_t commits_full = 0, commits_materials = 0, commits_skipped = 0, geometry_uploads_skipped = 0;
   // committed state
   bool ready = false;
+  bool bvh_ok = false;  // the committed BVH and flattened arrays are intact (ready may be false only because a texture / BTF
+                        // the material tables point at was replaced: the next commit re-resolves the tables and keeps the BVH)
+  uint64_t epoch = 0;   // bumped by every commit that changed the committed scene (camera accumulation restarts on a change)
   int morton_bits = 63;
   int depth = 0;
   uint32_t n_tris = 0, n_nodes = 0;
   uint32_t n_refs = 0;  // triangle references in the BVH (>= n_tris when long triangles are pre-split)
   int presplit = 8;     // option "presplit": most references one triangle may be cut into (1 = off)
+  int collapse_blocks = 0;  // resident k_collapse blocks per SM (occupancy query at the first build)
+  rtf::DevBuf d_tri_idx;
   rtf::DevBuf d_pos9, d_nrm9, d_tri_inst, d_nodes, d_tris48, d_insts, d_mats, d_inst_alpha, d_btfs, d_env_faces;
   rtf::BuildArrays ba;
   rtf::Workspace ws;
@@ -189,6 +197,12 @@ struct rtf_ctx {
   size_t batch_paths = (size_t)1 << 24;  // 2^24 paths: ~3 GB of queues + path state; +12..20 % over 2^22 (fewer, fuller waves)
   int sort_rays = 0;  // option "sort_rays": sort bounce rays by (octant, origin cell) before tracing (measured: DESIGN.md)
   int brdf = RTF_BRDF_REFERENCE;  // option "brdf"
+  // RenderToCamera's change detection (m_cameraRenderingLaunchParams.m_rayTracerProperties, RayTracer.cu:253-269): the
+  // environment / ray properties and scene epoch the last frame was rendered with
+  rtf_env cam_last_env;
+  rtf_ray_props cam_last_rp;
+  uint64_t cam_last_epoch = 0;
+  bool cam_last_valid = false;
   // build-stage events: flatten | bounds+morton | sort | karras+refit | collapse | end
   cudaEvent_t build_ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   float build_ms[6] = {0, 0, 0, 0, 0, 0};

@@ -120,9 +120,13 @@ RTF_D void ss_probe(const DevScene& sc, float3 o, float3 d, float tmin, float tm
     const float oz = fmaf(mgz, -kFarSlack, oz0) - sz, ozf = fmaf(mgz, kFarSlack, oz0) - sz;
     const float bound = (rec.n == 4 ? rec.t[3] : tmax) * kBoxSlack;
     const uint32_t imask = n0.w >> 24;
+    uint32_t first = n1.y;  // first triangle of the next leaf slot (node meta: rtf_bvh.cuh)
     for (int j = 0; j < 8; j++) {
-      const uint32_t meta = ((j < 4 ? n1.z : n1.w) >> (8 * (j & 3))) & 0xffu;
-      if (meta == 0u) continue;
+      const bool inner = (imask >> j) & 1u;
+      const uint32_t cnt = (n1.w >> (8 + 2 * j)) & 3u;  // triangles of leaf slot j
+      const uint32_t slot_first = first;
+      first += cnt;
+      if (!inner && cnt == 0u) continue;
       const int sh = 8 * (j & 3);
       const uint32_t qlx = ((j < 4 ? n2.x : n2.y) >> sh) & 0xffu, qly = ((j < 4 ? n2.z : n2.w) >> sh) & 0xffu;
       const uint32_t qlz = ((j < 4 ? n3.x : n3.y) >> sh) & 0xffu, qhx = ((j < 4 ? n3.z : n3.w) >> sh) & 0xffu;
@@ -136,14 +140,11 @@ RTF_D void ss_probe(const DevScene& sc, float3 o, float3 d, float tmin, float tm
       const float tnear = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
       const float tfar = fminf(fminf(tfx, tfy), fminf(tfz, bound));
       if (!(tnear <= tfar)) continue;
-      if ((meta & (meta << 1)) & 0x10u) {  // inner child: slot = low bits - 24
-        const uint32_t slot = (meta & 0x1fu) - 24u;
-        stack[sp++] = n1.x + (uint32_t)__popc(imask & ((1u << slot) - 1u));
-      } else {  // leaf: unary triangle count in bits 5..7, first triangle offset in bits 0..4
-        const uint32_t first = n1.y + (meta & 0x1fu);
-        for (uint32_t b = 0; b < 3; b++) {
-          if (!((meta >> (5 + b)) & 1u)) continue;
-          const float4* tp = sc.tris + (size_t)(first + b) * 3;
+      if (inner) {
+        stack[sp++] = n1.x + (uint32_t)__popc(imask & ((1u << j) - 1u));
+      } else {
+        for (uint32_t b = 0; b < cnt; b++) {
+          const float4* tp = sc.tris + (size_t)__ldg(sc.tri_idx + slot_first + b) * 3;
           const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
           float t, bu, bv;
           if (!ss_tri_test(o, mx, my, mz, t0, t1, t2, t, bu, bv)) continue;

@@ -46,6 +46,9 @@ constexpr int kRawTileBytes = 1024;  // 32 rays x 32 B
 #define RTF_NODE_QUORUM 24
 #endif
 constexpr int kNodeQuorum = RTF_NODE_QUORUM;  // lanes that must be ready before the warp runs a node visit
+#ifndef RTF_FFMA2
+#define RTF_FFMA2 0  // 1: plane distances with packed fma.rn.f32x2 (Blackwell FFMA2); needs more than 64 registers to pay
+#endif
 
 RTF_D float safe_dir(float d) {
   const float ooeps = __uint_as_float(0x17800000u);  // 2^-80
@@ -107,7 +110,8 @@ struct __align__(128) TraceSmem {
 //   void fetch(raw, base, slot, a, b, tmin, tag)              a = {o.xyz, *}, b = {d.xyz, tmax}
 //   void store(index, tag, hit, node_visits, tri_visits)
 template <bool STATS, class Src>
-RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const Src& src,
+RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restrict__ tris,
+                        const uint32_t* __restrict__ tri_idx, const Src& src,
                         uint32_t* __restrict__ work, TraceSmem& sm) {
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -135,8 +139,7 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
   bool have = false;
   float3 o = f3(0, 0, 0), mx = f3(0, 0, 0), my = f3(0, 0, 0), mz = f3(0, 0, 0);
   float tmin = 0, idx = 0, idy = 0, idz = 0;
-  bool negx = false, negy = false, negz = false;
-  uint32_t oct_inv = 0, oct_inv4 = 0, tag = 0, ridx = 0, nvis = 0, tvis = 0;
+  uint32_t oct_inv = 0, pmask = 0, tag = 0, ridx = 0, nvis = 0, tvis = 0;
   HitRec best;
   best.t = 0, best.u = 0, best.v = 0, best.prim = 0xFFFFFFFFu;
   int sp = 0;
@@ -203,9 +206,9 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
           idx = q1.x, idy = q1.y, idz = q1.z;
           best.t = q1.w, best.u = 0.0f, best.v = 0.0f, best.prim = 0xFFFFFFFFu;
           mx = f3(q2.x, q2.y, q2.z), my = f3(q2.w, q3.x, q3.y), mz = f3(q3.z, q3.w, q4.x);
-          negx = idx < 0.0f, negy = idy < 0.0f, negz = idz < 0.0f;
+          const bool negx = idx < 0.0f, negy = idy < 0.0f, negz = idz < 0.0f;
           oct_inv = (negx ? 0u : 4u) | (negy ? 0u : 2u) | (negz ? 0u : 1u);
-          oct_inv4 = oct_inv * 0x01010101u;
+          pmask = (negz ? 0u : 0x55u) | (negy ? 0u : 0x33u << 10) | (negx ? 0u : 0x0Fu << 20);
           cur = make_uint2(0u, 0x80000000u);
           tg = make_uint2(0u, 0u);
           sp = 0, nvis = 0, tvis = 0;
@@ -245,6 +248,7 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
         const uint4* np = nodes + (size_t)(cur.x + rel) * 5;
         const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
         if (STATS) nvis++;
+        const bool negx = idx < 0.0f, negy = idy < 0.0f, negz = idz < 0.0f;  // from the sign bits: no flag registers
         // s = 2^e / d scaled by 2^15, o = (p - origin) / d with the bias s*2^15 taken off (see byte_to_float)
         const float sx = (__uint_as_float((n0.w & 0xffu) << 23) * idx) * 32768.0f;
         const float sy = (__uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idy) * 32768.0f;
@@ -261,48 +265,90 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
         const float oy = fmaf(mgy, -kFarSlack, oy0) - sy, oyf = fmaf(mgy, kFarSlack, oy0) - sy;
         const float oz = fmaf(mgz, -kFarSlack, oz0) - sz, ozf = fmaf(mgz, kFarSlack, oz0) - sz;
         const float best_s = best.t * kBoxSlack;  // equal-t candidates behind a rounded box entry stay reachable
-        uint32_t hitmask = 0;
+        // A child is entered iff none of (tfar - tnear), (best_s - tnear), (tfar - tmin) is negative: the slab test
+        // max(tnear, tmin) <= min(tfar, best_s) as three subtractions on the FMA pipe whose sign bits are OR-ed (one LOP3)
+        // and shifted into an 8-bit miss mask (one funnel shift).  Children run from slot 7 down, so slot s ends at bit s.
+#if RTF_FFMA2
+        // packed FFMA2 / FADD2 (fma.rn.f32x2, Blackwell): the near and the far plane of one axis in one instruction —
+        // {tn, tf} = {qn, qf} * s + {o, of}, s broadcast — and the three differences of TWO children per instruction.
+        // Every half is the same IEEE operation as in the scalar form, so results do not change.
+        const float2 o_x = make_float2(ox, oxf), o_y = make_float2(oy, oyf), o_z = make_float2(oz, ozf);
+        const float2 s_x = make_float2(sx, sx), s_y = make_float2(sy, sy), s_z = make_float2(sz, sz);
+        const float2 m1 = make_float2(-1.0f, -1.0f), bs2 = make_float2(best_s, best_s), ntm2 = make_float2(-tmin, -tmin);
+#endif
+        uint32_t acc = 0;
 #pragma unroll
-        for (int half = 0; half < 2; half++) {
-          const uint32_t meta4 = half ? n1.w : n1.z;
-          const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-          const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
-          const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
-          const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+        for (int half = 1; half >= 0; half--) {
           const uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
           const uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
           const uint32_t nx = negx ? qhix : qlox, fx = negx ? qlox : qhix;
           const uint32_t ny = negy ? qhiy : qloy, fy = negy ? qloy : qhiy;
           const uint32_t nz = negz ? qhiz : qloz, fz = negz ? qloz : qhiz;
+#if RTF_FFMA2
 #pragma unroll
-          for (int j = 0; j < 4; j++) {
+          for (int j = 3; j >= 1; j -= 2) {
+            float tn[2], tf[2];
+#pragma unroll
+            for (int c = 0; c < 2; c++) {  // children j and j-1
+              const float2 px = __ffma2_rn(make_float2(byte_to_float(nx, j - c, magic), byte_to_float(fx, j - c, magic)), s_x, o_x);
+              const float2 py = __ffma2_rn(make_float2(byte_to_float(ny, j - c, magic), byte_to_float(fy, j - c, magic)), s_y, o_y);
+              const float2 pz = __ffma2_rn(make_float2(byte_to_float(nz, j - c, magic), byte_to_float(fz, j - c, magic)), s_z, o_z);
+              tn[c] = fmaxf(fmaxf(px.x, py.x), pz.x);
+              tf[c] = fminf(fminf(px.y, py.y), pz.y);
+            }
+            const float2 tn2 = make_float2(tn[0], tn[1]), tf2 = make_float2(tf[0], tf[1]);
+            const float2 d1 = __ffma2_rn(tn2, m1, tf2);    // tfar - tnear (the product with -1 is exact)
+            const float2 d2 = __ffma2_rn(tn2, m1, bs2);    // best_s - tnear
+            const float2 d3 = __fadd2_rn(tf2, ntm2);       // tfar - tmin
+            acc = __funnelshift_l(__float_as_uint(d1.x) | __float_as_uint(d2.x) | __float_as_uint(d3.x), acc, 1);
+            acc = __funnelshift_l(__float_as_uint(d1.y) | __float_as_uint(d2.y) | __float_as_uint(d3.y), acc, 1);
+          }
+#else
+#pragma unroll
+          for (int j = 3; j >= 0; j--) {
             const float tnx = fmaf(byte_to_float(nx, j, magic), sx, ox);
             const float tny = fmaf(byte_to_float(ny, j, magic), sy, oy);
             const float tnz = fmaf(byte_to_float(nz, j, magic), sz, oz);
             const float tfx = fmaf(byte_to_float(fx, j, magic), sx, oxf);
             const float tfy = fmaf(byte_to_float(fy, j, magic), sy, oyf);
             const float tfz = fmaf(byte_to_float(fz, j, magic), sz, ozf);
-            const float tnear = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
-            const float tfar = fminf(fminf(tfx, tfy), fminf(tfz, best_s));
-            if (tnear <= tfar) {
-              const uint32_t cb = extract_byte(child_bits4, j);
-              const uint32_t bi = extract_byte(bit_index4, j);
-              hitmask |= cb << bi;
-            }
+            const float tnear = fmaxf(fmaxf(tnx, tny), tnz);
+            const float tfar = fminf(fminf(tfx, tfy), tfz);
+            const uint32_t sgn = __float_as_uint(tfar - tnear) | __float_as_uint(best_s - tnear) | __float_as_uint(tfar - tmin);
+            acc = __funnelshift_l(sgn, acc, 1);
           }
+#endif
         }
+        // n1.z = VALID (bit 3s+j: leaf slot s holds more than j triangles), n1.w = imask | CNT << 8 (rtf_bvh.cuh)
+        const uint32_t hit8 = ~acc & 0xffu;
+        // leaf slots: bit s -> bits 3s..3s+2 (three "part by two" steps, the shifts as multiplies on the FMA pipe)
+        uint32_t sp3 = (hit8 * 0x101u) & 0x00F00Fu;
+        sp3 = (sp3 * 0x11u) & 0x0C30C3u;
+        sp3 = (sp3 * 0x5u) & 0x249249u;
+        // inner children: the hit bit of slot s moves to priority s ^ oct_inv — three conditional swap stages (adjacent
+        // bits, pairs, nibbles); the stage masks of this ray sit in ONE register at bits 0, 10 and 20 and the byte moves along
+        uint32_t pi = ~acc & n1.w & 0xffu;
+        uint32_t sw = ((pi >> 1) ^ pi) & pmask;
+        pi = (pi ^ (sw * 3u)) << 10;
+        sw = ((pi >> 2) ^ pi) & pmask;
+        pi = (pi ^ (sw * 5u)) << 10;
+        sw = ((pi >> 4) ^ pi) & pmask;
+        pi = pi ^ (sw * 17u);
         cur.x = n1.x;
-        cur.y = (hitmask & 0xff000000u) | (n0.w >> 24);
+        cur.y = (pi << 4) | n1.w;
         tg.x = n1.y;
-        tg.y = hitmask & 0x00ffffffu;
+        tg.y = (sp3 * 7u) & n1.z;
       }
       bool tested = false;
       do {
         if (tg.y == 0u) break;
         tested = true;
-        const uint32_t ti = 31u - (uint32_t)__clz((int)tg.y);
-        tg.y &= ~(1u << ti);
-        const float4* tp = tris + (size_t)(tg.x + ti) * 3;
+        const uint32_t pos = 31u - (uint32_t)__clz((int)tg.y);  // bit 3s+j = triangle j of leaf slot s
+        tg.y &= ~(1u << pos);
+        const uint32_t ts = (pos * 11u) >> 5;  // pos / 3 for pos < 24
+        const uint32_t below = (cur.y >> 8) & ~(0xffffffffu << (2u * ts));  // 2-bit triangle counts of the slots below s
+        const uint32_t ti = (pos - 3u * ts) + (uint32_t)__popc(below) + (uint32_t)__popc(below & 0xAAAAu);
+        const float4* tp = tris + (size_t)__ldg(tri_idx + tg.x + ti) * 3;  // leaf slot -> shared triangle record
         const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
         if (STATS) tvis++;
         const float3 A = f3(t0.x - o.x, t0.y - o.y, t0.z - o.z);

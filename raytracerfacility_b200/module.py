@@ -29,7 +29,7 @@ EXPORTS = [
     "rtf_set_geometry", "rtf_set_material", "rtf_set_instance", "rtf_remove_geometry", "rtf_remove_material",
     "rtf_remove_instance", "rtf_commit", "rtf_triangle_count", "rtf_estimate_illumination",
     "rtf_estimate_illumination_mesh", "rtf_estimate_illumination_mesh_device", "rtf_illumination_finalize_device",
-    "rtf_last_job_stats", "rtf_scan_point_cloud", "rtf_scan_grid_ray_count", "rtf_scan_grid_trace",
+    "rtf_last_job_stats", "rtf_scan_point_cloud", "rtf_scan_grid_ray_count", "rtf_scan_grid_dims", "rtf_scan_grid_trace",
     "rtf_scan_grid_trace_device", "rtf_trace_closest", "rtf_trace_closest_device", "rtf_trace_closest_counts",
     "rtf_camera_create", "rtf_camera_destroy", "rtf_camera_get_props", "rtf_camera_resize", "rtf_camera_set",
     "rtf_render_camera", "rtf_render_camera_rows", "rtf_camera_download", "rtf_camera_device_buffer", "rtf_debug_size", "rtf_debug_read",
@@ -425,10 +425,12 @@ class RayTracer:
         _check(lib().rtf_debug_read(self.h, int(what), _p(out), nbytes))
         return out
 
-    def debug_upload_bvh(self, nodes, tris, depth):
+    def debug_upload_bvh(self, nodes, tris, tri_idx, depth):
+        """nodes: wide nodes; tris: one record per triangle (primitive order); tri_idx: triangle of every leaf slot."""
         nodes, tris = np.ascontiguousarray(nodes), np.ascontiguousarray(tris)
+        tri_idx = np.ascontiguousarray(tri_idx, dtype=np.uint32)
         _check(lib().rtf_debug_upload_bvh(self.h, _p(nodes), C.c_uint64(len(nodes)), _p(tris), C.c_uint64(len(tris)),
-                                          int(depth)))
+                                          _p(tri_idx), C.c_uint64(len(tri_idx)), int(depth)))
 
     def microbench_fp32(self):
         v = C.c_double()

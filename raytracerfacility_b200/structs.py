@@ -135,13 +135,34 @@ TRI_DTYPE = np.dtype([("v0", "<f4", 3), ("prim", "<u4"), ("v1", "<f4", 3), ("ins
 SKINNED_VERTEX_DTYPE = np.dtype([("v", VERTEX_DTYPE), ("bone_id", "<i4", 4), ("weight", "<f4", 4), ("bone_id2", "<i4", 4),
                                  ("weight2", "<f4", 4)])
 assert VERTEX_DTYPE.itemsize == 80 and ILLUM_SAMPLER_DTYPE.itemsize == 268 and SKINNED_VERTEX_DTYPE.itemsize == 144
+
+
+def node_leaf_slots(node):
+    """Leaf slots of one wide node as (slot, offset of its first triangle from tri_base, triangle count); node meta
+    (csrc/rtf_bvh.cuh): word 0 = 24-bit valid mask (bit 3s+j: slot s holds more than j triangles), word 1 = imask |
+    eight 2-bit triangle counts << 8; a node's leaf triangles lie consecutively in slot order."""
+    m = [int(x) for x in node["meta"]]
+    w0 = m[0] | m[1] << 8 | m[2] << 16 | m[3] << 24
+    w1 = m[4] | m[5] << 8 | m[6] << 16 | m[7] << 24
+    assert (w1 & 0xff) == int(node["imask"]) and (w0 >> 24) == 0 and (w1 >> 24) == 0
+    out, off = [], 0
+    for s in range(8):
+        cnt = (w1 >> (8 + 2 * s)) & 3
+        assert ((w0 >> (3 * s)) & 7) == (0, 1, 3, 7)[cnt]
+        assert not (cnt and (int(node["imask"]) >> s) & 1)
+        if cnt:
+            out.append((s, off, cnt))
+            off += cnt
+    return out
+
+
 assert PC_SAMPLE_DTYPE.itemsize == 112 and NODE_DTYPE.itemsize == 80 and TRI_DTYPE.itemsize == 48
 
 DBG_MORTON, DBG_SORTED_IDS, DBG_BIN_CHILDREN, DBG_BIN_PARENT, DBG_BIN_BOXES = 0, 1, 2, 3, 4
 DBG_WIDE_NODES, DBG_WIDE_TRIS, DBG_FLAT_POS, DBG_FLAT_NRM, DBG_FLAT_INST, DBG_SCENE_BOUNDS = 5, 6, 7, 8, 9, 10
-DBG_REF_TRI, DBG_REF_BOX = 11, 12
+DBG_REF_TRI, DBG_REF_BOX, DBG_TRI_IDX = 11, 12, 13
 DEFAULT_PRESPLIT = 8  # librtf_b200's default for rtf_set_option("presplit")
-DBG_DTYPES = {DBG_REF_TRI: np.dtype("<u4"), DBG_REF_BOX: np.dtype("<f4"),
+DBG_DTYPES = {DBG_REF_TRI: np.dtype("<u4"), DBG_REF_BOX: np.dtype("<f4"), DBG_TRI_IDX: np.dtype("<u4"),
               DBG_MORTON: np.dtype("<u8"), DBG_SORTED_IDS: np.dtype("<u4"), DBG_BIN_CHILDREN: np.dtype("<i4"),
               DBG_BIN_PARENT: np.dtype("<i4"), DBG_BIN_BOXES: np.dtype("<f4"), DBG_WIDE_NODES: NODE_DTYPE,
               DBG_WIDE_TRIS: TRI_DTYPE, DBG_FLAT_POS: np.dtype("<f4"), DBG_FLAT_NRM: np.dtype("<f4"),

@@ -56,21 +56,19 @@ def _check_tree(osc, S):
                 assert np.all(boxes[idx, :3] >= boxes[i, :3]) and np.all(boxes[idx, 3:] <= boxes[i, 3:])
         assert seen[0] == 0 and np.all(seen[1:] == 1)
     nodes, tris = osc.debug(S.DBG_WIDE_NODES), osc.debug(S.DBG_WIDE_TRIS)
-    assert sorted(tris["prim"].tolist()) == ref_tri.tolist()  # every reference exactly once
+    idx = osc.debug(S.DBG_TRI_IDX)
+    assert sorted(idx.tolist()) == ref_tri.tolist()  # every reference exactly once in the leaf slots
+    assert tris["prim"].tolist() == list(range(osc.n_tris))  # one record per triangle, primitive order
     pos = osc.debug(S.DBG_FLAT_POS).reshape(-1, 3, 3)
     assert_bit_equal(tris["v0"], pos[tris["prim"], 0], "tri v0")
     # quantised child boxes contain the triangles they lead to (leaf slots checked directly)
     for nd in nodes:
         scale = (nd["e"].astype(np.uint32) << 23).view(np.float32)
-        for s in range(8):
-            meta = int(nd["meta"][s])
-            if meta == 0 or (meta >> 5) == 1 and (meta & 0x1f) >= 24:
-                continue
-            cnt = bin(meta >> 5).count("1")
-            t0 = int(nd["tri_base"]) + (meta & 0x1f)
+        for s, off, cnt in S.node_leaf_slots(nd):
+            t0 = int(nd["tri_base"]) + off
             lo = nd["p"] + nd["qlo"][:, s].astype(np.float32) * scale
             hi = nd["p"] + nd["qhi"][:, s].astype(np.float32) * scale
-            for t in tris[t0:t0 + cnt]:  # the slot holds (at least) one reference box of each of its triangles
+            for t in tris[idx[t0:t0 + cnt]]:  # the slot holds (at least) one reference box of each of its triangles
                 rb = ref_box[ref_tri == t["prim"]]
                 assert (np.all(rb[:, :3] >= lo, axis=1) & np.all(rb[:, 3:] <= hi, axis=1)).any()
     # child_base / imask consistency: internal children are contiguous, BFS order
