@@ -437,6 +437,77 @@ RTF_API int rtf_render_camera_rows(rtf_ctx* ctx, const rtf_env* env, rtf_camera*
 RTF_API int rtf_camera_download(rtf_camera* cam, int which, float* host_rgba);
 RTF_API int rtf_camera_device_buffer(rtf_camera* cam, int which, float** dev_rgba);
 
+/* ---- multi-GPU (no reference counterpart: CudaModule::Init is cudaSetDevice(0), CM.cpp:25; RT.cu:827) -------------
+ * The BVH is replicated (every device commits the same scene); an entry point's work is split and at most one NCCL
+ * collective per job runs on the context's stream.  Sharding modes of the illumination estimate: */
+enum {
+  RTF_SHARD_SAMPLES = 0,   /* rank r traces samples [r*S/G, (r+1)*S/G) of every triangle; ncclAllReduce(sum) of the raw
+                              6*nTris sums, normalisation after it (BASELINE config 3).  <= 1e-5 of the 1-GPU result */
+  RTF_SHARD_TRIANGLES = 1  /* contiguous triangle ranges; broadcasts of the finished ranges.  Bit-identical to 1 GPU */
+};
+#define RTF_COMM_ID_BYTES 128
+/* (a) one process per GPU: rank 0 calls rtf_comm_unique_id, ships the 128 bytes to the other ranks by any means (the
+ * launcher's store, MPI, a file), every rank calls rtf_comm_init_rank (collective: ncclCommInitRank). */
+RTF_API int rtf_comm_unique_id(void* out, size_t bytes);
+RTF_API int rtf_comm_init_rank(rtf_ctx* ctx, int nranks, int rank, const void* unique_id);
+RTF_API int rtf_comm_destroy(rtf_ctx* ctx);
+RTF_API int rtf_comm_rank(rtf_ctx* ctx, int* rank, int* nranks);
+RTF_API int rtf_comm_barrier(rtf_ctx* ctx);
+/* all-reduce (max if op_max else sum) of n <= 64 host doubles over the communicator: timings, ray counts */
+RTF_API int rtf_comm_reduce_f64(rtf_ctx* ctx, double* values, int n, int op_max);
+/* contiguous balanced split of n units: the first n % nranks ranks get one more */
+RTF_API int rtf_shard_range(uint64_t n, int nranks, int rank, uint64_t* begin, uint64_t* end);
+/* Sharded entry points of a context that belongs to a communicator (either kind); with nranks == 1 they are the plain
+ * calls.  *_device: results stay in device memory (dev_out6: 6 floats per committed triangle, identical on all ranks). */
+RTF_API int rtf_estimate_illumination_mesh_sharded_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* ray_props,
+                                                          uint32_t seed, float push_normal_distance, int front_face,
+                                                          int back_face, int mode, float* dev_out6);
+RTF_API int rtf_estimate_illumination_mesh_sharded(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* ray_props,
+                                                   uint32_t seed, float push_normal_distance, int front_face, int back_face,
+                                                   int mode, float* out6 /* host */);
+/* The rank's ray range [*begin, *end) of the scan grid is traced into elements [*begin, *end) of the FULL-SIZE device
+ * arrays (each nullable); gather != 0 completes them on every rank (grouped broadcasts). */
+RTF_API int rtf_scan_grid_trace_sharded_device(rtf_ctx* ctx, const rtf_scan_grid* grid, int gather, float* dev_t,
+                                               uint32_t* dev_prim, uint32_t* dev_inst, uint64_t* begin, uint64_t* end);
+/* RenderToCamera over interleaved row bands; outputs_mask: bit RTF_OUT_COLOR / NORMAL / ALBEDO = complete that buffer on
+ * every rank (one group of broadcasts each).  Pixels keep their global RNG streams: bit-identical to the 1-GPU frame. */
+RTF_API int rtf_render_camera_sharded(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* ray_props,
+                                      int outputs_mask);
+/* {compute, collective, finalize} device milliseconds of the context's last sharded call (CUDA events) */
+RTF_API int rtf_phase_timings(rtf_ctx* ctx, float* ms3);
+
+/* (b) one process, n devices (rtf_create(devices, n)): ncclCommInitAll, one context + stream + host thread per
+ * device.  Scene calls are replicated; rtf_multi_commit builds the n BVHs concurrently.  rtf_multi_ctx lends the context of
+ * one device for anything not wrapped here (textures, BTFs, options): repeat such calls for every rank. */
+typedef struct rtf_multi rtf_multi;
+typedef struct rtf_multi_camera rtf_multi_camera;
+RTF_API int rtf_create_multi(const int* devices, int n, rtf_multi** out);
+RTF_API int rtf_multi_destroy(rtf_multi* m);
+RTF_API int rtf_multi_size(rtf_multi* m, int* n);
+RTF_API int rtf_multi_ctx(rtf_multi* m, int rank, rtf_ctx** ctx);
+RTF_API int rtf_multi_set_geometry(rtf_multi* m, uint64_t handle, const void* vertices, size_t n_vertices,
+                                   size_t vertex_stride_bytes, const uint32_t* triangles, size_t n_triangles, uint64_t version);
+RTF_API int rtf_multi_set_material(rtf_multi* m, uint64_t handle, const rtf_material* material);
+RTF_API int rtf_multi_set_instance(rtf_multi* m, uint64_t handle, uint64_t geometry, uint64_t material, const float xform[16],
+                                   uint64_t component_handle);
+RTF_API int rtf_multi_set_option(rtf_multi* m, const char* name, int64_t value);
+RTF_API int rtf_multi_commit(rtf_multi* m, int morton_bits);
+RTF_API int rtf_multi_estimate_illumination_mesh(rtf_multi* m, const rtf_env* env, const rtf_ray_props* ray_props, uint32_t seed,
+                                                 float push_normal_distance, int front_face, int back_face, int mode,
+                                                 float* out6 /* host, 6 floats per triangle */);
+/* every device traces its ray range and copies its slice straight into the caller's arrays (n PCIe links, no collective) */
+RTF_API int rtf_multi_scan_grid_trace(rtf_multi* m, const rtf_scan_grid* grid, float* t_out, uint32_t* prim_id_out,
+                                      uint32_t* inst_id_out);
+RTF_API int rtf_multi_trace_closest(rtf_multi* m, const float* rays, size_t n, void* hits);
+RTF_API int rtf_multi_camera_create(rtf_multi* m, rtf_multi_camera** out);
+RTF_API int rtf_multi_camera_destroy(rtf_multi_camera* cam);
+RTF_API int rtf_multi_camera_resize(rtf_multi_camera* cam, int width, int height);
+RTF_API int rtf_multi_camera_set(rtf_multi_camera* cam, const float position[3], const float rotation_wxyz[4]);
+RTF_API int rtf_multi_camera_get_props(rtf_multi_camera* cam, rtf_camera_props** props);
+RTF_API int rtf_multi_render_camera(rtf_multi* m, const rtf_env* env, rtf_multi_camera* cam, const rtf_ray_props* ray_props,
+                                    int outputs_mask);
+RTF_API int rtf_multi_camera_download(rtf_multi_camera* cam, int which, float* host);
+
 /* ---- build-stage readback for parity tests (tests/ compares each with the oracle) --------- */
 enum {
   RTF_DBG_MORTON = 0,       /* u64 per triangle reference (unsorted order)       */
@@ -445,20 +516,19 @@ enum {
   RTF_DBG_BIN_PARENT = 3,   /* i32 per binary node: internals [0,n-1) then leaves [n-1, 2n-1) */
   RTF_DBG_BIN_BOXES = 4,    /* 6 floats per binary node, same numbering            */
   RTF_DBG_WIDE_NODES = 5,   /* 80 B per wide node                                */
-  RTF_DBG_WIDE_TRIS = 6,    /* 48 B per triangle, primitive order                */
+  RTF_DBG_WIDE_TRIS = 6,    /* 48 B per triangle reference, BVH (leaf-slot) order */
   RTF_DBG_FLAT_POS = 7,     /* 9 floats per triangle, commit order               */
   RTF_DBG_FLAT_NRM = 8,     /* 9 floats per triangle, commit order               */
   RTF_DBG_FLAT_INST = 9,    /* u32 per triangle                                  */
   RTF_DBG_SCENE_BOUNDS = 10, /* 6 floats                                         */
   RTF_DBG_REF_TRI = 11,     /* u32 per triangle reference: its triangle          */
-  RTF_DBG_REF_BOX = 12,     /* 6 floats per triangle reference: clipped bounds   */
-  RTF_DBG_TRI_IDX = 13      /* u32 per triangle reference, BVH (leaf-slot) order: its triangle */
+  RTF_DBG_REF_BOX = 12      /* 6 floats per triangle reference: clipped bounds   */
 };
 RTF_API int rtf_debug_size(rtf_ctx* ctx, int what, uint64_t* bytes);
 RTF_API int rtf_debug_read(rtf_ctx* ctx, int what, void* host_out, uint64_t bytes);
 /* Upload a BVH built elsewhere (the oracle, in tests) so traversal can be checked in isolation. */
 RTF_API int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* wide_nodes, uint64_t n_nodes, const void* wide_tris,
-                                 uint64_t n_tris, const uint32_t* tri_idx, uint64_t n_refs, int depth);
+                                 uint64_t n_tris, int depth);
 /* microbenchmarks for the roofline denominators BASELINE.md asks the builder to measure */
 /* Test hook: the BSSRDF spatial probe (SSAnyHit / BSSRDF, BSSDF.cuh:18-89) on its own.  rays: n x
  * {o.xyz, tmin, d.xyz, tmax}; handles: the private component handle each probe is restricted to;

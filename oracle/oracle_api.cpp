@@ -123,7 +123,6 @@ static const void* dbg_ptr(Scene* s, int what, uint64_t* bytes) {
     case RTF_DBG_BIN_BOXES: *bytes = b.boxes.size() * 24; return b.boxes.data();
     case RTF_DBG_WIDE_NODES: *bytes = b.nodes.size() * 80; return b.nodes.data();
     case RTF_DBG_WIDE_TRIS: *bytes = b.tris.size() * 48; return b.tris.data();
-    case RTF_DBG_TRI_IDX: *bytes = b.tri_idx.size() * 4; return b.tri_idx.data();
     case RTF_DBG_FLAT_POS: *bytes = s->pos9.size() * 4; return s->pos9.data();
     case RTF_DBG_FLAT_NRM: *bytes = s->nrm9.size() * 4; return s->nrm9.data();
     case RTF_DBG_FLAT_INST: *bytes = s->tri_inst.size() * 4; return s->tri_inst.data();

@@ -81,8 +81,7 @@ struct BVH {
   std::vector<uint32_t> range_last;
   std::vector<Box> boxes;            // per binary node
   std::vector<Node80> nodes;         // wide nodes, BFS order
-  std::vector<Tri48> tris;           // one record per triangle, primitive order (shared by all its references)
-  std::vector<uint32_t> tri_idx;     // per triangle reference, BVH (leaf-slot) order: its triangle
+  std::vector<Tri48> tris;           // per triangle reference, BVH (leaf-slot) order
   int depth = 0;                     // number of wide levels
 };
 
@@ -320,20 +319,7 @@ static inline void build(BVH& bvh, uint32_t ntri, const float* pos9, const uint3
   }
   // ---- greedy surface-area collapse to 8-wide, breadth first ----
   bvh.nodes.clear();
-  // triangle records: ONE per triangle in primitive order; the leaf slots hold 4-byte indices into it (tri_idx), so a
-  // triangle cut into k references costs 48 + 4k bytes, not 48k (1 M-triangle field: 120 MB of BVH instead of 277 MB)
-  bvh.tris.assign(ntri, Tri48{});
-  for (uint32_t prim = 0; prim < ntri; prim++) {
-    Tri48& T = bvh.tris[prim];
-    const float* p = pos9 + 9 * (size_t)prim;
-    T.v0[0] = p[0], T.v0[1] = p[1], T.v0[2] = p[2];
-    T.v1[0] = p[3], T.v1[1] = p[4], T.v1[2] = p[5];
-    T.v2[0] = p[6], T.v2[1] = p[7], T.v2[2] = p[8];
-    T.prim = prim;
-    T.inst = tri_inst ? tri_inst[prim] : 0;
-    T.flags = 0;
-  }
-  bvh.tri_idx.assign(N, 0u);
+  bvh.tris.assign(n, Tri48{});
   bvh.depth = 0;
   if (N == 0) return;
   auto bin_box = [&](int c) -> const Box& { return bvh.boxes[c >= 0 ? c : ni + ~c]; };
@@ -433,7 +419,17 @@ static inline void build(BVH& bvh, uint32_t ntri, const float* pos9, const uint3
           valid |= (cnt == 1 ? 1u : (cnt == 2 ? 3u : 7u)) << (3 * s);
           cnt16 |= cnt << (2 * s);
           uint32_t first = bin_first(c);
-          for (uint32_t j = 0; j < cnt; j++) bvh.tri_idx[tri_cursor + tri_off + j] = bvh.ref_tri[bvh.order[first + j]];
+          for (uint32_t j = 0; j < cnt; j++) {
+            uint32_t prim = bvh.ref_tri[bvh.order[first + j]];
+            Tri48& T = bvh.tris[tri_cursor + tri_off + j];
+            const float* p = pos9 + 9 * (size_t)prim;
+            T.v0[0] = p[0], T.v0[1] = p[1], T.v0[2] = p[2];
+            T.v1[0] = p[3], T.v1[1] = p[4], T.v1[2] = p[5];
+            T.v2[0] = p[6], T.v2[1] = p[7], T.v2[2] = p[8];
+            T.prim = prim;
+            T.inst = tri_inst ? tri_inst[prim] : 0;
+            T.flags = 0;
+          }
           tri_off += cnt;
         }
       }
@@ -512,7 +508,7 @@ static inline bool intersect_tri(const Ray& ray, const RayPrep& rp, const Tri48&
 static inline Hit trace_brute(const BVH& bvh, const Ray& ray) {
   Hit best{ray.tmax, 0.0f, 0.0f, 0xFFFFFFFFu};
   RayPrep rp = prep_ray(ray.d);
-  for (uint32_t i = 0; i < bvh.n; i++) intersect_tri(ray, rp, bvh.tris[i], best);
+  for (uint32_t i = 0; i < bvh.nref; i++) intersect_tri(ray, rp, bvh.tris[i], best);
   return best;
 }
 
@@ -612,7 +608,7 @@ static inline Hit trace(const BVH& bvh, const Ray& ray, TraceStats* stats = null
       const uint32_t ts = pos / 3u, tj = pos - 3u * ts;
       uint32_t before = 0;  // triangles of the leaf slots below ts (2-bit count fields of cur.bits, bits 8..23)
       for (uint32_t s = 0; s < ts; s++) before += (cur.bits >> (8 + 2 * s)) & 3u;
-      const Tri48& tri = bvh.tris[bvh.tri_idx[tg.base + before + tj]];
+      const Tri48& tri = bvh.tris[tg.base + before + tj];
       if (stats) stats->tris++;
       Hit cand = best;
       if (intersect_tri(ray, rp, tri, cand) && filter(tri, cand)) {

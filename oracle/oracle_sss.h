@@ -53,7 +53,7 @@ static inline SSRecords ss_probe_brute(const BVH& bvh, V3 o, V3 d, float tmin, f
   SSRecords rec;
   Ray ray{o, tmin, d, tmax};
   const RayPrep rp = prep_ray(d);
-  for (uint32_t i = 0; i < bvh.n; i++) {
+  for (uint32_t i = 0; i < bvh.nref; i++) {
     Hit cand{tmax, 0.0f, 0.0f, 0xFFFFFFFFu};
     if (intersect_tri(ray, rp, bvh.tris[i], cand) && handle_of(bvh.tris[i].inst) == handle)
       ss_insert(rec, cand.t, cand.u, cand.v, cand.prim);

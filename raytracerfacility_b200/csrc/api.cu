@@ -72,7 +72,7 @@ int rtf_destroy(rtf_ctx* ctx) {
                     &ctx->ba.children, &ctx->ba.parent, &ctx->ba.range, &ctx->ba.boxes, &ctx->ba.flags,
                     &ctx->ba.scene_bounds, &ctx->ba.keys_alt, &ctx->ba.ids_alt, &ctx->ba.ref_cnt, &ctx->ba.ref_first,
                     &ctx->ba.ref_tri, &ctx->ba.ref_box, &ctx->ba.scan_state, &ctx->ba.sort_hist, &ctx->ba.sort_status, &ctx->ba.level_a,
-                    &ctx->ba.level_b, &ctx->ba.collapse_state, &ctx->d_tri_idx, &ctx->ws.ray_a[0], &ctx->ws.ray_a[1], &ctx->ws.ray_b[0], &ctx->ws.ray_b[1],
+                    &ctx->ba.level_b, &ctx->ba.collapse_state, &ctx->ba.slot_pos, &ctx->ws.ray_a[0], &ctx->ws.ray_a[1], &ctx->ws.ray_b[0], &ctx->ws.ray_b[1],
                     &ctx->ws.hits, &ctx->ws.counters, &ctx->ws.thr,
                     &ctx->ws.acc, &ctx->ws.dir0w, &ctx->ws.first_n, &ctx->ws.first_a, &ctx->ws.first_p,
                     &ctx->ws.sort_keys, &ctx->ws.sort_keys_alt, &ctx->ws.sort_vals, &ctx->ws.sort_vals_alt,
@@ -89,6 +89,10 @@ int rtf_destroy(rtf_ctx* ctx) {
     }
     cudaStreamDestroy(ctx->pipe.in), cudaStreamDestroy(ctx->pipe.out);
   }
+  for (cudaEvent_t e : ctx->phase_ev)
+    if (e) cudaEventDestroy(e);
+  ctx->d_shard_out.release(), ctx->d_small.release();
+  if (ctx->comm) rtf_comm_destroy(ctx);
   if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return RTF_OK;
@@ -380,7 +384,7 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   ctx->geom_dirty = false, ctx->mat_dirty = false, ctx->topo_dirty = false;
   ctx->morton_bits = morton_bits;
   DevScene& s = ctx->scene;
-  s.nodes = ctx->d_nodes.as<uint4>(), s.tris = ctx->d_tris48.as<float4>(), s.tri_idx = ctx->d_tri_idx.as<uint32_t>();
+  s.nodes = ctx->d_nodes.as<uint4>(), s.tris = ctx->d_tris48.as<float4>();
   s.pos9 = ctx->d_pos9.as<float>(), s.nrm9 = ctx->d_nrm9.as<float>(), s.tri_inst = ctx->d_tri_inst.as<uint32_t>();
   s.mats = ctx->d_mats.as<DevMaterial>(), s.inst_alpha = ctx->d_inst_alpha.as<float>();
   s.btfs = ctx->d_btfs.as<DevBTF>(), s.env_faces = env_faces;
@@ -561,7 +565,7 @@ int rtf_illumination_flux_mesh_device(rtf_ctx* ctx, const float* dev_energy6, ui
 int rtf_last_job_stats(rtf_ctx* ctx, uint64_t* rays, uint64_t* paths) {
   CHECK_CTX(ctx);
   RTF_CUDA(cudaStreamSynchronize(ctx->stream));
-  int rc = fetch_stats(ctx);
+  int rc = ctx->stats_cached ? RTF_OK : fetch_stats(ctx);
   if (rc) return rc;
   if (rays) *rays = ctx->last_rays;
   if (paths) *paths = ctx->last_paths;
@@ -850,16 +854,21 @@ int rtf_camera_set(rtf_camera* cam, const float position[3], const float q[4]) {
   return RTF_OK;
 }
 
-static int render_camera_rows(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, int row_begin,
-                              int row_end) {
-  if (!env || !cam || !rp) return RTF_ERR_INVALID;
+}  // extern "C"
+namespace rtf {
+// RenderToCamera (RayTracer.cu:244-603) for a list of row bands [rows[2k], rows[2k+1]) of ONE frame: the change
+// detection runs once, every band sees the same frame id, the id advances once.  Returns 1 / 0 like the reference's bool
+// (0 = no acceleration structure), < 0 on error.  Blocks until the bands are rendered.
+int render_camera_bands(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, const int* rows, int n_bands) {
+  if (!env || !cam || !rp || (!rows && n_bands)) return RTF_ERR_INVALID;
   rtf_camera_props& p = cam->props;
   if (p.width == 0 || p.height == 0) return 1;  // RayTracer.cu:246-247
   if (!ctx->ready) return 0;                    // RayTracer.cu:248-249
-  if (row_begin < 0 || row_end > p.height || row_begin > row_end) {
-    set_error("rtf_render_camera_rows: bad row range");
-    return RTF_ERR_INVALID;
-  }
+  for (int k = 0; k < n_bands; k++)
+    if (rows[2 * k] < 0 || rows[2 * k + 1] > p.height || rows[2 * k] > rows[2 * k + 1]) {
+      set_error("rtf_render_camera_rows: bad row range");
+      return RTF_ERR_INVALID;
+    }
   bool changed = p.modified != 0;
   p.modified = 0;
   if (!ctx->cam_last_valid || memcmp(&ctx->cam_last_env, env, sizeof(rtf_env)) != 0) ctx->cam_last_env = *env, changed = true;
@@ -870,12 +879,37 @@ static int render_camera_rows(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam,
   ctx->cam_last_valid = true;
   if (!p.accumulate || changed) p.frame_id = 0;  // RayTracer.cu:266-269
   // the launch sees the frame id before the increment (RayTracer.cu:349-352)
-  int rc = render_camera_device(ctx, env, cam, rp, (uint64_t)row_begin * p.width, (uint64_t)row_end * p.width);
-  if (rc) return rc;
+  uint64_t paths = 0, rays = 0;
+  for (int k = 0; k < n_bands; k++) {
+    int rc = render_camera_device(ctx, env, cam, rp, (uint64_t)rows[2 * k] * p.width, (uint64_t)rows[2 * k + 1] * p.width);
+    if (rc) return rc;
+    paths += ctx->last_paths;
+    if (n_bands > 1) {  // the job statistics are per call of render_camera_device: sum them over the bands
+      RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+      unsigned long long st[2] = {0, 0};
+      if (ctx->d_stats.p) RTF_CUDA(cudaMemcpy(st, ctx->d_stats.p, 16, cudaMemcpyDeviceToHost));
+      rays += st[0];
+    }
+  }
   p.frame_id++;
   RTF_CUDA(cudaStreamSynchronize(ctx->stream));
-  if ((rc = fetch_stats(ctx))) return rc;
+  if (n_bands > 1) {
+    ctx->last_rays = rays;
+  } else {
+    unsigned long long st[2] = {0, 0};
+    if (ctx->d_stats.p) RTF_CUDA(cudaMemcpy(st, ctx->d_stats.p, 16, cudaMemcpyDeviceToHost));
+    ctx->last_rays = st[0];
+  }
+  ctx->last_paths = paths;
+  ctx->stats_cached = true;
   return 1;
+}
+}  // namespace rtf
+extern "C" {
+static int render_camera_rows(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, int row_begin,
+                              int row_end) {
+  const int rows[2] = {row_begin, row_end};
+  return render_camera_bands(ctx, env, cam, rp, rows, 1);
 }
 int rtf_render_camera(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp) {
   CHECK_CTX(ctx);
@@ -914,8 +948,7 @@ static const void* dbg_ptr(rtf_ctx* c, int what, uint64_t* bytes) {
     case RTF_DBG_BIN_PARENT: *bytes = (n ? 2 * n - 1 : 0) * 4; return c->ba.parent.p;
     case RTF_DBG_BIN_BOXES: *bytes = (n ? 2 * n - 1 : 0) * 24; return c->ba.boxes.p;
     case RTF_DBG_WIDE_NODES: *bytes = (uint64_t)c->n_nodes * 80; return c->d_nodes.p;
-    case RTF_DBG_WIDE_TRIS: *bytes = nt * 48; return c->d_tris48.p;
-    case RTF_DBG_TRI_IDX: *bytes = n * 4; return c->d_tri_idx.p;
+    case RTF_DBG_WIDE_TRIS: *bytes = n * 48; return c->d_tris48.p;
     case RTF_DBG_FLAT_POS: *bytes = nt * 36; return c->d_pos9.p;
     case RTF_DBG_FLAT_NRM: *bytes = nt * 36; return c->d_nrm9.p;
     case RTF_DBG_FLAT_INST: *bytes = nt * 4; return c->d_tri_inst.p;
@@ -940,24 +973,19 @@ int rtf_debug_read(rtf_ctx* ctx, int what, void* out, uint64_t bytes) {
   }
   return RTF_OK;
 }
-int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* nodes, uint64_t n_nodes, const void* tris, uint64_t n_tris,
-                         const uint32_t* tri_idx, uint64_t n_refs, int depth) {
+int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* nodes, uint64_t n_nodes, const void* tris, uint64_t n_tris, int depth) {
   CHECK_CTX(ctx);
-  if (!nodes || !tris || !tri_idx || depth > kMaxStackDepth) return RTF_ERR_INVALID;
+  if (!nodes || !tris || depth > kMaxStackDepth) return RTF_ERR_INVALID;
   int rc;
   RTF_CUDA(cudaStreamSynchronize(ctx->stream));
-  if ((rc = ctx->d_nodes.reserve(n_nodes * 80)) || (rc = ctx->d_tris48.reserve(n_tris * 48)) ||
-      (rc = ctx->d_tri_idx.reserve(n_refs * 4)))
-    return rc;
+  if ((rc = ctx->d_nodes.reserve(n_nodes * 80)) || (rc = ctx->d_tris48.reserve(n_tris * 48))) return rc;
   RTF_CUDA(cudaMemcpy(ctx->d_nodes.p, nodes, n_nodes * 80, cudaMemcpyHostToDevice));
   RTF_CUDA(cudaMemcpy(ctx->d_tris48.p, tris, n_tris * 48, cudaMemcpyHostToDevice));
-  RTF_CUDA(cudaMemcpy(ctx->d_tri_idx.p, tri_idx, n_refs * 4, cudaMemcpyHostToDevice));
   ctx->scene.nodes = ctx->d_nodes.as<uint4>(), ctx->scene.tris = ctx->d_tris48.as<float4>();
-  ctx->scene.tri_idx = ctx->d_tri_idx.as<uint32_t>();
   ctx->n_nodes = (uint32_t)n_nodes, ctx->depth = depth;
   ctx->scene.n_nodes = (uint32_t)n_nodes;
   if (!ctx->ready) ctx->n_tris = (uint32_t)n_tris, ctx->scene.n_tris = (uint32_t)n_tris;
-  ctx->n_refs = (uint32_t)n_refs;
+  ctx->n_refs = (uint32_t)n_tris;
   ctx->ready = true;
   return RTF_OK;
 }

@@ -417,7 +417,7 @@ __device__ __forceinline__ void collapse_plan(const CollapseArgs& a, int R, int 
 }
 
 // Encode node R (80 B), write its internal children into the next level and, per triangle slot, the SORTED POSITION of
-// the reference it holds (k_tri_index turns those into triangle ids with coalesced accesses).
+// the reference it holds (k_tri_records turns those into 48 B records with coalesced stores).
 __device__ __forceinline__ void collapse_emit(const CollapseArgs& a, int R, const int (&slot_child)[8], uint32_t child_base,
                                               uint32_t tri_base, int* __restrict__ next_level_at, Node80* __restrict__ out,
                                               uint32_t* __restrict__ slot_pos) {
@@ -570,18 +570,14 @@ __global__ void __launch_bounds__(kCollapseBlock)
   }
 }
 
-// Triangle ids of the leaf slots (4 B per reference, BVH order) from the sorted positions the collapse left there.
-__global__ void k_tri_index(uint32_t n, const uint32_t* __restrict__ sorted_ids, const uint32_t* __restrict__ ref_tri,
-                            uint32_t* __restrict__ slot_pos_to_prim) {
+// 48 B triangle records in leaf-slot order from the sorted positions the collapse left per slot: one thread per slot, three
+// coalesced 16 B stores (the collapse itself only writes 4 B per slot).
+__global__ void k_tri_records(uint32_t n, const uint32_t* __restrict__ slot_pos, const uint32_t* __restrict__ sorted_ids,
+                              const uint32_t* __restrict__ ref_tri, const float* __restrict__ pos9,
+                              const uint32_t* __restrict__ tri_inst, const float* __restrict__ inst_alpha, Tri48* __restrict__ tris) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  slot_pos_to_prim[i] = ref_tri[sorted_ids[slot_pos_to_prim[i]]];
-}
-// One 48 B record per TRIANGLE in primitive order, shared by all references of the triangle (rtf_bvh.cuh).
-__global__ void k_tri_records(uint32_t nt, const float* __restrict__ pos9, const uint32_t* __restrict__ tri_inst,
-                              const float* __restrict__ inst_alpha, Tri48* __restrict__ tris) {
-  const uint32_t prim = blockIdx.x * blockDim.x + threadIdx.x;
-  if (prim >= nt) return;
+  const uint32_t prim = ref_tri[sorted_ids[slot_pos[i]]];
   const float* p = pos9 + 9 * (size_t)prim;
   Tri48 T;
   T.v0[0] = p[0], T.v0[1] = p[1], T.v0[2] = p[2];
@@ -590,7 +586,7 @@ __global__ void k_tri_records(uint32_t nt, const float* __restrict__ pos9, const
   T.prim = prim;
   T.inst = tri_inst[prim];
   T.flags = (inst_alpha && inst_alpha[T.inst] < 1.0f) ? (uint32_t)TRI_FLAG_ALPHA : 0u;
-  tris[prim] = T;
+  tris[i] = T;
 }
 
 static void mark(rtf_ctx* ctx, int k) {
@@ -697,15 +693,14 @@ int build_bvh(rtf_ctx* ctx, int bits) {
 static int collapse_encode(rtf_ctx* ctx, uint32_t n) {
   BuildArrays& ba = ctx->ba;
   cudaStream_t st = ctx->stream;
-  const uint32_t nt = ctx->n_tris;
   int rc;
   mark(ctx, 4);
   const size_t max_nodes = (size_t)n / 2 + 64;
   const size_t max_level = (size_t)n / 4 + 64;
   const size_t max_tiles = max_nodes / kCollapseBlock + kCollapseLevels + 2;
   if ((rc = ctx->d_nodes.reserve(80 * max_nodes))) return rc;
-  if ((rc = ctx->d_tri_idx.reserve(4 * (size_t)n))) return rc;
-  if ((rc = ctx->d_tris48.reserve(48 * (size_t)nt))) return rc;
+  if ((rc = ba.slot_pos.reserve(4 * (size_t)n))) return rc;
+  if ((rc = ctx->d_tris48.reserve(48 * (size_t)n))) return rc;
   if ((rc = ba.level_a.reserve(4 * max_level))) return rc;
   if ((rc = ba.level_b.reserve(4 * max_level))) return rc;
   if ((rc = ba.collapse_state.reserve(sizeof(CollapseState) + 64))) return rc;
@@ -728,16 +723,15 @@ static int collapse_encode(rtf_ctx* ctx, uint32_t n) {
   int* lva = ba.level_a.as<int>();
   int* lvb = ba.level_b.as<int>();
   Node80* nodes = ctx->d_nodes.as<Node80>();
-  uint32_t* slot_pos = ctx->d_tri_idx.as<uint32_t>();
+  uint32_t* slot_pos = ba.slot_pos.as<uint32_t>();
   uint32_t mn = (uint32_t)max_nodes, ml = (uint32_t)max_level;
   const unsigned want = div_up(max_level, kCollapseBlock);
   const unsigned full = (unsigned)ctx->sm_count * (unsigned)ctx->collapse_blocks;
   void* args[] = {&ca, &cs, &desc, &lva, &lvb, &nodes, &slot_pos, &mn, &ml, &gbar};
   RTF_CUDA(cudaLaunchCooperativeKernel((const void*)k_collapse, dim3(want < full ? want : full), dim3(kCollapseBlock), args, 0, st));
   ctx->launches++;
-  LAUNCH(ctx, k_tri_index, div_up(n, 256), 256, 0, n, ba.sorted_ids.as<uint32_t>(), ba.ref_tri.as<uint32_t>(), slot_pos);
-  LAUNCH(ctx, k_tri_records, div_up(nt, 256), 256, 0, nt, ctx->d_pos9.as<float>(), ctx->d_tri_inst.as<uint32_t>(),
-         ctx->d_inst_alpha.as<float>(), ctx->d_tris48.as<Tri48>());
+  LAUNCH(ctx, k_tri_records, div_up(n, 256), 256, 0, n, slot_pos, ba.sorted_ids.as<uint32_t>(), ba.ref_tri.as<uint32_t>(),
+         ctx->d_pos9.as<float>(), ctx->d_tri_inst.as<uint32_t>(), ctx->d_inst_alpha.as<float>(), ctx->d_tris48.as<Tri48>());
   mark(ctx, 5);
   uint32_t res[4] = {0, 0, 0, 0};  // depth, nodes, triangle slots, error
   RTF_CUDA(cudaMemcpyAsync(res, &cs->depth, 16, cudaMemcpyDeviceToHost, st));

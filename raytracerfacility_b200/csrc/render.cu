@@ -71,7 +71,7 @@ struct SrcRays {
 template <bool STATS>
 __global__ void __launch_bounds__(kTraceBlock, RTF_TRACE_MIN_BLOCKS) k_trace_rays(DevScene sc, SrcRays src, uint32_t* work) {
   __shared__ TraceSmem sm;
-  trace_engine<STATS>(sc.nodes, sc.tris, sc.tri_idx, src, work, sm);
+  trace_engine<STATS>(sc.nodes, sc.tris, src, work, sm);
 }
 
 // Persistent-lane kernels run one resident wave: SMs x the blocks of THIS kernel variant that fit on an SM (its register
@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(kTraceBlock, ALPHA ? RTF_QUEUE_MIN_BLOCKS : RT
   const uint32_t n = q.count[wave];
   if (blockIdx.x == 0 && threadIdx.x == 0 && stats) atomicAdd(stats, (unsigned long long)n);
   SrcQueue<ALPHA> src{q.ray_a[qi], q.ray_b[qi], q.hits, n, tmin, ALPHA ? sc.inst_alpha : nullptr, sc, pm, seed, (uint32_t)wave};
-  trace_engine<false>(sc.nodes, sc.tris, sc.tri_idx, src, q.work + wave, sm);
+  trace_engine<false>(sc.nodes, sc.tris, src, q.work + wave, sm);
 }
 
 // ---- shade one wavefront: ClosestHitFunc (RayFunctions.cuh:25-172) / MissFunc (:260-272), unrolled ------
@@ -737,6 +737,7 @@ int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp,
   bind(ctx, q, ps, false);
   const uint64_t tris_per_batch = cap / per_probe;
   RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, ctx->stream));
+  ctx->stats_cached = false;
   uint64_t paths_total = 0;
   for (uint64_t t0 = tri_begin; t0 < tri_end; t0 += tris_per_batch) {
     const uint32_t nt = (uint32_t)((tri_end - t0) < tris_per_batch ? (tri_end - t0) : tris_per_batch);
@@ -796,7 +797,7 @@ struct SrcGrid {
 };
 __global__ void __launch_bounds__(kTraceBlock) k_scan_grid(DevScene sc, SrcGrid src, uint32_t* work) {
   __shared__ TraceSmem sm;
-  trace_engine<false>(sc.nodes, sc.tris, sc.tri_idx, src, work, sm);
+  trace_engine<false>(sc.nodes, sc.tris, src, work, sm);
 }
 // CudaModule::SamplePointCloud's AoS samples (112 B in-out): read in the converged prepare phase, written back with
 // the full HitInfo of __closesthit__PCS_R (PointCloudScanning.cu:15-28).
@@ -833,7 +834,7 @@ struct SrcSamples {
 };
 __global__ void __launch_bounds__(kTraceBlock) k_scan_samples(DevScene sc, SrcSamples src, uint32_t* work) {
   __shared__ TraceSmem sm;
-  trace_engine<false>(sc.nodes, sc.tris, sc.tri_idx, src, work, sm);
+  trace_engine<false>(sc.nodes, sc.tris, src, work, sm);
 }
 
 int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin, uint64_t ray_end, float* d_t,
@@ -990,6 +991,7 @@ int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, cons
   bind(ctx, q, ps, true);
   const uint64_t px_per_batch = cap / spp;
   RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, ctx->stream));
+  ctx->stats_cached = false;
   for (uint64_t p0 = px_begin; p0 < n_pixels; p0 += px_per_batch) {
     const uint32_t np = (uint32_t)((n_pixels - p0) < px_per_batch ? (n_pixels - p0) : px_per_batch);
     const size_t paths = (size_t)np * spp;

@@ -72,8 +72,7 @@ struct DevMaterial {
 // Everything a kernel needs to trace and shade, passed by value.
 struct DevScene {
   const uint4* nodes = nullptr;
-  const float4* tris = nullptr;        // one 48 B record per triangle, primitive order
-  const uint32_t* tri_idx = nullptr;   // per triangle reference (leaf-slot order): its triangle
+  const float4* tris = nullptr;
   const float* pos9 = nullptr;
   const float* nrm9 = nullptr;
   const uint32_t* tri_inst = nullptr;
@@ -123,7 +122,7 @@ struct BuildArrays {
   DevBuf keys_alt, ids_alt, level_a, level_b;
   DevBuf ref_cnt, ref_first, ref_tri, ref_box, scan_state;  // triangle references (pre-splitting)
   DevBuf sort_hist, sort_status;                            // radix sort scratch (rtf_sort.cuh)
-  DevBuf collapse_state;                                    // level table + tickets + grid barrier of k_collapse
+  DevBuf collapse_state, slot_pos;                          // k_collapse: level table + tickets + grid barrier; per leaf slot its sorted reference
 };
 
 struct Workspace {  // wavefront queues + path state, sized for `capacity` paths
@@ -184,7 +183,6 @@ struct rtf_ctx {
   uint32_t n_refs = 0;  // triangle references in the BVH (>= n_tris when long triangles are pre-split)
   int presplit = 8;     // option "presplit": most references one triangle may be cut into (1 = off)
   int collapse_blocks = 0;  // resident k_collapse blocks per SM (occupancy query at the first build)
-  rtf::DevBuf d_tri_idx;
   rtf::DevBuf d_pos9, d_nrm9, d_tri_inst, d_nodes, d_tris48, d_insts, d_mats, d_inst_alpha, d_btfs, d_env_faces;
   rtf::BuildArrays ba;
   rtf::Workspace ws;
@@ -192,6 +190,7 @@ struct rtf_ctx {
   size_t pipe_chunk_rays = (size_t)1 << 22;  // option "pipe_chunk_rays"
   rtf::DevScene scene;
   uint64_t last_rays = 0, last_paths = 0;
+  bool stats_cached = false;  // last_rays already holds the job's total (multi-band camera frames sum it on the host)
   rtf::DevBuf d_stats;  // {rays u64, paths u64}
   // options (rtf_set_option)
   size_t batch_paths = (size_t)1 << 24;  // 2^24 paths: ~3 GB of queues + path state; +12..20 % over 2^22 (fewer, fuller waves)
@@ -203,6 +202,13 @@ struct rtf_ctx {
   rtf_ray_props cam_last_rp;
   uint64_t cam_last_epoch = 0;
   bool cam_last_valid = false;
+  // multi-GPU (multi.cu): rank of this context in its communicator; comm is an ncclComm_t
+  void* comm = nullptr;
+  bool own_comm = false;
+  int rank = 0, nranks = 1;
+  rtf::DevBuf d_shard_out, d_small;
+  cudaEvent_t phase_ev[4] = {nullptr, nullptr, nullptr, nullptr};  // compute | collective | finalize | end of the last sharded call
+  bool phase_valid = false;
   // build-stage events: flatten | bounds+morton | sort | karras+refit | collapse | end
   cudaEvent_t build_ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   float build_ms[6] = {0, 0, 0, 0, 0, 0};
@@ -223,6 +229,11 @@ int bake_skinned(rtf_ctx* ctx, Geometry& g, const void* sverts, size_t nv, size_
 int make_probes_device(rtf_ctx* ctx, uint64_t tri_begin, uint64_t tri_end, int front, int back, rtf_illum_sampler* d_out);
 int flux_probes_device(rtf_ctx* ctx, const rtf_illum_sampler* d_probes, uint64_t n, float* out8_host);
 int flux_mesh_device(rtf_ctx* ctx, const float* d_energy6, uint64_t tri_begin, uint64_t tri_end, int faces, float* out8_host);
+// multi.cu
+void shard_range(uint64_t n, int nranks, int rank, uint64_t* b, uint64_t* e);
+int illum_sharded_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push, int front,
+                         int back, int mode, float* d_out6);
+int render_camera_sharded(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, int outputs_mask);
 // build.cu
 int build_bvh(rtf_ctx* ctx, int morton_bits);
 int refit_bvh(rtf_ctx* ctx);
@@ -242,6 +253,7 @@ int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin
 int scan_samples_device(rtf_ctx* ctx, rtf_pc_sample* d_samples, size_t n, uint32_t* d_prim);
 int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, uint64_t px_begin,
                          uint64_t px_end);
+int render_camera_bands(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, const int* rows, int n_bands);
 int sample_texture_device(rtf_ctx* ctx, const DevTexture& tex, size_t n, const float* d_uv, float* d_rgba);
 int sample_environment_device(rtf_ctx* ctx, const rtf_env* env, size_t n, const float* d_pos_dir6, float* d_rgb);
 int btf_eval_device(rtf_ctx* ctx, const DevBTF& btf, size_t n, const float* d_in14, float* d_rgb);

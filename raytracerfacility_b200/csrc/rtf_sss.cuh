@@ -144,7 +144,7 @@ RTF_D void ss_probe(const DevScene& sc, float3 o, float3 d, float tmin, float tm
         stack[sp++] = n1.x + (uint32_t)__popc(imask & ((1u << j) - 1u));
       } else {
         for (uint32_t b = 0; b < cnt; b++) {
-          const float4* tp = sc.tris + (size_t)__ldg(sc.tri_idx + slot_first + b) * 3;
+          const float4* tp = sc.tris + (size_t)(slot_first + b) * 3;
           const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
           float t, bu, bv;
           if (!ss_tri_test(o, mx, my, mz, t0, t1, t2, t, bu, bv)) continue;

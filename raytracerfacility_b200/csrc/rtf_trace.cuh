@@ -110,8 +110,7 @@ struct __align__(128) TraceSmem {
 //   void fetch(raw, base, slot, a, b, tmin, tag)              a = {o.xyz, *}, b = {d.xyz, tmax}
 //   void store(index, tag, hit, node_visits, tri_visits)
 template <bool STATS, class Src>
-RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restrict__ tris,
-                        const uint32_t* __restrict__ tri_idx, const Src& src,
+RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const Src& src,
                         uint32_t* __restrict__ work, TraceSmem& sm) {
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -348,7 +347,7 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
         const uint32_t ts = (pos * 11u) >> 5;  // pos / 3 for pos < 24
         const uint32_t below = (cur.y >> 8) & ~(0xffffffffu << (2u * ts));  // 2-bit triangle counts of the slots below s
         const uint32_t ti = (pos - 3u * ts) + (uint32_t)__popc(below) + (uint32_t)__popc(below & 0xAAAAu);
-        const float4* tp = tris + (size_t)__ldg(tri_idx + tg.x + ti) * 3;  // leaf slot -> shared triangle record
+        const float4* tp = tris + (size_t)(tg.x + ti) * 3;
         const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
         if (STATS) tvis++;
         const float3 A = f3(t0.x - o.x, t0.y - o.y, t0.z - o.z);

@@ -39,6 +39,15 @@ EXPORTS = [
     "rtf_btf_eval", "rtf_set_geometry_instanced", "rtf_set_geometry_skinned", "rtf_geometry_read_baked",
     "rtf_prepare_light_probes", "rtf_illumination_flux", "rtf_illumination_flux_mesh_device", "rtf_sss_probe",
     "rtf_commit_stats",
+    # multi-GPU (csrc/multi.cu)
+    "rtf_comm_unique_id", "rtf_comm_init_rank", "rtf_comm_destroy", "rtf_comm_rank", "rtf_comm_barrier",
+    "rtf_comm_reduce_f64", "rtf_shard_range", "rtf_estimate_illumination_mesh_sharded_device",
+    "rtf_estimate_illumination_mesh_sharded", "rtf_scan_grid_trace_sharded_device", "rtf_render_camera_sharded",
+    "rtf_phase_timings", "rtf_create_multi", "rtf_multi_destroy", "rtf_multi_size", "rtf_multi_ctx",
+    "rtf_multi_set_geometry", "rtf_multi_set_material", "rtf_multi_set_instance", "rtf_multi_set_option",
+    "rtf_multi_commit", "rtf_multi_estimate_illumination_mesh", "rtf_multi_scan_grid_trace", "rtf_multi_trace_closest",
+    "rtf_multi_camera_create", "rtf_multi_camera_destroy", "rtf_multi_camera_resize", "rtf_multi_camera_set",
+    "rtf_multi_camera_get_props", "rtf_multi_render_camera", "rtf_multi_camera_download",
 ]
 
 
@@ -57,6 +66,10 @@ def lib():
     if _lib is None:
         if not os.path.exists(LIB_PATH):
             raise ImportError(f"{LIB_PATH} is missing: build it with __graft_entry__.build(); there is no CPU fallback")
+        try:  # the library links libnccl.so.2: let torch's bundled NCCL be the one the process loads (same soname;
+            import torch  # noqa: F401  loading the system one first would leave torch.distributed with a mismatched NCCL)
+        except ImportError:
+            pass
         L = C.CDLL(LIB_PATH)
         L.rtf_last_error.restype = C.c_char_p
         L.rtf_version.restype = C.c_char_p
@@ -416,6 +429,62 @@ class RayTracer:
         return _check(lib().rtf_render_camera_rows(self.h, C.byref(env), camera.h, C.byref(ray_props), int(row_begin),
                                                    int(row_end))) == 1
 
+
+    # ---- multi-GPU, one process per GPU: the library's own NCCL communicator (csrc/multi.cu) ----
+    @staticmethod
+    def comm_unique_id():
+        buf = (C.c_ubyte * 128)()
+        _check(lib().rtf_comm_unique_id(buf, C.c_size_t(128)))
+        return bytes(buf)
+
+    def comm_init_rank(self, nranks, rank, unique_id):
+        idb = (C.c_ubyte * 128).from_buffer_copy(unique_id) if unique_id is not None else None
+        _check(lib().rtf_comm_init_rank(self.h, int(nranks), int(rank), idb))
+
+    def comm_destroy(self):
+        _check(lib().rtf_comm_destroy(self.h))
+
+    def comm_rank(self):
+        r, n = C.c_int(), C.c_int()
+        _check(lib().rtf_comm_rank(self.h, C.byref(r), C.byref(n)))
+        return r.value, n.value
+
+    def comm_barrier(self):
+        _check(lib().rtf_comm_barrier(self.h))
+
+    def comm_reduce(self, values, op="max"):
+        v = np.ascontiguousarray(values, dtype=np.float64).reshape(-1).copy()
+        _check(lib().rtf_comm_reduce_f64(self.h, _p(v), int(len(v)), 1 if op == "max" else 0))
+        return v
+
+    def estimate_illumination_mesh_sharded_device(self, env, ray_props, seed, push, front, back, mode, dev_out6_ptr):
+        _check(lib().rtf_estimate_illumination_mesh_sharded_device(self.h, C.byref(env), C.byref(ray_props), C.c_uint32(seed),
+                                                                   C.c_float(push), int(front), int(back), int(mode),
+                                                                   C.c_void_p(dev_out6_ptr)))
+
+    def estimate_illumination_mesh_sharded(self, env, ray_props, seed, push=0.001, front=True, back=True, mode=0):
+        out = np.zeros((self.triangle_count, 6), dtype=np.float32)
+        _check(lib().rtf_estimate_illumination_mesh_sharded(self.h, C.byref(env), C.byref(ray_props), C.c_uint32(seed),
+                                                            C.c_float(push), int(front), int(back), int(mode), _p(out)))
+        return out
+
+    def scan_grid_sharded_device(self, grid, gather, dev_t_ptr, dev_prim_ptr, dev_inst_ptr=None):
+        b, e = C.c_uint64(), C.c_uint64()
+        _check(lib().rtf_scan_grid_trace_sharded_device(self.h, C.byref(grid), int(gather), C.c_void_p(dev_t_ptr),
+                                                        C.c_void_p(dev_prim_ptr), C.c_void_p(dev_inst_ptr), C.byref(b),
+                                                        C.byref(e)))
+        return b.value, e.value
+
+    def render_to_camera_sharded(self, env, camera, ray_props, outputs_mask=1):
+        return _check(lib().rtf_render_camera_sharded(self.h, C.byref(env), camera.h, C.byref(ray_props),
+                                                      int(outputs_mask))) == 1
+
+    def phase_timings(self):
+        """{compute, collective, finalize} device ms of the last sharded call."""
+        out = (C.c_float * 3)()
+        _check(lib().rtf_phase_timings(self.h, out))
+        return {"compute_ms": float(out[0]), "collective_ms": float(out[1]), "finalize_ms": float(out[2])}
+
     # ---- parity read-back ----
     def debug(self, what):
         nbytes = C.c_uint64()
@@ -425,12 +494,10 @@ class RayTracer:
         _check(lib().rtf_debug_read(self.h, int(what), _p(out), nbytes))
         return out
 
-    def debug_upload_bvh(self, nodes, tris, tri_idx, depth):
-        """nodes: wide nodes; tris: one record per triangle (primitive order); tri_idx: triangle of every leaf slot."""
+    def debug_upload_bvh(self, nodes, tris, depth):
         nodes, tris = np.ascontiguousarray(nodes), np.ascontiguousarray(tris)
-        tri_idx = np.ascontiguousarray(tri_idx, dtype=np.uint32)
         _check(lib().rtf_debug_upload_bvh(self.h, _p(nodes), C.c_uint64(len(nodes)), _p(tris), C.c_uint64(len(tris)),
-                                          _p(tri_idx), C.c_uint64(len(tri_idx)), int(depth)))
+                                          int(depth)))
 
     def microbench_fp32(self):
         v = C.c_double()
@@ -441,6 +508,118 @@ class RayTracer:
         v = C.c_double()
         _check(lib().rtf_microbench_l2(self.h, C.c_double(footprint_bytes), C.byref(v)))
         return v.value
+
+
+def shard_range(n, nranks, rank):
+    b, e = C.c_uint64(), C.c_uint64()
+    _check(lib().rtf_shard_range(C.c_uint64(int(n)), int(nranks), int(rank), C.byref(b), C.byref(e)))
+    return b.value, e.value
+
+
+class _Borrowed(RayTracer):
+    """A context owned by a MultiRayTracer (never destroyed from here)."""
+
+    def __init__(self, handle, device):
+        self.h, self.device = handle, device
+
+    def destroy(self):
+        self.h = C.c_void_p()
+
+
+class MultiCamera:
+    def __init__(self, mrt):
+        self.h = C.c_void_p()
+        _check(lib().rtf_multi_camera_create(mrt.h, C.byref(self.h)))
+        pp = C.POINTER(S.CameraProps)()
+        _check(lib().rtf_multi_camera_get_props(self.h, C.byref(pp)))
+        self.props = pp.contents
+
+    def resize(self, width, height):
+        _check(lib().rtf_multi_camera_resize(self.h, int(width), int(height)))
+
+    def set(self, position, rotation_wxyz=(1.0, 0.0, 0.0, 0.0)):
+        _check(lib().rtf_multi_camera_set(self.h, (C.c_float * 3)(*position), (C.c_float * 4)(*rotation_wxyz)))
+
+    def download(self, which=S.OUT_COLOR):
+        out = np.empty((self.props.height, self.props.width, 4), dtype=np.float32)
+        _check(lib().rtf_multi_camera_download(self.h, int(which), _p(out)))
+        return out
+
+    def destroy(self):
+        if self.h:
+            lib().rtf_multi_camera_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+class MultiRayTracer:
+    """One process driving several GPUs through rtf_create_multi (ncclCommInitAll inside the library)."""
+
+    def __init__(self, devices):
+        self.devices = [int(d) for d in devices]
+        self.h = C.c_void_p()
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        _check(lib().rtf_create_multi(arr, len(self.devices), C.byref(self.h)))
+
+    def destroy(self):
+        if self.h:
+            lib().rtf_multi_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def ctx(self, rank):
+        c = C.c_void_p()
+        _check(lib().rtf_multi_ctx(self.h, int(rank), C.byref(c)))
+        return _Borrowed(c, self.devices[rank])
+
+    def set_option(self, name, value):
+        _check(lib().rtf_multi_set_option(self.h, name.encode(), C.c_int64(int(value))))
+
+    def load_scene(self, desc, morton_bits=63):
+        for gh, (v, t) in desc.geometries.items():
+            v = np.ascontiguousarray(v)
+            t = np.ascontiguousarray(t, dtype=np.uint32).reshape(-1, 3)
+            _check(lib().rtf_multi_set_geometry(self.h, C.c_uint64(gh), _p(v), C.c_size_t(len(v)), C.c_size_t(80), _p(t),
+                                                C.c_size_t(len(t)), C.c_uint64(0)))
+        for mh, m in desc.materials.items():
+            _check(lib().rtf_multi_set_material(self.h, C.c_uint64(mh), C.byref(m)))
+        for ih, (g, m, x, comp) in desc.instances.items():
+            x = np.ascontiguousarray(x, dtype=np.float32).reshape(16)
+            _check(lib().rtf_multi_set_instance(self.h, C.c_uint64(ih), C.c_uint64(g), C.c_uint64(m), _p(x), C.c_uint64(comp)))
+        for r in range(len(self.devices)):  # textures / BTFs / cube map: per-context calls, repeated for every device
+            c = self.ctx(r)
+            for th, img in getattr(desc, "textures", {}).items():
+                c.set_texture(th, img)
+            for mh, tex in getattr(desc, "material_textures", {}).items():
+                c.set_material_textures(mh, *tex)
+            for bh, tables in getattr(desc, "btfs", {}).items():
+                c.set_btf(bh, tables)
+            for mh, bh in getattr(desc, "material_btf", {}).items():
+                c.set_material_btf(mh, bh)
+            c.set_environment_map(getattr(desc, "env_map", None))
+        _check(lib().rtf_multi_commit(self.h, int(morton_bits)))
+
+    def estimate_illumination_mesh(self, env, ray_props, seed, push=0.001, front=True, back=True, mode=0):
+        out = np.zeros((self.ctx(0).triangle_count, 6), dtype=np.float32)
+        _check(lib().rtf_multi_estimate_illumination_mesh(self.h, C.byref(env), C.byref(ray_props), C.c_uint32(seed),
+                                                          C.c_float(push), int(front), int(back), int(mode), _p(out)))
+        return out
+
+    def scan_grid(self, grid):
+        n = self.ctx(0).scan_grid_ray_count(grid)
+        t, prim, inst = np.empty(n, np.float32), np.empty(n, np.uint32), np.empty(n, np.uint32)
+        _check(lib().rtf_multi_scan_grid_trace(self.h, C.byref(grid), _p(t), _p(prim), _p(inst)))
+        return t, prim, inst
+
+    def trace_closest(self, rays, out=None):
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+        hits = out if out is not None else np.empty(len(rays), dtype=S.HIT_DTYPE)
+        _check(lib().rtf_multi_trace_closest(self.h, _p(rays), C.c_size_t(len(rays)), _p(hits)))
+        return hits
+
+    def create_camera(self):
+        return MultiCamera(self)
+
+    def render_to_camera(self, env, camera, ray_props, outputs_mask=1):
+        return _check(lib().rtf_multi_render_camera(self.h, C.byref(env), camera.h, C.byref(ray_props), int(outputs_mask))) == 1
 
 
 class CudaModule:

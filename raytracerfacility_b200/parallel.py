@@ -1,6 +1,8 @@
 """Multi-GPU sharding of the three entry points: one process per GPU (torch.distributed), BVH replicated,
 work split, at most one collective per job.  The reference is single-GPU (CUDAModule.cpp:25
-`cudaSetDevice(0)`), so this layer is new; it only ever calls the C ABI through module.RayTracer.
+`cudaSetDevice(0)`), so this layer is new.  The sharding and the NCCL collectives live in the C library
+(csrc/multi.cu); DistributedRayTracer below is a thin mirror of its rtf_*_sharded entry points, and the pure functions
+of this file restate the partitioning rules for the CPU (gloo) tests of the host logic.
 
 * illumination: SAMPLE-sharded (rank r traces samples [r*S/G, (r+1)*S/G) of every triangle), partial sums
   {sum E, sum D} per triangle, ONE all-reduce(sum) of 6*nTris floats, then finalize (IlluminationEstimation.cu:125-128).
@@ -93,73 +95,58 @@ def illumination_triangle_sharded(n_tris, compute_range, all_gather, world, rank
 
 
 class DistributedRayTracer:
-    """One RayTracer per rank + the collectives.  Scene calls are replicated (every rank builds the same BVH)."""
+    """One RayTracer per rank (one process per GPU).  A thin mirror: sharding AND collectives run inside librtf_b200.so on
+    the library's own NCCL communicator (csrc/multi.cu: rtf_comm_init_rank + the rtf_*_sharded entry points);
+    torch.distributed only carries the 128-byte communicator id from rank 0 to the others at start-up.  Scene calls are
+    replicated (every rank commits the same scene).  Stream contract: the context and every tensor handed to it live on
+    ONE non-default torch stream (self.stream), so allocation, kernels and collectives are ordered."""
 
-    def __init__(self, rt, rank=0, world=1, group=None):
+    def __init__(self, rt, rank=0, world=1, group=None, stream=None):
+        import torch
         self.rt, self.rank, self.world, self.group = rt, rank, world, group
+        dev = torch.device("cuda", rt.device)
+        if stream is None:
+            stream = torch.cuda.Stream(device=dev)
+            rt.set_stream(stream.cuda_stream)
+        self.stream = stream
+        cur_rank, cur_n = rt.comm_rank()
+        if world > 1 and cur_n != world:
+            import torch.distributed as dist
+            box = [rt.comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(box, src=0, group=group)
+            rt.comm_init_rank(world, rank, box[0])
 
     def estimate_illumination_mesh(self, env, ray_props, seed, push=0.001, front=True, back=True, mode="sample"):
         """Returns a CUDA float32 tensor (n_tris, 6) = {energy, direction}, identical on all ranks."""
         import torch
-        import torch.distributed as dist
         rt = self.rt
         n = rt.triangle_count
-        faces = int(bool(front)) + int(bool(back))
-        dev = torch.device("cuda", rt.device)
-        if mode == "sample":
-            accum = torch.zeros(n * 6, dtype=torch.float32, device=dev)
-
-            def compute_partial(s0, s1, acc):
-                rt.estimate_illumination_mesh_device(env, ray_props, seed, push, front, back, 0, n, s0, s1, acc.data_ptr())
-
-            def finalize(acc, f, s):
-                rt.illumination_finalize_device(acc.data_ptr(), n, f, s)
-
-            def all_reduce_sum(acc):
-                dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=self.group)
-
-            illumination_sample_sharded(n, ray_props.samples, faces, compute_partial, finalize, all_reduce_sum,
-                                        self.world, self.rank, accum)
-            return accum.view(n, 6)
-        # triangle mode
-        out = torch.zeros(n * 6, dtype=torch.float32, device=dev)
-        t0, t1 = split_range(n, self.world, self.rank)
-        if t1 > t0:
-            rt.estimate_illumination_mesh_device(env, ray_props, seed, push, front, back, t0, t1, 0, ray_props.samples,
-                                                 out.data_ptr())
-            rt.illumination_finalize_device(out.data_ptr() + 24 * t0, t1 - t0, faces, ray_props.samples)
-        if self.world > 1:
-            parts = [out[6 * b:6 * e] for b, e in (split_range(n, self.world, r) for r in range(self.world))]
-            if len({p.numel() for p in parts}) == 1:
-                dist.all_gather(parts, parts[self.rank].clone(), group=self.group)
-            else:
-                for r, p in enumerate(parts):
-                    dist.broadcast(p, src=r, group=self.group)
+        with torch.cuda.stream(self.stream):
+            out = torch.empty(n * 6, dtype=torch.float32, device=torch.device("cuda", rt.device))
+            rt.estimate_illumination_mesh_sharded_device(env, ray_props, seed, push, front, back,
+                                                         0 if mode == "sample" else 1, out.data_ptr())
         return out.view(n, 6)
 
     def scan_grid(self, grid, gather=False):
-        """Each rank traces its contiguous ray range into device SoA tensors (t, prim); optional all-gather."""
+        """Each rank traces its contiguous ray range into elements [b, e) of full-size device tensors (t, prim); gather
+        completes them on every rank.  Returns ((b, e), t, prim) with the rank's slices, or the full arrays if gathered."""
         import torch
-        import torch.distributed as dist
         rt = self.rt
         total = rt.scan_grid_ray_count(grid)
-        b, e = split_range(total, self.world, self.rank)
-        dev = torch.device("cuda", rt.device)
-        t = torch.empty(e - b, dtype=torch.float32, device=dev)
-        prim = torch.empty(e - b, dtype=torch.int32, device=dev)
-        if e > b:
-            rt.scan_grid_device(grid, b, e, t.data_ptr(), prim.data_ptr())
-        if not gather or self.world == 1:
-            return (b, e), t, prim
-        sizes = [split_range(total, self.world, r) for r in range(self.world)]
-        full_t = torch.empty(total, dtype=torch.float32, device=dev)
-        full_p = torch.empty(total, dtype=torch.int32, device=dev)
-        for r, (rb, re) in enumerate(sizes):
-            if r == self.rank:
-                full_t[rb:re], full_p[rb:re] = t, prim
-            dist.broadcast(full_t[rb:re], src=r, group=self.group)
-            dist.broadcast(full_p[rb:re], src=r, group=self.group)
-        return (0, total), full_t, full_p
+        with torch.cuda.stream(self.stream):
+            dev = torch.device("cuda", rt.device)
+            t = torch.empty(total, dtype=torch.float32, device=dev)
+            prim = torch.empty(total, dtype=torch.int32, device=dev)
+            b, e = rt.scan_grid_sharded_device(grid, gather, t.data_ptr(), prim.data_ptr())
+        if gather and self.world > 1:
+            return (0, total), t, prim
+        return (b, e), t[b:e], prim[b:e]
+
+    def render_to_camera(self, env, camera, ray_props, outputs=(0,)):
+        mask = 0
+        for w in outputs:
+            mask |= 1 << int(w)
+        return self.rt.render_to_camera_sharded(env, camera, ray_props, mask)
 
 
 # ---- camera: interleaved row bands (load balance: sky rows are cheap, canopy rows are not) + ONE all-gather --------
@@ -197,51 +184,3 @@ def image_bands_sharded(height, width, channels, render_rows, all_gather_into, w
 def default_band_rows(height, world):
     """16 bands per rank: enough interleaving to balance sky against canopy, few enough calls to keep batches large."""
     return int(height) if world == 1 else max(BAND_ROWS, int(height) // (16 * world))
-
-
-class _DeviceArray:
-    """Zero-copy torch view of a raw device pointer (__cuda_array_interface__)."""
-
-    def __init__(self, ptr, shape):
-        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
-
-
-def _camera_frame_tensor(camera, which, device):
-    import torch
-    h, w = camera.props.height, camera.props.width
-    return torch.as_tensor(_DeviceArray(camera.device_buffer(which), (h, w, 4)), device=device)
-
-
-def render_to_camera_sharded(drt, env, camera, ray_props, outputs=(0,)):
-    """DistributedRayTracer camera render: every rank renders its interleaved row bands into its own camera buffers,
-    then one all-gather per requested output (structs.OUT_COLOR / OUT_NORMAL / OUT_ALBEDO) completes the frame on all
-    ranks.  Progressive accumulation state stays rank-local per band."""
-    import torch
-    import torch.distributed as dist
-    rt = drt.rt
-    dev = torch.device("cuda", rt.device)
-    h, w = camera.props.height, camera.props.width
-    band_rows = default_band_rows(h, drt.world)
-    bands = camera_bands(h, drt.world, drt.rank, band_rows)
-    modified = camera.props.modified
-    ok = True
-    for i, (r0, r1) in enumerate(bands):
-        # every band of one frame must see the same frame id / modified flag (the C call advances them per call)
-        camera.props.modified = modified if i == 0 else 0
-        if i > 0:
-            camera.props.frame_id = first_frame_id
-        ok = rt.render_to_camera_rows(env, camera, ray_props, r0, r1) and ok
-        if i == 0:
-            first_frame_id = camera.props.frame_id - 1
-    if not bands:
-        rt.render_to_camera_rows(env, camera, ray_props, 0, 0)
-    if drt.world > 1:
-        for which in outputs:
-            frame = _camera_frame_tensor(camera, which, dev)
-            image_bands_sharded(h, w, 4, lambda r0, r1: None,
-                                lambda out, local: dist.all_gather_into_tensor(out, local, group=drt.group), drt.world,
-                                drt.rank, frame, band_rows)
-    return ok
-
-
-DistributedRayTracer.render_to_camera = render_to_camera_sharded

@@ -160,9 +160,9 @@ assert PC_SAMPLE_DTYPE.itemsize == 112 and NODE_DTYPE.itemsize == 80 and TRI_DTY
 
 DBG_MORTON, DBG_SORTED_IDS, DBG_BIN_CHILDREN, DBG_BIN_PARENT, DBG_BIN_BOXES = 0, 1, 2, 3, 4
 DBG_WIDE_NODES, DBG_WIDE_TRIS, DBG_FLAT_POS, DBG_FLAT_NRM, DBG_FLAT_INST, DBG_SCENE_BOUNDS = 5, 6, 7, 8, 9, 10
-DBG_REF_TRI, DBG_REF_BOX, DBG_TRI_IDX = 11, 12, 13
+DBG_REF_TRI, DBG_REF_BOX = 11, 12
 DEFAULT_PRESPLIT = 8  # librtf_b200's default for rtf_set_option("presplit")
-DBG_DTYPES = {DBG_REF_TRI: np.dtype("<u4"), DBG_REF_BOX: np.dtype("<f4"), DBG_TRI_IDX: np.dtype("<u4"),
+DBG_DTYPES = {DBG_REF_TRI: np.dtype("<u4"), DBG_REF_BOX: np.dtype("<f4"),
               DBG_MORTON: np.dtype("<u8"), DBG_SORTED_IDS: np.dtype("<u4"), DBG_BIN_CHILDREN: np.dtype("<i4"),
               DBG_BIN_PARENT: np.dtype("<i4"), DBG_BIN_BOXES: np.dtype("<f4"), DBG_WIDE_NODES: NODE_DTYPE,
               DBG_WIDE_TRIS: TRI_DTYPE, DBG_FLAT_POS: np.dtype("<f4"), DBG_FLAT_NRM: np.dtype("<f4"),

@@ -14,8 +14,7 @@ def _compare_all(rt, osc, S):
                        (S.DBG_SCENE_BOUNDS, "scene bounds"), (S.DBG_REF_TRI, "reference triangles"),
                        (S.DBG_REF_BOX, "reference boxes"), (S.DBG_MORTON, "morton"), (S.DBG_SORTED_IDS, "sorted ids"),
                        (S.DBG_BIN_CHILDREN, "children"), (S.DBG_BIN_PARENT, "parent"), (S.DBG_BIN_BOXES, "boxes"),
-                       (S.DBG_WIDE_NODES, "wide nodes"), (S.DBG_WIDE_TRIS, "triangle records"),
-                       (S.DBG_TRI_IDX, "leaf-slot triangle indices")]:
+                       (S.DBG_WIDE_NODES, "wide nodes"), (S.DBG_WIDE_TRIS, "wide tris")]:
         assert_bit_equal(rt.debug(what), osc.debug(what), name)
 
 

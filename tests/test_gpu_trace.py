@@ -26,7 +26,7 @@ def test_oracle_bvh_uploaded(rt, orc, S, scenes):
     """Traversal in isolation: BVH built by the oracle, uploaded, traced on the GPU."""
     sd = scenes.random_soup(3000, seed=21, size=0.25)
     osc = orc.OracleScene(sd, 63)
-    rt.debug_upload_bvh(osc.debug(S.DBG_WIDE_NODES), osc.debug(S.DBG_WIDE_TRIS), osc.debug(S.DBG_TRI_IDX), osc.depth)
+    rt.debug_upload_bvh(osc.debug(S.DBG_WIDE_NODES), osc.debug(S.DBG_WIDE_TRIS), osc.depth)
     lo, hi = scenes.scene_bounds(sd)
     rays = scenes.incoherent_rays(50000, lo, hi, seed=4)
     assert_bit_equal(rt.trace_closest(rays), osc.trace(rays), "hits")

@@ -56,9 +56,7 @@ def _check_tree(osc, S):
                 assert np.all(boxes[idx, :3] >= boxes[i, :3]) and np.all(boxes[idx, 3:] <= boxes[i, 3:])
         assert seen[0] == 0 and np.all(seen[1:] == 1)
     nodes, tris = osc.debug(S.DBG_WIDE_NODES), osc.debug(S.DBG_WIDE_TRIS)
-    idx = osc.debug(S.DBG_TRI_IDX)
-    assert sorted(idx.tolist()) == ref_tri.tolist()  # every reference exactly once in the leaf slots
-    assert tris["prim"].tolist() == list(range(osc.n_tris))  # one record per triangle, primitive order
+    assert sorted(tris["prim"].tolist()) == ref_tri.tolist()  # every reference exactly once
     pos = osc.debug(S.DBG_FLAT_POS).reshape(-1, 3, 3)
     assert_bit_equal(tris["v0"], pos[tris["prim"], 0], "tri v0")
     # quantised child boxes contain the triangles they lead to (leaf slots checked directly)
@@ -68,7 +66,7 @@ def _check_tree(osc, S):
             t0 = int(nd["tri_base"]) + off
             lo = nd["p"] + nd["qlo"][:, s].astype(np.float32) * scale
             hi = nd["p"] + nd["qhi"][:, s].astype(np.float32) * scale
-            for t in tris[idx[t0:t0 + cnt]]:  # the slot holds (at least) one reference box of each of its triangles
+            for t in tris[t0:t0 + cnt]:  # the slot holds (at least) one reference box of each of its triangles
                 rb = ref_box[ref_tri == t["prim"]]
                 assert (np.all(rb[:, :3] >= lo, axis=1) & np.all(rb[:, 3:] <= hi, axis=1)).any()
     # child_base / imask consistency: internal children are contiguous, BFS order

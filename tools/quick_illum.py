@@ -39,7 +39,7 @@ def main():
         _o = _orc.OracleScene(sd, 63)
         _nodes, _tris = _o.debug(_S.DBG_WIDE_NODES), _o.debug(_S.DBG_WIDE_TRIS)
         print(f"oracle BVH: {len(_nodes)} nodes, {len(_tris)} triangle refs, depth {_o.depth}", flush=True)
-        rt.debug_upload_bvh(_nodes, _tris, _o.debug(_S.DBG_TRI_IDX), _o.depth)
+        rt.debug_upload_bvh(_nodes, _tris, _o.depth)
     n = args.tris or rt.triangle_count
     env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=4, samples=args.samples)
     acc = torch.zeros(rt.triangle_count * 6, dtype=torch.float32, device=dev)

@@ -37,7 +37,7 @@ def main():
         _o = _orc.OracleScene(sd, 63)
         _nodes, _tris = _o.debug(_S.DBG_WIDE_NODES), _o.debug(_S.DBG_WIDE_TRIS)
         print(f"oracle BVH: {len(_nodes)} nodes, {len(_tris)} triangle refs, depth {_o.depth}", flush=True)
-        rt.debug_upload_bvh(_nodes, _tris, _o.debug(_S.DBG_TRI_IDX), _o.depth)
+        rt.debug_upload_bvh(_nodes, _tris, _o.depth)
     lo, hi = scenes.scene_bounds(sd)
     n = 1 << args.log2_rays
     rays = scenes.incoherent_rays_torch(n, lo, hi, seed=3, device=dev)
