@@ -473,6 +473,10 @@ RTF_API int rtf_scan_grid_trace_sharded_device(rtf_ctx* ctx, const rtf_scan_grid
  * every rank (one group of broadcasts each).  Pixels keep their global RNG streams: bit-identical to the 1-GPU frame. */
 RTF_API int rtf_render_camera_sharded(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* ray_props,
                                       int outputs_mask);
+/* rtf_set_option(ctx, "profile", 1): an event pair around every wavefront kernel; rtf_profile_read returns the device
+ * milliseconds per category since the last read {ray generation, traversal, shading, reduction / resolve, ray sort,
+ * other} and consumes the records (SURVEY §5 tracing row: the reference has no timing at all). */
+RTF_API int rtf_profile_read(rtf_ctx* ctx, float* ms6);
 /* {compute, collective, finalize} device milliseconds of the context's last sharded call (CUDA events) */
 RTF_API int rtf_phase_timings(rtf_ctx* ctx, float* ms3);
 

@@ -89,6 +89,7 @@ int rtf_destroy(rtf_ctx* ctx) {
     }
     cudaStreamDestroy(ctx->pipe.in), cudaStreamDestroy(ctx->pipe.out);
   }
+  for (cudaEvent_t e : ctx->prof.pool) cudaEventDestroy(e);
   for (cudaEvent_t e : ctx->phase_ev)
     if (e) cudaEventDestroy(e);
   ctx->d_shard_out.release(), ctx->d_small.release();
@@ -371,14 +372,6 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
     if ((rc = build_bvh(ctx, morton_bits))) return rc;
     ctx->commits_full++;
   }
-  {  // shrink the node array to its final size (collapse allocated the n/2 worst case)
-    DevBuf exact;
-    if ((rc = exact.reserve(80 * (size_t)ctx->n_nodes))) return rc;
-    RTF_CUDA(cudaMemcpyAsync(exact.p, ctx->d_nodes.p, 80 * (size_t)ctx->n_nodes, cudaMemcpyDeviceToDevice, st));
-    RTF_CUDA(cudaStreamSynchronize(st));
-    ctx->d_nodes.release();
-    ctx->d_nodes = exact;
-  }
   }
   ctx->alpha_class = alpha_class;
   ctx->geom_dirty = false, ctx->mat_dirty = false, ctx->topo_dirty = false;
@@ -438,6 +431,10 @@ int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value) {
       return RTF_ERR_INVALID;
     }
     ctx->brdf = (int)value;
+  } else if (!strcmp(name, "profile")) {  // per-category kernel time (rtf_profile_read); switching resets the sums
+    cudaStreamSynchronize(ctx->stream);
+    ctx->prof.on = value != 0;
+    ctx->prof.recs.clear(), ctx->prof.used = 0;
   } else if (!strcmp(name, "refit")) {
     ctx->refit = value != 0;
   } else if (!strcmp(name, "sort_rays")) {
@@ -446,6 +443,20 @@ int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value) {
     set_error(std::string("unknown option ") + name);
     return RTF_ERR_INVALID;
   }
+  return RTF_OK;
+}
+// Device milliseconds per kernel category since the last read (option "profile" = 1): {ray generation, traversal,
+// shading, reduction / resolve, ray sort, other}; the records are consumed.
+int rtf_profile_read(rtf_ctx* ctx, float* ms6) {
+  CHECK_CTX(ctx);
+  if (!ms6) return RTF_ERR_INVALID;
+  for (int k = 0; k < PROF_COUNT; k++) ms6[k] = 0.0f;
+  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+  for (const Profiler::Rec& r : ctx->prof.recs) {
+    float ms = 0.0f;
+    if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess && r.cat >= 0 && r.cat < PROF_COUNT) ms6[r.cat] += ms;
+  }
+  ctx->prof.recs.clear(), ctx->prof.used = 0;
   return RTF_OK;
 }
 int rtf_triangle_count(rtf_ctx* ctx, uint64_t* n) {

@@ -312,8 +312,8 @@ __global__ void k_refit(const float* __restrict__ ref_box, const uint32_t* __res
 // ---- 7. collapse to 8-wide: ONE persistent cooperative kernel for all breadth-first levels ----------------------------
 // The node layout is breadth first (a node's internal children are consecutive in the next level, its triangles
 // consecutive in the index array), so a level needs the exclusive prefix sums of its nodes' child and triangle counts.
-// Each block takes 128-node tiles of the current level in ticket order: greedy expansion + slot assignment per node
-// (registers only), a block scan, a decoupled look-back over the tile descriptors of the level (Merrill & Garland), then
+// Each WARP takes 32-node tiles of the current level in ticket order: greedy expansion + slot assignment per node
+// (registers only), a warp scan, a decoupled look-back over the tile descriptors of the level (Merrill & Garland), then
 // the nodes are encoded and the next level's roots written — one pass per level, no intermediate arrays.  Levels are
 // separated by a grid barrier; the level sizes never leave the device (the previous version ran four launches per level
 // and read two counters back to the host after each: 2.5 ms of a 4.8 ms build were that).
@@ -459,12 +459,11 @@ __device__ __forceinline__ void collapse_emit(const CollapseArgs& a, int R, cons
 
 // Tile descriptor of the look-back: bits 62..63 = state (1 aggregate, 2 inclusive prefix), bits 32..61 = internal
 // children, bits 0..31 = triangles (references <= 2^31, nodes < 2^30: the fields cannot carry into each other).
+constexpr int kCollapseTile = 32;  // nodes per tile: one WARP owns a tile, so a level runs without block barriers
 __global__ void __launch_bounds__(kCollapseBlock)
     k_collapse(CollapseArgs a, CollapseState* cs, unsigned long long* desc_all, int* lv_a, int* lv_b, Node80* __restrict__ nodes,
                uint32_t* __restrict__ slot_pos, uint32_t max_nodes, uint32_t max_level, unsigned* gbar) {
-  __shared__ uint32_t s_tile;
-  __shared__ unsigned long long s_warp[kCollapseBlock / 32], s_prefix;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
   int L = 0;
   for (;; L++) {
     if (L >= kCollapseLevels - 1) {
@@ -480,14 +479,13 @@ __global__ void __launch_bounds__(kCollapseBlock)
     const int* level = (L & 1) ? lv_b : lv_a;
     int* next = (L & 1) ? lv_a : lv_b;
     volatile unsigned long long* desc = desc_all + lv.desc_base;
-    const uint32_t tiles = (lv.n + kCollapseBlock - 1) / kCollapseBlock;
+    const uint32_t tiles = (lv.n + kCollapseTile - 1) / kCollapseTile;
     for (;;) {
-      __syncthreads();
-      if (threadIdx.x == 0) s_tile = atomicAdd(&cs->ticket[L], 1u);
-      __syncthreads();
-      const uint32_t tile = s_tile;
+      uint32_t tile = 0;
+      if (lane == 0) tile = atomicAdd(&cs->ticket[L], 1u);
+      tile = __shfl_sync(0xffffffffu, tile, 0);
       if (tile >= tiles) break;
-      const uint32_t li = tile * kCollapseBlock + threadIdx.x;
+      const uint32_t li = tile * kCollapseTile + (uint32_t)lane;
       const bool active = li < lv.n;
       int slot_child[8];
       uint32_t ci = 0, ct = 0;
@@ -496,6 +494,7 @@ __global__ void __launch_bounds__(kCollapseBlock)
         R = level[li];
         collapse_plan(a, R, slot_child, ci, ct);
       }
+      __syncwarp();
       const unsigned long long mine = ((unsigned long long)ci << 32) | ct;
       unsigned long long incl = mine;
 #pragma unroll
@@ -503,56 +502,44 @@ __global__ void __launch_bounds__(kCollapseBlock)
         const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, off);
         if (lane >= off) incl += t;
       }
-      if (lane == 31) s_warp[warp] = incl;
-      __syncthreads();
-      unsigned long long warp_off = 0, total = 0;
+      const unsigned long long total = __shfl_sync(0xffffffffu, incl, 31);
+      unsigned long long prefix = 0;
+      if (tile == 0) {
+        if (lane == 0) desc[0] = (2ull << 62) | total;
+      } else {
+        if (lane == 0) desc[tile] = (1ull << 62) | total;
+        int look = (int)tile - 1;
+        for (;;) {
+          const int idx = look - lane;
+          unsigned long long d = idx >= 0 ? desc[idx] : (2ull << 62);
+          while (__any_sync(0xffffffffu, (d >> 62) == 0ull)) d = idx >= 0 ? desc[idx] : (2ull << 62);
+          const unsigned done = __ballot_sync(0xffffffffu, (d >> 62) == 2ull);
+          const int first_done = done ? __ffs((int)done) - 1 : 32;
+          unsigned long long contrib = lane <= first_done ? (d & 0x3fffffffffffffffull) : 0ull;
 #pragma unroll
-      for (int w = 0; w < kCollapseBlock / 32; w++) {
-        if (w < warp) warp_off += s_warp[w];
-        total += s_warp[w];
-      }
-      if (warp == 0) {
-        unsigned long long prefix = 0;
-        if (tile == 0) {
-          if (lane == 0) desc[0] = (2ull << 62) | total;
-        } else {
-          if (lane == 0) desc[tile] = (1ull << 62) | total;
-          int look = (int)tile - 1;
-          for (;;) {
-            const int idx = look - lane;
-            unsigned long long d = idx >= 0 ? desc[idx] : (2ull << 62);
-            while (__any_sync(0xffffffffu, (d >> 62) == 0ull)) d = idx >= 0 ? desc[idx] : (2ull << 62);
-            const unsigned done = __ballot_sync(0xffffffffu, (d >> 62) == 2ull);
-            const int first_done = done ? __ffs((int)done) - 1 : 32;
-            unsigned long long contrib = lane <= first_done ? (d & 0x3fffffffffffffffull) : 0ull;
-#pragma unroll
-            for (int off = 16; off >= 1; off >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, off);
-            prefix += contrib;
-            if (done) break;
-            look -= 32;
-          }
-          if (lane == 0) desc[tile] = (2ull << 62) | (prefix + total);
+          for (int off = 16; off >= 1; off >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, off);
+          prefix += contrib;
+          if (done) break;
+          look -= 32;
         }
-        if (lane == 0) {
-          s_prefix = prefix;
-          if (tile == tiles - 1) {  // the level's totals: the next level's size and cursors
-            const unsigned long long all = prefix + total;
-            CollapseLevel nx;
-            nx.n = (uint32_t)(all >> 32), nx.start = lv.start + lv.n, nx.tri_cursor = lv.tri_cursor + (uint32_t)all;
-            nx.desc_base = lv.desc_base + tiles;
-            level_store(&cs->level[L + 1], nx);
-          }
-        }
+        if (lane == 0) desc[tile] = (2ull << 62) | (prefix + total);
       }
-      __syncthreads();
+      if (lane == 0 && tile == tiles - 1) {  // the level's totals: the next level's size and cursors
+        const unsigned long long all = prefix + total;
+        CollapseLevel nx;
+        nx.n = (uint32_t)(all >> 32), nx.start = lv.start + lv.n, nx.tri_cursor = lv.tri_cursor + (uint32_t)all;
+        nx.desc_base = lv.desc_base + tiles;
+        level_store(&cs->level[L + 1], nx);
+      }
       if (active) {
-        const unsigned long long excl = s_prefix + warp_off + (incl - mine);
+        const unsigned long long excl = prefix + (incl - mine);
         const uint32_t child_off = (uint32_t)(excl >> 32), tri_off = (uint32_t)excl;
         collapse_emit(a, R, slot_child, lv.start + lv.n + child_off, lv.tri_cursor + tri_off, next + child_off,
                       nodes + lv.start + li, slot_pos);
       }
+      __syncwarp();
     }
-    // grid barrier between levels (all blocks are resident: cooperative launch): generation counter
+    // grid barrier between levels (all blocks are resident: cooperative launch): arrival counter
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -697,7 +684,7 @@ static int collapse_encode(rtf_ctx* ctx, uint32_t n) {
   mark(ctx, 4);
   const size_t max_nodes = (size_t)n / 2 + 64;
   const size_t max_level = (size_t)n / 4 + 64;
-  const size_t max_tiles = max_nodes / kCollapseBlock + kCollapseLevels + 2;
+  const size_t max_tiles = max_nodes / kCollapseTile + kCollapseLevels + 2;
   if ((rc = ctx->d_nodes.reserve(80 * max_nodes))) return rc;
   if ((rc = ba.slot_pos.reserve(4 * (size_t)n))) return rc;
   if ((rc = ctx->d_tris48.reserve(48 * (size_t)n))) return rc;
@@ -725,7 +712,7 @@ static int collapse_encode(rtf_ctx* ctx, uint32_t n) {
   Node80* nodes = ctx->d_nodes.as<Node80>();
   uint32_t* slot_pos = ba.slot_pos.as<uint32_t>();
   uint32_t mn = (uint32_t)max_nodes, ml = (uint32_t)max_level;
-  const unsigned want = div_up(max_level, kCollapseBlock);
+  const unsigned want = div_up(max_level, kCollapseBlock);  // more blocks than the widest level has tiles would only spin
   const unsigned full = (unsigned)ctx->sm_count * (unsigned)ctx->collapse_blocks;
   void* args[] = {&ca, &cs, &desc, &lva, &lvb, &nodes, &slot_pos, &mn, &ml, &gbar};
   RTF_CUDA(cudaLaunchCooperativeKernel((const void*)k_collapse, dim3(want < full ? want : full), dim3(kCollapseBlock), args, 0, st));

@@ -27,6 +27,14 @@ static_assert(kSmemStack + kLocalStack == kMaxStackDepth, "stack split must cove
     (ctx)->launches++;                                               \
   } while (0)
 
+#define LAUNCH_P(ctx, cat, kernel, grid, block, smem, ...)            \
+  do {                                                               \
+    (ctx)->prof.begin((cat), (ctx)->stream);                         \
+    kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__); \
+    (ctx)->launches++;                                               \
+    (ctx)->prof.end((ctx)->stream);                                  \
+  } while (0)
+
 static inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
 
 constexpr uint32_t kShadowBit = 0x80000000u;   // first-hit ray (TERMINATE_ON_FIRST_HIT | DISABLE_ANYHIT | DISABLE_CLOSESTHIT)
@@ -698,17 +706,20 @@ static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_
     const float tmin = (camera && w == 0) ? 0.0f : 1e-3f;
     if (ctx->sort_rays && w >= 1) {  // bounce rays leave the surfaces in random directions: restore some coherence
       int rc;
-      if ((rc = sort_wavefront(ctx, q, qi, w, paths))) return rc;
+      ctx->prof.begin(PROF_SORT, ctx->stream);
+      rc = sort_wavefront(ctx, q, qi, w, paths);
+      ctx->prof.end(ctx->stream);
+      if (rc) return rc;
       qi ^= 1;
     }
     if (ctx->scene.has_alpha)
-      LAUNCH(ctx, k_trace_queue<true>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
+      LAUNCH_P(ctx, PROF_TRACE, k_trace_queue<true>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
     else
-      LAUNCH(ctx, k_trace_queue<false>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
+      LAUNCH_P(ctx, PROF_TRACE, k_trace_queue<false>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
     if (sss)
-      LAUNCH(ctx, k_shade<true>, div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
+      LAUNCH_P(ctx, PROF_SHADE, k_shade<true>, div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
     else
-      LAUNCH(ctx, k_shade<false>, div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
+      LAUNCH_P(ctx, PROF_SHADE, k_shade<false>, div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
     qi ^= 1;
   }
   return RTF_OK;
@@ -744,10 +755,10 @@ int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp,
     const size_t paths = (size_t)nt * per_probe;
     RTF_CUDA(cudaMemsetAsync(ctx->ws.counters.p, 0, 4096, ctx->stream));
     IllumGen g{t0, nt, sc_, (uint32_t)s0, (uint32_t)rp->samples, seed, push, front, back, d_probes, probe_base};
-    LAUNCH(ctx, k_gen_illum, div_up(paths, 256), 256, 0, ctx->scene, g, q, ps);
+    LAUNCH_P(ctx, PROF_GEN, k_gen_illum, div_up(paths, 256), 256, 0, ctx->scene, g, q, ps);
     PathMap pm{0, 0ull, t0, (uint32_t)per_probe, sc_, (uint32_t)s0, (uint32_t)rp->samples};
     if ((rc = run_wavefronts(ctx, env, rp->bounces, seed, pm, paths, q, ps, false))) return rc;
-    LAUNCH(ctx, k_reduce_illum, div_up((size_t)nt * 32, 256), 256, 0, nt, sc_, ps, d_accum6 + 6 * (t0 - tri_begin));
+    LAUNCH_P(ctx, PROF_REDUCE, k_reduce_illum, div_up((size_t)nt * 32, 256), 256, 0, nt, sc_, ps, d_accum6 + 6 * (t0 - tri_begin));
     paths_total += paths;
   }
   RTF_CUDA(cudaGetLastError());
@@ -757,7 +768,7 @@ int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp,
 
 int illum_finalize_device(rtf_ctx* ctx, float* d_accum6, uint64_t n, int faces, int samples, rtf_illum_sampler* d_probes) {
   if (n == 0) return RTF_OK;
-  LAUNCH(ctx, k_finalize_illum, div_up(n, 256), 256, 0, d_accum6, n, faces, samples, d_probes);
+  LAUNCH_P(ctx, PROF_REDUCE, k_finalize_illum, div_up(n, 256), 256, 0, d_accum6, n, faces, samples, d_probes);
   RTF_CUDA(cudaGetLastError());
   return RTF_OK;
 }
@@ -861,7 +872,7 @@ int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin
     SrcGrid src{*grid, row, -(int)(column / 2), -(int)(row / 2),
                 normalize3(f3(grid->direction[0], grid->direction[1], grid->direction[2])), off, m,
                 d_t ? d_t + o : nullptr, d_prim ? d_prim + o : nullptr, d_inst ? d_inst + o : nullptr, ctx->scene.tri_inst};
-    LAUNCH(ctx, k_scan_grid, trace_grid(ctx, TK_GRID, k_scan_grid, m), kTraceBlock, 0, ctx->scene, src, work);
+    LAUNCH_P(ctx, PROF_TRACE, k_scan_grid, trace_grid(ctx, TK_GRID, k_scan_grid, m), kTraceBlock, 0, ctx->scene, src, work);
   }
   RTF_CUDA(cudaGetLastError());
   return RTF_OK;
@@ -877,7 +888,7 @@ int scan_samples_device(rtf_ctx* ctx, rtf_pc_sample* d_samples, size_t n, uint32
   uint32_t* work = ctx->ws.counters.as<uint32_t>();
   RTF_CUDA(cudaMemsetAsync(work, 0, 4, ctx->stream));
   SrcSamples src{ctx->scene, d_samples, d_prim, (uint32_t)n};
-  LAUNCH(ctx, k_scan_samples, trace_grid(ctx, TK_SAMPLES, k_scan_samples, n), kTraceBlock, 0, ctx->scene, src, work);
+  LAUNCH_P(ctx, PROF_TRACE, k_scan_samples, trace_grid(ctx, TK_SAMPLES, k_scan_samples, n), kTraceBlock, 0, ctx->scene, src, work);
   RTF_CUDA(cudaGetLastError());
   return RTF_OK;
 }
@@ -996,10 +1007,10 @@ int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, cons
     const uint32_t np = (uint32_t)((n_pixels - p0) < px_per_batch ? (n_pixels - p0) : px_per_batch);
     const size_t paths = (size_t)np * spp;
     RTF_CUDA(cudaMemsetAsync(ctx->ws.counters.p, 0, 4096, ctx->stream));
-    LAUNCH(ctx, k_gen_camera, div_up(paths, 256), 256, 0, cp, p0, np, spp, q, ps);
+    LAUNCH_P(ctx, PROF_GEN, k_gen_camera, div_up(paths, 256), 256, 0, cp, p0, np, spp, q, ps);
     PathMap pm{1, p0 * spp, 0ull, 0u, 0u, 0u, 0u};
     if ((rc = run_wavefronts(ctx, env, rp->bounces, (uint32_t)cp.frame_id, pm, paths, q, ps, true))) return rc;
-    LAUNCH(ctx, k_resolve_camera, div_up(np, 256), 256, 0, cp, p0, np, spp, ps, cam->color.as<float4>(),
+    LAUNCH_P(ctx, PROF_REDUCE, k_resolve_camera, div_up(np, 256), 256, 0, cp, p0, np, spp, ps, cam->color.as<float4>(),
            cam->normal.as<float4>(), cam->albedo.as<float4>());
   }
   RTF_CUDA(cudaGetLastError());

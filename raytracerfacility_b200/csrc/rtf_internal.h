@@ -125,6 +125,41 @@ struct BuildArrays {
   DevBuf collapse_state, slot_pos;                          // k_collapse: level table + tickets + grid barrier; per leaf slot its sorted reference
 };
 
+// Per-category device time of the wavefront kernels (option "profile"): an event pair around every launch, summed when
+// read (rtf_profile_read).  Categories follow the phases the bench reports.
+enum { PROF_GEN = 0, PROF_TRACE, PROF_SHADE, PROF_REDUCE, PROF_SORT, PROF_OTHER, PROF_COUNT };
+struct Profiler {
+  bool on = false;
+  std::vector<cudaEvent_t> pool;
+  size_t used = 0;
+  struct Rec {
+    int cat;
+    cudaEvent_t a, b;
+  };
+  std::vector<Rec> recs;
+  cudaEvent_t open_a = nullptr;
+  int open_cat = 0;
+  cudaEvent_t take() {
+    if (used == pool.size()) {
+      cudaEvent_t e = nullptr;
+      cudaEventCreate(&e);
+      pool.push_back(e);
+    }
+    return pool[used++];
+  }
+  void begin(int cat, cudaStream_t st) {
+    if (!on) return;
+    open_a = take(), open_cat = cat;
+    cudaEventRecord(open_a, st);
+  }
+  void end(cudaStream_t st) {
+    if (!on) return;
+    cudaEvent_t b = take();
+    cudaEventRecord(b, st);
+    recs.push_back(Rec{open_cat, open_a, b});
+  }
+};
+
 struct Workspace {  // wavefront queues + path state, sized for `capacity` paths
   size_t capacity = 0;
   DevBuf ray_a[2], ray_b[2], hits, counters;
@@ -189,6 +224,7 @@ struct rtf_ctx {
   rtf::HostPipe pipe;
   size_t pipe_chunk_rays = (size_t)1 << 22;  // option "pipe_chunk_rays"
   rtf::DevScene scene;
+  rtf::Profiler prof;
   uint64_t last_rays = 0, last_paths = 0;
   bool stats_cached = false;  // last_rays already holds the job's total (multi-band camera frames sum it on the host)
   rtf::DevBuf d_stats;  // {rays u64, paths u64}

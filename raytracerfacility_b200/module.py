@@ -43,7 +43,7 @@ EXPORTS = [
     "rtf_comm_unique_id", "rtf_comm_init_rank", "rtf_comm_destroy", "rtf_comm_rank", "rtf_comm_barrier",
     "rtf_comm_reduce_f64", "rtf_shard_range", "rtf_estimate_illumination_mesh_sharded_device",
     "rtf_estimate_illumination_mesh_sharded", "rtf_scan_grid_trace_sharded_device", "rtf_render_camera_sharded",
-    "rtf_phase_timings", "rtf_create_multi", "rtf_multi_destroy", "rtf_multi_size", "rtf_multi_ctx",
+    "rtf_phase_timings", "rtf_profile_read", "rtf_create_multi", "rtf_multi_destroy", "rtf_multi_size", "rtf_multi_ctx",
     "rtf_multi_set_geometry", "rtf_multi_set_material", "rtf_multi_set_instance", "rtf_multi_set_option",
     "rtf_multi_commit", "rtf_multi_estimate_illumination_mesh", "rtf_multi_scan_grid_trace", "rtf_multi_trace_closest",
     "rtf_multi_camera_create", "rtf_multi_camera_destroy", "rtf_multi_camera_resize", "rtf_multi_camera_set",
@@ -478,6 +478,12 @@ class RayTracer:
     def render_to_camera_sharded(self, env, camera, ray_props, outputs_mask=1):
         return _check(lib().rtf_render_camera_sharded(self.h, C.byref(env), camera.h, C.byref(ray_props),
                                                       int(outputs_mask))) == 1
+
+    def profile_read(self):
+        """Device ms per kernel category since the last read (set_option("profile", 1) first)."""
+        out = (C.c_float * 6)()
+        _check(lib().rtf_profile_read(self.h, out))
+        return dict(zip(("gen_ms", "trace_ms", "shade_ms", "reduce_ms", "sort_ms", "other_ms"), [float(x) for x in out]))
 
     def phase_timings(self):
         """{compute, collective, finalize} device ms of the last sharded call."""
