@@ -517,7 +517,7 @@ enum {
   RTF_DBG_MORTON = 0,       /* u64 per triangle reference (unsorted order)       */
   RTF_DBG_SORTED_IDS = 1,   /* u32 per triangle reference: sorted position -> reference */
   RTF_DBG_BIN_CHILDREN = 2, /* 2 x i32 per internal binary node (>=0 internal, <0 = ~leaf) */
-  RTF_DBG_BIN_PARENT = 3,   /* i32 per binary node: internals [0,n-1) then leaves [n-1, 2n-1) */
+  RTF_DBG_BIN_PARENT = 3,   /* oracle only (i32 per binary node); the CUDA builder has no parent array: 0 bytes */
   RTF_DBG_BIN_BOXES = 4,    /* 6 floats per binary node, same numbering            */
   RTF_DBG_WIDE_NODES = 5,   /* 80 B per wide node                                */
   RTF_DBG_WIDE_TRIS = 6,    /* 48 B per triangle reference, BVH (leaf-slot) order */

@@ -69,7 +69,7 @@ int rtf_destroy(rtf_ctx* ctx) {
   for (auto& g : ctx->geoms) g.second.d_verts.release(), g.second.d_tris.release();
   DevBuf* bufs[] = {&ctx->d_pos9, &ctx->d_nrm9, &ctx->d_tri_inst, &ctx->d_nodes, &ctx->d_tris48, &ctx->d_insts, &ctx->d_mats,
                     &ctx->d_inst_alpha, &ctx->d_stats, &ctx->ba.morton, &ctx->ba.sorted_keys, &ctx->ba.sorted_ids,
-                    &ctx->ba.children, &ctx->ba.parent, &ctx->ba.range, &ctx->ba.boxes, &ctx->ba.flags,
+                    &ctx->ba.children, &ctx->ba.range, &ctx->ba.boxes, &ctx->ba.seg, &ctx->ba.wide_src,
                     &ctx->ba.scene_bounds, &ctx->ba.keys_alt, &ctx->ba.ids_alt, &ctx->ba.ref_cnt, &ctx->ba.ref_first,
                     &ctx->ba.ref_tri, &ctx->ba.ref_box, &ctx->ba.scan_state, &ctx->ba.sort_hist, &ctx->ba.sort_status, &ctx->ba.level_a,
                     &ctx->ba.level_b, &ctx->ba.collapse_state, &ctx->ba.slot_pos, &ctx->ws.ray_a[0], &ctx->ws.ray_a[1], &ctx->ws.ray_b[0], &ctx->ws.ray_b[1],
@@ -281,7 +281,7 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
     return RTF_OK;
   }
   const bool keep_bvh_if_possible = was_ready && !ctx->geom_dirty;
-  const bool refit_if_possible = was_ready && ctx->geom_dirty && !ctx->topo_dirty && ctx->refit && ctx->n_refs > 0;
+  const bool refit_if_possible = was_ready && ctx->geom_dirty && !ctx->topo_dirty && ctx->refit && ctx->n_refs > 0 && ctx->refit_ok;
   const uint32_t old_tris = ctx->n_tris;
   ctx->ready = false, ctx->bvh_ok = false;
   int rc;
@@ -956,7 +956,6 @@ static const void* dbg_ptr(rtf_ctx* c, int what, uint64_t* bytes) {
     case RTF_DBG_MORTON: *bytes = n * 8; return c->ba.morton.p;
     case RTF_DBG_SORTED_IDS: *bytes = n * 4; return c->ba.sorted_ids.p;
     case RTF_DBG_BIN_CHILDREN: *bytes = ni * 8; return c->ba.children.p;
-    case RTF_DBG_BIN_PARENT: *bytes = (n ? 2 * n - 1 : 0) * 4; return c->ba.parent.p;
     case RTF_DBG_BIN_BOXES: *bytes = (n ? 2 * n - 1 : 0) * 24; return c->ba.boxes.p;
     case RTF_DBG_WIDE_NODES: *bytes = (uint64_t)c->n_nodes * 80; return c->d_nodes.p;
     case RTF_DBG_WIDE_TRIS: *bytes = n * 48; return c->d_tris48.p;
@@ -997,6 +996,7 @@ int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* nodes, uint64_t n_nodes, cons
   ctx->scene.n_nodes = (uint32_t)n_nodes;
   if (!ctx->ready) ctx->n_tris = (uint32_t)n_tris, ctx->scene.n_tris = (uint32_t)n_tris;
   ctx->n_refs = (uint32_t)n_tris;
+  ctx->refit_ok = false;  // the builder's arrays do not describe an uploaded tree
   ctx->ready = true;
   return RTF_OK;
 }

@@ -118,7 +118,8 @@ struct Instance {
 
 // Intermediate arrays of the builder kept for parity read-back (rtf_debug_read).
 struct BuildArrays {
-  DevBuf morton, sorted_keys, sorted_ids, children, parent, range, boxes, flags, scene_bounds;
+  DevBuf morton, sorted_keys, sorted_ids, children, range, boxes, scene_bounds;
+  DevBuf seg, wide_src;  // segment tree over the sorted leaf boxes (32 B entries); binary roots {R, 8 slot children} per wide node
   DevBuf keys_alt, ids_alt, level_a, level_b;
   DevBuf ref_cnt, ref_first, ref_tri, ref_box, scan_state;  // triangle references (pre-splitting)
   DevBuf sort_hist, sort_status;                            // radix sort scratch (rtf_sort.cuh)
@@ -201,6 +202,7 @@ struct rtf_ctx {
   // geom_dirty = a geometry or instance changed since the last commit (BVH rebuild); mat_dirty = only material-side
   // tables changed (materials, textures, BTFs, cube map: re-resolved without touching the BVH)
   bool geom_dirty = true, mat_dirty = true;
+  bool refit_ok = false;  // the builder arrays (sorted order, radix tree, wide_src, slot_pos) describe the committed tree
   bool topo_dirty = true;  // a geometry / instance appeared, vanished or changed its triangle count, or "presplit" changed
                            // (geom_dirty && !topo_dirty = vertices or transforms moved: candidates for the refit path)
   int refit = 0;           // option "refit"
