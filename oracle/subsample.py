@@ -1,0 +1,95 @@
+"""TEST INFRASTRUCTURE — sub-sample parity of the full-size BASELINE configurations against the CPU oracle.
+
+The counter-based RNG makes every triangle / ray / pixel independent of the others, so the oracle can redo every k-th
+unit of a job the GPU ran in full and must reproduce it (every 1024-th triangle for C3, every 1024-th
+ray for C4 with bit-exact ids, every 4096-th pixel for the cameras).  The same run is the timed CPU baseline of the
+configuration (SURVEY.md 8(d) "CPU baseline": the extrapolated rate alongside the sample size).
+
+Used by tests/test_gpu_configs.py and by bench.py's cpu_baseline legs only; the product never imports this.
+Tolerances: ids and LiDAR distances bit-exact; irradiance, direction and colour <= 1e-5 relative (north_star).
+"""
+import ctypes
+import time
+
+import numpy as np
+
+from raytracerfacility_b200 import structs as S
+
+from . import pyoracle as orc
+
+RTOL = 1e-5
+THREADS = 16  # the reference arm and every CPU baseline use min(hardware threads, 16): a box-independent core count
+
+
+def threads():
+    return max(1, min(int(orc.lib().orc_hardware_threads()), THREADS))
+
+
+def _excess(gpu, cpu, rtol=RTOL, atol=0.0):
+    """max over elements of |gpu - cpu| / (atol + rtol |cpu|): <= 1 means within tolerance."""
+    g, c = np.asarray(gpu, dtype=np.float64), np.asarray(cpu, dtype=np.float64)
+    den = atol + rtol * np.abs(c)
+    err = np.abs(g - c)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        q = np.where(err == 0.0, 0.0, err / den)
+    return float(np.nanmax(q)) if q.size else 0.0, float(err.max()) if err.size else 0.0
+
+
+def build(cfg, morton_bits=63):
+    t0 = time.perf_counter()
+    osc = orc.OracleScene(cfg.scene, morton_bits)
+    osc.set_brdf(cfg.brdf)
+    return osc, time.perf_counter() - t0
+
+
+def illumination(osc, cfg, gpu_out6, stride, seed, push, nthreads=None):
+    """gpu_out6: (n_tris, 6) finalised {energy, direction} of the whole job.  Oracle: triangles 0, stride, 2*stride, ..."""
+    nthreads = threads() if nthreads is None else nthreads
+    t0 = time.perf_counter()
+    cpu, st = osc.illum_mesh(cfg.env, cfg.rp, seed=seed, push=push, tri_stride=stride, nthreads=nthreads)
+    dt = time.perf_counter() - t0
+    gpu = np.asarray(gpu_out6)[::stride]
+    assert gpu.shape == cpu.shape, (gpu.shape, cpu.shape)
+    e_q, e_abs = _excess(gpu[:, :3], cpu[:, :3])
+    d_q, d_abs = _excess(gpu[:, 3:], cpu[:, 3:], atol=1e-5)
+    units = len(cpu) * cfg.rp.samples * 2
+    return {"ok": bool(e_q <= 1.0 and d_q <= 1.0), "sample": f"every {stride}-th triangle ({len(cpu)} triangles, {units} paths, "
+            f"{int(st.rays)} rays)", "energy_max_err_over_tol": e_q, "energy_max_abs_err": e_abs,
+            "direction_max_err_over_tol": d_q, "tolerance": "energy <= 1e-5 relative; direction <= 1e-5 relative + 1e-5",
+            "cpu_s": dt, "cpu_threads": nthreads, "cpu_triangle_samples_per_s": units / dt, "cpu_Mrays_per_s": st.rays / dt / 1e6,
+            "mean_rays_per_path": float(st.rays) / max(1, int(st.paths))}
+
+
+def lidar(osc, cfg, gpu_t, gpu_prim, stride, ray_begin=0, nthreads=None):
+    """gpu_t / gpu_prim: the scan's arrays from ray `ray_begin` on.  Bit-exact distances and primitive ids."""
+    nthreads = threads() if nthreads is None else nthreads
+    total = int(orc.lib().orc_scan_grid_count(ctypes.byref(cfg.grid)))
+    n = len(gpu_t)
+    first = (-ray_begin) % stride  # the oracle takes rays 0, stride, ... of the whole grid
+    t0 = time.perf_counter()
+    t, prim, inst, st = osc.scan_grid(cfg.grid, ray_begin=ray_begin + first, ray_end=min(total, ray_begin + n), stride=stride,
+                                      nthreads=nthreads)
+    dt = time.perf_counter() - t0
+    gt = np.asarray(gpu_t)[first::stride].view(np.uint32)
+    gp = np.asarray(gpu_prim)[first::stride].view(np.uint32)
+    same_t = bool(np.array_equal(gt, t.view(np.uint32)))
+    same_p = bool(np.array_equal(gp, prim.view(np.uint32)))
+    return {"ok": same_t and same_p, "sample": f"every {stride}-th ray ({len(t)} rays)", "prim_ids_bit_exact": same_p,
+            "distances_bit_exact": same_t, "hit_fraction_on_sample": float((prim != 0xFFFFFFFF).mean()) if len(prim) else 0.0,
+            "cpu_s": dt, "cpu_threads": nthreads, "cpu_Mrays_per_s": len(t) / dt / 1e6}
+
+
+def camera(osc, cfg, cam_props, gpu_color, stride, nthreads=None):
+    """gpu_color: (h, w, 4) colour buffer of frame 0.  Oracle: pixels 0, stride, ... (row-major)."""
+    nthreads = threads() if nthreads is None else nthreads
+    cp = S.CameraProps.from_buffer_copy(cam_props)
+    cp.frame_id = 0
+    t0 = time.perf_counter()
+    col, _, _, st = osc.camera(cfg.env, cfg.rp, cp, stride=stride, nthreads=nthreads)
+    dt = time.perf_counter() - t0
+    gpu = np.asarray(gpu_color).reshape(-1, 4)[::stride]
+    q, a = _excess(gpu, col)
+    paths = len(col) * cfg.rp.samples
+    return {"ok": bool(q <= 1.0), "sample": f"every {stride}-th pixel ({len(col)} pixels, {paths} paths, {int(st.rays)} rays)",
+            "colour_max_err_over_tol": q, "colour_max_abs_err": a, "tolerance": "<= 1e-5 relative", "cpu_s": dt,
+            "cpu_threads": nthreads, "cpu_Mpaths_per_s": paths / dt / 1e6, "cpu_Mrays_per_s": st.rays / dt / 1e6}

@@ -83,9 +83,9 @@ int rtf_destroy(rtf_ctx* ctx) {
   for (cudaEvent_t e : ctx->build_ev)
     if (e) cudaEventDestroy(e);
   if (ctx->pipe.init) {
-    for (int k = 0; k < 2; k++) {
+    for (int k = 0; k < HostPipe::kDepth; k++) {
       cudaEventDestroy(ctx->pipe.ev_in[k]), cudaEventDestroy(ctx->pipe.ev_done[k]), cudaEventDestroy(ctx->pipe.ev_out[k]);
-      ctx->pipe.rays[k].release(), ctx->pipe.hits[k].release();
+      ctx->pipe.rays[k].release(), ctx->pipe.hits[k].release(), ctx->pipe.aos[k].release(), ctx->pipe.aux[k].release();
     }
     cudaStreamDestroy(ctx->pipe.in), cudaStreamDestroy(ctx->pipe.out);
   }
@@ -431,6 +431,12 @@ int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value) {
       return RTF_ERR_INVALID;
     }
     ctx->brdf = (int)value;
+  } else if (!strcmp(name, "pipe_chunk_probes") || !strcmp(name, "pipe_chunk_samples")) {
+    if (value < 1 || value > ((int64_t)1 << 28)) {
+      set_error("pipe chunk sizes must be in [1, 2^28]");
+      return RTF_ERR_INVALID;
+    }
+    (name[11] == 'p' ? ctx->pipe_chunk_probes : ctx->pipe_chunk_samples) = (size_t)value;
   } else if (!strcmp(name, "profile")) {  // per-category kernel time (rtf_profile_read); switching resets the sums
     cudaStreamSynchronize(ctx->stream);
     ctx->prof.on = value != 0;
@@ -471,12 +477,18 @@ static int fetch_stats(rtf_ctx* ctx) {
   ctx->last_rays = s[0];
   return RTF_OK;
 }
+static int pipe_init(rtf_ctx* ctx);
 static int not_ready() {
   set_error("no acceleration structure (call rtf_commit)");
   return RTF_ERR_NOT_READY;
 }
 
 // ---- illumination ----------------------------------------------------------------------------------------
+// CudaModule::EstimateIlluminationRayTracing (CUDAModule.cpp:39-51, RayTracer.cu:606-653): AoS probes in host memory,
+// updated in place.  The reference uploads all probes, launches, synchronises and downloads them, serially.  Here probe
+// chunks run as a three-stage pipeline — H2D of chunk i+1 (copy-in stream), path tracing of chunk i (context stream),
+// D2H of chunk i-1 (copy-out stream) — so both PCIe directions and the SMs are busy at once.  A probe's RNG streams are
+// keyed by its index in the caller's array, so chunking does not change a single bit of the result.
 int rtf_estimate_illumination(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, rtf_illum_sampler* probes, size_t n,
                               uint32_t seed, float push) {
   CHECK_CTX(ctx);
@@ -485,16 +497,39 @@ int rtf_estimate_illumination(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_pr
   if (n == 0) return RTF_OK;            // reference: message + return (RayTracer.cu:612-615)
   int rc;
   cudaStream_t st = ctx->stream;
-  const size_t aos = n * sizeof(rtf_illum_sampler), acc = n * 24;
-  if ((rc = ctx->ws.io.reserve(aos + acc + 256))) return rc;
-  rtf_illum_sampler* d_probes = ctx->ws.io.as<rtf_illum_sampler>();
-  float* d_acc = (float*)((char*)ctx->ws.io.p + ((aos + 255) & ~(size_t)255));
-  RTF_CUDA(cudaMemcpyAsync(d_probes, probes, aos, cudaMemcpyHostToDevice, st));
-  RTF_CUDA(cudaMemsetAsync(d_acc, 0, acc, st));
-  if ((rc = illum_mesh_device(ctx, env, rp, seed, push, 1, 1, 0, n, 0, rp->samples, d_acc, d_probes, 0))) return rc;
-  if ((rc = illum_finalize_device(ctx, d_acc, n, 2, rp->samples, d_probes))) return rc;
-  RTF_CUDA(cudaMemcpyAsync(probes, d_probes, aos, cudaMemcpyDeviceToHost, st));
+  if ((rc = pipe_init(ctx))) return rc;
+  HostPipe& p = ctx->pipe;
+  const size_t chunk = ctx->pipe_chunk_probes ? ctx->pipe_chunk_probes : 1;
+  const size_t cm = n < chunk ? n : chunk;
+  for (int k = 0; k < HostPipe::kDepth; k++)
+    if ((rc = p.aos[k].reserve(cm * sizeof(rtf_illum_sampler))) || (rc = p.aux[k].reserve(cm * 24))) return rc;
+  RTF_CUDA(cudaStreamSynchronize(st));  // earlier work of the caller on the context stream
+  RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, st));
+  ctx->stats_hold = true, ctx->last_paths = 0;
+  size_t i = 0;
+  for (size_t off = 0; off < n && !rc; off += chunk, i++) {
+    const size_t m = (n - off) < chunk ? (n - off) : chunk;
+    const int b = (int)(i % HostPipe::kDepth);
+    rtf_illum_sampler* d_probes = p.aos[b].as<rtf_illum_sampler>();
+    float* d_acc = p.aux[b].as<float>();
+    if (i >= (size_t)HostPipe::kDepth) cudaStreamWaitEvent(p.in, p.ev_out[b], 0);  // the chunk before has left aos[b]
+    cudaMemcpyAsync(d_probes, probes + off, m * sizeof(rtf_illum_sampler), cudaMemcpyHostToDevice, p.in);
+    cudaEventRecord(p.ev_in[b], p.in);
+    cudaStreamWaitEvent(st, p.ev_in[b], 0);
+    cudaMemsetAsync(d_acc, 0, m * 24, st);
+    if ((rc = illum_mesh_device(ctx, env, rp, seed, push, 1, 1, off, off + m, 0, rp->samples, d_acc, d_probes, off))) break;
+    if ((rc = illum_finalize_device(ctx, d_acc, m, 2, rp->samples, d_probes))) break;
+    cudaEventRecord(p.ev_done[b], st);
+    cudaStreamWaitEvent(p.out, p.ev_done[b], 0);
+    cudaMemcpyAsync(probes + off, d_probes, m * sizeof(rtf_illum_sampler), cudaMemcpyDeviceToHost, p.out);
+    cudaEventRecord(p.ev_out[b], p.out);
+  }
+  ctx->stats_hold = false;
+  cudaStreamSynchronize(p.in);
+  cudaStreamSynchronize(p.out);
   RTF_CUDA(cudaStreamSynchronize(st));
+  if (rc) return rc;
+  RTF_CUDA(cudaGetLastError());
   return fetch_stats(ctx);
 }
 
@@ -584,6 +619,10 @@ int rtf_last_job_stats(rtf_ctx* ctx, uint64_t* rays, uint64_t* paths) {
 }
 
 // ---- LiDAR --------------------------------------------------------------------------------------------------
+// CudaModule::SamplePointCloud (CUDAModule.cpp:53-64, RayTracer.cu:758-795): AoS samples in host memory, updated in
+// place.  224 B cross PCIe per ray (112 up, 112 down) against ~0.3 ns of traversal, so the call is a copy pipeline:
+// chunk i+1 goes up while chunk i is traced and chunk i-1 comes down (full duplex), instead of the reference's serial
+// upload -> launch -> synchronise -> download.
 int rtf_scan_point_cloud(rtf_ctx* ctx, const rtf_env* env, rtf_pc_sample* samples, size_t n, uint32_t* prim_ids_out) {
   CHECK_CTX(ctx);
   (void)env;  // the reference passes it but PCS never reads it (RayTracer.cu:758-795)
@@ -595,15 +634,36 @@ int rtf_scan_point_cloud(rtf_ctx* ctx, const rtf_env* env, rtf_pc_sample* sample
     return RTF_ERR_LIMIT;
   }
   int rc;
-  const size_t aos = n * sizeof(rtf_pc_sample);
-  if ((rc = ctx->ws.io.reserve(aos + 256 + n * 4))) return rc;
-  rtf_pc_sample* d = ctx->ws.io.as<rtf_pc_sample>();
-  uint32_t* d_prim = (uint32_t*)((char*)ctx->ws.io.p + ((aos + 255) & ~(size_t)255));
-  RTF_CUDA(cudaMemcpyAsync(d, samples, aos, cudaMemcpyHostToDevice, ctx->stream));
-  if ((rc = scan_samples_device(ctx, d, n, d_prim))) return rc;
-  RTF_CUDA(cudaMemcpyAsync(samples, d, aos, cudaMemcpyDeviceToHost, ctx->stream));
-  if (prim_ids_out) RTF_CUDA(cudaMemcpyAsync(prim_ids_out, d_prim, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
-  RTF_CUDA(cudaStreamSynchronize(ctx->stream));
+  cudaStream_t st = ctx->stream;
+  if ((rc = pipe_init(ctx))) return rc;
+  HostPipe& p = ctx->pipe;
+  const size_t chunk = ctx->pipe_chunk_samples ? ctx->pipe_chunk_samples : 1;
+  const size_t cm = n < chunk ? n : chunk;
+  for (int k = 0; k < HostPipe::kDepth; k++)
+    if ((rc = p.aos[k].reserve(cm * sizeof(rtf_pc_sample))) || (rc = p.aux[k].reserve(cm * 4))) return rc;
+  RTF_CUDA(cudaStreamSynchronize(st));
+  size_t i = 0;
+  for (size_t off = 0; off < n && !rc; off += chunk, i++) {
+    const size_t m = (n - off) < chunk ? (n - off) : chunk;
+    const int b = (int)(i % HostPipe::kDepth);
+    rtf_pc_sample* d = p.aos[b].as<rtf_pc_sample>();
+    uint32_t* d_prim = p.aux[b].as<uint32_t>();
+    if (i >= (size_t)HostPipe::kDepth) cudaStreamWaitEvent(p.in, p.ev_out[b], 0);
+    cudaMemcpyAsync(d, samples + off, m * sizeof(rtf_pc_sample), cudaMemcpyHostToDevice, p.in);
+    cudaEventRecord(p.ev_in[b], p.in);
+    cudaStreamWaitEvent(st, p.ev_in[b], 0);
+    if ((rc = scan_samples_device(ctx, d, m, d_prim))) break;
+    cudaEventRecord(p.ev_done[b], st);
+    cudaStreamWaitEvent(p.out, p.ev_done[b], 0);
+    cudaMemcpyAsync(samples + off, d, m * sizeof(rtf_pc_sample), cudaMemcpyDeviceToHost, p.out);
+    if (prim_ids_out) cudaMemcpyAsync(prim_ids_out + off, d_prim, m * 4, cudaMemcpyDeviceToHost, p.out);
+    cudaEventRecord(p.ev_out[b], p.out);
+  }
+  cudaStreamSynchronize(p.in);
+  cudaStreamSynchronize(p.out);
+  RTF_CUDA(cudaStreamSynchronize(st));
+  if (rc) return rc;
+  RTF_CUDA(cudaGetLastError());
   return RTF_OK;
 }
 // column = uint(size.x / distance.x), row = uint(size.y / distance.y) (PointCloudScanner.cpp:71-75); the float -> unsigned
@@ -689,7 +749,7 @@ static int pipe_init(rtf_ctx* ctx) {
   if (p.init) return RTF_OK;
   RTF_CUDA(cudaStreamCreateWithFlags(&p.in, cudaStreamNonBlocking));
   RTF_CUDA(cudaStreamCreateWithFlags(&p.out, cudaStreamNonBlocking));
-  for (int k = 0; k < 2; k++) {
+  for (int k = 0; k < HostPipe::kDepth; k++) {
     RTF_CUDA(cudaEventCreateWithFlags(&p.ev_in[k], cudaEventDisableTiming));
     RTF_CUDA(cudaEventCreateWithFlags(&p.ev_done[k], cudaEventDisableTiming));
     RTF_CUDA(cudaEventCreateWithFlags(&p.ev_out[k], cudaEventDisableTiming));
@@ -711,18 +771,18 @@ int rtf_trace_closest(rtf_ctx* ctx, const float* rays, size_t n, void* hits) {
   int rc;
   if ((rc = pipe_init(ctx))) return rc;
   HostPipe& p = ctx->pipe;
-  for (int k = 0; k < 2; k++)
+  for (int k = 0; k < HostPipe::kDepth; k++)
     if ((rc = p.rays[k].reserve(chunk * 32)) || (rc = p.hits[k].reserve(chunk * 16))) return rc;
   RTF_CUDA(cudaStreamSynchronize(ctx->stream));  // earlier work of the caller on the context stream
   size_t i = 0;
   for (size_t off = 0; off < n; off += chunk, i++) {
     const size_t m = (n - off) < chunk ? (n - off) : chunk;
-    const int b = (int)(i & 1);
-    if (i >= 2) RTF_CUDA(cudaStreamWaitEvent(p.in, p.ev_done[b], 0));  // chunk i-2 no longer reads rays[b]
+    const int b = (int)(i % HostPipe::kDepth);
+    if (i >= (size_t)HostPipe::kDepth) RTF_CUDA(cudaStreamWaitEvent(p.in, p.ev_done[b], 0));  // the chunk before no longer reads rays[b]
     RTF_CUDA(cudaMemcpyAsync(p.rays[b].p, rays + off * 8, m * 32, cudaMemcpyHostToDevice, p.in));
     RTF_CUDA(cudaEventRecord(p.ev_in[b], p.in));
     RTF_CUDA(cudaStreamWaitEvent(ctx->stream, p.ev_in[b], 0));
-    if (i >= 2) RTF_CUDA(cudaStreamWaitEvent(ctx->stream, p.ev_out[b], 0));  // hits[b] of chunk i-2 has left the device
+    if (i >= (size_t)HostPipe::kDepth) RTF_CUDA(cudaStreamWaitEvent(ctx->stream, p.ev_out[b], 0));  // hits[b] of the chunk before has left the device
     if ((rc = trace_rays_device(ctx, p.rays[b].as<float4>(), m, p.hits[b].as<float4>(), nullptr, nullptr))) return rc;
     RTF_CUDA(cudaEventRecord(p.ev_done[b], ctx->stream));
     RTF_CUDA(cudaStreamWaitEvent(p.out, p.ev_done[b], 0));

@@ -747,9 +747,9 @@ int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp,
   PathState ps;
   bind(ctx, q, ps, false);
   const uint64_t tris_per_batch = cap / per_probe;
-  RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, ctx->stream));
+  if (!ctx->stats_hold) RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, ctx->stream));
   ctx->stats_cached = false;
-  uint64_t paths_total = 0;
+  uint64_t paths_total = ctx->stats_hold ? ctx->last_paths : 0;
   for (uint64_t t0 = tri_begin; t0 < tri_end; t0 += tris_per_batch) {
     const uint32_t nt = (uint32_t)((tri_end - t0) < tris_per_batch ? (tri_end - t0) : tris_per_batch);
     const size_t paths = (size_t)nt * per_probe;

@@ -176,8 +176,12 @@ struct Workspace {  // wavefront queues + path state, sized for `capacity` paths
 struct HostPipe {
   bool init = false;
   cudaStream_t in = nullptr, out = nullptr;
-  cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
-  DevBuf rays[2], hits[2];
+  // kDepth chunks in flight: with two, a buffer is busy for upload + kernel + download, so neither PCIe direction stays
+  // saturated (measured: 25 GB/s each way on the 112 B LiDAR records); four keep both directions and the SMs busy.
+  static constexpr int kDepth = 4;
+  cudaEvent_t ev_in[kDepth] = {}, ev_done[kDepth] = {}, ev_out[kDepth] = {};
+  DevBuf rays[kDepth], hits[kDepth];
+  DevBuf aos[kDepth], aux[kDepth];  // AoS entry points: record chunk (updated in place) + per-record side array
 };
 
 }  // namespace rtf
@@ -225,6 +229,9 @@ struct rtf_ctx {
   rtf::Workspace ws;
   rtf::HostPipe pipe;
   size_t pipe_chunk_rays = (size_t)1 << 22;  // option "pipe_chunk_rays"
+  size_t pipe_chunk_probes = (size_t)1 << 17;   // option "pipe_chunk_probes": 268 B IlluminationSampler records per chunk
+  size_t pipe_chunk_samples = (size_t)1 << 19;  // option "pipe_chunk_samples": 112 B PointCloudSample records per chunk
+  bool stats_hold = false;  // a chunked job is running: the ray / path counters keep adding up across its calls
   rtf::DevScene scene;
   rtf::Profiler prof;
   uint64_t last_rays = 0, last_paths = 0;

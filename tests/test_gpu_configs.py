@@ -5,7 +5,12 @@
       the whole job (1e-5); energies are bounded by the sky.
 * C4  100 M LiDAR rays over the 5 M-triangle field: ray-range shards concatenate to the whole scan bit for bit; rays that
       reach the ground report t = scanner height; primitive ids are valid.
-* C5  3840x2160 compressed-BTF render: row bands reproduce the full frame bit for bit."""
+* C5  3840x2160 compressed-BTF render: row bands reproduce the full frame bit for bit.
+
+AND against the CPU oracle on a sub-sample of the same full-size jobs (oracle/subsample.py; the counter RNG makes every
+triangle / ray / pixel independent): every 1024-th triangle of C3 (<= 1e-5), every 1024-th ray of C4 (distances and
+primitive ids bit-exact), every 4096-th pixel of C2 (both BRDFs) and C5 (<= 1e-5).  bench.py asserts nothing but reports
+the same checks at the full sample counts."""
 import numpy as np
 import pytest
 
@@ -30,6 +35,7 @@ def test_c3_ten_million_triangles_shards(rt, scenes, S):
 
     def run(t0, t1, s0, s1, finalize=True):
         acc = torch.zeros(n * 6, dtype=torch.float32, device=dev)
+        torch.cuda.synchronize()  # the fill runs on torch's stream, the job on the library's
         rt.estimate_illumination_mesh_device(env, rp, 0x5EED, 1e-3, True, True, t0, t1, s0, s1, acc.data_ptr())
         torch.cuda.synchronize()
         if finalize:
@@ -120,3 +126,53 @@ def test_c5_btf_4k_row_bands(rt, scenes, S):
     alb = full.download(S.OUT_ALBEDO)[..., :3]
     assert alb.std() > 0.01  # first-hit BTF colours vary with the view/illumination angles
     full.destroy(), bands.destroy()
+
+
+# ---- oracle sub-sample parity at full size (recipes: raytracerfacility_b200/configs.py) ---------------------------------
+def test_c3_oracle_subsample_every_1024th_triangle(rt, S):
+    from oracle import subsample as sub
+    from raytracerfacility_b200 import configs
+    cfg = configs.c3(samples=16)  # full 10 000 002-triangle geometry; 16 of the 256 samples keep the oracle to seconds
+    rt.load_scene(cfg.scene, 63)
+    assert rt.triangle_count == cfg.triangles == 10_000_002
+    gpu = rt.estimate_illumination_mesh(cfg.env, cfg.rp, configs.SEED, configs.PUSH)
+    osc, _ = sub.build(cfg)
+    par = sub.illumination(osc, cfg, gpu, 1024, configs.SEED, configs.PUSH)
+    assert par["ok"], par
+    # the sample-sharded entry point of the library (one rank: the all-reduce is skipped) gives the same numbers
+    sharded = rt.estimate_illumination_mesh_sharded(cfg.env, cfg.rp, configs.SEED, configs.PUSH)
+    assert sub.illumination(osc, cfg, sharded, 1024, configs.SEED, configs.PUSH)["ok"]
+
+
+def test_c4_oracle_subsample_every_1024th_ray_bit_exact(rt, S):
+    from oracle import subsample as sub
+    from raytracerfacility_b200 import configs, module
+    cfg = configs.c4()
+    rt.load_scene(cfg.scene, 63)
+    assert rt.triangle_count == 5_000_002
+    total = rt.scan_grid_ray_count(cfg.grid)
+    assert 0.99e8 <= total <= 1.01e8
+    osc, _ = sub.build(cfg)
+    b, e = module.shard_range(total, 8, 5)  # what rank 5 of 8 traces: a range that does not start on the stride
+    for rb, re in ((0, total), (b, e)):
+        t, prim, _ = rt.scan_grid(cfg.grid, rb, re)
+        par = sub.lidar(osc, cfg, t, prim, 1024, ray_begin=rb)
+        assert par["ok"] and par["hit_fraction_on_sample"] > 0.5, par
+
+
+@pytest.mark.parametrize("which", ["C2 lambert_ggx", "C2 reference", "C5"])
+def test_camera_configs_oracle_subsample_every_4096th_pixel(rt, S, which):
+    from oracle import subsample as sub
+    from raytracerfacility_b200 import configs
+    cfg = {"C2 lambert_ggx": lambda: configs.c2(S.BRDF_LAMBERT_GGX), "C2 reference": lambda: configs.c2(S.BRDF_REFERENCE),
+           "C5": lambda: configs.c5(spp=16)}[which]()  # C5: full 3840x2160 frame, 16 of the 64 spp
+    rt.set_option("brdf", cfg.brdf)
+    rt.load_scene(cfg.scene, 63)
+    cam = configs.setup_camera(rt.create_camera(), cfg)
+    assert rt.render_to_camera(cfg.env, cam, cfg.rp)
+    img = cam.download(S.OUT_COLOR)
+    osc, _ = sub.build(cfg)
+    par = sub.camera(osc, cfg, cam.props, img, 4096)
+    assert par["ok"], par
+    assert img[..., :3].std() > 0.02
+    cam.destroy()

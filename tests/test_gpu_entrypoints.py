@@ -262,3 +262,118 @@ def test_ray_sort_option_changes_nothing_but_order(rt, S, scenes):
     assert_bit_equal(out[0][2], out[1][2], "colour")
     assert out[0][1] == out[1][1] and out[0][3] == out[1][3]
     cam.destroy()
+
+
+# ---- state-machine edges the advisor asked for ---------------------------------------------------------------------------
+def test_replacing_a_texture_needs_a_new_commit(rt, mod, S, scenes):
+    """rtf_set_texture on an existing handle may move the texels: the committed material tables are stale until the next
+    rtf_commit, so jobs are refused (as after rtf_remove_texture) instead of reading freed memory."""
+    sd = scenes.materials_scene(seed=9)
+    rt.load_scene(sd, 63)
+    th = next(iter(sd.textures))
+    lo, hi = scenes.scene_bounds(sd)
+    rays = scenes.incoherent_rays(1024, lo, hi, seed=2)
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=2, samples=2)
+    before = rt.estimate_illumination_mesh(env, rp, seed=3)
+    h, w = sd.textures[th].shape[:2]
+    rt.set_texture(th, scenes.checker_texture(4 * w, 4 * h, seed=77))  # larger: the old allocation is released
+    with pytest.raises(mod.RtfError) as e:
+        rt.estimate_illumination_mesh(env, rp, seed=3)
+    assert e.value.code == mod.ERR_NOT_READY
+    with pytest.raises(mod.RtfError):
+        rt.trace_closest(rays)
+    rt.build_ias(63)
+    st = rt.commit_stats()
+    assert st["full"] == 1 and st["materials"] == 1  # material tables re-resolved, BVH kept
+    after = rt.estimate_illumination_mesh(env, rp, seed=3)
+    assert after.shape == before.shape and np.isfinite(after).all()
+    rt.set_texture(th, sd.textures[th])
+    rt.build_ias(63)
+    assert_bit_equal(rt.estimate_illumination_mesh(env, rp, seed=3), before, "texture restored")
+
+
+def test_camera_accumulation_restarts_after_a_commit(rt, S, scenes):
+    """The reference resets the progressive accumulation when the scene was rebuilt (RayTracer.cu:254 statusChanged from
+    m_requireUpdate, raised after BuildIAS, RayTracerLayer.cpp:382-389)."""
+    sd = scenes.sorghum_scene(1)
+    rt.load_scene(sd, 63)
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=2, samples=2)
+    cam = rt.create_camera()
+    cam.resize(64, 36)
+    cam.props.accumulate = 1
+    cam.set((0.0, 1.5, 4.0), (0.9950042, -0.0998334, 0.0, 0.0))
+    for k in range(3):
+        assert rt.render_to_camera(env, cam, rp) and cam.props.frame_id == k + 1
+    first = None
+    ih = max(sd.instances)
+    g, m, x, comp = sd.instances[ih]
+    x2 = x.copy()
+    x2[12] += 0.3
+    for refit in (0, 1):  # full rebuild, then the refit path
+        rt.set_option("refit", refit)
+        rt.set_instance(ih, g, m, x2 if refit == 0 else x, comp)
+        rt.build_ias(63)
+        assert rt.render_to_camera(env, cam, rp) and cam.props.frame_id == 1, "accumulation must restart"
+        assert rt.render_to_camera(env, cam, rp) and cam.props.frame_id == 2
+    # material-only commit
+    rt.set_material(1, S.Material(albedo=(0.9, 0.1, 0.1)))
+    rt.build_ias(63)
+    assert rt.commit_stats()["materials"] == 1
+    assert rt.render_to_camera(env, cam, rp) and cam.props.frame_id == 1
+    # a skipped commit (nothing changed) keeps accumulating
+    rt.build_ias(63)
+    assert rt.render_to_camera(env, cam, rp) and cam.props.frame_id == 2
+    cam.destroy()
+
+
+def test_scan_grid_rejects_degenerate_grids(rt, mod, S, scenes):
+    sd = scenes.random_soup(100, seed=3, size=0.4)
+    rt.load_scene(sd, 63)
+    good = scenes.lidar_grid(center=(0.0, 5.0, 0.0), size=(1.0, 1.0), distance=(0.1, 0.1))
+    assert rt.scan_grid_ray_count(good) > 0
+    for size, dist in (((1.0, 1.0), (0.0, 0.1)), ((1.0, 1.0), (-0.1, 0.1)), ((1.0, 1.0), (float("nan"), 0.1)),
+                       ((-1.0, 1.0), (0.1, 0.1)), ((float("inf"), 1.0), (0.1, 0.1)), ((1.0, 1.0), (1e-12, 1e-12))):
+        bad = scenes.lidar_grid(center=(0.0, 5.0, 0.0), size=(1.0, 1.0), distance=(0.1, 0.1))
+        bad.size[:] = size
+        bad.distance[:] = dist
+        with pytest.raises(mod.RtfError) as e:
+            rt.scan_grid_ray_count(bad)
+        assert e.value.code == mod.ERR_INVALID, (size, dist)
+        with pytest.raises(mod.RtfError):
+            rt.scan_grid(bad, 0, 1)
+    empty = scenes.lidar_grid(center=(0.0, 5.0, 0.0), size=(0.01, 0.01), distance=(0.1, 0.1))  # fewer than one cell: no rays
+    assert rt.scan_grid_ray_count(empty) == 0
+    t, prim, inst = rt.scan_grid(empty)
+    assert len(t) == 0 and len(prim) == 0
+
+
+def test_aos_entry_points_chunk_pipeline_is_bit_identical(rt, S, scenes, mod):
+    """The host-buffer entry points run as H2D / compute / D2H pipelines over record chunks; RNG streams are keyed by the
+    record's index in the caller's array, so any chunk size gives the bytes of the single-chunk call."""
+    sd = scenes.random_soup(900, seed=8, size=0.3)
+    rt.load_scene(sd, 63)
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=3, samples=8)
+    probes = mod.probes_from_scene(sd)
+    whole = probes.copy()
+    rt.estimate_illumination(env, rp, whole, 5, 1e-3)
+    stats = rt.last_job_stats()
+    assert np.abs(whole["energy"]).sum() > 0
+    for chunk in (1, 7, 128, 899, 900):
+        rt.set_option("pipe_chunk_probes", chunk)
+        got = probes.copy()
+        rt.estimate_illumination(env, rp, got, 5, 1e-3)
+        assert_bit_equal(got.view(np.uint8), whole.view(np.uint8), f"probe chunk {chunk}")
+        assert rt.last_job_stats() == stats, chunk
+    lo, hi = scenes.scene_bounds(sd)
+    rays = scenes.incoherent_rays(5000, lo - 0.2, hi + 0.2, seed=4)
+    smp = np.zeros(len(rays), dtype=S.PC_SAMPLE_DTYPE)
+    smp["start"], smp["direction"] = rays[:, 0:3], rays[:, 4:7]
+    whole_s = smp.copy()
+    whole_p = rt.sample_point_cloud(env, whole_s, want_prim_ids=True)
+    assert 0 < whole_s["hit"].sum() < len(smp)
+    for chunk in (1, 33, 1024, 4999, 1 << 20):
+        rt.set_option("pipe_chunk_samples", chunk)
+        got = smp.copy()
+        gp = rt.sample_point_cloud(env, got, want_prim_ids=True)
+        assert_bit_equal(got.view(np.uint8), whole_s.view(np.uint8), f"sample chunk {chunk}")
+        assert np.array_equal(gp, whole_p)

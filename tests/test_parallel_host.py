@@ -79,6 +79,15 @@ def _worker(rank, world, port, out_dir):
     dist.destroy_process_group()
 
 
+def test_library_shard_rule_equals_the_python_restatement(mod):
+    """csrc/multi.cu shards by rtf_shard_range; parallel.split_range restates it for the gloo tests of the host logic."""
+    from raytracerfacility_b200 import parallel
+    for n in (0, 1, 7, 8, 9, 1000, 10_000_002, 100_000_000, (1 << 40) + 3):
+        for world in (1, 2, 3, 4, 8):
+            for r in range(world):
+                assert mod.shard_range(n, world, r) == parallel.split_range(n, world, r), (n, world, r)
+
+
 def test_world2_gloo_sharded_illumination(tmp_path, orc, S, scenes):
     world = 2
     mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
