@@ -385,6 +385,9 @@ int rtf_commit(rtf_ctx* ctx, int morton_bits) {
   s.has_alpha = 0;
   for (float a : alpha)
     if (a < 1.0f) s.has_alpha = 1;  // includes the "textured alpha" marker (-1)
+  s.has_btf = 0;
+  for (const DevMaterial& dm : mats)
+    if (dm.m.material_type == RTF_MAT_COMPRESSED_BTF) s.has_btf = 1;
   s.has_sss = 0;
   for (const DevMaterial& dm : mats)
     if (dm.m.material_type != RTF_MAT_COMPRESSED_BTF && dm.m.subsurface_factor > 0.0f && dm.m.subsurface_radius[0] > 0.0f)
@@ -504,6 +507,7 @@ int rtf_estimate_illumination(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_pr
   for (int k = 0; k < HostPipe::kDepth; k++)
     if ((rc = p.aos[k].reserve(cm * sizeof(rtf_illum_sampler))) || (rc = p.aux[k].reserve(cm * 24))) return rc;
   RTF_CUDA(cudaStreamSynchronize(st));  // earlier work of the caller on the context stream
+  if ((rc = ctx->d_stats.reserve(64))) return rc;  // first job of a context: the wavefront workspace does not exist yet
   RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, st));
   ctx->stats_hold = true, ctx->last_paths = 0;
   size_t i = 0;

@@ -134,7 +134,7 @@ __global__ void k_btf_eval(DevBTF btf, uint32_t n, const float* __restrict__ in1
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float* q = in14 + 14 * (size_t)i;
-  const float3 c = btf_get_value(btf, q[0], q[1], f3(q[2], q[3], q[4]), f3(q[5], q[6], q[7]), f3(q[8], q[9], q[10]),
+  const float3 c = btf_get_value<true>(btf, q[0], q[1], f3(q[2], q[3], q[4]), f3(q[5], q[6], q[7]), f3(q[8], q[9], q[10]),
                                  f3(q[11], q[12], q[13]));
   out[3 * (size_t)i] = c.x, out[3 * (size_t)i + 1] = c.y, out[3 * (size_t)i + 2] = c.z;
 }

@@ -241,8 +241,16 @@ struct ShadeParams {
 #ifndef RTF_SHADE_MIN_BLOCKS
 #define RTF_SHADE_MIN_BLOCKS 3
 #endif
-template <bool SSS>
-__global__ void __launch_bounds__(256, SSS ? 1 : RTF_SHADE_MIN_BLOCKS)
+// BTF = some material is a compressed BTF: the kernel carries the MLVQ evaluator in its wide (level-by-level) form, which
+// wants registers for the loads it keeps in flight — 2 blocks per SM; scenes without one run the leaner variant.
+#ifndef RTF_SHADE_BTF_MIN_BLOCKS
+#define RTF_SHADE_BTF_MIN_BLOCKS 2
+#endif
+#ifndef RTF_BTF_WIDE
+#define RTF_BTF_WIDE 1
+#endif
+template <bool SSS, bool BTF>
+__global__ void __launch_bounds__(256, SSS ? 1 : (BTF ? RTF_SHADE_BTF_MIN_BLOCKS : RTF_SHADE_MIN_BLOCKS))
     k_shade(DevScene sc, rtf_env env, ShadeParams sp, PathMap pm, Queues q, int qi, int wave, PathState ps) {
   const uint32_t n = q.count[wave];
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -285,7 +293,9 @@ __global__ void __launch_bounds__(256, SSS ? 1 : RTF_SHADE_MIN_BLOCKS)
       at.u = 0.0f, at.v = 0.0f, at.tangent = f3(0, 0, 0), at.color = f3(0, 0, 0);
       if (dm.rich) at = hit_attrs(sc, prim, h.y, h.z, sh.inst);
       const uint64_t unit = unit_of(pm, p);
-      if (m.material_type == RTF_MAT_COMPRESSED_BTF) {  // RayFunctions.cuh:172-258
+      bool is_btf = false;
+      if constexpr (BTF) is_btf = m.material_type == RTF_MAT_COMPRESSED_BTF;
+      if (is_btf) {  // RayFunctions.cuh:172-258
         const DevBTF& btf = sc.btfs[dm.btf];
         float3 btf_color = f3(0, 0, 0);  // the reference leaves it uninitialised past the bounce limit: 0 here
         if ((int)hit_count <= sp.bounces) {
@@ -293,7 +303,7 @@ __global__ void __launch_bounds__(256, SSS ? 1 : RTF_SHADE_MIN_BLOCKS)
           if (env.lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE) {  // :180-218
             const float3 sun = f3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
             const float3 nd = sample_lobe(r.x, r.y, sun, 1.0f - env.light_size);
-            btf_color = btf_get_value(btf, at.u, at.v, d, nd, sh.normal, at.tangent);
+            btf_color = btf_get_value<RTF_BTF_WIDE != 0>(btf, at.u, at.v, d, nd, sh.normal, at.tangent);
             const float3 col = f3(env.color[0], env.color[1], env.color[2]);
             acc = acc + T * ((col * env.ambient_light_intensity) * btf_color);
             const float ndl = dot3(sh.normal, nd);
@@ -309,7 +319,7 @@ __global__ void __launch_bounds__(256, SSS ? 1 : RTF_SHADE_MIN_BLOCKS)
           } else {  // :219-246
             const float3 refl = reflect3(d, sh.normal);
             const float3 nd = sample_lobe(r.x, r.y, refl, 0.0f);
-            btf_color = btf_get_value(btf, at.u, at.v, d, nd, sh.normal, at.tangent);
+            btf_color = btf_get_value<RTF_BTF_WIDE != 0>(btf, at.u, at.v, d, nd, sh.normal, at.tangent);
             T = T * btf_color;
             const float3 so = sh.position + sh.normal * 1e-3f;
             ps.thr[p] = make_float4(T.x, T.y, T.z, __uint_as_float(hit_count));
@@ -716,10 +726,14 @@ static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_
       LAUNCH_P(ctx, PROF_TRACE, k_trace_queue<true>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
     else
       LAUNCH_P(ctx, PROF_TRACE, k_trace_queue<false>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
-    if (sss)
-      LAUNCH_P(ctx, PROF_SHADE, k_shade<true>, div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
+    if (sss && ctx->scene.has_btf)
+      LAUNCH_P(ctx, PROF_SHADE, (k_shade<true, true>), div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
+    else if (sss)
+      LAUNCH_P(ctx, PROF_SHADE, (k_shade<true, false>), div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
+    else if (ctx->scene.has_btf)
+      LAUNCH_P(ctx, PROF_SHADE, (k_shade<false, true>), div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
     else
-      LAUNCH_P(ctx, PROF_SHADE, k_shade<false>, div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
+      LAUNCH_P(ctx, PROF_SHADE, (k_shade<false, false>), div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
     qi ^= 1;
   }
   return RTF_OK;

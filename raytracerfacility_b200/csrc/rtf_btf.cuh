@@ -210,6 +210,91 @@ RTF_D float3 btf_pdf4(const DevBTF& b, int idx, const BtfCoords& tc) {
   const float s2 = __ldg(b.pdf4d_scales + (size_t)idx * np + hi) * w;
   return o1 * s1 + o2 * s2;
 }
+// The same value as btf_pdf4 — every float operation and its order unchanged — with the table reads issued level by
+// level: the cascade is a chain of dependent gathers (PDF4D slice -> PDF3D slice -> PDF2D index pair -> alpha slices ->
+// beta rows -> colour vectors), and walked depth-first a thread has two or three loads in flight while it waits an L2
+// round trip per link, sixteen times over.  Here the 2 phi x 2 theta corners advance together (2, 4, 8 loads per level),
+// then each phi pair finishes its 2 theta x 2 alpha leaves with 12 + 20 + 16 loads in flight: 9 round trips instead of
+// ~30, at the cost of registers (the BTF shading kernel is compiled for 2 blocks of 256 threads per SM).
+RTF_D float3 btf_pdf4_wide(const DevBTF& b, int idx, const BtfCoords& tc) {
+  const int np = b.num_phi, lo = tc.i_phi, hi = lo != np - 1 ? lo + 1 : 0;
+  const int nt = b.num_theta, it = tc.i_theta, na = b.num_alpha, ia = tc.i_alpha, nb = b.num_beta, ib = tc.i_beta;
+  const int* p4 = b.pdf4d_slices + (size_t)idx * np;
+  const float* q4 = b.pdf4d_scales + (size_t)idx * np;
+  const int i4[2] = {__ldg(p4 + lo), __ldg(p4 + hi)};
+  const float s4[2] = {__ldg(q4 + lo), __ldg(q4 + hi)};
+  int i3[4];
+  float s3[4];
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    i3[k] = __ldg(b.pdf3d_slices + (size_t)i4[k >> 1] * nt + it + (k & 1));
+    s3[k] = __ldg(b.pdf3d_scales + (size_t)i4[k >> 1] * nt + it + (k & 1));
+  }
+  int lum[4], col[4];
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    lum[k] = __ldg(b.pdf2d_indices + (size_t)i3[k] * b.pdf2d_slice_len);
+    col[k] = __ldg(b.pdf2d_indices + (size_t)i3[k] * b.pdf2d_slice_len + 1);
+  }
+  const float wa = tc.w_alpha, wb = tc.w_beta, wt = tc.w_theta;
+  const float t2 = wb * wb, t3 = t2 * wb;
+  const float h01 = -2.0f * t3 + 3.0f * t2, h00 = 1.0f - h01, h11 = t3 - t2, h10 = h11 - t2 + wb;
+  float3 o3[2];
+#pragma unroll
+  for (int c = 0; c < 2; c++) {  // one phi corner: 2 theta x 2 alpha leaves, j = 2*theta + alpha
+    int cs[4], ls[4];
+    float lsc[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int k = 2 * c + (j >> 1), a = j & 1;
+      cs[j] = __ldg(b.pdf2d_colors + (size_t)col[k] * na + ia + a);
+      ls[j] = __ldg(b.pdf2d_slices + (size_t)lum[k] * na + ia + a);
+      lsc[j] = __ldg(b.pdf2d_scales + (size_t)lum[k] * na + ia + a);
+    }
+    int c0[4], c1[4];
+    float p0[4], p1[4], pm[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int* row = b.index_ab + (size_t)cs[j] * nb;
+      c0[j] = __ldg(row + ib), c1[j] = __ldg(row + ib + 1);
+      const float* br = b.pdf1d_basis + (size_t)ls[j] * nb;
+      p0[j] = __ldg(br + ib), p1[j] = __ldg(br + ib + 1);
+      pm[j] = ib == 0 ? 0.0f : __ldg(br + ib - 1);
+    }
+    float ax[4], ay[4], bx[4], by[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const float* a0 = b.colors + (size_t)c0[j] * b.n_channels;
+      const float* a1 = b.colors + (size_t)c1[j] * b.n_channels;
+      ax[j] = __ldg(a0), ay[j] = __ldg(a0 + 1), bx[j] = __ldg(a1), by[j] = __ldg(a1 + 1);
+    }
+    float3 o2[2];
+#pragma unroll
+    for (int t = 0; t < 2; t++) {
+      float l[2];
+      float2 ab[2];
+#pragma unroll
+      for (int a = 0; a < 2; a++) {
+        const int j = 2 * t + a;
+        const float m0h = ib == 0 ? p1[j] - p0[j] : 0.5f * (p1[j] - pm[j]);
+        const float m1h = ib == nb - 2 ? p1[j] - p0[j] : 0.5f * (p1[j] - p0[j]);
+        l[a] = lsc[j] * (((h00 * p0[j] + h10 * m0h) + h01 * p1[j]) + h11 * m1h);
+        ab[a].x = (1.f - wb) * ax[j] + wb * bx[j];
+        ab[a].y = (1.f - wb) * ay[j] + wb * by[j];
+      }
+      float3 cm;
+      cm.y = ab[0].x * (1.0f - wa) + ab[1].x * wa;
+      cm.z = ab[0].y * (1.0f - wa) + ab[1].y * wa;
+      cm.x = (1.f - wa) * l[0] + wa * l[1];
+      o2[t] = b.hdr ? btf_logluv(cm, b.code_btf_flag != 0) : btf_ycbcr(cm, b.code_btf_flag != 0);
+    }
+    const float s1 = s3[2 * c] * (1.0f - wt), s2 = s3[2 * c + 1] * wt;
+    o3[c] = o2[0] * s1 + o2[1] * s2;
+  }
+  const float w = tc.w_phi;
+  const float s1 = s4[0] * (1.0f - w), s2 = s4[1] * w;
+  return o3[0] * s1 + o3[1] * s2;
+}
 // ConvertThetaPhiToBetaAlpha, SharedCoordinates.cuh:126-165.  With m_codeBtfFlag the reference subtracts tc.m_phi, a
 // member of the by-value SharedCoordinates copy that nothing sets before the call (BTFBase.cuh:65-66): 0 here.
 RTF_D void btf_theta_phi_to_beta_alpha(const DevBTF& b, float theta, float phi, float& beta, float& alpha) {
@@ -237,6 +322,7 @@ RTF_D void btf_theta_phi_to_beta_alpha(const DevBTF& b, float theta, float phi, 
   alpha = asinp(clampf(y / cb, -1.0f, 1.0f));
 }
 // BTFBase::GetValueDeg (BTFBase.cuh:49-81) -> PDF6D::GetValDeg2 (PDF6D.cuh:32-95)
+template <bool WIDE = false>
 RTF_D float3 btf_value_deg(const DevBTF& b, float u, float v, float illum_theta, float illum_phi, float view_theta,
                            float view_phi) {
   if (illum_theta > 90.0f || view_theta > 90.0f) return f3(0, 0, 0);
@@ -286,7 +372,8 @@ RTF_D float3 btf_value_deg(const DevBTF& b, float u, float v, float illum_theta,
       tc.w_phi = (ph - (float)tc.i_phi * step) / step;
     }
     const size_t texel = (size_t)y * b.pdf6_cols + x;
-    out = btf_pdf4(b, __ldg(b.pdf6_slices + texel) - 1, tc) * __ldg(b.pdf6_scales + texel);
+    const int idx4 = __ldg(b.pdf6_slices + texel) - 1;
+    out = (WIDE ? btf_pdf4_wide(b, idx4, tc) : btf_pdf4(b, idx4, tc)) * __ldg(b.pdf6_scales + texel);
   } while (false);
   out = out * b.multiplier;
   if (b.hdr) out = out * (1.0f / b.hdr_value);
@@ -310,11 +397,12 @@ RTF_D void btf_compute_angles(float3 dir, float3 normal, float3 tangent, float& 
   phi = p;
 }
 // SurfaceCompressedBTF::GetValue, RDD.hpp:329-354
+template <bool WIDE = false>
 RTF_D float3 btf_get_value(const DevBTF& b, float u, float v, float3 view_dir, float3 illum_dir, float3 normal, float3 tangent) {
   float it, ip, vt, vp;
   btf_compute_angles(neg3(view_dir), normal, tangent, vt, vp);
   btf_compute_angles(illum_dir, normal, tangent, it, ip);
-  return btf_value_deg(b, u, v, it, ip, vt, vp) * (1.0f / 256.0f);
+  return btf_value_deg<WIDE>(b, u, v, it, ip, vt, vp) * (1.0f / 256.0f);
 }
 
 }  // namespace rtf

@@ -84,6 +84,7 @@ struct DevScene {
   uint32_t n_tris = 0, n_nodes = 0, n_insts = 0;
   int has_alpha = 0;
   int has_sss = 0;  // some material has subsurfaceFactor > 0 and subsurfaceRadius.x > 0 (BSSRDF, RF.cuh:97-133)
+  int has_btf = 0;  // some material is a compressed BTF (RF.cuh:172-258)
 };
 
 struct Geometry {

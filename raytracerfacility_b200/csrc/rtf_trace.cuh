@@ -46,6 +46,10 @@ constexpr int kRawTileBytes = 1024;  // 32 rays x 32 B
 #define RTF_NODE_QUORUM 24
 #endif
 constexpr int kNodeQuorum = RTF_NODE_QUORUM;  // lanes that must be ready before the warp runs a node visit
+#ifndef RTF_REFILL_MIN
+#define RTF_REFILL_MIN 1
+#endif
+constexpr int kRefillMin = RTF_REFILL_MIN;  // idle lanes that must have gathered before the warp goes to the pool
 #ifndef RTF_FFMA2
 #define RTF_FFMA2 0  // 1: plane distances with packed fma.rn.f32x2 (Blackwell FFMA2); needs more than 64 registers to pay
 #endif
@@ -148,7 +152,7 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
 
   for (;;) {
     unsigned idle = __ballot_sync(0xffffffffu, !have);
-    if (idle) {
+    if (kRefillMin > 1 ? (__popc(idle) >= kRefillMin) : (idle != 0u)) {
       for (;;) {
         if (pool_pos >= pool_cnt) {
           if (next_base >= n) break;
@@ -191,7 +195,10 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
             pool[1][lane] = make_float4(1.0f / sdx, 1.0f / sdy, 1.0f / sdz, b.w);
             pool[2][lane] = make_float4(rx.x, rx.y, rx.z, ry.x);
             pool[3][lane] = make_float4(ry.y, ry.z, rz.x, rz.y);
-            pool[4][lane] = make_float4(rz.z, __uint_as_float(r_tag), 0.0f, 0.0f);
+            const bool ngx = sdx < 0.0f, ngy = sdy < 0.0f, ngz = sdz < 0.0f;  // sign of 1/sd = sign of sd
+            const uint32_t r_oct = (ngx ? 0u : 4u) | (ngy ? 0u : 2u) | (ngz ? 0u : 1u);
+            const uint32_t r_pm = (ngz ? 0u : 0x55u) | (ngy ? 0u : 0x33u << 10) | (ngx ? 0u : 0x0Fu << 20);
+            pool[4][lane] = make_float4(rz.z, __uint_as_float(r_tag), __uint_as_float(r_oct), __uint_as_float(r_pm));
           }
           __syncwarp();
           pool_base = base, pool_pos = 0, pool_cnt = cnt;
@@ -205,9 +212,7 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
           idx = q1.x, idy = q1.y, idz = q1.z;
           best.t = q1.w, best.u = 0.0f, best.v = 0.0f, best.prim = 0xFFFFFFFFu;
           mx = f3(q2.x, q2.y, q2.z), my = f3(q2.w, q3.x, q3.y), mz = f3(q3.z, q3.w, q4.x);
-          const bool negx = idx < 0.0f, negy = idy < 0.0f, negz = idz < 0.0f;
-          oct_inv = (negx ? 0u : 4u) | (negy ? 0u : 2u) | (negz ? 0u : 1u);
-          pmask = (negz ? 0u : 0x55u) | (negy ? 0u : 0x33u << 10) | (negx ? 0u : 0x0Fu << 20);
+          oct_inv = __float_as_uint(q4.z), pmask = __float_as_uint(q4.w);  // octant words, built at 32 lanes above
           cur = make_uint2(0u, 0x80000000u);
           tg = make_uint2(0u, 0u);
           sp = 0, nvis = 0, tvis = 0;
