@@ -242,9 +242,10 @@ struct ShadeParams {
 #define RTF_SHADE_MIN_BLOCKS 3
 #endif
 // BTF = some material is a compressed BTF: the kernel carries the MLVQ evaluator in its wide (level-by-level) form, which
-// wants registers for the loads it keeps in flight — 2 blocks per SM; scenes without one run the leaner variant.
+// wants registers for the loads it keeps in flight; scenes without one run the leaner variant.  Measured on C5: wide at
+// 2 blocks/SM (96 registers) 156 ms of shading, wide at 3 blocks (80 registers) 134.7 ms, depth-first at 3 blocks 135.1 ms.
 #ifndef RTF_SHADE_BTF_MIN_BLOCKS
-#define RTF_SHADE_BTF_MIN_BLOCKS 2
+#define RTF_SHADE_BTF_MIN_BLOCKS 3
 #endif
 #ifndef RTF_BTF_WIDE
 #define RTF_BTF_WIDE 1
