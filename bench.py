@@ -345,7 +345,19 @@ def run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, par
         t0 = time.perf_counter()
         rt.load_scene(cfg.scene, 63)
         torch.cuda.synchronize()
-        return {"commit_wall_s": time.perf_counter() - t0, "build_ms": rt.build_timings()}
+        info = {"commit_wall_s": time.perf_counter() - t0, "build_ms": rt.build_timings()}
+        # steady-state rebuild of the same scene (build arrays already sized; the first build of a size pays cudaMalloc
+        # inside its stages): move one instance, commit, move it back, commit — the second commit is reported
+        ih = max(cfg.scene.instances)
+        g_, m_, x_, c_ = cfg.scene.instances[ih]
+        x_moved = x_.copy()
+        x_moved[12] += 0.125
+        for x in (x_moved, x_):
+            rt.set_instance(ih, g_, m_, x, c_)
+            rt.build_ias(63)
+        torch.cuda.synchronize()
+        info["rebuild_ms"] = rt.build_timings()
+        return info
 
     def profiled(fn):
         """One extra run with an event pair around every kernel launch: device ms per kernel category."""
@@ -522,6 +534,14 @@ def main():
     def sum_over_ranks(x):
         return x if world == 1 else float(rt.comm_reduce([x], "sum")[0])
 
+    def per_rank(x):
+        """[x of rank 0, x of rank 1, ...] on every rank (one in-library reduction of a one-hot vector)."""
+        if world == 1:
+            return [float(x)]
+        v = [0.0] * world
+        v[rank] = float(x)
+        return [float(y) for y in rt.comm_reduce(v, "sum")]
+
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
     def timed(fn):
@@ -603,8 +623,13 @@ def main():
     for _ in range(args.steps):
         rt.trace_closest(np_rays, out=np_hits)  # H2D rays -> trace -> D2H hits, blocking (CudaModule.cpp:39-64 style)
     torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    own_s = time.perf_counter() - t0
+    e2e_s = max_over_ranks(own_s)
     e2e = world * n * args.steps / e2e_s / 1e6
+    # which rank's host link is the slow one: every rank's own PCIe rate (48 B per ray both ways) and its first CPU core
+    # (ranks pin themselves to their GPU's NUMA-local cores before allocating the pinned buffers: parallel.init_distributed)
+    e2e_rank_gbs = [round(g, 2) for g in per_rank(n * 48 * args.steps / own_s / 1e9)]
+    e2e_rank_core = [int(c) for c in per_rank(min(os.sched_getaffinity(0)))]
     assert np.array_equal(np_hits.view(np.uint32).reshape(-1, 4)[:4096], hits[:4096].cpu().numpy().view(np.uint32))
 
     # ---- roofline of the dominant kernel (k_trace_rays<false>: exactly one launch per step) --------------------------
@@ -643,7 +668,8 @@ def main():
            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
            "data": "synthetic", "config": headline_config(args, n_tris), "hit_rate": hit_rate,
            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 16,
-                   "api": "rtf_trace_closest (host rays in, host hits out, pinned)"},
+                   "api": "rtf_trace_closest (host rays in, host hits out, pinned)",
+                   "pcie_gbs_per_rank": e2e_rank_gbs, "first_cpu_core_per_rank": e2e_rank_core},
            "gpu_launches": launches, "clocks": clk, "roofline": roofline,
            "multi_gpu": "sharding + collectives inside librtf_b200.so (NCCL communicator of the library, csrc/multi.cu)",
            "build": dict(first_build, wall_s_incl_upload=build_wall), "rebuild": rebuild, "refit": refit}

@@ -35,6 +35,13 @@ def _excess(gpu, cpu, rtol=RTOL, atol=0.0):
     return float(np.nanmax(q)) if q.size else 0.0, float(err.max()) if err.size else 0.0
 
 
+def _visits(st):
+    """Per-ray node visits and triangle tests of the deterministic traversal order on the sample (the GPU's counters equal
+    the oracle's bit for bit, tests/test_gpu_trace.py): what a ray of this workload costs, next to M1's 10.95 / 2.29."""
+    r = max(1, int(st.rays))
+    return {"mean_nodes_per_ray": float(st.nodes) / r, "mean_tris_per_ray": float(st.tris) / r}
+
+
 def build(cfg, morton_bits=63):
     t0 = time.perf_counter()
     osc = orc.OracleScene(cfg.scene, morton_bits)
@@ -57,7 +64,7 @@ def illumination(osc, cfg, gpu_out6, stride, seed, push, nthreads=None):
             f"{int(st.rays)} rays)", "energy_max_err_over_tol": e_q, "energy_max_abs_err": e_abs,
             "direction_max_err_over_tol": d_q, "tolerance": "energy <= 1e-5 relative; direction <= 1e-5 relative + 1e-5",
             "cpu_s": dt, "cpu_threads": nthreads, "cpu_triangle_samples_per_s": units / dt, "cpu_Mrays_per_s": st.rays / dt / 1e6,
-            "mean_rays_per_path": float(st.rays) / max(1, int(st.paths))}
+            "mean_rays_per_path": float(st.rays) / max(1, int(st.paths)), **_visits(st)}
 
 
 def lidar(osc, cfg, gpu_t, gpu_prim, stride, ray_begin=0, nthreads=None):
@@ -76,7 +83,7 @@ def lidar(osc, cfg, gpu_t, gpu_prim, stride, ray_begin=0, nthreads=None):
     same_p = bool(np.array_equal(gp, prim.view(np.uint32)))
     return {"ok": same_t and same_p, "sample": f"every {stride}-th ray ({len(t)} rays)", "prim_ids_bit_exact": same_p,
             "distances_bit_exact": same_t, "hit_fraction_on_sample": float((prim != 0xFFFFFFFF).mean()) if len(prim) else 0.0,
-            "cpu_s": dt, "cpu_threads": nthreads, "cpu_Mrays_per_s": len(t) / dt / 1e6}
+            "cpu_s": dt, "cpu_threads": nthreads, "cpu_Mrays_per_s": len(t) / dt / 1e6, **_visits(st)}
 
 
 def camera(osc, cfg, cam_props, gpu_color, stride, nthreads=None):
@@ -92,4 +99,4 @@ def camera(osc, cfg, cam_props, gpu_color, stride, nthreads=None):
     paths = len(col) * cfg.rp.samples
     return {"ok": bool(q <= 1.0), "sample": f"every {stride}-th pixel ({len(col)} pixels, {paths} paths, {int(st.rays)} rays)",
             "colour_max_err_over_tol": q, "colour_max_abs_err": a, "tolerance": "<= 1e-5 relative", "cpu_s": dt,
-            "cpu_threads": nthreads, "cpu_Mpaths_per_s": paths / dt / 1e6, "cpu_Mrays_per_s": st.rays / dt / 1e6}
+            "cpu_threads": nthreads, "cpu_Mpaths_per_s": paths / dt / 1e6, "cpu_Mrays_per_s": st.rays / dt / 1e6, **_visits(st)}

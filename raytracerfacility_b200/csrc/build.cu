@@ -433,59 +433,97 @@ struct CollapseState {  // device memory, zeroed before the launch except level[
 
 // Greedy expansion by largest half-area + greedy octant slot assignment of binary subtree R: the binary child of every
 // slot (kEmptySlot: none), the number of internal children and of leaf triangles.
+// Written as straight-line register code: every array index below is a compile-time constant after unrolling (a dynamic
+// index would put ch / dv / the slot tables into local memory — the first version did, and the kernel sat at 15 % issue
+// utilisation waiting for its own stack), each child's half-area and centre offset are computed once when the child
+// enters the set, and the (child, slot) search runs as eight independent per-child chains.  The decisions — first
+// maximum in index order, strict comparisons — are those of the loop form, which the CPU oracle keeps.
 __device__ __forceinline__ void collapse_plan(const CollapseArgs& a, int R, int (&slot_child)[8], uint32_t& ci, uint32_t& ct) {
   const int ni = a.n - 1;
+  const Box3 nb = load_box(a.boxes, ni, R);
+  const float3 center = (nb.lo + nb.hi) * 0.5f;
   int ch[8];
+  float ar[8];  // half-area of an internal child; -inf: leaf or unused (never chosen for expansion)
+  float3 dv[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) ch[i] = kEmptySlot, ar[i] = -INFINITY, dv[i] = f3(0, 0, 0);
+  auto enter = [&](int c, float& area, float3& d) {
+    const Box3 cb = load_box(a.boxes, ni, c);
+    area = c >= 0 ? half_area(cb) : -INFINITY;
+    d = (cb.lo + cb.hi) * 0.5f - center;
+  };
   int nc;
   if (R < 0) {
     ch[0] = R, nc = 1;
+    enter(R, ar[0], dv[0]);
   } else {
     const int2 c2 = a.children[R];
     ch[0] = c2.x, ch[1] = c2.y, nc = 2;
+    enter(c2.x, ar[0], dv[0]);
+    enter(c2.y, ar[1], dv[1]);
   }
   while (nc < 8) {
     int best = -1;
     float best_area = -INFINITY;
-    for (int i = 0; i < nc; i++) {
-      if (ch[i] < 0) continue;
-      const float ar = half_area(load_box(a.boxes, ni, ch[i]));
-      if (ar > best_area) best_area = ar, best = i;
-    }
-    if (best < 0) break;
-    const int2 c2 = a.children[ch[best]];
-    ch[best] = c2.x;
-    ch[nc++] = c2.y;
-  }
-  const Box3 nb = load_box(a.boxes, ni, R);
-  const float3 center = (nb.lo + nb.hi) * 0.5f;
-  float3 dv[8];
-  for (int i = 0; i < nc; i++) {
-    const Box3 cb = load_box(a.boxes, ni, ch[i]);
-    dv[i] = (cb.lo + cb.hi) * 0.5f - center;
-  }
-  int slot_of[8], child_in_slot[8];
 #pragma unroll
-  for (int i = 0; i < 8; i++) slot_of[i] = -1, child_in_slot[i] = -1;
-  for (int it = 0; it < nc; it++) {
-    float best = -INFINITY;
-    int bi = -1, bs = -1;
-    for (int i = 0; i < nc; i++) {
-      if (slot_of[i] >= 0) continue;
-      for (int s = 0; s < 8; s++) {
-        if (child_in_slot[s] >= 0) continue;
-        const float cost = (((s & 4) ? dv[i].x : -dv[i].x) + ((s & 2) ? dv[i].y : -dv[i].y)) + ((s & 1) ? dv[i].z : -dv[i].z);
-        if (bi < 0 || cost > best) best = cost, bi = i, bs = s;
-      }
+    for (int i = 0; i < 8; i++)
+      if (ar[i] > best_area) best_area = ar[i], best = i;
+    if (best < 0) break;
+    int cb = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+      if (i == best) cb = ch[i];
+    const int2 c2 = a.children[cb];
+    float ax, ay;
+    float3 dx, dy;
+    enter(c2.x, ax, dx);
+    enter(c2.y, ay, dy);
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      if (i == best) ch[i] = c2.x, ar[i] = ax, dv[i] = dx;
+      if (i == nc) ch[i] = c2.y, ar[i] = ay, dv[i] = dy;
     }
-    slot_of[bi] = bs;
-    child_in_slot[bs] = bi;
+    nc++;
+  }
+  // greedy slot assignment: nc times, the (child, slot) pair of largest cost among the unassigned children and free
+  // slots, first pair in (child, slot) order on ties
+  uint32_t open_i = (1u << nc) - 1u, free_s = 0xffu;
+  int child_in_slot[8];
+#pragma unroll
+  for (int s = 0; s < 8; s++) child_in_slot[s] = -1;
+  for (int it = 0; it < nc; it++) {
+    float bc[8];
+    int bsl[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {  // best free slot of child i (independent chains)
+      float best = 0.0f;
+      int bs = -1;
+#pragma unroll
+      for (int s = 0; s < 8; s++) {
+        const float cost = (((s & 4) ? dv[i].x : -dv[i].x) + ((s & 2) ? dv[i].y : -dv[i].y)) + ((s & 1) ? dv[i].z : -dv[i].z);
+        if (((free_s >> s) & 1u) && (bs < 0 || cost > best)) best = cost, bs = s;
+      }
+      bc[i] = best, bsl[i] = bs;
+    }
+    float best = 0.0f;
+    int bi = -1, bs = -1;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+      if (((open_i >> i) & 1u) && (bi < 0 || bc[i] > best)) best = bc[i], bi = i, bs = bsl[i];
+    open_i &= ~(1u << bi), free_s &= ~(1u << bs);
+#pragma unroll
+    for (int s = 0; s < 8; s++)
+      if (s == bs) child_in_slot[s] = bi;
   }
   ci = 0, ct = 0;
+#pragma unroll
   for (int s = 0; s < 8; s++) {
     const int i = child_in_slot[s];
     int c = kEmptySlot;
+#pragma unroll
+    for (int k = 0; k < 8; k++)
+      if (k == i) c = ch[k];
     if (i >= 0) {
-      c = ch[i];
       const uint32_t cnt = c >= 0 ? (a.range[c].y - a.range[c].x + 1u) : 1u;
       if (c >= 0 && cnt > 3u)
         ci++;

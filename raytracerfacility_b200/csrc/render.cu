@@ -247,11 +247,14 @@ struct ShadeParams {
 #ifndef RTF_SHADE_BTF_MIN_BLOCKS
 #define RTF_SHADE_BTF_MIN_BLOCKS 3
 #endif
+#ifndef RTF_SHADE_SSS_MIN_BLOCKS
+#define RTF_SHADE_SSS_MIN_BLOCKS 3  // C2 scene, every plant subsurface: shading 23.6 / 15.0 / 13.3 ms at 1 / 2 / 3 blocks
+#endif
 #ifndef RTF_BTF_WIDE
 #define RTF_BTF_WIDE 1
 #endif
 template <bool SSS, bool BTF>
-__global__ void __launch_bounds__(256, SSS ? 1 : (BTF ? RTF_SHADE_BTF_MIN_BLOCKS : RTF_SHADE_MIN_BLOCKS))
+__global__ void __launch_bounds__(256, SSS ? RTF_SHADE_SSS_MIN_BLOCKS : (BTF ? RTF_SHADE_BTF_MIN_BLOCKS : RTF_SHADE_MIN_BLOCKS))
     k_shade(DevScene sc, rtf_env env, ShadeParams sp, PathMap pm, Queues q, int qi, int wave, PathState ps) {
   const uint32_t n = q.count[wave];
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;

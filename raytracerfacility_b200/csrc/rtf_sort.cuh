@@ -13,6 +13,9 @@
 
 namespace rtf {
 
+#ifndef RTF_SORT_MATCH
+#define RTF_SORT_MATCH 0  // 1: rank with match.any instead of eight ballots
+#endif
 constexpr int kSortBlock = 256;
 constexpr int kSortWarps = kSortBlock / 32;
 constexpr int kSortItems = 16;
@@ -76,7 +79,7 @@ struct SortSmem {
 };
 
 template <class K>
-__global__ void __launch_bounds__(kSortBlock) k_sort_pass(const K* __restrict__ kin, K* __restrict__ kout,
+__global__ void __launch_bounds__(kSortBlock, 3) k_sort_pass(const K* __restrict__ kin, K* __restrict__ kout,
                                                           const uint32_t* __restrict__ vin, uint32_t* __restrict__ vout,
                                                           uint32_t n, int shift, const uint32_t* __restrict__ hist_scan,
                                                           uint32_t* status /* [0] ticket, [256 + tile*256 + d] */) {
@@ -101,15 +104,25 @@ __global__ void __launch_bounds__(kSortBlock) k_sort_pass(const K* __restrict__ 
     const uint32_t idx = wbase + (uint32_t)i * 32u;
     const bool valid = idx < n;
     key[i] = valid ? kin[idx] : (K)0;
+    const uint32_t d = valid ? (uint32_t)((key[i] >> shift) & 255) : 0u;
+#if RTF_SORT_MATCH
     // invalid lanes (tail of the last tile) get a private digit so they match nobody and count nowhere
-    const uint32_t d = valid ? (uint32_t)((key[i] >> shift) & 255) : 256u + (uint32_t)lane;
-    const uint32_t peers = __match_any_sync(0xffffffffu, d);
+    const uint32_t peers = __match_any_sync(0xffffffffu, valid ? d : 256u + (uint32_t)lane);
+#else
+    // lanes with the same digit, from eight ballots (one per digit bit): match.any serialises over the distinct values
+    // of the warp — about 28 of them for random digits
+    uint32_t peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+    for (int b = 0; b < 8; b++) {
+      const bool bit = (d >> b) & 1u;
+      const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+      peers &= bit ? bal : ~bal;
+    }
+    if (!valid) peers = 1u << lane;
+#endif
     const int leader = __ffs((int)peers) - 1;
     uint32_t old = 0;
-    if (valid && lane == leader) {
-      old = sm.cnt[warp][d];
-      sm.cnt[warp][d] = old + (uint32_t)__popc(peers);
-    }
+    if (valid && lane == leader) old = atomicAdd(&sm.cnt[warp][d], (uint32_t)__popc(peers));
     old = __shfl_sync(0xffffffffu, old, leader);
     lrank[i] = (uint16_t)(old + (uint32_t)__popc(peers & lt_mask));
     __syncwarp();
@@ -130,13 +143,22 @@ __global__ void __launch_bounds__(kSortBlock) k_sort_pass(const K* __restrict__ 
     const uint32_t start = block_exclusive_scan_256(tile_cnt, sm.warp_sums);
     uint32_t excl = 0;
     if (tile > 0) {
-      for (int t = (int)tile - 1; t >= 0; t--) {
-        uint32_t v;
-        do {
-          v = st[(size_t)t * 256 + d];
-        } while ((v & ~kSortValueMask) == 0u);
-        excl += v & kSortValueMask;
-        if (v & kSortFlagPrefix) break;
+      // look-back over the preceding tiles' counts of digit d, kLook descriptors per round: the loads of a round are
+      // independent (one L2 round trip for all of them) — walking back one tile at a time made a pass latency-bound,
+      // ~30 dependent reads per tile with some hundred tiles in flight
+      constexpr int kLook = 8;
+      bool done = false;
+      for (int t = (int)tile - 1; !done; t -= kLook) {
+        uint32_t v[kLook];
+#pragma unroll
+        for (int k = 0; k < kLook; k++) v[k] = t - k >= 0 ? st[(size_t)(t - k) * 256 + d] : (uint32_t)(2u << 30);
+#pragma unroll
+        for (int k = 0; k < kLook; k++) {
+          if (done) break;
+          while ((v[k] & ~kSortValueMask) == 0u) v[k] = st[(size_t)(t - k) * 256 + d];
+          excl += v[k] & kSortValueMask;
+          done = (v[k] & kSortFlagPrefix) != 0u;
+        }
       }
       st[(size_t)tile * 256 + d] = kSortFlagPrefix | (excl + tile_cnt);
     }
