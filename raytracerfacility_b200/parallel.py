@@ -99,7 +99,9 @@ class DistributedRayTracer:
     the library's own NCCL communicator (csrc/multi.cu: rtf_comm_init_rank + the rtf_*_sharded entry points);
     torch.distributed only carries the 128-byte communicator id from rank 0 to the others at start-up.  Scene calls are
     replicated (every rank commits the same scene).  Stream contract: the context and every tensor handed to it live on
-    ONE non-default torch stream (self.stream), so allocation, kernels and collectives are ordered."""
+    ONE non-default torch stream (self.stream), so allocation, kernels and collectives are ordered; before a method
+    returns a tensor, the caller's current stream is made to wait for self.stream (the `_device` entry points only enqueue),
+    so `.cpu()` or any torch op on the result is ordered after the job whatever stream the caller runs on."""
 
     def __init__(self, rt, rank=0, world=1, group=None, stream=None):
         import torch
@@ -125,6 +127,7 @@ class DistributedRayTracer:
             out = torch.empty(n * 6, dtype=torch.float32, device=torch.device("cuda", rt.device))
             rt.estimate_illumination_mesh_sharded_device(env, ray_props, seed, push, front, back,
                                                          0 if mode == "sample" else 1, out.data_ptr())
+        torch.cuda.current_stream(out.device).wait_stream(self.stream)
         return out.view(n, 6)
 
     def scan_grid(self, grid, gather=False):
@@ -138,6 +141,7 @@ class DistributedRayTracer:
             t = torch.empty(total, dtype=torch.float32, device=dev)
             prim = torch.empty(total, dtype=torch.int32, device=dev)
             b, e = rt.scan_grid_sharded_device(grid, gather, t.data_ptr(), prim.data_ptr())
+        torch.cuda.current_stream(dev).wait_stream(self.stream)
         if gather and self.world > 1:
             return (0, total), t, prim
         return (b, e), t[b:e], prim[b:e]
