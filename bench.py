@@ -225,13 +225,13 @@ def reference_arm(args):
         ref_prog = {"value": k / rdt / 1e6, "unit": UNIT, "cores": 1, "kind": "reference",
                     "sample": f"first {k} rays through the reference's PointCloudScanning programs on the host, one thread",
                     "hit_rate": float(smp["hit"].mean())}
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": headline_config(args, osc.n_tris),
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "reference_programs": ref_prog, "gpu_launches": 0}))
+        "reference_programs": ref_prog, "gpu_launches": 0})
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -495,7 +495,26 @@ def run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, par
     return res
 
 
+_JSON_FD = None
+
+
+def emit(obj):
+    """The ONE JSON line of the contract, on the process's real stdout."""
+    line = (json.dumps(obj) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, line)
+
+
 def main():
+    # Libraries print to stdout behind our back (NCCL's "NCCL version ..." banner at communicator creation, torchrun's
+    # notices): keep file descriptor 1 for the JSON line alone and send everything else to stderr.
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     args = parse()
     if args.impl == "reference":
         return reference_arm(args)
@@ -709,7 +728,7 @@ def main():
             out["illum"] = {"metric": "illum triangle-samples/s", "value": c3["triangle_samples_per_s"], "ms": c3["ms"],
                             "scaling": "strong", "config": c3["what"], "Mrays/s": c3["Mrays_per_s"]}
     if rank == 0:
-        print(json.dumps(out))
+        emit(out)
     rt.destroy()
     if world > 1:
         import torch.distributed as dist
