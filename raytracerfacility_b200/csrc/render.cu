@@ -824,7 +824,10 @@ struct SrcGrid {
     if (inst_out) inst_out[k] = h.prim == 0xFFFFFFFFu ? 0xFFFFFFFFu : __ldg(tri_inst + h.prim);
   }
 };
-__global__ void __launch_bounds__(kTraceBlock) k_scan_grid(DevScene sc, SrcGrid src, uint32_t* work) {
+#ifndef RTF_SCAN_MIN_BLOCKS
+#define RTF_SCAN_MIN_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(kTraceBlock, RTF_SCAN_MIN_BLOCKS) k_scan_grid(DevScene sc, SrcGrid src, uint32_t* work) {
   __shared__ TraceSmem sm;
   trace_engine<false>(sc.nodes, sc.tris, src, work, sm);
 }
