@@ -333,7 +333,7 @@ def entry_point_e2e(rt, torch, S, world, barrier, max_over_ranks):
     return res
 
 
-def run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, parity_on, timed, sum_over_ranks, peak):
+def run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, parity_on, timed, sum_over_ranks, peak, per_rank):
     """BASELINE.json's five configurations at full size through the sharded entry points of the library."""
     res = {}
     sub = None
@@ -440,24 +440,30 @@ def run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, par
             box["r"] = drt.scan_grid(cfg.grid)
         job()
         ms = min(timed(job) for _ in range(reps))
-        (b, e), t, prim = box["r"]
+        t2d, p2d, _ = box["r"]
+        block = int(t2d.shape[1])
+        prim, starts = drt.local_rays(total, p2d)
+        n_local = int(prim.numel())
         hits = sum_over_ranks(float((prim != -1).sum().item()))
-        host_t = torch.empty(e - b, dtype=torch.float32).pin_memory()
-        host_p = torch.empty(e - b, dtype=torch.int32).pin_memory()
+        host_t = torch.empty(n_local, dtype=torch.float32).pin_memory()
+        host_p = torch.empty(n_local, dtype=torch.int32).pin_memory()
 
         def e2e():
-            (_, _), tt, pp = drt.scan_grid(cfg.grid)
-            host_t.copy_(tt, non_blocking=True), host_p.copy_(pp, non_blocking=True)
+            tt, pp, _ = drt.scan_grid(cfg.grid)
+            host_t.copy_(drt.local_rays(total, tt)[0], non_blocking=True)
+            host_p.copy_(drt.local_rays(total, pp)[0], non_blocking=True)
         e2e()
         ms2 = min(timed(e2e) for _ in range(reps))
         phases = dict(profiled(job), **rt.phase_timings())
-        d = {"what": f"{cfg.what}; ray ranges x{world}, no collective", "rays": total, "ms": ms, "Mrays_per_s": total / ms / 1e3,
-             "ms_incl_d2h": ms2, "Mrays_per_s_incl_d2h": total / ms2 / 1e3, "d2h_bytes_per_gpu": (e - b) * 8,
-             "hit_fraction": hits / total, "phases_ms_rank0": phases, "timed_runs": reps, **info}
+        trace_ms_ranks = [round(x, 3) for x in per_rank(phases["trace_ms"])]
+        d = {"what": f"{cfg.what}; interleaved blocks of {block} rays x{world}, no collective", "rays": total, "ms": ms,
+             "Mrays_per_s": total / ms / 1e3, "ms_incl_d2h": ms2, "Mrays_per_s_incl_d2h": total / ms2 / 1e3,
+             "d2h_bytes_per_gpu": n_local * 8, "hit_fraction": hits / total, "phases_ms_rank0": phases,
+             "trace_ms_per_rank": trace_ms_ranks, "timed_runs": reps, **info}
         if sub is not None:
             osc, bs = sub.build(cfg)
-            par = sub.lidar(osc, cfg, host_t.numpy(), host_p.numpy(), 1024, ray_begin=b)
-            d["parity"] = dict(par, oracle_build_s=bs, rank0_ray_range=[b, e])
+            par = sub.lidar_blocks(osc, cfg, host_t.numpy(), host_p.numpy(), starts, block, 1024)
+            d["parity"] = dict(par, oracle_build_s=bs, rank0_blocks=len(starts))
             d["cpu_baseline"] = {"value": par["cpu_Mrays_per_s"], "unit": "Mrays/s", "cores": par["cpu_threads"], "kind": "port",
                                  "sample": par["sample"]}
         box.clear()
@@ -722,7 +728,7 @@ def main():
         want = [c for c in args.configs.split(",") if c]
         configs.clear_scene(rt, sd)
         out["configs"] = run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, parity_on, timed,
-                                     sum_over_ranks, peak)
+                                     sum_over_ranks, peak, per_rank)
         c3 = out["configs"].get("C3")
         if c3:  # M2 of BASELINE.json, on its own configuration
             out["illum"] = {"metric": "illum triangle-samples/s", "value": c3["triangle_samples_per_s"], "ms": c3["ms"],

@@ -465,10 +465,13 @@ RTF_API int rtf_estimate_illumination_mesh_sharded_device(rtf_ctx* ctx, const rt
 RTF_API int rtf_estimate_illumination_mesh_sharded(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* ray_props,
                                                    uint32_t seed, float push_normal_distance, int front_face, int back_face,
                                                    int mode, float* out6 /* host */);
-/* The rank's ray range [*begin, *end) of the scan grid is traced into elements [*begin, *end) of the FULL-SIZE device
- * arrays (each nullable); gather != 0 completes them on every rank (grouped broadcasts). */
+/* LiDAR shards are interleaved blocks of *block_rays consecutive rays (a power of two, about 16 blocks per rank): block k
+ * of the *n_blocks blocks of the grid belongs to rank k mod nranks, the last block may be partial.  The rank traces its
+ * blocks into the rays' own elements of the FULL-SIZE device arrays (each nullable); gather != 0 completes them on every
+ * rank (grouped broadcasts).  Contiguous ranges per rank left the ranks over a field's bare rim idle. */
 RTF_API int rtf_scan_grid_trace_sharded_device(rtf_ctx* ctx, const rtf_scan_grid* grid, int gather, float* dev_t,
-                                               uint32_t* dev_prim, uint32_t* dev_inst, uint64_t* begin, uint64_t* end);
+                                               uint32_t* dev_prim, uint32_t* dev_inst, uint64_t* block_rays,
+                                               uint64_t* n_blocks);
 /* RenderToCamera over interleaved row bands; outputs_mask: bit RTF_OUT_COLOR / NORMAL / ALBEDO = complete that buffer on
  * every rank (one group of broadcasts each).  Pixels keep their global RNG streams: bit-identical to the 1-GPU frame. */
 RTF_API int rtf_render_camera_sharded(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* ray_props,
@@ -499,7 +502,8 @@ RTF_API int rtf_multi_commit(rtf_multi* m, int morton_bits);
 RTF_API int rtf_multi_estimate_illumination_mesh(rtf_multi* m, const rtf_env* env, const rtf_ray_props* ray_props, uint32_t seed,
                                                  float push_normal_distance, int front_face, int back_face, int mode,
                                                  float* out6 /* host, 6 floats per triangle */);
-/* every device traces its ray range and copies its slice straight into the caller's arrays (n PCIe links, no collective) */
+/* every device traces its interleaved blocks and copies them straight to their places in the caller's arrays (n PCIe
+ * links, no collective) */
 RTF_API int rtf_multi_scan_grid_trace(rtf_multi* m, const rtf_scan_grid* grid, float* t_out, uint32_t* prim_id_out,
                                       uint32_t* inst_id_out);
 RTF_API int rtf_multi_trace_closest(rtf_multi* m, const float* rays, size_t n, void* hits);

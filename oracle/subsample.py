@@ -86,6 +86,29 @@ def lidar(osc, cfg, gpu_t, gpu_prim, stride, ray_begin=0, nthreads=None):
             "cpu_s": dt, "cpu_threads": nthreads, "cpu_Mrays_per_s": len(t) / dt / 1e6, **_visits(st)}
 
 
+def lidar_blocks(osc, cfg, gpu_t, gpu_prim, block_starts, block, stride, nthreads=None):
+    """lidar() over interleaved shards: gpu_t / gpu_prim hold the rays of the blocks starting at `block_starts`
+    (`block` rays each, the last one possibly shorter), one after the other."""
+    parts, off = [], 0
+    for b in block_starts:
+        n = min(block, len(gpu_t) - off)
+        if n <= 0:
+            break
+        parts.append(lidar(osc, cfg, gpu_t[off:off + n], gpu_prim[off:off + n], stride, ray_begin=b, nthreads=nthreads))
+        off += n
+    rays = sum(int(p["sample"].split("(")[1].split()[0]) for p in parts)
+    cpu_s = sum(p["cpu_s"] for p in parts)
+    w = [int(p["sample"].split("(")[1].split()[0]) for p in parts]
+    tot = max(1, sum(w))
+    return {"ok": all(p["ok"] for p in parts), "sample": f"every {stride}-th ray of {len(parts)} interleaved blocks ({rays} rays)",
+            "prim_ids_bit_exact": all(p["prim_ids_bit_exact"] for p in parts),
+            "distances_bit_exact": all(p["distances_bit_exact"] for p in parts),
+            "hit_fraction_on_sample": sum(p["hit_fraction_on_sample"] * x for p, x in zip(parts, w)) / tot,
+            "cpu_s": cpu_s, "cpu_threads": parts[0]["cpu_threads"] if parts else 0, "cpu_Mrays_per_s": rays / max(cpu_s, 1e-12) / 1e6,
+            "mean_nodes_per_ray": sum(p["mean_nodes_per_ray"] * x for p, x in zip(parts, w)) / tot,
+            "mean_tris_per_ray": sum(p["mean_tris_per_ray"] * x for p, x in zip(parts, w)) / tot}
+
+
 def camera(osc, cfg, cam_props, gpu_color, stride, nthreads=None):
     """gpu_color: (h, w, 4) colour buffer of frame 0.  Oracle: pixels 0, stride, ... (row-major)."""
     nthreads = threads() if nthreads is None else nthreads

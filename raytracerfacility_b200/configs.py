@@ -1,5 +1,5 @@
 """The five BASELINE.json configurations as data: scene, environment, ray properties, camera pose / scan grid.
-One place, so that bench.py, tools/run_configs.py and tests/test_gpu_configs.py run the SAME jobs (SURVEY.md 8(d)
+One place, so that bench.py and tests/test_gpu_configs.py run the SAME jobs (SURVEY.md 8(d)
 "Synthetic inputs": the reference ships no meshes, scenes or BTF data, everything is generated from fixed seeds).
 
 C1  per-triangle illumination, one sorghum plant + ground (20 002 triangles), sky light, 64 samples/triangle

@@ -106,25 +106,40 @@ int illum_sharded_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* 
   return RTF_OK;
 }
 
+// Broadcast every rank's interleaved blocks of a full-size array in place (one group).
+static int gather_blocks(rtf_ctx* ctx, void* buf, uint64_t total, uint32_t shift, uint64_t n_blocks, size_t elem) {
+  if (ctx->nranks <= 1) return RTF_OK;
+  const uint64_t B = 1ull << shift;
+  RTF_NCCL(ncclGroupStart());
+  for (uint64_t k = 0; k < n_blocks; k++) {
+    const uint64_t b = k * B, e = (k + 1) * B < total ? (k + 1) * B : total;
+    char* p = (char*)buf + b * elem;
+    RTF_NCCL(ncclBroadcast(p, p, (e - b) * elem, ncclChar, (int)(k % (uint64_t)ctx->nranks), comm_of(ctx), ctx->stream));
+  }
+  RTF_NCCL(ncclGroupEnd());
+  return RTF_OK;
+}
+
+// LiDAR shards are INTERLEAVED blocks of the ray grid (block k belongs to rank k mod nranks, ~16 blocks per rank): a
+// contiguous range per rank left the ranks that scan the bare rim of a field idle while the ones over the canopy worked
+// (C4 at 8 GPUs: 1.5 ms against 5.8 ms, 74 % efficiency).  Results land at the rays' own indices of the full-size arrays.
 int scan_grid_sharded_device(rtf_ctx* ctx, const rtf_scan_grid* grid, int gather, float* d_t, uint32_t* d_prim, uint32_t* d_inst,
-                             uint64_t* begin, uint64_t* end) {
-  uint32_t column = 0, row = 0;
+                             uint64_t* block_rays, uint64_t* n_blocks) {
+  uint32_t column = 0, row = 0, shift = 0;
   int rc;
   if ((rc = rtf_scan_grid_dims(grid, &column, &row))) return rc;
   const uint64_t total = (uint64_t)column * row;
-  uint64_t b, e;
-  shard_range(total, ctx->nranks, ctx->rank, &b, &e);
-  if (begin) *begin = b;
-  if (end) *end = e;
+  uint64_t nb = 0, n_local = 0;
+  scan_interleave_layout(total, ctx->nranks, ctx->rank, &shift, &nb, &n_local);
+  if (block_rays) *block_rays = 1ull << shift;
+  if (n_blocks) *n_blocks = nb;
   phase_mark(ctx, 0);
-  if (e > b)
-    if ((rc = scan_grid_device(ctx, grid, b, e, d_t ? d_t + b : nullptr, d_prim ? d_prim + b : nullptr, d_inst ? d_inst + b : nullptr)))
-      return rc;
+  if ((rc = scan_grid_interleaved_device(ctx, grid, ctx->nranks, ctx->rank, true, d_t, d_prim, d_inst))) return rc;
   phase_mark(ctx, 1);
   if (gather) {
-    if (d_t && (rc = gather_ranges(ctx, d_t, total, 4))) return rc;
-    if (d_prim && (rc = gather_ranges(ctx, d_prim, total, 4))) return rc;
-    if (d_inst && (rc = gather_ranges(ctx, d_inst, total, 4))) return rc;
+    if (d_t && (rc = gather_blocks(ctx, d_t, total, shift, nb, 4))) return rc;
+    if (d_prim && (rc = gather_blocks(ctx, d_prim, total, shift, nb, 4))) return rc;
+    if (d_inst && (rc = gather_blocks(ctx, d_inst, total, shift, nb, 4))) return rc;
   }
   phase_mark(ctx, 2);
   phase_mark(ctx, 3);
@@ -271,10 +286,10 @@ int rtf_estimate_illumination_mesh_sharded(rtf_ctx* ctx, const rtf_env* env, con
   return RTF_OK;
 }
 int rtf_scan_grid_trace_sharded_device(rtf_ctx* ctx, const rtf_scan_grid* grid, int gather, float* dev_t, uint32_t* dev_prim,
-                                       uint32_t* dev_inst, uint64_t* begin, uint64_t* end) {
+                                       uint32_t* dev_inst, uint64_t* block_rays, uint64_t* n_blocks) {
   CHECK_CTX(ctx);
   if (!grid || (!dev_t && !dev_prim && !dev_inst)) return RTF_ERR_INVALID;
-  return scan_grid_sharded_device(ctx, grid, gather, dev_t, dev_prim, dev_inst, begin, end);
+  return scan_grid_sharded_device(ctx, grid, gather, dev_t, dev_prim, dev_inst, block_rays, n_blocks);
 }
 int rtf_render_camera_sharded(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, int outputs_mask) {
   CHECK_CTX(ctx);
@@ -438,8 +453,9 @@ int rtf_multi_estimate_illumination_mesh(rtf_multi* m, const rtf_env* env, const
     return RTF_OK;
   });
 }
-// Every device traces its ray range and copies ITS slice straight into the caller's arrays: n PCIe links in parallel,
-// no collective (SURVEY §8e "preferred").
+// Every device traces its interleaved blocks of the grid into dense device arrays and copies them straight to their
+// places in the caller's arrays (one strided copy per array: n PCIe links in parallel, no collective — SURVEY §8e
+// "preferred").
 int rtf_multi_scan_grid_trace(rtf_multi* m, const rtf_scan_grid* grid, float* t_out, uint32_t* prim_out, uint32_t* inst_out) {
   if (!m || !grid) return RTF_ERR_INVALID;
   uint32_t column = 0, row = 0;
@@ -447,11 +463,40 @@ int rtf_multi_scan_grid_trace(rtf_multi* m, const rtf_scan_grid* grid, float* t_
   if (rc0) return rc0;
   const uint64_t total = (uint64_t)column * row;
   return run_all(m, [&](int, rtf_ctx* c) -> int {
-    cudaSetDevice(c->device);
-    uint64_t b, e;
-    shard_range(total, c->nranks, c->rank, &b, &e);
-    return rtf_scan_grid_trace(c, grid, b, e, t_out ? t_out + b : nullptr, prim_out ? prim_out + b : nullptr,
-                               inst_out ? inst_out + b : nullptr);
+    RTF_CUDA(cudaSetDevice(c->device));
+    if (!c->ready) {
+      set_error("no acceleration structure (call rtf_commit)");
+      return RTF_ERR_NOT_READY;
+    }
+    uint32_t shift = 0;
+    uint64_t nb = 0, n_local = 0;
+    scan_interleave_layout(total, c->nranks, c->rank, &shift, &nb, &n_local);
+    if (n_local == 0) return RTF_OK;
+    int rc;
+    if ((rc = c->ws.io.reserve(n_local * 12))) return rc;
+    float* dt = c->ws.io.as<float>();
+    uint32_t* dp = (uint32_t*)(dt + n_local);
+    uint32_t* di = dp + n_local;
+    if ((rc = scan_grid_interleaved_device(c, grid, c->nranks, c->rank, false, t_out ? dt : nullptr, prim_out ? dp : nullptr,
+                                           inst_out ? di : nullptr)))
+      return rc;
+    const uint64_t B = 1ull << shift;
+    const uint64_t mine = ((nb - (uint64_t)c->rank) + (uint64_t)c->nranks - 1) / (uint64_t)c->nranks;  // blocks of this rank
+    const bool partial_last = (nb - 1) % (uint64_t)c->nranks == (uint64_t)c->rank && nb * B != total;
+    const uint64_t full = partial_last ? mine - 1 : mine;
+    void* host[3] = {t_out, prim_out, inst_out};
+    void* dev[3] = {dt, dp, di};
+    for (int a = 0; a < 3; a++) {
+      if (!host[a]) continue;
+      char* h = (char*)host[a] + (uint64_t)c->rank * B * 4;
+      if (full)
+        RTF_CUDA(cudaMemcpy2DAsync(h, (size_t)c->nranks * B * 4, dev[a], B * 4, B * 4, full, cudaMemcpyDeviceToHost, c->stream));
+      if (partial_last)
+        RTF_CUDA(cudaMemcpyAsync((char*)host[a] + (nb - 1) * B * 4, (char*)dev[a] + full * B * 4, (total - (nb - 1) * B) * 4,
+                                 cudaMemcpyDeviceToHost, c->stream));
+    }
+    RTF_CUDA(cudaStreamSynchronize(c->stream));
+    return RTF_OK;
   });
 }
 // Host rays in, host hits out: contiguous ray ranges, each device running its own upload / trace / download pipeline.

@@ -806,8 +806,18 @@ struct SrcGrid {
   uint32_t* prim_out;
   uint32_t* inst_out;
   const uint32_t* tri_inst;
+  // Interleaved shards (multi-GPU, il_stride = number of ranks, 0 = one contiguous range): the launch's ray j is ray
+  // (j mod B) of block (j / B) * il_stride + il_rank of the grid, B = 2^il_shift — contiguous ranges of a plant field
+  // differ several-fold in cost (bare ground at the rim, canopy in the middle).  out_global: results go to the ray's
+  // own index of full-size arrays instead of the launch-local one.
+  uint32_t il_shift, il_stride, il_rank, out_global;
+  RTF_D uint64_t ray_index(uint32_t j) const {
+    if (il_stride == 0u) return ray_begin + j;
+    const uint64_t blk = (uint64_t)(j >> il_shift) * il_stride + il_rank;
+    return (blk << il_shift) | (uint64_t)(j & ((1u << il_shift) - 1u));
+  }
   RTF_D void fetch(const unsigned char*, uint32_t base, uint32_t slot, float4& a, float4& b, float& tmin, uint32_t& tag) const {
-    const uint64_t i = ray_begin + base + slot;
+    const uint64_t i = ray_index(base + slot);
     const int ci = (int)(i / row), ri = (int)(i % row);
     const float3 center = f3(g.center[0], g.center[1], g.center[2]);
     const float3 left = f3(g.left[0], g.left[1], g.left[2]), up = f3(g.up[0], g.up[1], g.up[2]);
@@ -818,7 +828,8 @@ struct SrcGrid {
   }
   RTF_D bool any_hit(uint32_t) const { return false; }
   RTF_D bool alpha_pass(uint32_t, uint32_t, uint32_t, float, float) const { return true; }
-  RTF_D void store(uint32_t k, uint32_t, const HitRec& h, uint32_t, uint32_t) const {
+  RTF_D void store(uint32_t j, uint32_t, const HitRec& h, uint32_t, uint32_t) const {
+    const uint64_t k = out_global ? ray_index(j) : (uint64_t)j;
     if (t_out) t_out[k] = h.t;
     if (prim_out) prim_out[k] = h.prim;
     if (inst_out) inst_out[k] = h.prim == 0xFFFFFFFFu ? 0xFFFFFFFFu : __ldg(tri_inst + h.prim);
@@ -892,9 +903,48 @@ int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin
     const uint64_t o = off - ray_begin;
     SrcGrid src{*grid, row, -(int)(column / 2), -(int)(row / 2),
                 normalize3(f3(grid->direction[0], grid->direction[1], grid->direction[2])), off, m,
-                d_t ? d_t + o : nullptr, d_prim ? d_prim + o : nullptr, d_inst ? d_inst + o : nullptr, ctx->scene.tri_inst};
+                d_t ? d_t + o : nullptr, d_prim ? d_prim + o : nullptr, d_inst ? d_inst + o : nullptr, ctx->scene.tri_inst,
+                0u, 0u, 0u, 0u};
     LAUNCH_P(ctx, PROF_TRACE, k_scan_grid, trace_grid(ctx, TK_GRID, k_scan_grid, m), kTraceBlock, 0, ctx->scene, src, work);
   }
+  RTF_CUDA(cudaGetLastError());
+  return RTF_OK;
+}
+// Block layout of the interleaved LiDAR shards: about 16 blocks per rank, 2^12 .. 2^24 rays each.
+void scan_interleave_layout(uint64_t total, int nranks, int rank, uint32_t* shift, uint64_t* n_blocks, uint64_t* n_local) {
+  uint32_t sh = 12;
+  while (sh < 24 && (total >> sh) > 16ull * (uint64_t)nranks) sh++;
+  const uint64_t B = 1ull << sh, nb = (total + B - 1) / B;
+  uint64_t mine = (uint64_t)rank < nb ? (nb - (uint64_t)rank + (uint64_t)nranks - 1) / (uint64_t)nranks : 0;
+  uint64_t rays = mine * B;
+  if (mine && (nb - 1) % (uint64_t)nranks == (uint64_t)rank) rays -= nb * B - total;  // the grid's last block is partial
+  *shift = sh, *n_blocks = nb, *n_local = rays;
+}
+// The rank's interleaved blocks of the grid in one launch.  global_out: d_* are full-size arrays indexed by ray;
+// otherwise they hold the rank's rays densely, block after block.
+int scan_grid_interleaved_device(rtf_ctx* ctx, const rtf_scan_grid* grid, int nranks, int rank, bool global_out, float* d_t,
+                                 uint32_t* d_prim, uint32_t* d_inst) {
+  if (!ctx->ready) {
+    set_error("no acceleration structure (call rtf_commit)");
+    return RTF_ERR_NOT_READY;
+  }
+  uint32_t column = 0, row = 0, shift = 0;
+  int rc;
+  if ((rc = rtf_scan_grid_dims(grid, &column, &row))) return rc;
+  uint64_t nb = 0, n_local = 0;
+  scan_interleave_layout((uint64_t)column * row, nranks, rank, &shift, &nb, &n_local);
+  if (n_local == 0) return RTF_OK;
+  if (n_local >= (1ull << 32)) {
+    set_error("interleaved scan: more than 2^32 rays per rank");
+    return RTF_ERR_LIMIT;
+  }
+  if ((rc = ctx->ws.counters.reserve(4096))) return rc;
+  uint32_t* work = ctx->ws.counters.as<uint32_t>();
+  RTF_CUDA(cudaMemsetAsync(work, 0, 4, ctx->stream));
+  SrcGrid src{*grid, row, -(int)(column / 2), -(int)(row / 2),
+              normalize3(f3(grid->direction[0], grid->direction[1], grid->direction[2])), 0, (uint32_t)n_local,
+              d_t, d_prim, d_inst, ctx->scene.tri_inst, shift, (uint32_t)nranks, (uint32_t)rank, global_out ? 1u : 0u};
+  LAUNCH_P(ctx, PROF_TRACE, k_scan_grid, trace_grid(ctx, TK_GRID, k_scan_grid, n_local), kTraceBlock, 0, ctx->scene, src, work);
   RTF_CUDA(cudaGetLastError());
   return RTF_OK;
 }

@@ -296,6 +296,9 @@ int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp,
 int illum_finalize_device(rtf_ctx* ctx, float* d_accum6, uint64_t n, int faces, int samples, rtf_illum_sampler* d_probes);
 int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin, uint64_t ray_end, float* d_t,
                      uint32_t* d_prim, uint32_t* d_inst);
+void scan_interleave_layout(uint64_t total, int nranks, int rank, uint32_t* shift, uint64_t* n_blocks, uint64_t* n_local);
+int scan_grid_interleaved_device(rtf_ctx* ctx, const rtf_scan_grid* grid, int nranks, int rank, bool global_out, float* d_t,
+                                 uint32_t* d_prim, uint32_t* d_inst);
 int scan_samples_device(rtf_ctx* ctx, rtf_pc_sample* d_samples, size_t n, uint32_t* d_prim);
 int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, uint64_t px_begin,
                          uint64_t px_end);

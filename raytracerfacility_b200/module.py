@@ -469,11 +469,13 @@ class RayTracer:
         return out
 
     def scan_grid_sharded_device(self, grid, gather, dev_t_ptr, dev_prim_ptr, dev_inst_ptr=None):
-        b, e = C.c_uint64(), C.c_uint64()
+        """Traces this rank's interleaved blocks into full-size device arrays; returns (block_rays, n_blocks): block k of
+        the grid (rays [k * block_rays, (k + 1) * block_rays)) belongs to rank k mod nranks."""
+        blk, nb = C.c_uint64(), C.c_uint64()
         _check(lib().rtf_scan_grid_trace_sharded_device(self.h, C.byref(grid), int(gather), C.c_void_p(dev_t_ptr),
-                                                        C.c_void_p(dev_prim_ptr), C.c_void_p(dev_inst_ptr), C.byref(b),
-                                                        C.byref(e)))
-        return b.value, e.value
+                                                        C.c_void_p(dev_prim_ptr), C.c_void_p(dev_inst_ptr), C.byref(blk),
+                                                        C.byref(nb)))
+        return blk.value, nb.value
 
     def render_to_camera_sharded(self, env, camera, ray_props, outputs_mask=1):
         return _check(lib().rtf_render_camera_sharded(self.h, C.byref(env), camera.h, C.byref(ray_props),

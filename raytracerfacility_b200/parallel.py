@@ -131,20 +131,32 @@ class DistributedRayTracer:
         return out.view(n, 6)
 
     def scan_grid(self, grid, gather=False):
-        """Each rank traces its contiguous ray range into elements [b, e) of full-size device tensors (t, prim); gather
-        completes them on every rank.  Returns ((b, e), t, prim) with the rank's slices, or the full arrays if gathered."""
+        """Each rank traces its INTERLEAVED blocks of the ray grid (block k belongs to rank k mod world) into full-size
+        device tensors; gather completes them on every rank.  Returns (t, prim, mine): t and prim are (n_blocks, block)
+        views of the padded arrays (ray i = element [i // block, i % block]; the tail of the last block is padding),
+        mine = slice(rank, None, world) selects this rank's blocks (`local_rays` flattens them without the padding)."""
         import torch
         rt = self.rt
         total = rt.scan_grid_ray_count(grid)
         with torch.cuda.stream(self.stream):
             dev = torch.device("cuda", rt.device)
-            t = torch.empty(total, dtype=torch.float32, device=dev)
-            prim = torch.empty(total, dtype=torch.int32, device=dev)
-            b, e = rt.scan_grid_sharded_device(grid, gather, t.data_ptr(), prim.data_ptr())
+            # one block more than any layout needs (blocks are at most 2^24 rays), so that the padded view always fits
+            t = torch.empty(total + (1 << 24), dtype=torch.float32, device=dev)
+            prim = torch.empty(total + (1 << 24), dtype=torch.int32, device=dev)
+            block, n_blocks = rt.scan_grid_sharded_device(grid, gather, t.data_ptr(), prim.data_ptr())
         torch.cuda.current_stream(dev).wait_stream(self.stream)
-        if gather and self.world > 1:
-            return (0, total), t, prim
-        return (b, e), t[b:e], prim[b:e]
+        return t[:n_blocks * block].view(n_blocks, block), prim[:n_blocks * block].view(n_blocks, block), \
+            slice(self.rank, None, self.world)
+
+    def local_rays(self, total, arr2d):
+        """This rank's rays of a (n_blocks, block) scan array as one flat tensor (block after block, padding cut off) and
+        the first ray index of every block in it."""
+        n_blocks, block = arr2d.shape
+        rows = arr2d[self.rank::self.world]
+        flat = rows.reshape(-1)
+        owns_last = n_blocks > 0 and (n_blocks - 1) % self.world == self.rank
+        n = flat.numel() - ((n_blocks * block - total) if owns_last else 0)
+        return flat[:n], [k * block for k in range(self.rank, n_blocks, self.world)]
 
     def render_to_camera(self, env, camera, ray_props, outputs=(0,)):
         mask = 0

@@ -25,10 +25,18 @@ def main():
     err = np.abs(a[:, :3] - whole[:, :3]) / np.maximum(np.abs(whole[:, :3]), 1e-30)
     assert err.max() <= 1e-5, err.max()
     assert np.array_equal(b.view(np.uint32), whole.view(np.uint32)), "triangle-sharded result differs from one GPU"
-    grid = scenes.lidar_grid(center=(0.0, 5.0, 0.0), size=(4.0, 4.0), distance=(0.01, 0.01))
+    grid = scenes.lidar_grid(center=(0.0, 5.0, 0.0), size=(4.0, 4.0), distance=(0.01, 0.01))  # 160 000 rays: 40 blocks of 4096
     t1, p1, _ = rt.scan_grid(grid)
-    (_, _), tg, pg = drt.scan_grid(grid, gather=True)
-    assert np.array_equal(tg.cpu().numpy().view(np.uint32), t1.view(np.uint32)) and np.array_equal(pg.cpu().numpy().view(np.uint32), p1)
+    tg, pg, mine = drt.scan_grid(grid, gather=True)  # interleaved blocks, completed on every rank
+    n = len(t1)
+    assert np.array_equal(tg.reshape(-1)[:n].cpu().numpy().view(np.uint32), t1.view(np.uint32))
+    assert np.array_equal(pg.reshape(-1)[:n].cpu().numpy().view(np.uint32), p1)
+    tl, pl, _ = drt.scan_grid(grid, gather=False)  # only this rank's blocks are written
+    loc, starts = drt.local_rays(n, pl)
+    blk = pl.shape[1]
+    ref = np.concatenate([p1[b:b + blk] for b in starts]) if starts else p1[:0]
+    assert np.array_equal(loc.cpu().numpy().view(np.uint32), ref), "interleaved blocks differ from one GPU"
+    assert tl.shape[0] >= world, "grid too small to give every rank a block"
     cam1, camn = rt.create_camera(), rt.create_camera()
     for c in (cam1, camn):
         c.resize(256, 160)
