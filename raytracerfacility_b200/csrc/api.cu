@@ -934,16 +934,14 @@ namespace rtf {
 // RenderToCamera (RayTracer.cu:244-603) for a list of row bands [rows[2k], rows[2k+1]) of ONE frame: the change
 // detection runs once, every band sees the same frame id, the id advances once.  Returns 1 / 0 like the reference's bool
 // (0 = no acceleration structure), < 0 on error.  Blocks until the bands are rendered.
-int render_camera_bands(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, const int* rows, int n_bands) {
-  if (!env || !cam || !rp || (!rows && n_bands)) return RTF_ERR_INVALID;
+// RenderToCamera's bookkeeping around the launch (RayTracer.cu:244-269, 349-352): 1 = render, 0 / 1-without-work as the
+// reference returns them.
+static int camera_job_begin(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, bool* skip) {
   rtf_camera_props& p = cam->props;
+  *skip = true;
   if (p.width == 0 || p.height == 0) return 1;  // RayTracer.cu:246-247
   if (!ctx->ready) return 0;                    // RayTracer.cu:248-249
-  for (int k = 0; k < n_bands; k++)
-    if (rows[2 * k] < 0 || rows[2 * k + 1] > p.height || rows[2 * k] > rows[2 * k + 1]) {
-      set_error("rtf_render_camera_rows: bad row range");
-      return RTF_ERR_INVALID;
-    }
+  *skip = false;
   bool changed = p.modified != 0;
   p.modified = 0;
   if (!ctx->cam_last_valid || memcmp(&ctx->cam_last_env, env, sizeof(rtf_env)) != 0) ctx->cam_last_env = *env, changed = true;
@@ -953,31 +951,51 @@ int render_camera_bands(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const
   if (ctx->cam_last_epoch != ctx->epoch) ctx->cam_last_epoch = ctx->epoch, changed = true;
   ctx->cam_last_valid = true;
   if (!p.accumulate || changed) p.frame_id = 0;  // RayTracer.cu:266-269
-  // the launch sees the frame id before the increment (RayTracer.cu:349-352)
-  uint64_t paths = 0, rays = 0;
-  for (int k = 0; k < n_bands; k++) {
-    int rc = render_camera_device(ctx, env, cam, rp, (uint64_t)rows[2 * k] * p.width, (uint64_t)rows[2 * k + 1] * p.width);
-    if (rc) return rc;
-    paths += ctx->last_paths;
-    if (n_bands > 1) {  // the job statistics are per call of render_camera_device: sum them over the bands
-      RTF_CUDA(cudaStreamSynchronize(ctx->stream));
-      unsigned long long st[2] = {0, 0};
-      if (ctx->d_stats.p) RTF_CUDA(cudaMemcpy(st, ctx->d_stats.p, 16, cudaMemcpyDeviceToHost));
-      rays += st[0];
-    }
-  }
-  p.frame_id++;
+  return 1;
+}
+static int camera_job_end(rtf_ctx* ctx, rtf_camera* cam, uint64_t paths) {
+  cam->props.frame_id++;  // the launch saw the frame id before the increment (RayTracer.cu:349-352)
   RTF_CUDA(cudaStreamSynchronize(ctx->stream));
-  if (n_bands > 1) {
-    ctx->last_rays = rays;
-  } else {
-    unsigned long long st[2] = {0, 0};
-    if (ctx->d_stats.p) RTF_CUDA(cudaMemcpy(st, ctx->d_stats.p, 16, cudaMemcpyDeviceToHost));
-    ctx->last_rays = st[0];
-  }
+  unsigned long long st[2] = {0, 0};
+  if (ctx->d_stats.p) RTF_CUDA(cudaMemcpy(st, ctx->d_stats.p, 16, cudaMemcpyDeviceToHost));
+  ctx->last_rays = st[0];
   ctx->last_paths = paths;
   ctx->stats_cached = true;
   return 1;
+}
+int render_camera_bands(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, const int* rows, int n_bands) {
+  if (!env || !cam || !rp || (!rows && n_bands)) return RTF_ERR_INVALID;
+  rtf_camera_props& p = cam->props;
+  for (int k = 0; k < n_bands; k++)
+    if (rows[2 * k] < 0 || (p.height > 0 && rows[2 * k + 1] > p.height) || rows[2 * k] > rows[2 * k + 1]) {
+      set_error("rtf_render_camera_rows: bad row range");
+      return RTF_ERR_INVALID;
+    }
+  bool skip;
+  const int st = camera_job_begin(ctx, env, cam, rp, &skip);
+  if (skip) return st;
+  int rc;
+  if ((rc = ctx->d_stats.reserve(64))) return rc;
+  RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, ctx->stream));  // the job counters run over all bands
+  uint64_t paths = 0;
+  ctx->stats_hold = true;
+  for (int k = 0; k < n_bands && !rc; k++) {
+    rc = render_camera_device(ctx, env, cam, rp, (uint64_t)rows[2 * k] * p.width, (uint64_t)rows[2 * k + 1] * p.width);
+    paths += ctx->last_paths;
+  }
+  ctx->stats_hold = false;
+  if (rc) return rc;
+  return camera_job_end(ctx, cam, paths);
+}
+int render_camera_interleaved(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, int band_rows, int nranks,
+                              int rank) {
+  if (!env || !cam || !rp) return RTF_ERR_INVALID;
+  bool skip;
+  const int st = camera_job_begin(ctx, env, cam, rp, &skip);
+  if (skip) return st;
+  int rc;
+  if ((rc = render_camera_interleaved_device(ctx, env, cam, rp, band_rows, nranks, rank))) return rc;
+  return camera_job_end(ctx, cam, ctx->last_paths);
 }
 }  // namespace rtf
 extern "C" {

@@ -159,13 +159,8 @@ int render_camera_sharded(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, con
   const int h = cam->props.height, w = cam->props.width;
   const int br = band_rows_for(h, ctx->nranks);
   const int n_bands = h > 0 ? (h + br - 1) / br : 0;
-  std::vector<int> rows;
-  for (int k = ctx->rank; k < n_bands; k += ctx->nranks) {
-    rows.push_back(k * br);
-    rows.push_back((k + 1) * br < h ? (k + 1) * br : h);
-  }
   phase_mark(ctx, 0);
-  const int ok = render_camera_bands(ctx, env, cam, rp, rows.data(), (int)rows.size() / 2);
+  const int ok = render_camera_interleaved(ctx, env, cam, rp, br, ctx->nranks, ctx->rank);
   if (ok < 0) return ok;
   phase_mark(ctx, 1);
   if (ctx->nranks > 1 && ok == 1 && w > 0) {

@@ -126,17 +126,40 @@ int trace_rays_device(rtf_ctx* ctx, const float4* rays, size_t n, float4* hits, 
 
 // ============================ wavefront machinery ==================================================
 // How a path index of the current batch maps to its RNG unit (and probe / pixel).
+// Local pixel L of a camera job -> pixel of the frame.  band_px == 0: the job is the contiguous range from `first`.
+// Otherwise the job is this rank's interleaved row bands (multi-GPU): local band L / band_px is band
+// (L / band_px) * stride + rank of the frame, band_px = band rows * width pixels each — all bands of a rank run as ONE
+// job, batched like a full frame (one job per band cost a host round trip and five short wavefronts each).
+// A PixelMap describes one BATCH: k is the pixel's index inside the batch (32-bit arithmetic only: a 64-bit division per
+// path doubled the time of the generation kernel).
+struct PixelMap {
+  uint64_t first;                  // contiguous: first pixel of the batch
+  uint32_t band_px, stride, rank;  // interleaved: pixels per band (< 2^31), number of ranks, this rank
+  uint64_t blk0;                   // interleaved: local band and offset inside it of the batch's first pixel
+  uint32_t off0;
+};
+__device__ __forceinline__ uint64_t pixel_of(const PixelMap& m, uint32_t k) {
+  if (m.band_px == 0u) return m.first + k;
+  const uint32_t t = m.off0 + k, b = t / m.band_px, off = t - b * m.band_px;
+  return ((m.blk0 + b) * m.stride + m.rank) * (uint64_t)m.band_px + off;
+}
 struct PathMap {
   int mode;            // 0 = illumination, 1 = camera
-  uint64_t unit_base;  // camera: first pixel * spp
+  uint64_t unit_base;  // camera, contiguous job: first pixel of the batch * spp
   uint64_t tri_begin;  // illumination: first probe of the batch
   uint32_t per_probe;  // 2 * sc
   uint32_t sc;         // samples in this call
   uint32_t s0;         // first sample
   uint32_t s_total;    // RayProperties::m_samples
+  PixelMap px;         // camera, interleaved job (px.band_px != 0): pixel map of the batch, spp
+  uint32_t spp;
 };
 __device__ __forceinline__ uint64_t unit_of(const PathMap& pm, uint32_t p) {
-  if (pm.mode == 1) return pm.unit_base + p;
+  if (pm.mode == 1) {
+    if (pm.px.band_px == 0u) return pm.unit_base + p;
+    const uint32_t k = p / pm.spp;
+    return pixel_of(pm.px, k) * (uint64_t)pm.spp + (p - k * pm.spp);
+  }
   const uint32_t tl = p / pm.per_probe, rem = p - tl * pm.per_probe;
   const uint32_t face = rem / pm.sc, s = pm.s0 + (rem - face * pm.sc);
   return ((pm.tri_begin + tl) * 2ull + face) * (uint64_t)pm.s_total + s;
@@ -774,7 +797,7 @@ int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp,
     RTF_CUDA(cudaMemsetAsync(ctx->ws.counters.p, 0, 4096, ctx->stream));
     IllumGen g{t0, nt, sc_, (uint32_t)s0, (uint32_t)rp->samples, seed, push, front, back, d_probes, probe_base};
     LAUNCH_P(ctx, PROF_GEN, k_gen_illum, div_up(paths, 256), 256, 0, ctx->scene, g, q, ps);
-    PathMap pm{0, 0ull, t0, (uint32_t)per_probe, sc_, (uint32_t)s0, (uint32_t)rp->samples};
+    PathMap pm{0, 0ull, t0, (uint32_t)per_probe, sc_, (uint32_t)s0, (uint32_t)rp->samples, PixelMap{0ull, 0u, 0u, 0u, 0ull, 0u}, 0u};
     if ((rc = run_wavefronts(ctx, env, rp->bounces, seed, pm, paths, q, ps, false))) return rc;
     LAUNCH_P(ctx, PROF_REDUCE, k_reduce_illum, div_up((size_t)nt * 32, 256), 256, 0, nt, sc_, ps, d_accum6 + 6 * (t0 - tri_begin));
     paths_total += paths;
@@ -967,15 +990,16 @@ int scan_samples_device(rtf_ctx* ctx, rtf_pc_sample* d_samples, size_t n, uint32
 // ============================ camera ================================================================
 // __raygen__CR path start, CameraRendering.cu:63-85.
 __global__ void __launch_bounds__(256)
-    k_gen_camera(rtf_camera_props cam, uint64_t pixel_begin, uint32_t n_pixels, uint32_t spp, Queues q, PathState ps) {
+    k_gen_camera(rtf_camera_props cam, PixelMap pxm, uint32_t n_pixels, uint32_t spp, Queues q, PathState ps) {
   const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t total = (uint64_t)n_pixels * spp;
   bool emit = false;
   float4 na = make_float4(0, 0, 0, 0), nb = make_float4(0, 0, 0, 0);
   if (p < total) {
-    const uint64_t pixel = pixel_begin + p / spp;
+    const uint32_t lk = p / spp;
+    const uint64_t pixel = pixel_of(pxm, lk);
     const uint32_t ix = (uint32_t)(pixel % (uint64_t)cam.width), iy = (uint32_t)(pixel / (uint64_t)cam.width);
-    const uint64_t unit = pixel_begin * spp + p;
+    const uint64_t unit = pixel * spp + (p - lk * spp);
     const float4 r = path_rng((uint32_t)cam.frame_id, STREAM_CAMERA, unit, 0u, 0u);
     const float halfX = cam.width / 2.0f, halfY = cam.height / 2.0f;
     const float sx = (((float)ix + r.x) - halfX) / halfX;
@@ -1014,11 +1038,11 @@ __global__ void __launch_bounds__(256)
 }
 // CameraRendering.cu:101-146: per-pixel sums in sample order, progressive accumulation in gamma space.
 __global__ void __launch_bounds__(256)
-    k_resolve_camera(rtf_camera_props cam, uint64_t pixel_begin, uint32_t n_pixels, uint32_t spp, PathState ps,
+    k_resolve_camera(rtf_camera_props cam, PixelMap pxm, uint32_t n_pixels, uint32_t spp, PathState ps,
                      float4* __restrict__ color, float4* __restrict__ normal, float4* __restrict__ albedo) {
   const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n_pixels) return;
-  const uint64_t pixel = pixel_begin + k;
+  const uint64_t pixel = pixel_of(pxm, k);
   const float nsf = (float)spp;
   float3 pc = f3(0, 0, 0), pn = f3(0, 0, 0), pa = f3(0, 0, 0), pp = f3(0, 0, 0);
   for (uint32_t s = 0; s < spp; s++) {
@@ -1051,14 +1075,12 @@ __global__ void __launch_bounds__(256)
   normal[pixel] = make_float4(pn.x, pn.y, pn.z, 1.0f);
 }
 
-int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, uint64_t px_begin,
-                         uint64_t px_end) {
+// One camera job over `n_local` pixels addressed through `pxm`, in batches of the wavefront capacity.
+static int render_camera_mapped(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, const PixelMap& job,
+                                uint64_t n_local) {
   const rtf_camera_props& cp = cam->props;
-  const uint64_t all_pixels = (uint64_t)cp.width * (uint64_t)cp.height;
-  if (px_end > all_pixels) px_end = all_pixels;
   ctx->last_paths = 0;
-  if (px_begin >= px_end || rp->samples <= 0) return RTF_OK;
-  const uint64_t n_pixels = px_end;  // the loop below runs over [px_begin, px_end)
+  if (n_local == 0 || rp->samples <= 0) return RTF_OK;
   if (env->environmental_map_id != 0 && env->lighting_type == RTF_ENV_SCENE && ctx->scene.env_faces == nullptr) {
     set_error("environmental_map_id != 0 but no cube map is registered (rtf_set_environment_map, then rtf_commit)");
     return RTF_ERR_INVALID;
@@ -1072,21 +1094,50 @@ int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, cons
   PathState ps;
   bind(ctx, q, ps, true);
   const uint64_t px_per_batch = cap / spp;
-  RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, ctx->stream));
+  if (!ctx->stats_hold) RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, ctx->stream));
   ctx->stats_cached = false;
-  for (uint64_t p0 = px_begin; p0 < n_pixels; p0 += px_per_batch) {
-    const uint32_t np = (uint32_t)((n_pixels - p0) < px_per_batch ? (n_pixels - p0) : px_per_batch);
+  for (uint64_t l0 = 0; l0 < n_local; l0 += px_per_batch) {
+    const uint32_t np = (uint32_t)((n_local - l0) < px_per_batch ? (n_local - l0) : px_per_batch);
     const size_t paths = (size_t)np * spp;
     RTF_CUDA(cudaMemsetAsync(ctx->ws.counters.p, 0, 4096, ctx->stream));
-    LAUNCH_P(ctx, PROF_GEN, k_gen_camera, div_up(paths, 256), 256, 0, cp, p0, np, spp, q, ps);
-    PathMap pm{1, p0 * spp, 0ull, 0u, 0u, 0u, 0u};
+    PixelMap pxm = job;  // the batch's view of the job
+    pxm.first = job.first + l0;
+    if (job.band_px) pxm.blk0 = l0 / job.band_px, pxm.off0 = (uint32_t)(l0 % job.band_px);
+    LAUNCH_P(ctx, PROF_GEN, k_gen_camera, div_up(paths, 256), 256, 0, cp, pxm, np, spp, q, ps);
+    PathMap pm{1, pxm.first * spp, 0ull, 0u, 0u, 0u, 0u, pxm, spp};
     if ((rc = run_wavefronts(ctx, env, rp->bounces, (uint32_t)cp.frame_id, pm, paths, q, ps, true))) return rc;
-    LAUNCH_P(ctx, PROF_REDUCE, k_resolve_camera, div_up(np, 256), 256, 0, cp, p0, np, spp, ps, cam->color.as<float4>(),
-           cam->normal.as<float4>(), cam->albedo.as<float4>());
+    LAUNCH_P(ctx, PROF_REDUCE, k_resolve_camera, div_up(np, 256), 256, 0, cp, pxm, np, spp, ps, cam->color.as<float4>(),
+             cam->normal.as<float4>(), cam->albedo.as<float4>());
   }
   RTF_CUDA(cudaGetLastError());
-  ctx->last_paths = (px_end - px_begin) * spp;
+  ctx->last_paths = n_local * spp;
   return RTF_OK;
+}
+int render_camera_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, uint64_t px_begin,
+                         uint64_t px_end) {
+  const uint64_t all_pixels = (uint64_t)cam->props.width * (uint64_t)cam->props.height;
+  if (px_end > all_pixels) px_end = all_pixels;
+  ctx->last_paths = 0;
+  if (px_begin >= px_end) return RTF_OK;
+  return render_camera_mapped(ctx, env, cam, rp, PixelMap{px_begin, 0u, 0u, 0u, 0ull, 0u}, px_end - px_begin);
+}
+// This rank's interleaved bands of `band_rows` rows (band k belongs to rank k mod nranks) as one job.
+int render_camera_interleaved_device(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, int band_rows,
+                                     int nranks, int rank) {
+  const int h = cam->props.height, w = cam->props.width;
+  ctx->last_paths = 0;
+  if (h <= 0 || w <= 0 || band_rows <= 0) return RTF_OK;
+  const int n_bands = (h + band_rows - 1) / band_rows;
+  uint64_t rows = 0;
+  for (int k = rank; k < n_bands; k += nranks) rows += (uint64_t)(((k + 1) * band_rows < h ? (k + 1) * band_rows : h) - k * band_rows);
+  if (nranks <= 1) return render_camera_mapped(ctx, env, cam, rp, PixelMap{0ull, 0u, 0u, 0u, 0ull, 0u}, (uint64_t)h * (uint64_t)w);
+  if ((uint64_t)band_rows * (uint64_t)w >= (1ull << 31) || batch_capacity(ctx) >= (1ull << 31)) {
+    set_error("interleaved camera bands: band or batch larger than 2^31 pixels");
+    return RTF_ERR_LIMIT;
+  }
+  return render_camera_mapped(ctx, env, cam, rp,
+                              PixelMap{0ull, (uint32_t)band_rows * (uint32_t)w, (uint32_t)nranks, (uint32_t)rank, 0ull, 0u},
+                              rows * (uint64_t)w);
 }
 
 // ---- test hook: the BSSRDF spatial probe on its own (rtf_sss.cuh) ----------------------------------------------------
