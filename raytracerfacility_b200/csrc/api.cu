@@ -448,6 +448,12 @@ int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value) {
     ctx->refit = value != 0;
   } else if (!strcmp(name, "sort_rays")) {
     ctx->sort_rays = value != 0;
+  } else if (!strcmp(name, "rng")) {
+    if (value != RTF_RNG_PHILOX && value != RTF_RNG_REFERENCE_LCG) {
+      set_error("rng must be RTF_RNG_PHILOX or RTF_RNG_REFERENCE_LCG");
+      return RTF_ERR_INVALID;
+    }
+    ctx->rng = (int)value;
   } else {
     set_error(std::string("unknown option ") + name);
     return RTF_ERR_INVALID;
@@ -500,6 +506,19 @@ int rtf_estimate_illumination(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_pr
   if (n == 0) return RTF_OK;            // reference: message + return (RayTracer.cu:612-615)
   int rc;
   cudaStream_t st = ctx->stream;
+  if (ctx->rng == RTF_RNG_REFERENCE_LCG) {  // verification mode: the reference's stream, samples in sequence (render.cu)
+    if ((rc = ctx->ws.io.reserve(n * (sizeof(rtf_illum_sampler) + 24)))) return rc;
+    if ((rc = ctx->d_stats.reserve(64))) return rc;
+    rtf_illum_sampler* d_probes = ctx->ws.io.as<rtf_illum_sampler>();
+    float* d_acc = (float*)(d_probes + n);
+    RTF_CUDA(cudaMemcpyAsync(d_probes, probes, n * sizeof(rtf_illum_sampler), cudaMemcpyHostToDevice, st));
+    RTF_CUDA(cudaMemsetAsync(d_acc, 0, n * 24, st));
+    if ((rc = illum_probes_lcg_device(ctx, env, rp, seed, push, d_probes, n, 0, d_acc))) return rc;
+    if ((rc = illum_finalize_device(ctx, d_acc, n, 2, rp->samples, d_probes))) return rc;
+    RTF_CUDA(cudaMemcpyAsync(probes, d_probes, n * sizeof(rtf_illum_sampler), cudaMemcpyDeviceToHost, st));
+    RTF_CUDA(cudaStreamSynchronize(st));
+    return fetch_stats(ctx);
+  }
   if ((rc = pipe_init(ctx))) return rc;
   HostPipe& p = ctx->pipe;
   const size_t chunk = ctx->pipe_chunk_probes ? ctx->pipe_chunk_probes : 1;

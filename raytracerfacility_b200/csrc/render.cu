@@ -214,6 +214,10 @@ struct SrcQueue {
   DevScene sc;              // alpha from an albedo texture needs the hit's texture coordinate (ALPHA variant only)
   PathMap pm;
   uint32_t seed, bounce;
+  uint32_t* lcg;  // option "rng" = reference: per-path LCG state, drawn from in traversal order (else nullptr)
+  // The reference's any-hit program draws at EVERY candidate of a default-material surface, also where alpha = 1 and the
+  // draw cannot reject (RF.cuh:19): a sequential stream sees those draws, so that mode visits every candidate.
+  RTF_D bool all_candidates() const { return ALPHA && lcg != nullptr; }
   RTF_D void issue(uint32_t base, uint32_t cnt, uint32_t raw_s, uint32_t mbar_s) const {
     mbar_expect_tx(mbar_s, cnt * 32u);
     tma_load_1d(raw_s, ra + base, cnt * 16u, mbar_s);
@@ -229,6 +233,18 @@ struct SrcQueue {
   // so it does not depend on traversal order.  Shadow rays and BTF bounce rays run with DISABLE_ANYHIT.
   RTF_D bool alpha_pass(uint32_t tag, uint32_t prim, uint32_t inst, float bu, float bv) const {
     if (inst_alpha == nullptr || (tag & (kShadowBit | kNoAnyHitBit))) return true;
+    if (lcg != nullptr) {  // reference stream: one draw per any-hit invocation (RF.cuh:5-23)
+      if (sc.mats[sc.insts[inst].mat].m.material_type != RTF_MAT_DEFAULT) return true;
+      float al = inst_alpha[inst];
+      if (al < 0.0f) {
+        const HitAttrs at = hit_attrs(sc, prim, bu, bv, inst);
+        al = tex2d(sc.mats[sc.insts[inst].mat].tex[MAT_TEX_ALBEDO], at.u, at.v).w;
+      }
+      uint32_t st = lcg[tag & kPathMask];
+      const float rnd = lcg_next(st);
+      lcg[tag & kPathMask] = st;
+      return !(al <= rnd);
+    }
     float alpha = inst_alpha[inst];
     if (alpha < 0.0f) {  // SurfaceMaterial::GetAlbedo(texCoord).w, RDD.hpp:248-254
       const HitAttrs at = hit_attrs(sc, prim, bu, bv, inst);
@@ -244,11 +260,13 @@ struct SrcQueue {
 // ALPHA = some material can ignore hits (transmission > 0): only then does the kernel carry the path map and RNG keys.
 template <bool ALPHA>
 __global__ void __launch_bounds__(kTraceBlock, ALPHA ? RTF_QUEUE_MIN_BLOCKS : RTF_QUEUE_MIN_BLOCKS + 1)
-    k_trace_queue(DevScene sc, Queues q, int qi, int wave, float tmin, PathMap pm, uint32_t seed, unsigned long long* stats) {
+    k_trace_queue(DevScene sc, Queues q, int qi, int wave, float tmin, PathMap pm, uint32_t seed, unsigned long long* stats,
+                  uint32_t* lcg) {
   __shared__ TraceSmem sm;
   const uint32_t n = q.count[wave];
   if (blockIdx.x == 0 && threadIdx.x == 0 && stats) atomicAdd(stats, (unsigned long long)n);
-  SrcQueue<ALPHA> src{q.ray_a[qi], q.ray_b[qi], q.hits, n, tmin, ALPHA ? sc.inst_alpha : nullptr, sc, pm, seed, (uint32_t)wave};
+  SrcQueue<ALPHA> src{q.ray_a[qi], q.ray_b[qi], q.hits, n, tmin, ALPHA ? sc.inst_alpha : nullptr, sc, pm, seed, (uint32_t)wave,
+                      ALPHA ? lcg : nullptr};
   trace_engine<false>(sc.nodes, sc.tris, src, q.work + wave, sm);
 }
 
@@ -258,7 +276,19 @@ struct ShadeParams {
   uint32_t seed;
   int camera;
   int brdf;  // RTF_BRDF_REFERENCE / RTF_BRDF_LAMBERT_GGX
+  uint32_t* lcg;  // option "rng" = reference: per-path LCG state (else nullptr: keyed Philox draws)
 };
+// The bounce draws of a shading event: keyed Philox numbers, or the next `n` numbers of the path's reference stream.
+__device__ __forceinline__ float4 shade_draws(const ShadeParams& sp, uint32_t p, uint64_t unit, uint32_t hit_count, int n) {
+  if (sp.lcg == nullptr) return path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
+  uint32_t st = sp.lcg[p];
+  float4 r = make_float4(0, 0, 0, 0);
+  r.x = lcg_next(st);
+  if (n > 1) r.y = lcg_next(st);
+  if (n > 2) r.z = lcg_next(st);
+  sp.lcg[p] = st;
+  return r;
+}
 // SSS = some material has subsurfaceFactor > 0: the kernel carries the BSSRDF spatial probe (rtf_sss.cuh) and the
 // pending-bounce state.
 #ifndef RTF_SHADE_MIN_BLOCKS
@@ -326,7 +356,7 @@ __global__ void __launch_bounds__(256, SSS ? RTF_SHADE_SSS_MIN_BLOCKS : (BTF ? R
         const DevBTF& btf = sc.btfs[dm.btf];
         float3 btf_color = f3(0, 0, 0);  // the reference leaves it uninitialised past the bounce limit: 0 here
         if ((int)hit_count <= sp.bounces) {
-          const float4 r = path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
+          const float4 r = shade_draws(sp, p, unit, hit_count, 2);
           if (env.lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE) {  // :180-218
             const float3 sun = f3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
             const float3 nd = sample_lobe(r.x, r.y, sun, 1.0f - env.light_size);
@@ -387,7 +417,7 @@ __global__ void __launch_bounds__(256, SSS ? RTF_SHADE_SSS_MIN_BLOCKS : (BTF ? R
         if (metallic >= 0.0f) f = (metallic + 2) / (metallic + 1);
         const float3 emis = m.emission * albedo;
         if (env.lighting_type == RTF_ENV_SINGLE_LIGHT_SOURCE) {  // RayFunctions.cuh:61-92
-          const float4 r = path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
+          const float4 r = shade_draws(sp, p, unit, hit_count, 2);
           const float3 sun = f3(env.sun_direction[0], env.sun_direction[1], env.sun_direction[2]);
           const float3 nd = sample_lobe(r.x, r.y, sun, 1.0f - env.light_size);
           const float3 col = f3(env.color[0], env.color[1], env.color[2]);
@@ -449,7 +479,7 @@ __global__ void __launch_bounds__(256, SSS ? RTF_SHADE_SSS_MIN_BLOCKS : (BTF ? R
               }
             }
           }
-          const float4 r = path_rng(sp.seed, STREAM_PATH, unit, hit_count, 0u);
+          const float4 r = shade_draws(sp, p, unit, hit_count, sp.brdf == RTF_BRDF_LAMBERT_GGX ? 3 : 2);
           float3 nd, wgt;
           if (sp.brdf == RTF_BRDF_LAMBERT_GGX) {
             wgt = sample_lambert_ggx(albedo, metallic, roughness, normal, neg3(d), r.x, r.y, r.z, nd);
@@ -724,7 +754,7 @@ static void bind(rtf_ctx* ctx, Queues& q, PathState& ps, bool camera) {
 
 // Runs the trace/shade loop for the wavefronts of one batch (no host synchronisation inside).
 static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_t seed, const PathMap& pm, size_t paths,
-                          Queues& q, PathState& ps, bool camera) {
+                          Queues& q, PathState& ps, bool camera, uint32_t* lcg = nullptr) {
   // BSSRDF: the subsurface path and the waiting bounce path share one hit counter, so together they add at most one ray
   // to the longest chain (primary + `bounces` hits + the resumed ray).
   const bool sss = ctx->scene.has_sss && env->lighting_type != RTF_ENV_SINGLE_LIGHT_SOURCE;
@@ -734,10 +764,11 @@ static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_
     set_error("too many bounces");
     return RTF_ERR_INVALID;
   }
-  ShadeParams sp{bounces, seed, camera ? 1 : 0, ctx->brdf};
+  ShadeParams sp{bounces, seed, camera ? 1 : 0, ctx->brdf, lcg};
   unsigned long long* stats = ctx->d_stats.as<unsigned long long>();
-  const unsigned tgrid = ctx->scene.has_alpha ? trace_grid(ctx, TK_QUEUE_ALPHA, k_trace_queue<true>, paths)
-                                              : trace_grid(ctx, TK_QUEUE, k_trace_queue<false>, paths);
+  const bool alpha_kernel = ctx->scene.has_alpha || lcg != nullptr;  // the reference stream draws at every any-hit candidate
+  const unsigned tgrid = alpha_kernel ? trace_grid(ctx, TK_QUEUE_ALPHA, k_trace_queue<true>, paths)
+                                      : trace_grid(ctx, TK_QUEUE, k_trace_queue<false>, paths);
   int qi = 0;
   for (int w = 0; w < waves; w++) {
     const float tmin = (camera && w == 0) ? 0.0f : 1e-3f;
@@ -749,10 +780,10 @@ static int run_wavefronts(rtf_ctx* ctx, const rtf_env* env, int bounces, uint32_
       if (rc) return rc;
       qi ^= 1;
     }
-    if (ctx->scene.has_alpha)
-      LAUNCH_P(ctx, PROF_TRACE, k_trace_queue<true>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
+    if (alpha_kernel)
+      LAUNCH_P(ctx, PROF_TRACE, k_trace_queue<true>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats, lcg);
     else
-      LAUNCH_P(ctx, PROF_TRACE, k_trace_queue<false>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats);
+      LAUNCH_P(ctx, PROF_TRACE, k_trace_queue<false>, tgrid, kTraceBlock, 0, ctx->scene, q, qi, w, tmin, pm, seed, stats, lcg);
     if (sss && ctx->scene.has_btf)
       LAUNCH_P(ctx, PROF_SHADE, (k_shade<true, true>), div_up(paths, 256), 256, 0, ctx->scene, *env, sp, pm, q, qi, w, ps);
     else if (sss)
@@ -801,6 +832,113 @@ int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp,
     if ((rc = run_wavefronts(ctx, env, rp->bounces, seed, pm, paths, q, ps, false))) return rc;
     LAUNCH_P(ctx, PROF_REDUCE, k_reduce_illum, div_up((size_t)nt * 32, 256), 256, 0, nt, sc_, ps, d_accum6 + 6 * (t0 - tri_begin));
     paths_total += paths;
+  }
+  RTF_CUDA(cudaGetLastError());
+  ctx->last_paths = paths_total;
+  return RTF_OK;
+}
+
+// ---- option "rng" = RTF_RNG_REFERENCE_LCG: __raygen__IE with the reference's own random stream ---------------------
+// One LCG per probe, seeded (probe index, seed) (IE.cu:47), consumed in the reference's order: front-face samples one
+// after the other, then the back face; per sample the two barycentric draws, the two of RandomSampleHemisphere, and
+// whatever the path draws on its way (one per any-hit candidate, two per bounce).  The length of a path decides where the
+// next sample's draws start, so the samples of a probe run in sequence: one single-path wavefront set per (face, sample)
+// over all probes of the batch.  pointEnergy / pointDirection accumulate in sample order as IE.cu:81-84 does.
+__global__ void k_lcg_init(uint32_t n, uint64_t first_probe, uint32_t seed, uint32_t* __restrict__ lcg) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) lcg[i] = lcg_seed((uint32_t)(first_probe + i), seed);
+}
+__global__ void __launch_bounds__(256) k_gen_illum_lcg(const rtf_illum_sampler* __restrict__ probes, uint32_t n, int face, float push,
+                                                       uint32_t* __restrict__ lcg, Queues q, PathState ps) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  bool emit = false;
+  float4 na = make_float4(0, 0, 0, 0), nb = make_float4(0, 0, 0, 0);
+  if (p < n) {
+    const rtf_illum_sampler& pr = probes[p];
+    float4 d0w = make_float4(0, 0, 0, 0);
+    if (face == 0 ? pr.front_face != 0 : pr.back_face != 0) {
+      const float3 P0 = f3(pr.a.position[0], pr.a.position[1], pr.a.position[2]);
+      const float3 P1 = f3(pr.b.position[0], pr.b.position[1], pr.b.position[2]);
+      const float3 P2 = f3(pr.c.position[0], pr.c.position[1], pr.c.position[2]);
+      const float3 N0 = f3(pr.a.normal[0], pr.a.normal[1], pr.a.normal[2]);
+      const float3 N1 = f3(pr.b.normal[0], pr.b.normal[1], pr.b.normal[2]);
+      const float3 N2 = f3(pr.c.normal[0], pr.c.normal[1], pr.c.normal[2]);
+      uint32_t st = lcg[p];
+      const float a = lcg_next(st), b = lcg_next(st), u0 = lcg_next(st), u1 = lcg_next(st);
+      lcg[p] = st;
+      const float w = (1.0f - a) - b;
+      const float3 position = (w * P0 + a * P1) + b * P2;
+      float3 normal = (w * N0 + a * N1) + b * N2;
+      if (face == 1) normal = neg3(normal);
+      const float3 dir = sample_hemisphere(u0, u1, normal);
+      const float3 origin = position + normal * push;
+      emit = true;
+      na = make_float4(origin.x, origin.y, origin.z, __uint_as_float(p));
+      nb = make_float4(dir.x, dir.y, dir.z, 1e20f);
+      d0w = make_float4(dir.x, dir.y, dir.z, fabsf(dot3(normal, dir)));
+    }
+    ps.thr[p] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(0u));
+    ps.acc[p] = make_float4(0, 0, 0, 0);
+    ps.dir0w[p] = d0w;
+  }
+  const uint32_t slot = warp_append(emit, q.count + 0);
+  if (emit) {
+    q.ray_a[0][slot] = na;
+    q.ray_b[0][slot] = nb;
+  }
+}
+__global__ void k_accum_illum_lcg(const rtf_illum_sampler* __restrict__ probes, uint32_t n, int face, PathState ps,
+                                  float* __restrict__ accum6) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n) return;
+  if (!(face == 0 ? probes[p].front_face != 0 : probes[p].back_face != 0)) return;
+  const float4 a = ps.acc[p], dw = ps.dir0w[p];
+  const float3 e = f3(a.x, a.y, a.z) * dw.w;
+  const float le = length3(e);
+  float* o = accum6 + 6 * (size_t)p;
+  o[0] = o[0] + e.x, o[1] = o[1] + e.y, o[2] = o[2] + e.z;
+  o[3] = o[3] + dw.x * le, o[4] = o[4] + dw.y * le, o[5] = o[5] + dw.z * le;
+}
+// d_probes: the n probes of this call on the device (index 0 = probe `first_probe` of the caller's array); d_accum6: n x 6
+// zeroed floats.  Subsurface materials are refused: their probe collects records in an order of its own.
+int illum_probes_lcg_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push,
+                            const rtf_illum_sampler* d_probes, uint64_t n, uint64_t first_probe, float* d_accum6) {
+  if (!ctx->ready) {
+    set_error("no acceleration structure (call rtf_commit)");
+    return RTF_ERR_NOT_READY;
+  }
+  if (ctx->scene.has_sss) {
+    set_error("option rng = reference: scenes with a subsurface material are not supported (order-dependent probe)");
+    return RTF_ERR_INVALID;
+  }
+  if (env->environmental_map_id != 0 && env->lighting_type == RTF_ENV_SCENE && ctx->scene.env_faces == nullptr) {
+    set_error("environmental_map_id != 0 but no cube map is registered (rtf_set_environment_map, then rtf_commit)");
+    return RTF_ERR_INVALID;
+  }
+  if (n == 0 || rp->samples <= 0) return RTF_OK;
+  const size_t cap = batch_capacity(ctx);
+  int rc;
+  if ((rc = ensure_workspace(ctx, cap, false))) return rc;
+  if ((rc = ctx->ws.lcg.reserve(4 * cap))) return rc;
+  uint32_t* lcg = ctx->ws.lcg.as<uint32_t>();
+  Queues q;
+  PathState ps;
+  bind(ctx, q, ps, false);
+  if (!ctx->stats_hold) RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, ctx->stream));
+  ctx->stats_cached = false;
+  uint64_t paths_total = ctx->stats_hold ? ctx->last_paths : 0;
+  const PathMap pm{0, 0ull, 0ull, 1u, 1u, 0u, 1u, PixelMap{0ull, 0u, 0u, 0u, 0ull, 0u}, 0u};  // unused by the LCG draws
+  for (uint64_t b0 = 0; b0 < n; b0 += cap) {
+    const uint32_t nb = (uint32_t)((n - b0) < cap ? (n - b0) : cap);
+    LAUNCH(ctx, k_lcg_init, div_up(nb, 256), 256, 0, nb, first_probe + b0, seed, lcg);
+    for (int face = 0; face < 2; face++)
+      for (int s = 0; s < rp->samples; s++) {
+        RTF_CUDA(cudaMemsetAsync(ctx->ws.counters.p, 0, 4096, ctx->stream));
+        LAUNCH_P(ctx, PROF_GEN, k_gen_illum_lcg, div_up(nb, 256), 256, 0, d_probes + b0, nb, face, push, lcg, q, ps);
+        if ((rc = run_wavefronts(ctx, env, rp->bounces, seed, pm, nb, q, ps, false, lcg))) return rc;
+        LAUNCH_P(ctx, PROF_REDUCE, k_accum_illum_lcg, div_up(nb, 256), 256, 0, d_probes + b0, nb, face, ps, d_accum6 + 6 * b0);
+      }
+    paths_total += 2ull * (uint64_t)rp->samples * nb;
   }
   RTF_CUDA(cudaGetLastError());
   ctx->last_paths = paths_total;

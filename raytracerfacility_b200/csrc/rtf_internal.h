@@ -169,6 +169,7 @@ struct Workspace {  // wavefront queues + path state, sized for `capacity` paths
   DevBuf pend_o, pend_d, pend_t;                      // BSSRDF: bounce ray waiting for the subsurface path
   DevBuf sort_keys, sort_keys_alt, sort_vals, sort_vals_alt, sort_tmp, sort_kin;
   DevBuf io;  // staging for AoS entry points
+  DevBuf lcg;  // option "rng" = reference: one LCG state per path of a batch
 };
 
 // Double-buffered host<->device pipeline of the host-buffer entry points (upload chunk i+1 and download chunk i-1
@@ -242,6 +243,7 @@ struct rtf_ctx {
   size_t batch_paths = (size_t)1 << 24;  // 2^24 paths: ~3 GB of queues + path state; +12..20 % over 2^22 (fewer, fuller waves)
   int sort_rays = 0;  // option "sort_rays": sort bounce rays by (octant, origin cell) before tracing (measured: DESIGN.md)
   int brdf = RTF_BRDF_REFERENCE;  // option "brdf"
+  int rng = RTF_RNG_PHILOX;       // option "rng" (rtf_estimate_illumination only)
   // RenderToCamera's change detection (m_cameraRenderingLaunchParams.m_rayTracerProperties, RayTracer.cu:253-269): the
   // environment / ray properties and scene epoch the last frame was rendered with
   rtf_env cam_last_env;
@@ -294,6 +296,8 @@ int illum_mesh_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp,
                       int back, uint64_t tri_begin, uint64_t tri_end, int s0, int s1, float* d_accum6,
                       const rtf_illum_sampler* d_probes, uint64_t probe_base);
 int illum_finalize_device(rtf_ctx* ctx, float* d_accum6, uint64_t n, int faces, int samples, rtf_illum_sampler* d_probes);
+int illum_probes_lcg_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push,
+                            const rtf_illum_sampler* d_probes, uint64_t n, uint64_t first_probe, float* d_accum6);
 int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin, uint64_t ray_end, float* d_t,
                      uint32_t* d_prim, uint32_t* d_inst);
 void scan_interleave_layout(uint64_t total, int nranks, int rank, uint32_t* shift, uint64_t* n_blocks, uint64_t* n_local);

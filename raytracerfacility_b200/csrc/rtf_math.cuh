@@ -111,6 +111,23 @@ RTF_HD float4 path_rng(uint32_t seed, uint32_t stream, uint64_t unit, uint32_t b
   return make_float4(u01(o.x), u01(o.y), u01(o.z), u01(o.w));
 }
 
+// ---- the reference's per-thread generator (LinearCongruenceGenerator.hpp:6-35: 16 TEA rounds seed an LCG; 24 bits per
+//      draw).  Used only by the option "rng" = RTF_RNG_REFERENCE_LCG of the AoS illumination entry point, which serves the
+//      reference's own stream in the reference's own order so that the GPU can be compared with its programs directly.
+RTF_HD uint32_t lcg_seed(uint32_t val0, uint32_t val1) {
+  uint32_t v0 = val0, v1 = val1, s0 = 0u;
+  for (int n = 0; n < 16; n++) {
+    s0 += 0x9e3779b9u;
+    v0 += ((v1 << 4) + 0xa341316cu) ^ (v1 + s0) ^ ((v1 >> 5) + 0xc8013ea4u);
+    v1 += ((v0 << 4) + 0xad90777du) ^ (v0 + s0) ^ ((v0 >> 5) + 0x7e95761eu);
+  }
+  return v0;
+}
+RTF_HD float lcg_next(uint32_t& state) {
+  state = 1664525u * state + 1013904223u;
+  return (float)(state & 0x00FFFFFFu) / 16777216.0f;
+}
+
 // ---- portable sin/cos(2*pi*u): only + * fma, so host and device agree bit for bit.
 //      Stands in for glm::sin/cos(2*pi*rnd) at RayTracerUtilities.cuh:127-131,139-143, CameraRendering.cu:75-79.
 RTF_HD void sincos2pi(float u, float& s, float& c) {

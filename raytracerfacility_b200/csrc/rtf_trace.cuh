@@ -108,7 +108,8 @@ struct __align__(128) TraceSmem {
 // A ray source/sink ("Src") provides:
 //   static constexpr bool kTma     — tiles arrive by TMA bulk copy (issue()) or are read/generated in fetch()
 //   static constexpr bool kAnyHit  — rays may be first-hit rays (any_hit(tag))
-//   static constexpr bool kAlpha   — stochastic alpha test may reject candidates (alpha_pass(tag, prim, inst, u, v))
+//   static constexpr bool kAlpha   — stochastic alpha test may reject candidates (alpha_pass(tag, prim, inst, u, v));
+//                                    all_candidates(): call it for every candidate, not only flagged triangles
 //   uint32_t n                     — rays in this launch
 //   void issue(base, cnt, raw_smem_u32, mbar_u32)            (lane 0; kTma only)
 //   void fetch(raw, base, slot, a, b, tmin, tag)              a = {o.xyz, *}, b = {d.xyz, tmax}
@@ -387,7 +388,7 @@ RTF_D void trace_engine(const uint4* __restrict__ nodes, const float4* __restric
         if (t == best.t && prim >= best.prim) break;
         const float bu = V * rcp, bv = W * rcp;
         if constexpr (Src::kAlpha) {
-          if (__float_as_uint(t2.w) & TRI_FLAG_ALPHA)
+          if ((__float_as_uint(t2.w) & TRI_FLAG_ALPHA) || src.all_candidates())
             if (!src.alpha_pass(tag, prim, __float_as_uint(t1.w), bu, bv)) break;
         }
         best.t = t, best.u = bu, best.v = bv, best.prim = prim;

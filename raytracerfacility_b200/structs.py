@@ -43,6 +43,7 @@ ENV_SCENE, ENV_SKYDOME, ENV_SINGLE_LIGHT_SOURCE = 0, 1, 2
 MAT_DEFAULT, MAT_VERTEX_COLOR, MAT_COMPRESSED_BTF = 0, 1, 2
 OUT_COLOR, OUT_NORMAL, OUT_ALBEDO, OUT_DEPTH = 0, 1, 2, 3
 BRDF_REFERENCE, BRDF_LAMBERT_GGX = 0, 1
+RNG_PHILOX, RNG_REFERENCE_LCG = 0, 1  # rtf_set_option(ctx, "rng", ...): rtf.h
 
 
 class EnvironmentProperties(C.Structure):

@@ -1,0 +1,83 @@
+"""The GPU against the REFERENCE's own device programs, directly.
+
+Option "rng" = RTF_RNG_REFERENCE_LCG makes rtf_estimate_illumination serve the reference's generator
+(LinearCongruenceGenerator.hpp:6-35), one stream per probe seeded as __raygen__IE seeds it (IlluminationEstimation.cu:47),
+in the reference's draw order: barycentric pair, hemisphere pair, one draw per any-hit candidate of a default-material
+surface in traversal order (RayFunctions.cuh:19), two per bounce; samples of a probe one after the other, front face
+first; pointEnergy / pointDirection summed in that order (IlluminationEstimation.cu:81-84).  The result is compared with
+tests/golden/programs_ref.npz — what the reference's unmodified programs produce on the host over the same scenes, probes
+and seed (tests/test_ref_programs.py describes the fixture).
+
+What can differ: the GPU takes sin / cos(2 pi u) from the repository's portable polynomial (1.2e-7 from libm, which the
+reference calls) and exp / pow from CUDA's libm, and it carries the path throughput forward instead of recursing — a few
+ulp per value.  A direction that moves by an ulp can in principle flip a hit into a miss; on these cases it does not:
+the ray counts are equal.  Bars: ray count equal; energy error of 99 % of the probes within 1e-5 of the probe's largest
+channel, of every probe within 1e-3 of it and within 1e-5 of the case's brightest probe (a probe lit at grazing incidence
+has a small |N.dir| that a 1e-7 change of the direction moves by 1e-5 of itself); direction (a normalised sum) within 1e-5
+for 90 % of the probes and 2e-3 for all.  Scenes with a subsurface material are refused by the mode (order-dependent
+probe).  The BTF scene has looser bars at 4 bounces (the evaluator's angle arithmetic is portable here and libm's there;
+that part is pinned bit for bit by the oracle's libm mode instead, tests/test_golden.py)."""
+import os
+
+import numpy as np
+import pytest
+
+from tests.golden import make_golden as G
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module")
+def ref():
+    return np.load(os.path.join(GOLDEN, "programs_ref.npz"))
+
+
+@pytest.mark.parametrize("scene", ["plants", "mixed", "btf"])
+def test_illumination_with_the_reference_stream(rt, orc, S, ref, scene):
+    sd = G.programs_ref_scenes()[scene]
+    rt.load_scene(sd, 63)
+    osc = orc.OracleScene(sd)
+    rt.set_option("rng", S.RNG_REFERENCE_LCG)
+    try:
+        cases = [(sc, e, b, n) for sc, e, b, n in G.PROGRAMS_IE if sc == scene]
+        assert cases
+        stats = []
+        for sc, e, b, n in cases:
+            key = f"ie_{sc}_{e}_{b}_{n}"
+            want = ref[key].view(np.float32)
+            pr = osc.make_probes(0, min(400, osc.n_tris))
+            env, rp = S.EnvironmentProperties(**G.PROGRAMS_ENVS[e]), S.RayProperties(b, n)
+            rt.estimate_illumination(env, rp, pr, seed=7, push_normal_distance=1e-3)
+            rays = rt.last_job_stats()[0]
+            assert rays == int(ref[key + "_rays"][0]), (key, rays, int(ref[key + "_rays"][0]))
+            got = np.concatenate([pr["energy"], pr["direction"]], 1)
+            assert np.array_equal(np.isnan(got), np.isnan(want)), key
+            aerr = np.abs(got[:, :3] - want[:, :3])
+            rel = aerr.max(1) / np.maximum(np.abs(want[:, :3]).max(1), 1e-6)  # per probe, against its largest channel
+            glob = aerr.max() / np.abs(want[:, :3]).max()                     # against the brightest probe of the case
+            ok = ~np.isnan(want[:, 3:]).any(1)
+            derr = np.abs(got[ok, 3:] - want[ok, 3:]).max(1)
+            stats.append((key, float(np.percentile(rel, 99)), float(rel.max()), float(glob), float(np.percentile(derr, 90)),
+                          float(derr.max())))
+        # multi-bounce BTF paths amplify the 2e-4 the evaluator's portable trigonometry is off libm's (tests/test_golden.py):
+        # observed 3e-3 (99 %) / 1.3e-2 (worst probe) / 2.4e-4 (of the brightest probe) at 4 bounces x 8 samples
+        bars = (1e-2, 5e-2, 1e-3, 1e-5, 2e-2) if scene == "btf" else (1e-5, 1e-3, 1e-5, 1e-5, 2e-3)
+        bad = [s_ for s_ in stats if not all(v <= b for v, b in zip(s_[1:], bars))]
+        assert not bad, (bad, stats)
+    finally:
+        rt.set_option("rng", S.RNG_PHILOX)
+
+
+def test_the_mode_refuses_subsurface_scenes(rt, mod, S, orc):
+    sd = G.programs_ref_scenes()["sss"]
+    rt.load_scene(sd, 63)
+    pr = orc.OracleScene(sd).make_probes(0, 8)
+    rt.set_option("rng", S.RNG_REFERENCE_LCG)
+    try:
+        with pytest.raises(mod.RtfError):
+            rt.estimate_illumination(S.EnvironmentProperties(), S.RayProperties(1, 1), pr, seed=7)
+    finally:
+        rt.set_option("rng", S.RNG_PHILOX)
+    with pytest.raises(mod.RtfError):
+        rt.set_option("rng", 7)
