@@ -482,6 +482,9 @@ RTF_API int rtf_estimate_illumination_mesh_sharded(rtf_ctx* ctx, const rtf_env* 
 RTF_API int rtf_scan_grid_trace_sharded_device(rtf_ctx* ctx, const rtf_scan_grid* grid, int gather, float* dev_t,
                                                uint32_t* dev_prim, uint32_t* dev_inst, uint64_t* block_rays,
                                                uint64_t* n_blocks);
+/* The layout above for any (nranks, rank), without a device: block size, number of blocks of the grid, rays of `rank`. */
+RTF_API int rtf_scan_grid_shard_layout(const rtf_scan_grid* grid, int nranks, int rank, uint64_t* block_rays,
+                                       uint64_t* n_blocks, uint64_t* n_local);
 /* RenderToCamera over interleaved row bands; outputs_mask: bit RTF_OUT_COLOR / NORMAL / ALBEDO = complete that buffer on
  * every rank (one group of broadcasts each).  Pixels keep their global RNG streams: bit-identical to the 1-GPU frame. */
 RTF_API int rtf_render_camera_sharded(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* ray_props,

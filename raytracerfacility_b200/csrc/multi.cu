@@ -286,6 +286,20 @@ int rtf_scan_grid_trace_sharded_device(rtf_ctx* ctx, const rtf_scan_grid* grid, 
   if (!grid || (!dev_t && !dev_prim && !dev_inst)) return RTF_ERR_INVALID;
   return scan_grid_sharded_device(ctx, grid, gather, dev_t, dev_prim, dev_inst, block_rays, n_blocks);
 }
+// Pure host arithmetic (no device): the block layout the sharded LiDAR entry points use for `nranks` ranks.
+int rtf_scan_grid_shard_layout(const rtf_scan_grid* grid, int nranks, int rank, uint64_t* block_rays, uint64_t* n_blocks,
+                               uint64_t* n_local) {
+  if (!grid || nranks < 1 || rank < 0 || rank >= nranks) return RTF_ERR_INVALID;
+  uint32_t column = 0, row = 0, shift = 0;
+  int rc = rtf_scan_grid_dims(grid, &column, &row);
+  if (rc) return rc;
+  uint64_t nb = 0, nl = 0;
+  scan_interleave_layout((uint64_t)column * row, nranks, rank, &shift, &nb, &nl);
+  if (block_rays) *block_rays = 1ull << shift;
+  if (n_blocks) *n_blocks = nb;
+  if (n_local) *n_local = nl;
+  return RTF_OK;
+}
 int rtf_render_camera_sharded(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, int outputs_mask) {
   CHECK_CTX(ctx);
   return render_camera_sharded(ctx, env, cam, rp, outputs_mask);

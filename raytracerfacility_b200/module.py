@@ -42,7 +42,8 @@ EXPORTS = [
     # multi-GPU (csrc/multi.cu)
     "rtf_comm_unique_id", "rtf_comm_init_rank", "rtf_comm_destroy", "rtf_comm_rank", "rtf_comm_barrier",
     "rtf_comm_reduce_f64", "rtf_shard_range", "rtf_estimate_illumination_mesh_sharded_device",
-    "rtf_estimate_illumination_mesh_sharded", "rtf_scan_grid_trace_sharded_device", "rtf_render_camera_sharded",
+    "rtf_estimate_illumination_mesh_sharded", "rtf_scan_grid_trace_sharded_device", "rtf_scan_grid_shard_layout",
+    "rtf_render_camera_sharded",
     "rtf_phase_timings", "rtf_profile_read", "rtf_create_multi", "rtf_multi_destroy", "rtf_multi_size", "rtf_multi_ctx",
     "rtf_multi_set_geometry", "rtf_multi_set_material", "rtf_multi_set_instance", "rtf_multi_set_option",
     "rtf_multi_commit", "rtf_multi_estimate_illumination_mesh", "rtf_multi_scan_grid_trace", "rtf_multi_trace_closest",
@@ -58,6 +59,13 @@ class RtfError(RuntimeError):
 
 
 _lib = None
+
+
+def scan_grid_shard_layout(grid, nranks, rank):
+    """(block_rays, n_blocks, n_local) of the interleaved LiDAR shards (host arithmetic of the library, no device)."""
+    blk, nb, nl = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    _check(lib().rtf_scan_grid_shard_layout(C.byref(grid), int(nranks), int(rank), C.byref(blk), C.byref(nb), C.byref(nl)))
+    return blk.value, nb.value, nl.value
 
 
 def lib():

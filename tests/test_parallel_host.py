@@ -24,6 +24,44 @@ def test_split_range_partitions():
             assert max(sizes) - min(sizes) <= 1
 
 
+def test_interleaved_lidar_shard_layout():
+    """rtf_scan_grid_shard_layout (host arithmetic of the library, what the sharded LiDAR entry points use): the blocks
+    of all ranks cover every ray of the grid exactly once, block k belongs to rank k mod world, only the grid's last block
+    is partial, about 16 blocks per rank, and a rank's blocks are what DistributedRayTracer.local_rays cuts out."""
+    from raytracerfacility_b200 import module, scenes
+    from raytracerfacility_b200.parallel import DistributedRayTracer
+    for side_x, side_y in ((400, 200), (130, 140), (10000, 10000), (1, 1), (4097, 3)):
+        grid = scenes.lidar_grid(center=(0.0, 5.0, 0.0), size=(float(side_x), float(side_y)), distance=(1.0, 1.0))
+        total = side_x * side_y
+        for world in (1, 2, 3, 8):
+            lay = [module.scan_grid_shard_layout(grid, world, r) for r in range(world)]
+            block, n_blocks = lay[0][0], lay[0][1]
+            assert all(l[0] == block and l[1] == n_blocks for l in lay)
+            assert block & (block - 1) == 0 and 1 << 12 <= block <= 1 << 24
+            assert n_blocks == (total + block - 1) // block
+            assert n_blocks <= 16 * world or block == 1 << 24
+            assert sum(l[2] for l in lay) == total
+            seen = np.zeros(n_blocks, dtype=np.int32)
+            for r in range(world):
+                mine = list(range(r, n_blocks, world))
+                seen[mine] += 1
+                rays = sum(min(block, total - k * block) for k in mine)
+                assert rays == lay[r][2], (side_x, side_y, world, r)
+                if total > 1 << 20:
+                    continue
+                # the mirror's view of the same layout (no device needed for the index arithmetic)
+                drt = DistributedRayTracer.__new__(DistributedRayTracer)
+                drt.rank, drt.world = r, world
+                arr = torch.arange(n_blocks * block, dtype=torch.int64).view(n_blocks, block)
+                flat, starts = drt.local_rays(total, arr)
+                assert starts == [k * block for k in mine] and flat.numel() == lay[r][2]
+                if flat.numel():
+                    assert int(flat.max()) < total and int(flat[0]) == (starts[0] if starts else 0)
+            assert (seen == 1).all()
+    with pytest.raises(module.RtfError):
+        module.scan_grid_shard_layout(grid, 2, 2)
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
