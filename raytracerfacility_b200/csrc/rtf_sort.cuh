@@ -1,7 +1,7 @@
 // rtf_sort.cuh — stable LSD radix sort of (key, u32 value) pairs, hand-written for sm_100a.
 //
 // "Onesweep" organisation (Adinets & Merrill 2022): ONE histogram kernel reads the keys once and counts the digits
-// of every pass; each pass is then ONE kernel that ranks a tile of 4096 keys, obtains the tile's global offset per
+// of every pass; each pass is then ONE kernel that ranks a tile of 3072 keys, obtains the tile's global offset per
 // digit by decoupled look-back over the preceding tiles' digit counts, reorders the tile in shared memory and writes
 // out digit runs (coalesced).  A pass moves 12 B in + 12 B out per 63-bit pair: the sort is an HBM-bound streaming
 // kernel; 8-bit digits -> 8 passes for 63-bit Morton codes, 4 for 30-bit codes.
@@ -18,7 +18,13 @@ namespace rtf {
 #endif
 constexpr int kSortBlock = 256;
 constexpr int kSortWarps = kSortBlock / 32;
-constexpr int kSortItems = 16;
+#ifndef RTF_SORT_ITEMS
+#define RTF_SORT_ITEMS 12  // keys per thread: 3072-key tiles (46 KB of shared memory) -> 4 blocks per SM; 16 / 3 blocks: 0.60 ms, 12 / 4: 0.51, 8 / 5: 0.53 (C2 scene, 8 passes)
+#endif
+constexpr int kSortItems = RTF_SORT_ITEMS;
+#ifndef RTF_SORT_MIN_BLOCKS
+#define RTF_SORT_MIN_BLOCKS 4
+#endif
 constexpr int kSortTile = kSortBlock * kSortItems;  // 4096 keys per tile
 constexpr int kSortMaxPasses = 8;
 constexpr uint32_t kSortFlagAgg = 1u << 30, kSortFlagPrefix = 2u << 30, kSortValueMask = (1u << 30) - 1u;
@@ -79,7 +85,7 @@ struct SortSmem {
 };
 
 template <class K>
-__global__ void __launch_bounds__(kSortBlock, 3) k_sort_pass(const K* __restrict__ kin, K* __restrict__ kout,
+__global__ void __launch_bounds__(kSortBlock, RTF_SORT_MIN_BLOCKS) k_sort_pass(const K* __restrict__ kin, K* __restrict__ kout,
                                                           const uint32_t* __restrict__ vin, uint32_t* __restrict__ vout,
                                                           uint32_t n, int shift, const uint32_t* __restrict__ hist_scan,
                                                           uint32_t* status /* [0] ticket, [256 + tile*256 + d] */) {
