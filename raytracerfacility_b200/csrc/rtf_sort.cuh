@@ -25,7 +25,7 @@ constexpr int kSortItems = RTF_SORT_ITEMS;
 #ifndef RTF_SORT_MIN_BLOCKS
 #define RTF_SORT_MIN_BLOCKS 4
 #endif
-constexpr int kSortTile = kSortBlock * kSortItems;  // 4096 keys per tile
+constexpr int kSortTile = kSortBlock * kSortItems;  // 3072 keys per tile
 constexpr int kSortMaxPasses = 8;
 constexpr uint32_t kSortFlagAgg = 1u << 30, kSortFlagPrefix = 2u << 30, kSortValueMask = (1u << 30) - 1u;
 
