@@ -475,7 +475,7 @@ RTF_API int rtf_estimate_illumination_mesh_sharded_device(rtf_ctx* ctx, const rt
 RTF_API int rtf_estimate_illumination_mesh_sharded(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* ray_props,
                                                    uint32_t seed, float push_normal_distance, int front_face, int back_face,
                                                    int mode, float* out6 /* host */);
-/* LiDAR shards are interleaved blocks of *block_rays consecutive rays (a power of two, about 16 blocks per rank): block k
+/* LiDAR shards are interleaved blocks of *block_rays consecutive rays (a power of two, about 64 blocks per rank): block k
  * of the *n_blocks blocks of the grid belongs to rank k mod nranks, the last block may be partial.  The rank traces its
  * blocks into the rays' own elements of the FULL-SIZE device arrays (each nullable); gather != 0 completes them on every
  * rank (grouped broadcasts).  Contiguous ranges per rank left the ranks over a field's bare rim idle. */

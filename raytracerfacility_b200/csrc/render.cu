@@ -1071,10 +1071,11 @@ int scan_grid_device(rtf_ctx* ctx, const rtf_scan_grid* grid, uint64_t ray_begin
   RTF_CUDA(cudaGetLastError());
   return RTF_OK;
 }
-// Block layout of the interleaved LiDAR shards: about 16 blocks per rank, 2^12 .. 2^24 rays each.
+// Block layout of the interleaved LiDAR shards: about 64 blocks per rank, 2^12 .. 2^24 rays each (at 16 per rank the ranks
+// of C4 on 8 GPUs still differed by 15 %: 4.06 .. 4.73 ms).
 void scan_interleave_layout(uint64_t total, int nranks, int rank, uint32_t* shift, uint64_t* n_blocks, uint64_t* n_local) {
   uint32_t sh = 12;
-  while (sh < 24 && (total >> sh) > 16ull * (uint64_t)nranks) sh++;
+  while (sh < 24 && (total >> sh) > 64ull * (uint64_t)nranks) sh++;
   const uint64_t B = 1ull << sh, nb = (total + B - 1) / B;
   uint64_t mine = (uint64_t)rank < nb ? (nb - (uint64_t)rank + (uint64_t)nranks - 1) / (uint64_t)nranks : 0;
   uint64_t rays = mine * B;

@@ -27,7 +27,7 @@ def test_split_range_partitions():
 def test_interleaved_lidar_shard_layout():
     """rtf_scan_grid_shard_layout (host arithmetic of the library, what the sharded LiDAR entry points use): the blocks
     of all ranks cover every ray of the grid exactly once, block k belongs to rank k mod world, only the grid's last block
-    is partial, about 16 blocks per rank, and a rank's blocks are what DistributedRayTracer.local_rays cuts out."""
+    is partial, about 64 blocks per rank, and a rank's blocks are what DistributedRayTracer.local_rays cuts out."""
     from raytracerfacility_b200 import module, scenes
     from raytracerfacility_b200.parallel import DistributedRayTracer
     for side_x, side_y in ((400, 200), (130, 140), (10000, 10000), (1, 1), (4097, 3)):
@@ -39,7 +39,7 @@ def test_interleaved_lidar_shard_layout():
             assert all(l[0] == block and l[1] == n_blocks for l in lay)
             assert block & (block - 1) == 0 and 1 << 12 <= block <= 1 << 24
             assert n_blocks == (total + block - 1) // block
-            assert n_blocks <= 16 * world or block == 1 << 24
+            assert n_blocks <= 64 * world or block in (1 << 12, 1 << 24)
             assert sum(l[2] for l in lay) == total
             seen = np.zeros(n_blocks, dtype=np.int32)
             for r in range(world):
