@@ -166,36 +166,35 @@ __global__ void k_split_count(const float* __restrict__ pos9, uint32_t n, int ma
   load_tri(pos9, t, a, b, c);
   cnt[t] = (uint32_t)split_plan(a, b, c, max_split).k;
 }
-__global__ void k_split_emit(const float* __restrict__ pos9, uint32_t n, int max_split, const uint32_t* __restrict__ first,
-                             uint32_t* __restrict__ ref_tri, float* __restrict__ ref_box) {
-  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= n) return;
-  float3 a, b, c;
-  load_tri(pos9, t, a, b, c);
-  const SplitPlan sp = split_plan(a, b, c, max_split);
-  const uint32_t r0 = first[t];
-  for (int j = 0; j < sp.k; j++) {
-    const Box3 bx = split_slab_box(a, b, c, sp.axis, sp.k, j);
-    ref_tri[r0 + j] = t;
-    float* o = ref_box + 6 * (size_t)(r0 + j);
-    o[0] = bx.lo.x, o[1] = bx.lo.y, o[2] = bx.lo.z, o[3] = bx.hi.x, o[4] = bx.hi.y, o[5] = bx.hi.z;
-  }
-}
-// Refit: the reference counts of the last build are kept (first[t+1] - first[t] slabs per triangle), only the boxes are
-// recomputed from the moved vertices; the slab axis is the longest axis of the triangle's current box.
-__global__ void k_split_emit_fixed(const float* __restrict__ pos9, uint32_t n, const uint32_t* __restrict__ first,
-                                   float* __restrict__ ref_box) {
-  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= n) return;
-  float3 a, b, c;
-  load_tri(pos9, t, a, b, c);
-  const int axis = split_plan(a, b, c, 1).axis;
-  const uint32_t r0 = first[t];
-  const int k = (int)(first[t + 1] - r0);
-  for (int j = 0; j < k; j++) {
+// One thread per REFERENCE: a block owns 256 consecutive triangles, i.e. the contiguous run of references
+// [first[T0], first[T0 + 256)), and its threads stride over that run — every lane clips one slab per step and the stores
+// are coalesced.  (One thread per triangle looping over its 1..8 slabs ran at the lane count of the longest loop in the
+// warp and scattered 28-byte stores: 161 us for the C2 scene.)  The triangle of a reference is found by a binary search
+// over the block's 257 offsets in shared memory; the slab axis is the longest axis of the triangle's box, the slab count
+// the one k_split_count planned (build) or the last build kept (refit: ref_tri == nullptr).
+__global__ void __launch_bounds__(256) k_split_emit(const float* __restrict__ pos9, uint32_t n, const uint32_t* __restrict__ first,
+                                                    uint32_t* __restrict__ ref_tri, float* __restrict__ ref_box) {
+  __shared__ uint32_t s_first[257];
+  const uint32_t T0 = blockIdx.x * 256u;
+  const uint32_t nt = min(256u, n - T0);
+  for (uint32_t k = threadIdx.x; k <= nt; k += 256u) s_first[k] = first[T0 + k];
+  __syncthreads();
+  const uint32_t R0 = s_first[0], R1 = s_first[nt];
+  for (uint32_t r = R0 + threadIdx.x; r < R1; r += 256u) {
+    uint32_t lo = 0, hi = nt;  // s_first[lo] <= r < s_first[hi]
+    while (hi - lo > 1u) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (s_first[mid] <= r) lo = mid; else hi = mid;
+    }
+    const uint32_t t = T0 + lo;
+    const int k = (int)(s_first[lo + 1] - s_first[lo]), j = (int)(r - s_first[lo]);
+    float3 a, b, c;
+    load_tri(pos9, t, a, b, c);
+    const int axis = split_plan(a, b, c, 1).axis;
     const Box3 bx = split_slab_box(a, b, c, axis, k, j);
-    float* o = ref_box + 6 * (size_t)(r0 + j);
-    o[0] = bx.lo.x, o[1] = bx.lo.y, o[2] = bx.lo.z, o[3] = bx.hi.x, o[4] = bx.hi.y, o[5] = bx.hi.z;
+    if (ref_tri) ref_tri[r] = t;
+    float2* o = (float2*)(ref_box + 6 * (size_t)r);
+    o[0] = make_float2(bx.lo.x, bx.lo.y), o[1] = make_float2(bx.lo.z, bx.hi.x), o[2] = make_float2(bx.hi.y, bx.hi.z);
   }
 }
 __device__ __forceinline__ Box3 ref_box_load(const float* __restrict__ ref_box, uint32_t r) {
@@ -486,7 +485,14 @@ __device__ __forceinline__ void collapse_plan(const CollapseArgs& a, int R, int 
     nc++;
   }
   // greedy slot assignment: nc times, the (child, slot) pair of largest cost among the unassigned children and free
-  // slots, first pair in (child, slot) order on ties
+  // slots, first pair in (child, slot) order on ties.  cost(i, s) = ((+-dx) + (+-dy)) + (+-dz) with the signs of slot s;
+  // the complementary slot 7 - s flips all three signs and IEEE addition is symmetric under negation, so
+  // cost(i, 7 - s) = -cost(i, s) exactly: four sums per child, computed once, serve all eight slots of every round.
+  float cst[8][4];
+#pragma unroll
+  for (int i = 0; i < 8; i++)
+#pragma unroll
+    for (int k = 0; k < 4; k++) cst[i][k] = ((-dv[i].x) + ((k & 2) ? dv[i].y : -dv[i].y)) + ((k & 1) ? dv[i].z : -dv[i].z);
   uint32_t open_i = (1u << nc) - 1u, free_s = 0xffu;
   int child_in_slot[8];
 #pragma unroll
@@ -500,7 +506,7 @@ __device__ __forceinline__ void collapse_plan(const CollapseArgs& a, int R, int 
       int bs = -1;
 #pragma unroll
       for (int s = 0; s < 8; s++) {
-        const float cost = (((s & 4) ? dv[i].x : -dv[i].x) + ((s & 2) ? dv[i].y : -dv[i].y)) + ((s & 1) ? dv[i].z : -dv[i].z);
+        const float cost = s < 4 ? cst[i][s] : -cst[i][7 - s];
         if (((free_s >> s) & 1u) && (bs < 0 || cost > best)) best = cost, bs = s;
       }
       bc[i] = best, bsl[i] = bs;
@@ -775,7 +781,7 @@ int refit_bvh(rtf_ctx* ctx) {
   if (nt == 0 || n == 0 || !ctx->refit_ok || ctx->n_nodes == 0) return RTF_ERR_NOT_READY;
   int rc;
   mark(ctx, 1);
-  LAUNCH(ctx, k_split_emit_fixed, div_up(nt, 256), 256, 0, ctx->d_pos9.as<float>(), nt, ba.ref_first.as<uint32_t>(),
+  LAUNCH(ctx, k_split_emit, div_up(nt, 256), 256, 0, ctx->d_pos9.as<float>(), nt, ba.ref_first.as<uint32_t>(), (uint32_t*)nullptr,
          ba.ref_box.as<float>());
   mark(ctx, 2);
   mark(ctx, 3);
@@ -830,7 +836,7 @@ int build_bvh(rtf_ctx* ctx, int bits) {
   if ((rc = ba.children.reserve(8 * (size_t)n))) return rc;
   if ((rc = ba.range.reserve(8 * (size_t)n))) return rc;
   if ((rc = ba.boxes.reserve(24 * (size_t)(2 * (size_t)n)))) return rc;
-  LAUNCH(ctx, k_split_emit, div_up(nt, 256), 256, 0, ctx->d_pos9.as<float>(), nt, ctx->presplit, ba.ref_first.as<uint32_t>(),
+  LAUNCH(ctx, k_split_emit, div_up(nt, 256), 256, 0, ctx->d_pos9.as<float>(), nt, ba.ref_first.as<uint32_t>(),
          ba.ref_tri.as<uint32_t>(), ba.ref_box.as<float>());
   LAUNCH(ctx, k_morton, div_up(n, 256), 256, 0, ba.ref_box.as<float>(), n, fb, bits, ba.morton.as<uint64_t>());
   mark(ctx, 2);
