@@ -236,13 +236,21 @@ def reference_arm(args):
 
 # ---------------------------------------------------------------------------------------------------------
 def kernel_source_hash():
-    """sha256 over the sources that decide what the traversal kernel reads (the kernel, the node format, the builder):
-    profiles/traffic.json carries the hash of the tree its ncu capture was taken from, and is ignored when it differs."""
+    """sha256 over the sources that decide what the traversal kernel executes and reads: the engine, the node format, the
+    builder and its sort, and the raw closest-hit section of render.cu (ray source + kernel; the rest of that file is the
+    wavefront path tracer, which k_trace_rays does not touch).  profiles/traffic.json carries the hash of the tree its ncu
+    capture was taken from, and is ignored when it differs."""
     import hashlib
     h = hashlib.sha256()
-    for f in ("rtf_trace.cuh", "rtf_bvh.cuh", "build.cu", "render.cu"):
-        with open(os.path.join(ROOT, "raytracerfacility_b200", "csrc", f), "rb") as fh:
+    csrc = os.path.join(ROOT, "raytracerfacility_b200", "csrc")
+    for f in ("rtf_trace.cuh", "rtf_bvh.cuh", "build.cu", "rtf_sort.cuh"):
+        with open(os.path.join(csrc, f), "rb") as fh:
             h.update(fh.read())
+    with open(os.path.join(csrc, "render.cu"), "rb") as fh:
+        text = fh.read()
+    a = text.index(b"// ============================ raw closest-hit (M1 metric)")
+    b = text.index(b"// ====", a + 8)
+    h.update(text[a:b])
     return h.hexdigest()[:16]
 
 

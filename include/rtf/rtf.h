@@ -183,14 +183,15 @@ typedef struct rtf_scan_grid {
  * BSDF.cuh:6-13 + RF.cuh:152-161 (the reference's only model).  RTF_BRDF_LAMBERT_GGX (BASELINE config 2) = importance-
  * sampled Lambert + GGX (Schlick Fresnel, Smith G); a new capability, checked against its own closed forms only. */
 enum { RTF_BRDF_REFERENCE = 0, RTF_BRDF_LAMBERT_GGX = 1 };
-/* Random numbers of rtf_estimate_illumination, rtf_set_option(ctx, "rng", ...).  RTF_RNG_PHILOX (default, every entry
+/* Random numbers of rtf_estimate_illumination and rtf_render_camera[_rows], rtf_set_option(ctx, "rng", ...).  RTF_RNG_PHILOX (default, every entry
  * point): counter-based Philox-4x32-10 keyed (seed, stream, unit, bounce, primitive) — a draw does not depend on what other
  * rays drew, which is what lets samples run in parallel and results be independent of batching and GPU count.
- * RTF_RNG_REFERENCE_LCG (verification mode, AoS illumination entry point only): the reference's own generator
- * (LinearCongruenceGenerator.hpp:6-35), one stream per probe seeded (probe index, seed) as __raygen__IE does
- * (IlluminationEstimation.cu:47) and consumed in the reference's order — the samples of a probe run one after the other,
- * so it is slow; results are comparable with the reference's programs directly (tests/test_gpu_lcg.py).  Scenes with a
- * subsurface material are refused. */
+ * RTF_RNG_REFERENCE_LCG (verification mode; the AoS illumination entry point and the single-context camera calls): the
+ * reference's own generator (LinearCongruenceGenerator.hpp:6-35), one stream per probe seeded (probe index, seed) as
+ * __raygen__IE does (IlluminationEstimation.cu:47), one per pixel seeded (pixel, frame id) as __raygen__CR does
+ * (CameraRendering.cu:42-44), consumed in the reference's order — the samples of a probe / pixel run one after the other, so
+ * it is slow; results are comparable with the reference's programs directly (tests/test_gpu_lcg.py).  Scenes with a
+ * subsurface material and the sharded camera calls are refused. */
 enum { RTF_RNG_PHILOX = 0, RTF_RNG_REFERENCE_LCG = 1 };
 
 typedef struct rtf_ctx rtf_ctx;
@@ -283,7 +284,7 @@ RTF_API int rtf_build_timings(rtf_ctx* ctx, float* ms_out, int n);
  * "presplit" = most references a long thin triangle may be cut into before the Morton sort
  * (default 8, 1 = off; applies at the next rtf_commit; hits do not depend on it),
  * "brdf" = RTF_BRDF_REFERENCE (default) or RTF_BRDF_LAMBERT_GGX,
- * "rng" = RTF_RNG_PHILOX (default) or RTF_RNG_REFERENCE_LCG (rtf_estimate_illumination only),
+ * "rng" = RTF_RNG_PHILOX (default) or RTF_RNG_REFERENCE_LCG (rtf_estimate_illumination, rtf_render_camera[_rows]),
  * "refit" = 0/1 allow the refit path of rtf_commit (see rtf_commit_stats; default 0). */
 RTF_API int rtf_set_option(rtf_ctx* ctx, const char* name, int64_t value);
 

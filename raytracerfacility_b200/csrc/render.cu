@@ -1175,25 +1175,9 @@ __global__ void __launch_bounds__(256)
     q.ray_b[0][slot] = nb;
   }
 }
-// CameraRendering.cu:101-146: per-pixel sums in sample order, progressive accumulation in gamma space.
-__global__ void __launch_bounds__(256)
-    k_resolve_camera(rtf_camera_props cam, PixelMap pxm, uint32_t n_pixels, uint32_t spp, PathState ps,
-                     float4* __restrict__ color, float4* __restrict__ normal, float4* __restrict__ albedo) {
-  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= n_pixels) return;
-  const uint64_t pixel = pixel_of(pxm, k);
-  const float nsf = (float)spp;
-  float3 pc = f3(0, 0, 0), pn = f3(0, 0, 0), pa = f3(0, 0, 0), pp = f3(0, 0, 0);
-  for (uint32_t s = 0; s < spp; s++) {
-    const size_t p = (size_t)k * spp + s;
-    const float4 e = ps.acc[p], n4 = ps.first_n[p], a4 = ps.first_a[p], p4 = ps.first_p[p];
-    float3 pos = f3(p4.x, p4.y, p4.z);
-    if (p4.w == 0.0f) pos = s == 0 ? f3(999999.0f, 999999.0f, 999999.0f) : f3(0, 0, 0);  // CameraRendering.cu:48,108
-    pc = pc + f3(e.x / nsf, e.y / nsf, e.z / nsf);
-    pn = pn + f3(n4.x / nsf, n4.y / nsf, n4.z / nsf);
-    pa = pa + f3(a4.x / nsf, a4.y / nsf, a4.z / nsf);
-    pp = pp + f3(pos.x / nsf, pos.y / nsf, pos.z / nsf);
-  }
+// CameraRendering.cu:112-146: progressive accumulation in gamma space and the three output writes of a pixel.
+__device__ __forceinline__ void camera_write(const rtf_camera_props& cam, uint64_t pixel, float3 pc, float3 pn, float3 pa, float3 pp,
+                                             float4* __restrict__ color, float4* __restrict__ normal, float4* __restrict__ albedo) {
   if (cam.accumulate && cam.frame_id > 1) {
     const float4 prev = color[pixel];
     const float3 accd = f3(powf(prev.x, cam.gamma), powf(prev.y, cam.gamma), powf(prev.z, cam.gamma));
@@ -1213,6 +1197,145 @@ __global__ void __launch_bounds__(256)
   }
   normal[pixel] = make_float4(pn.x, pn.y, pn.z, 1.0f);
 }
+// CameraRendering.cu:101-146: per-pixel sums in sample order, progressive accumulation in gamma space.
+__global__ void __launch_bounds__(256)
+    k_resolve_camera(rtf_camera_props cam, PixelMap pxm, uint32_t n_pixels, uint32_t spp, PathState ps,
+                     float4* __restrict__ color, float4* __restrict__ normal, float4* __restrict__ albedo) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_pixels) return;
+  const uint64_t pixel = pixel_of(pxm, k);
+  const float nsf = (float)spp;
+  float3 pc = f3(0, 0, 0), pn = f3(0, 0, 0), pa = f3(0, 0, 0), pp = f3(0, 0, 0);
+  for (uint32_t s = 0; s < spp; s++) {
+    const size_t p = (size_t)k * spp + s;
+    const float4 e = ps.acc[p], n4 = ps.first_n[p], a4 = ps.first_a[p], p4 = ps.first_p[p];
+    float3 pos = f3(p4.x, p4.y, p4.z);
+    if (p4.w == 0.0f) pos = s == 0 ? f3(999999.0f, 999999.0f, 999999.0f) : f3(0, 0, 0);  // CameraRendering.cu:48,108
+    pc = pc + f3(e.x / nsf, e.y / nsf, e.z / nsf);
+    pn = pn + f3(n4.x / nsf, n4.y / nsf, n4.z / nsf);
+    pa = pa + f3(a4.x / nsf, a4.y / nsf, a4.z / nsf);
+    pp = pp + f3(pos.x / nsf, pos.y / nsf, pos.z / nsf);
+  }
+  camera_write(cam, pixel, pc, pn, pa, pp, color, normal, albedo);
+}
+// ---- option "rng" = RTF_RNG_REFERENCE_LCG for the camera: __raygen__CR with the reference's own random stream --------
+// One LCG per pixel seeded (pixel index computed in float as CR.cu:42-44 does, frame id); per sample the two jitters — the
+// second drawn first: CR.cu:60-61 draws both inside one constructor call whose argument order the language leaves open, and
+// the host build of the reference's program that made the fixture takes the second first — then the aperture angle, then
+// the path's draws.  Samples of a pixel run in sequence; the four pixel sums accumulate in sample order (CR.cu:101-110).
+__global__ void k_lcg_init_camera(rtf_camera_props cam, uint64_t first_pixel, uint32_t n, uint32_t* __restrict__ lcg,
+                                  float4* __restrict__ sums) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const uint64_t pixel = first_pixel + k;
+  const uint32_t ix = (uint32_t)(pixel % (uint64_t)cam.width), iy = (uint32_t)(pixel / (uint64_t)cam.width);
+  lcg[k] = lcg_seed((uint32_t)((float)ix + (float)cam.width * (float)iy), (uint32_t)cam.frame_id);
+#pragma unroll
+  for (int j = 0; j < 4; j++) sums[4 * (size_t)k + j] = make_float4(0, 0, 0, 0);
+}
+__global__ void __launch_bounds__(256) k_gen_camera_lcg(rtf_camera_props cam, uint64_t first_pixel, uint32_t n,
+                                                        uint32_t* __restrict__ lcg, Queues q, PathState ps) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  bool emit = false;
+  float4 na = make_float4(0, 0, 0, 0), nb = make_float4(0, 0, 0, 0);
+  if (p < n) {
+    const uint64_t pixel = first_pixel + p;
+    const uint32_t ix = (uint32_t)(pixel % (uint64_t)cam.width), iy = (uint32_t)(pixel / (uint64_t)cam.width);
+    uint32_t st_ = lcg[p];
+    const float r1 = lcg_next(st_), r0 = lcg_next(st_), r2 = lcg_next(st_);
+    lcg[p] = st_;
+    const float halfX = cam.width / 2.0f, halfY = cam.height / 2.0f;
+    const float sx = (((float)ix + r0) - halfX) / halfX;
+    const float sy = (((float)iy + r1) - halfY) / halfY;
+    const float* m = cam.inverse_projection_view;
+    float st[4], en[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      st[k] = (m[k] * sx + m[4 + k] * sy) + (m[8 + k] * -1.0f + m[12 + k] * 1.0f);
+      en[k] = (m[k] * sx + m[4 + k] * sy) + (m[8 + k] * 1.0f + m[12 + k] * 1.0f);
+    }
+    const float3 start = f3(st[0] / st[3], st[1] / st[3], st[2] / st[3]);
+    const float3 end = f3(en[0] / en[3], en[1] / en[3], en[2] / en[3]);
+    const float3 pdir = normalize3(end - start);
+    const float3 conv = start + pdir * cam.focal_length;
+    float sn, cs;
+    sincos2pi(r2, sn, cs);
+    const float3 hor = f3(cam.horizontal[0], cam.horizontal[1], cam.horizontal[2]);
+    const float3 ver = f3(cam.vertical[0], cam.vertical[1], cam.vertical[2]);
+    const float3 ap = start + cam.aperture * (hor * sn + ver * cs);
+    const float3 dir = normalize3(conv - ap);
+    emit = true;
+    na = make_float4(ap.x, ap.y, ap.z, __uint_as_float(p));
+    nb = make_float4(dir.x, dir.y, dir.z, 1e20f);
+    ps.thr[p] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(0u));
+    ps.acc[p] = make_float4(0, 0, 0, 0);
+    ps.first_n[p] = make_float4(0, 0, 0, 0);
+    ps.first_a[p] = make_float4(0, 0, 0, 0);
+    ps.first_p[p] = make_float4(0, 0, 0, 0);
+  }
+  const uint32_t slot = warp_append(emit, q.count + 0);
+  if (emit) {
+    q.ray_a[0][slot] = na;
+    q.ray_b[0][slot] = nb;
+  }
+}
+__global__ void k_accum_camera_lcg(uint32_t n, uint32_t sample, uint32_t spp, PathState ps, float4* __restrict__ sums) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n) return;
+  const float nsf = (float)spp;
+  const float4 e = ps.acc[p], n4 = ps.first_n[p], a4 = ps.first_a[p], p4 = ps.first_p[p];
+  float3 pos = f3(p4.x, p4.y, p4.z);
+  if (p4.w == 0.0f) pos = sample == 0u ? f3(999999.0f, 999999.0f, 999999.0f) : f3(0, 0, 0);  // CameraRendering.cu:48,108
+  float4* s4 = sums + 4 * (size_t)p;
+  const float4 c = s4[0], nn = s4[1], aa = s4[2], pp = s4[3];
+  s4[0] = make_float4(c.x + e.x / nsf, c.y + e.y / nsf, c.z + e.z / nsf, 0.0f);
+  s4[1] = make_float4(nn.x + n4.x / nsf, nn.y + n4.y / nsf, nn.z + n4.z / nsf, 0.0f);
+  s4[2] = make_float4(aa.x + a4.x / nsf, aa.y + a4.y / nsf, aa.z + a4.z / nsf, 0.0f);
+  s4[3] = make_float4(pp.x + pos.x / nsf, pp.y + pos.y / nsf, pp.z + pos.z / nsf, 0.0f);
+}
+__global__ void k_resolve_camera_lcg(rtf_camera_props cam, uint64_t first_pixel, uint32_t n, const float4* __restrict__ sums,
+                                     float4* __restrict__ color, float4* __restrict__ normal, float4* __restrict__ albedo) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const float4* s4 = sums + 4 * (size_t)k;
+  camera_write(cam, first_pixel + k, f3(s4[0].x, s4[0].y, s4[0].z), f3(s4[1].x, s4[1].y, s4[1].z), f3(s4[2].x, s4[2].y, s4[2].z),
+               f3(s4[3].x, s4[3].y, s4[3].z), color, normal, albedo);
+}
+static int render_camera_lcg(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, uint64_t px_begin,
+                             uint64_t n_pixels) {
+  const rtf_camera_props& cp = cam->props;
+  if (ctx->scene.has_sss) {
+    set_error("option rng = reference: scenes with a subsurface material are not supported (order-dependent probe)");
+    return RTF_ERR_INVALID;
+  }
+  const size_t cap = batch_capacity(ctx);
+  int rc;
+  if ((rc = ensure_workspace(ctx, cap, true))) return rc;
+  if ((rc = ctx->ws.lcg.reserve(4 * cap + 64 * cap))) return rc;
+  uint32_t* lcg = ctx->ws.lcg.as<uint32_t>();
+  float4* sums = (float4*)(lcg + cap);
+  Queues q;
+  PathState ps;
+  bind(ctx, q, ps, true);
+  if (!ctx->stats_hold) RTF_CUDA(cudaMemsetAsync(ctx->d_stats.p, 0, 16, ctx->stream));
+  ctx->stats_cached = false;
+  const PathMap pm{1, 0ull, 0ull, 0u, 0u, 0u, 0u, PixelMap{0ull, 0u, 0u, 0u, 0ull, 0u}, 1u};  // unused by the LCG draws
+  for (uint64_t b0 = 0; b0 < n_pixels; b0 += cap) {
+    const uint32_t nb = (uint32_t)((n_pixels - b0) < cap ? (n_pixels - b0) : cap);
+    LAUNCH(ctx, k_lcg_init_camera, div_up(nb, 256), 256, 0, cp, px_begin + b0, nb, lcg, sums);
+    for (int s = 0; s < rp->samples; s++) {
+      RTF_CUDA(cudaMemsetAsync(ctx->ws.counters.p, 0, 4096, ctx->stream));
+      LAUNCH_P(ctx, PROF_GEN, k_gen_camera_lcg, div_up(nb, 256), 256, 0, cp, px_begin + b0, nb, lcg, q, ps);
+      if ((rc = run_wavefronts(ctx, env, rp->bounces, (uint32_t)cp.frame_id, pm, nb, q, ps, true, lcg))) return rc;
+      LAUNCH_P(ctx, PROF_REDUCE, k_accum_camera_lcg, div_up(nb, 256), 256, 0, nb, (uint32_t)s, (uint32_t)rp->samples, ps, sums);
+    }
+    LAUNCH_P(ctx, PROF_REDUCE, k_resolve_camera_lcg, div_up(nb, 256), 256, 0, cp, px_begin + b0, nb, sums, cam->color.as<float4>(),
+             cam->normal.as<float4>(), cam->albedo.as<float4>());
+  }
+  RTF_CUDA(cudaGetLastError());
+  ctx->last_paths = n_pixels * (uint64_t)rp->samples;
+  return RTF_OK;
+}
 
 // One camera job over `n_local` pixels addressed through `pxm`, in batches of the wavefront capacity.
 static int render_camera_mapped(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, const PixelMap& job,
@@ -1223,6 +1346,13 @@ static int render_camera_mapped(rtf_ctx* ctx, const rtf_env* env, rtf_camera* ca
   if (env->environmental_map_id != 0 && env->lighting_type == RTF_ENV_SCENE && ctx->scene.env_faces == nullptr) {
     set_error("environmental_map_id != 0 but no cube map is registered (rtf_set_environment_map, then rtf_commit)");
     return RTF_ERR_INVALID;
+  }
+  if (ctx->rng == RTF_RNG_REFERENCE_LCG) {
+    if (job.band_px != 0u) {
+      set_error("option rng = reference: not available for sharded camera jobs");
+      return RTF_ERR_INVALID;
+    }
+    return render_camera_lcg(ctx, env, cam, rp, job.first, n_local);
   }
   const uint32_t spp = (uint32_t)rp->samples;
   size_t cap = batch_capacity(ctx);

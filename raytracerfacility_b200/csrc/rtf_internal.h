@@ -243,7 +243,7 @@ struct rtf_ctx {
   size_t batch_paths = (size_t)1 << 24;  // 2^24 paths: ~3 GB of queues + path state; +12..20 % over 2^22 (fewer, fuller waves)
   int sort_rays = 0;  // option "sort_rays": sort bounce rays by (octant, origin cell) before tracing (measured: DESIGN.md)
   int brdf = RTF_BRDF_REFERENCE;  // option "brdf"
-  int rng = RTF_RNG_PHILOX;       // option "rng" (rtf_estimate_illumination only)
+  int rng = RTF_RNG_PHILOX;       // option "rng" (rtf_estimate_illumination, single-context camera calls)
   // RenderToCamera's change detection (m_cameraRenderingLaunchParams.m_rayTracerProperties, RayTracer.cu:253-269): the
   // environment / ray properties and scene epoch the last frame was rendered with
   rtf_env cam_last_env;

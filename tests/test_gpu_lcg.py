@@ -69,6 +69,43 @@ def test_illumination_with_the_reference_stream(rt, orc, S, ref, scene):
         rt.set_option("rng", S.RNG_PHILOX)
 
 
+def test_camera_with_the_reference_stream(rt, S, ref):
+    """__raygen__CR: one stream per pixel seeded (pixel, frame id), second jitter drawn first (the argument order of the host
+    build that made the fixture), aperture angle, path draws; pixel sums in sample order.  Against the fixture of the
+    reference's camera program on the `mixed` scene (depth of field, depth output, skydome, cube map): ray counts equal,
+    first-hit buffers and colours to 1e-5 (the aperture point goes through the portable sin / cos here, libm there).  The
+    progressive-accumulation case needs the previous frame in the colour buffer and is left to the oracle's comparison."""
+    import ctypes as C
+    sd = G.programs_ref_scenes()["mixed"]
+    rt.load_scene(sd, 63)
+    rt.set_option("rng", S.RNG_REFERENCE_LCG)
+    try:
+        stats = []
+        for k, (e, b, n, ot, acc) in enumerate(G.PROGRAMS_CR):
+            if acc:
+                continue
+            props = G.programs_camera(acc)
+            props.output_type = ot
+            cam = rt.create_camera()
+            cam.resize(props.width, props.height)
+            C.memmove(C.addressof(cam.props), C.addressof(props), C.sizeof(S.CameraProps))
+            cam.props.modified = 1
+            env, rp = S.EnvironmentProperties(**G.PROGRAMS_ENVS[e]), S.RayProperties(b, n)
+            assert rt.render_to_camera(env, cam, rp)
+            want = ref[f"cr_{k}"].view(np.float32)
+            rays = rt.last_job_stats()[0]
+            assert rays == int(ref[f"cr_{k}_rays"][0]), (k, rays, int(ref[f"cr_{k}_rays"][0]))
+            got = np.concatenate([cam.download(w).reshape(-1, 4) for w in (S.OUT_COLOR, S.OUT_NORMAL, S.OUT_ALBEDO)], 1)
+            err = np.abs(got - want)
+            scale = np.maximum(np.abs(want), 1.0)
+            stats.append((k, float((err / scale)[:, :4].max()), float((err / scale)[:, 4:].max())))
+            cam.destroy()
+        bad = [s_ for s_ in stats if not (s_[1] <= 1e-5 and s_[2] <= 1e-5)]
+        assert len(stats) == 4 and not bad, (bad, stats)
+    finally:
+        rt.set_option("rng", S.RNG_PHILOX)
+
+
 def test_the_mode_refuses_subsurface_scenes(rt, mod, S, orc):
     sd = G.programs_ref_scenes()["sss"]
     rt.load_scene(sd, 63)
