@@ -446,6 +446,8 @@ RTF_API int rtf_render_camera_rows(rtf_ctx* ctx, const rtf_env* env, rtf_camera*
                                    int row_begin, int row_end);
 /* which: RTF_OUT_COLOR / NORMAL / ALBEDO(also depth when output_type == DEPTH); host float4 per pixel */
 RTF_API int rtf_camera_download(rtf_camera* cam, int which, float* host_rgba);
+/* host -> frame buffer (width * height float4): restores a buffer, e.g. the colour buffer progressive accumulation blends into */
+RTF_API int rtf_camera_upload(rtf_camera* cam, int which, const float* host);
 RTF_API int rtf_camera_device_buffer(rtf_camera* cam, int which, float** dev_rgba);
 
 /* ---- multi-GPU (no reference counterpart: CudaModule::Init is cudaSetDevice(0), CM.cpp:25; RT.cu:827) -------------

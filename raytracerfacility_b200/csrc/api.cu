@@ -1048,6 +1048,20 @@ int rtf_camera_download(rtf_camera* cam, int which, float* host) {
   return RTF_OK;
 }
 
+// The inverse of rtf_camera_download: restores a frame buffer (e.g. the colour buffer of an earlier session, so that
+// progressive accumulation — CameraRendering.cu:112-128 blends into what the buffer holds — can go on).
+int rtf_camera_upload(rtf_camera* cam, int which, const float* host) {
+  if (!cam || !host) return RTF_ERR_INVALID;
+  RTF_CUDA(cudaSetDevice(cam->ctx->device));
+  float* d = nullptr;
+  rtf_camera_device_buffer(cam, which, &d);
+  const size_t bytes = (size_t)cam->props.width * cam->props.height * 16;
+  if (!d || bytes == 0) return RTF_ERR_INVALID;
+  RTF_CUDA(cudaMemcpyAsync(d, host, bytes, cudaMemcpyHostToDevice, cam->ctx->stream));
+  RTF_CUDA(cudaStreamSynchronize(cam->ctx->stream));
+  return RTF_OK;
+}
+
 // ---- parity read-back ----------------------------------------------------------------------------------------------
 static const void* dbg_ptr(rtf_ctx* c, int what, uint64_t* bytes) {
   const uint64_t nt = c->n_tris, n = c->n_refs, ni = n ? n - 1 : 0;  // n: triangle references

@@ -32,7 +32,7 @@ EXPORTS = [
     "rtf_last_job_stats", "rtf_scan_point_cloud", "rtf_scan_grid_ray_count", "rtf_scan_grid_dims", "rtf_scan_grid_trace",
     "rtf_scan_grid_trace_device", "rtf_trace_closest", "rtf_trace_closest_device", "rtf_trace_closest_counts",
     "rtf_camera_create", "rtf_camera_destroy", "rtf_camera_get_props", "rtf_camera_resize", "rtf_camera_set",
-    "rtf_render_camera", "rtf_render_camera_rows", "rtf_camera_download", "rtf_camera_device_buffer", "rtf_debug_size", "rtf_debug_read",
+    "rtf_render_camera", "rtf_render_camera_rows", "rtf_camera_download", "rtf_camera_upload", "rtf_camera_device_buffer", "rtf_debug_size", "rtf_debug_read",
     "rtf_debug_upload_bvh", "rtf_microbench_fp32", "rtf_microbench_l2", "rtf_build_timings", "rtf_set_option",
     "rtf_set_texture", "rtf_remove_texture", "rtf_set_material_textures", "rtf_set_environment_map", "rtf_sample_texture",
     "rtf_sample_environment", "rtf_set_btf", "rtf_btf_import_folder", "rtf_remove_btf", "rtf_set_material_btf",
@@ -122,6 +122,11 @@ class Camera:
         out = np.empty((self.props.height, self.props.width, 4), dtype=np.float32)
         _check(lib().rtf_camera_download(self.h, int(which), _p(out)))
         return out
+
+    def upload(self, data, which=S.OUT_COLOR):
+        a = np.ascontiguousarray(data, dtype=np.float32)
+        assert a.size == self.props.height * self.props.width * 4
+        _check(lib().rtf_camera_upload(self.h, int(which), _p(a)))
 
     def device_buffer(self, which=S.OUT_COLOR):
         d = C.c_void_p()

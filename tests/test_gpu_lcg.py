@@ -74,7 +74,7 @@ def test_camera_with_the_reference_stream(rt, S, ref):
     build that made the fixture), aperture angle, path draws; pixel sums in sample order.  Against the fixture of the
     reference's camera program on the `mixed` scene (depth of field, depth output, skydome, cube map): ray counts equal,
     first-hit buffers and colours to 1e-5 (the aperture point goes through the portable sin / cos here, libm there).  The
-    progressive-accumulation case needs the previous frame in the colour buffer and is left to the oracle's comparison."""
+    progressive-accumulation case restores the previous frame with rtf_camera_upload and renders frame 3 of the sequence."""
     import ctypes as C
     sd = G.programs_ref_scenes()["mixed"]
     rt.load_scene(sd, 63)
@@ -82,15 +82,20 @@ def test_camera_with_the_reference_stream(rt, S, ref):
     try:
         stats = []
         for k, (e, b, n, ot, acc) in enumerate(G.PROGRAMS_CR):
-            if acc:
-                continue
             props = G.programs_camera(acc)
             props.output_type = ot
             cam = rt.create_camera()
             cam.resize(props.width, props.height)
             C.memmove(C.addressof(cam.props), C.addressof(props), C.sizeof(S.CameraProps))
-            cam.props.modified = 1
             env, rp = S.EnvironmentProperties(**G.PROGRAMS_ENVS[e]), S.RayProperties(b, n)
+            if acc:  # frame 3 of a progressive render: the colour buffer holds the previous result, nothing has changed since
+                cam.props.accumulate = 0
+                assert rt.render_to_camera(env, cam, rp)  # registers env / ray properties / scene epoch as seen
+                C.memmove(C.addressof(cam.props), C.addressof(props), C.sizeof(S.CameraProps))
+                cam.props.modified = 0
+                cam.upload(G.programs_prev_color())
+            else:
+                cam.props.modified = 1
             assert rt.render_to_camera(env, cam, rp)
             want = ref[f"cr_{k}"].view(np.float32)
             rays = rt.last_job_stats()[0]
@@ -101,7 +106,7 @@ def test_camera_with_the_reference_stream(rt, S, ref):
             stats.append((k, float((err / scale)[:, :4].max()), float((err / scale)[:, 4:].max())))
             cam.destroy()
         bad = [s_ for s_ in stats if not (s_[1] <= 1e-5 and s_[2] <= 1e-5)]
-        assert len(stats) == 4 and not bad, (bad, stats)
+        assert len(stats) == 5 and not bad, (bad, stats)
     finally:
         rt.set_option("rng", S.RNG_PHILOX)
 
