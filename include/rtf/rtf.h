@@ -400,6 +400,24 @@ RTF_API int rtf_prepare_light_probes(rtf_ctx* ctx, uint64_t tri_begin, uint64_t 
 RTF_API int rtf_illumination_flux(rtf_ctx* ctx, const rtf_illum_sampler* probes /* host */, size_t n, float* out8);
 RTF_API int rtf_illumination_flux_mesh_device(rtf_ctx* ctx, const float* dev_energy6, uint64_t tri_begin,
                                               uint64_t tri_end, int front_face, int back_face, float* out8);
+/* No counterpart in the reference.  rtf_illumination_flux_mesh_device for hosts that cannot let this library allocate
+ * device memory: an engine that claimed the whole GPU for a pool of its own at start-up (cudaMalloc then fails, and with
+ * it the workspace the ordinary call grows on first use), or a frame loop that cannot take the device-wide
+ * synchronisation cudaMalloc / cudaFree imply.  This call never allocates or frees, on the device or through any
+ * library: the partial sums of the reduction tree live in a 525 312-byte array that is part of the library image, so
+ * every GPU that loads librtf_b200.so holds it until the process exits.
+ *   - Limit: tri_end - tri_begin <= 16 777 216 (2^24) triangles per call; more returns RTF_ERR_LIMIT with a message
+ *     (split the range, or use rtf_illumination_flux_mesh_device).
+ *   - dev_out8: DEVICE pointer to 8 floats, same contents and the same bits as the ordinary call's out8.  The call only
+ *     enqueues on the context's stream, like every *_device entry point; nothing is copied to the host.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device current)
+ *     and keeps it.  Make that first call during set-up, before any stream capture begins.
+ *   - One array per GPU is shared by every call and every context on that GPU.  It keeps what the last call wrote; no
+ *     part of it needs clearing, because each level of the tree reads only what the level below wrote in the same
+ *     call.  Two calls whose kernels can overlap on the GPU (different streams, no ordering between them) race on it:
+ *     order them. */
+RTF_API int rtf_illumination_flux_mesh_device_static(rtf_ctx* ctx, const float* dev_energy6, uint64_t tri_begin,
+                                                     uint64_t tri_end, int front_face, int back_face, float* dev_out8);
 /* Statistics of the last illumination / render call: rays traced, paths started. */
 RTF_API int rtf_last_job_stats(rtf_ctx* ctx, uint64_t* rays_traced, uint64_t* paths);
 

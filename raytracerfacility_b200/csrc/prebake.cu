@@ -10,6 +10,8 @@
 // record allows); arithmetic is written in glm's operation order so that the CPU oracle reproduces every bit.
 #include <string.h>
 
+#include <mutex>
+
 #include "rtf_internal.h"
 
 namespace rtf {
@@ -316,4 +318,97 @@ int bake_skinned(rtf_ctx* ctx, Geometry& g, const void* sverts, size_t nv, size_
   return RTF_OK;
 }
 
+
+// ---- flux integration without any allocation --------------------------------------------------------------------------
+// Some hosts of this library cannot let it call cudaMalloc: an engine that took the whole device into a memory pool of
+// its own at start-up (the driver allocator then has nothing left to give, and the grow-only workspace of flux_reduce
+// above fails with out-of-memory), and a frame loop that cannot afford the device-wide synchronisation cudaMalloc and
+// cudaFree imply.  For them the partial sums of the tree live in the array below, which is part of the library image:
+// every GPU that loads librtf_b200.so holds these bytes from module load until the process exits, used or not.
+//
+// Capacity: kFluxStaticMaxTris triangles per call = 2^14 first-level tiles of 1024 terms, then 16 second-level sums, then
+// the total.  Level 1 writes slots [0, 2^14), level 2 writes [2^14, 2^14 + 16), level 3 writes slot 0 again (level 1 is
+// dead by then) — the same ping-pong as flux_reduce, so the bits of the result are the same.
+constexpr uint64_t kFluxStaticMaxTris = 1ull << 24;
+constexpr uint64_t kFluxStaticSlots = (kFluxStaticMaxTris / 1024) + 32;  // 16 416 x 32 B = 525 312 B per GPU
+static __device__ __align__(256) Flux4 g_flux_static[kFluxStaticSlots];
+
+// In host code `g_flux_static` is only a handle the runtime uses to find the symbol; it is not a device address and must
+// never be handed to a kernel.  The address is asked for once per device, with that device current, and kept here.
+constexpr int kMaxDevices = 64;
+static Flux4* g_flux_static_ptr[kMaxDevices] = {};
+static std::mutex g_flux_static_mutex;
+
+static int flux_static_address(int device, Flux4** out) {
+  if (device < 0 || device >= kMaxDevices) {
+    set_error("rtf_illumination_flux_mesh_device_static: device ordinal beyond the 64 the address table holds");
+    return RTF_ERR_LIMIT;
+  }
+  std::lock_guard<std::mutex> lock(g_flux_static_mutex);
+  if (!g_flux_static_ptr[device]) {
+    Flux4* p = nullptr;
+    RTF_CUDA(cudaGetSymbolAddress((void**)&p, g_flux_static));  // the caller made `device` current (CHECK_CTX)
+    if (!p) {
+      set_error("cudaGetSymbolAddress returned a null address for the static flux scratch");
+      return RTF_ERR_CUDA;
+    }
+    g_flux_static_ptr[device] = p;
+  }
+  *out = g_flux_static_ptr[device];
+  return RTF_OK;
+}
+
 }  // namespace rtf
+
+using namespace rtf;
+
+extern "C" int rtf_illumination_flux_mesh_device_static(rtf_ctx* ctx, const float* dev_energy6, uint64_t tri_begin,
+                                                        uint64_t tri_end, int front, int back, float* dev_out8) {
+  if (!ctx) {
+    set_error("null context");
+    return RTF_ERR_INVALID;
+  }
+  RTF_CUDA(cudaSetDevice(ctx->device));
+  if (!dev_energy6 || !dev_out8) {
+    set_error("rtf_illumination_flux_mesh_device_static: null energy or output pointer");
+    return RTF_ERR_INVALID;
+  }
+  if (!ctx->ready) {
+    set_error("no acceleration structure (call rtf_commit)");
+    return RTF_ERR_NOT_READY;
+  }
+  if (tri_begin > tri_end) {
+    set_error("triangle range out of bounds");
+    return RTF_ERR_INVALID;
+  }
+  const uint64_t n = tri_end - tri_begin;
+  if (n > kFluxStaticMaxTris) {  // said first: the answer to "too many" is to split the range, whatever the scene holds
+    set_error("rtf_illumination_flux_mesh_device_static: " + std::to_string(n) + " triangles in the range, the static scratch "
+              "holds the partial sums of at most 16777216 (2^24); split the range or use rtf_illumination_flux_mesh_device");
+    return RTF_ERR_LIMIT;
+  }
+  if (tri_end > ctx->n_tris) {
+    set_error("triangle range out of bounds");
+    return RTF_ERR_INVALID;
+  }
+  int rc;
+  Flux4* a = nullptr;
+  if ((rc = flux_static_address(ctx->device, &a))) return rc;
+  Flux4* b = a + kFluxStaticMaxTris / 1024;
+  // Nothing here has to start at zero: every slot a level reads was written by the level below in this same call, and a
+  // tile's absent terms are added as +0 inside the kernel.  What the previous call left behind is never read.
+  uint64_t m = (n + 1023) / 1024;
+  if (m == 0) m = 1;
+  const LeafMesh leaf{ctx->d_pos9.as<float>(), dev_energy6, tri_begin, (front ? 1 : 0) + (back ? 1 : 0)};
+  LAUNCH(ctx, k_flux_tile<LeafMesh>, (unsigned)m, 256, 0, leaf, n, a);
+  while (m > 1) {
+    const uint64_t t2 = (m + 1023) / 1024;
+    LAUNCH(ctx, k_flux_tile<LeafPartials>, (unsigned)t2, 256, 0, LeafPartials{a}, m, b);
+    Flux4* tmp = a;
+    a = b, b = tmp;
+    m = t2;
+  }
+  LAUNCH(ctx, k_flux_finish, 1, 1, 0, a, dev_out8);
+  RTF_CUDA(cudaGetLastError());
+  return RTF_OK;
+}

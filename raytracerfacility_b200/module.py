@@ -38,7 +38,7 @@ EXPORTS = [
     "rtf_sample_environment", "rtf_set_btf", "rtf_btf_import_folder", "rtf_remove_btf", "rtf_set_material_btf",
     "rtf_btf_eval", "rtf_set_geometry_instanced", "rtf_set_geometry_skinned", "rtf_geometry_read_baked",
     "rtf_prepare_light_probes", "rtf_illumination_flux", "rtf_illumination_flux_mesh_device", "rtf_sss_probe",
-    "rtf_commit_stats",
+    "rtf_commit_stats", "rtf_illumination_flux_mesh_device_static",
     # multi-GPU (csrc/multi.cu)
     "rtf_comm_unique_id", "rtf_comm_init_rank", "rtf_comm_destroy", "rtf_comm_rank", "rtf_comm_barrier",
     "rtf_comm_reduce_f64", "rtf_shard_range", "rtf_estimate_illumination_mesh_sharded_device",
@@ -372,6 +372,13 @@ class RayTracer:
         _check(lib().rtf_illumination_flux_mesh_device(self.h, C.c_void_p(dev_energy6_ptr), C.c_uint64(tri_begin),
                                                        C.c_uint64(tri_end), int(front), int(back), _p(out)))
         return out
+
+    def illumination_flux_mesh_device_static(self, dev_energy6_ptr, tri_begin, tri_end, dev_out8_ptr, front=True, back=True):
+        """The flux integration with its scratch in the library's static device array: no allocation on any path, at most
+        2^24 triangles per call, result left in the caller's 8 device floats (enqueued on the context's stream)."""
+        _check(lib().rtf_illumination_flux_mesh_device_static(self.h, C.c_void_p(dev_energy6_ptr), C.c_uint64(tri_begin),
+                                                              C.c_uint64(tri_end), int(front), int(back),
+                                                              C.c_void_p(dev_out8_ptr)))
 
     def sss_probe(self, rays, handles):
         """Test hook: BSSRDF spatial probe (BSSDF.cuh:18-89); per ray {n, prim[4], t[4], u[4], v[4]} (uint32 view)."""
