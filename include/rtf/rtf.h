@@ -571,12 +571,12 @@ RTF_API int rtf_debug_read(rtf_ctx* ctx, int what, void* host_out, uint64_t byte
 /* Upload a BVH built elsewhere (the oracle, in tests) so traversal can be checked in isolation. */
 RTF_API int rtf_debug_upload_bvh(rtf_ctx* ctx, const void* wide_nodes, uint64_t n_nodes, const void* wide_tris,
                                  uint64_t n_tris, int depth);
-/* microbenchmarks for the roofline denominators BASELINE.md asks the builder to measure */
 /* Test hook: the BSSRDF spatial probe (SSAnyHit / BSSRDF, BSSDF.cuh:18-89) on its own.  rays: n x
  * {o.xyz, tmin, d.xyz, tmax}; handles: the private component handle each probe is restricted to;
  * out17: per probe {n_records, prim[4], t[4], u[4], v[4]} (float bits) = the up-to-four nearest
  * same-handle intersections in [tmin, tmax], ascending (t, prim).  See rtf_material.subsurface_*. */
 RTF_API int rtf_sss_probe(rtf_ctx* ctx, const float* rays, const uint64_t* handles, size_t n, uint32_t* out17);
+/* microbenchmarks for the roofline denominators BASELINE.md asks the builder to measure */
 RTF_API int rtf_microbench_fp32(rtf_ctx* ctx, double* tflops);
 RTF_API int rtf_microbench_l2(rtf_ctx* ctx, double bytes_footprint, double* gbs);
 

@@ -7,8 +7,11 @@ of this file restate the partitioning rules for the CPU (gloo) tests of the host
 * illumination: SAMPLE-sharded (rank r traces samples [r*S/G, (r+1)*S/G) of every triangle), partial sums
   {sum E, sum D} per triangle, ONE all-reduce(sum) of 6*nTris floats, then finalize (IlluminationEstimation.cu:125-128).
   Alternative `triangle` mode: contiguous triangle ranges + all-gather, bit-identical to one GPU.
-* LiDAR: contiguous ray ranges, no data-path collective (each rank writes its own slice), optional all-gather.
-* camera: contiguous row bands per rank, all-gather of the float4 bands.
+* LiDAR: interleaved blocks of the ray grid (block k of about 64 per rank belongs to rank k mod G; see
+  rtf_scan_grid_shard_layout), no data-path collective (each rank writes its rays' own elements), optional grouped
+  broadcasts to complete the arrays on every rank.
+* camera: interleaved row bands (band k belongs to rank k mod G), all of a rank's bands traced as one job, grouped
+  broadcasts of the float4 bands.
 
 `compute` callbacks make the wiring testable on CPU with the gloo backend (tests inject the oracle there).
 """
