@@ -65,26 +65,70 @@ static void phase_mark(rtf_ctx* ctx, int k) {
   cudaEventRecord(ctx->phase_ev[k], ctx->stream);
 }
 
-int illum_sharded_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push, int front,
-                         int back, int mode, float* d_out6) {
+// Agreement before a data collective.  Everything a rank does ahead of the collective can fail on that rank alone
+// (workspace growth on a fuller device, a scene that was not committed there, a batch limit): a rank that returned early
+// would leave the others blocked inside the collective for ever.  So every rank of a sharded call passes here EXACTLY ONCE,
+// on every path, with its own status (>= 0 fine, < 0 its error): a 4-byte all-reduce(min) on the job's stream, read back.
+// *agreed = the minimum over the ranks; the data collective runs only if that is >= 0 (the camera also skips it on 0 =
+// "some rank has no acceleration structure").  Return: the rank's own error if it has one, RTF_ERR_CUDA naming the
+// situation if only another rank failed, else RTF_OK.  The word lives in d_small, reserved when the communicator is formed,
+// so this step itself allocates nothing.  Cost: one host round trip per sharded call (tens of microseconds).
+// Not covered: a rank whose device has a sticky CUDA error cannot enqueue the agreement either; its NCCL call fails, the
+// communicator is aborted locally (ncclCommAbort) and the other ranks need NCCL's own asynchronous error handling.
+static int agree(rtf_ctx* ctx, int local, int* agreed) {
+  *agreed = local;
+  if (ctx->nranks <= 1 || !ctx->comm) return local < 0 ? local : RTF_OK;
+  const std::string mine = local < 0 ? std::string(rtf_last_error()) : std::string();
+  int32_t* d_word = reinterpret_cast<int32_t*>(ctx->d_small.as<char>() + 512);
+  int32_t word = local;
+  cudaError_t e = ctx->d_small.cap >= 1024 ? cudaMemcpyAsync(d_word, &word, 4, cudaMemcpyHostToDevice, ctx->stream)
+                                           : cudaErrorInvalidValue;
+  ncclResult_t r = ncclSuccess;
+  if (e == cudaSuccess) r = ncclAllReduce(d_word, d_word, 1, ncclInt32, ncclMin, comm_of(ctx), ctx->stream);
+  if (e == cudaSuccess && r == ncclSuccess) e = cudaMemcpyAsync(&word, d_word, 4, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && r == ncclSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess || r != ncclSuccess) {
+    if (ctx->own_comm) ncclCommAbort(comm_of(ctx));  // this rank cannot take part any more: do not leave a half-entered collective
+    ctx->comm = nullptr, ctx->own_comm = false;
+    if (local < 0) {
+      set_error(mine);
+      return local;
+    }
+    return e != cudaSuccess ? cuda_fail(e, "agreement before the collective", __FILE__, __LINE__)
+                            : nccl_fail(r, "agreement before the collective", __LINE__);
+  }
+  *agreed = word;
+  if (local < 0) {
+    set_error(mine);
+    return local;
+  }
+  if (word < 0) {
+    set_error("another rank failed before the collective (status " + std::to_string(word) + "); the job was abandoned on every rank");
+    return RTF_ERR_CUDA;
+  }
+  return RTF_OK;
+}
+
+// The part of a sharded illumination job that runs before its collective (fallible per rank).
+static int illum_sharded_compute(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push, int front,
+                                 int back, int mode, float* d_out6) {
   if (!ctx->ready) {
     set_error("no acceleration structure (call rtf_commit)");
     return RTF_ERR_NOT_READY;
   }
+  if (ctx->rng == RTF_RNG_REFERENCE_LCG) {  // as the sharded camera: the reference's sequential stream does not shard
+    set_error("option rng = RTF_RNG_REFERENCE_LCG is a single-context verification mode: the sharded illumination entry points refuse it");
+    return RTF_ERR_INVALID;
+  }
   const uint64_t n = ctx->n_tris;
   const int faces = (front ? 1 : 0) + (back ? 1 : 0);
   int rc;
-  phase_mark(ctx, 0);
   if (mode == RTF_SHARD_SAMPLES) {
     RTF_CUDA(cudaMemsetAsync(d_out6, 0, 24 * n, ctx->stream));
     uint64_t s0, s1;
     shard_range((uint64_t)rp->samples, ctx->nranks, ctx->rank, &s0, &s1);
     if (s1 > s0)
       if ((rc = illum_mesh_device(ctx, env, rp, seed, push, front, back, 0, n, (int)s0, (int)s1, d_out6, nullptr, 0))) return rc;
-    phase_mark(ctx, 1);
-    if (ctx->nranks > 1) RTF_NCCL(ncclAllReduce(d_out6, d_out6, 6 * n, ncclFloat, ncclSum, comm_of(ctx), ctx->stream));
-    phase_mark(ctx, 2);
-    if ((rc = illum_finalize_device(ctx, d_out6, n, faces, rp->samples, nullptr))) return rc;
   } else if (mode == RTF_SHARD_TRIANGLES) {
     uint64_t t0, t1;
     shard_range(n, ctx->nranks, ctx->rank, &t0, &t1);
@@ -94,12 +138,30 @@ int illum_sharded_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* 
         return rc;
       if ((rc = illum_finalize_device(ctx, d_out6 + 6 * t0, t1 - t0, faces, rp->samples, nullptr))) return rc;
     }
-    phase_mark(ctx, 1);
-    if ((rc = gather_ranges(ctx, d_out6, n, 24))) return rc;
-    phase_mark(ctx, 2);
   } else {
     set_error("mode must be RTF_SHARD_SAMPLES or RTF_SHARD_TRIANGLES");
     return RTF_ERR_INVALID;
+  }
+  return RTF_OK;
+}
+
+// pre_rc: status of the caller's own fallible preparation (its output buffer); non-zero skips the compute part, but the
+// rank still takes part in the agreement, so that the others abandon the job instead of waiting for it.
+int illum_sharded_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push, int front,
+                         int back, int mode, float* d_out6, int pre_rc) {
+  phase_mark(ctx, 0);
+  int rc = pre_rc ? pre_rc : illum_sharded_compute(ctx, env, rp, seed, push, front, back, mode, d_out6);
+  phase_mark(ctx, 1);
+  int agreed;
+  if ((rc = agree(ctx, rc, &agreed))) return rc;
+  const uint64_t n = ctx->n_tris;
+  if (mode == RTF_SHARD_SAMPLES) {
+    if (ctx->nranks > 1) RTF_NCCL(ncclAllReduce(d_out6, d_out6, 6 * n, ncclFloat, ncclSum, comm_of(ctx), ctx->stream));
+    phase_mark(ctx, 2);
+    if ((rc = illum_finalize_device(ctx, d_out6, n, (front ? 1 : 0) + (back ? 1 : 0), rp->samples, nullptr))) return rc;
+  } else {
+    if ((rc = gather_ranges(ctx, d_out6, n, 24))) return rc;
+    phase_mark(ctx, 2);
   }
   phase_mark(ctx, 3);
   ctx->phase_valid = true;
@@ -134,8 +196,13 @@ int scan_grid_sharded_device(rtf_ctx* ctx, const rtf_scan_grid* grid, int gather
   if (block_rays) *block_rays = 1ull << shift;
   if (n_blocks) *n_blocks = nb;
   phase_mark(ctx, 0);
-  if ((rc = scan_grid_interleaved_device(ctx, grid, ctx->nranks, ctx->rank, true, d_t, d_prim, d_inst))) return rc;
+  rc = scan_grid_interleaved_device(ctx, grid, ctx->nranks, ctx->rank, true, d_t, d_prim, d_inst);
   phase_mark(ctx, 1);
+  if (gather) {  // the only collective of the LiDAR path; without it a rank's failure is its own
+    int agreed;
+    rc = agree(ctx, rc, &agreed);
+  }
+  if (rc) return rc;
   if (gather) {
     if (d_t && (rc = gather_blocks(ctx, d_t, total, shift, nb, 4))) return rc;
     if (d_prim && (rc = gather_blocks(ctx, d_prim, total, shift, nb, 4))) return rc;
@@ -155,14 +222,23 @@ static int band_rows_for(int height, int nranks) {
 }
 
 int render_camera_sharded(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, int outputs_mask) {
-  if (!env || !cam || !rp) return RTF_ERR_INVALID;
+  if (!env || !cam || !rp) {  // no agreement possible without a camera to size the bands: argument errors are the caller's, on every rank
+    set_error("rtf_render_camera_sharded: null environment, camera or ray properties");
+    return RTF_ERR_INVALID;
+  }
   const int h = cam->props.height, w = cam->props.width;
   const int br = band_rows_for(h, ctx->nranks);
   const int n_bands = h > 0 ? (h + br - 1) / br : 0;
   phase_mark(ctx, 0);
-  const int ok = render_camera_interleaved(ctx, env, cam, rp, br, ctx->nranks, ctx->rank);
-  if (ok < 0) return ok;
+  int ok = render_camera_interleaved(ctx, env, cam, rp, br, ctx->nranks, ctx->rank);
   phase_mark(ctx, 1);
+  if (ctx->nranks > 1) {  // the frame is gathered only if every rank rendered its bands (1); 0 on any rank: nobody gathers
+    int agreed;
+    const int rc = agree(ctx, ok, &agreed);
+    if (rc) return rc;
+    if (agreed == 0) ok = 0;
+  }
+  if (ok < 0) return ok;
   if (ctx->nranks > 1 && ok == 1 && w > 0) {
     float* bufs[3] = {cam->color.as<float>(), cam->normal.as<float>(), cam->albedo.as<float>()};
     for (int which = 0; which < 3; which++) {
@@ -216,13 +292,18 @@ int rtf_comm_init_rank(rtf_ctx* ctx, int nranks, int rank, const void* unique_id
     set_error("rtf_comm_init_rank: the context already has a communicator");
     return RTF_ERR_INVALID;
   }
-  ctx->nranks = nranks, ctx->rank = rank;
-  if (nranks == 1) return RTF_OK;
+  if (nranks == 1) {
+    ctx->nranks = 1, ctx->rank = 0;
+    return RTF_OK;
+  }
+  int rc;
+  if ((rc = ctx->d_small.reserve(1024))) return rc;  // reduce values + the agreement word: nothing to allocate later
   ncclUniqueId id;
   memcpy(&id, unique_id, sizeof(id));
   ncclComm_t c = nullptr;
-  RTF_NCCL(ncclCommInitRank(&c, nranks, id, rank));
+  RTF_NCCL(ncclCommInitRank(&c, nranks, id, rank));  // on failure the context stays a single-rank one
   ctx->comm = c, ctx->own_comm = true;
+  ctx->nranks = nranks, ctx->rank = rank;
   return RTF_OK;
 }
 int rtf_comm_destroy(rtf_ctx* ctx) {
@@ -266,16 +347,15 @@ int rtf_estimate_illumination_mesh_sharded_device(rtf_ctx* ctx, const rtf_env* e
                                                   float push, int front, int back, int mode, float* dev_out6) {
   CHECK_CTX(ctx);
   if (!env || !rp || !dev_out6) return RTF_ERR_INVALID;
-  return illum_sharded_device(ctx, env, rp, seed, push, front, back, mode, dev_out6);
+  return illum_sharded_device(ctx, env, rp, seed, push, front, back, mode, dev_out6, RTF_OK);
 }
 int rtf_estimate_illumination_mesh_sharded(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push,
                                            int front, int back, int mode, float* out6) {
   CHECK_CTX(ctx);
   if (!env || !rp || !out6) return RTF_ERR_INVALID;
   const uint64_t n = ctx->n_tris;
-  int rc;
-  if ((rc = ctx->d_shard_out.reserve(24 * (n ? n : 1)))) return rc;
-  if ((rc = illum_sharded_device(ctx, env, rp, seed, push, front, back, mode, ctx->d_shard_out.as<float>()))) return rc;
+  int rc = ctx->d_shard_out.reserve(24 * (n ? n : 1));  // may fail on this rank alone: the others learn of it in the agreement
+  if ((rc = illum_sharded_device(ctx, env, rp, seed, push, front, back, mode, ctx->d_shard_out.as<float>(), rc))) return rc;
   RTF_CUDA(cudaMemcpyAsync(out6, ctx->d_shard_out.p, 24 * n, cudaMemcpyDeviceToHost, ctx->stream));
   RTF_CUDA(cudaStreamSynchronize(ctx->stream));
   return RTF_OK;
@@ -345,11 +425,13 @@ static int run_all(rtf_multi* m, F fn) {
     for (int r = 0; r < n; r++) th.emplace_back(body, r);
     for (auto& t : th) t.join();
   }
-  for (int r = 0; r < n; r++)
-    if (rc[r] < 0) {
-      set_error("device " + std::to_string(m->ctx[r]->device) + ": " + err[r]);
-      return rc[r];
-    }
+  // report the rank that failed on its own account, not one that only heard of it in the agreement step
+  for (int pass = 0; pass < 2; pass++)
+    for (int r = 0; r < n; r++)
+      if (rc[r] < 0 && (pass == 1 || err[r].rfind("another rank failed", 0) != 0)) {
+        set_error("device " + std::to_string(m->ctx[r]->device) + ": " + err[r]);
+        return rc[r];
+      }
   return rc[0];
 }
 }  // namespace rtf
@@ -378,6 +460,11 @@ int rtf_create_multi(const int* devices, int n, rtf_multi** out) {
     }
     c->rank = r, c->nranks = n;
     m->ctx.push_back(c);
+    if (n > 1 && (rc = c->d_small.reserve(1024))) {  // reduce values + the agreement word
+      for (rtf_ctx* x : m->ctx) rtf_destroy(x);
+      delete m;
+      return rc;
+    }
   }
   if (n > 1) {
     std::vector<ncclComm_t> comms(n);
@@ -454,9 +541,8 @@ int rtf_multi_estimate_illumination_mesh(rtf_multi* m, const rtf_env* env, const
   return run_all(m, [&](int r, rtf_ctx* c) -> int {
     cudaSetDevice(c->device);
     const uint64_t n = c->n_tris;
-    int rc;
-    if ((rc = c->d_shard_out.reserve(24 * (n ? n : 1)))) return rc;
-    if ((rc = illum_sharded_device(c, env, rp, seed, push, front, back, mode, c->d_shard_out.as<float>()))) return rc;
+    int rc = c->d_shard_out.reserve(24 * (n ? n : 1));
+    if ((rc = illum_sharded_device(c, env, rp, seed, push, front, back, mode, c->d_shard_out.as<float>(), rc))) return rc;
     if (r == 0) RTF_CUDA(cudaMemcpyAsync(out6, c->d_shard_out.p, 24 * n, cudaMemcpyDeviceToHost, c->stream));
     RTF_CUDA(cudaStreamSynchronize(c->stream));
     return RTF_OK;

@@ -280,7 +280,7 @@ int flux_mesh_device(rtf_ctx* ctx, const float* d_energy6, uint64_t tri_begin, u
 // multi.cu
 void shard_range(uint64_t n, int nranks, int rank, uint64_t* b, uint64_t* e);
 int illum_sharded_device(rtf_ctx* ctx, const rtf_env* env, const rtf_ray_props* rp, uint32_t seed, float push, int front,
-                         int back, int mode, float* d_out6);
+                         int back, int mode, float* d_out6, int pre_rc);
 int render_camera_sharded(rtf_ctx* ctx, const rtf_env* env, rtf_camera* cam, const rtf_ray_props* rp, int outputs_mask);
 // build.cu
 int build_bvh(rtf_ctx* ctx, int morton_bits);

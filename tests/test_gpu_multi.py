@@ -66,3 +66,42 @@ def test_one_process_per_gpu_sharded(tmp_path):
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert "SHARDED OK" in out.stdout
+
+
+_ONE_RANK_FAILS = r"""
+import numpy as np
+from raytracerfacility_b200 import module as mod, scenes, structs as S
+sd = scenes.sorghum_scene(1)
+mrt = mod.MultiRayTracer([0, 1])
+mrt.ctx(0).load_scene(sd, 63)          # device 1 never commits: its part of every job fails before the collective
+env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=2, samples=8)
+for mode in (0, 1):
+    try:
+        mrt.estimate_illumination_mesh(env, rp, 11, mode=mode)
+        raise SystemExit("no error raised")
+    except mod.RtfError as e:
+        assert e.code == mod.ERR_NOT_READY and "device 1" in str(e), str(e)
+cam = mrt.create_camera()
+cam.resize(64, 48)
+cam.set((0.0, 1.0, 4.0))
+assert mrt.render_to_camera(env, cam, rp, outputs_mask=7) is False   # the reference's "no acceleration structure" answer
+mrt.ctx(1).load_scene(sd, 63)          # the communicator survived: the same calls now work
+a = mrt.estimate_illumination_mesh(env, rp, 11, mode=1)
+one = mod.RayTracer(0)
+one.load_scene(sd, 63)
+b = one.estimate_illumination_mesh(env, rp, seed=11, push=1e-3)
+assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+assert mrt.render_to_camera(env, cam, rp, outputs_mask=7) is True
+print("AGREEMENT OK")
+"""
+
+
+def test_one_rank_failing_does_not_hang_the_others():
+    """A rank that fails before the job's collective (here: device 1 has no committed scene) must make the call return
+    an error on every rank instead of leaving the others inside ncclAllReduce / ncclBroadcast.  Runs in a child process
+    under a timeout, so a regression shows as a failure, not as a hung suite."""
+    if n_gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = subprocess.run([sys.executable, "-c", _ONE_RANK_FAILS], capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert "AGREEMENT OK" in out.stdout
