@@ -341,12 +341,37 @@ def entry_point_e2e(rt, torch, S, world, barrier, max_over_ranks):
     return res
 
 
-def run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, parity_on, timed, sum_over_ranks, peak, per_rank):
+def run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, parity_on, timed, sum_over_ranks, peak, per_rank,
+                l2_peak=None):
     """BASELINE.json's five configurations at full size through the sharded entry points of the library."""
     res = {}
     sub = None
     if parity_on:
         from oracle import subsample as sub
+
+    def leg_roofline(par, rays, ms, stream_bytes, trace_ms=None, gpus=world):
+        """Roofline of a whole leg from SURVEY 8(d)'s per-ray figure: algorithmic bytes per ray = the ray / hit streams
+        (48 B for queue rays; 12 B of results for LiDAR rays, which are generated in registers) + 80 B x node visits +
+        48 B x triangle tests.  The visit means are the oracle's over the parity sub-sample (the GPU's traversal order is
+        the oracle's: visit counts are checked equal on M1).  rays = the rays the GPUs actually traced, all ranks;
+        achieved = those bytes / the leg's device time (generation, shading and reduction included), against the measured
+        HBM peak x GPUs.  A BVH that fits the L2 makes the L2 the honest bound: both fractions are given.  trace_only =
+        the same bytes over rank 0's traversal-kernel time alone (its share of the rays)."""
+        n_node, n_tri = par["mean_nodes_per_ray"], par["mean_tris_per_ray"]
+        bpr = stream_bytes + NODE_BYTES * n_node + TRI_BYTES * n_tri
+        ach = bpr * rays / (ms * 1e-3) / 1e9
+        bvh_mb = (rt.debug_bytes(S.DBG_WIDE_NODES) + rt.debug_bytes(S.DBG_WIDE_TRIS)) / 1e6
+        r = {"bound": "l2" if (l2_peak and bvh_mb <= 96.0) else "hbm", "achieved": ach, "peak": peak * gpus, "unit": "GB/s",
+             "frac": ach / (peak * gpus), "alg_bytes_per_ray": bpr, "rays": rays, "gpus": gpus, "mean_nodes_per_ray": n_node,
+             "mean_tris_per_ray": n_tri, "bvh_mb": bvh_mb, "time": "whole leg (all kernels of the job)",
+             "visit_counts": "oracle, parity sub-sample"}
+        if l2_peak:
+            r["frac_of_l2"] = ach / (l2_peak * gpus)
+        if trace_ms:
+            r["trace_only"] = {"kernel": "k_trace_queue<0> / k_trace_rays (rank 0)", "ms": trace_ms,
+                               "achieved": bpr * (rays / gpus) / (trace_ms * 1e-3) / 1e9,
+                               "frac": bpr * (rays / gpus) / (trace_ms * 1e-3) / 1e9 / peak}
+        return r
 
     def load(cfg):
         rt.set_option("brdf", cfg.brdf)
@@ -403,8 +428,9 @@ def run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, par
             d["parity"] = dict(par, oracle_build_s=bs)
             d["cpu_baseline"] = {"value": par["cpu_triangle_samples_per_s"], "unit": "triangle-samples/s",
                                  "cores": par["cpu_threads"], "kind": "port", "sample": par["sample"]}
-            # algorithmic bytes per triangle-sample: mean rays per path x bytes per ray is not known without
-            # visit counters of the shading rays; the rate against the CPU port is what this leg reports
+            d["roofline"] = leg_roofline(par, rays, ms, RAY_BYTES + HIT_BYTES, phases.get("trace_ms"))
+            d["roofline"]["alg_bytes_per_triangle_sample"] = d["roofline"]["alg_bytes_per_ray"] * par["mean_rays_per_path"]
+            d["parity"]["t16_flux_and_probes"] = "restatement-pinned (TriangleIlluminationEstimator.cpp needs UniEngine's ECS: not compilable here)"
         box.clear()
         return d
 
@@ -436,6 +462,7 @@ def run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, par
             d["parity"] = dict(par, oracle_build_s=bs)
             d["cpu_baseline"] = {"value": par["cpu_Mpaths_per_s"], "unit": "Mpaths/s", "cores": par["cpu_threads"],
                                  "kind": "port", "sample": par["sample"]}
+            d["roofline"] = leg_roofline(par, rays, ms, RAY_BYTES + HIT_BYTES, phases.get("trace_ms"), world if sharded else 1)
         cam.destroy()
         return d
 
@@ -468,12 +495,21 @@ def run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, par
              "Mrays_per_s": total / ms / 1e3, "ms_incl_d2h": ms2, "Mrays_per_s_incl_d2h": total / ms2 / 1e3,
              "d2h_bytes_per_gpu": n_local * 8, "hit_fraction": hits / total, "phases_ms_rank0": phases,
              "trace_ms_per_rank": trace_ms_ranks, "timed_runs": reps, **info}
+        # parity over EVERY rank's blocks: one more (untimed) scan with the in-library gather, so that rank 0 holds the whole
+        # grid, then every 128-th ray of it against ONE oracle call (about 8e5 rays: the same sample at any GPU count, and
+        # long enough for the CPU rate to be tracing rather than thread start-up)
+        STRIDE = 128
+        tg, pg, _ = drt.scan_grid(cfg.grid, gather=True)
+        samp_t = tg.reshape(-1)[:total][::STRIDE].contiguous().cpu().numpy()
+        samp_p = pg.reshape(-1)[:total][::STRIDE].contiguous().cpu().numpy()
+        del tg, pg
         if sub is not None:
             osc, bs = sub.build(cfg)
-            par = sub.lidar_blocks(osc, cfg, host_t.numpy(), host_p.numpy(), starts, block, 1024)
-            d["parity"] = dict(par, oracle_build_s=bs, rank0_blocks=len(starts))
+            par = sub.lidar(osc, cfg, samp_t, samp_p, STRIDE, strided=True)
+            d["parity"] = dict(par, oracle_build_s=bs, ranks_checked=world, gathered_by="rtf_scan_grid_trace_sharded_device(gather=1)")
             d["cpu_baseline"] = {"value": par["cpu_Mrays_per_s"], "unit": "Mrays/s", "cores": par["cpu_threads"], "kind": "port",
                                  "sample": par["sample"]}
+            d["roofline"] = leg_roofline(par, float(total), ms, 12, max(trace_ms_ranks))
         box.clear()
         return d
 
@@ -736,11 +772,23 @@ def main():
         want = [c for c in args.configs.split(",") if c]
         configs.clear_scene(rt, sd)
         out["configs"] = run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, parity_on, timed,
-                                     sum_over_ranks, peak, per_rank)
+                                     sum_over_ranks, peak, per_rank, l2_peak)
         c3 = out["configs"].get("C3")
         if c3:  # M2 of BASELINE.json, on its own configuration
             out["illum"] = {"metric": "illum triangle-samples/s", "value": c3["triangle_samples_per_s"], "ms": c3["ms"],
-                            "scaling": "strong", "config": c3["what"], "Mrays/s": c3["Mrays_per_s"]}
+                            "scaling": "strong", "config": c3["what"], "Mrays/s": c3["Mrays_per_s"],
+                            "roofline": c3.get("roofline")}
+        # the LAST key, compact: what a 1500-character tail of this line still shows — per leg device ms, fraction of the
+        # HBM roofline (whole leg), parity verdict, in-library collective ms (N > 1)
+        out["configs_summary"] = {
+            k: {"ms": round(v["ms"], 3), "frac": round(v["roofline"]["frac"], 3) if v.get("roofline") else None,
+                "ok": v.get("parity", {}).get("ok"),
+                "coll_ms": round(v.get("phases_ms_rank0", {}).get("collective_ms", 0.0), 3) if world > 1 else None}
+            for k, v in out["configs"].items()}
+        out["configs_summary"]["M1"] = {"Mrays_s": round(value, 1), "frac": round(roofline["frac"], 3),
+                                        "ok": out.get("parity", {}).get("hits_bit_exact_on_sample")}
+        if c3:
+            out["configs_summary"]["M2"] = {"Mtri_samples_s": round(c3["triangle_samples_per_s"] / 1e6, 1), "n_gpus": world}
     if rank == 0:
         emit(out)
     rt.destroy()

@@ -9,7 +9,9 @@
 //   flux_*          = TriangleIlluminationEstimator::SampleLightProbeGroup (:84-92) with
 //                     IlluminationSampler::GetArea (RayTracer.hpp:204-210); the sum runs in double over the fixed
 //                     tree documented in include/rtf/rtf.h (the reference adds floats serially).
-// Parity unpinned by the reference (it has no tests); pinned by closed forms in tests/test_oracle_prebake.py.
+// bake_instanced / bake_skinned are pinned by the reference's own two kernels compiled unmodified (oracle/_ref/libprebake_ref.so,
+// tests/golden/prebake_ref.npz, byte-equal).  make_probes / flux_*: parity unpinned by the reference (it has no tests and
+// TriangleIlluminationEstimator.cpp does not compile here); pinned by closed forms in tests/test_oracle_prebake.py.
 #pragma once
 #include <vector>
 

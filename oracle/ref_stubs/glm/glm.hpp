@@ -115,6 +115,16 @@ struct mat3x3 {
   const vec3& operator[](int i) const { return c[i]; }
 };
 typedef mat3x3 mat3;
+// mat4 * scalar and mat4 += mat4, glm/detail/type_mat4x4.inl: column by column (CopySkinnedVerticesKernel's bone blend)
+inline mat4 operator*(const mat4& m, float s) {
+  mat4 r;
+  r[0] = m[0] * s, r[1] = m[1] * s, r[2] = m[2] * s, r[3] = m[3] * s;
+  return r;
+}
+inline mat4& operator+=(mat4& a, const mat4& b) {
+  a[0] = a[0] + b[0], a[1] = a[1] + b[1], a[2] = a[2] + b[2], a[3] = a[3] + b[3];
+  return a;
+}
 // mat4 * vec4, glm/detail/type_mat4x4.inl: (m[0] * x + m[1] * y) + (m[2] * z + m[3] * w)
 inline vec4 operator*(const mat4& m, const vec4& v) { return (m[0] * v.x + m[1] * v.y) + (m[2] * v.z + m[3] * v.w); }
 inline bool operator==(const vec3& a, const vec3& b) { return a.x == b.x && a.y == b.y && a.z == b.z; }

@@ -67,10 +67,26 @@ def illumination(osc, cfg, gpu_out6, stride, seed, push, nthreads=None):
             "mean_rays_per_path": float(st.rays) / max(1, int(st.paths)), **_visits(st)}
 
 
-def lidar(osc, cfg, gpu_t, gpu_prim, stride, ray_begin=0, nthreads=None):
-    """gpu_t / gpu_prim: the scan's arrays from ray `ray_begin` on.  Bit-exact distances and primitive ids."""
+def lidar(osc, cfg, gpu_t, gpu_prim, stride, ray_begin=0, nthreads=None, strided=False):
+    """gpu_t / gpu_prim: the scan's arrays from ray `ray_begin` on.  Bit-exact distances and primitive ids.
+    strided=True: the arrays already hold rays 0, stride, 2*stride, ... of the WHOLE grid only (the caller cut the sample
+    on the device) — ONE oracle call over a sample that does not depend on how the scan was sharded, which is also what
+    the CPU rate is timed on (per-block calls of a few hundred rays each time thread start-up, not tracing)."""
     nthreads = threads() if nthreads is None else nthreads
     total = int(orc.lib().orc_scan_grid_count(ctypes.byref(cfg.grid)))
+    if strided:
+        assert ray_begin == 0
+        t0 = time.perf_counter()
+        t, prim, inst, st = osc.scan_grid(cfg.grid, ray_begin=0, ray_end=total, stride=stride, nthreads=nthreads)
+        dt = time.perf_counter() - t0
+        gt, gp = np.asarray(gpu_t).view(np.uint32), np.asarray(gpu_prim).view(np.uint32)
+        assert len(gt) == len(t), (len(gt), len(t))
+        same_t = bool(np.array_equal(gt, t.view(np.uint32)))
+        same_p = bool(np.array_equal(gp, prim.view(np.uint32)))
+        return {"ok": same_t and same_p, "sample": f"every {stride}-th ray of the whole grid ({len(t)} rays, one oracle call)",
+                "prim_ids_bit_exact": same_p, "distances_bit_exact": same_t,
+                "hit_fraction_on_sample": float((prim != 0xFFFFFFFF).mean()) if len(prim) else 0.0, "cpu_s": dt,
+                "cpu_threads": nthreads, "cpu_Mrays_per_s": len(t) / dt / 1e6, **_visits(st)}
     n = len(gpu_t)
     first = (-ray_begin) % stride  # the oracle takes rays 0, stride, ... of the whole grid
     t0 = time.perf_counter()

@@ -522,6 +522,12 @@ class RayTracer:
         _check(lib().rtf_debug_read(self.h, int(what), _p(out), nbytes))
         return out
 
+    def debug_bytes(self, what):
+        """Size in bytes of a build-stage array without reading it back."""
+        nbytes = C.c_uint64()
+        _check(lib().rtf_debug_size(self.h, int(what), C.byref(nbytes)))
+        return int(nbytes.value)
+
     def debug_upload_bvh(self, nodes, tris, depth):
         nodes, tris = np.ascontiguousarray(nodes), np.ascontiguousarray(tris)
         _check(lib().rtf_debug_upload_bvh(self.h, _p(nodes), C.c_uint64(len(nodes)), _p(tris), C.c_uint64(len(tris)),

@@ -130,8 +130,19 @@ class DistributedRayTracer:
             out = torch.empty(n * 6, dtype=torch.float32, device=torch.device("cuda", rt.device))
             rt.estimate_illumination_mesh_sharded_device(env, ray_props, seed, push, front, back,
                                                          0 if mode == "sample" else 1, out.data_ptr())
-        torch.cuda.current_stream(out.device).wait_stream(self.stream)
+        self._hand_over(out)
         return out.view(n, 6)
+
+    def _hand_over(self, *tensors):
+        """Results were allocated and written on self.stream and are about to be read on the caller's stream: make that
+        stream wait for the job, and tell the caching allocator about the second stream (record_stream) so that a block the
+        caller drops is not handed to the next job on self.stream while the caller's stream is still reading it."""
+        import torch
+        cur = torch.cuda.current_stream(tensors[0].device)
+        cur.wait_stream(self.stream)
+        if cur != self.stream:
+            for x in tensors:
+                x.record_stream(cur)
 
     def scan_grid(self, grid, gather=False):
         """Each rank traces its INTERLEAVED blocks of the ray grid (block k belongs to rank k mod world) into full-size
@@ -147,7 +158,7 @@ class DistributedRayTracer:
             t = torch.empty(total + (1 << 24), dtype=torch.float32, device=dev)
             prim = torch.empty(total + (1 << 24), dtype=torch.int32, device=dev)
             block, n_blocks = rt.scan_grid_sharded_device(grid, gather, t.data_ptr(), prim.data_ptr())
-        torch.cuda.current_stream(dev).wait_stream(self.stream)
+        self._hand_over(t, prim)
         return t[:n_blocks * block].view(n_blocks, block), prim[:n_blocks * block].view(n_blocks, block), \
             slice(self.rank, None, self.world)
 

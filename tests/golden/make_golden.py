@@ -19,6 +19,10 @@
                    run through the REFERENCE's own illumination programs on the host (as programs_ref.npz) with two seeds:
                    the per-triangle energies of both runs.  Their difference is the Monte-Carlo noise of the reference's
                    own estimator, against which the GPU's (keyed Philox draws) is tested statistically.
+* prebake_ref.npz — outputs of the REFERENCE's own geometry pre-kernels (CopyVerticesInstancedKernel RayTracer.cu:1148-1175,
+                   CopySkinnedVerticesKernel :1194-1249, cut out of the reference file at build time and compiled unmodified
+                   into oracle/_ref/libprebake_ref.so over the glm stand-in) for the seeded inputs of prebake_ref_cases().
+                   Pins orc::bake_instanced / bake_skinned and, on the GPU, k_bake_instanced / k_bake_skinned.
 * btf_ref.npz    — outputs of the REFERENCE's own compressed-BTF evaluator (include/RayTracerFacility/MLVQ/*.cuh compiled
                    unmodified into oracle/_ref/libbtf_ref.so against oracle/ref_stubs).  Pins orc::btf_value_deg.
 * oracle_extra.npz — the same for the BSSRDF probe / irradiance, the instanced and skinned pre-kernels, light probes, flux.
@@ -90,6 +94,78 @@ def extra_cases():
 
 BTF_REF_VARIANTS = [dict(), dict(use_cos_beta=0), dict(hdr=1, hdr_value=2.5, multiplier=2.5), dict(code_btf_flag=1),
                     dict(gamma=1.0, tex_coord_multiplier=2.5, rows_offset=3, cols_offset=7)]
+
+
+def _rigid(seed, k, scale=True):
+    """Column-major 4x4: rotation about a hashed axis, hashed (non-uniform when `scale`) scale and translation."""
+    h = lambda d: float(scenes.hash_uniform(seed, np.array([k]), d)[0])  # noqa: E731
+    ax = np.array([h(0) - 0.5, h(1) - 0.5, h(2) - 0.5])
+    ax /= np.linalg.norm(ax)
+    a = 6.0 * h(3)
+    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
+    R = np.eye(3) + np.sin(a) * K + (1 - np.cos(a)) * (K @ K)
+    sc = np.diag([0.5 + h(4), 0.5 + h(5), 0.5 + h(6)]) if scale else np.eye(3)
+    m = np.eye(4)
+    m[:3, :3] = R @ sc
+    m[:3, 3] = [4 * h(7) - 2, 4 * h(8) - 2, 4 * h(9) - 2]
+    return m.T.astype(np.float32).reshape(16)
+
+
+def prebake_ref_cases():
+    """Seeded inputs of prebake_ref.npz: a 120-vertex soup mesh with non-trivial tangents, colours and paddings; 9 instance
+    matrices (identity first, then rotations with non-uniform scale) with colours; skinned vertices with 1..8 influences
+    (-1 = unused, in both quadruples), weights that sum to 1, and 6 bone matrices."""
+    sd = scenes.random_soup(40, seed=23, size=0.5)
+    v, t = sd.geometries[1]
+    v = v.copy()
+    n = len(v)
+    idx = np.arange(n)
+    v["tangent"] = np.stack([scenes.hash_uniform(31, idx, d) - 0.5 for d in range(3)], 1).astype(np.float32)
+    v["color"] = np.stack([scenes.hash_uniform(32, idx, d) for d in range(4)], 1).astype(np.float32)
+    v["tex_coord"] = np.stack([scenes.hash_uniform(33, idx, d) * 3 - 1 for d in range(2)], 1).astype(np.float32)
+    v["position_padding"] = scenes.hash_uniform(34, idx, 0).astype(np.float32)
+    v["normal_padding"] = scenes.hash_uniform(34, idx, 1).astype(np.float32)
+    v["tangent_padding"] = scenes.hash_uniform(34, idx, 2).astype(np.float32)
+    v["tex_coord_padding"] = np.stack([scenes.hash_uniform(34, idx, 3 + d) for d in range(2)], 1).astype(np.float32)
+    mats = np.stack([np.eye(4, dtype=np.float32).reshape(16)] + [_rigid(41, k) for k in range(8)])
+    cols = np.stack([scenes.hash_uniform(42, np.arange(9), d) for d in range(4)], 1).astype(np.float32)
+    bones = np.stack([_rigid(43, k, scale=(k % 2 == 1)) for k in range(6)])
+    sv = np.zeros(n, dtype=S.SKINNED_VERTEX_DTYPE)
+    sv["v"] = v
+    ids = np.full((n, 8), -1, dtype=np.int32)
+    w = np.zeros((n, 8), dtype=np.float32)
+    for i in range(n):
+        k = 1 + i % 8                                  # number of influences
+        slots = [0] + sorted(((np.arange(1, 8) * (i + 3)) % 7 + 1)[:k - 1].tolist())  # slot 0 always (the kernel reads it unconditionally)
+        slots = sorted(set(slots))
+        raw = np.array([scenes.hash_uniform(44, np.array([i]), s)[0] + 0.05 for s in slots])
+        raw /= raw.sum()
+        for s_, r_ in zip(slots, raw):
+            ids[i, s_] = int(scenes.hash_uniform(45, np.array([i]), s_)[0] * 6) % 6
+            w[i, s_] = np.float32(r_)
+    sv["bone_id"], sv["bone_id2"] = ids[:, :4], ids[:, 4:]
+    sv["weight"], sv["weight2"] = w[:, :4], w[:, 4:]
+    return dict(vertices=v, triangles=t, matrices=mats, colors=cols, skinned=sv, bones=bones)
+
+
+def prebake_ref_run(c):
+    """The reference's two kernels on prebake_ref_cases() through oracle/_ref/libprebake_ref.so."""
+    ref = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libprebake_ref.so"))
+    v, mats, cols, sv, bones = c["vertices"], c["matrices"], c["colors"], c["skinned"], c["bones"]
+    ptr = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    n, ni = len(v), len(mats)
+    inst_v = np.zeros(n * ni, dtype=S.VERTEX_DTYPE)
+    inst_p = np.zeros((n * ni, 3), dtype=np.float32)
+    ref.ref_copy_vertices_instanced(C.c_int(ni), C.c_int(n), ptr(mats), ptr(cols), ptr(v), ptr(inst_p), ptr(inst_v))
+    skin_v = np.zeros(n, dtype=S.VERTEX_DTYPE)
+    skin_p = np.zeros((n, 3), dtype=np.float32)
+    ref.ref_copy_skinned_vertices(C.c_int(n), ptr(sv), ptr(bones), ptr(skin_p), ptr(skin_v))
+    return dict(instanced_vertices=inst_v.view(np.uint8), instanced_positions=inst_p.view(np.uint32),
+                skinned_vertices=skin_v.view(np.uint8), skinned_positions=skin_p.view(np.uint32))
+
+
+def write_prebake_ref():
+    np.savez_compressed(os.path.join(HERE, "prebake_ref.npz"), **prebake_ref_run(prebake_ref_cases()))
 
 
 def btf_ref_cases():
@@ -268,6 +344,7 @@ def main():
                         camera_normal=nrm.view(np.uint32), camera_albedo=alb.view(np.uint32))
     write_extra()
     write_btf_ref()
+    write_prebake_ref()
     write_env_ref()
     write_programs_ref()
     write_c1_ref()

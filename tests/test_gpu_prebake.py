@@ -79,6 +79,26 @@ def test_skinned_geometry_bake(rt, orc, S, scenes):
         rt.set_geometry_skinned(3, sv, t, bones)
 
 
+def test_pre_kernels_equal_the_reference_kernels(rt):
+    """T20 on the GPU: k_bake_instanced / k_bake_skinned against tests/golden/prebake_ref.npz, the output of the reference's
+    own CopyVerticesInstancedKernel / CopySkinnedVerticesKernel (compiled unmodified, oracle/Makefile) — every byte."""
+    import os
+
+    from tests.golden import make_golden as G
+    g = np.load(os.path.join(G.HERE, "prebake_ref.npz"))
+    c = G.prebake_ref_cases()
+    v, t = c["vertices"], c["triangles"]
+    ni = len(c["matrices"])
+    rt.set_geometry_instanced(5, v, t, c["matrices"], c["colors"])
+    gv, gt = rt.read_baked_geometry(5, len(v) * ni, len(t) * ni)
+    assert gv.view(np.uint8).tobytes() == g["instanced_vertices"].tobytes(), "instanced bake differs from the reference kernel"
+    assert np.array_equal(gt, np.concatenate([t + k * len(v) for k in range(ni)]))
+    rt.set_geometry_skinned(6, c["skinned"], t, c["bones"])
+    sv, st = rt.read_baked_geometry(6, len(v), len(t))
+    assert sv.view(np.uint8).tobytes() == g["skinned_vertices"].tobytes(), "skinned bake differs from the reference kernel"
+    assert np.array_equal(st, t)
+
+
 def test_light_probes_and_flux(rt, orc, mod, S, scenes):
     sd = scenes.sorghum_scene(2)
     rt.load_scene(sd, 63)

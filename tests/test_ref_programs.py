@@ -123,6 +123,28 @@ def test_point_cloud_programs(orc, S, ref, oscs):
             assert live.tobytes() == want.tobytes(), sc
 
 
+def test_geometry_pre_kernels_equal_the_reference_kernels(orc):
+    """T20: orc::bake_instanced / bake_skinned against tests/golden/prebake_ref.npz = what the reference's own
+    CopyVerticesInstancedKernel (RayTracer.cu:1148-1175) and CopySkinnedVerticesKernel (:1194-1249) write for the seeded
+    inputs of make_golden.prebake_ref_cases(), compiled unmodified from a build-time extract (oracle/Makefile) over the glm
+    stand-in.  Every byte of every 80 B vertex: identity and scaled-rotation instances with instance colours in the
+    paddings, 1..8 bone influences in both quadruples.  Where oracle/_ref/libprebake_ref.so exists it is re-run too."""
+    g = np.load(os.path.join(GOLDEN, "prebake_ref.npz"))
+    c = G.prebake_ref_cases()
+    ov, ot = orc.bake_instanced(c["vertices"], c["triangles"], c["matrices"], c["colors"])
+    assert ov.view(np.uint8).tobytes() == g["instanced_vertices"].tobytes()
+    assert np.array_equal(ov["position"].view(np.uint32), g["instanced_positions"])  # the kernel's targetPositions array
+    sk = orc.bake_skinned(c["skinned"], c["bones"])
+    assert sk.view(np.uint8).tobytes() == g["skinned_vertices"].tobytes()
+    assert np.array_equal(sk["position"].view(np.uint32), g["skinned_positions"])
+    used = (c["skinned"]["bone_id"] != -1).sum(1) + (c["skinned"]["bone_id2"] != -1).sum(1)
+    assert set(used.tolist()) == set(range(1, 9))
+    if os.path.exists(os.path.join(G.ROOT, "oracle", "_ref", "libprebake_ref.so")):
+        live = G.prebake_ref_run(c)
+        for k in live:
+            assert np.array_equal(live[k], g[k]), k
+
+
 def c1_statistics(energy, rays, g):
     """BASELINE config 1 against the reference's own programs run with the reference's own LCG under two seeds (a, b):
     a different random stream must be statistically indistinguishable from them.  RMS per-triangle difference to run a

@@ -14,6 +14,7 @@ def main():
     ap.add_argument("--plants", type=int, default=50)
     ap.add_argument("--samples", type=int, default=64)
     ap.add_argument("--tris", type=int, default=0)
+    ap.add_argument("--tri-begin", type=int, default=0, help="first triangle of the probed range (profiling: a range in the middle of the field)")
     ap.add_argument("--batch-log2", type=int, default=0)
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--sort-rays", type=int, default=0, help="option sort_rays: sort bounce rays by (octant, origin cell)")
@@ -41,14 +42,15 @@ def main():
         print(f"oracle BVH: {len(_nodes)} nodes, {len(_tris)} triangle refs, depth {_o.depth}", flush=True)
         rt.debug_upload_bvh(_nodes, _tris, _o.depth)
     n = args.tris or rt.triangle_count
+    t0 = min(args.tri_begin, rt.triangle_count - n)
     env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=4, samples=args.samples)
     acc = torch.zeros(rt.triangle_count * 6, dtype=torch.float32, device=dev)
-    rt.estimate_illumination_mesh_device(env, rp, 0x5EED, 1e-3, True, True, 0, n, 0, rp.samples, acc.data_ptr())
+    rt.estimate_illumination_mesh_device(env, rp, 0x5EED, 1e-3, True, True, t0, t0 + n, 0, rp.samples, acc.data_ptr())
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     e0.record(stream)
     for _ in range(args.reps):
-        rt.estimate_illumination_mesh_device(env, rp, 0x5EED, 1e-3, True, True, 0, n, 0, rp.samples, acc.data_ptr())
+        rt.estimate_illumination_mesh_device(env, rp, 0x5EED, 1e-3, True, True, t0, t0 + n, 0, rp.samples, acc.data_ptr())
     e1.record(stream)
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / args.reps

@@ -44,10 +44,11 @@ def main():
     print("flux (static scratch):", d_out.cpu().numpy()[:4], rt.illumination_flux_mesh_device(d_e6.data_ptr(), 0, rt.triangle_count)[:4])
     # refit path: move an instance, commit with refit allowed
     rt.set_option("refit", 1)
-    g, m, x, comp = sd.instances[1]
-    x2 = x.copy()
-    x2.reshape(4, 4)[3, 0] += np.float32(0.05)
-    rt.set_instance(1, g, m, x2, comp)
+    ih = max(sd.instances)
+    g, m, x, comp = sd.instances[ih]
+    x2 = np.array(x, dtype=np.float32).copy()
+    x2.reshape(-1)[12] += np.float32(0.05)
+    rt.set_instance(ih, g, m, x2, comp)
     rt.build_ias(63)
     print("refit: commit stats", rt.commit_stats() if hasattr(rt, "commit_stats") else "-", flush=True)
     rt.trace_closest(rays[:4096])
