@@ -545,6 +545,54 @@ def run_configs(args, want, rt, drt, torch, S, configs, stream, rank, world, par
     return res
 
 
+def multi_gpu_parity(rt, drt, torch, S, scenes, configs, rank, world):
+    """N > 1 only: a C1-sized job through every sharded entry point AND through the plain single-context calls of the same
+    rank, compared on the device.  The equivalence tests of tests/test_gpu_multi.py need two GPUs and are skipped on a
+    one-GPU test box; this puts the same statement into the bench line.  Bars: triangle-sharded illumination, LiDAR and
+    camera bit-identical (every unit keeps its own RNG stream and arithmetic); sample-sharded illumination <= 1e-5 relative
+    (the all-reduce adds the ranks' partial sums in another order than one GPU adds its samples)."""
+    sd = scenes.sorghum_scene(1)
+    rt.load_scene(sd, 63)
+    env, rp = S.EnvironmentProperties(), S.RayProperties(bounces=3, samples=16)
+    one = torch.from_numpy(rt.estimate_illumination_mesh(env, rp, seed=configs.SEED, push=configs.PUSH)).to(drt.stream.device)
+    res = {}
+    tri = drt.estimate_illumination_mesh(env, rp, configs.SEED, configs.PUSH, mode="triangle")
+    res["illum_triangle_sharded_bit_identical"] = bool(torch.equal(tri.view(torch.int32), one.view(torch.int32)))
+    smp = drt.estimate_illumination_mesh(env, rp, configs.SEED, configs.PUSH, mode="sample")
+    rel = ((smp[:, :3] - one[:, :3]).abs() / one[:, :3].abs().clamp_min(1e-30)).max().item()
+    res["illum_sample_sharded_max_rel_err"] = rel
+    grid = scenes.lidar_grid(center=(0.0, 5.0, 0.0), size=(4.0, 4.0), distance=(0.004, 0.004))
+    total = rt.scan_grid_ray_count(grid)
+    t2d, p2d, _ = drt.scan_grid(grid, gather=True)
+    t1, p1, _ = rt.scan_grid(grid)
+    res["lidar_gathered_bit_identical"] = bool(
+        torch.equal(t2d.reshape(-1)[:total].view(torch.int32).cpu(), torch.from_numpy(t1.view(np.int32)))
+        and torch.equal(p2d.reshape(-1)[:total].cpu(), torch.from_numpy(p1.view(np.int32))))
+    res["lidar_rays"] = total
+    frames = []
+    for sharded in (True, False):
+        cam = rt.create_camera()
+        cam.resize(256, 144)
+        cam.props.accumulate = 0
+        cam.set(configs.CAMERA_POSITION, configs.CAMERA_ROTATION_WXYZ)
+        if sharded:
+            drt.render_to_camera(env, cam, rp, outputs=(S.OUT_COLOR, S.OUT_NORMAL, S.OUT_ALBEDO))
+        else:
+            rt.render_to_camera(env, cam, rp)
+        frames.append([cam.download(w) for w in (S.OUT_COLOR, S.OUT_NORMAL, S.OUT_ALBEDO)])
+        cam.destroy()
+    res["camera_sharded_bit_identical"] = bool(all(np.array_equal(a.view(np.uint32), b.view(np.uint32))
+                                                   for a, b in zip(frames[0], frames[1])))
+    ok = (res["illum_triangle_sharded_bit_identical"] and rel <= 1e-5 and res["lidar_gathered_bit_identical"]
+          and res["camera_sharded_bit_identical"])
+    # every rank's verdict counts: min over ranks
+    res["ok"] = bool(rt.comm_reduce([0.0 if ok else 1.0], "sum")[0] == 0.0)
+    res["ranks"] = world
+    res["job"] = "C1 scene (20 002 triangles): 16 samples x 3 bounces illumination, 10^6-ray LiDAR grid, 256x144 camera"
+    configs.clear_scene(rt, sd)
+    return res
+
+
 _JSON_FD = None
 
 
@@ -697,6 +745,30 @@ def main():
     e2e = world * n * args.steps / e2e_s / 1e6
     # which rank's host link is the slow one: every rank's own PCIe rate (48 B per ray both ways) and its first CPU core
     # (ranks pin themselves to their GPU's NUMA-local cores before allocating the pinned buffers: parallel.init_distributed)
+    # the ceiling of that call: the same pinned buffers, copy-only — rays up on one stream while hits come down on another
+    # (what the library's chunk pipeline overlaps), no tracing, all ranks at once (they share the host's memory and PCIe
+    # root complexes).  e2e as a fraction of it says whether the entry point or the host link is the limit.
+    cs_up, cs_dn = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    d_rays2, d_hits2 = torch.empty_like(rays), torch.zeros_like(hits)
+    h_hits2 = torch.empty((n, 4), dtype=torch.float32, pin_memory=True)  # its own landing buffer: h_hits holds the traced hits
+
+    def copy_only():
+        with torch.cuda.stream(cs_up):
+            d_rays2.copy_(h_rays, non_blocking=True)
+        with torch.cuda.stream(cs_dn):
+            h_hits2.copy_(d_hits2, non_blocking=True)
+    copy_only()
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        copy_only()
+    torch.cuda.synchronize()
+    copy_own_s = time.perf_counter() - t0
+    copy_s = max_over_ranks(copy_own_s)
+    ceiling = world * n * args.steps / copy_s / 1e6
+    ceiling_rank_gbs = [round(g, 2) for g in per_rank(n * 48 * args.steps / copy_own_s / 1e9)]
+    del d_rays2, d_hits2, h_hits2
     e2e_rank_gbs = [round(g, 2) for g in per_rank(n * 48 * args.steps / own_s / 1e9)]
     e2e_rank_core = [int(c) for c in per_rank(min(os.sched_getaffinity(0)))]
     assert np.array_equal(np_hits.view(np.uint32).reshape(-1, 4)[:4096], hits[:4096].cpu().numpy().view(np.uint32))
@@ -738,7 +810,10 @@ def main():
            "data": "synthetic", "config": headline_config(args, n_tris), "hit_rate": hit_rate,
            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 16,
                    "api": "rtf_trace_closest (host rays in, host hits out, pinned)",
-                   "pcie_gbs_per_rank": e2e_rank_gbs, "first_cpu_core_per_rank": e2e_rank_core},
+                   "pcie_gbs_per_rank": e2e_rank_gbs, "first_cpu_core_per_rank": e2e_rank_core,
+                   "host_ceiling": {"value": ceiling, "unit": UNIT, "frac": e2e / ceiling, "gbs_per_rank": ceiling_rank_gbs,
+                                    "what": "copy-only: the same pinned buffers, 32 B/ray up and 16 B/ray down concurrently on two "
+                                            "streams, no tracing, all ranks at once"}},
            "gpu_launches": launches, "clocks": clk, "roofline": roofline,
            "multi_gpu": "sharding + collectives inside librtf_b200.so (NCCL communicator of the library, csrc/multi.cu)",
            "build": dict(first_build, wall_s_incl_upload=build_wall), "rebuild": rebuild, "refit": refit}
@@ -789,6 +864,12 @@ def main():
                                         "ok": out.get("parity", {}).get("hits_bit_exact_on_sample")}
         if c3:
             out["configs_summary"]["M2"] = {"Mtri_samples_s": round(c3["triangle_samples_per_s"] / 1e6, 1), "n_gpus": world}
+    if not args.no_extras and world > 1:
+        out["multi_gpu_parity"] = multi_gpu_parity(rt, drt, torch, S, scenes, configs, rank, world)
+        cs = out.pop("configs_summary", None)
+        if cs is not None:  # keep the compact summary the last key, with the sharded-vs-one-context verdict in it
+            cs["multi_gpu_parity_ok"] = out["multi_gpu_parity"]["ok"]
+            out["configs_summary"] = cs
     if rank == 0:
         emit(out)
     rt.destroy()
